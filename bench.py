@@ -1,0 +1,510 @@
+#!/usr/bin/env python
+"""Benchmark of the filter/scan hot path (BASELINE.json metric: filter-scan rows/s and HBM GB/s).
+
+  python bench.py --gpus N --steps K --warmup W            our CUDA path
+  python bench.py --impl reference ...                     the reference's CPU algorithm (oracle port) on host cores
+
+Workload (BASELINE.json configs[1]): one int64 column of 1e9 rows per GPU,
+`col < k` with k chosen for 1 % / 50 % / 99 % selectivity, output = selection
+vector + compacted column.  One step = that three-filter sweep over the
+resident column.  Inputs (8 GB per GPU) are far larger than L2, so nothing is
+cached between launches.  Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+SELECTIVITIES = (0.01, 0.50, 0.99)
+SEED = 42
+METRIC = "filter_scan_rows_per_s"
+UNIT = "rows/s"
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json, device copy)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def filter_expr(s: float):
+    from queryengine_b200.ast import DataType, Function, col, fn
+    k = float(int(s * 2 ** 40))
+    return fn(Function.CMP_LT, col(0, DataType.INT64, "col"), k)
+
+
+def splitmix64(x: np.ndarray) -> np.ndarray:
+    with np.errstate(over="ignore"):
+        x = x + np.uint64(0x9E3779B97F4A7C15)
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        return x ^ (x >> np.uint64(31))
+
+
+def synthetic_column(n: int, offset: int = 0) -> np.ndarray:
+    """Same values as qe_table_generate(QE_GEN_UNIFORM_U40, seed 42) for rows offset..offset+n."""
+    i = np.arange(n, dtype=np.uint64) + np.uint64(offset)
+    return (splitmix64(np.uint64(SEED) ^ i) >> np.uint64(24)).astype(np.int64)
+
+
+# ------------------------------------------------------------------ clocks
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons of one GPU while the timed region runs."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                mask = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def __enter__(self):
+        if self.nv:
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thread:
+            self._thread.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------- CPU baseline legs
+
+def cpu_leg(sample_rows: int, threads: int, repeats: int = 1):
+    """The reference's row-at-a-time algorithm (oracle port) over a bounded sample of the same
+    workload.  Returns (rows/s over the three-filter sweep, seconds, kept counts)."""
+    from oracle_binding import OracleTable, timed_pipeline
+    from queryengine_b200.ast import DataType, col
+    vals = synthetic_column(sample_rows)
+    t = OracleTable([DataType.INT64], sample_rows)
+    t.set_column(0, vals)
+    best = None
+    kept = []
+    for _ in range(repeats):
+        secs = 0.0
+        kept = []
+        for s in SELECTIVITIES:
+            dt, rows, _ = timed_pipeline(t, [0], filter_expr(s), [col(0, DataType.INT64)], [], threads)
+            secs += dt
+            kept.append(rows)
+        best = secs if best is None else min(best, secs)
+    return len(SELECTIVITIES) * sample_rows / best, best, kept
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    sample = args.cpu_rows
+    cpu_leg(min(sample, 1_000_000), threads)                       # warm-up (page in the library)
+    vals, times = [], []
+    for _ in range(max(1, args.warmup)):
+        cpu_leg(sample, threads)
+    for _ in range(max(1, args.steps)):
+        v, secs, kept = cpu_leg(sample, threads)
+        vals.append(v)
+        times.append(secs)
+    value = float(np.mean(vals))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(np.mean(times)) * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.rows, args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{sample} rows of the same column, three-filter sweep per step; "
+                                   "oracle/qe_oracle.c (C restatement of the Kotlin evaluator; no JVM in this image), "
+                                   "row-range sharded over all host threads"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(rows: int, gpus: int):
+    return {"workload": "configs[1]: single int64 column, `col < k`, selectivity sweep 1%/50%/99%, "
+                        "output selection vector + compacted column",
+            "rows_per_gpu": rows, "selectivities": list(SELECTIVITIES), "seed": SEED,
+            "partitioning": f"row ranges, {gpus} partition(s), no data-path collective",
+            "cache": "inputs (8 B/row) larger than L2; no flush needed"}
+
+
+# ---------------------------------------------------------------- GPU arm
+
+def host_memory_available() -> int:
+    avail = None
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available
+    except Exception:
+        pass
+    for p in ("/sys/fs/cgroup/memory.max", "/sys/fs/cgroup/memory/memory.limit_in_bytes"):
+        try:
+            v = open(p).read().strip()
+            if v.isdigit():
+                used = 0
+                try:
+                    used = int(open(os.path.join(os.path.dirname(p), "memory.current")).read())
+                except Exception:
+                    pass
+                lim = int(v) - used
+                avail = lim if avail is None else min(avail, lim)
+        except Exception:
+            pass
+    return avail if avail is not None else 8 << 30
+
+
+class PinnedBuffer:
+    def __init__(self, nbytes: int):
+        from queryengine_b200 import capi
+        self.ptr = C.c_void_p()
+        capi.check(capi.lib().qe_host_alloc(nbytes, C.byref(self.ptr)))
+        self.nbytes = nbytes
+
+    def free(self):
+        from queryengine_b200 import capi
+        if self.ptr:
+            capi.lib().qe_host_free(self.ptr)
+            self.ptr = C.c_void_p()
+
+
+def timed_steps(torch, ctx, stream, fn_step, steps, dist, device):
+    """K steps bracketed by barrier + synchronize, CUDA events on the library's stream; max over ranks."""
+    ev0 = torch.cuda.Event(enable_timing=True)
+    ev1 = torch.cuda.Event(enable_timing=True)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ev0.record(stream)
+    for _ in range(steps):
+        fn_step()
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    ms = ev0.elapsed_time(ev1)
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms
+
+
+def extra_q6(ctx, torch, stream, rows, steps, warmup, peak):
+    """BASELINE.json configs[2]: Q6-shaped filter + SUM(extendedprice * discount), four f64 columns."""
+    from queryengine_b200 import capi
+    from queryengine_b200.ast import AggregationFunction, DataType, Function, col, fn
+    from queryengine_b200.engine import ColumnarTable, Field, Pipeline
+    D = DataType.DOUBLE
+    t = ColumnarTable(ctx, [Field("l_quantity", D), Field("l_extendedprice", D), Field("l_discount", D),
+                            Field("l_shipdate", D)], rows)
+    t.generate(0, capi.QE_GEN_UNIFORM_INT, SEED + 1, 1, 50)
+    t.generate(1, capi.QE_GEN_CENTS, SEED + 2, 90000, 10499999)
+    t.generate(2, capi.QE_GEN_CENTS, SEED + 3, 0, 10)
+    t.generate(3, capi.QE_GEN_UNIFORM_INT, SEED + 4, 8036, 10561)
+    filt = fn(Function.AND, fn(Function.AND, fn(Function.AND, fn(Function.AND,
+              fn(Function.CMP_GE, col(3), 8766.0), fn(Function.CMP_LT, col(3), 9131.0)),
+              fn(Function.CMP_GE, col(2), 0.05)), fn(Function.CMP_LE, col(2), 0.07)), fn(Function.CMP_LT, col(0), 24.0))
+    pipe = Pipeline(t, filt, [fn(Function.MUL, col(1), col(2))], [AggregationFunction.SUM])
+    res = pipe.run()
+    for _ in range(warmup):
+        pipe.run(res)
+    ms0, runs0 = res.kernel_stats()
+    for _ in range(steps):
+        pipe.run(res)
+    ms1, runs1 = res.kernel_stats()
+    kms = (ms1 - ms0) / max(1, runs1 - runs0)
+    part = res.agg_partial(0)
+    out = {"rows": rows, "kernel_ms": kms, "rows_per_s": rows / (kms * 1e-3),
+           "gb_per_s": rows * 32 / (kms * 1e-3) / 1e9, "frac_of_peak": rows * 32 / (kms * 1e-3) / 1e9 / peak,
+           "algorithmic_bytes_per_row": 32, "selectivity": part.count / rows, "sum": res.agg(0), "jit": res.used_jit}
+    res.close()
+    t.close()
+    return out
+
+
+def extra_tree(ctx, torch, stream, rows, steps, warmup, peak):
+    """BASELINE.json configs[3]: nullable f64 arithmetic tree (depth 8) with validity bitmaps, dense projection."""
+    from queryengine_b200 import capi
+    from queryengine_b200.ast import DataType, Function, col, fn
+    from queryengine_b200.engine import ColumnarTable, Field, Pipeline
+    D = DataType.DOUBLE
+    t = ColumnarTable(ctx, [Field("a", D, True), Field("b", D, True), Field("c", D, True), Field("d", D, True)], rows)
+    for c, rate in enumerate((0.0, 0.01, 0.10, 0.50)):
+        t.generate(c, capi.QE_GEN_UNIFORM_REAL, SEED + 10 + c, -1000.0, 1000.0, null_rate=rate)
+    a, b, c_, d = col(0), col(1), col(2), col(3)
+    inner = fn(Function.DIV, fn(Function.MUL, fn(Function.ADD, a, b), fn(Function.SUB, c_, d)),
+               fn(Function.ADD, fn(Function.MUL, a, 0.5), fn(Function.SUB, fn(Function.MOD, c_, 7.0), fn(Function.UNARY_MINUS, b))))
+    tree = fn(Function.IF, fn(Function.CMP_GT, inner, 0.0),
+              fn(Function.ADD, fn(Function.MUL, inner, fn(Function.SUB, a, d)), fn(Function.DIV, c_, fn(Function.ADD, b, 1.5))),
+              fn(Function.SUB, fn(Function.UNARY_MINUS, inner), fn(Function.MUL, d, 0.25)))
+    pipe = Pipeline(t, None, [tree])
+    res = pipe.run()
+    for _ in range(warmup):
+        pipe.run(res)
+    ms0, runs0 = res.kernel_stats()
+    for _ in range(steps):
+        pipe.run(res)
+    ms1, runs1 = res.kernel_stats()
+    kms = (ms1 - ms0) / max(1, runs1 - runs0)
+    bpr = 5 * (8 + 1 / 8)
+    out = {"rows": rows, "kernel_ms": kms, "rows_per_s": rows / (kms * 1e-3), "gb_per_s": rows * bpr / (kms * 1e-3) / 1e9,
+           "frac_of_peak": rows * bpr / (kms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_row": bpr, "jit": res.used_jit}
+    res.close()
+    t.close()
+    return out
+
+
+def run_ours(args):
+    import torch
+    from queryengine_b200 import capi
+    from queryengine_b200.ast import DataType, col
+    from queryengine_b200.engine import ColumnarTable, Context, Field, Pipeline
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist_mod.init_process_group("nccl", device_id=device)
+        dist = dist_mod
+    peak, peak_kind = measured_peak_gbs()
+
+    ctx = Context(local_rank)
+    if args.steps_opt:
+        ctx.set_option("steps", args.steps_opt)
+    if args.vec_opt:
+        ctx.set_option("vec", args.vec_opt)
+    if args.grid_per_sm:
+        ctx.set_option("grid_per_sm", args.grid_per_sm)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=device)
+    rows = args.rows
+    I64 = DataType.INT64
+    table = ColumnarTable(ctx, [Field("col", I64, False)], rows)
+    table.generate(0, capi.QE_GEN_UNIFORM_U40, SEED, row_offset=rank * rows)
+    pipes = [Pipeline(table, filter_expr(s), [col(0, I64, "col")]) for s in SELECTIVITIES]
+    results = [p.run() for p in pipes]
+    kept = [r.num_rows for r in results]
+    for s, k in zip(SELECTIVITIES, kept):
+        assert abs(k / rows - s) < 0.01, f"selectivity {s}: kept {k} of {rows}"
+    assert all(r.used_jit for r in results) or args.allow_interpreter, "generated code did not run (NVRTC missing?)"
+
+    def step():
+        for i, p in enumerate(pipes):
+            results[i] = p.run(results[i])
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    ctx.synchronize()
+    stats0 = [r.kernel_stats() for r in results]
+    launches0 = ctx.launch_count
+    with ClockSampler(local_rank) as clocks:
+        ms = timed_steps(torch, ctx, stream, step, args.steps, dist, device)
+    launches = ctx.launch_count - launches0
+    stats1 = [r.kernel_stats() for r in results]
+    total_rows = world * rows * len(SELECTIVITIES) * args.steps
+    value = total_rows / (ms * 1e-3)
+
+    # roofline of the filter + compaction kernel: algorithmic bytes = 8 B read per row + (8 + 4) B written per kept row
+    per_sel = []
+    tot_bytes = tot_ms = 0.0
+    for s, k, (m0, n0), (m1, n1) in zip(SELECTIVITIES, kept, stats0, stats1):
+        kms = (m1 - m0) / max(1, n1 - n0)
+        nbytes = 8.0 * rows + 12.0 * k
+        per_sel.append({"selectivity": s, "kept": k, "kernel_ms": kms, "rows_per_s": rows / (kms * 1e-3),
+                        "gb_per_s": nbytes / (kms * 1e-3) / 1e9, "frac_of_peak": nbytes / (kms * 1e-3) / 1e9 / peak,
+                        "algorithmic_bytes": nbytes})
+        tot_bytes += nbytes
+        tot_ms += kms
+    achieved = tot_bytes / (tot_ms * 1e-3) / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        try:
+            traffic = json.load(open(tp)).get("filter_sweep_dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    roofline = {"bound": "hbm", "kernel": "qe_kernel (generated filter+compaction, qe_filter_body)", "achieved": achieved,
+                "peak": peak, "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak,
+                "frac_of_nominal_8000": achieved / 8000.0, "traffic": traffic,
+                "algorithmic_bytes_per_launch": tot_bytes / len(SELECTIVITIES),
+                "avg_launch_ms": tot_ms / len(SELECTIVITIES), "per_selectivity": per_sel}
+
+    # ---- end to end through the C ABI with host buffers: upload -> filter -> download, every pass
+    e2e = run_e2e(args, torch, ctx, dist, device, rows, world, rank)
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "config": workload_config(rows, world),
+        "roofline": roofline, "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches),
+        "hbm_gb_per_s_aggregate": world * len(SELECTIVITIES) * args.steps * (tot_bytes / len(SELECTIVITIES)) / (ms * 1e-3) / 1e9,
+    }
+    for r in results:
+        r.close()
+    table.close()
+
+    extra = {}
+    if rank == 0 and world == 1 and not args.no_extra:
+        for name, fn_, n in (("q6_sf100", extra_q6, args.q6_rows), ("nullable_tree", extra_tree, args.tree_rows)):
+            try:
+                extra[name] = fn_(ctx, torch, stream, n, max(3, args.steps), 3, peak)
+            except Exception as e:  # reported, never hidden
+                extra[name] = {"error": repr(e)}
+    if rank == 0 and world == 1 and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        v, secs, ckept = cpu_leg(args.cpu_rows, threads)
+        line["cpu_baseline"] = {
+            "value": v, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{args.cpu_rows} rows of the same column, one three-filter sweep ({secs:.2f} s); oracle/qe_oracle.c, "
+                      "the C restatement of the reference's Kotlin evaluator (no JVM in this image), row-range sharded"}
+        v1, secs1, _ = cpu_leg(max(1, args.cpu_rows // 8), 1)
+        extra["cpu_single_thread_rows_per_s"] = v1
+    if extra:
+        line["extra"] = extra
+    ctx.close()
+    if rank == 0:
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def run_e2e(args, torch, ctx, dist, device, rows, world, rank):
+    from queryengine_b200 import capi
+    from queryengine_b200.ast import DataType, col
+    from queryengine_b200.engine import ColumnarTable, Field, Pipeline
+    I64 = DataType.INT64
+    e2e_rows = min(rows, args.e2e_rows) if args.e2e_rows else rows
+    budget = int(host_memory_available() * 0.5) // max(1, world if world <= 8 else 8)
+    e2e_rows = max(1 << 20, min(e2e_rows, budget // 20 // (1 << 20) * (1 << 20)))
+    bufs = []
+    try:
+        h_in = PinnedBuffer(e2e_rows * 8); bufs.append(h_in)
+        h_sel = PinnedBuffer(e2e_rows * 4); bufs.append(h_sel)
+        h_val = PinnedBuffer(e2e_rows * 8); bufs.append(h_val)
+    except capi.QeError:
+        for b in bufs:
+            b.free()
+        return {"value": None, "unit": UNIT, "error": "pinned host allocation failed", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0}
+    # host copy of the synthetic column (untimed): generated on the device, read back through the ABI
+    t = ColumnarTable(ctx, [Field("col", I64, False)], e2e_rows)
+    t.generate(0, capi.QE_GEN_UNIFORM_U40, SEED, row_offset=rank * rows)
+    dense = Pipeline(t, None, [col(0, I64, "col")]).run()
+    capi.check(capi.lib().qe_result_column(dense.handle, 0, h_in.ptr, None))
+    dense.close()
+    pipes = [Pipeline(t, filter_expr(s), [col(0, I64, "col")]) for s in SELECTIVITIES]
+    results = [None] * len(pipes)
+    kept = [0] * len(pipes)
+
+    def one_pass(i):
+        t.upload_raw(0, h_in.ptr.value, None, 0, e2e_rows)           # host -> HBM (pinned, async)
+        results[i] = pipes[i].run(results[i])
+        kept[i] = results[i].num_rows                                # waits for the kernel
+        capi.check(capi.lib().qe_result_selection(results[i].handle, h_sel.ptr))
+        capi.check(capi.lib().qe_result_column(results[i].handle, 0, h_val.ptr, None))
+
+    for i in range(len(pipes)):
+        one_pass(i)                                                  # warm-up
+    steps = max(1, min(args.steps, args.e2e_steps))
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        for i in range(len(pipes)):
+            one_pass(i)
+    torch.cuda.synchronize()
+    secs = time.perf_counter() - t0
+    if dist is not None:
+        tt = torch.tensor([secs], dtype=torch.float64, device=device)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        secs = float(tt.item())
+    h2d = len(pipes) * e2e_rows * 8
+    d2h = sum(k * 12 + 8 for k in kept)
+    for r in results:
+        r.close()
+    t.close()
+    for b in bufs:
+        b.free()
+    return {"value": world * len(pipes) * e2e_rows * steps / secs, "unit": UNIT, "rows_per_gpu": e2e_rows, "steps": steps,
+            "ms_per_step": secs / steps * 1e3, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "what": "per filter pass: qe_table_upload from pinned host memory, qe_pipeline_run, "
+                    "qe_result_selection + qe_result_column into pinned host memory"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=int, default=1_000_000_000, help="rows per GPU")
+    ap.add_argument("--cpu-rows", type=int, default=40_000_000, help="rows of the bounded CPU sample")
+    ap.add_argument("--e2e-rows", type=int, default=0, help="rows per GPU for the end-to-end leg (0 = same as --rows)")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--q6-rows", type=int, default=600_037_902)
+    ap.add_argument("--tree-rows", type=int, default=1_000_000_000)
+    ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--allow-interpreter", action="store_true")
+    ap.add_argument("--steps-opt", type=int, default=0, help="tile shape override: steps per warp")
+    ap.add_argument("--vec-opt", type=int, default=0, help="tile shape override: rows per lane per step (2 or 4)")
+    ap.add_argument("--grid-per-sm", type=int, default=0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

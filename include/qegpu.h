@@ -1,0 +1,235 @@
+/*
+ * qegpu.h -- C ABI of libqegpu.so, the B200 (sm_100a) implementation of
+ * jhorstmann/queryengine's filter/scan hot path.
+ *
+ * The reference has no FFI, plugin or SPI of any kind; its seams are three
+ * abstract classes and one enum (M/ = src/main/java/net/jhorstmann/queryengine/):
+ *
+ *   Operator    { open(); next(): Array<Any?>?; close() }   M/operator/Operators.kt:5-11
+ *   RowCallable { invoke(row: Array<Any?>): Any? }          M/evaluator/Compiler.kt:9-11
+ *   Table       { schema; getScanOperator(projection) }     M/data/Table.kt:6-10
+ *   Mode        { INTERPRETER, CLOSURE_COMPILER, BYTECODE_COMPILER }   M/evaluator/Compiler.kt:5-7
+ *
+ * and the one place they are assembled, buildPhysicalPlan (M/evaluator/Planner.kt:30-63).
+ * This library replaces the subtree that function builds for
+ *     Scan -> [Filter] -> [Projection] -> [GlobalAggregation]
+ * with one call.  Each entry point below names the reference interface it
+ * stands in for.  INTEGRATION.md shows the Kotlin/JNI binding a maintainer
+ * would add (Mode.GPU + GpuPipelineOperator).
+ *
+ * Conventions
+ *   - every function returns a qe_status (0 = OK); the message of the last
+ *     failure on the calling thread is qe_last_error().  No C++ exception
+ *     crosses this boundary.  (The reference throws unchecked exceptions.)
+ *   - handles are opaque, created and destroyed by the library.  A handle is
+ *     used by one thread at a time; different handles may be used concurrently.
+ *   - host buffers passed in or filled are owned by the caller and are not
+ *     retained after the call returns.
+ *   - there is no CPU fallback: without a CUDA device qe_ctx_create fails.
+ */
+#ifndef QEGPU_H
+#define QEGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define QE_API __attribute__((visibility("default")))
+#else
+#define QE_API
+#endif
+
+typedef enum qe_status {
+    QE_OK = 0,
+    QE_ERR_INVALID_ARGUMENT = 1,
+    QE_ERR_PROGRAM = 2,        /* malformed program or operand types the reference's TypeCheck rejects */
+    QE_ERR_CUDA = 3,
+    QE_ERR_UNSUPPORTED = 4,    /* e.g. STRING expressions (not on the GPU path yet) */
+    QE_ERR_CAPACITY = 5,       /* more rows passed the filter than out_capacity_rows */
+    QE_ERR_JIT = 6,
+    QE_ERR_STATE = 7
+} qe_status;
+
+/* Physical column types.  DOUBLE and BOOLEAN are the reference's DataType
+ * members (M/data/Schema.kt:3-5, same ordinals); INT64 and DATE32 are
+ * extensions that widen exactly to DOUBLE when loaded (|x| < 2^53). */
+typedef enum qe_type {
+    QE_TYPE_STRING = 0,        /* reserved, not supported on this path */
+    QE_TYPE_DOUBLE = 1,        /* double[n] */
+    QE_TYPE_BOOLEAN = 2,       /* bitmap, LSB first */
+    QE_TYPE_INT64 = 3,         /* int64_t[n] */
+    QE_TYPE_DATE32 = 4         /* int32_t[n], days since epoch */
+} qe_type;
+
+/* AggregationFunction ordinals, M/ast/Functions.kt:24-26 */
+typedef enum qe_agg_fn {
+    QE_AGG_FN_MIN = 0, QE_AGG_FN_MAX = 1, QE_AGG_FN_SUM = 2, QE_AGG_FN_COUNT = 3, QE_AGG_FN_AVG = 4
+} qe_agg_fn;
+
+/* ---- flattened expression program -----------------------------------------
+ * A tree (M/ast/Expressions.kt:6-62) in postfix order, one 32-bit word per
+ * node:  word = opcode | (argument << 8).
+ *   opcodes 0..16   the reference's Function enum ordinals (M/ast/Functions.kt:7-22):
+ *                   AND OR IF NOT UNARY_MINUS UNARY_PLUS MUL DIV MOD ADD SUB
+ *                   CMP_LT CMP_LE CMP_GE CMP_GT CMP_EQ CMP_NE; operands were
+ *                   pushed left to right (IF: condition, then, else).
+ *   QE_OP_LOAD_COL  ColumnExpression; argument = column index in the qe_table
+ *   QE_OP_CONST_F64 NumericLiteralExpression; the next two words are the low
+ *                   and high halves of the IEEE-754 bits
+ *   QE_OP_CONST_BOOL BooleanLiteralExpression; argument = 0 / 1
+ */
+enum {
+    QE_OP_LOAD_COL = 32,
+    QE_OP_CONST_F64 = 33,
+    QE_OP_CONST_BOOL = 34
+};
+#define QE_MAX_PROGRAM_WORDS 1024
+#define QE_MAX_STACK 32
+#define QE_MAX_PIPELINE_COLUMNS 16
+#define QE_MAX_PROJECTIONS 8
+
+typedef struct qe_ctx qe_ctx;
+typedef struct qe_program qe_program;
+typedef struct qe_table qe_table;
+typedef struct qe_result qe_result;
+
+typedef struct qe_col_desc {
+    int32_t type;              /* qe_type */
+    int32_t nullable;          /* 1: a validity bitmap is stored */
+} qe_col_desc;
+
+/* Partial aggregate of one partition, for combining across GPUs in fixed rank order. */
+typedef struct qe_agg_partial {
+    double  sum;
+    int64_t count;             /* non-null inputs seen */
+    double  min;
+    double  max;
+} qe_agg_partial;
+
+typedef struct qe_pipeline_desc {
+    const qe_program *filter;          /* FilterOperator predicate, may be NULL */
+    const qe_program *const *proj;     /* ProjectionOperator expressions */
+    int32_t nproj;
+    const int32_t *agg_fns;            /* GlobalAggregationOperator functions; agg k consumes projection k */
+    int32_t nagg;                      /* 0, or == nproj */
+    int64_t row_begin;                 /* batch = rows [row_begin, row_end); row_begin % 128 == 0 */
+    int64_t row_end;                   /* -1 = to the end of the table */
+    int64_t out_capacity_rows;         /* rows the compacted outputs may hold; 0 = worst case (all rows) */
+    uint32_t flags;                    /* QE_RUN_* */
+} qe_pipeline_desc;
+
+enum {
+    QE_RUN_NO_SELECTION = 1u << 0,     /* do not materialise the selection vector */
+    QE_RUN_INTERPRETER  = 1u << 1      /* use the generic interpreter kernels instead of generated code */
+};
+
+/* ---- context: one CUDA device, one stream, a device memory pool ------------ */
+QE_API int qe_ctx_create(int device, qe_ctx **out);
+QE_API int qe_ctx_destroy(qe_ctx *ctx);
+QE_API int qe_ctx_synchronize(qe_ctx *ctx);
+/* cudaStream_t all work of this context is enqueued on (for event timing by the caller) */
+QE_API void *qe_ctx_stream(qe_ctx *ctx);
+/* options: "jit" (1 default / 0 = always interpret), "steps", "vec" (tile shape overrides, 0 = auto),
+ * "grid_per_sm" (0 = auto) */
+QE_API int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value);
+/* kernels launched by this context so far */
+QE_API int64_t qe_ctx_launch_count(const qe_ctx *ctx);
+
+/* pinned host memory for staging-free uploads / downloads */
+QE_API int qe_host_alloc(size_t bytes, void **out);
+QE_API int qe_host_free(void *p);
+
+/* ---- program: stands in for compileExpression(expr, mode): RowCallable
+ *      (M/evaluator/Compiler.kt:20-26).  Structure is checked here; operand types are
+ *      checked against the table when the pipeline runs (the rules of
+ *      M/evaluator/TypeCheck.kt:38-96 with the evident intent for AND/OR). */
+QE_API int qe_program_create(qe_ctx *ctx, const uint32_t *words, size_t nwords, qe_program **out);
+QE_API int qe_program_destroy(qe_program *program);
+
+/* ---- table: columnar stand-in for MemoryTable (M/data/MemoryTable.kt:7-19) -- */
+QE_API int qe_table_create(qe_ctx *ctx, int ncols, const qe_col_desc *cols, int64_t nrows, qe_table **out);
+/* Copy rows [row0, row0+n) of one column from host memory (pinned or pageable)
+ * into HBM, asynchronously on the context's stream.  `values`: see qe_type.
+ * `validity`: Arrow bitmap for those n rows (bit i = row0+i non-null) or NULL
+ * = all non-null.  row0 must be a multiple of 8 when a bitmap is involved. */
+QE_API int qe_table_upload(qe_table *table, int col, const void *values, const uint8_t *validity,
+                           int64_t row0, int64_t n);
+/* Device addresses (values: which = 0, validity bitmap: which = 1) for callers
+ * that produce columns on the device. */
+QE_API void *qe_table_device_ptr(qe_table *table, int col, int which);
+/* Synthetic column generators (counter-based, a pure function of the global
+ * row index `row_offset + i`, so results do not depend on the GPU count).
+ * kind: see QE_GEN_* ; p0, p1 are kind-specific; null_rate in [0,1] applies
+ * to nullable columns. */
+enum {
+    QE_GEN_UNIFORM_U40 = 0,    /* splitmix64(seed ^ i) >> 24, as the column's type */
+    QE_GEN_UNIFORM_INT = 1,    /* p0 + (hash % (p1 - p0 + 1)), integers in [p0, p1] */
+    QE_GEN_UNIFORM_REAL = 2,   /* p0 + u * (p1 - p0), u in [0,1) with 53 random bits */
+    QE_GEN_CENTS = 3,          /* uniform integer in [p0, p1] divided by 100.0 */
+    QE_GEN_ROW_INDEX = 4       /* the global row index itself */
+};
+QE_API int qe_table_generate(qe_table *table, int col, int kind, uint64_t seed, double p0, double p1,
+                             double null_rate, int64_t row_offset);
+QE_API int qe_table_destroy(qe_table *table);
+
+/* ---- pipeline: stands in for the operator subtree buildPhysicalPlan builds
+ *      (M/evaluator/Planner.kt:30-63) and for pulling it dry (Operator.forEach,
+ *      M/operator/Operators.kt:13-23).  *result may hold a result of an earlier
+ *      run of the same shape, whose buffers are then reused. */
+QE_API int qe_pipeline_run(qe_ctx *ctx, const qe_table *table,
+                           const qe_program *filter,
+                           const qe_program *const *proj, int nproj,
+                           const int32_t *agg_fns, int nagg,
+                           qe_result **result);
+QE_API int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_pipeline_desc *desc,
+                              qe_result **result);
+
+/* ---- results ------------------------------------------------------------- */
+/* rows the pipeline emitted (kept rows; 1 for an aggregation).  Waits for the run. */
+QE_API int qe_result_num_rows(qe_result *result, int64_t *nrows);
+QE_API int qe_result_num_columns(const qe_result *result, int *ncols);
+QE_API int qe_result_column_type(const qe_result *result, int k, int *type, int *has_validity);
+/* Copy output column k to host: values as for qe_type (BOOLEAN: bitmap of
+ * ceil(n/8) bytes), validity bitmap likewise (all ones when the column cannot
+ * be null).  Either pointer may be NULL. */
+QE_API int qe_result_column(qe_result *result, int k, void *dst_values, uint8_t *dst_validity);
+/* ascending table row indices of the rows that passed the filter */
+QE_API int qe_result_selection(qe_result *result, uint32_t *dst);
+/* finish() of accumulator k (M/evaluator/Accumulators.kt:21-107); COUNT is returned as a double */
+QE_API int qe_result_agg(qe_result *result, int k, double *value, int *is_null);
+QE_API int qe_result_agg_partial(qe_result *result, int k, qe_agg_partial *out);
+/* device addresses of the result buffers: which = 0 values, 1 validity, 2 selection vector (k ignored) */
+QE_API void *qe_result_device_ptr(qe_result *result, int k, int which);
+/* device time of the main kernel of the last run that produced this result, in milliseconds */
+QE_API int qe_result_kernel_ms(qe_result *result, float *ms);
+/* device time of the main kernel summed over every completed run into this result, and the run count */
+QE_API int qe_result_kernel_stats(qe_result *result, double *total_ms, int64_t *runs);
+/* 1 if the last run used generated (JIT) code, 0 for the interpreter kernels */
+QE_API int qe_result_used_jit(const qe_result *result);
+QE_API int qe_result_destroy(qe_result *result);
+
+/* Combine per-partition partials in array order (deterministic) and finish. */
+QE_API int qe_agg_combine(int agg_fn, const qe_agg_partial *partials, int n, double *value, int *is_null);
+
+/* Diagnostics, no GPU needed: bind `programs` (filter first when has_filter,
+ * then nproj projections) against a schema, write the generated CUDA source
+ * into src_buf and, when compile != 0, compile it with NVRTC for sm_100a
+ * (cubin copied into cubin_buf when it fits; its size into *cubin_bytes).
+ * steps / vec: tile shape overrides, 0 = the library's choice. */
+QE_API int qe_debug_generate(const qe_col_desc *cols, int ncols,
+                             const uint32_t *const *programs, const size_t *nwords,
+                             int has_filter, int nproj, const int32_t *agg_fns, int nagg,
+                             int steps, int vec, int compile,
+                             char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes);
+
+QE_API const char *qe_last_error(void);
+QE_API const char *qe_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QEGPU_H */

@@ -1,0 +1,125 @@
+"""ctypes binding of the C ABI in include/qegpu.h (libqegpu.so, built in-tree).
+
+This is the same binding shape a JNI stub would have: plain
+pointers and sizes, integer status codes, qe_last_error() for the message.
+There is no fallback: if the library is missing, importing the symbols raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libqegpu.so")
+
+QE_OK = 0
+QE_ERR_INVALID_ARGUMENT = 1
+QE_ERR_PROGRAM = 2
+QE_ERR_CUDA = 3
+QE_ERR_UNSUPPORTED = 4
+QE_ERR_CAPACITY = 5
+QE_ERR_JIT = 6
+QE_ERR_STATE = 7
+
+QE_RUN_NO_SELECTION = 1
+QE_RUN_INTERPRETER = 2
+
+QE_GEN_UNIFORM_U40 = 0
+QE_GEN_UNIFORM_INT = 1
+QE_GEN_UNIFORM_REAL = 2
+QE_GEN_CENTS = 3
+QE_GEN_ROW_INDEX = 4
+
+
+class QeError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"qegpu status {status}: {message}")
+        self.status = status
+        self.message = message
+
+
+class ColDesc(C.Structure):
+    _fields_ = [("type", C.c_int32), ("nullable", C.c_int32)]
+
+
+class AggPartial(C.Structure):
+    _fields_ = [("sum", C.c_double), ("count", C.c_int64), ("min", C.c_double), ("max", C.c_double)]
+
+
+class PipelineDesc(C.Structure):
+    _fields_ = [
+        ("filter", C.c_void_p),
+        ("proj", C.POINTER(C.c_void_p)),
+        ("nproj", C.c_int32),
+        ("agg_fns", C.POINTER(C.c_int32)),
+        ("nagg", C.c_int32),
+        ("row_begin", C.c_int64),
+        ("row_end", C.c_int64),
+        ("out_capacity_rows", C.c_int64),
+        ("flags", C.c_uint32),
+    ]
+
+
+# every symbol include/qegpu.h declares: name -> (restype, argtypes)
+_vp = C.c_void_p
+SYMBOLS = {
+    "qe_ctx_create": (C.c_int, [C.c_int, C.POINTER(_vp)]),
+    "qe_ctx_destroy": (C.c_int, [_vp]),
+    "qe_ctx_synchronize": (C.c_int, [_vp]),
+    "qe_ctx_stream": (_vp, [_vp]),
+    "qe_ctx_set_option": (C.c_int, [_vp, C.c_char_p, C.c_int64]),
+    "qe_ctx_launch_count": (C.c_int64, [_vp]),
+    "qe_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(_vp)]),
+    "qe_host_free": (C.c_int, [_vp]),
+    "qe_program_create": (C.c_int, [_vp, _vp, C.c_size_t, C.POINTER(_vp)]),
+    "qe_program_destroy": (C.c_int, [_vp]),
+    "qe_table_create": (C.c_int, [_vp, C.c_int, C.POINTER(ColDesc), C.c_int64, C.POINTER(_vp)]),
+    "qe_table_upload": (C.c_int, [_vp, C.c_int, _vp, _vp, C.c_int64, C.c_int64]),
+    "qe_table_device_ptr": (_vp, [_vp, C.c_int, C.c_int]),
+    "qe_table_generate": (C.c_int, [_vp, C.c_int, C.c_int, C.c_uint64, C.c_double, C.c_double, C.c_double, C.c_int64]),
+    "qe_table_destroy": (C.c_int, [_vp]),
+    "qe_pipeline_run": (C.c_int, [_vp, _vp, _vp, C.POINTER(_vp), C.c_int, C.POINTER(C.c_int32), C.c_int, C.POINTER(_vp)]),
+    "qe_pipeline_run_ex": (C.c_int, [_vp, _vp, C.POINTER(PipelineDesc), C.POINTER(_vp)]),
+    "qe_result_num_rows": (C.c_int, [_vp, C.POINTER(C.c_int64)]),
+    "qe_result_num_columns": (C.c_int, [_vp, C.POINTER(C.c_int)]),
+    "qe_result_column_type": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "qe_result_column": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "qe_result_selection": (C.c_int, [_vp, _vp]),
+    "qe_result_agg": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
+    "qe_result_agg_partial": (C.c_int, [_vp, C.c_int, C.POINTER(AggPartial)]),
+    "qe_result_device_ptr": (_vp, [_vp, C.c_int, C.c_int]),
+    "qe_result_kernel_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    "qe_result_kernel_stats": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
+    "qe_result_used_jit": (C.c_int, [_vp]),
+    "qe_result_destroy": (C.c_int, [_vp]),
+    "qe_agg_combine": (C.c_int, [C.c_int, C.POINTER(AggPartial), C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
+    "qe_debug_generate": (C.c_int, [C.POINTER(ColDesc), C.c_int, C.POINTER(_vp), C.POINTER(C.c_size_t), C.c_int, C.c_int,
+                                    C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.c_int,
+                                    C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "qe_last_error": (C.c_char_p, []),
+    "qe_version": (C.c_char_p, []),
+}
+
+_lib = None
+
+
+def lib():
+    """Load libqegpu.so.  Raises if it has not been built (python -m queryengine_b200.build)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FileNotFoundError(
+                f"{LIB_PATH} is missing: build the CUDA extension with `python -m queryengine_b200.build` "
+                "(there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            f = getattr(L, name)
+            f.restype = res
+            f.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(status: int) -> None:
+    if status != QE_OK:
+        raise QeError(status, lib().qe_last_error().decode(errors="replace"))

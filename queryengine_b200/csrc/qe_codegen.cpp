@@ -1,0 +1,374 @@
+// qe_codegen.cpp -- see qe_codegen.h
+#include "qe_codegen.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+namespace qe {
+namespace {
+
+struct SV {                  // one entry of the compile-time operand stack
+    std::string val;
+    std::string valid;       // "true" when the value is statically non-null
+    VType t = VT_NONE;
+    bool is_const = false;
+    double k = 0.0;
+};
+
+struct Gen {
+    std::string body;
+    int ntmp = 0;
+
+    std::string tmp(const char *prefix)
+    {
+        char b[32];
+        snprintf(b, sizeof b, "%s%d", prefix, ntmp++);
+        return b;
+    }
+    void line(const std::string &s) { body += "        " + s + "\n"; }
+};
+
+std::string f64_literal(double k)
+{
+    uint64_t bits;
+    memcpy(&bits, &k, sizeof bits);
+    char b[64];
+    snprintf(b, sizeof b, "qe_bits_f64((qe_i64)0x%016llxULL)", (unsigned long long)bits);
+    return b;
+}
+
+std::string and_valid(const std::string &a, const std::string &b)
+{
+    if (a == "true") return b;
+    if (b == "true") return a;
+    if (a == b) return a;
+    return "(" + a + " && " + b + ")";
+}
+
+bool plain_literal(const SV &s)      // usable with the one-instruction comparison forms
+{
+    return s.is_const && s.k == s.k && s.k != 0.0;
+}
+
+const char *cmp_fn(int op)
+{
+    switch (op) {
+    case OP_CMP_LT: return "qe_cmp_lt";
+    case OP_CMP_LE: return "qe_cmp_le";
+    case OP_CMP_GE: return "qe_cmp_ge";
+    case OP_CMP_GT: return "qe_cmp_gt";
+    case OP_CMP_EQ: return "qe_cmp_eq";
+    default:        return "qe_cmp_ne";
+    }
+}
+
+int cmp_swapped(int op)              // k OP x  ==  x OP' k
+{
+    switch (op) {
+    case OP_CMP_LT: return OP_CMP_GT;
+    case OP_CMP_LE: return OP_CMP_GE;
+    case OP_CMP_GE: return OP_CMP_LE;
+    case OP_CMP_GT: return OP_CMP_LT;
+    default: return op;
+    }
+}
+
+std::string slot_value(const BoundPipeline &bp, int slot)
+{
+    char b[48];
+    const int t = bp.slot_info[slot].type;
+    if (t == 3 || t == 4) snprintf(b, sizeof b, "(double)in.c%d", slot);   // exact widening, |x| < 2^53
+    else snprintf(b, sizeof b, "in.c%d", slot);
+    return b;
+}
+
+// Emit straight-line code for one expression; returns its value / validity.
+SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
+{
+    std::vector<SV> st;
+    for (const Instr &in : e.code) {
+        SV r;
+        switch (in.op) {
+        case OP_LOAD_COL: {
+            const int slot = (int)in.arg;
+            r.t = (bp.slot_info[slot].type == 2) ? VT_BOOL : VT_F64;
+            r.val = slot_value(bp, slot);
+            char b[32];
+            snprintf(b, sizeof b, "in.v%d", slot);
+            r.valid = bp.slot_info[slot].nullable ? b : "true";
+            break;
+        }
+        case OP_CONST_F64:
+            r.t = VT_F64; r.val = f64_literal(in.k); r.valid = "true"; r.is_const = true; r.k = in.k;
+            break;
+        case OP_CONST_BOOL:
+            r.t = VT_BOOL; r.val = in.arg ? "true" : "false"; r.valid = "true";
+            break;
+        case OP_UNARY_PLUS: {                       // M/evaluator/Interpreter.kt:94
+            r = st.back(); st.pop_back(); r.is_const = false;
+            break;
+        }
+        case OP_UNARY_MINUS: {                      // Interpreter.kt:95
+            SV a = st.back(); st.pop_back();
+            r.t = VT_F64; r.valid = a.valid; r.val = g.tmp("t");
+            g.line("const double " + r.val + " = qe_neg(" + a.val + ");");
+            break;
+        }
+        case OP_NOT: {                              // ClosureCompiler.kt:115 / BytecodeCompiler.kt:346-351
+            SV a = st.back(); st.pop_back();
+            r.t = VT_BOOL; r.valid = a.valid; r.val = g.tmp("t");
+            g.line("const bool " + r.val + " = !" + a.val + ";");
+            break;
+        }
+        case OP_ADD: case OP_SUB: case OP_MUL: case OP_DIV: case OP_MOD: {   // Interpreter.kt:96-100
+            SV b = st.back(); st.pop_back();
+            SV a = st.back(); st.pop_back();
+            const char *f = in.op == OP_ADD ? "qe_add" : in.op == OP_SUB ? "qe_sub" : in.op == OP_MUL ? "qe_mul"
+                          : in.op == OP_DIV ? "qe_div" : "qe_mod";
+            r.t = VT_F64; r.valid = and_valid(a.valid, b.valid); r.val = g.tmp("t");
+            g.line("const double " + r.val + " = " + f + "(" + a.val + ", " + b.val + ");");
+            break;
+        }
+        case OP_CMP_LT: case OP_CMP_LE: case OP_CMP_GE: case OP_CMP_GT: case OP_CMP_EQ: case OP_CMP_NE: {
+            SV b = st.back(); st.pop_back();
+            SV a = st.back(); st.pop_back();
+            r.t = VT_BOOL; r.valid = and_valid(a.valid, b.valid); r.val = g.tmp("t");
+            std::string rhs;
+            if (a.t == VT_BOOL) {                   // Boolean equality, TypeCheck.kt:65-71
+                rhs = std::string("(") + a.val + (in.op == OP_CMP_EQ ? " == " : " != ") + b.val + ")";
+            } else if (plain_literal(b) && !a.is_const) {
+                rhs = std::string(cmp_fn(in.op)) + "_k(" + a.val + ", " + b.val + ")";
+            } else if (plain_literal(a) && !b.is_const) {
+                rhs = std::string(cmp_fn(cmp_swapped(in.op))) + "_k(" + b.val + ", " + a.val + ")";
+            } else {
+                rhs = std::string(cmp_fn(in.op)) + "(" + a.val + ", " + b.val + ")";
+            }
+            g.line("const bool " + r.val + " = " + rhs + ";");
+            break;
+        }
+        case OP_AND: case OP_OR: {                  // Kleene, Interpreter.kt:54-91
+            SV b = st.back(); st.pop_back();
+            SV a = st.back(); st.pop_back();
+            r.t = VT_BOOL; r.val = g.tmp("t");
+            if (a.valid == "true" && b.valid == "true") {
+                r.valid = "true";
+                g.line("const bool " + r.val + " = " + a.val + (in.op == OP_AND ? " && " : " || ") + b.val + ";");
+            } else {
+                r.valid = g.tmp("n");
+                g.line("bool " + r.val + ", " + r.valid + ";");
+                g.line(std::string(in.op == OP_AND ? "qe_and(" : "qe_or(") + a.val + ", " + a.valid + ", " + b.val + ", " +
+                       b.valid + ", " + r.val + ", " + r.valid + ");");
+            }
+            break;
+        }
+        case OP_IF: {                               // Interpreter.kt:46-53
+            SV f = st.back(); st.pop_back();
+            SV t = st.back(); st.pop_back();
+            SV c = st.back(); st.pop_back();
+            r.t = t.t; r.val = g.tmp("t");
+            g.line(std::string("const ") + (r.t == VT_F64 ? "double " : "bool ") + r.val + " = " + c.val + " ? " + t.val +
+                   " : " + f.val + ";");
+            std::string branch_valid = (t.valid == "true" && f.valid == "true")
+                                           ? "true" : "(" + c.val + " ? " + t.valid + " : " + f.valid + ")";
+            r.valid = and_valid(c.valid, branch_valid);
+            if (r.valid != "true" && r.valid != c.valid) {
+                std::string n = g.tmp("n");
+                g.line("const bool " + n + " = " + r.valid + ";");
+                r.valid = n;
+            }
+            break;
+        }
+        }
+        st.push_back(r);
+    }
+    return st.back();
+}
+
+const char *ctype_of(int qtype)
+{
+    switch (qtype) {
+    case 1: return "double";
+    case 2: return "bool";
+    case 3: return "qe_i64";
+    default: return "qe_i32";
+    }
+}
+
+const char *suffix_of(int qtype) { return qtype == 1 ? "f64" : qtype == 3 ? "i64" : "i32"; }
+
+}  // namespace
+
+std::string generate_source(const BoundPipeline &bp, KernelMode mode, const TileShape &shape)
+{
+    std::string s;
+    char b[256];
+    const int nslots = (int)bp.slot_info.size();
+    const int nproj = (int)bp.proj.size();
+
+    s += "// generated by qe_codegen.cpp -- pipeline: " + bp.signature() + "\n";
+    s += "#include \"qe_device.cuh\"\n\nstruct P {\n";
+    // bit columns of the outputs (validity bitmaps and BOOLEAN values)
+    struct BitCol { std::string ptr, bit; };
+    std::vector<BitCol> bitcols;
+    if (mode != KM_AGG) {
+        for (int k = 0; k < nproj; k++) {
+            if (bp.outs[k].has_validity) {
+                snprintf(b, sizeof b, "p.out_valid[%d]", k);
+                BitCol bc; bc.ptr = b;
+                snprintf(b, sizeof b, "o.n%d", k); bc.bit = b;
+                bitcols.push_back(bc);
+            }
+            if (bp.outs[k].type == 2) {
+                snprintf(b, sizeof b, "(qe_u32 *)p.out_values[%d]", k);
+                BitCol bc; bc.ptr = b;
+                if (bp.outs[k].has_validity) snprintf(b, sizeof b, "(o.o%d && o.n%d)", k, k);
+                else snprintf(b, sizeof b, "o.o%d", k);
+                bc.bit = b;
+                bitcols.push_back(bc);
+            }
+        }
+    }
+    snprintf(b, sizeof b, "    static constexpr int STEPS = %d, VEC = %d, NBITCOLS = %d;\n", shape.steps, shape.vec,
+             (int)bitcols.size());
+    s += b;
+
+    // ---- Row
+    s += "    struct Row {\n";
+    for (int i = 0; i < nslots; i++) {
+        snprintf(b, sizeof b, "        %s c%d;\n", ctype_of(bp.slot_info[i].type), i); s += b;
+        if (bp.slot_info[i].nullable) { snprintf(b, sizeof b, "        bool v%d;\n", i); s += b; }
+    }
+    if (nslots == 0) s += "        int unused;\n";
+    s += "    };\n";
+    // ---- Out
+    s += "    struct Out {\n";
+    for (int k = 0; k < nproj; k++) {
+        snprintf(b, sizeof b, "        %s o%d;\n", ctype_of(bp.outs[k].type), k); s += b;
+        if (bp.proj[k].nullable) { snprintf(b, sizeof b, "        bool n%d;\n", k); s += b; }
+    }
+    if (nproj == 0) s += "        int unused;\n";
+    s += "    };\n";
+
+    // ---- load: one vector load per column, MemorySourceOperator.next (M/operator/MemorySourceOperator.kt:18-36)
+    s += "    static __device__ __forceinline__ void load(const QeParams &p, qe_i64 r, Row (&rows)[VEC]) {\n";
+    for (int i = 0; i < nslots; i++) {
+        const int t = bp.slot_info[i].type;
+        if (t == 2) {
+            snprintf(b, sizeof b,
+                     "        { const qe_u32 m = qe_load_bits<VEC>((const qe_u32 *)p.col_values[%d], r);\n"
+                     "          _Pragma(\"unroll\") for (int j = 0; j < VEC; j++) rows[j].c%d = (m >> j) & 1u; }\n", i, i);
+        } else {
+            snprintf(b, sizeof b,
+                     "        { %s t[VEC]; qe_load_%s<VEC>(p.col_values[%d], r, t);\n"
+                     "          _Pragma(\"unroll\") for (int j = 0; j < VEC; j++) rows[j].c%d = t[j]; }\n",
+                     ctype_of(t), suffix_of(t), i, i);
+        }
+        s += b;
+        if (bp.slot_info[i].nullable) {
+            snprintf(b, sizeof b,
+                     "        { const qe_u32 m = qe_load_bits<VEC>(p.col_valid[%d], r);\n"
+                     "          _Pragma(\"unroll\") for (int j = 0; j < VEC; j++) rows[j].v%d = (m >> j) & 1u; }\n", i, i);
+            s += b;
+        }
+    }
+    s += "    }\n";
+
+    // ---- eval: RowCallable.invoke for the filter and every projection
+    s += "    static __device__ __forceinline__ bool eval(const QeParams &p, const Row &in, Out &o) {\n";
+    {
+        Gen g;
+        std::string keep = "true";
+        if (bp.has_filter) {
+            SV f = gen_expr(bp, bp.filter, g);
+            keep = and_valid(f.val, f.valid);        // FilterOperator.kt:20: non-null AND true
+        }
+        for (int k = 0; k < nproj; k++) {
+            const BoundExpr &e = bp.proj[k];
+            if (e.identity_slot >= 0) {
+                snprintf(b, sizeof b, "o.o%d = in.c%d;", k, e.identity_slot); g.line(b);
+                if (e.nullable) { snprintf(b, sizeof b, "o.n%d = in.v%d;", k, e.identity_slot); g.line(b); }
+            } else {
+                SV v = gen_expr(bp, e, g);
+                snprintf(b, sizeof b, "o.o%d = ", k); g.line(std::string(b) + v.val + ";");
+                if (e.nullable) { snprintf(b, sizeof b, "o.n%d = ", k); g.line(std::string(b) + v.valid + ";"); }
+            }
+        }
+        s += g.body;
+        s += "        return " + keep + ";\n";
+    }
+    s += "    }\n";
+
+    if (mode == KM_FILTER) {
+        s += "    static __device__ __forceinline__ void emit(const QeParams &p, qe_u64 pos, const Out &o) {\n";
+        for (int k = 0; k < nproj; k++) {
+            if (bp.outs[k].type == 2) continue;
+            snprintf(b, sizeof b, "        ((%s *)p.out_values[%d])[pos] = o.o%d;\n", ctype_of(bp.outs[k].type), k, k);
+            s += b;
+        }
+        s += "    }\n";
+    }
+    if (mode == KM_PROJECT) {
+        s += "    static __device__ __forceinline__ void emit_dense(const QeParams &p, qe_i64 r, const Out (&o)[VEC], qe_u32 inb) {\n";
+        for (int k = 0; k < nproj; k++) {
+            if (bp.outs[k].type == 2) continue;
+            snprintf(b, sizeof b,
+                     "        { %s t[VEC]; _Pragma(\"unroll\") for (int j = 0; j < VEC; j++) t[j] = o[j].o%d;\n"
+                     "          qe_store_%s<VEC>(p.out_values[%d], r, t); }\n",
+                     ctype_of(bp.outs[k].type), k, suffix_of(bp.outs[k].type), k);
+            s += b;
+        }
+        s += "    }\n";
+    }
+    if (mode != KM_AGG) {
+        s += "    static __device__ __forceinline__ qe_u32 *bitcol(const QeParams &p, int b) {\n        switch (b) {\n";
+        for (size_t i = 0; i < bitcols.size(); i++) {
+            snprintf(b, sizeof b, "        case %d: return ", (int)i); s += b; s += bitcols[i].ptr + ";\n";
+        }
+        s += "        }\n        return 0;\n    }\n";
+        s += "    static __device__ __forceinline__ bool bit(const Out &o, int b) {\n        switch (b) {\n";
+        for (size_t i = 0; i < bitcols.size(); i++) {
+            snprintf(b, sizeof b, "        case %d: return ", (int)i); s += b; s += bitcols[i].bit + ";\n";
+        }
+        s += "        }\n        return false;\n    }\n";
+    }
+    if (mode == KM_AGG) {
+        // GlobalAggregationOperator.open (M/operator/GlobalAggregationOperator.kt:10-25): accumulator k takes
+        // projection k, nulls are skipped
+        s += "    struct Accs {";
+        for (size_t k = 0; k < bp.agg_fns.size(); k++) { snprintf(b, sizeof b, " QeAcc a%d;", (int)k); s += b; }
+        s += " };\n";
+        s += "    static __device__ __forceinline__ void acc_init(Accs &a) {";
+        for (size_t k = 0; k < bp.agg_fns.size(); k++) { snprintf(b, sizeof b, " qe_acc_init(a.a%d);", (int)k); s += b; }
+        s += " }\n";
+        s += "    static __device__ __forceinline__ void acc_add(const QeParams &p, Accs &a, const Out &o, bool keep) {\n";
+        for (size_t k = 0; k < bp.agg_fns.size(); k++) {
+            std::string val = "0.0";
+            if (bp.outs[k].type == 1) { snprintf(b, sizeof b, "o.o%d", (int)k); val = b; }
+            else if (bp.outs[k].type == 3 || bp.outs[k].type == 4) { snprintf(b, sizeof b, "(double)o.o%d", (int)k); val = b; }
+            std::string on = "keep";
+            if (bp.proj[k].nullable) { snprintf(b, sizeof b, "(keep && o.n%d)", (int)k); on = b; }
+            snprintf(b, sizeof b, "        qe_acc_add<%d>(a.a%d, ", bp.agg_fns[k], (int)k);
+            s += b; s += val + ", " + on + ");\n";
+        }
+        s += "    }\n";
+        s += "    static __device__ __forceinline__ void acc_store(const QeParams &p, Accs &a, QeAcc *slot) {\n";
+        for (size_t k = 0; k < bp.agg_fns.size(); k++) {
+            snprintf(b, sizeof b, "        qe_acc_block_reduce_store<%d>(a.a%d, slot, p.agg_partials, %d);\n", bp.agg_fns[k],
+                     (int)k, (int)k);
+            s += b;
+        }
+        s += "    }\n";
+    }
+    s += "};\n\n";
+    const char *body = mode == KM_FILTER ? "qe_filter_body" : mode == KM_PROJECT ? "qe_project_body" : "qe_agg_body";
+    snprintf(b, sizeof b,
+             "extern \"C\" __global__ void __launch_bounds__(QE_BLOCK, %d) " QE_JIT_ENTRY
+             "(const __grid_constant__ QeParams p)\n{\n    %s<P>(p);\n}\n",
+             shape.min_blocks, body);
+    s += b;
+    return s;
+}
+
+}  // namespace qe

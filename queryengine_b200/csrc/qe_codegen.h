@@ -1,0 +1,33 @@
+// qe_codegen.h -- turns a bound pipeline into CUDA source: a "pipeline program"
+// struct P with straight-line, fully typed code for every expression tree, plus
+// the __global__ entry point that plugs it into the hand-written kernel body of
+// qe_device.cuh.  NVRTC compiles the result for sm_100a (qe_jit.cpp).
+//
+// This is the B200 counterpart of the reference's JVM bytecode back end
+// (M/evaluator/BytecodeCompiler.kt:134-175 `compile`, :37-132 `compileProjection`):
+// specialise once per query so the per-row cost has no dispatch, no boxing and
+// no operand stack -- the whole tree lives in registers.
+#ifndef QE_CODEGEN_H
+#define QE_CODEGEN_H
+
+#include <string>
+
+#include "qe_program.h"
+
+namespace qe {
+
+enum KernelMode { KM_FILTER = 0, KM_PROJECT = 1, KM_AGG = 2 };
+
+struct TileShape {
+    int steps = 2;          // steps per warp per tile
+    int vec = 2;            // adjacent rows per lane per step (2: 128-bit loads, 4: 256-bit loads)
+    int min_blocks = 1;     // __launch_bounds__ second argument
+};
+
+// name of the generated entry point
+#define QE_JIT_ENTRY "qe_kernel"
+
+std::string generate_source(const BoundPipeline &bp, KernelMode mode, const TileShape &shape);
+
+}  // namespace qe
+#endif

@@ -1,0 +1,653 @@
+// qe_device.cuh -- hand-written sm_100a kernel skeletons of the filter/scan hot path.
+//
+// Three kernel bodies share one structure (the __global__ entry points that call
+// them are in the generated source and in qe_kernels.cu).  Each is a template
+// over a "pipeline program" P that supplies the per-row work (load the referenced columns,
+// evaluate the flattened expression trees in registers, say what to emit):
+//
+//   qe_filter_body<P>     Scan -> Filter -> [Projection]  -> selection vector +
+//                         order-preserving compacted outputs      (K1)
+//   qe_project_body<P>    Scan -> Projection (no filter)  -> dense outputs +
+//                         validity words                           (K2)
+//   qe_agg_body<P>        Scan -> [Filter] -> Projection -> GlobalAggregation
+//                         -> per-CTA partials, fixed-order final reduce (K3)
+//
+// P is either generated per query (qe_codegen.cpp emits straight-line code and
+// NVRTC compiles it together with this header -- the B200 counterpart of the
+// reference's JVM bytecode back end, M/evaluator/BytecodeCompiler.kt:134-175)
+// or the generic interpreter in qe_interp.cuh.
+//
+// Replaces, per row: RowCallable.invoke (M/evaluator/Compiler.kt:9-11),
+// FilterOperator.next (M/operator/FilterOperator.kt:14-25), ProjectionOperator.next
+// (M/operator/ProjectionOperator.kt:15-19), MemorySourceOperator.next
+// (M/operator/MemorySourceOperator.kt:18-36) and GlobalAggregationOperator.open
+// (M/operator/GlobalAggregationOperator.kt:10-25).
+//
+// Row -> thread mapping.  A CTA has QE_BLOCK = 256 threads (8 warps).  A tile is
+// 8 warps x STEPS steps x (32 lanes x VEC rows).  Warp w owns the contiguous
+// rows [w*STEPS*32*VEC, (w+1)*STEPS*32*VEC) of the tile; in step s lane l holds
+// the VEC adjacent rows starting at  s*32*VEC + l*VEC, so one step of one warp
+// reads 32*VEC*8 contiguous bytes per 8-byte column with one 128-bit (VEC=2) or
+// 256-bit (VEC=4) load per lane, and VEC*32 validity bits = whole 32-bit words.
+//
+// This header must compile under NVRTC: no standard headers, no host code.
+#ifndef QE_DEVICE_CUH
+#define QE_DEVICE_CUH
+
+#include "qe_ops.h"
+
+#define QE_BLOCK 256
+#define QE_WARPS 8
+#define QE_FULL_MASK 0xffffffffu
+
+#define QE_MAX_COLS 16      // referenced scan columns per pipeline
+#define QE_MAX_OUTS 8       // projection outputs per pipeline
+#define QE_MAX_AGGS 8
+
+// physical column types (values match include/qegpu.h)
+#define QE_T_F64 1
+#define QE_T_BOOL 2
+#define QE_T_I64 3
+#define QE_T_DATE32 4
+
+// aggregation functions (ordinals of the reference's AggregationFunction enum,
+// M/ast/Functions.kt:24-26)
+#define QE_AGG_MIN 0
+#define QE_AGG_MAX 1
+#define QE_AGG_SUM 2
+#define QE_AGG_COUNT 3
+#define QE_AGG_AVG 4
+
+// Kernel arguments.  Column pointers are already offset to the first row of the
+// batch; every column / bitmap allocation is zero-padded to a whole number of
+// tiles, so loads never need a bounds check -- only the results are masked with
+// `row < nrows`.
+struct QeParams {
+    const void   *col_values[QE_MAX_COLS];
+    const qe_u32 *col_valid[QE_MAX_COLS];     // Arrow validity bitmap (LSB first, 1 = non-null), 0 = non-nullable
+    void         *out_values[QE_MAX_OUTS];    // f64 / i64 / i32 arrays, or bitmap words for BOOLEAN outputs
+    qe_u32       *out_valid[QE_MAX_OUTS];     // validity bitmap words of the output, 0 = statically non-null
+    qe_u32       *sel;                        // selection vector (row indices relative to the table), may be 0
+    qe_u64       *tile_state;                 // decoupled-lookback descriptors, one per tile, zeroed per run
+    qe_u32       *ticket;                     // dynamic tile counter, zeroed per run
+    qe_u64       *out_count;                  // number of rows kept
+    double       *agg_partials;               // [gridDim.x][QE_MAX_AGGS][4] = sum, count (bits), min, max
+    const qe_u32 *iprog;                      // interpreter only: serialized pipeline (qe_interp.cuh)
+    qe_i64        nrows;                      // rows in this batch
+    qe_i64        out_capacity;               // rows the compacted outputs can hold
+    qe_u32        ntiles;
+    qe_u32        sel_base;                   // table row index of the batch's first row
+};
+
+// ---------------------------------------------------------------- memory ops
+
+// Streaming loads: read-only path, no L1 allocation (every byte is used once).
+__device__ __forceinline__ void qe_ldg_f64x2(const double *p, double &a, double &b)
+{
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(a), "=d"(b) : "l"(p));
+}
+
+// 256-bit load (new in sm_100: LDG.E.256), with an evict-first L2 hint
+__device__ __forceinline__ void qe_ldg_f64x4(const double *p, double &a, double &b, double &c, double &d)
+{
+    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.f64 {%0,%1,%2,%3}, [%4];"
+                 : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+}
+
+__device__ __forceinline__ void qe_ldg_i64x2(const qe_i64 *p, qe_i64 &a, qe_i64 &b)
+{
+    asm volatile("ld.global.nc.L1::no_allocate.v2.s64 {%0,%1}, [%2];" : "=l"(a), "=l"(b) : "l"(p));
+}
+
+__device__ __forceinline__ void qe_ldg_i64x4(const qe_i64 *p, qe_i64 &a, qe_i64 &b, qe_i64 &c, qe_i64 &d)
+{
+    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.s64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(p));
+}
+
+__device__ __forceinline__ void qe_ldg_i32x2(const qe_i32 *p, qe_i32 &a, qe_i32 &b)
+{
+    asm volatile("ld.global.nc.L1::no_allocate.v2.s32 {%0,%1}, [%2];" : "=r"(a), "=r"(b) : "l"(p));
+}
+
+__device__ __forceinline__ void qe_ldg_i32x4(const qe_i32 *p, qe_i32 &a, qe_i32 &b, qe_i32 &c, qe_i32 &d)
+{
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "l"(p));
+}
+
+__device__ __forceinline__ qe_u32 qe_ldg_u32(const qe_u32 *p)
+{
+    qe_u32 v;
+    asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+
+// Lookback descriptors: value and status share one 64-bit word, so relaxed
+// gpu-scope accesses are enough (nothing else is published through them).
+__device__ __forceinline__ qe_u64 qe_ld_relaxed(const qe_u64 *p)
+{
+    qe_u64 v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void qe_st_relaxed(qe_u64 *p, qe_u64 v)
+{
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+
+// ------------------------------------------------------- column load helpers
+// `r` is the first of the VEC adjacent rows this lane holds (a multiple of VEC).
+
+template <int VEC>
+__device__ __forceinline__ void qe_load_f64(const void *col, qe_i64 r, double (&v)[VEC])
+{
+    const double *p = (const double *)col + r;
+    if constexpr (VEC == 4) qe_ldg_f64x4(p, v[0], v[1], v[2], v[3]);
+    else qe_ldg_f64x2(p, v[0], v[1]);
+}
+
+template <int VEC>
+__device__ __forceinline__ void qe_load_i64(const void *col, qe_i64 r, qe_i64 (&v)[VEC])
+{
+    const qe_i64 *p = (const qe_i64 *)col + r;
+    if constexpr (VEC == 4) qe_ldg_i64x4(p, v[0], v[1], v[2], v[3]);
+    else qe_ldg_i64x2(p, v[0], v[1]);
+}
+
+template <int VEC>
+__device__ __forceinline__ void qe_load_i32(const void *col, qe_i64 r, qe_i32 (&v)[VEC])
+{
+    const qe_i32 *p = (const qe_i32 *)col + r;
+    if constexpr (VEC == 4) qe_ldg_i32x4(p, v[0], v[1], v[2], v[3]);
+    else qe_ldg_i32x2(p, v[0], v[1]);
+}
+
+// The VEC bits of rows r .. r+VEC-1 of a bitmap.  The lanes of a warp ask for
+// VEC*32 consecutive bits = VEC/… whole 32-bit words; lanes that share a word
+// issue the same address, which the LSU broadcasts.
+template <int VEC>
+__device__ __forceinline__ qe_u32 qe_load_bits(const qe_u32 *bitmap, qe_i64 r)
+{
+    qe_u32 w = qe_ldg_u32(bitmap + (r >> 5));
+    return (w >> ((qe_u32)r & 31u)) & ((1u << VEC) - 1u);
+}
+
+// Dense output stores: the VEC adjacent values of one lane, one 128/256-bit store.
+template <int VEC>
+__device__ __forceinline__ void qe_store_f64(void *col, qe_i64 r, const double (&v)[VEC])
+{
+    double *p = (double *)col + r;
+    if constexpr (VEC == 4)
+        asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" :: "l"(p), "d"(v[0]), "d"(v[1]), "d"(v[2]), "d"(v[3]) : "memory");
+    else
+        asm volatile("st.global.v2.f64 [%0], {%1,%2};" :: "l"(p), "d"(v[0]), "d"(v[1]) : "memory");
+}
+
+template <int VEC>
+__device__ __forceinline__ void qe_store_i64(void *col, qe_i64 r, const qe_i64 (&v)[VEC])
+{
+    qe_i64 *p = (qe_i64 *)col + r;
+    if constexpr (VEC == 4)
+        asm volatile("st.global.v4.s64 [%0], {%1,%2,%3,%4};" :: "l"(p), "l"(v[0]), "l"(v[1]), "l"(v[2]), "l"(v[3]) : "memory");
+    else
+        asm volatile("st.global.v2.s64 [%0], {%1,%2};" :: "l"(p), "l"(v[0]), "l"(v[1]) : "memory");
+}
+
+template <int VEC>
+__device__ __forceinline__ void qe_store_i32(void *col, qe_i64 r, const qe_i32 (&v)[VEC])
+{
+    qe_i32 *p = (qe_i32 *)col + r;
+    if constexpr (VEC == 4)
+        asm volatile("st.global.v4.s32 [%0], {%1,%2,%3,%4};" :: "l"(p), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]) : "memory");
+    else
+        asm volatile("st.global.v2.s32 [%0], {%1,%2};" :: "l"(p), "r"(v[0]), "r"(v[1]) : "memory");
+}
+
+// ------------------------------------------------------------ warp utilities
+
+__device__ __forceinline__ qe_u32 qe_lane() { return threadIdx.x & 31u; }
+__device__ __forceinline__ qe_u32 qe_warp() { return threadIdx.x >> 5; }
+
+__device__ __forceinline__ qe_u32 qe_lanemask_lt()
+{
+    qe_u32 m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+__device__ __forceinline__ double qe_shfl_down_f64(double v, int d)
+{
+    return __shfl_down_sync(QE_FULL_MASK, v, d);
+}
+
+// Validity / boolean words of one warp step (dense output).  Lane l holds VEC
+// bits for rows l*VEC ..; the warp assembles the VEC 32-bit words with one
+// REDUX.OR each and lane 0 stores them.
+template <int VEC>
+__device__ __forceinline__ void qe_store_bits_dense(qe_u32 *bitmap, qe_i64 warp_row0, qe_u32 bits)
+{
+    const qe_u32 q = qe_lane() * VEC;                 // bit position inside the warp step
+    qe_u32 words[VEC];
+#pragma unroll
+    for (int h = 0; h < VEC; h++)
+        words[h] = __reduce_or_sync(QE_FULL_MASK, (q >> 5) == (qe_u32)h ? bits << (q & 31u) : 0u);
+    if (qe_lane() == 0) {
+        qe_u32 *dst = bitmap + (warp_row0 >> 5);
+        if constexpr (VEC == 4) {
+            asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};"
+                         :: "l"(dst), "r"(words[0]), "r"(words[1]), "r"(words[2]), "r"(words[3]) : "memory");
+        } else {
+            asm volatile("st.global.v2.u32 [%0], {%1,%2};" :: "l"(dst), "r"(words[0]), "r"(words[1]) : "memory");
+        }
+    }
+}
+
+// Compacted bit column: the kept rows of one warp step occupy output bits
+// [gpos, gpos + n) with n <= 32*VEC.  Every kept lane drops its bit at its rank,
+// the warp ORs the words together and lanes 0..VEC OR them into the (pre-zeroed)
+// output bitmap.  Tiles meet inside a word, hence the atomics; OR makes the
+// result independent of arrival order.
+template <int VEC>
+__device__ __forceinline__ void qe_store_bits_compact(qe_u32 *bitmap, qe_u64 gpos, const qe_u32 (&rank)[VEC],
+                                                      qe_u32 keep, qe_u32 bits)
+{
+    qe_u32 words[VEC + 1];
+#pragma unroll
+    for (int h = 0; h < VEC; h++) {
+        qe_u32 mine = 0;
+#pragma unroll
+        for (int j = 0; j < VEC; j++) {
+            const bool on = ((keep >> j) & 1u) && ((bits >> j) & 1u) && (rank[j] >> 5) == (qe_u32)h;
+            mine |= on ? 1u << (rank[j] & 31u) : 0u;
+        }
+        words[h] = __reduce_or_sync(QE_FULL_MASK, mine);
+    }
+    words[VEC] = 0;
+    const qe_u32 sh = (qe_u32)gpos & 31u;
+    const qe_u32 l = qe_lane();
+    if (l <= VEC) {
+        // word l of the shifted bit string = (words[l] << sh) | (words[l-1] >> (32 - sh))
+        qe_u32 cur = 0, prev = 0;
+#pragma unroll
+        for (int h = 0; h <= VEC; h++) {
+            if ((qe_u32)h == l) cur = words[h];
+            if ((qe_u32)h + 1 == l) prev = words[h];
+        }
+        const qe_u32 v = (cur << sh) | (sh ? prev >> (32u - sh) : 0u);
+        if (v) atomicOr(bitmap + (gpos >> 5) + l, v);
+    }
+}
+
+// --------------------------------------------------------- decoupled lookback
+// Single-pass prefix over the per-tile kept-row counts (Merrill & Garland).
+// Descriptor = status (2 bits) | value (62 bits).  Tiles are handed out through
+// an atomic ticket, so every predecessor of a tile is already resident or done
+// and the spin below cannot deadlock.
+
+#define QE_TS_INVALID   0ull
+#define QE_TS_AGGREGATE 1ull
+#define QE_TS_PREFIX    2ull
+#define QE_TS_VALUE_MASK ((1ull << 62) - 1ull)
+
+// Called by warp 0.  Returns the number of kept rows in all earlier tiles.
+__device__ __forceinline__ qe_u64 qe_lookback(qe_u64 *state, qe_u32 tile, qe_u32 tile_total)
+{
+    const qe_u32 lane = qe_lane();
+    if (tile == 0) {
+        if (lane == 0) qe_st_relaxed(state, (QE_TS_PREFIX << 62) | (qe_u64)tile_total);
+        return 0;
+    }
+    if (lane == 0) qe_st_relaxed(state + tile, (QE_TS_AGGREGATE << 62) | (qe_u64)tile_total);
+
+    qe_u64 exclusive = 0;
+    qe_i64 look = (qe_i64)tile - 1;
+    for (;;) {
+        const qe_i64 idx = look - (qe_i64)lane;
+        qe_u64 d = QE_TS_PREFIX << 62;                       // before tile 0: prefix 0
+        if (idx >= 0) {
+            do { d = qe_ld_relaxed(state + idx); } while ((d >> 62) == QE_TS_INVALID);
+        }
+        const qe_u32 has_prefix = __ballot_sync(QE_FULL_MASK, (d >> 62) == QE_TS_PREFIX);
+        const qe_u32 first = has_prefix ? (qe_u32)__ffs((int)has_prefix) - 1u : 32u;
+        qe_u64 v = lane <= first ? (d & QE_TS_VALUE_MASK) : 0ull;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(QE_FULL_MASK, v, o);
+        exclusive += v;
+        if (has_prefix) break;
+        look -= 32;
+    }
+    if (lane == 0) qe_st_relaxed(state + tile, (QE_TS_PREFIX << 62) | (exclusive + (qe_u64)tile_total));
+    return exclusive;
+}
+
+// ------------------------------------------------------------- accumulators
+// One per aggregate, per thread.  Only the fields the function needs are
+// touched (FN is a compile-time constant), so the rest folds away.
+struct QeAcc {
+    double sum;
+    qe_i64 count;
+    double mn;
+    double mx;
+};
+
+__device__ __forceinline__ void qe_acc_init(QeAcc &a)
+{
+    a.sum = 0.0;
+    a.count = 0;
+    a.mn = qe_bits_f64((qe_i64)0x7ff0000000000000LL);       // +Infinity, M/evaluator/Accumulators.kt:57
+    a.mx = qe_bits_f64((qe_i64)0xfff0000000000000ULL);      // -Infinity, :75
+}
+
+// accumulate(value) when the value is non-null and the row passed the filter
+// (M/operator/GlobalAggregationOperator.kt:17-20)
+template <int FN>
+__device__ __forceinline__ void qe_acc_add(QeAcc &a, double v, bool on)
+{
+    if (on) {
+        a.count += 1;
+        if (FN == QE_AGG_SUM || FN == QE_AGG_AVG) a.sum += v;
+        if (FN == QE_AGG_MIN) a.mn = qe_math_min(a.mn, v);
+        if (FN == QE_AGG_MAX) a.mx = qe_math_max(a.mx, v);
+    }
+}
+
+__device__ __forceinline__ qe_i64 qe_shfl_down_i64(qe_i64 v, int d)
+{
+    return __shfl_down_sync(QE_FULL_MASK, v, d);
+}
+
+// Merge `b` into `a` (fixed operand order: a is the lower-numbered lane / warp / CTA)
+template <int FN>
+__device__ __forceinline__ void qe_acc_merge(QeAcc &a, const QeAcc &b)
+{
+    a.count += b.count;
+    if (FN == QE_AGG_SUM || FN == QE_AGG_AVG) a.sum += b.sum;
+    if (FN == QE_AGG_MIN) a.mn = qe_math_min(a.mn, b.mn);
+    if (FN == QE_AGG_MAX) a.mx = qe_math_max(a.mx, b.mx);
+}
+
+template <int FN>
+__device__ __forceinline__ void qe_acc_warp_reduce(QeAcc &a)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        QeAcc b;
+        b.count = qe_shfl_down_i64(a.count, o);
+        b.sum = (FN == QE_AGG_SUM || FN == QE_AGG_AVG) ? qe_shfl_down_f64(a.sum, o) : 0.0;
+        b.mn = (FN == QE_AGG_MIN) ? qe_shfl_down_f64(a.mn, o) : a.mn;
+        b.mx = (FN == QE_AGG_MAX) ? qe_shfl_down_f64(a.mx, o) : a.mx;
+        qe_acc_merge<FN>(a, b);
+    }
+}
+
+// Block reduce in fixed order (lane tree, then warps 0..7 sequentially) and
+// write this CTA's partial.  `slot` is a [QE_WARPS] shared array.
+template <int FN>
+__device__ __forceinline__ void qe_acc_block_reduce_store(QeAcc a, QeAcc *slot, double *partials, int k)
+{
+    qe_acc_warp_reduce<FN>(a);
+    __syncthreads();
+    if (qe_lane() == 0) slot[qe_warp()] = a;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        QeAcc t = slot[0];
+        for (int w = 1; w < QE_WARPS; w++) qe_acc_merge<FN>(t, slot[w]);
+        double *dst = partials + ((qe_i64)blockIdx.x * QE_MAX_AGGS + k) * 4;
+        dst[0] = t.sum;
+        dst[1] = qe_bits_f64(t.count);
+        dst[2] = t.mn;
+        dst[3] = t.mx;
+    }
+}
+
+// Field-agnostic merge (every field folded; fields an aggregate does not use
+// hold their init values or are ignored by the host).  Used by the interpreter
+// and by the final reduce of the per-CTA partials.
+__device__ __forceinline__ void qe_acc_merge_all(QeAcc &a, const QeAcc &b)
+{
+    a.count += b.count;
+    a.sum += b.sum;
+    a.mn = qe_math_min(a.mn, b.mn);
+    a.mx = qe_math_max(a.mx, b.mx);
+}
+
+// Same block reduce as qe_acc_block_reduce_store, all four fields.
+__device__ __forceinline__ void qe_acc_block_reduce_store_all(QeAcc a, QeAcc *slot, double *partials, int k)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        QeAcc b;
+        b.count = qe_shfl_down_i64(a.count, o);
+        b.sum = qe_shfl_down_f64(a.sum, o);
+        b.mn = qe_shfl_down_f64(a.mn, o);
+        b.mx = qe_shfl_down_f64(a.mx, o);
+        qe_acc_merge_all(a, b);
+    }
+    __syncthreads();
+    if (qe_lane() == 0) slot[qe_warp()] = a;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        QeAcc t = slot[0];
+        for (int w = 1; w < QE_WARPS; w++) qe_acc_merge_all(t, slot[w]);
+        double *dst = partials + ((qe_i64)blockIdx.x * QE_MAX_AGGS + k) * 4;
+        dst[0] = t.sum;
+        dst[1] = qe_bits_f64(t.count);
+        dst[2] = t.mn;
+        dst[3] = t.mx;
+    }
+}
+
+// ------------------------------------------------------------------ kernels
+//
+// What a pipeline program P provides:
+//   static constexpr int STEPS, VEC, NBITCOLS;
+//   struct Row;   inputs of one row, in registers
+//   struct Out;   outputs of one row (projection values), in registers
+//   static void load(const QeParams&, qe_i64 r, Row (&rows)[VEC]);      r = lane's first row
+//   static bool eval(const QeParams&, const Row&, Out&);               returns the filter verdict
+//                                                                      (non-null AND true, FilterOperator.kt:20)
+//   filter kernel:
+//     static void emit(const QeParams&, qe_u64 pos, const Out&);       value outputs at compacted position
+//     static qe_u32* bitcol(const QeParams&, int b);                   b-th compacted bit column (or 0)
+//     static bool bit(const Out&, int b);
+//   project kernel:
+//     static void emit_dense(const QeParams&, qe_i64 r, const Out (&)[VEC], qe_u32 inb);
+//     bitcol / bit as above (dense words)
+//   agg kernel:
+//     struct Accs; static void acc_init(Accs&); static void acc_add(const QeParams&, Accs&, const Out&, bool keep);
+//     static void acc_store(const QeParams&, Accs&, QeAcc *slot);
+
+template <class P>
+__device__ __forceinline__ void qe_tile_eval(const QeParams &p, qe_i64 warp_row0,
+                                             typename P::Out (&outs)[P::STEPS][P::VEC],
+                                             qe_u32 (&keep)[P::STEPS], qe_u32 (&inb)[P::STEPS])
+{
+    constexpr int STEPS = P::STEPS, VEC = P::VEC;
+    typename P::Row rows[STEPS][VEC];
+    const qe_u32 lane = qe_lane();
+    // issue every load of the tile first: STEPS x (columns) independent 16/32-byte
+    // requests per thread in flight before the first use
+#pragma unroll
+    for (int s = 0; s < STEPS; s++)
+        P::load(p, warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC, rows[s]);
+#pragma unroll
+    for (int s = 0; s < STEPS; s++) {
+        const qe_i64 r = warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC;
+        keep[s] = 0;
+        inb[s] = 0;
+#pragma unroll
+        for (int j = 0; j < VEC; j++) {
+            const bool in = r + j < p.nrows;
+            const bool k = P::eval(p, rows[s][j], outs[s][j]) && in;
+            keep[s] |= (k ? 1u : 0u) << j;
+            inb[s] |= (in ? 1u : 0u) << j;
+        }
+    }
+}
+
+template <class P>
+__device__ __forceinline__ void qe_filter_body(const QeParams &p)
+{
+    constexpr int STEPS = P::STEPS, VEC = P::VEC;
+    constexpr int WARP_ROWS = STEPS * 32 * VEC;
+    constexpr int TILE = QE_WARPS * WARP_ROWS;
+
+    __shared__ qe_u32 s_tile;
+    __shared__ qe_u32 s_warp_cnt[QE_WARPS];
+    __shared__ qe_u64 s_prefix;
+
+    const qe_u32 lane = qe_lane(), warp = qe_warp();
+    const qe_u32 lt = qe_lanemask_lt();
+
+    for (;;) {
+        if (threadIdx.x == 0) s_tile = atomicAdd(p.ticket, 1u);
+        __syncthreads();
+        const qe_u32 tile = s_tile;
+        if (tile >= p.ntiles) break;
+        const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
+
+        typename P::Out outs[STEPS][VEC];
+        qe_u32 keep[STEPS], inb[STEPS];
+        qe_tile_eval<P>(p, warp_row0, outs, keep, inb);
+
+        // rank of every kept row inside its warp's slice (row order = step, lane, j)
+        qe_u32 rank[STEPS][VEC];
+        qe_u32 step_off[STEPS];
+        qe_u32 wcnt = 0;
+#pragma unroll
+        for (int s = 0; s < STEPS; s++) {
+            qe_u32 before = 0, total = 0;
+#pragma unroll
+            for (int j = 0; j < VEC; j++) {
+                const qe_u32 b = __ballot_sync(QE_FULL_MASK, (keep[s] >> j) & 1u);
+                before += __popc(b & lt);
+                total += __popc(b);
+            }
+            step_off[s] = wcnt;
+            qe_u32 r = before;
+#pragma unroll
+            for (int j = 0; j < VEC; j++) {
+                rank[s][j] = r;                      // rank within the warp step
+                r += (keep[s] >> j) & 1u;
+            }
+            wcnt += total;
+        }
+        if (lane == 0) s_warp_cnt[warp] = wcnt;
+        __syncthreads();
+
+        qe_u32 woff = 0, tile_total = 0;
+#pragma unroll
+        for (int w = 0; w < QE_WARPS; w++) {
+            const qe_u32 c = s_warp_cnt[w];
+            woff += (qe_u32)w < warp ? c : 0u;
+            tile_total += c;
+        }
+        if (warp == 0) {
+            const qe_u64 excl = qe_lookback(p.tile_state, tile, tile_total);
+            if (lane == 0) {
+                s_prefix = excl;
+                if (tile == p.ntiles - 1) *p.out_count = excl + tile_total;
+            }
+        }
+        __syncthreads();
+        const qe_u64 gbase = s_prefix + woff;
+
+        // ordered scatter: a warp step's kept rows land on consecutive addresses
+#pragma unroll
+        for (int s = 0; s < STEPS; s++) {
+            const qe_u64 gstep = gbase + step_off[s];
+            const qe_i64 r = warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC;
+#pragma unroll
+            for (int j = 0; j < VEC; j++) {
+                const qe_u64 pos = gstep + rank[s][j];
+                if (((keep[s] >> j) & 1u) && pos < (qe_u64)p.out_capacity) {
+                    if (p.sel) p.sel[pos] = p.sel_base + (qe_u32)(r + j);
+                    P::emit(p, pos, outs[s][j]);
+                }
+            }
+            if (P::NBITCOLS > 0 && gstep < (qe_u64)p.out_capacity) {
+#pragma unroll
+                for (int b = 0; b < P::NBITCOLS; b++) {
+                    qe_u32 *bm = P::bitcol(p, b);
+                    if (bm) {
+                        qe_u32 bits = 0;
+#pragma unroll
+                        for (int j = 0; j < VEC; j++) bits |= (P::bit(outs[s][j], b) ? 1u : 0u) << j;
+                        qe_store_bits_compact<VEC>(bm, gstep, rank[s], keep[s], bits);
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <class P>
+__device__ __forceinline__ void qe_project_body(const QeParams &p)
+{
+    constexpr int STEPS = P::STEPS, VEC = P::VEC;
+    constexpr int WARP_ROWS = STEPS * 32 * VEC;
+    constexpr int TILE = QE_WARPS * WARP_ROWS;
+    const qe_u32 lane = qe_lane(), warp = qe_warp();
+
+    for (qe_u32 tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+        const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
+        typename P::Out outs[STEPS][VEC];
+        qe_u32 keep[STEPS], inb[STEPS];
+        qe_tile_eval<P>(p, warp_row0, outs, keep, inb);
+#pragma unroll
+        for (int s = 0; s < STEPS; s++) {
+            const qe_i64 step_row0 = warp_row0 + (qe_i64)s * 32 * VEC;
+            P::emit_dense(p, step_row0 + lane * VEC, outs[s], inb[s]);
+#pragma unroll
+            for (int b = 0; b < P::NBITCOLS; b++) {
+                qe_u32 *bm = P::bitcol(p, b);
+                if (bm) {
+                    qe_u32 bits = 0;
+#pragma unroll
+                    for (int j = 0; j < VEC; j++) bits |= (P::bit(outs[s][j], b) ? 1u : 0u) << j;
+                    qe_store_bits_dense<VEC>(bm, step_row0, bits & inb[s]);
+                }
+            }
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) *p.out_count = (qe_u64)p.nrows;
+}
+
+template <class P>
+__device__ __forceinline__ void qe_agg_body(const QeParams &p)
+{
+    constexpr int STEPS = P::STEPS, VEC = P::VEC;
+    constexpr int WARP_ROWS = STEPS * 32 * VEC;
+    constexpr int TILE = QE_WARPS * WARP_ROWS;
+    __shared__ QeAcc s_slot[QE_WARPS];
+    const qe_u32 warp = qe_warp();
+
+    typename P::Accs accs;
+    P::acc_init(accs);
+    qe_i64 kept = 0;
+    // static tile -> CTA assignment: the summation order depends only on the grid size
+    for (qe_u32 tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+        const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
+        typename P::Out outs[STEPS][VEC];
+        qe_u32 keep[STEPS], inb[STEPS];
+        qe_tile_eval<P>(p, warp_row0, outs, keep, inb);
+#pragma unroll
+        for (int s = 0; s < STEPS; s++) {
+#pragma unroll
+            for (int j = 0; j < VEC; j++) {
+                const bool k = (keep[s] >> j) & 1u;
+                P::acc_add(p, accs, outs[s][j], k);
+                kept += k ? 1 : 0;
+            }
+        }
+    }
+    P::acc_store(p, accs, s_slot);
+    // rows that reached the aggregation (diagnostic; the result row count is 1)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) kept += __shfl_down_sync(QE_FULL_MASK, kept, o);
+    if (qe_lane() == 0 && kept) atomicAdd((unsigned long long *)p.out_count, (unsigned long long)kept);
+}
+
+#endif  // QE_DEVICE_CUH

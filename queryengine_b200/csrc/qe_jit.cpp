@@ -1,0 +1,133 @@
+// qe_jit.cpp -- see qe_jit.h
+#include "qe_jit.h"
+
+#include <dlfcn.h>
+
+#include <cstdlib>
+#include <mutex>
+
+namespace qe {
+namespace {
+
+// The handful of NVRTC entry points used, resolved with dlsym.
+typedef struct _nvrtcProgram *nvrtcProgram;
+typedef int nvrtcResult;
+
+struct Nvrtc {
+    void *handle = nullptr;
+    std::string why;
+    nvrtcResult (*CreateProgram)(nvrtcProgram *, const char *, const char *, int, const char *const *, const char *const *) = nullptr;
+    nvrtcResult (*CompileProgram)(nvrtcProgram, int, const char *const *) = nullptr;
+    nvrtcResult (*DestroyProgram)(nvrtcProgram *) = nullptr;
+    nvrtcResult (*GetCUBINSize)(nvrtcProgram, size_t *) = nullptr;
+    nvrtcResult (*GetCUBIN)(nvrtcProgram, char *) = nullptr;
+    nvrtcResult (*GetProgramLogSize)(nvrtcProgram, size_t *) = nullptr;
+    nvrtcResult (*GetProgramLog)(nvrtcProgram, char *) = nullptr;
+    const char *(*GetErrorString)(nvrtcResult) = nullptr;
+};
+
+Nvrtc &nvrtc()
+{
+    static Nvrtc n;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        const char *candidates[] = {
+            getenv("QE_NVRTC_PATH"),
+            "libnvrtc.so.12",
+            "libnvrtc.so",
+            "/usr/local/cuda/lib64/libnvrtc.so.12",
+            "/usr/local/cuda/targets/x86_64-linux/lib/libnvrtc.so.12",
+            "libnvrtc.so.13",
+        };
+        for (const char *c : candidates) {
+            if (!c || !*c) continue;
+            n.handle = dlopen(c, RTLD_NOW | RTLD_LOCAL);
+            if (n.handle) break;
+        }
+        if (!n.handle) { n.why = "libnvrtc.so.12 not found (set QE_NVRTC_PATH)"; return; }
+#define QE_SYM(name) \
+        *(void **)(&n.name) = dlsym(n.handle, "nvrtc" #name); \
+        if (!n.name) { n.why = "nvrtc" #name " missing from libnvrtc"; n.handle = nullptr; return; }
+        QE_SYM(CreateProgram) QE_SYM(CompileProgram) QE_SYM(DestroyProgram) QE_SYM(GetCUBINSize) QE_SYM(GetCUBIN)
+        QE_SYM(GetProgramLogSize) QE_SYM(GetProgramLog) QE_SYM(GetErrorString)
+#undef QE_SYM
+    });
+    return n;
+}
+
+}  // namespace
+
+bool jit_available(std::string *why)
+{
+    Nvrtc &n = nvrtc();
+    if (!n.handle && why) *why = n.why;
+    return n.handle != nullptr;
+}
+
+bool jit_compile(const std::string &source, std::vector<char> &cubin, std::string &log)
+{
+    Nvrtc &n = nvrtc();
+    if (!n.handle) { log = n.why; return false; }
+    const char *headers[] = {kEmbeddedDeviceHeader, kEmbeddedOpsHeader};
+    const char *names[] = {"qe_device.cuh", "qe_ops.h"};
+    nvrtcProgram prog = nullptr;
+    nvrtcResult rc = n.CreateProgram(&prog, source.c_str(), "qe_pipeline.cu", 2, headers, names);
+    if (rc != 0) { log = std::string("nvrtcCreateProgram: ") + n.GetErrorString(rc); return false; }
+    // -fmad=false: a*b+c must stay a separate multiply and add, as on the JVM
+    const char *opts[] = {"--gpu-architecture=sm_100a", "--std=c++17", "--fmad=false", "-lineinfo"};
+    rc = n.CompileProgram(prog, 4, opts);
+    size_t logsz = 0;
+    n.GetProgramLogSize(prog, &logsz);
+    if (logsz > 1) {
+        std::vector<char> buf(logsz);
+        n.GetProgramLog(prog, buf.data());
+        log.assign(buf.data());
+    }
+    if (rc != 0) {
+        log = std::string("nvrtcCompileProgram: ") + n.GetErrorString(rc) + "\n" + log;
+        n.DestroyProgram(&prog);
+        return false;
+    }
+    size_t sz = 0;
+    rc = n.GetCUBINSize(prog, &sz);
+    if (rc != 0 || sz == 0) {
+        log = "nvrtcGetCUBINSize failed";
+        n.DestroyProgram(&prog);
+        return false;
+    }
+    cubin.resize(sz);
+    n.GetCUBIN(prog, cubin.data());
+    n.DestroyProgram(&prog);
+    return true;
+}
+
+bool jit_load(const std::vector<char> &cubin, const char *entry, JitKernel &out, std::string &err)
+{
+    cudaError_t e = cudaLibraryLoadData(&out.library, cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0);
+    if (e != cudaSuccess) { err = std::string("cudaLibraryLoadData: ") + cudaGetErrorString(e); return false; }
+    e = cudaLibraryGetKernel(&out.kernel, out.library, entry);
+    if (e != cudaSuccess) {
+        err = std::string("cudaLibraryGetKernel: ") + cudaGetErrorString(e);
+        cudaLibraryUnload(out.library);
+        out.library = nullptr;
+        return false;
+    }
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, (const void *)out.kernel, 256, 0) == cudaSuccess && n > 0)
+        out.blocks_per_sm = n;
+    else
+        (void)cudaGetLastError();
+    cudaFuncAttributes fa;
+    if (cudaFuncGetAttributes(&fa, (const void *)out.kernel) == cudaSuccess) out.regs = fa.numRegs;
+    else (void)cudaGetLastError();
+    return true;
+}
+
+void jit_unload(JitKernel &k)
+{
+    if (k.library) cudaLibraryUnload(k.library);
+    k.library = nullptr;
+    k.kernel = nullptr;
+}
+
+}  // namespace qe

@@ -1,0 +1,39 @@
+// qe_jit.h -- run-time compilation of generated pipeline programs with NVRTC
+// (loaded lazily with dlopen, so libqegpu.so itself has no link-time
+// dependency on it) and loading of the resulting sm_100a cubin through the
+// CUDA runtime's library API.
+#ifndef QE_JIT_H
+#define QE_JIT_H
+
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+namespace qe {
+
+// Text of the device headers, embedded at build time (qe_embedded_src.cpp is
+// generated from qe_device.cuh / qe_ops.h by the build script).
+extern const char *const kEmbeddedDeviceHeader;
+extern const char *const kEmbeddedOpsHeader;
+
+struct JitKernel {
+    cudaLibrary_t library = nullptr;
+    cudaKernel_t kernel = nullptr;
+    int blocks_per_sm = 1;
+    int regs = 0;
+};
+
+// True when libnvrtc could be loaded.  `why` receives the reason otherwise.
+bool jit_available(std::string *why);
+
+// Compile `source` (which includes "qe_device.cuh") to a cubin for sm_100a.
+// Does not need a GPU.  Returns false and fills `log` on failure.
+bool jit_compile(const std::string &source, std::vector<char> &cubin, std::string &log);
+
+// Load a cubin on the current device and look up the entry point.
+bool jit_load(const std::vector<char> &cubin, const char *entry, JitKernel &out, std::string &err);
+void jit_unload(JitKernel &k);
+
+}  // namespace qe
+#endif

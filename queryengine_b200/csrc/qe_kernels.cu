@@ -1,0 +1,148 @@
+// qe_kernels.cu -- ahead-of-time compiled kernels of libqegpu.so (sm_100a):
+//   * the three kernel bodies of qe_device.cuh instantiated with the generic
+//     interpreter program (always-available path, cross-check for generated code)
+//   * the final fixed-order reduce of per-CTA aggregate partials (K4's on-GPU half)
+//   * the synthetic column generators (K5)
+// Compiled with -fmad=false so arithmetic matches the JVM's unfused DMUL/DADD.
+#include <cuda_runtime.h>
+
+#include "qe_interp.cuh"
+#include "qe_kernels.h"
+
+namespace {
+
+using InterpProgram = QeInterpProgram<QE_INTERP_STEPS, QE_INTERP_VEC>;
+
+__global__ void __launch_bounds__(QE_BLOCK) qe_interp_filter_kernel(const __grid_constant__ QeParams p)
+{
+    qe_filter_body<InterpProgram>(p);
+}
+
+__global__ void __launch_bounds__(QE_BLOCK) qe_interp_project_kernel(const __grid_constant__ QeParams p)
+{
+    qe_project_body<InterpProgram>(p);
+}
+
+__global__ void __launch_bounds__(QE_BLOCK) qe_interp_agg_kernel(const __grid_constant__ QeParams p)
+{
+    qe_agg_body<InterpProgram>(p);
+}
+
+// One block.  Thread t folds CTAs t, t+256, ... in order, then the fixed block
+// tree: the result depends only on the number of partials.
+__global__ void __launch_bounds__(QE_BLOCK) qe_agg_final_kernel(const double *partials, int nblocks, int nagg, double *out)
+{
+    __shared__ QeAcc s_slot[QE_WARPS];
+    for (int k = 0; k < nagg; k++) {
+        QeAcc a;
+        qe_acc_init(a);
+        for (int b = threadIdx.x; b < nblocks; b += QE_BLOCK) {
+            const double *src = partials + ((qe_i64)b * QE_MAX_AGGS + k) * 4;
+            QeAcc x;
+            x.sum = src[0];
+            x.count = qe_f64_bits(src[1]);
+            x.mn = src[2];
+            x.mx = src[3];
+            qe_acc_merge_all(a, x);
+        }
+        // blockIdx.x == 0, so the helper writes slot k of "CTA 0" of `out`
+        qe_acc_block_reduce_store_all(a, s_slot, out, k);
+    }
+}
+
+// ---- synthetic columns ------------------------------------------------------
+// Counter-based: value(i) is a pure function of (seed, global row index i).
+
+__device__ __forceinline__ qe_u64 qe_splitmix64(qe_u64 x)
+{
+    x += 0x9e3779b97f4a7c15ull;
+    x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ull;
+    x = (x ^ (x >> 27)) * 0x94d049bb133111ebull;
+    return x ^ (x >> 31);
+}
+
+__device__ __forceinline__ double qe_gen_value(int kind, qe_u64 seed, qe_u64 i, double p0, double p1)
+{
+    const qe_u64 h = qe_splitmix64(seed ^ i);
+    switch (kind) {
+    case 0: return (double)(h >> 24);                                          // QE_GEN_UNIFORM_U40
+    case 1: {                                                                  // QE_GEN_UNIFORM_INT
+        const qe_u64 span = (qe_u64)(p1 - p0) + 1ull;
+        return p0 + (double)(h % span);
+    }
+    case 2: return p0 + ((double)(h >> 11) * (1.0 / 9007199254740992.0)) * (p1 - p0);   // QE_GEN_UNIFORM_REAL
+    case 3: {                                                                  // QE_GEN_CENTS
+        const qe_u64 span = (qe_u64)(p1 - p0) + 1ull;
+        return (p0 + (double)(h % span)) / 100.0;
+    }
+    default: return (double)i;                                                 // QE_GEN_ROW_INDEX
+    }
+}
+
+__global__ void qe_generate_kernel(void *values, qe_u32 *validity, int type, int kind, qe_u64 seed, double p0, double p1,
+                                   double null_rate, qe_i64 row_offset, qe_i64 nrows)
+{
+    // one thread per 32 rows so that validity / boolean words are written whole
+    const qe_i64 word = (qe_i64)blockIdx.x * blockDim.x + threadIdx.x;
+    const qe_i64 r0 = word * 32;
+    if (r0 >= nrows) return;
+    qe_u32 vbits = 0, bbits = 0;
+    const qe_u64 null_threshold = null_rate >= 1.0 ? ~0ull : (qe_u64)(null_rate * 18446744073709551616.0);
+    for (int j = 0; j < 32; j++) {
+        const qe_i64 r = r0 + j;
+        if (r >= nrows) break;
+        const qe_u64 g = (qe_u64)(row_offset + r);
+        const double v = qe_gen_value(kind, seed, g, p0, p1);
+        if (type == QE_T_F64) ((double *)values)[r] = v;
+        else if (type == QE_T_I64) ((qe_i64 *)values)[r] = (qe_i64)v;
+        else if (type == QE_T_DATE32) ((qe_i32 *)values)[r] = (qe_i32)v;
+        else bbits |= (((qe_u64)v) & 1ull ? 1u : 0u) << j;
+        const bool valid = qe_splitmix64(~seed ^ (g * 0x9e3779b97f4a7c15ull)) >= null_threshold || null_rate <= 0.0;
+        vbits |= (valid ? 1u : 0u) << j;
+    }
+    if (type == QE_T_BOOL) ((qe_u32 *)values)[word] = bbits;
+    if (validity) validity[word] = vbits;
+}
+
+}  // namespace
+
+namespace qe {
+
+cudaError_t launch_interp(int mode, const QeParams &p, int grid, cudaStream_t stream)
+{
+    switch (mode) {
+    case 0: qe_interp_filter_kernel<<<grid, QE_BLOCK, 0, stream>>>(p); break;
+    case 1: qe_interp_project_kernel<<<grid, QE_BLOCK, 0, stream>>>(p); break;
+    default: qe_interp_agg_kernel<<<grid, QE_BLOCK, 0, stream>>>(p); break;
+    }
+    return cudaGetLastError();
+}
+
+int interp_blocks_per_sm(int mode)
+{
+    int n = 0;
+    const void *f = mode == 0 ? (const void *)qe_interp_filter_kernel
+                  : mode == 1 ? (const void *)qe_interp_project_kernel : (const void *)qe_interp_agg_kernel;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, f, QE_BLOCK, 0) != cudaSuccess || n < 1) n = 1;
+    return n;
+}
+
+cudaError_t launch_agg_final(const double *partials, int nblocks, int nagg, double *out, cudaStream_t stream)
+{
+    qe_agg_final_kernel<<<1, QE_BLOCK, 0, stream>>>(partials, nblocks, nagg, out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_generate(void *values, uint32_t *validity, int type, int kind, uint64_t seed, double p0, double p1,
+                            double null_rate, int64_t row_offset, int64_t nrows, cudaStream_t stream)
+{
+    const int64_t words = (nrows + 31) / 32;
+    if (words == 0) return cudaSuccess;
+    const int block = 128;
+    const int64_t grid = (words + block - 1) / block;
+    qe_generate_kernel<<<(unsigned)grid, block, 0, stream>>>(values, (qe_u32 *)validity, type, kind, (qe_u64)seed, p0, p1,
+                                                             null_rate, (qe_i64)row_offset, (qe_i64)nrows);
+    return cudaGetLastError();
+}
+
+}  // namespace qe

@@ -1,0 +1,1086 @@
+// qe_runtime.cu -- host runtime behind the C ABI of include/qegpu.h: context,
+// device memory pool, columnar tables with pinned-staged asynchronous uploads,
+// pipeline binding / specialisation / launch, results.  Host code only; the
+// kernels are in qe_device.cuh (bodies), qe_kernels.cu (ahead of time) and the
+// NVRTC-compiled output of qe_codegen.cpp.
+//
+// There is no CPU evaluation path anywhere in this file: a pipeline either runs
+// on the GPU or the call fails.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/qegpu.h"
+#include "qe_codegen.h"
+#include "qe_device.cuh"
+#include "qe_interp.cuh"
+#include "qe_jit.h"
+#include "qe_kernels.h"
+#include "qe_program.h"
+
+#define QE_VERSION_STRING "0.1.0"
+
+// Column allocations are padded so that any tile shape (<= 8192 rows) starting
+// at any 128-aligned batch offset can be loaded without bounds checks.
+static const int64_t kPadRows = 8192;
+static const size_t kStagingBytes = 16u << 20;
+
+// ------------------------------------------------------------------ errors
+
+static thread_local std::string tls_error;
+
+static int fail(int code, const std::string &msg)
+{
+    tls_error = msg;
+    return code;
+}
+
+static int fail_cuda(const char *what, cudaError_t e)
+{
+    tls_error = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
+    return QE_ERR_CUDA;
+}
+
+#define QE_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return fail_cuda(#call, e__); } while (0)
+
+extern "C" const char *qe_last_error(void) { return tls_error.c_str(); }
+extern "C" const char *qe_version(void) { return QE_VERSION_STRING; }
+
+// ------------------------------------------------------------- memory pool
+// Freed blocks are kept by size and handed out again, so steady-state pipeline
+// runs do no cudaMalloc / cudaFree (both synchronise the device).
+
+struct Pool {
+    std::multimap<size_t, void *> free_blocks;
+    std::unordered_map<void *, size_t> sizes;
+    size_t live = 0, reserved = 0;
+
+    static size_t round(size_t n)
+    {
+        const size_t q = n < (1u << 20) ? 512 : (2u << 20);
+        return (n + q - 1) / q * q;
+    }
+
+    cudaError_t alloc(size_t n, void **out)
+    {
+        n = round(n ? n : 1);
+        auto it = free_blocks.lower_bound(n);
+        if (it != free_blocks.end() && it->first <= n + n / 4) {
+            *out = it->second;
+            free_blocks.erase(it);
+            live += sizes[*out];
+            return cudaSuccess;
+        }
+        cudaError_t e = cudaMalloc(out, n);
+        if (e != cudaSuccess) {
+            // give cached blocks back and retry once
+            release_cached();
+            e = cudaMalloc(out, n);
+            if (e != cudaSuccess) return e;
+        }
+        sizes[*out] = n;
+        reserved += n;
+        live += n;
+        return cudaSuccess;
+    }
+
+    void free(void *p)
+    {
+        if (!p) return;
+        auto it = sizes.find(p);
+        if (it == sizes.end()) return;
+        live -= it->second;
+        free_blocks.emplace(it->second, p);
+    }
+
+    void release_cached()
+    {
+        for (auto &kv : free_blocks) {
+            cudaFree(kv.second);
+            reserved -= kv.first;
+            sizes.erase(kv.second);
+        }
+        free_blocks.clear();
+    }
+
+    void destroy()
+    {
+        release_cached();
+        for (auto &kv : sizes) cudaFree(kv.first);
+        sizes.clear();
+    }
+};
+
+// ----------------------------------------------------------------- handles
+
+struct JitEntry {
+    qe::JitKernel kernel;
+    qe::TileShape shape;
+};
+
+struct qe_ctx {
+    int device = 0;
+    int num_sms = 0;
+    cudaStream_t stream = nullptr;
+    Pool pool;
+    std::unordered_map<std::string, JitEntry> jit_cache;
+    // options
+    int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0;
+    int64_t launches = 0;
+    bool warned_no_nvrtc = false;
+    // pinned staging ring for uploads from pageable memory
+    void *staging[2] = {nullptr, nullptr};
+    cudaEvent_t staging_free[2] = {nullptr, nullptr};
+};
+
+struct qe_program {
+    qe_ctx *ctx;
+    qe::Program prog;
+};
+
+struct qe_table {
+    qe_ctx *ctx;
+    int64_t nrows = 0;
+    int64_t padded_rows = 0;
+    std::vector<qe_col_desc> cols;
+    std::vector<void *> values;
+    std::vector<uint32_t *> valid;
+};
+
+static size_t type_width(int type)
+{
+    switch (type) {
+    case QE_TYPE_DOUBLE: case QE_TYPE_INT64: return 8;
+    case QE_TYPE_DATE32: return 4;
+    default: return 0;    // BOOLEAN: bitmap
+    }
+}
+
+static size_t column_bytes(int type, int64_t rows)
+{
+    if (type == QE_TYPE_BOOLEAN) return (size_t)((rows + 31) / 32) * 4;
+    return (size_t)rows * type_width(type);
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev)
+    {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev); else prev = -1;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+// ----------------------------------------------------------------- context
+
+extern "C" int qe_ctx_create(int device, qe_ctx **out)
+{
+    if (!out) return fail(QE_ERR_INVALID_ARGUMENT, "out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        (void)cudaGetLastError();
+        return fail(QE_ERR_CUDA, std::string("no CUDA device available (") + cudaGetErrorString(e) +
+                                 "); libqegpu has no CPU fallback");
+    }
+    if (device < 0 || device >= count) return fail(QE_ERR_INVALID_ARGUMENT, "device index out of range");
+    QE_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    QE_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) {
+        return fail(QE_ERR_UNSUPPORTED, std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major) +
+                                        std::to_string(prop.minor) + "; this library is built for sm_100a (B200) only");
+    }
+    qe_ctx *ctx = new qe_ctx();
+    ctx->device = device;
+    ctx->num_sms = prop.multiProcessorCount;
+    e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { delete ctx; return fail_cuda("cudaStreamCreate", e); }
+    *out = ctx;
+    return QE_OK;
+}
+
+extern "C" int qe_ctx_destroy(qe_ctx *ctx)
+{
+    if (!ctx) return QE_OK;
+    DeviceGuard g(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (auto &kv : ctx->jit_cache) qe::jit_unload(kv.second.kernel);
+    for (int i = 0; i < 2; i++) {
+        if (ctx->staging[i]) cudaFreeHost(ctx->staging[i]);
+        if (ctx->staging_free[i]) cudaEventDestroy(ctx->staging_free[i]);
+    }
+    ctx->pool.destroy();
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return QE_OK;
+}
+
+extern "C" int qe_ctx_synchronize(qe_ctx *ctx)
+{
+    if (!ctx) return fail(QE_ERR_INVALID_ARGUMENT, "ctx is NULL");
+    DeviceGuard g(ctx->device);
+    QE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return QE_OK;
+}
+
+extern "C" void *qe_ctx_stream(qe_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+
+extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
+{
+    if (!ctx || !key) return fail(QE_ERR_INVALID_ARGUMENT, "ctx or key is NULL");
+    const std::string k(key);
+    if (k == "jit") ctx->opt_jit = value;
+    else if (k == "steps") {
+        if (value != 0 && value != 1 && value != 2 && value != 4 && value != 8)
+            return fail(QE_ERR_INVALID_ARGUMENT, "steps must be 0 (auto), 1, 2, 4 or 8");
+        ctx->opt_steps = value;
+    } else if (k == "vec") {
+        if (value != 0 && value != 2 && value != 4) return fail(QE_ERR_INVALID_ARGUMENT, "vec must be 0 (auto), 2 or 4");
+        ctx->opt_vec = value;
+    } else if (k == "grid_per_sm") {
+        if (value < 0 || value > 32) return fail(QE_ERR_INVALID_ARGUMENT, "grid_per_sm must be in [0, 32]");
+        ctx->opt_grid_per_sm = value;
+    } else return fail(QE_ERR_INVALID_ARGUMENT, "unknown option '" + k + "'");
+    return QE_OK;
+}
+
+extern "C" int64_t qe_ctx_launch_count(const qe_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int qe_host_alloc(size_t bytes, void **out)
+{
+    if (!out) return fail(QE_ERR_INVALID_ARGUMENT, "out is NULL");
+    QE_CUDA(cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault));
+    return QE_OK;
+}
+
+extern "C" int qe_host_free(void *p)
+{
+    if (p) QE_CUDA(cudaFreeHost(p));
+    return QE_OK;
+}
+
+// ----------------------------------------------------------------- program
+
+extern "C" int qe_program_create(qe_ctx *ctx, const uint32_t *words, size_t nwords, qe_program **out)
+{
+    if (!out) return fail(QE_ERR_INVALID_ARGUMENT, "out is NULL");
+    *out = nullptr;
+    if (!ctx) return fail(QE_ERR_INVALID_ARGUMENT, "ctx is NULL");
+    qe_program *p = new qe_program();
+    p->ctx = ctx;
+    std::string err;
+    if (!qe::parse_program(words, nwords, p->prog, err)) {
+        delete p;
+        return fail(QE_ERR_PROGRAM, err);
+    }
+    *out = p;
+    return QE_OK;
+}
+
+extern "C" int qe_program_destroy(qe_program *program)
+{
+    delete program;
+    return QE_OK;
+}
+
+// ------------------------------------------------------------------- table
+
+extern "C" int qe_table_create(qe_ctx *ctx, int ncols, const qe_col_desc *cols, int64_t nrows, qe_table **out)
+{
+    if (!out) return fail(QE_ERR_INVALID_ARGUMENT, "out is NULL");
+    *out = nullptr;
+    if (!ctx || !cols || ncols <= 0) return fail(QE_ERR_INVALID_ARGUMENT, "ctx/cols is NULL or ncols <= 0");
+    if (nrows < 0 || nrows > 0xffffffffLL)
+        return fail(QE_ERR_INVALID_ARGUMENT, "nrows must fit the 32-bit selection vector (shard larger tables by row range)");
+    for (int c = 0; c < ncols; c++) {
+        if (cols[c].type == QE_TYPE_STRING) return fail(QE_ERR_UNSUPPORTED, "STRING columns are not supported on the GPU path");
+        if (cols[c].type < 1 || cols[c].type > 4) return fail(QE_ERR_INVALID_ARGUMENT, "unknown column type");
+    }
+    DeviceGuard g(ctx->device);
+    qe_table *t = new qe_table();
+    t->ctx = ctx;
+    t->nrows = nrows;
+    t->padded_rows = (nrows + kPadRows - 1) / kPadRows * kPadRows + kPadRows;
+    t->cols.assign(cols, cols + ncols);
+    t->values.assign(ncols, nullptr);
+    t->valid.assign(ncols, nullptr);
+    for (int c = 0; c < ncols; c++) {
+        const size_t bytes = column_bytes(cols[c].type, t->padded_rows);
+        cudaError_t e = ctx->pool.alloc(bytes, &t->values[c]);
+        if (e == cudaSuccess && cols[c].nullable) {
+            void *v = nullptr;
+            e = ctx->pool.alloc(column_bytes(QE_TYPE_BOOLEAN, t->padded_rows), &v);
+            t->valid[c] = (uint32_t *)v;
+        }
+        if (e != cudaSuccess) {
+            (void)cudaGetLastError();
+            qe_table_destroy(t);
+            return fail_cuda("device allocation for table column", e);
+        }
+        // zero the padding (whole bitmaps; the tail of value arrays)
+        if (cols[c].type == QE_TYPE_BOOLEAN) {
+            cudaMemsetAsync(t->values[c], 0, bytes, ctx->stream);
+        } else {
+            const size_t w = type_width(cols[c].type);
+            const int64_t tail0 = nrows / 128 * 128;
+            cudaMemsetAsync((char *)t->values[c] + (size_t)tail0 * w, 0, (size_t)(t->padded_rows - tail0) * w, ctx->stream);
+        }
+        if (t->valid[c]) cudaMemsetAsync(t->valid[c], 0, column_bytes(QE_TYPE_BOOLEAN, t->padded_rows), ctx->stream);
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { qe_table_destroy(t); return fail_cuda("cudaMemsetAsync", e); }
+    *out = t;
+    return QE_OK;
+}
+
+extern "C" int qe_table_destroy(qe_table *table)
+{
+    if (!table) return QE_OK;
+    DeviceGuard g(table->ctx->device);
+    cudaStreamSynchronize(table->ctx->stream);
+    for (void *p : table->values) table->ctx->pool.free(p);
+    for (uint32_t *p : table->valid) table->ctx->pool.free(p);
+    delete table;
+    return QE_OK;
+}
+
+static bool is_pinned(const void *p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
+// host -> HBM.  Pinned sources go straight to cudaMemcpyAsync; pageable ones are
+// staged through two pinned buffers so the copy engine always has a chunk in
+// flight while the CPU fills the other.
+static int upload_bytes(qe_ctx *ctx, void *dst, const void *src, size_t bytes)
+{
+    if (bytes == 0) return QE_OK;
+    if (is_pinned(src)) {
+        QE_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        return QE_OK;
+    }
+    for (int i = 0; i < 2; i++) {
+        if (!ctx->staging[i]) {
+            QE_CUDA(cudaHostAlloc(&ctx->staging[i], kStagingBytes, cudaHostAllocDefault));
+            QE_CUDA(cudaEventCreateWithFlags(&ctx->staging_free[i], cudaEventDisableTiming));
+        }
+    }
+    size_t off = 0;
+    int slot = 0;
+    while (off < bytes) {
+        const size_t n = std::min(kStagingBytes, bytes - off);
+        QE_CUDA(cudaEventSynchronize(ctx->staging_free[slot]));       // previous copy out of this buffer done
+        memcpy(ctx->staging[slot], (const char *)src + off, n);
+        QE_CUDA(cudaMemcpyAsync((char *)dst + off, ctx->staging[slot], n, cudaMemcpyHostToDevice, ctx->stream));
+        QE_CUDA(cudaEventRecord(ctx->staging_free[slot], ctx->stream));
+        off += n;
+        slot ^= 1;
+    }
+    return QE_OK;
+}
+
+extern "C" int qe_table_upload(qe_table *table, int col, const void *values, const uint8_t *validity,
+                               int64_t row0, int64_t n)
+{
+    if (!table) return fail(QE_ERR_INVALID_ARGUMENT, "table is NULL");
+    if (col < 0 || col >= (int)table->cols.size()) return fail(QE_ERR_INVALID_ARGUMENT, "column index out of range");
+    if (row0 < 0 || n < 0 || row0 + n > table->nrows) return fail(QE_ERR_INVALID_ARGUMENT, "row range outside the table");
+    const qe_col_desc &cd = table->cols[col];
+    const bool bitmap_involved = cd.type == QE_TYPE_BOOLEAN || cd.nullable;
+    if (bitmap_involved && (row0 % 8) != 0) return fail(QE_ERR_INVALID_ARGUMENT, "row0 must be a multiple of 8 for bitmap columns");
+    qe_ctx *ctx = table->ctx;
+    DeviceGuard g(ctx->device);
+    int rc = QE_OK;
+    if (values) {
+        if (cd.type == QE_TYPE_BOOLEAN)
+            rc = upload_bytes(ctx, (char *)table->values[col] + row0 / 8, values, (size_t)((n + 7) / 8));
+        else
+            rc = upload_bytes(ctx, (char *)table->values[col] + (size_t)row0 * type_width(cd.type), values,
+                              (size_t)n * type_width(cd.type));
+        if (rc) return rc;
+    }
+    if (cd.nullable) {
+        char *dst = (char *)table->valid[col] + row0 / 8;
+        const size_t nbytes = (size_t)((n + 7) / 8);
+        if (validity) {
+            rc = upload_bytes(ctx, dst, validity, nbytes);
+        } else if (n > 0) {
+            // all non-null: whole bytes of ones, then the partial last byte
+            QE_CUDA(cudaMemsetAsync(dst, 0xff, (size_t)(n / 8), ctx->stream));
+            if (n % 8) QE_CUDA(cudaMemsetAsync(dst + n / 8, (1 << (n % 8)) - 1, 1, ctx->stream));
+        }
+        if (rc) return rc;
+    } else if (validity) {
+        return fail(QE_ERR_INVALID_ARGUMENT, "validity bitmap given for a column declared non-nullable");
+    }
+    return QE_OK;
+}
+
+extern "C" void *qe_table_device_ptr(qe_table *table, int col, int which)
+{
+    if (!table || col < 0 || col >= (int)table->cols.size()) return nullptr;
+    return which == 0 ? table->values[col] : (void *)table->valid[col];
+}
+
+extern "C" int qe_table_generate(qe_table *table, int col, int kind, uint64_t seed, double p0, double p1,
+                                 double null_rate, int64_t row_offset)
+{
+    if (!table) return fail(QE_ERR_INVALID_ARGUMENT, "table is NULL");
+    if (col < 0 || col >= (int)table->cols.size()) return fail(QE_ERR_INVALID_ARGUMENT, "column index out of range");
+    if (kind < 0 || kind > 4) return fail(QE_ERR_INVALID_ARGUMENT, "unknown generator kind");
+    qe_ctx *ctx = table->ctx;
+    DeviceGuard g(ctx->device);
+    QE_CUDA(qe::launch_generate(table->values[col], table->valid[col], table->cols[col].type, kind, seed, p0, p1,
+                                table->cols[col].nullable ? null_rate : 0.0, row_offset, table->nrows, ctx->stream));
+    ctx->launches++;
+    return QE_OK;
+}
+
+// ------------------------------------------------------------------ result
+
+struct DevBuf {
+    void *ptr = nullptr;
+    size_t bytes = 0;
+};
+
+struct ResultColumn {
+    int type = 0;
+    bool has_validity = false;
+    DevBuf values, valid;
+};
+
+// host-visible words the kernels' results are copied into (pinned)
+struct ResultHost {
+    unsigned long long count;
+    double agg[QE_MAX_AGGS][4];
+};
+
+struct qe_result {
+    qe_ctx *ctx = nullptr;
+    int mode = 0;                       // qe::KernelMode of the last run
+    bool used_jit = false;
+    int64_t batch_rows = 0;
+    int64_t capacity = 0;
+    std::vector<ResultColumn> cols;
+    std::vector<int> agg_fns;
+    DevBuf sel, ctl, partials, final_aggs;
+    ResultHost *host = nullptr;         // pinned
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_done = nullptr;
+    bool pending = false;
+    bool timed = false;                 // ev_begin / ev_end hold a run not yet folded into the totals
+    double total_kernel_ms = 0.0;       // device time of the main kernel over all runs into this result
+    int64_t kernel_runs = 0;
+};
+
+// Fold the last run's kernel time into the totals (the run must have completed).
+static void fold_timing(qe_result *r)
+{
+    if (!r->timed) return;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r->ev_begin, r->ev_end) == cudaSuccess) {
+        r->total_kernel_ms += ms;
+        r->kernel_runs += 1;
+    } else {
+        (void)cudaGetLastError();
+    }
+    r->timed = false;
+}
+
+static int ensure(qe_ctx *ctx, DevBuf &b, size_t bytes)
+{
+    if (b.ptr && b.bytes >= bytes) return QE_OK;
+    if (b.ptr) ctx->pool.free(b.ptr);
+    b.ptr = nullptr;
+    b.bytes = 0;
+    cudaError_t e = ctx->pool.alloc(bytes, &b.ptr);
+    if (e != cudaSuccess) { (void)cudaGetLastError(); return fail_cuda("device allocation for result", e); }
+    b.bytes = bytes;
+    return QE_OK;
+}
+
+static void release(qe_ctx *ctx, DevBuf &b)
+{
+    if (b.ptr) ctx->pool.free(b.ptr);
+    b.ptr = nullptr;
+    b.bytes = 0;
+}
+
+extern "C" int qe_result_destroy(qe_result *r)
+{
+    if (!r) return QE_OK;
+    DeviceGuard g(r->ctx->device);
+    if (r->pending) cudaEventSynchronize(r->ev_done);
+    for (ResultColumn &c : r->cols) { release(r->ctx, c.values); release(r->ctx, c.valid); }
+    release(r->ctx, r->sel);
+    release(r->ctx, r->ctl);
+    release(r->ctx, r->partials);
+    release(r->ctx, r->final_aggs);
+    if (r->host) cudaFreeHost(r->host);
+    if (r->ev_begin) cudaEventDestroy(r->ev_begin);
+    if (r->ev_end) cudaEventDestroy(r->ev_end);
+    if (r->ev_done) cudaEventDestroy(r->ev_done);
+    delete r;
+    return QE_OK;
+}
+
+// ---------------------------------------------------------------- pipeline
+
+static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMode mode)
+{
+    // Aim for ~128 bytes of column data in flight per thread: enough 16/32-byte
+    // requests outstanding to cover HBM latency at 8+ warps per scheduler,
+    // without pushing the register count past 64 (4 CTAs of 256 threads per SM).
+    size_t row_bytes = 0;
+    for (const qe::ColumnInfo &c : bp.slot_info) row_bytes += c.type == QE_TYPE_BOOLEAN ? 1 : type_width(c.type);
+    if (row_bytes == 0) row_bytes = 8;
+    qe::TileShape s;
+    size_t rows_per_thread = std::min<size_t>(std::max<size_t>(128 / row_bytes, 2), 32);
+    if (mode == qe::KM_FILTER) rows_per_thread = std::max<size_t>(rows_per_thread, 8);   // amortise scan + lookback
+    size_t pow2 = 2;
+    while (pow2 * 2 <= rows_per_thread) pow2 *= 2;
+    s.vec = pow2 >= 4 ? 4 : 2;
+    s.steps = (int)(pow2 / (size_t)s.vec);
+    if (ctx->opt_vec) s.vec = (int)ctx->opt_vec;
+    if (ctx->opt_steps) s.steps = (int)ctx->opt_steps;
+    s.min_blocks = 1;
+    return s;
+}
+
+static void serialize_interp(const qe::BoundPipeline &bp, std::vector<uint32_t> &w)
+{
+    w.assign(QE_IP_PROGRAMS, 0);
+    w[0] = bp.has_filter ? 1 : 0;
+    w[1] = (uint32_t)bp.proj.size();
+    w[2] = (uint32_t)bp.agg_fns.size();
+    w[3] = (uint32_t)bp.slot_info.size();
+    for (size_t s = 0; s < bp.slot_info.size(); s++)
+        w[QE_IP_SLOTS + s] = (uint32_t)bp.slot_info[s].type | ((bp.slot_info[s].nullable ? 1u : 0u) << 8);
+    for (size_t k = 0; k < bp.proj.size(); k++) {
+        w[QE_IP_OUTS + k] = (uint32_t)bp.outs[k].type | ((bp.outs[k].has_validity ? 1u : 0u) << 8) |
+                            ((uint32_t)(bp.proj[k].identity_slot + 1) << 16);
+        if (k < bp.agg_fns.size()) w[QE_IP_AGGS + k] = (uint32_t)bp.agg_fns[k];
+    }
+    auto put = [&](const qe::BoundExpr &e) {
+        const size_t at = w.size();
+        w.push_back(0);
+        for (const qe::Instr &in : e.code) {
+            w.push_back((uint32_t)in.op | (in.arg << 8));
+            if (in.op == qe::OP_CONST_F64) {
+                uint64_t bits;
+                memcpy(&bits, &in.k, sizeof bits);
+                w.push_back((uint32_t)bits);
+                w.push_back((uint32_t)(bits >> 32));
+            }
+        }
+        w[at] = (uint32_t)(w.size() - at - 1);
+    };
+    if (bp.has_filter) put(bp.filter);
+    for (const qe::BoundExpr &e : bp.proj) put(e);
+}
+
+static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMode mode, const qe::TileShape &shape,
+                          JitEntry **out)
+{
+    char suffix[64];
+    snprintf(suffix, sizeof suffix, "|M%d|S%d|V%d", (int)mode, shape.steps, shape.vec);
+    const std::string key = bp.signature() + suffix;
+    auto it = ctx->jit_cache.find(key);
+    if (it != ctx->jit_cache.end()) { *out = &it->second; return QE_OK; }
+    const std::string src = qe::generate_source(bp, mode, shape);
+    std::vector<char> cubin;
+    std::string log;
+    if (!qe::jit_compile(src, cubin, log)) {
+        if (getenv("QE_DUMP_JIT")) fprintf(stderr, "%s\n", src.c_str());
+        return fail(QE_ERR_JIT, "compiling the generated pipeline failed: " + log);
+    }
+    JitEntry e;
+    e.shape = shape;
+    std::string err;
+    if (!qe::jit_load(cubin, QE_JIT_ENTRY, e.kernel, err)) return fail(QE_ERR_JIT, err);
+    if (getenv("QE_DUMP_JIT"))
+        fprintf(stderr, "[qegpu] jit %s: %d regs, %d CTAs/SM\n", key.c_str(), e.kernel.regs, e.kernel.blocks_per_sm);
+    auto ins = ctx->jit_cache.emplace(key, e);
+    *out = &ins.first->second;
+    return QE_OK;
+}
+
+extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_pipeline_desc *d, qe_result **result)
+{
+    if (!ctx || !table || !d || !result) return fail(QE_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (table->ctx != ctx) return fail(QE_ERR_INVALID_ARGUMENT, "table belongs to another context");
+    if (d->nproj < 0 || d->nproj > QE_MAX_PROJECTIONS) return fail(QE_ERR_UNSUPPORTED, "nproj out of range");
+    if (d->nagg < 0 || (d->nagg > 0 && !d->agg_fns)) return fail(QE_ERR_INVALID_ARGUMENT, "bad aggregate list");
+    DeviceGuard g(ctx->device);
+
+    // ---- bind: resolve columns, type-check, decide output types
+    std::vector<qe::ColumnInfo> schema(table->cols.size());
+    for (size_t c = 0; c < table->cols.size(); c++) {
+        schema[c].type = table->cols[c].type;
+        schema[c].nullable = table->cols[c].nullable != 0;
+    }
+    std::vector<const qe::Program *> proj;
+    for (int k = 0; k < d->nproj; k++) {
+        if (!d->proj || !d->proj[k]) return fail(QE_ERR_INVALID_ARGUMENT, "NULL projection program");
+        proj.push_back(&d->proj[k]->prog);
+    }
+    std::vector<int> aggs(d->agg_fns, d->agg_fns + d->nagg);
+    qe::BoundPipeline bp;
+    std::string err;
+    int rc = qe::bind_pipeline(schema, d->filter ? &d->filter->prog : nullptr, proj, aggs, bp, err);
+    if (rc) return fail(rc, err);
+
+    const qe::KernelMode mode = !bp.agg_fns.empty() ? qe::KM_AGG : bp.has_filter ? qe::KM_FILTER : qe::KM_PROJECT;
+
+    // ---- batch
+    const int64_t row_begin = d->row_begin;
+    const int64_t row_end = d->row_end < 0 ? table->nrows : d->row_end;
+    if (row_begin < 0 || row_end < row_begin || row_end > table->nrows) return fail(QE_ERR_INVALID_ARGUMENT, "bad row range");
+    if (row_begin % 128) return fail(QE_ERR_INVALID_ARGUMENT, "row_begin must be a multiple of 128");
+    const int64_t n = row_end - row_begin;
+
+    // ---- kernel: generated code, or the interpreter
+    bool use_jit = ctx->opt_jit != 0 && !(d->flags & QE_RUN_INTERPRETER);
+    if (use_jit) {
+        std::string why;
+        if (!qe::jit_available(&why)) {
+            if (!ctx->warned_no_nvrtc) {
+                fprintf(stderr, "[qegpu] warning: %s; using the interpreter kernels (slower, still on the GPU)\n", why.c_str());
+                ctx->warned_no_nvrtc = true;
+            }
+            use_jit = false;
+        }
+    }
+    qe::TileShape shape;
+    JitEntry *jit = nullptr;
+    int blocks_per_sm = 1;
+    if (use_jit) {
+        shape = choose_shape(ctx, bp, mode);
+        rc = get_jit_kernel(ctx, bp, mode, shape, &jit);
+        if (rc) return rc;
+        blocks_per_sm = jit->kernel.blocks_per_sm;
+    } else {
+        shape.steps = QE_INTERP_STEPS;
+        shape.vec = QE_INTERP_VEC;
+        blocks_per_sm = qe::interp_blocks_per_sm((int)mode);
+    }
+    const int64_t tile_rows = (int64_t)QE_WARPS * shape.steps * 32 * shape.vec;
+    const int64_t ntiles64 = (n + tile_rows - 1) / tile_rows;
+    const uint32_t ntiles = (uint32_t)ntiles64;
+    if (ctx->opt_grid_per_sm) blocks_per_sm = std::min<int>(blocks_per_sm, (int)ctx->opt_grid_per_sm);
+    if (mode == qe::KM_AGG) blocks_per_sm = std::min(blocks_per_sm, 8);
+    int grid = (int)std::min<int64_t>(std::max<int64_t>(ntiles64, 1), (int64_t)ctx->num_sms * blocks_per_sm);
+
+    // ---- result buffers (reused when the caller passes the previous result back)
+    qe_result *r = *result;
+    if (r && r->ctx != ctx) return fail(QE_ERR_INVALID_ARGUMENT, "result belongs to another context");
+    if (r && r->pending) { QE_CUDA(cudaEventSynchronize(r->ev_done)); r->pending = false; }
+    if (r) fold_timing(r);
+    if (!r) {
+        r = new qe_result();
+        r->ctx = ctx;
+        cudaError_t e = cudaHostAlloc((void **)&r->host, sizeof(ResultHost), cudaHostAllocDefault);
+        if (e == cudaSuccess) e = cudaEventCreate(&r->ev_begin);
+        if (e == cudaSuccess) e = cudaEventCreate(&r->ev_end);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&r->ev_done, cudaEventDisableTiming);
+        if (e != cudaSuccess) { qe_result_destroy(r); return fail_cuda("result setup", e); }
+    }
+    struct Cleanup {      // on error paths, do not leak a result we created
+        qe_result *r; qe_result **slot; bool armed;
+        ~Cleanup() { if (armed && *slot != r) qe_result_destroy(r); }
+    } cleanup{r, result, true};
+
+    r->mode = (int)mode;
+    r->used_jit = use_jit;
+    r->batch_rows = n;
+    r->agg_fns = bp.agg_fns;
+    const int64_t capacity = mode == qe::KM_FILTER ? (d->out_capacity_rows > 0 ? std::min(d->out_capacity_rows, n) : n)
+                           : mode == qe::KM_PROJECT ? ntiles64 * tile_rows : 0;
+    r->capacity = capacity;
+    if (r->cols.size() != bp.outs.size()) {
+        for (ResultColumn &c : r->cols) { release(ctx, c.values); release(ctx, c.valid); }
+        r->cols.assign(bp.outs.size(), ResultColumn());
+    }
+
+    QeParams p;
+    memset(&p, 0, sizeof p);
+    for (size_t s = 0; s < bp.slot_table_col.size(); s++) {
+        const int c = bp.slot_table_col[s];
+        const int type = table->cols[c].type;
+        if (type == QE_TYPE_BOOLEAN) p.col_values[s] = (const char *)table->values[c] + row_begin / 8;
+        else p.col_values[s] = (const char *)table->values[c] + (size_t)row_begin * type_width(type);
+        p.col_valid[s] = table->valid[c] ? table->valid[c] + row_begin / 32 : nullptr;
+    }
+    p.nrows = n;
+    p.ntiles = ntiles;
+    p.sel_base = (uint32_t)row_begin;
+    p.out_capacity = capacity;
+
+    const size_t bitmap_bytes = (size_t)((capacity + 31) / 32 + 16) * 4;
+    if (mode != qe::KM_AGG) {
+        for (size_t k = 0; k < bp.outs.size(); k++) {
+            ResultColumn &c = r->cols[k];
+            c.type = bp.outs[k].type;
+            c.has_validity = bp.outs[k].has_validity;
+            const size_t vbytes = c.type == QE_TYPE_BOOLEAN ? bitmap_bytes : (size_t)std::max<int64_t>(capacity, 1) * type_width(c.type);
+            if ((rc = ensure(ctx, c.values, vbytes))) return rc;
+            p.out_values[k] = c.values.ptr;
+            if (c.has_validity) {
+                if ((rc = ensure(ctx, c.valid, bitmap_bytes))) return rc;
+                p.out_valid[k] = (qe_u32 *)c.valid.ptr;
+            }
+            if (mode == qe::KM_FILTER) {      // compacted bit columns are OR-ed into: start from zero
+                if (c.type == QE_TYPE_BOOLEAN) QE_CUDA(cudaMemsetAsync(c.values.ptr, 0, bitmap_bytes, ctx->stream));
+                if (c.has_validity) QE_CUDA(cudaMemsetAsync(c.valid.ptr, 0, bitmap_bytes, ctx->stream));
+            }
+        }
+    } else {
+        for (size_t k = 0; k < bp.outs.size(); k++) {
+            r->cols[k].type = QE_TYPE_DOUBLE;       // every aggregate is DOUBLE, M/evaluator/TypeCheck.kt:110-120
+            r->cols[k].has_validity = true;
+        }
+    }
+    if (mode == qe::KM_FILTER && !(d->flags & QE_RUN_NO_SELECTION)) {
+        if ((rc = ensure(ctx, r->sel, (size_t)std::max<int64_t>(capacity, 1) * 4))) return rc;
+        p.sel = (qe_u32 *)r->sel.ptr;
+    } else if (mode != qe::KM_FILTER) {
+        release(ctx, r->sel);
+    }
+    // control block: [0] kept-row count (u64)  [8] ticket (u32)  [16...] tile descriptors
+    const size_t ctl_bytes = 16 + (mode == qe::KM_FILTER ? (size_t)ntiles * 8 : 0);
+    if ((rc = ensure(ctx, r->ctl, ctl_bytes))) return rc;
+    QE_CUDA(cudaMemsetAsync(r->ctl.ptr, 0, ctl_bytes, ctx->stream));
+    p.out_count = (qe_u64 *)r->ctl.ptr;
+    p.ticket = (qe_u32 *)((char *)r->ctl.ptr + 8);
+    p.tile_state = (qe_u64 *)((char *)r->ctl.ptr + 16);
+    if (mode == qe::KM_AGG) {
+        if ((rc = ensure(ctx, r->partials, (size_t)grid * QE_MAX_AGGS * 4 * sizeof(double)))) return rc;
+        if ((rc = ensure(ctx, r->final_aggs, QE_MAX_AGGS * 4 * sizeof(double)))) return rc;
+        p.agg_partials = (double *)r->partials.ptr;
+    }
+    DevBuf iprog;
+    if (!use_jit) {
+        std::vector<uint32_t> words;
+        serialize_interp(bp, words);
+        if ((rc = ensure(ctx, iprog, words.size() * 4))) return rc;
+        // pageable source: the runtime stages it before returning, so `words` may go out of scope
+        QE_CUDA(cudaMemcpyAsync(iprog.ptr, words.data(), words.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+        p.iprog = (const qe_u32 *)iprog.ptr;
+    }
+
+    // ---- launch
+    QE_CUDA(cudaEventRecord(r->ev_begin, ctx->stream));
+    if (n > 0) {
+        if (use_jit) {
+            void *args[] = {&p};
+            QE_CUDA(cudaLaunchKernel((const void *)jit->kernel.kernel, dim3(grid), dim3(QE_BLOCK), args, 0, ctx->stream));
+        } else {
+            QE_CUDA(qe::launch_interp((int)mode, p, grid, ctx->stream));
+        }
+        ctx->launches++;
+    }
+    QE_CUDA(cudaEventRecord(r->ev_end, ctx->stream));
+    if (mode == qe::KM_AGG) {
+        if (n > 0) {
+            QE_CUDA(qe::launch_agg_final((const double *)r->partials.ptr, grid, (int)bp.agg_fns.size(),
+                                         (double *)r->final_aggs.ptr, ctx->stream));
+            ctx->launches++;
+            QE_CUDA(cudaMemcpyAsync(r->host->agg, r->final_aggs.ptr, sizeof r->host->agg, cudaMemcpyDeviceToHost, ctx->stream));
+        } else {
+            for (int k = 0; k < QE_MAX_AGGS; k++) {
+                r->host->agg[k][0] = 0.0;
+                r->host->agg[k][1] = 0.0;      // count bits = 0
+                r->host->agg[k][2] = 0.0;
+                r->host->agg[k][3] = 0.0;
+            }
+        }
+    }
+    QE_CUDA(cudaMemcpyAsync(&r->host->count, r->ctl.ptr, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    QE_CUDA(cudaEventRecord(r->ev_done, ctx->stream));
+    r->pending = true;
+    r->timed = true;
+    if (iprog.ptr) {
+        // returned to the pool only after the stream has consumed it
+        cudaStreamSynchronize(ctx->stream);
+        release(ctx, iprog);
+    }
+    cleanup.armed = false;
+    *result = r;
+    return QE_OK;
+}
+
+extern "C" int qe_pipeline_run(qe_ctx *ctx, const qe_table *table, const qe_program *filter,
+                               const qe_program *const *proj, int nproj, const int32_t *agg_fns, int nagg,
+                               qe_result **result)
+{
+    qe_pipeline_desc d;
+    memset(&d, 0, sizeof d);
+    d.filter = filter;
+    d.proj = proj;
+    d.nproj = nproj;
+    d.agg_fns = agg_fns;
+    d.nagg = nagg;
+    d.row_begin = 0;
+    d.row_end = -1;
+    return qe_pipeline_run_ex(ctx, table, &d, result);
+}
+
+// ------------------------------------------------------- result accessors
+
+static int wait_result(qe_result *r)
+{
+    if (!r) return fail(QE_ERR_INVALID_ARGUMENT, "result is NULL");
+    if (r->pending) {
+        DeviceGuard g(r->ctx->device);
+        QE_CUDA(cudaEventSynchronize(r->ev_done));
+        r->pending = false;
+    }
+    return QE_OK;
+}
+
+static int64_t emitted_rows(const qe_result *r)
+{
+    if (r->mode == qe::KM_AGG) return 1;
+    if (r->mode == qe::KM_PROJECT) return r->batch_rows;
+    return (int64_t)r->host->count;
+}
+
+extern "C" int qe_result_num_rows(qe_result *r, int64_t *nrows)
+{
+    int rc = wait_result(r);
+    if (rc) return rc;
+    if (nrows) *nrows = emitted_rows(r);
+    if (r->mode == qe::KM_FILTER && (int64_t)r->host->count > r->capacity) {
+        return fail(QE_ERR_CAPACITY, "filter kept " + std::to_string(r->host->count) + " rows but out_capacity_rows is " +
+                                     std::to_string(r->capacity) + "; rerun with a larger capacity");
+    }
+    return QE_OK;
+}
+
+extern "C" int qe_result_num_columns(const qe_result *r, int *ncols)
+{
+    if (!r || !ncols) return fail(QE_ERR_INVALID_ARGUMENT, "NULL argument");
+    *ncols = (int)r->cols.size();
+    return QE_OK;
+}
+
+extern "C" int qe_result_column_type(const qe_result *r, int k, int *type, int *has_validity)
+{
+    if (!r || k < 0 || k >= (int)r->cols.size()) return fail(QE_ERR_INVALID_ARGUMENT, "column index out of range");
+    if (type) *type = r->cols[k].type;
+    if (has_validity) *has_validity = r->cols[k].has_validity ? 1 : 0;
+    return QE_OK;
+}
+
+static void fill_valid_bitmap(uint8_t *dst, int64_t n)
+{
+    memset(dst, 0xff, (size_t)(n / 8));
+    if (n % 8) dst[n / 8] = (uint8_t)((1u << (n % 8)) - 1u);
+}
+
+extern "C" int qe_result_column(qe_result *r, int k, void *dst_values, uint8_t *dst_validity)
+{
+    int64_t n = 0;
+    int rc = qe_result_num_rows(r, &n);
+    if (rc) return rc;
+    if (k < 0 || k >= (int)r->cols.size()) return fail(QE_ERR_INVALID_ARGUMENT, "column index out of range");
+    qe_ctx *ctx = r->ctx;
+    DeviceGuard g(ctx->device);
+    const ResultColumn &c = r->cols[k];
+    if (r->mode == qe::KM_AGG) {
+        double v = 0.0;
+        int is_null = 0;
+        rc = qe_result_agg(r, k, &v, &is_null);
+        if (rc) return rc;
+        if (dst_values) *(double *)dst_values = v;
+        if (dst_validity) *dst_validity = is_null ? 0 : 1;
+        return QE_OK;
+    }
+    if (n == 0) return QE_OK;
+    if (dst_values) {
+        const size_t bytes = c.type == QE_TYPE_BOOLEAN ? (size_t)((n + 7) / 8) : (size_t)n * type_width(c.type);
+        QE_CUDA(cudaMemcpyAsync(dst_values, c.values.ptr, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (dst_validity) {
+        if (c.has_validity)
+            QE_CUDA(cudaMemcpyAsync(dst_validity, c.valid.ptr, (size_t)((n + 7) / 8), cudaMemcpyDeviceToHost, ctx->stream));
+        else
+            fill_valid_bitmap(dst_validity, n);
+    }
+    QE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return QE_OK;
+}
+
+extern "C" int qe_result_selection(qe_result *r, uint32_t *dst)
+{
+    int64_t n = 0;
+    int rc = qe_result_num_rows(r, &n);
+    if (rc) return rc;
+    if (r->mode != qe::KM_FILTER || !r->sel.ptr) return fail(QE_ERR_STATE, "this result has no selection vector");
+    if (!dst) return fail(QE_ERR_INVALID_ARGUMENT, "dst is NULL");
+    if (n == 0) return QE_OK;
+    DeviceGuard g(r->ctx->device);
+    QE_CUDA(cudaMemcpyAsync(dst, r->sel.ptr, (size_t)n * 4, cudaMemcpyDeviceToHost, r->ctx->stream));
+    QE_CUDA(cudaStreamSynchronize(r->ctx->stream));
+    return QE_OK;
+}
+
+static qe_agg_partial partial_of(const qe_result *r, int k)
+{
+    qe_agg_partial p;
+    p.sum = r->host->agg[k][0];
+    memcpy(&p.count, &r->host->agg[k][1], sizeof p.count);
+    p.min = r->host->agg[k][2];
+    p.max = r->host->agg[k][3];
+    return p;
+}
+
+extern "C" int qe_result_agg_partial(qe_result *r, int k, qe_agg_partial *out)
+{
+    int rc = wait_result(r);
+    if (rc) return rc;
+    if (r->mode != qe::KM_AGG) return fail(QE_ERR_STATE, "this result is not an aggregation");
+    if (k < 0 || k >= (int)r->agg_fns.size() || !out) return fail(QE_ERR_INVALID_ARGUMENT, "aggregate index out of range");
+    *out = partial_of(r, k);
+    if (r->batch_rows == 0) {
+        out->count = 0;
+        out->sum = 0.0;
+    }
+    return QE_OK;
+}
+
+// finish() of the reference's accumulators, M/evaluator/Accumulators.kt:33-35,47-53,65-71,83-89,101-107.
+// COUNT is int64 here; the reference's Kotlin Int would wrap above 2^31-1 rows.
+static void finish_agg(int fn, const qe_agg_partial &p, double *value, int *is_null)
+{
+    double v = 0.0;
+    int null = 0;
+    switch (fn) {
+    case QE_AGG_FN_COUNT: v = (double)p.count; break;
+    case QE_AGG_FN_SUM: if (p.count == 0) null = 1; else v = p.sum; break;
+    case QE_AGG_FN_AVG: if (p.count == 0) null = 1; else v = p.sum / (double)p.count; break;
+    case QE_AGG_FN_MIN: if (p.count == 0) null = 1; else v = p.min; break;
+    case QE_AGG_FN_MAX: if (p.count == 0) null = 1; else v = p.max; break;
+    }
+    if (value) *value = v;
+    if (is_null) *is_null = null;
+}
+
+extern "C" int qe_result_agg(qe_result *r, int k, double *value, int *is_null)
+{
+    qe_agg_partial p;
+    int rc = qe_result_agg_partial(r, k, &p);
+    if (rc) return rc;
+    finish_agg(r->agg_fns[k], p, value, is_null);
+    return QE_OK;
+}
+
+extern "C" int qe_agg_combine(int agg_fn, const qe_agg_partial *partials, int n, double *value, int *is_null)
+{
+    if (agg_fn < 0 || agg_fn > 4) return fail(QE_ERR_INVALID_ARGUMENT, "unknown aggregation function");
+    if (n < 0 || (n > 0 && !partials)) return fail(QE_ERR_INVALID_ARGUMENT, "bad partial list");
+    qe_agg_partial t;
+    t.sum = 0.0;
+    t.count = 0;
+    t.min = qe_bits_f64((qe_i64)0x7ff0000000000000LL);
+    t.max = qe_bits_f64((qe_i64)0xfff0000000000000ULL);
+    for (int i = 0; i < n; i++) {          // array order = rank order: deterministic
+        if (partials[i].count == 0) continue;
+        t.count += partials[i].count;
+        t.sum += partials[i].sum;
+        t.min = qe_math_min(t.min, partials[i].min);
+        t.max = qe_math_max(t.max, partials[i].max);
+    }
+    finish_agg(agg_fn, t, value, is_null);
+    return QE_OK;
+}
+
+extern "C" void *qe_result_device_ptr(qe_result *r, int k, int which)
+{
+    if (!r) return nullptr;
+    if (which == 2) return r->sel.ptr;
+    if (k < 0 || k >= (int)r->cols.size()) return nullptr;
+    return which == 0 ? r->cols[k].values.ptr : r->cols[k].valid.ptr;
+}
+
+extern "C" int qe_result_kernel_ms(qe_result *r, float *ms)
+{
+    int rc = wait_result(r);
+    if (rc) return rc;
+    if (!ms) return fail(QE_ERR_INVALID_ARGUMENT, "ms is NULL");
+    DeviceGuard g(r->ctx->device);
+    QE_CUDA(cudaEventElapsedTime(ms, r->ev_begin, r->ev_end));     // events keep their timestamps after folding
+    return QE_OK;
+}
+
+extern "C" int qe_result_kernel_stats(qe_result *r, double *total_ms, int64_t *runs)
+{
+    int rc = wait_result(r);
+    if (rc) return rc;
+    DeviceGuard g(r->ctx->device);
+    fold_timing(r);
+    if (total_ms) *total_ms = r->total_kernel_ms;
+    if (runs) *runs = r->kernel_runs;
+    return QE_OK;
+}
+
+extern "C" int qe_result_used_jit(const qe_result *r) { return r && r->used_jit ? 1 : 0; }
+
+// ------------------------------------------------------------ diagnostics
+// Bind a pipeline against a schema, generate its CUDA source and optionally
+// compile it with NVRTC.  Needs no GPU: used by the CPU-side tests and for
+// inspecting the generated code (SASS via cuobjdump on the returned cubin).
+extern "C" int qe_debug_generate(const qe_col_desc *cols, int ncols,
+                                 const uint32_t *const *programs, const size_t *nwords,
+                                 int has_filter, int nproj, const int32_t *agg_fns, int nagg,
+                                 int steps, int vec, int compile,
+                                 char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes)
+{
+    if (!cols || ncols <= 0 || !programs || !nwords) return fail(QE_ERR_INVALID_ARGUMENT, "NULL argument");
+    std::vector<qe::ColumnInfo> schema(ncols);
+    for (int c = 0; c < ncols; c++) { schema[c].type = cols[c].type; schema[c].nullable = cols[c].nullable != 0; }
+    const int nprog = (has_filter ? 1 : 0) + nproj;
+    std::vector<qe::Program> progs(nprog);
+    std::string err;
+    for (int i = 0; i < nprog; i++)
+        if (!qe::parse_program(programs[i], nwords[i], progs[i], err)) return fail(QE_ERR_PROGRAM, err);
+    std::vector<const qe::Program *> proj;
+    for (int k = 0; k < nproj; k++) proj.push_back(&progs[(has_filter ? 1 : 0) + k]);
+    std::vector<int> aggs;
+    if (nagg > 0) aggs.assign(agg_fns, agg_fns + nagg);
+    qe::BoundPipeline bp;
+    int rc = qe::bind_pipeline(schema, has_filter ? &progs[0] : nullptr, proj, aggs, bp, err);
+    if (rc) return fail(rc, err);
+    const qe::KernelMode mode = !bp.agg_fns.empty() ? qe::KM_AGG : bp.has_filter ? qe::KM_FILTER : qe::KM_PROJECT;
+    qe_ctx dummy;
+    dummy.opt_steps = steps;
+    dummy.opt_vec = vec;
+    const qe::TileShape shape = choose_shape(&dummy, bp, mode);
+    const std::string src = qe::generate_source(bp, mode, shape);
+    if (src_buf && src_cap) {
+        const size_t n = std::min(src_cap - 1, src.size());
+        memcpy(src_buf, src.data(), n);
+        src_buf[n] = 0;
+    }
+    if (cubin_bytes) *cubin_bytes = 0;
+    if (compile) {
+        std::vector<char> cubin;
+        std::string log;
+        if (!qe::jit_compile(src, cubin, log)) return fail(QE_ERR_JIT, log);
+        if (cubin_bytes) *cubin_bytes = cubin.size();
+        if (cubin_buf && cubin_cap >= cubin.size()) memcpy(cubin_buf, cubin.data(), cubin.size());
+    }
+    return QE_OK;
+}

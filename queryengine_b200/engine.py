@@ -1,0 +1,383 @@
+"""Host-side mirror of the reference's operator interface for the GPU path.
+
+The reference assembles ``Scan -> [Filter] -> [Projection] -> [GlobalAggregation]``
+in ``buildPhysicalPlan`` (src/main/java/net/jhorstmann/queryengine/evaluator/Planner.kt:30-63)
+out of ``Operator`` objects with ``open() / next() / close()``
+(.../operator/Operators.kt:5-11).  ``GpuPipelineOperator`` is that whole subtree
+as one operator: it runs the pipeline on the GPU through the C ABI
+(include/qegpu.h) when opened and then hands rows out one at a time, exactly
+like the operators it replaces; ``next_batch()`` exposes the columnar result
+beside ``next()``.
+
+Everything here is plumbing over libqegpu.so.  Nothing is evaluated on the
+host; if the library or a GPU is missing the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from . import capi
+from .ast import AggregationFunction, ColumnExpression, DataType, Expression
+from .program import serialize
+
+_NP_OF = {DataType.DOUBLE: np.float64, DataType.INT64: np.int64, DataType.DATE32: np.int32}
+
+
+def pack_bits(mask) -> np.ndarray:
+    """bool array -> Arrow bitmap (LSB first)."""
+    return np.packbits(np.asarray(mask, dtype=np.uint8), bitorder="little")
+
+
+def unpack_bits(bitmap: np.ndarray, n: int) -> np.ndarray:
+    return np.unpackbits(bitmap, bitorder="little")[:n].astype(bool)
+
+
+class Context:
+    """qe_ctx: one device, one stream, one memory pool."""
+
+    def __init__(self, device: int = 0):
+        self.handle = C.c_void_p()
+        capi.check(capi.lib().qe_ctx_create(device, C.byref(self.handle)))
+        self.device = device
+
+    def set_option(self, key: str, value: int) -> None:
+        capi.check(capi.lib().qe_ctx_set_option(self.handle, key.encode(), int(value)))
+
+    def synchronize(self) -> None:
+        capi.check(capi.lib().qe_ctx_synchronize(self.handle))
+
+    @property
+    def stream(self) -> int:
+        return capi.lib().qe_ctx_stream(self.handle) or 0
+
+    @property
+    def launch_count(self) -> int:
+        return capi.lib().qe_ctx_launch_count(self.handle)
+
+    def close(self) -> None:
+        if self.handle:
+            capi.lib().qe_ctx_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Program:
+    """compileExpression(expr, Mode.GPU): the flattened tree, held by the library."""
+
+    def __init__(self, ctx: Context, expr: Expression):
+        self.ctx = ctx
+        self.expr = expr
+        self.words = serialize(expr)
+        self.handle = C.c_void_p()
+        capi.check(capi.lib().qe_program_create(ctx.handle, self.words.ctypes.data, self.words.size, C.byref(self.handle)))
+
+    def close(self) -> None:
+        if self.handle and self.ctx.handle:      # a closed context has already released everything
+            capi.lib().qe_program_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+@dataclass
+class Field:
+    """data class Field(name, type) (.../data/Schema.kt:7) plus nullability."""
+    name: str
+    type: DataType
+    nullable: bool = False
+
+
+class ColumnarTable:
+    """Columnar counterpart of MemoryTable (.../data/MemoryTable.kt:7-19), resident in HBM."""
+
+    def __init__(self, ctx: Context, fields: Sequence[Field], nrows: int):
+        self.ctx = ctx
+        self.fields = list(fields)
+        self.nrows = int(nrows)
+        descs = (capi.ColDesc * len(self.fields))(*[capi.ColDesc(int(f.type), 1 if f.nullable else 0) for f in self.fields])
+        self.handle = C.c_void_p()
+        capi.check(capi.lib().qe_table_create(ctx.handle, len(self.fields), descs, self.nrows, C.byref(self.handle)))
+
+    @classmethod
+    def from_arrays(cls, ctx: Context, fields: Sequence[Field], columns: Sequence, validity: Optional[Sequence] = None):
+        n = len(columns[0]) if len(columns) else 0
+        t = cls(ctx, fields, n)
+        for c, f in enumerate(fields):
+            v = None if validity is None else validity[c]
+            t.upload(c, columns[c], v)
+        return t
+
+    def upload(self, col: int, values, valid_mask=None, row0: int = 0) -> None:
+        """values: array of the column's type (bool array for BOOLEAN); valid_mask: bool array or None."""
+        f = self.fields[col]
+        if f.type == DataType.BOOLEAN:
+            n = len(values)
+            data = pack_bits(values)
+        else:
+            data = np.ascontiguousarray(values, dtype=_NP_OF[f.type])
+            n = data.size
+        vbits = None
+        if valid_mask is not None:
+            if f.nullable:
+                vbits = pack_bits(valid_mask)
+            elif not np.asarray(valid_mask).all():
+                raise ValueError(f"column {f.name} is declared non-nullable but has nulls")
+        capi.check(capi.lib().qe_table_upload(
+            self.handle, col, data.ctypes.data if n else None,
+            vbits.ctypes.data if vbits is not None and n else None, row0, n))
+        # uploads are asynchronous on the context's stream and may read `data` (pinned) later
+        self.ctx.synchronize()
+
+    def upload_raw(self, col: int, values_ptr: int, validity_ptr: Optional[int], row0: int, n: int) -> None:
+        """Asynchronous upload from caller-managed (ideally pinned) memory."""
+        capi.check(capi.lib().qe_table_upload(self.handle, col, values_ptr, validity_ptr, row0, n))
+
+    def generate(self, col: int, kind: int, seed: int, p0: float = 0.0, p1: float = 0.0,
+                 null_rate: float = 0.0, row_offset: int = 0) -> None:
+        capi.check(capi.lib().qe_table_generate(self.handle, col, kind, seed, p0, p1, null_rate, row_offset))
+
+    def device_ptr(self, col: int, which: int = 0) -> int:
+        return capi.lib().qe_table_device_ptr(self.handle, col, which) or 0
+
+    def getScanOperator(self, projection: Sequence[str]) -> "GpuPipelineOperator":
+        """Table.getScanOperator(projection) (.../data/Table.kt:8): a scan of the named columns."""
+        idx = []
+        for name in projection:
+            hits = [i for i, f in enumerate(self.fields) if f.name == name]
+            if not hits:
+                raise ValueError(f"Unknown field {name}")          # IllegalArgumentException, MemoryTable.kt:12
+            idx.append(hits[0])
+        exprs = [ColumnExpression(self.fields[i].name, i, self.fields[i].type) for i in idx]
+        return GpuPipelineOperator(self, None, exprs, None)
+
+    def close(self) -> None:
+        if self.handle and self.ctx.handle:
+            capi.lib().qe_table_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class PipelineResult:
+    """qe_result: device buffers of one pipeline run."""
+
+    def __init__(self, ctx: Context):
+        self.ctx = ctx
+        self.handle = C.c_void_p()
+
+    @property
+    def num_rows(self) -> int:
+        n = C.c_int64(0)
+        capi.check(capi.lib().qe_result_num_rows(self.handle, C.byref(n)))
+        return n.value
+
+    @property
+    def num_columns(self) -> int:
+        n = C.c_int(0)
+        capi.check(capi.lib().qe_result_num_columns(self.handle, C.byref(n)))
+        return n.value
+
+    def column_type(self, k: int):
+        t, hv = C.c_int(0), C.c_int(0)
+        capi.check(capi.lib().qe_result_column_type(self.handle, k, C.byref(t), C.byref(hv)))
+        return DataType(t.value), bool(hv.value)
+
+    def column(self, k: int):
+        """(values, valid): numpy arrays of the column's type and a bool mask."""
+        n = self.num_rows
+        t, _ = self.column_type(k)
+        vbits = np.zeros((n + 7) // 8 + 1, np.uint8)
+        if t == DataType.BOOLEAN:
+            data = np.zeros((n + 7) // 8 + 1, np.uint8)
+        else:
+            data = np.zeros(max(n, 1), _NP_OF[t])
+        capi.check(capi.lib().qe_result_column(self.handle, k, data.ctypes.data, vbits.ctypes.data))
+        valid = unpack_bits(vbits, n)
+        if t == DataType.BOOLEAN:
+            return unpack_bits(data, n), valid
+        return data[:n], valid
+
+    def selection(self) -> np.ndarray:
+        n = self.num_rows
+        out = np.zeros(max(n, 1), np.uint32)
+        capi.check(capi.lib().qe_result_selection(self.handle, out.ctypes.data))
+        return out[:n]
+
+    def agg(self, k: int):
+        v, isnull = C.c_double(0.0), C.c_int(0)
+        capi.check(capi.lib().qe_result_agg(self.handle, k, C.byref(v), C.byref(isnull)))
+        return None if isnull.value else v.value
+
+    def agg_partial(self, k: int) -> capi.AggPartial:
+        p = capi.AggPartial()
+        capi.check(capi.lib().qe_result_agg_partial(self.handle, k, C.byref(p)))
+        return p
+
+    @property
+    def kernel_ms(self) -> float:
+        ms = C.c_float(0.0)
+        capi.check(capi.lib().qe_result_kernel_ms(self.handle, C.byref(ms)))
+        return ms.value
+
+    def kernel_stats(self):
+        """(total device ms of the main kernel over all completed runs into this result, number of runs)"""
+        ms, runs = C.c_double(0.0), C.c_int64(0)
+        capi.check(capi.lib().qe_result_kernel_stats(self.handle, C.byref(ms), C.byref(runs)))
+        return ms.value, runs.value
+
+    @property
+    def used_jit(self) -> bool:
+        return bool(capi.lib().qe_result_used_jit(self.handle))
+
+    def device_ptr(self, k: int, which: int) -> int:
+        return capi.lib().qe_result_device_ptr(self.handle, k, which) or 0
+
+    def close(self) -> None:
+        if self.handle and self.ctx.handle:
+            capi.lib().qe_result_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def combine_aggregate(fn: AggregationFunction, partials: Sequence[capi.AggPartial]):
+    """Fixed-order combination of per-partition partial aggregates (rank order)."""
+    arr = (capi.AggPartial * max(1, len(partials)))(*partials)
+    v, isnull = C.c_double(0.0), C.c_int(0)
+    capi.check(capi.lib().qe_agg_combine(int(fn), arr, len(partials), C.byref(v), C.byref(isnull)))
+    return None if isnull.value else v.value
+
+
+class Pipeline:
+    """A bound Scan -> [Filter] -> [Projection] -> [GlobalAggregation] subtree, runnable repeatedly."""
+
+    def __init__(self, table: ColumnarTable, filter: Optional[Expression] = None,
+                 projections: Optional[Sequence[Expression]] = None,
+                 aggregates: Optional[Sequence[AggregationFunction]] = None,
+                 interpreter: bool = False, selection: bool = True, out_capacity_rows: int = 0):
+        self.table = table
+        self.ctx = table.ctx
+        self.filter = Program(self.ctx, filter) if filter is not None else None
+        self.projs = [Program(self.ctx, e) for e in (projections or [])]
+        self.aggs = [int(a) for a in (aggregates or [])]
+        self.flags = (capi.QE_RUN_INTERPRETER if interpreter else 0) | (0 if selection else capi.QE_RUN_NO_SELECTION)
+        self.out_capacity_rows = out_capacity_rows
+        self._proj_arr = (C.c_void_p * max(1, len(self.projs)))(*[p.handle for p in self.projs])
+        self._agg_arr = (C.c_int32 * max(1, len(self.aggs)))(*self.aggs)
+
+    def run(self, result: Optional[PipelineResult] = None, row_begin: int = 0, row_end: int = -1) -> PipelineResult:
+        """Enqueue the pipeline on the context's stream; accessors of the result wait for it."""
+        r = result or PipelineResult(self.ctx)
+        d = capi.PipelineDesc()
+        d.filter = self.filter.handle if self.filter else None
+        d.proj = self._proj_arr
+        d.nproj = len(self.projs)
+        d.agg_fns = self._agg_arr
+        d.nagg = len(self.aggs)
+        d.row_begin = row_begin
+        d.row_end = row_end
+        d.out_capacity_rows = self.out_capacity_rows
+        d.flags = self.flags
+        capi.check(capi.lib().qe_pipeline_run_ex(self.ctx.handle, self.table.handle, C.byref(d), C.byref(r.handle)))
+        return r
+
+
+class GpuPipelineOperator:
+    """Operator { open(); next(): Array<Any?>?; close() } for the whole GPU subtree.
+
+    Stands where buildPhysicalPlan would put
+    ``[GlobalAggregationOperator(] [ProjectionOperator(] [FilterOperator(] scan [)])])``.
+    A filter without projections returns the scanned row unchanged, like
+    FilterOperator.next (.../operator/FilterOperator.kt:14-25).
+    """
+
+    def __init__(self, table: ColumnarTable, filter: Optional[Expression],
+                 projections: Optional[Sequence[Expression]],
+                 aggregates: Optional[Sequence[AggregationFunction]], interpreter: bool = False,
+                 scan_columns: Optional[Sequence[int]] = None):
+        if not projections:
+            cols = scan_columns if scan_columns is not None else range(len(table.fields))
+            projections = [ColumnExpression(table.fields[i].name, i, table.fields[i].type) for i in cols]
+        self.pipeline = Pipeline(table, filter, projections, aggregates, interpreter=interpreter)
+        self.aggregates = list(aggregates or [])
+        self._result: Optional[PipelineResult] = None
+        self._cols = None
+        self._idx = 0
+        self._n = 0
+
+    def open(self) -> None:
+        self._result = self.pipeline.run(self._result)
+        self._n = self._result.num_rows
+        self._idx = 0
+        self._cols = None
+
+    def next_batch(self):
+        """Columnar view: list of (values, valid) per output column, or None when consumed."""
+        if self._result is None:
+            raise RuntimeError("Operator not opened")          # IllegalStateException in the reference
+        if self._cols is None:
+            if self.aggregates:
+                vals = [self._result.agg(k) for k in range(len(self.aggregates))]
+                self._cols = [(np.array([0.0 if v is None else v]), np.array([v is not None])) for v in vals]
+            else:
+                self._cols = [self._result.column(k) for k in range(self._result.num_columns)]
+        return self._cols
+
+    def next(self):
+        if self._result is None:
+            raise RuntimeError("Operator not opened")
+        if self._idx >= self._n:
+            return None
+        cols = self.next_batch()
+        i = self._idx
+        self._idx += 1
+        row = []
+        for k, (vals, valid) in enumerate(cols):
+            if not valid[i]:
+                row.append(None)
+            elif vals.dtype == np.bool_:
+                row.append(bool(vals[i]))
+            elif self.aggregates and self.aggregates[k] == AggregationFunction.COUNT:
+                row.append(int(vals[i]))                       # CountAccumulator.finish() is an Int
+            else:
+                row.append(float(vals[i]))
+        return row
+
+    def close(self) -> None:
+        self._cols = None
+        self._idx = self._n = 0
+
+    def map(self, mapper=lambda r: r) -> List:
+        """Operator.map (.../operator/Operators.kt:25-32): open, pull until null, close."""
+        out = []
+        self.open()
+        try:
+            while True:
+                r = self.next()
+                if r is None:
+                    break
+                out.append(mapper(r))
+        finally:
+            self.close()
+        return out

@@ -1,0 +1,288 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle.  Needs a B200.
+
+Small cases transcribe the reference's own tests
+(T/ = src/test/java/net/jhorstmann/queryengine/); the rest are seeded random
+trees and tables at sizes the oracle finishes in seconds, plus size-independent
+properties at larger sizes.
+"""
+import numpy as np
+import pytest
+
+from exprgen import ExprGen
+from parity import TableSpec, compare_aggregation, compare_pipeline, f64_equal, random_table
+from queryengine_b200 import capi
+from queryengine_b200.ast import (
+    AggregationFunction, BooleanLiteralExpression, ColumnExpression, DataType, Function, FunctionExpression,
+    NumericLiteralExpression, col, fn, lit,
+)
+from queryengine_b200.engine import ColumnarTable, Context, Field, GpuPipelineOperator, Pipeline
+
+pytestmark = pytest.mark.gpu
+D, B, I, T = DataType.DOUBLE, DataType.BOOLEAN, DataType.INT64, DataType.DATE32
+A = AggregationFunction
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = Context(0)
+    yield c
+    c.close()
+
+
+def _rows_table(ctx, fields, rows):
+    cols, valid = [], []
+    for c, f in enumerate(fields):
+        vals = [r[c] for r in rows]
+        valid.append(np.array([v is not None for v in vals]))
+        if f.type == B:
+            cols.append(np.array([bool(v) for v in vals]))
+        else:
+            cols.append(np.array([0.0 if v is None else v for v in vals], dtype=np.float64))
+    return ColumnarTable.from_arrays(ctx, fields, cols, valid)
+
+
+def _eval_rows(ctx, fields, rows, expr, interpreter):
+    """compileExpression(expr, Mode.GPU) applied to each row (RowCallable.invoke)."""
+    t = _rows_table(ctx, fields, rows)
+    op = GpuPipelineOperator(t, None, [expr], None, interpreter=interpreter)
+    out = [r[0] for r in op.map()]
+    t.close()
+    return out
+
+
+@pytest.mark.parametrize("interpreter", [False, True])
+def test_compilertest_golden_vectors(ctx, interpreter):
+    # T/evaluator/CompilerTest.kt:27-35  1.0 + 2.0 == 3.0 (evaluated once per row of a 3-row table)
+    e = FunctionExpression(Function.ADD, [NumericLiteralExpression(1.0), NumericLiteralExpression(2.0)], D)
+    assert _eval_rows(ctx, [Field("x", D, False)], [[0.0], [1.0], [2.0]], e, interpreter) == [3.0, 3.0, 3.0]
+    # :39-47  10.0 * null == null
+    e = FunctionExpression(Function.MUL, [ColumnExpression("foo", 0, D), ColumnExpression("bar", 1, D)], D)
+    assert _eval_rows(ctx, [Field("foo", D, True), Field("bar", D, True)], [[10.0, None], [10.0, 2.0]], e,
+                      interpreter) == [None, 20.0]
+    # :52-74 AND truth table, :78-100 OR truth table
+    rows = [[p, q] for p in (True, False, None) for q in (True, False, None)]
+    fields = [Field("p", B, True), Field("q", B, True)]
+    e = FunctionExpression(Function.AND, [ColumnExpression("p", 0, B), ColumnExpression("q", 1, B)], B)
+    assert _eval_rows(ctx, fields, rows, e, interpreter) == [True, False, None, False, False, False, None, False, None]
+    e = FunctionExpression(Function.OR, [ColumnExpression("p", 0, B), ColumnExpression("q", 1, B)], B)
+    assert _eval_rows(ctx, fields, rows, e, interpreter) == [True, True, True, True, False, None, True, None, None]
+    # :104-120 IF with a null condition (string literals replaced by doubles: strings are not on the GPU path)
+    e = FunctionExpression(Function.IF, [ColumnExpression("cond", 0, B), NumericLiteralExpression(1.0),
+                                         NumericLiteralExpression(2.0)], D)
+    assert _eval_rows(ctx, [Field("cond", B, True)], [[True], [False], [None]], e, interpreter) == [1.0, 2.0, None]
+
+
+@pytest.mark.parametrize("interpreter", [False, True])
+def test_bytecode_compiler_projection_example(ctx, interpreter):
+    # T/ByteCodeCompilerTest.kt:12-40
+    fields = [Field("foo", D, False), Field("bar", D, False), Field("baz", D, False)]
+    t = _rows_table(ctx, fields, [[10.0, 11.0, 12.0], [20.0, 21.0, 22.0], [30.0, 31.0, 32.0]])
+    op = GpuPipelineOperator(t, None, [fn(Function.ADD, col(0), col(1)), fn(Function.ADD, col(1), col(2))], None,
+                             interpreter=interpreter)
+    assert op.map() == [[21.0, 23.0], [41.0, 43.0], [61.0, 63.0]]
+
+
+@pytest.mark.parametrize("size", [1000, 1_000_000])
+def test_simple_sum_benchmark_known_answer(ctx, size):
+    # T/SimpleSumBenchmark.java:41-53  SELECT SUM(foo + 10*bar); exact in any summation order
+    v = (np.arange(size) // 1000).astype(np.float64)
+    t = ColumnarTable.from_arrays(ctx, [Field("foo", D, False), Field("bar", D, False)], [v, v])
+    e = fn(Function.ADD, col(0), fn(Function.MUL, 10.0, col(1)))
+    op = GpuPipelineOperator(t, None, [e], [A.SUM])
+    assert op.map() == [[11.0 * 1000.0 * sum(range(size // 1000))]]
+    if size == 1_000_000:
+        assert op.map() == [[5_494_500_000.0]]
+    t.close()
+
+
+def test_filter_returns_row_unchanged_and_drops_null_predicate(ctx):
+    # M/operator/FilterOperator.kt:14-25
+    fields = [Field("x", D, False), Field("p", B, True)]
+    t = _rows_table(ctx, fields, [[0.0, True], [1.0, None], [2.0, False], [3.0, True]])
+    op = GpuPipelineOperator(t, ColumnExpression("p", 1, B), None, None)
+    assert op.map() == [[0.0, True], [3.0, True]]
+    assert op.next() is None          # exhausted and closed
+    t.close()
+
+
+@pytest.mark.parametrize("nrows", [0, 1, 63, 64, 65, 511, 4096, 4097, 8191, 20000])
+@pytest.mark.parametrize("interpreter", [False, True])
+def test_single_column_filter_all_sizes(ctx, nrows, interpreter):
+    rng = np.random.default_rng(nrows + 7)
+    spec = random_table(rng, nrows, "d")
+    compare_pipeline(ctx, spec, fn(Function.CMP_LT, col(0), 0.0), [col(0)], interpreter=interpreter)
+
+
+@pytest.mark.parametrize("k", [-np.inf, -1000.0, -0.0, 0.0, 5e-324, np.inf, np.nan])
+def test_compare_against_extreme_literals(ctx, k):
+    rng = np.random.default_rng(11)
+    spec = random_table(rng, 5000, "dD", special_rate=0.3)
+    for f in (Function.CMP_LT, Function.CMP_LE, Function.CMP_GE, Function.CMP_GT, Function.CMP_EQ, Function.CMP_NE):
+        compare_pipeline(ctx, spec, fn(f, col(0), float(k)), [fn(f, float(k), col(1))])
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_trees_jit(ctx, seed):
+    rng = np.random.default_rng(1000 + seed)
+    layout = ["dDbB", "DDDD", "dibT", "DBIt", "dd", "BB d".replace(" ", "")][seed % 6]
+    spec = random_table(rng, int(rng.integers(1, 30000)), layout)
+    g = ExprGen(rng, spec.fields)
+    filt = g.boolean(4) if seed % 4 != 3 else None
+    projs = [g.double(5), g.boolean(3), g.double(2)]
+    if seed % 3 == 0:
+        projs.append(ColumnExpression(spec.fields[0].name, 0, spec.fields[0].type))
+    compare_pipeline(ctx, spec, filt, projs, interpreter=False)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_random_trees_interpreter(ctx, seed):
+    rng = np.random.default_rng(2000 + seed)
+    spec = random_table(rng, int(rng.integers(1, 5000)), ["dDbB", "DIbt", "DDBB"][seed % 3])
+    g = ExprGen(rng, spec.fields)
+    filt = g.boolean(4) if seed % 3 != 2 else None
+    compare_pipeline(ctx, spec, filt, [g.double(5), g.boolean(3)], interpreter=True)
+
+
+@pytest.mark.parametrize("steps,vec", [(1, 2), (2, 2), (8, 2), (1, 4), (4, 4), (8, 4)])
+def test_every_tile_shape(ctx, steps, vec):
+    c = Context(0)
+    c.set_option("steps", steps)
+    c.set_option("vec", vec)
+    rng = np.random.default_rng(steps * 10 + vec)
+    spec = random_table(rng, 30011, "DbiT")
+    g = ExprGen(rng, spec.fields)
+    compare_pipeline(c, spec, g.boolean(3), [g.double(4), g.boolean(2), col(2, I), col(3, T)])
+    compare_pipeline(c, spec, None, [g.double(4), g.boolean(2), col(2, I)])
+    compare_aggregation(c, spec, g.boolean(2), [g.double(3), col(0)], [A.SUM, A.MAX])
+    c.close()
+
+
+@pytest.mark.parametrize("interpreter", [False, True])
+def test_aggregates(ctx, interpreter):
+    rng = np.random.default_rng(5)
+    spec = random_table(rng, 50000, "DdB", special_rate=0.0)
+    e = fn(Function.MUL, col(0), col(1))
+    compare_aggregation(ctx, spec, fn(Function.CMP_GT, col(1), -500.0), [e, e, e, e, e, col(2, B)],
+                        [A.MIN, A.MAX, A.SUM, A.COUNT, A.AVG, A.COUNT], interpreter=interpreter)
+    # no row passes: SUM/AVG/MIN/MAX null, COUNT 0 (M/evaluator/Accumulators.kt:33-35,47-53)
+    out = compare_aggregation(ctx, spec, fn(Function.CMP_GT, col(1), 1e9), [e, e, e, e, e],
+                              [A.MIN, A.MAX, A.SUM, A.COUNT, A.AVG], interpreter=interpreter)
+    assert out == [None, None, None, 0.0, None]
+    # NaN and signed zeros through MIN / MAX (Math.min / Math.max)
+    spec = random_table(rng, 3000, "D", special_rate=0.5)
+    compare_aggregation(ctx, spec, None, [col(0), col(0)], [A.MIN, A.MAX], interpreter=interpreter)
+    zeros = TableSpec([Field("z", D, False)], [np.array([0.0, -0.0, 0.0])], [None])
+    mn, mx = compare_aggregation(ctx, zeros, None, [col(0), col(0)], [A.MIN, A.MAX], interpreter=interpreter)
+    assert np.signbit(mn) and not np.signbit(mx)
+
+
+def test_q6_shaped_query(ctx):
+    # BASELINE.json configs[2] at a size the oracle handles: filter + SUM(extendedprice * discount)
+    n = 200_000
+    rng = np.random.default_rng(42)
+    qty = rng.integers(1, 51, n).astype(np.float64)
+    disc = rng.integers(0, 11, n) / 100.0
+    ep = np.round(qty * rng.uniform(900, 2100, n) * 100) / 100
+    sd = rng.integers(8036, 10562, n).astype(np.float64)
+    spec = TableSpec([Field("l_quantity", D, False), Field("l_extendedprice", D, False), Field("l_discount", D, False),
+                      Field("l_shipdate", D, False)], [qty, ep, disc, sd], [None] * 4)
+    filt = fn(Function.AND, fn(Function.AND, fn(Function.AND, fn(Function.AND,
+              fn(Function.CMP_GE, col(3), 8766.0), fn(Function.CMP_LT, col(3), 9131.0)),
+              fn(Function.CMP_GE, col(2), 0.05)), fn(Function.CMP_LE, col(2), 0.07)), fn(Function.CMP_LT, col(0), 24.0))
+    compare_aggregation(ctx, spec, filt, [fn(Function.MUL, col(1), col(2))], [A.SUM])
+    compare_pipeline(ctx, spec, filt, [fn(Function.MUL, col(1), col(2))])
+    # date32 variant of the ship date: same rows
+    spec32 = TableSpec(spec.fields[:3] + [Field("l_shipdate", T, False)], [qty, ep, disc, sd.astype(np.int32)], [None] * 4)
+    compare_pipeline(ctx, spec32, filt, [fn(Function.MUL, col(1), col(2)), col(3, T)])
+
+
+def test_generators_match_their_published_formulas(ctx):
+    # qe_table_generate: value(i) = f(splitmix64(seed ^ i)); reproduced here in numpy
+    def splitmix64(x):
+        x = (x + np.uint64(0x9E3779B97F4A7C15))
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        return x ^ (x >> np.uint64(31))
+    n, seed, off = 10007, 42, 1 << 33
+    t = ColumnarTable(ctx, [Field("a", I, False), Field("b", D, True), Field("c", D, False), Field("d", T, False)], n)
+    t.generate(0, capi.QE_GEN_UNIFORM_U40, seed, row_offset=off)
+    t.generate(1, capi.QE_GEN_UNIFORM_REAL, seed + 1, -1000.0, 1000.0, null_rate=0.1, row_offset=off)
+    t.generate(2, capi.QE_GEN_CENTS, seed + 2, 0, 10, row_offset=off)
+    t.generate(3, capi.QE_GEN_UNIFORM_INT, seed + 3, 8036, 10561, row_offset=off)
+    res = Pipeline(t, None, [col(0, I), col(1), col(2), col(3, T)]).run()
+    with np.errstate(over="ignore"):
+        i = np.arange(n, dtype=np.uint64) + np.uint64(off)
+        h = splitmix64(np.uint64(seed) ^ i)
+        assert np.array_equal(res.column(0)[0], (h >> np.uint64(24)).astype(np.int64))
+        h1 = splitmix64(np.uint64(seed + 1) ^ i)
+        exp1 = -1000.0 + ((h1 >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)) * 2000.0
+        vals, valid = res.column(1)
+        vh = splitmix64(~np.uint64(seed + 1) ^ (i * np.uint64(0x9E3779B97F4A7C15)))
+        exp_valid = vh >= np.uint64(int(0.1 * 18446744073709551616.0))
+        assert np.array_equal(valid, exp_valid) and 0.05 < 1 - valid.mean() < 0.15
+        assert f64_equal(vals[valid], exp1[valid]).all()
+        h2 = splitmix64(np.uint64(seed + 2) ^ i)
+        assert np.array_equal(res.column(2)[0], (h2 % np.uint64(11)).astype(np.float64) / 100.0)
+        h3 = splitmix64(np.uint64(seed + 3) ^ i)
+        assert np.array_equal(res.column(3)[0], (8036 + (h3 % np.uint64(2526)).astype(np.int64)).astype(np.int32))
+    res.close()
+    t.close()
+
+
+def test_capacity_overflow_is_reported_not_written(ctx):
+    v = np.arange(100000, dtype=np.float64)
+    t = ColumnarTable.from_arrays(ctx, [Field("x", D, False)], [v])
+    res = Pipeline(t, fn(Function.CMP_GE, col(0), 0.0), [col(0)], out_capacity_rows=1000).run()
+    with pytest.raises(capi.QeError) as ei:
+        _ = res.num_rows
+    assert ei.value.status == capi.QE_ERR_CAPACITY
+    res2 = Pipeline(t, fn(Function.CMP_LT, col(0), 1000.0), [col(0)], out_capacity_rows=1000).run()
+    assert res2.num_rows == 1000 and np.array_equal(res2.column(0)[0], v[:1000])
+    t.close()
+
+
+def test_row_range_batches_concatenate_to_the_whole(ctx):
+    # MemorySourceOperator scans in order; batches are row ranges of the same scan
+    rng = np.random.default_rng(3)
+    n = 100_000
+    v = rng.uniform(-1, 1, n)
+    t = ColumnarTable.from_arrays(ctx, [Field("x", D, False)], [v])
+    pipe = Pipeline(t, fn(Function.CMP_LT, col(0), 0.25), [col(0)])
+    whole = pipe.run()
+    sel_whole = whole.selection()
+    parts = []
+    for b in range(0, n, 32768):
+        r = pipe.run(row_begin=b, row_end=min(n, b + 32768))
+        parts.append(r.selection())
+        r.close()
+    assert np.array_equal(np.concatenate(parts), sel_whole)
+    assert np.array_equal(sel_whole, np.nonzero(v < 0.25)[0].astype(np.uint32))
+    t.close()
+
+
+def test_large_scan_properties(ctx):
+    """BASELINE.json configs[1] shape at 64 Mi rows: properties that hold at any size."""
+    n = 1 << 26
+    t = ColumnarTable(ctx, [Field("col", I, False)], n)
+    t.generate(0, capi.QE_GEN_UNIFORM_U40, 42)
+    expect_total = None
+    for s in (0.01, 0.5, 0.99):
+        k = float(int(s * 2 ** 40))
+        res = Pipeline(t, fn(Function.CMP_LT, col(0, I), k), [col(0, I)]).run()
+        assert res.used_jit
+        m = res.num_rows
+        assert abs(m / n - s) < 1e-3
+        sel = res.selection()
+        vals, _ = res.column(0)
+        assert (np.diff(sel.astype(np.int64)) > 0).all()                  # sorted, unique
+        assert (vals < k).all()                                           # every kept row passes
+        # idempotence: complement filter keeps exactly the rest
+        res2 = Pipeline(t, fn(Function.CMP_GE, col(0, I), k), [col(0, I)]).run()
+        assert res2.num_rows == n - m
+        # checksum of checksums: kept + dropped values add up to the column total (exact in int64 wraparound)
+        total = int(vals.sum(dtype=np.int64)) + int(res2.column(0)[0].sum(dtype=np.int64))
+        expect_total = total if expect_total is None else expect_total
+        assert total == expect_total
+        res.close()
+        res2.close()
+    t.close()
