@@ -134,7 +134,8 @@ QE_API int qe_ctx_synchronize(qe_ctx *ctx);
 /* cudaStream_t all work of this context is enqueued on (for event timing by the caller) */
 QE_API void *qe_ctx_stream(qe_ctx *ctx);
 /* options: "jit" (1 default / 0 = always interpret), "steps", "vec" (tile shape overrides, 0 = auto),
- * "grid_per_sm" (0 = auto) */
+ * "grid_per_sm" (0 = auto), "staging" (filter kernel loads through cp.async.bulk shared-memory stages:
+ * -1 auto, 0 off, 1 on), "stages" (0 = auto, 2..8) */
 QE_API int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value);
 /* kernels launched by this context so far */
 QE_API int64_t qe_ctx_launch_count(const qe_ctx *ctx);
@@ -219,11 +220,11 @@ QE_API int qe_agg_combine(int agg_fn, const qe_agg_partial *partials, int n, dou
  * then nproj projections) against a schema, write the generated CUDA source
  * into src_buf and, when compile != 0, compile it with NVRTC for sm_100a
  * (cubin copied into cubin_buf when it fits; its size into *cubin_bytes).
- * steps / vec: tile shape overrides, 0 = the library's choice. */
+ * steps / vec: tile shape overrides, 0 = the library's choice; staging: -1 auto, 0 off, 1 on. */
 QE_API int qe_debug_generate(const qe_col_desc *cols, int ncols,
                              const uint32_t *const *programs, const size_t *nwords,
                              int has_filter, int nproj, const int32_t *agg_fns, int nagg,
-                             int steps, int vec, int compile,
+                             int steps, int vec, int staging, int compile,
                              char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes);
 
 QE_API const char *qe_last_error(void);

@@ -94,7 +94,7 @@ SYMBOLS = {
     "qe_result_destroy": (C.c_int, [_vp]),
     "qe_agg_combine": (C.c_int, [C.c_int, C.POINTER(AggPartial), C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
     "qe_debug_generate": (C.c_int, [C.POINTER(ColDesc), C.c_int, C.POINTER(_vp), C.POINTER(C.c_size_t), C.c_int, C.c_int,
-                                    C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.c_int,
+                                    C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),
     "qe_last_error": (C.c_char_p, []),
     "qe_version": (C.c_char_p, []),

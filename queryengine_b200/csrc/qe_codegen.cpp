@@ -15,6 +15,7 @@ struct SV {                  // one entry of the compile-time operand stack
     VType t = VT_NONE;
     bool is_const = false;
     double k = 0.0;
+    std::string raw_int;     // non-empty: the value is a bare INT64 / DATE32 column, this is its integer payload
 };
 
 struct Gen {
@@ -79,8 +80,39 @@ std::string slot_value(const BoundPipeline &bp, int slot)
 {
     char b[48];
     const int t = bp.slot_info[slot].type;
-    if (t == 3 || t == 4) snprintf(b, sizeof b, "(double)in.c%d", slot);   // exact widening, |x| < 2^53
+    if (t == 3) snprintf(b, sizeof b, "qe_i64_to_f64(in.c%d)", slot);      // exact widening, |x| < 2^53
+    else if (t == 4) snprintf(b, sizeof b, "qe_i32_to_f64(in.c%d)", slot);
     else snprintf(b, sizeof b, "in.c%d", slot);
+    return b;
+}
+
+// Integer column against a literal: compare in the integer domain, no widening at all.
+// For an integer x and a finite k:  x < k <=> x < ceil(k),  x <= k <=> x <= floor(k), and so on.
+// (Literals that are NaN, -0.0 or out of the int64 range take the generic path.)
+bool int_literal_ok(const SV &s)
+{
+    return s.is_const && s.k == s.k && std::fabs(s.k) < 4.0e18 && !(s.k == 0.0 && std::signbit(s.k));
+}
+
+std::string int_compare(int op, const std::string &x, double k)
+{
+    const long long lo = (long long)std::floor(k), hi = (long long)std::ceil(k);
+    const bool integral = lo == hi;
+    char b[96];
+    switch (op) {
+    case OP_CMP_LT: snprintf(b, sizeof b, "((qe_i64)%s < %lldLL)", x.c_str(), hi); break;
+    case OP_CMP_LE: snprintf(b, sizeof b, "((qe_i64)%s <= %lldLL)", x.c_str(), lo); break;
+    case OP_CMP_GE: snprintf(b, sizeof b, "((qe_i64)%s >= %lldLL)", x.c_str(), hi); break;
+    case OP_CMP_GT: snprintf(b, sizeof b, "((qe_i64)%s > %lldLL)", x.c_str(), lo); break;
+    case OP_CMP_EQ:
+        if (integral) snprintf(b, sizeof b, "((qe_i64)%s == %lldLL)", x.c_str(), lo);
+        else snprintf(b, sizeof b, "false");
+        break;
+    default:
+        if (integral) snprintf(b, sizeof b, "((qe_i64)%s != %lldLL)", x.c_str(), lo);
+        else snprintf(b, sizeof b, "true");
+        break;
+    }
     return b;
 }
 
@@ -96,6 +128,10 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
             r.t = (bp.slot_info[slot].type == 2) ? VT_BOOL : VT_F64;
             r.val = slot_value(bp, slot);
             char b[32];
+            if (bp.slot_info[slot].type == 3 || bp.slot_info[slot].type == 4) {
+                snprintf(b, sizeof b, "in.c%d", slot);
+                r.raw_int = b;
+            }
             snprintf(b, sizeof b, "in.v%d", slot);
             r.valid = bp.slot_info[slot].nullable ? b : "true";
             break;
@@ -107,7 +143,7 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
             r.t = VT_BOOL; r.val = in.arg ? "true" : "false"; r.valid = "true";
             break;
         case OP_UNARY_PLUS: {                       // M/evaluator/Interpreter.kt:94
-            r = st.back(); st.pop_back(); r.is_const = false;
+            r = st.back(); st.pop_back(); r.is_const = false; r.raw_int.clear();
             break;
         }
         case OP_UNARY_MINUS: {                      // Interpreter.kt:95
@@ -138,6 +174,10 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
             std::string rhs;
             if (a.t == VT_BOOL) {                   // Boolean equality, TypeCheck.kt:65-71
                 rhs = std::string("(") + a.val + (in.op == OP_CMP_EQ ? " == " : " != ") + b.val + ")";
+            } else if (int_literal_ok(b) && !a.raw_int.empty()) {
+                rhs = int_compare(in.op, a.raw_int, b.k);
+            } else if (int_literal_ok(a) && !b.raw_int.empty()) {
+                rhs = int_compare(cmp_swapped(in.op), b.raw_int, a.k);
             } else if (plain_literal(b) && !a.is_const) {
                 rhs = std::string(cmp_fn(in.op)) + "_k(" + a.val + ", " + b.val + ")";
             } else if (plain_literal(a) && !b.is_const) {
@@ -198,7 +238,44 @@ const char *ctype_of(int qtype)
 
 const char *suffix_of(int qtype) { return qtype == 1 ? "f64" : qtype == 3 ? "i64" : "i32"; }
 
+// Layout of one shared-memory stage: per slot the values run, then (if nullable) the validity run.
+struct StageLayout {
+    std::vector<int> val_off, val_bytes, valid_off;
+    int valid_bytes = 0, stride = 0, tx = 0;
+};
+
+StageLayout stage_layout(const BoundPipeline &bp, const TileShape &shape)
+{
+    StageLayout L;
+    const int tile = 8 * shape.steps * 32 * shape.vec;
+    int off = 0;
+    L.valid_bytes = tile / 8;
+    for (const ColumnInfo &c : bp.slot_info) {
+        const int w = c.type == 2 ? 0 : (c.type == 4 ? 4 : 8);
+        const int bytes = w ? tile * w : tile / 8;
+        L.val_off.push_back(off);
+        L.val_bytes.push_back(bytes);
+        L.tx += bytes;
+        off += (bytes + 127) / 128 * 128;
+        if (c.nullable) {
+            L.valid_off.push_back(off);
+            L.tx += L.valid_bytes;
+            off += (L.valid_bytes + 127) / 128 * 128;
+        } else {
+            L.valid_off.push_back(-1);
+        }
+    }
+    L.stride = off ? off : 128;
+    return L;
+}
+
 }  // namespace
+
+size_t staged_smem_bytes(const BoundPipeline &bp, const TileShape &shape)
+{
+    if (!shape.staged) return 0;
+    return (size_t)stage_layout(bp, shape).stride * (size_t)shape.nstages;
+}
 
 std::string generate_source(const BoundPipeline &bp, KernelMode mode, const TileShape &shape)
 {
@@ -275,6 +352,52 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     }
     s += "    }\n";
 
+    if (mode == KM_FILTER && shape.staged) {
+        const StageLayout L = stage_layout(bp, shape);
+        snprintf(b, sizeof b, "    static constexpr int NSTAGES = %d, STAGE_BYTES = %d, STAGE_TX = %d;\n", shape.nstages, L.stride, L.tx);
+        s += b;
+        // one thread: a bulk copy per column run of the tile, all signalling the stage's mbarrier
+        s += "    static __device__ __forceinline__ void issue(const QeParams &p, qe_i64 row0, qe_u32 stage, qe_u32 mbar) {\n";
+        for (int i = 0; i < nslots; i++) {
+            const int t = bp.slot_info[i].type;
+            if (t == 2)
+                snprintf(b, sizeof b, "        qe_bulk_g2s(stage + %d, (const char *)p.col_values[%d] + (row0 >> 3), %d, mbar);\n",
+                         L.val_off[i], i, L.val_bytes[i]);
+            else
+                snprintf(b, sizeof b, "        qe_bulk_g2s(stage + %d, (const char *)p.col_values[%d] + row0 * %d, %d, mbar);\n",
+                         L.val_off[i], i, t == 4 ? 4 : 8, L.val_bytes[i]);
+            s += b;
+            if (bp.slot_info[i].nullable) {
+                snprintf(b, sizeof b, "        qe_bulk_g2s(stage + %d, (const char *)p.col_valid[%d] + (row0 >> 3), %d, mbar);\n",
+                         L.valid_off[i], i, L.valid_bytes);
+                s += b;
+            }
+        }
+        s += "    }\n";
+        s += "    static __device__ __forceinline__ void load_stage(const unsigned char *stage, int r, Row (&rows)[VEC]) {\n";
+        for (int i = 0; i < nslots; i++) {
+            const int t = bp.slot_info[i].type;
+            if (t == 2) {
+                snprintf(b, sizeof b,
+                         "        { const qe_u32 m = qe_stage_bits(stage + %d, r);\n"
+                         "          _Pragma(\"unroll\") for (int j = 0; j < VEC; j++) rows[j].c%d = (m >> j) & 1u; }\n", L.val_off[i], i);
+            } else {
+                snprintf(b, sizeof b,
+                         "        { %s t[VEC]; qe_stage_%s(stage + %d, r, t);\n"
+                         "          _Pragma(\"unroll\") for (int j = 0; j < VEC; j++) rows[j].c%d = t[j]; }\n",
+                         ctype_of(t), suffix_of(t), L.val_off[i], i);
+            }
+            s += b;
+            if (bp.slot_info[i].nullable) {
+                snprintf(b, sizeof b,
+                         "        { const qe_u32 m = qe_stage_bits(stage + %d, r);\n"
+                         "          _Pragma(\"unroll\") for (int j = 0; j < VEC; j++) rows[j].v%d = (m >> j) & 1u; }\n", L.valid_off[i], i);
+                s += b;
+            }
+        }
+        s += "    }\n";
+    }
+
     // ---- eval: RowCallable.invoke for the filter and every projection
     s += "    static __device__ __forceinline__ bool eval(const QeParams &p, const Row &in, Out &o) {\n";
     {
@@ -346,7 +469,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         for (size_t k = 0; k < bp.agg_fns.size(); k++) {
             std::string val = "0.0";
             if (bp.outs[k].type == 1) { snprintf(b, sizeof b, "o.o%d", (int)k); val = b; }
-            else if (bp.outs[k].type == 3 || bp.outs[k].type == 4) { snprintf(b, sizeof b, "(double)o.o%d", (int)k); val = b; }
+            else if (bp.outs[k].type == 3) { snprintf(b, sizeof b, "qe_i64_to_f64(o.o%d)", (int)k); val = b; }
+            else if (bp.outs[k].type == 4) { snprintf(b, sizeof b, "qe_i32_to_f64(o.o%d)", (int)k); val = b; }
             std::string on = "keep";
             if (bp.proj[k].nullable) { snprintf(b, sizeof b, "(keep && o.n%d)", (int)k); on = b; }
             snprintf(b, sizeof b, "        qe_acc_add<%d>(a.a%d, ", bp.agg_fns[k], (int)k);
@@ -362,7 +486,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         s += "    }\n";
     }
     s += "};\n\n";
-    const char *body = mode == KM_FILTER ? "qe_filter_body" : mode == KM_PROJECT ? "qe_project_body" : "qe_agg_body";
+    const char *body = mode == KM_FILTER ? (shape.staged ? "qe_filter_staged_body" : "qe_filter_body")
+                     : mode == KM_PROJECT ? "qe_project_body" : "qe_agg_body";
     snprintf(b, sizeof b,
              "extern \"C\" __global__ void __launch_bounds__(QE_BLOCK, %d) " QE_JIT_ENTRY
              "(const __grid_constant__ QeParams p)\n{\n    %s<P>(p);\n}\n",

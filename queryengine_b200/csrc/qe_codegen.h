@@ -22,7 +22,12 @@ struct TileShape {
     int steps = 2;          // steps per warp per tile
     int vec = 2;            // adjacent rows per lane per step (2: 128-bit loads, 4: 256-bit loads)
     int min_blocks = 1;     // __launch_bounds__ second argument
+    bool staged = false;    // filter kernel: columns arrive through cp.async.bulk into shared-memory stages (vec must be 2)
+    int nstages = 3;
 };
+
+// bytes of dynamic shared memory the staged filter kernel needs (0 when not staged)
+size_t staged_smem_bytes(const BoundPipeline &bp, const TileShape &shape);
 
 // name of the generated entry point
 #define QE_JIT_ENTRY "qe_kernel"

@@ -487,6 +487,97 @@ __device__ __forceinline__ void qe_tile_eval(const QeParams &p, qe_i64 warp_row0
     }
 }
 
+// Evaluate rows that are already in registers (used by both filter bodies).
+template <class P>
+__device__ __forceinline__ void qe_rows_eval(const QeParams &p, qe_i64 warp_row0,
+                                             const typename P::Row (&rows)[P::STEPS][P::VEC],
+                                             typename P::Out (&outs)[P::STEPS][P::VEC],
+                                             qe_u32 (&keep)[P::STEPS])
+{
+    constexpr int STEPS = P::STEPS, VEC = P::VEC;
+    const qe_u32 lane = qe_lane();
+#pragma unroll
+    for (int s = 0; s < STEPS; s++) {
+        const qe_i64 r = warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC;
+        keep[s] = 0;
+#pragma unroll
+        for (int j = 0; j < VEC; j++) {
+            const bool k = P::eval(p, rows[s][j], outs[s][j]) && (r + j < p.nrows);
+            keep[s] |= (k ? 1u : 0u) << j;
+        }
+    }
+}
+
+// Rank of every kept row inside its warp's slice (row order = step, lane, j): one
+// ballot + two popcounts per (step, j).  rank0[s] = rank of the lane's first kept row
+// of step s within the step; step_off[s] = kept rows of the warp in earlier steps.
+template <int STEPS, int VEC>
+__device__ __forceinline__ qe_u32 qe_warp_ranks(const qe_u32 (&keep)[STEPS], qe_u32 (&rank0)[STEPS], qe_u32 (&step_off)[STEPS])
+{
+    const qe_u32 lt = qe_lanemask_lt();
+    qe_u32 wcnt = 0;
+#pragma unroll
+    for (int s = 0; s < STEPS; s++) {
+        qe_u32 before = 0, total = 0;
+#pragma unroll
+        for (int j = 0; j < VEC; j++) {
+            const qe_u32 b = __ballot_sync(QE_FULL_MASK, (keep[s] >> j) & 1u);
+            before += __popc(b & lt);
+            total += __popc(b);
+        }
+        rank0[s] = before;
+        step_off[s] = wcnt;
+        wcnt += total;
+    }
+    return wcnt;
+}
+
+// Ordered scatter of one warp's kept rows: a warp step's survivors land on
+// consecutive addresses starting at gbase + step_off[s].
+template <class P>
+__device__ __forceinline__ void qe_warp_scatter(const QeParams &p, qe_i64 warp_row0, qe_u64 gbase,
+                                                const typename P::Out (&outs)[P::STEPS][P::VEC],
+                                                const qe_u32 (&keep)[P::STEPS], const qe_u32 (&rank0)[P::STEPS],
+                                                const qe_u32 (&step_off)[P::STEPS])
+{
+    constexpr int STEPS = P::STEPS, VEC = P::VEC;
+    const qe_u32 lane = qe_lane();
+#pragma unroll
+    for (int s = 0; s < STEPS; s++) {
+        const qe_u64 gstep = gbase + step_off[s];
+        const qe_i64 r = warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC;
+        qe_u32 rank[VEC];
+        qe_u32 rr = rank0[s];
+#pragma unroll
+        for (int j = 0; j < VEC; j++) {
+            rank[j] = rr;
+            rr += (keep[s] >> j) & 1u;
+        }
+#pragma unroll
+        for (int j = 0; j < VEC; j++) {
+            const qe_u64 pos = gstep + rank[j];
+            if (((keep[s] >> j) & 1u) && pos < (qe_u64)p.out_capacity) {
+                if (p.sel) p.sel[pos] = p.sel_base + (qe_u32)(r + j);
+                P::emit(p, pos, outs[s][j]);
+            }
+        }
+        if (P::NBITCOLS > 0 && gstep < (qe_u64)p.out_capacity) {
+#pragma unroll
+            for (int b = 0; b < P::NBITCOLS; b++) {
+                qe_u32 *bm = P::bitcol(p, b);
+                if (bm) {
+                    qe_u32 bits = 0;
+#pragma unroll
+                    for (int j = 0; j < VEC; j++) bits |= (P::bit(outs[s][j], b) ? 1u : 0u) << j;
+                    qe_store_bits_compact<VEC>(bm, gstep, rank, keep[s], bits);
+                }
+            }
+        }
+    }
+}
+
+// K1, register-sourced variant: the columns are loaded straight into registers
+// with 128/256-bit LDGs.  One ticket, three block barriers per tile.
 template <class P>
 __device__ __forceinline__ void qe_filter_body(const QeParams &p)
 {
@@ -499,7 +590,6 @@ __device__ __forceinline__ void qe_filter_body(const QeParams &p)
     __shared__ qe_u64 s_prefix;
 
     const qe_u32 lane = qe_lane(), warp = qe_warp();
-    const qe_u32 lt = qe_lanemask_lt();
 
     for (;;) {
         if (threadIdx.x == 0) s_tile = atomicAdd(p.ticket, 1u);
@@ -509,31 +599,16 @@ __device__ __forceinline__ void qe_filter_body(const QeParams &p)
         const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
 
         typename P::Out outs[STEPS][VEC];
-        qe_u32 keep[STEPS], inb[STEPS];
-        qe_tile_eval<P>(p, warp_row0, outs, keep, inb);
-
-        // rank of every kept row inside its warp's slice (row order = step, lane, j)
-        qe_u32 rank[STEPS][VEC];
-        qe_u32 step_off[STEPS];
-        qe_u32 wcnt = 0;
+        qe_u32 keep[STEPS];
+        {
+            typename P::Row rows[STEPS][VEC];
 #pragma unroll
-        for (int s = 0; s < STEPS; s++) {
-            qe_u32 before = 0, total = 0;
-#pragma unroll
-            for (int j = 0; j < VEC; j++) {
-                const qe_u32 b = __ballot_sync(QE_FULL_MASK, (keep[s] >> j) & 1u);
-                before += __popc(b & lt);
-                total += __popc(b);
-            }
-            step_off[s] = wcnt;
-            qe_u32 r = before;
-#pragma unroll
-            for (int j = 0; j < VEC; j++) {
-                rank[s][j] = r;                      // rank within the warp step
-                r += (keep[s] >> j) & 1u;
-            }
-            wcnt += total;
+            for (int s = 0; s < STEPS; s++)
+                P::load(p, warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC, rows[s]);
+            qe_rows_eval<P>(p, warp_row0, rows, outs, keep);
         }
+        qe_u32 rank0[STEPS], step_off[STEPS];
+        const qe_u32 wcnt = qe_warp_ranks<STEPS, VEC>(keep, rank0, step_off);
         if (lane == 0) s_warp_cnt[warp] = wcnt;
         __syncthreads();
 
@@ -552,34 +627,174 @@ __device__ __forceinline__ void qe_filter_body(const QeParams &p)
             }
         }
         __syncthreads();
-        const qe_u64 gbase = s_prefix + woff;
+        qe_warp_scatter<P>(p, warp_row0, s_prefix + woff, outs, keep, rank0, step_off);
+    }
+}
 
-        // ordered scatter: a warp step's kept rows land on consecutive addresses
+// ---- bulk-copy (TMA) staging ---------------------------------------------------
+// cp.async.bulk moves a contiguous run of a column from HBM into shared memory
+// without touching the register file and signals an mbarrier when the bytes have
+// landed (SASS: UBLKCP + SYNCS).  With the tile's columns landing in a ring of
+// shared-memory stages, the bytes in flight per SM are bounded by shared memory
+// (up to 227 KB) instead of by registers, and the loads of the next tiles overlap
+// the scan / look-back / scatter of the current one.
+
+__device__ __forceinline__ qe_u32 qe_smem_addr(const void *p)
+{
+    return (qe_u32)__cvta_generic_to_shared(p);
+}
+
+__device__ __forceinline__ void qe_mbar_init(qe_u32 mbar, qe_u32 count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(mbar), "r"(count) : "memory");
+}
+
+__device__ __forceinline__ void qe_mbar_expect_tx(qe_u32 mbar, qe_u32 bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(mbar), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void qe_mbar_wait(qe_u32 mbar, qe_u32 parity)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "QE_WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra QE_DONE_%=;\n\t"
+        "bra QE_WAIT_%=;\n\t"
+        "QE_DONE_%=:\n\t"
+        "}" :: "r"(mbar), "r"(parity) : "memory");
+}
+
+// global -> shared bulk copy; size and both addresses are multiples of 16 bytes
+__device__ __forceinline__ void qe_bulk_g2s(qe_u32 dst_smem, const void *src, qe_u32 bytes, qe_u32 mbar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(dst_smem), "l"(src), "r"(bytes), "r"(mbar) : "memory");
+}
+
+__device__ __forceinline__ void qe_lds_f64x2(const void *p, double &a, double &b)
+{
+    asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(a), "=d"(b) : "r"(qe_smem_addr(p)));
+}
+
+__device__ __forceinline__ void qe_lds_i64x2(const void *p, qe_i64 &a, qe_i64 &b)
+{
+    asm volatile("ld.shared.v2.s64 {%0,%1}, [%2];" : "=l"(a), "=l"(b) : "r"(qe_smem_addr(p)));
+}
+
+__device__ __forceinline__ void qe_lds_i32x2(const void *p, qe_i32 &a, qe_i32 &b)
+{
+    asm volatile("ld.shared.v2.s32 {%0,%1}, [%2];" : "=r"(a), "=r"(b) : "r"(qe_smem_addr(p)));
+}
+
+// VEC = 2 only: lane l reads the 16 bytes at l*16 of each 512-byte warp step (conflict-free)
+__device__ __forceinline__ void qe_stage_f64(const unsigned char *col, int r, double (&v)[2])
+{
+    qe_lds_f64x2(col + (size_t)r * 8, v[0], v[1]);
+}
+
+__device__ __forceinline__ void qe_stage_i64(const unsigned char *col, int r, qe_i64 (&v)[2])
+{
+    qe_lds_i64x2(col + (size_t)r * 8, v[0], v[1]);
+}
+
+__device__ __forceinline__ void qe_stage_i32(const unsigned char *col, int r, qe_i32 (&v)[2])
+{
+    qe_lds_i32x2(col + (size_t)r * 4, v[0], v[1]);
+}
+
+__device__ __forceinline__ qe_u32 qe_stage_bits(const unsigned char *bitmap, int r)
+{
+    const qe_u32 w = *(const qe_u32 *)(bitmap + (r >> 5) * 4);
+    return (w >> (r & 31)) & 3u;
+}
+
+// K1, staged variant.  Additional members of P:
+//   static constexpr int NSTAGES, STAGE_BYTES (stride of one stage), STAGE_TX (bytes the copies of one stage move);
+//   static void issue(const QeParams&, qe_i64 tile_row0, qe_u32 stage_smem, qe_u32 mbar);   one thread
+//   static void load_stage(const unsigned char *stage, int r, Row (&rows)[VEC]);             r = row within the tile
+template <class P>
+__device__ __forceinline__ void qe_filter_staged_body(const QeParams &p)
+{
+    constexpr int STEPS = P::STEPS, VEC = P::VEC, NST = P::NSTAGES;
+    constexpr int WARP_ROWS = STEPS * 32 * VEC;
+    constexpr int TILE = QE_WARPS * WARP_ROWS;
+
+    extern __shared__ __align__(128) unsigned char qe_dyn_smem[];
+    __shared__ __align__(8) qe_u64 s_full[NST];
+    __shared__ qe_u32 s_tile[NST];
+    __shared__ qe_u32 s_warp_cnt[QE_WARPS];
+    __shared__ qe_u64 s_prefix;
+
+    const qe_u32 lane = qe_lane(), warp = qe_warp();
+
+    // warp 1, lane 0 is the producer: it owns the tickets and issues every bulk copy
+    const bool producer = threadIdx.x == 32;
+    if (producer) {
 #pragma unroll
-        for (int s = 0; s < STEPS; s++) {
-            const qe_u64 gstep = gbase + step_off[s];
-            const qe_i64 r = warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC;
+        for (int st = 0; st < NST; st++) qe_mbar_init(qe_smem_addr(&s_full[st]), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 #pragma unroll
-            for (int j = 0; j < VEC; j++) {
-                const qe_u64 pos = gstep + rank[s][j];
-                if (((keep[s] >> j) & 1u) && pos < (qe_u64)p.out_capacity) {
-                    if (p.sel) p.sel[pos] = p.sel_base + (qe_u32)(r + j);
-                    P::emit(p, pos, outs[s][j]);
-                }
-            }
-            if (P::NBITCOLS > 0 && gstep < (qe_u64)p.out_capacity) {
-#pragma unroll
-                for (int b = 0; b < P::NBITCOLS; b++) {
-                    qe_u32 *bm = P::bitcol(p, b);
-                    if (bm) {
-                        qe_u32 bits = 0;
-#pragma unroll
-                        for (int j = 0; j < VEC; j++) bits |= (P::bit(outs[s][j], b) ? 1u : 0u) << j;
-                        qe_store_bits_compact<VEC>(bm, gstep, rank[s], keep[s], bits);
-                    }
-                }
+        for (int st = 0; st < NST; st++) {
+            const qe_u32 t = atomicAdd(p.ticket, 1u);
+            s_tile[st] = t;
+            if (t < p.ntiles) {
+                qe_mbar_expect_tx(qe_smem_addr(&s_full[st]), (qe_u32)P::STAGE_TX);
+                P::issue(p, (qe_i64)t * TILE, qe_smem_addr(qe_dyn_smem + (size_t)st * P::STAGE_BYTES), qe_smem_addr(&s_full[st]));
             }
         }
+    }
+    __syncthreads();
+
+    for (qe_u32 it = 0;; it++) {
+        const int st = (int)(it % NST);
+        const qe_u32 tile = s_tile[st];
+        if (tile >= p.ntiles) break;                      // tickets only grow: every later stage is past the end too
+        const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
+        const unsigned char *stage = qe_dyn_smem + (size_t)st * P::STAGE_BYTES;
+
+        qe_mbar_wait(qe_smem_addr(&s_full[st]), (it / NST) & 1u);
+
+        typename P::Out outs[STEPS][VEC];
+        qe_u32 keep[STEPS];
+        {
+            typename P::Row rows[STEPS][VEC];
+#pragma unroll
+            for (int s = 0; s < STEPS; s++)
+                P::load_stage(stage, (int)(warp * WARP_ROWS + s * 32 * VEC + lane * VEC), rows[s]);
+            qe_rows_eval<P>(p, warp_row0, rows, outs, keep);
+        }
+        qe_u32 rank0[STEPS], step_off[STEPS];
+        const qe_u32 wcnt = qe_warp_ranks<STEPS, VEC>(keep, rank0, step_off);
+        if (lane == 0) s_warp_cnt[warp] = wcnt;
+        __syncthreads();                                  // stage `st` and s_tile[st] have been consumed by everyone
+
+        if (producer) {                                   // refill the stage for iteration it + NST
+            const qe_u32 t = atomicAdd(p.ticket, 1u);
+            s_tile[st] = t;
+            if (t < p.ntiles) {
+                qe_mbar_expect_tx(qe_smem_addr(&s_full[st]), (qe_u32)P::STAGE_TX);
+                P::issue(p, (qe_i64)t * TILE, qe_smem_addr(stage), qe_smem_addr(&s_full[st]));
+            }
+        }
+        qe_u32 woff = 0, tile_total = 0;
+#pragma unroll
+        for (int w = 0; w < QE_WARPS; w++) {
+            const qe_u32 c = s_warp_cnt[w];
+            woff += (qe_u32)w < warp ? c : 0u;
+            tile_total += c;
+        }
+        if (warp == 0) {
+            const qe_u64 excl = qe_lookback(p.tile_state, tile, tile_total);
+            if (lane == 0) {
+                s_prefix = excl;
+                if (tile == p.ntiles - 1) *p.out_count = excl + tile_total;
+            }
+        }
+        __syncthreads();
+        qe_warp_scatter<P>(p, warp_row0, s_prefix + woff, outs, keep, rank0, step_off);
     }
 }
 

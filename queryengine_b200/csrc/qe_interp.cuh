@@ -50,8 +50,8 @@ static __device__ __noinline__ QeInterpValue qe_interp_run(const QeParams &p, co
             bool bv = false;
             const void *col = p.col_values[arg];
             if (type == QE_T_F64) f = ((const double *)col)[r];
-            else if (type == QE_T_I64) f = (double)((const qe_i64 *)col)[r];
-            else if (type == QE_T_DATE32) f = (double)((const qe_i32 *)col)[r];
+            else if (type == QE_T_I64) f = qe_i64_to_f64(((const qe_i64 *)col)[r]);
+            else if (type == QE_T_DATE32) f = qe_i32_to_f64(((const qe_i32 *)col)[r]);
             else bv = (((const qe_u32 *)col)[r >> 5] >> ((qe_u32)r & 31u)) & 1u;
             sf[sp] = f;
             sb = (sb & ~(1u << sp)) | ((bv ? 1u : 0u) << sp);
@@ -219,7 +219,7 @@ struct QeInterpProgram {
             const qe_u32 type = p.iprog[QE_IP_OUTS + k] & 0xffu;
             double v = 0.0;
             if (type == QE_T_F64) v = o.f[k];
-            else if (type == QE_T_I64 || type == QE_T_DATE32) v = (double)qe_f64_bits(o.f[k]);
+            else if (type == QE_T_I64 || type == QE_T_DATE32) v = qe_i64_to_f64(qe_f64_bits(o.f[k]));
             if (keep && ((o.v >> k) & 1u)) {
                 QeAcc one;
                 one.count = 1; one.sum = v; one.mn = v; one.mx = v;

@@ -24,6 +24,8 @@ struct Nvrtc {
     nvrtcResult (*GetProgramLogSize)(nvrtcProgram, size_t *) = nullptr;
     nvrtcResult (*GetProgramLog)(nvrtcProgram, char *) = nullptr;
     const char *(*GetErrorString)(nvrtcResult) = nullptr;
+    nvrtcResult (*Version)(int *, int *) = nullptr;
+    int major = 0, minor = 0;
 };
 
 Nvrtc &nvrtc()
@@ -31,12 +33,16 @@ Nvrtc &nvrtc()
     static Nvrtc n;
     static std::once_flag once;
     std::call_once(once, [] {
+        // Absolute paths of the toolkit first: a bare soname would resolve to whatever libnvrtc the
+        // process already has loaded (PyTorch bundles an older one whose ptxas lacks the 256-bit
+        // loads of sm_100), and loading by path gets the toolkit's own copy beside it.
         const char *candidates[] = {
             getenv("QE_NVRTC_PATH"),
-            "libnvrtc.so.12",
-            "libnvrtc.so",
             "/usr/local/cuda/lib64/libnvrtc.so.12",
             "/usr/local/cuda/targets/x86_64-linux/lib/libnvrtc.so.12",
+            "/usr/local/cuda-12.9/targets/x86_64-linux/lib/libnvrtc.so.12",
+            "libnvrtc.so.12",
+            "libnvrtc.so",
             "libnvrtc.so.13",
         };
         for (const char *c : candidates) {
@@ -49,8 +55,9 @@ Nvrtc &nvrtc()
         *(void **)(&n.name) = dlsym(n.handle, "nvrtc" #name); \
         if (!n.name) { n.why = "nvrtc" #name " missing from libnvrtc"; n.handle = nullptr; return; }
         QE_SYM(CreateProgram) QE_SYM(CompileProgram) QE_SYM(DestroyProgram) QE_SYM(GetCUBINSize) QE_SYM(GetCUBIN)
-        QE_SYM(GetProgramLogSize) QE_SYM(GetProgramLog) QE_SYM(GetErrorString)
+        QE_SYM(GetProgramLogSize) QE_SYM(GetProgramLog) QE_SYM(GetErrorString) QE_SYM(Version)
 #undef QE_SYM
+        n.Version(&n.major, &n.minor);
     });
     return n;
 }
@@ -62,6 +69,19 @@ bool jit_available(std::string *why)
     Nvrtc &n = nvrtc();
     if (!n.handle && why) *why = n.why;
     return n.handle != nullptr;
+}
+
+bool jit_wide_loads_supported()
+{
+    Nvrtc &n = nvrtc();
+    // ld.global.v4.f64 / .v4.b64 (LDG.E.256) needs PTX ISA 8.8 = CUDA 12.9
+    return n.handle && (n.major > 12 || (n.major == 12 && n.minor >= 9));
+}
+
+std::string jit_version()
+{
+    Nvrtc &n = nvrtc();
+    return n.handle ? std::to_string(n.major) + "." + std::to_string(n.minor) : std::string("unavailable");
 }
 
 bool jit_compile(const std::string &source, std::vector<char> &cubin, std::string &log)
@@ -101,7 +121,7 @@ bool jit_compile(const std::string &source, std::vector<char> &cubin, std::strin
     return true;
 }
 
-bool jit_load(const std::vector<char> &cubin, const char *entry, JitKernel &out, std::string &err)
+bool jit_load(const std::vector<char> &cubin, const char *entry, size_t dyn_smem, JitKernel &out, std::string &err)
 {
     cudaError_t e = cudaLibraryLoadData(&out.library, cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0);
     if (e != cudaSuccess) { err = std::string("cudaLibraryLoadData: ") + cudaGetErrorString(e); return false; }
@@ -112,8 +132,18 @@ bool jit_load(const std::vector<char> &cubin, const char *entry, JitKernel &out,
         out.library = nullptr;
         return false;
     }
+    out.dyn_smem = dyn_smem;
+    if (dyn_smem > 0) {
+        e = cudaFuncSetAttribute((const void *)out.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_smem);
+        if (e != cudaSuccess) {
+            err = std::string("cudaFuncSetAttribute(MaxDynamicSharedMemorySize): ") + cudaGetErrorString(e);
+            cudaLibraryUnload(out.library);
+            out.library = nullptr;
+            return false;
+        }
+    }
     int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, (const void *)out.kernel, 256, 0) == cudaSuccess && n > 0)
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, (const void *)out.kernel, 256, dyn_smem) == cudaSuccess && n > 0)
         out.blocks_per_sm = n;
     else
         (void)cudaGetLastError();

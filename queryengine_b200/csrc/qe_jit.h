@@ -22,17 +22,22 @@ struct JitKernel {
     cudaKernel_t kernel = nullptr;
     int blocks_per_sm = 1;
     int regs = 0;
+    size_t dyn_smem = 0;    // dynamic shared memory per CTA
 };
 
 // True when libnvrtc could be loaded.  `why` receives the reason otherwise.
 bool jit_available(std::string *why);
+
+// 256-bit global loads/stores (VEC = 4 tile shapes) need NVRTC >= 12.9.
+bool jit_wide_loads_supported();
+std::string jit_version();
 
 // Compile `source` (which includes "qe_device.cuh") to a cubin for sm_100a.
 // Does not need a GPU.  Returns false and fills `log` on failure.
 bool jit_compile(const std::string &source, std::vector<char> &cubin, std::string &log);
 
 // Load a cubin on the current device and look up the entry point.
-bool jit_load(const std::vector<char> &cubin, const char *entry, JitKernel &out, std::string &err);
+bool jit_load(const std::vector<char> &cubin, const char *entry, size_t dyn_smem, JitKernel &out, std::string &err);
 void jit_unload(JitKernel &k);
 
 }  // namespace qe

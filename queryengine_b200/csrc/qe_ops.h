@@ -51,6 +51,24 @@ QE_HD double qe_bits_f64(qe_i64 i)
 #endif
 }
 
+// ---- exact integer -> double widening (INT64 / DATE32 columns) -----------------
+// The hardware conversion (I2F.F64.S64) runs on the quarter-rate XU pipe and was
+// the limiter of the int64 scan (ncu: XU 78 % busy, HBM 19 %).  For |x| < 2^51
+// the classic magic-number form is exact and uses one integer add and one DADD:
+//   bits(2^52 + 2^51) + x  is the double  2^52 + 2^51 + x ; subtract the bias.
+QE_HD double qe_i64_to_f64(qe_i64 x)
+{
+    const qe_i64 lim = (qe_i64)1 << 51;
+    if ((qe_u64)(x + lim) < ((qe_u64)1 << 52))
+        return qe_bits_f64(x + (qe_i64)0x4338000000000000LL) - 6755399441055744.0;
+    return (double)x;
+}
+
+QE_HD double qe_i32_to_f64(qe_i32 x)
+{
+    return qe_bits_f64((qe_i64)x + (qe_i64)0x4338000000000000LL) - 6755399441055744.0;
+}
+
 // ---- java.lang.Double.compare as a monotone integer key ---------------------
 // Double.compare orders  -Inf < ... < -0.0 < 0.0 < ... < +Inf < NaN  and treats
 // every NaN as one value.  Canonicalise NaN to 0x7ff8000000000000 (what

@@ -133,7 +133,7 @@ struct qe_ctx {
     Pool pool;
     std::unordered_map<std::string, JitEntry> jit_cache;
     // options
-    int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0;
+    int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = -1, opt_stages = 0;
     int64_t launches = 0;
     bool warned_no_nvrtc = false;
     // pinned staging ring for uploads from pageable memory
@@ -251,6 +251,12 @@ extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
     } else if (k == "grid_per_sm") {
         if (value < 0 || value > 32) return fail(QE_ERR_INVALID_ARGUMENT, "grid_per_sm must be in [0, 32]");
         ctx->opt_grid_per_sm = value;
+    } else if (k == "staging") {
+        if (value < -1 || value > 1) return fail(QE_ERR_INVALID_ARGUMENT, "staging must be -1 (auto), 0 or 1");
+        ctx->opt_staging = value;
+    } else if (k == "stages") {
+        if (value != 0 && (value < 2 || value > 8)) return fail(QE_ERR_INVALID_ARGUMENT, "stages must be 0 (auto) or 2..8");
+        ctx->opt_stages = value;
     } else return fail(QE_ERR_INVALID_ARGUMENT, "unknown option '" + k + "'");
     return QE_OK;
 }
@@ -555,6 +561,25 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
     s.steps = (int)(pow2 / (size_t)s.vec);
     if (ctx->opt_vec) s.vec = (int)ctx->opt_vec;
     if (ctx->opt_steps) s.steps = (int)ctx->opt_steps;
+    if (s.vec == 4 && !qe::jit_wide_loads_supported()) {      // older NVRTC: same rows per thread with 128-bit accesses
+        s.vec = 2;
+        if (!ctx->opt_steps) s.steps = std::min(8, s.steps * 2);
+    }
+    // Filter kernel: land the columns in shared-memory stages with bulk copies, so the bytes in
+    // flight are not bounded by registers and the next tiles load during scan / look-back / scatter.
+    s.staged = mode == qe::KM_FILTER && ctx->opt_staging != 0;
+    if (s.staged) {
+        s.vec = 2;                                             // staged rows are read back with 128-bit LDS
+        if (!ctx->opt_steps) {                                 // ~16 KB per stage, 8 rows per thread at most
+            const size_t rows = std::max<size_t>(512, std::min<size_t>(2048, (16u << 10) / row_bytes / 512 * 512));
+            s.steps = (int)(rows / 512);
+        }
+        const size_t stage = qe::staged_smem_bytes(bp, s) / (size_t)s.nstages;
+        size_t n = ctx->opt_stages ? (size_t)ctx->opt_stages : std::min<size_t>(4, std::max<size_t>(2, (48u << 10) / stage));
+        while (n > 2 && n * stage > (200u << 10)) n--;
+        s.nstages = (int)n;
+        if ((size_t)s.nstages * stage > (220u << 10)) s.staged = false;   // does not fit: register-sourced kernel
+    }
     s.min_blocks = 1;
     return s;
 }
@@ -595,7 +620,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
                           JitEntry **out)
 {
     char suffix[64];
-    snprintf(suffix, sizeof suffix, "|M%d|S%d|V%d", (int)mode, shape.steps, shape.vec);
+    snprintf(suffix, sizeof suffix, "|M%d|S%d|V%d|T%d.%d", (int)mode, shape.steps, shape.vec, shape.staged ? 1 : 0, shape.nstages);
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) { *out = &it->second; return QE_OK; }
@@ -609,7 +634,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     JitEntry e;
     e.shape = shape;
     std::string err;
-    if (!qe::jit_load(cubin, QE_JIT_ENTRY, e.kernel, err)) return fail(QE_ERR_JIT, err);
+    if (!qe::jit_load(cubin, QE_JIT_ENTRY, qe::staged_smem_bytes(bp, shape), e.kernel, err)) return fail(QE_ERR_JIT, err);
     if (getenv("QE_DUMP_JIT"))
         fprintf(stderr, "[qegpu] jit %s: %d regs, %d CTAs/SM\n", key.c_str(), e.kernel.regs, e.kernel.blocks_per_sm);
     auto ins = ctx->jit_cache.emplace(key, e);
@@ -785,7 +810,7 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
     if (n > 0) {
         if (use_jit) {
             void *args[] = {&p};
-            QE_CUDA(cudaLaunchKernel((const void *)jit->kernel.kernel, dim3(grid), dim3(QE_BLOCK), args, 0, ctx->stream));
+            QE_CUDA(cudaLaunchKernel((const void *)jit->kernel.kernel, dim3(grid), dim3(QE_BLOCK), args, jit->kernel.dyn_smem, ctx->stream));
         } else {
             QE_CUDA(qe::launch_interp((int)mode, p, grid, ctx->stream));
         }
@@ -1045,7 +1070,7 @@ extern "C" int qe_result_used_jit(const qe_result *r) { return r && r->used_jit 
 extern "C" int qe_debug_generate(const qe_col_desc *cols, int ncols,
                                  const uint32_t *const *programs, const size_t *nwords,
                                  int has_filter, int nproj, const int32_t *agg_fns, int nagg,
-                                 int steps, int vec, int compile,
+                                 int steps, int vec, int staging, int compile,
                                  char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes)
 {
     if (!cols || ncols <= 0 || !programs || !nwords) return fail(QE_ERR_INVALID_ARGUMENT, "NULL argument");
@@ -1067,6 +1092,7 @@ extern "C" int qe_debug_generate(const qe_col_desc *cols, int ncols,
     qe_ctx dummy;
     dummy.opt_steps = steps;
     dummy.opt_vec = vec;
+    dummy.opt_staging = staging;
     const qe::TileShape shape = choose_shape(&dummy, bp, mode);
     const std::string src = qe::generate_source(bp, mode, shape);
     if (src_buf && src_cap) {

@@ -95,10 +95,14 @@ def ulp(x: float) -> float:
 
 
 def check_sum(gpu: float, terms: np.ndarray, sequential: float) -> None:
-    exact = math.fsum(terms.tolist())
-    if not math.isfinite(exact) or not math.isfinite(sequential):
-        assert (math.isnan(gpu) and math.isnan(sequential)) or gpu == sequential or not math.isfinite(gpu)
+    if not np.isfinite(terms).all() or not math.isfinite(sequential):
+        # Inf / NaN terms or an overflowing sequential sum: the order of additions decides between
+        # Inf and NaN, so only "not finite" is comparable
+        assert not math.isfinite(gpu) or not np.isfinite(terms).all(), (gpu, sequential)
+        if np.isnan(terms).any():
+            assert math.isnan(gpu)
         return
+    exact = math.fsum(terms.tolist())
     tol = max(abs(sequential - exact), 4 * ulp(exact))
     assert abs(gpu - exact) <= tol, (gpu, exact, sequential, tol)
 

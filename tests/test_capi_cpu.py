@@ -49,7 +49,7 @@ def test_serializer_postfix_words():
         FunctionExpression(Function.ADD, [lit(1.0)])
 
 
-def _generate(schema, filter_, projs, aggs=(), steps=0, vec=0, compile_=True):
+def _generate(schema, filter_, projs, aggs=(), steps=0, vec=0, compile_=True, staging=-1):
     L = capi.lib()
     descs = (capi.ColDesc * len(schema))(*[capi.ColDesc(int(t), 1 if n else 0) for t, n in schema])
     exprs = ([filter_] if filter_ is not None else []) + list(projs)
@@ -60,7 +60,7 @@ def _generate(schema, filter_, projs, aggs=(), steps=0, vec=0, compile_=True):
     src = C.create_string_buffer(1 << 16)
     nbytes = C.c_size_t(0)
     rc = L.qe_debug_generate(descs, len(schema), ptrs, lens, 1 if filter_ is not None else 0, len(projs),
-                             aggarr, len(aggs), steps, vec, 1 if compile_ else 0, src, len(src), None, 0, C.byref(nbytes))
+                             aggarr, len(aggs), steps, vec, staging, 1 if compile_ else 0, src, len(src), None, 0, C.byref(nbytes))
     return rc, src.value.decode(), nbytes.value, L.qe_last_error().decode()
 
 
@@ -75,7 +75,8 @@ Q6_PROJ = fn(Function.MUL, col(1), col(2))
 def test_generated_code_compiles_for_sm100a():
     rc, src, nbytes, err = _generate([(I, False)], fn(Function.CMP_LT, col(0, I), 1e6), [col(0, I)])
     assert rc == 0, err
-    assert "qe_filter_body<P>" in src and "qe_cmp_lt_k((double)in.c0" in src and nbytes > 1000
+    assert "qe_filter_staged_body<P>" in src and "((qe_i64)in.c0 < 1000000LL)" in src and nbytes > 1000
+    assert "qe_bulk_g2s(stage + 0, (const char *)p.col_values[0] + row0 * 8" in src
     rc, src, nbytes, err = _generate(Q6_SCHEMA, Q6_FILTER, [Q6_PROJ], [AggregationFunction.SUM])
     assert rc == 0, err
     assert "qe_agg_body<P>" in src and "qe_acc_add<2>" in src
@@ -89,11 +90,13 @@ def test_generated_code_compiles_for_sm100a():
     # every tile shape the runtime may pick
     for steps in (1, 2, 4, 8):
         for vec in (2, 4):
-            rc, src, nbytes, err = _generate([(D, True), (B, True), (T, False)],
-                                             fn(Function.OR, col(1, B), fn(Function.CMP_GE, col(2, T), 9000.0)),
-                                             [fn(Function.IF, col(1, B), col(0), 1.0), col(1, B), col(2, T)],
-                                             steps=steps, vec=vec)
-            assert rc == 0, (steps, vec, err)
+            for staging in (0, 1):
+                rc, src, nbytes, err = _generate([(D, True), (B, True), (T, False)],
+                                                 fn(Function.OR, col(1, B), fn(Function.CMP_GE, col(2, T), 9000.0)),
+                                                 [fn(Function.IF, col(1, B), col(0), 1.0), col(1, B), col(2, T)],
+                                                 steps=steps, vec=vec, staging=staging)
+                assert rc == 0, (steps, vec, staging, err)
+                assert ("qe_filter_staged_body<P>" in src) == bool(staging)
 
 
 def test_type_errors_follow_the_reference_typecheck():
@@ -125,7 +128,7 @@ def test_malformed_programs_are_rejected():
         w = np.asarray(words, dtype=np.uint32)
         ptrs = (C.c_void_p * 1)(w.ctypes.data)
         lens = (C.c_size_t * 1)(w.size)
-        return L.qe_debug_generate(descs, 1, ptrs, lens, 0, 1, None, 0, 0, 0, 0, None, 0, None, 0, None)
+        return L.qe_debug_generate(descs, 1, ptrs, lens, 0, 1, None, 0, 0, 0, -1, 0, None, 0, None, 0, None)
     assert run([int(Function.ADD)]) == capi.QE_ERR_PROGRAM                     # stack underflow
     assert run([32, 32]) == capi.QE_ERR_PROGRAM                                # two values left
     assert run([33, 0]) == capi.QE_ERR_PROGRAM                                 # truncated constant
@@ -160,3 +163,29 @@ def test_agg_combine_is_fixed_order_and_matches_accumulator_rules():
     # order matters for floating-point sums: the combination is by array (rank) order
     big = [P(1e16, 1, 0, 0), P(1.0, 1, 0, 0), P(-1e16, 1, 0, 0)]
     assert combine_aggregate(A.SUM, big) == (1e16 + 1.0) + -1e16
+
+
+def test_toolkit_nvrtc_is_used_even_when_an_older_one_is_already_loaded():
+    """PyTorch bundles libnvrtc 12.8, whose ptxas rejects the 256-bit loads of sm_100.  With it
+    loaded first (as in bench.py, which imports torch), the library must still pick the
+    toolkit's 12.9 copy -- or fall back to 128-bit tile shapes -- and compile."""
+    import glob
+    import subprocess
+    import sys
+    import sysconfig
+    site = sysconfig.get_paths()["purelib"]
+    old = glob.glob(os.path.join(site, "nvidia", "cuda_nvrtc", "lib", "libnvrtc.so.12"))
+    if not old:
+        pytest.skip("no bundled libnvrtc to collide with")
+    code = f"""
+import ctypes, sys
+sys.path.insert(0, {ROOT!r}); sys.path.insert(0, {os.path.join(ROOT, 'tests')!r})
+ctypes.CDLL({old[0]!r}, mode=ctypes.RTLD_GLOBAL)
+from test_capi_cpu import _generate, I
+from queryengine_b200.ast import Function, col, fn
+rc, src, nbytes, err = _generate([(I, False)], fn(Function.CMP_LT, col(0, I), 1e6), [col(0, I)], steps=4, vec=4)
+assert rc == 0, err
+print("ok", nbytes)
+"""
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]

@@ -121,6 +121,17 @@ def test_compare_against_extreme_literals(ctx, k):
         compare_pipeline(ctx, spec, fn(f, col(0), float(k)), [fn(f, float(k), col(1))])
 
 
+@pytest.mark.parametrize("k", [-3.5, -3.0, -0.0, 0.0, 2.0, 2.5, 9000.0, 1e18, 1e19, -1e19, np.inf, -np.inf, np.nan])
+def test_integer_columns_against_literals(ctx, k):
+    # INT64 / DATE32 columns compare in the integer domain when the literal allows it; same answers
+    # as widening to DOUBLE first (the oracle sees the widened values)
+    rng = np.random.default_rng(17)
+    spec = random_table(rng, 3000, "iIt")
+    for f in (Function.CMP_LT, Function.CMP_LE, Function.CMP_GE, Function.CMP_GT, Function.CMP_EQ, Function.CMP_NE):
+        compare_pipeline(ctx, spec, fn(f, col(0, I), float(k)),
+                         [fn(f, float(k), col(1, I)), fn(f, col(2, T), float(k) + 9000.0), col(0, I)])
+
+
 @pytest.mark.parametrize("seed", range(12))
 def test_random_trees_jit(ctx, seed):
     rng = np.random.default_rng(1000 + seed)
@@ -143,17 +154,22 @@ def test_random_trees_interpreter(ctx, seed):
     compare_pipeline(ctx, spec, filt, [g.double(5), g.boolean(3)], interpreter=True)
 
 
-@pytest.mark.parametrize("steps,vec", [(1, 2), (2, 2), (8, 2), (1, 4), (4, 4), (8, 4)])
-def test_every_tile_shape(ctx, steps, vec):
+@pytest.mark.parametrize("steps,vec,staging", [(1, 2, 0), (2, 2, 0), (8, 2, 0), (1, 4, 0), (4, 4, 0), (8, 4, 0),
+                                               (1, 2, 1), (2, 2, 1), (4, 2, 1), (8, 2, 1)])
+def test_every_tile_shape(ctx, steps, vec, staging):
     c = Context(0)
     c.set_option("steps", steps)
     c.set_option("vec", vec)
+    c.set_option("staging", staging)
+    if staging and steps == 2:
+        c.set_option("stages", 4)
     rng = np.random.default_rng(steps * 10 + vec)
     spec = random_table(rng, 30011, "DbiT")
     g = ExprGen(rng, spec.fields)
     compare_pipeline(c, spec, g.boolean(3), [g.double(4), g.boolean(2), col(2, I), col(3, T)])
     compare_pipeline(c, spec, None, [g.double(4), g.boolean(2), col(2, I)])
-    compare_aggregation(c, spec, g.boolean(2), [g.double(3), col(0)], [A.SUM, A.MAX])
+    finite = random_table(rng, 30011, "DbiT", special_rate=0.0)        # sums of Inf/NaN depend on the order
+    compare_aggregation(c, finite, g.boolean(2), [fn(Function.MUL, col(0), col(2, I)), col(0)], [A.SUM, A.MAX])
     c.close()
 
 
