@@ -209,6 +209,8 @@ QE_API void *qe_result_device_ptr(qe_result *result, int k, int which);
 QE_API int qe_result_kernel_ms(qe_result *result, float *ms);
 /* device time of the main kernel summed over every completed run into this result, and the run count */
 QE_API int qe_result_kernel_stats(qe_result *result, double *total_ms, int64_t *runs);
+/* development aid: per-CTA phase cycle counters recorded when option "debug_flags" has bit 16 ([cta][8] words) */
+QE_API int qe_result_debug_counters(qe_result *result, uint64_t *dst, size_t nwords);
 /* 1 if the last run used generated (JIT) code, 0 for the interpreter kernels */
 QE_API int qe_result_used_jit(const qe_result *result);
 QE_API int qe_result_destroy(qe_result *result);

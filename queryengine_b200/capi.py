@@ -90,6 +90,7 @@ SYMBOLS = {
     "qe_result_device_ptr": (_vp, [_vp, C.c_int, C.c_int]),
     "qe_result_kernel_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "qe_result_kernel_stats": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
+    "qe_result_debug_counters": (C.c_int, [_vp, _vp, C.c_size_t]),
     "qe_result_used_jit": (C.c_int, [_vp]),
     "qe_result_destroy": (C.c_int, [_vp]),
     "qe_agg_combine": (C.c_int, [C.c_int, C.POINTER(AggPartial), C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]),

@@ -486,7 +486,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         s += "    }\n";
     }
     s += "};\n\n";
-    const char *body = mode == KM_FILTER ? (shape.staged ? "qe_filter_staged_body" : "qe_filter_body")
+    const char *body = mode == KM_FILTER ? (shape.staged ? "qe_filter_staged_body" : shape.pipelined ? "qe_filter_pipelined_body" : "qe_filter_body")
                      : mode == KM_PROJECT ? "qe_project_body" : "qe_agg_body";
     snprintf(b, sizeof b,
              "extern \"C\" __global__ void __launch_bounds__(QE_BLOCK, %d) " QE_JIT_ENTRY

@@ -24,6 +24,7 @@ struct TileShape {
     int min_blocks = 1;     // __launch_bounds__ second argument
     bool staged = false;    // filter kernel: columns arrive through cp.async.bulk into shared-memory stages (vec must be 2)
     int nstages = 3;
+    bool pipelined = true;  // filter kernel (register-sourced): look-back and scatter deferred by one tile
 };
 
 // bytes of dynamic shared memory the staged filter kernel needs (0 when not staged)

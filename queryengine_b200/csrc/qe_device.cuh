@@ -73,6 +73,7 @@ struct QeParams {
     qe_u64       *out_count;                  // number of rows kept
     double       *agg_partials;               // [gridDim.x][QE_MAX_AGGS][4] = sum, count (bits), min, max
     const qe_u32 *iprog;                      // interpreter only: serialized pipeline (qe_interp.cuh)
+    qe_u64       *debug;                      // [4096][8] per-CTA phase cycle counters (QE_DEBUG_FLAGS & 16)
     qe_i64        nrows;                      // rows in this batch
     qe_i64        out_capacity;               // rows the compacted outputs can hold
     qe_u32        ntiles;
@@ -319,6 +320,78 @@ __device__ __forceinline__ qe_u64 qe_lookback(qe_u64 *state, qe_u32 tile, qe_u32
         look -= 32;
     }
     if (lane == 0) qe_st_relaxed(state + tile, (QE_TS_PREFIX << 62) | (exclusive + (qe_u64)tile_total));
+    return exclusive;
+}
+
+// Block-wide look-back.  A persistent grid keeps every resident CTA in the same
+// phase, so when a tile starts looking back none of the ~600 tiles in flight has
+// its prefix yet and a warp-wide window (32 descriptors per L2 round trip) walks
+// ~20 windows = 7 us per tile (measured).  Here all 256 threads look at
+// 256 * QE_LB_PER_THREAD predecessors per round trip; warp w covers the w-th
+// nearest run of 32 * QE_LB_PER_THREAD tiles.  Called by every thread of the CTA
+// (contains block barriers); returns the exclusive prefix to all of them.
+#define QE_LB_PER_THREAD 2
+
+// one thread: make the tile's kept-row count visible to its successors
+__device__ __forceinline__ void qe_publish_aggregate(qe_u64 *state, qe_u32 tile, qe_u32 tile_total)
+{
+    qe_st_relaxed(state + tile, ((tile == 0 ? QE_TS_PREFIX : QE_TS_AGGREGATE) << 62) | (qe_u64)tile_total);
+}
+
+template <bool PUBLISH_FIRST = true>
+__device__ __forceinline__ qe_u64 qe_block_lookback(qe_u64 *state, qe_u32 tile, qe_u32 tile_total,
+                                                    qe_u64 *s_sum, qe_u32 *s_found)
+{
+    const qe_u32 lane = qe_lane(), warp = qe_warp();
+    if (PUBLISH_FIRST && threadIdx.x == 0) qe_publish_aggregate(state, tile, tile_total);
+    if (tile == 0) {
+        __syncthreads();                                      // callers rely on one barrier in here
+        return 0;
+    }
+
+    qe_u64 exclusive = 0;
+    qe_i64 look = (qe_i64)tile - 1;
+    for (;;) {
+        qe_u64 d[QE_LB_PER_THREAD];
+        qe_i64 idx[QE_LB_PER_THREAD];
+#pragma unroll
+        for (int k = 0; k < QE_LB_PER_THREAD; k++) {          // all reads in flight together
+            idx[k] = look - (qe_i64)(warp * 32 * QE_LB_PER_THREAD + k * 32 + lane);
+            d[k] = idx[k] >= 0 ? qe_ld_relaxed(state + idx[k]) : (QE_TS_PREFIX << 62);
+        }
+        qe_u64 wsum = 0;
+        bool wfound = false;
+#pragma unroll
+        for (int k = 0; k < QE_LB_PER_THREAD; k++) {
+            if (!wfound) {                                    // warp-uniform
+                while ((d[k] >> 62) == QE_TS_INVALID) d[k] = qe_ld_relaxed(state + idx[k]);
+                const qe_u32 has_prefix = __ballot_sync(QE_FULL_MASK, (d[k] >> 62) == QE_TS_PREFIX);
+                const qe_u32 first = has_prefix ? (qe_u32)__ffs((int)has_prefix) - 1u : 32u;
+                qe_u64 v = lane <= first ? (d[k] & QE_TS_VALUE_MASK) : 0ull;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(QE_FULL_MASK, v, o);
+                wsum += v;
+                wfound = has_prefix != 0;
+            }
+        }
+        if (lane == 0) {
+            s_sum[warp] = wsum;
+            s_found[warp] = wfound ? 1u : 0u;
+        }
+        __syncthreads();
+        bool found = false;
+#pragma unroll
+        for (int w = 0; w < QE_WARPS; w++) {
+            if (!found) {
+                exclusive += s_sum[w];
+                found = s_found[w] != 0;
+            }
+        }
+        if (found) break;
+        look -= QE_WARPS * 32 * QE_LB_PER_THREAD;
+        __syncthreads();                                      // s_sum / s_found are rewritten next round
+    }
+    if (threadIdx.x == 0) qe_st_relaxed(state + tile, (QE_TS_PREFIX << 62) | (exclusive + (qe_u64)tile_total));
     return exclusive;
 }
 
@@ -587,13 +660,27 @@ __device__ __forceinline__ void qe_filter_body(const QeParams &p)
 
     __shared__ qe_u32 s_tile;
     __shared__ qe_u32 s_warp_cnt[QE_WARPS];
-    __shared__ qe_u64 s_prefix;
+    __shared__ qe_u64 s_lb_sum[QE_WARPS];
+    __shared__ qe_u32 s_lb_found[QE_WARPS];
 
     const qe_u32 lane = qe_lane(), warp = qe_warp();
 
-    for (;;) {
-        if (threadIdx.x == 0) s_tile = atomicAdd(p.ticket, 1u);
+#ifndef QE_DEBUG_FLAGS
+#define QE_DEBUG_FLAGS 0      // timing experiments only: 1 no look-back, 2 static tiles, 4 no scatter, 8 warp look-back
+#endif
+    // phase timing (experiments): 0 ticket wait, 1 loads+eval, 2 barrier, 3 look-back, 4 scatter, 5 tiles
+    qe_u64 dbg_acc[6] = {0, 0, 0, 0, 0, 0};
+    qe_u64 dbg_last = (QE_DEBUG_FLAGS & 16) ? clock64() : 0;
+#define QE_TICK(i) do { if (QE_DEBUG_FLAGS & 16) { const qe_u64 now_ = clock64(); dbg_acc[i] += now_ - dbg_last; \
+                         dbg_last = now_; if ((i) == 4) dbg_acc[5] += 1; } } while (0)
+    for (qe_u32 it = 0;; it++) {
+        if (QE_DEBUG_FLAGS & 2) {
+            if (threadIdx.x == 0) s_tile = it * gridDim.x + blockIdx.x;
+        } else {
+            if (threadIdx.x == 0) s_tile = atomicAdd(p.ticket, 1u);
+        }
         __syncthreads();
+        QE_TICK(0);
         const qe_u32 tile = s_tile;
         if (tile >= p.ntiles) break;
         const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
@@ -610,7 +697,9 @@ __device__ __forceinline__ void qe_filter_body(const QeParams &p)
         qe_u32 rank0[STEPS], step_off[STEPS];
         const qe_u32 wcnt = qe_warp_ranks<STEPS, VEC>(keep, rank0, step_off);
         if (lane == 0) s_warp_cnt[warp] = wcnt;
+        QE_TICK(1);
         __syncthreads();
+        QE_TICK(2);
 
         qe_u32 woff = 0, tile_total = 0;
 #pragma unroll
@@ -619,15 +708,105 @@ __device__ __forceinline__ void qe_filter_body(const QeParams &p)
             woff += (qe_u32)w < warp ? c : 0u;
             tile_total += c;
         }
-        if (warp == 0) {
-            const qe_u64 excl = qe_lookback(p.tile_state, tile, tile_total);
-            if (lane == 0) {
-                s_prefix = excl;
-                if (tile == p.ntiles - 1) *p.out_count = excl + tile_total;
+        qe_u64 excl;
+        if (QE_DEBUG_FLAGS & 1) {
+            excl = (qe_u64)tile * (TILE / 2);
+            __syncthreads();
+        } else if (QE_DEBUG_FLAGS & 8) {
+            if (warp == 0) {
+                const qe_u64 e = qe_lookback(p.tile_state, tile, tile_total);
+                if (lane == 0) s_lb_sum[0] = e;
             }
+            __syncthreads();
+            excl = s_lb_sum[0];
+        } else {
+            excl = qe_block_lookback(p.tile_state, tile, tile_total, s_lb_sum, s_lb_found);
         }
+        QE_TICK(3);
+        if (threadIdx.x == 0 && tile == p.ntiles - 1) *p.out_count = excl + tile_total;
+        if (!(QE_DEBUG_FLAGS & 4)) qe_warp_scatter<P>(p, warp_row0, excl + woff, outs, keep, rank0, step_off);
+        QE_TICK(4);
+    }
+    if ((QE_DEBUG_FLAGS & 16) && threadIdx.x == 0 && blockIdx.x < 4096) {
+#pragma unroll
+        for (int i = 0; i < 6; i++) p.debug[blockIdx.x * 8 + i] = dbg_acc[i];
+    }
+}
+
+// K1, software-pipelined variant (the default).
+//
+// Stable compaction has a true dependency: tile t cannot be written before every
+// earlier tile has been evaluated.  Measured on B200 (tools/phase_timing.py): with
+// look-back right after evaluation a CTA spends 7 000 - 15 000 cycles per tile
+// polling descriptors (one L2 round trip under streaming load is ~900 cycles, and
+// a persistent grid keeps all resident tiles in the same phase), while loading and
+// evaluating the tile takes ~2 000.  So the look-back and scatter of tile i are
+// deferred by one iteration: the CTA publishes the tile's count, claims and loads
+// its next tile, and only then -- with those loads in flight -- reads the
+// predecessors' descriptors (published a whole tile time ago, so there is nothing to
+// spin on) and scatters tile i from registers.
+template <class P>
+__device__ __forceinline__ void qe_filter_pipelined_body(const QeParams &p)
+{
+    constexpr int STEPS = P::STEPS, VEC = P::VEC;
+    constexpr int WARP_ROWS = STEPS * 32 * VEC;
+    constexpr int TILE = QE_WARPS * WARP_ROWS;
+
+    __shared__ qe_u32 s_tile[2];
+    __shared__ qe_u32 s_warp_cnt[QE_WARPS];
+    __shared__ qe_u64 s_lb_sum[QE_WARPS];
+    __shared__ qe_u32 s_lb_found[QE_WARPS];
+
+    const qe_u32 lane = qe_lane(), warp = qe_warp();
+
+    if (threadIdx.x == 0) s_tile[0] = atomicAdd(p.ticket, 1u);
+    __syncthreads();
+    qe_u32 cur = s_tile[0];
+
+    // state of the previous tile, kept in registers until its prefix is known
+    typename P::Out prev_outs[STEPS][VEC];
+    qe_u32 prev_keep[STEPS], prev_rank0[STEPS], prev_step_off[STEPS];
+    qe_u32 prev_tile = 0, prev_woff = 0, prev_total = 0;
+    bool have_prev = false;
+
+    for (qe_u32 it = 0;; it++) {
+        const bool have_cur = cur < p.ntiles;
+        const qe_i64 warp_row0 = (qe_i64)cur * TILE + (qe_i64)warp * WARP_ROWS;
+        typename P::Row rows[STEPS][VEC];
+        if (have_cur) {
+            // claim the tile after this one (its id is read after the next barrier) and start loading this one
+            if (threadIdx.x == 0) s_tile[(it + 1) & 1] = atomicAdd(p.ticket, 1u);
+#pragma unroll
+            for (int s = 0; s < STEPS; s++)
+                P::load(p, warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC, rows[s]);
+        }
+        if (have_prev) {
+            // the previous tile: prefix (its predecessors published long ago) and ordered scatter
+            const qe_u64 excl = qe_block_lookback<false>(p.tile_state, prev_tile, prev_total, s_lb_sum, s_lb_found);
+            if (threadIdx.x == 0 && prev_tile == p.ntiles - 1) *p.out_count = excl + prev_total;
+            const qe_i64 prev_row0 = (qe_i64)prev_tile * TILE + (qe_i64)warp * WARP_ROWS;
+            qe_warp_scatter<P>(p, prev_row0, excl + prev_woff, prev_outs, prev_keep, prev_rank0, prev_step_off);
+        }
+        if (!have_cur) break;
+
+        qe_rows_eval<P>(p, warp_row0, rows, prev_outs, prev_keep);
+        const qe_u32 wcnt = qe_warp_ranks<STEPS, VEC>(prev_keep, prev_rank0, prev_step_off);
+        if (lane == 0) s_warp_cnt[warp] = wcnt;
         __syncthreads();
-        qe_warp_scatter<P>(p, warp_row0, s_prefix + woff, outs, keep, rank0, step_off);
+        qe_u32 woff = 0, tile_total = 0;
+#pragma unroll
+        for (int w = 0; w < QE_WARPS; w++) {
+            const qe_u32 c = s_warp_cnt[w];
+            woff += (qe_u32)w < warp ? c : 0u;
+            tile_total += c;
+        }
+        if (threadIdx.x == 0) qe_publish_aggregate(p.tile_state, cur, tile_total);
+        prev_tile = cur;
+        prev_woff = woff;
+        prev_total = tile_total;
+        have_prev = true;
+        cur = s_tile[(it + 1) & 1];
+        // s_warp_cnt is rewritten only after the barrier inside the next look-back
     }
 }
 
@@ -726,7 +905,8 @@ __device__ __forceinline__ void qe_filter_staged_body(const QeParams &p)
     __shared__ __align__(8) qe_u64 s_full[NST];
     __shared__ qe_u32 s_tile[NST];
     __shared__ qe_u32 s_warp_cnt[QE_WARPS];
-    __shared__ qe_u64 s_prefix;
+    __shared__ qe_u64 s_lb_sum[QE_WARPS];
+    __shared__ qe_u32 s_lb_found[QE_WARPS];
 
     const qe_u32 lane = qe_lane(), warp = qe_warp();
 
@@ -786,15 +966,9 @@ __device__ __forceinline__ void qe_filter_staged_body(const QeParams &p)
             woff += (qe_u32)w < warp ? c : 0u;
             tile_total += c;
         }
-        if (warp == 0) {
-            const qe_u64 excl = qe_lookback(p.tile_state, tile, tile_total);
-            if (lane == 0) {
-                s_prefix = excl;
-                if (tile == p.ntiles - 1) *p.out_count = excl + tile_total;
-            }
-        }
-        __syncthreads();
-        qe_warp_scatter<P>(p, warp_row0, s_prefix + woff, outs, keep, rank0, step_off);
+        const qe_u64 excl = qe_block_lookback(p.tile_state, tile, tile_total, s_lb_sum, s_lb_found);
+        if (threadIdx.x == 0 && tile == p.ntiles - 1) *p.out_count = excl + tile_total;
+        qe_warp_scatter<P>(p, warp_row0, excl + woff, outs, keep, rank0, step_off);
     }
 }
 

@@ -84,7 +84,8 @@ std::string jit_version()
     return n.handle ? std::to_string(n.major) + "." + std::to_string(n.minor) : std::string("unavailable");
 }
 
-bool jit_compile(const std::string &source, std::vector<char> &cubin, std::string &log)
+bool jit_compile(const std::string &source, std::vector<char> &cubin, std::string &log,
+                 const std::vector<std::string> &extra_options)
 {
     Nvrtc &n = nvrtc();
     if (!n.handle) { log = n.why; return false; }
@@ -94,8 +95,9 @@ bool jit_compile(const std::string &source, std::vector<char> &cubin, std::strin
     nvrtcResult rc = n.CreateProgram(&prog, source.c_str(), "qe_pipeline.cu", 2, headers, names);
     if (rc != 0) { log = std::string("nvrtcCreateProgram: ") + n.GetErrorString(rc); return false; }
     // -fmad=false: a*b+c must stay a separate multiply and add, as on the JVM
-    const char *opts[] = {"--gpu-architecture=sm_100a", "--std=c++17", "--fmad=false", "-lineinfo"};
-    rc = n.CompileProgram(prog, 4, opts);
+    std::vector<const char *> opts = {"--gpu-architecture=sm_100a", "--std=c++17", "--fmad=false", "-lineinfo"};
+    for (const std::string &o : extra_options) opts.push_back(o.c_str());
+    rc = n.CompileProgram(prog, (int)opts.size(), opts.data());
     size_t logsz = 0;
     n.GetProgramLogSize(prog, &logsz);
     if (logsz > 1) {

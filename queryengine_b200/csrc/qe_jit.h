@@ -34,7 +34,8 @@ std::string jit_version();
 
 // Compile `source` (which includes "qe_device.cuh") to a cubin for sm_100a.
 // Does not need a GPU.  Returns false and fills `log` on failure.
-bool jit_compile(const std::string &source, std::vector<char> &cubin, std::string &log);
+bool jit_compile(const std::string &source, std::vector<char> &cubin, std::string &log,
+                 const std::vector<std::string> &extra_options = std::vector<std::string>());
 
 // Load a cubin on the current device and look up the entry point.
 bool jit_load(const std::vector<char> &cubin, const char *entry, size_t dyn_smem, JitKernel &out, std::string &err);

@@ -133,7 +133,7 @@ struct qe_ctx {
     Pool pool;
     std::unordered_map<std::string, JitEntry> jit_cache;
     // options
-    int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = -1, opt_stages = 0;
+    int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = 0, opt_stages = 0, opt_debug_flags = 0, opt_pipeline = 1;
     int64_t launches = 0;
     bool warned_no_nvrtc = false;
     // pinned staging ring for uploads from pageable memory
@@ -254,6 +254,10 @@ extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
     } else if (k == "staging") {
         if (value < -1 || value > 1) return fail(QE_ERR_INVALID_ARGUMENT, "staging must be -1 (auto), 0 or 1");
         ctx->opt_staging = value;
+    } else if (k == "pipeline") {
+        ctx->opt_pipeline = value != 0;
+    } else if (k == "debug_flags") {
+        ctx->opt_debug_flags = value;                       // timing experiments only (results are wrong)
     } else if (k == "stages") {
         if (value != 0 && (value < 2 || value > 8)) return fail(QE_ERR_INVALID_ARGUMENT, "stages must be 0 (auto) or 2..8");
         ctx->opt_stages = value;
@@ -482,7 +486,7 @@ struct qe_result {
     int64_t capacity = 0;
     std::vector<ResultColumn> cols;
     std::vector<int> agg_fns;
-    DevBuf sel, ctl, partials, final_aggs;
+    DevBuf sel, ctl, partials, final_aggs, debug;
     ResultHost *host = nullptr;         // pinned
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_done = nullptr;
     bool pending = false;
@@ -534,6 +538,7 @@ extern "C" int qe_result_destroy(qe_result *r)
     release(r->ctx, r->ctl);
     release(r->ctx, r->partials);
     release(r->ctx, r->final_aggs);
+    release(r->ctx, r->debug);
     if (r->host) cudaFreeHost(r->host);
     if (r->ev_begin) cudaEventDestroy(r->ev_begin);
     if (r->ev_end) cudaEventDestroy(r->ev_end);
@@ -567,7 +572,8 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
     }
     // Filter kernel: land the columns in shared-memory stages with bulk copies, so the bytes in
     // flight are not bounded by registers and the next tiles load during scan / look-back / scatter.
-    s.staged = mode == qe::KM_FILTER && ctx->opt_staging != 0;
+    s.staged = mode == qe::KM_FILTER && ctx->opt_staging > 0;
+    s.pipelined = ctx->opt_pipeline != 0;
     if (s.staged) {
         s.vec = 2;                                             // staged rows are read back with 128-bit LDS
         if (!ctx->opt_steps) {                                 // ~16 KB per stage, 8 rows per thread at most
@@ -620,14 +626,17 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
                           JitEntry **out)
 {
     char suffix[64];
-    snprintf(suffix, sizeof suffix, "|M%d|S%d|V%d|T%d.%d", (int)mode, shape.steps, shape.vec, shape.staged ? 1 : 0, shape.nstages);
+    snprintf(suffix, sizeof suffix, "|M%d|S%d|V%d|T%d.%d|D%d|P%d", (int)mode, shape.steps, shape.vec, shape.staged ? 1 : 0,
+             shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0);
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) { *out = &it->second; return QE_OK; }
     const std::string src = qe::generate_source(bp, mode, shape);
     std::vector<char> cubin;
     std::string log;
-    if (!qe::jit_compile(src, cubin, log)) {
+    std::vector<std::string> extra;
+    if (ctx->opt_debug_flags) extra.push_back("-DQE_DEBUG_FLAGS=" + std::to_string(ctx->opt_debug_flags));
+    if (!qe::jit_compile(src, cubin, log, extra)) {
         if (getenv("QE_DUMP_JIT")) fprintf(stderr, "%s\n", src.c_str());
         return fail(QE_ERR_JIT, "compiling the generated pipeline failed: " + log);
     }
@@ -794,6 +803,11 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
         if ((rc = ensure(ctx, r->partials, (size_t)grid * QE_MAX_AGGS * 4 * sizeof(double)))) return rc;
         if ((rc = ensure(ctx, r->final_aggs, QE_MAX_AGGS * 4 * sizeof(double)))) return rc;
         p.agg_partials = (double *)r->partials.ptr;
+    }
+    if (ctx->opt_debug_flags & 16) {
+        if ((rc = ensure(ctx, r->debug, 4096 * 8 * sizeof(uint64_t)))) return rc;
+        QE_CUDA(cudaMemsetAsync(r->debug.ptr, 0, 4096 * 8 * sizeof(uint64_t), ctx->stream));
+        p.debug = (qe_u64 *)r->debug.ptr;
     }
     DevBuf iprog;
     if (!use_jit) {
@@ -1058,6 +1072,16 @@ extern "C" int qe_result_kernel_stats(qe_result *r, double *total_ms, int64_t *r
     fold_timing(r);
     if (total_ms) *total_ms = r->total_kernel_ms;
     if (runs) *runs = r->kernel_runs;
+    return QE_OK;
+}
+
+extern "C" int qe_result_debug_counters(qe_result *r, uint64_t *dst, size_t n)
+{
+    int rc = wait_result(r);
+    if (rc) return rc;
+    if (!r->debug.ptr) return fail(QE_ERR_STATE, "no debug counters were recorded");
+    DeviceGuard g(r->ctx->device);
+    QE_CUDA(cudaMemcpy(dst, r->debug.ptr, std::min(n, (size_t)4096 * 8) * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     return QE_OK;
 }
 

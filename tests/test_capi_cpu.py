@@ -75,8 +75,10 @@ Q6_PROJ = fn(Function.MUL, col(1), col(2))
 def test_generated_code_compiles_for_sm100a():
     rc, src, nbytes, err = _generate([(I, False)], fn(Function.CMP_LT, col(0, I), 1e6), [col(0, I)])
     assert rc == 0, err
-    assert "qe_filter_staged_body<P>" in src and "((qe_i64)in.c0 < 1000000LL)" in src and nbytes > 1000
-    assert "qe_bulk_g2s(stage + 0, (const char *)p.col_values[0] + row0 * 8" in src
+    assert "qe_filter_pipelined_body<P>" in src and "((qe_i64)in.c0 < 1000000LL)" in src and nbytes > 1000
+    rc, src, nbytes, err = _generate([(I, False)], fn(Function.CMP_LT, col(0, I), 1e6), [col(0, I)], staging=1)
+    assert rc == 0, err
+    assert "qe_bulk_g2s(stage + 0, (const char *)p.col_values[0] + row0 * 8" in src and "qe_filter_staged_body<P>" in src
     rc, src, nbytes, err = _generate(Q6_SCHEMA, Q6_FILTER, [Q6_PROJ], [AggregationFunction.SUM])
     assert rc == 0, err
     assert "qe_agg_body<P>" in src and "qe_acc_add<2>" in src
@@ -96,7 +98,7 @@ def test_generated_code_compiles_for_sm100a():
                                                  [fn(Function.IF, col(1, B), col(0), 1.0), col(1, B), col(2, T)],
                                                  steps=steps, vec=vec, staging=staging)
                 assert rc == 0, (steps, vec, staging, err)
-                assert ("qe_filter_staged_body<P>" in src) == bool(staging)
+                assert ("qe_filter_staged_body<P>" in src) == (staging == 1)
 
 
 def test_type_errors_follow_the_reference_typecheck():

@@ -41,14 +41,18 @@ def main():
     ap.add_argument("--grids", default="0")
     ap.add_argument("--staging", default="1", help="comma list of 0/1")
     ap.add_argument("--stages", default="0", help="comma list")
+    ap.add_argument("--debug-flags", default="0", help="comma list of QE_DEBUG_FLAGS values (timing experiments)")
+    ap.add_argument("--sels", default="0.01,0.5,0.99")
+    ap.add_argument("--pipeline", default="1", help="comma list of 0/1")
     args = ap.parse_args()
     peak, _ = measured_peak_gbs()
     dt = DataType.INT64 if args.type == "i64" else DataType.DOUBLE
     out = []
     for shape in args.shapes.split(","):
         steps, vec = (int(x) for x in shape.split("x"))
-        for g, stg, nst in [(int(g), int(a), int(b)) for g in args.grids.split(",") for a in args.staging.split(",")
-                            for b in (args.stages.split(",") if a == "1" else ["0"])]:
+        for g, stg, nst, dbg, pl in [(int(g), int(a), int(b), int(d), int(e)) for g in args.grids.split(",")
+                                     for a in args.staging.split(",") for b in (args.stages.split(",") if a == "1" else ["0"])
+                                     for d in args.debug_flags.split(",") for e in args.pipeline.split(",")]:
             if stg and vec != 2:
                 continue
             ctx = Context(0)
@@ -57,10 +61,12 @@ def main():
             ctx.set_option("grid_per_sm", g)
             ctx.set_option("staging", stg)
             ctx.set_option("stages", nst)
+            ctx.set_option("debug_flags", dbg)
+            ctx.set_option("pipeline", pl)
             t = ColumnarTable(ctx, [Field("col", dt, False)], args.rows)
             t.generate(0, capi.QE_GEN_UNIFORM_U40, SEED)
-            row = {"steps": steps, "vec": vec, "grid_per_sm": g, "staging": stg, "stages": nst}
-            for s in SELECTIVITIES:
+            row = {"steps": steps, "vec": vec, "grid_per_sm": g, "staging": stg, "stages": nst, "dbg": dbg, "pipeline": pl}
+            for s in [float(x) for x in args.sels.split(",")]:
                 from queryengine_b200.ast import Function, fn
                 k = float(int(s * 2 ** 40))
                 pipe = Pipeline(t, fn(Function.CMP_LT, col(0, dt, "col"), k), [col(0, dt, "col")])
