@@ -233,7 +233,7 @@ def timed_steps(torch, ctx, stream, fn_step, steps, dist, device):
     return ms
 
 
-def extra_q6(ctx, torch, stream, rows, steps, warmup, peak):
+def q6_pipeline(ctx, rows):
     """BASELINE.json configs[2]: Q6-shaped filter + SUM(extendedprice * discount), four f64 columns."""
     from queryengine_b200 import capi
     from queryengine_b200.ast import AggregationFunction, DataType, Function, col, fn
@@ -248,7 +248,11 @@ def extra_q6(ctx, torch, stream, rows, steps, warmup, peak):
     filt = fn(Function.AND, fn(Function.AND, fn(Function.AND, fn(Function.AND,
               fn(Function.CMP_GE, col(3), 8766.0), fn(Function.CMP_LT, col(3), 9131.0)),
               fn(Function.CMP_GE, col(2), 0.05)), fn(Function.CMP_LE, col(2), 0.07)), fn(Function.CMP_LT, col(0), 24.0))
-    pipe = Pipeline(t, filt, [fn(Function.MUL, col(1), col(2))], [AggregationFunction.SUM])
+    return t, Pipeline(t, filt, [fn(Function.MUL, col(1), col(2))], [AggregationFunction.SUM])
+
+
+def extra_q6(ctx, torch, stream, rows, steps, warmup, peak):
+    t, pipe = q6_pipeline(ctx, rows)
     res = pipe.run()
     for _ in range(warmup):
         pipe.run(res)
@@ -266,21 +270,27 @@ def extra_q6(ctx, torch, stream, rows, steps, warmup, peak):
     return out
 
 
+def tree_expr():
+    """The depth-8 nullable arithmetic tree of BASELINE.json configs[3] (fixed here, evaluated by the oracle in tests)."""
+    from queryengine_b200.ast import Function, col, fn
+    a, b, c_, d = col(0), col(1), col(2), col(3)
+    inner = fn(Function.DIV, fn(Function.MUL, fn(Function.ADD, a, b), fn(Function.SUB, c_, d)),
+               fn(Function.ADD, fn(Function.MUL, a, 0.5), fn(Function.SUB, fn(Function.MOD, c_, 7.0), fn(Function.UNARY_MINUS, b))))
+    return fn(Function.IF, fn(Function.CMP_GT, inner, 0.0),
+              fn(Function.ADD, fn(Function.MUL, inner, fn(Function.SUB, a, d)), fn(Function.DIV, c_, fn(Function.ADD, b, 1.5))),
+              fn(Function.SUB, fn(Function.UNARY_MINUS, inner), fn(Function.MUL, d, 0.25)))
+
+
 def extra_tree(ctx, torch, stream, rows, steps, warmup, peak):
     """BASELINE.json configs[3]: nullable f64 arithmetic tree (depth 8) with validity bitmaps, dense projection."""
     from queryengine_b200 import capi
-    from queryengine_b200.ast import DataType, Function, col, fn
+    from queryengine_b200.ast import DataType
     from queryengine_b200.engine import ColumnarTable, Field, Pipeline
     D = DataType.DOUBLE
     t = ColumnarTable(ctx, [Field("a", D, True), Field("b", D, True), Field("c", D, True), Field("d", D, True)], rows)
     for c, rate in enumerate((0.0, 0.01, 0.10, 0.50)):
         t.generate(c, capi.QE_GEN_UNIFORM_REAL, SEED + 10 + c, -1000.0, 1000.0, null_rate=rate)
-    a, b, c_, d = col(0), col(1), col(2), col(3)
-    inner = fn(Function.DIV, fn(Function.MUL, fn(Function.ADD, a, b), fn(Function.SUB, c_, d)),
-               fn(Function.ADD, fn(Function.MUL, a, 0.5), fn(Function.SUB, fn(Function.MOD, c_, 7.0), fn(Function.UNARY_MINUS, b))))
-    tree = fn(Function.IF, fn(Function.CMP_GT, inner, 0.0),
-              fn(Function.ADD, fn(Function.MUL, inner, fn(Function.SUB, a, d)), fn(Function.DIV, c_, fn(Function.ADD, b, 1.5))),
-              fn(Function.SUB, fn(Function.UNARY_MINUS, inner), fn(Function.MUL, d, 0.25)))
+    tree = tree_expr()
     pipe = Pipeline(t, None, [tree])
     res = pipe.run()
     for _ in range(warmup):

@@ -134,8 +134,10 @@ QE_API int qe_ctx_synchronize(qe_ctx *ctx);
 /* cudaStream_t all work of this context is enqueued on (for event timing by the caller) */
 QE_API void *qe_ctx_stream(qe_ctx *ctx);
 /* options: "jit" (1 default / 0 = always interpret), "steps", "vec" (tile shape overrides, 0 = auto),
- * "grid_per_sm" (0 = auto), "staging" (filter kernel loads through cp.async.bulk shared-memory stages:
- * -1 auto, 0 off, 1 on), "stages" (0 = auto, 2..8) */
+ * "grid_per_sm" (0 = auto), "staging" (filter kernel variant: -1 auto = 2; 0 register-sourced; 1 bulk-copy stages,
+ * look-back in line; 2 warp-specialised ring of bulk-copy stages with deferred scatter), "stages" (0 = auto, 2..32),
+ * ring variant: "stage_kb" (bytes of column data per stage, 0 = auto), "tile_rows" (0 = auto), "ncw" (consumer
+ * warps, 0 = auto), "defer" (tiles between evaluation and scatter, 0 = auto) */
 QE_API int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value);
 /* kernels launched by this context so far */
 QE_API int64_t qe_ctx_launch_count(const qe_ctx *ctx);
@@ -222,7 +224,7 @@ QE_API int qe_agg_combine(int agg_fn, const qe_agg_partial *partials, int n, dou
  * then nproj projections) against a schema, write the generated CUDA source
  * into src_buf and, when compile != 0, compile it with NVRTC for sm_100a
  * (cubin copied into cubin_buf when it fits; its size into *cubin_bytes).
- * steps / vec: tile shape overrides, 0 = the library's choice; staging: -1 auto, 0 off, 1 on. */
+ * steps / vec: tile shape overrides, 0 = the library's choice; staging: as the "staging" option. */
 QE_API int qe_debug_generate(const qe_col_desc *cols, int ncols,
                              const uint32_t *const *programs, const size_t *nwords,
                              int has_filter, int nproj, const int32_t *agg_fns, int nagg,

@@ -247,7 +247,7 @@ struct StageLayout {
 StageLayout stage_layout(const BoundPipeline &bp, const TileShape &shape)
 {
     StageLayout L;
-    const int tile = 8 * shape.steps * 32 * shape.vec;
+    const int tile = shape.rows_per_tile();
     int off = 0;
     L.valid_bytes = tile / 8;
     for (const ColumnInfo &c : bp.slot_info) {
@@ -273,7 +273,7 @@ StageLayout stage_layout(const BoundPipeline &bp, const TileShape &shape)
 
 size_t staged_smem_bytes(const BoundPipeline &bp, const TileShape &shape)
 {
-    if (!shape.staged) return 0;
+    if (!shape.staged && !shape.ring) return 0;
     return (size_t)stage_layout(bp, shape).stride * (size_t)shape.nstages;
 }
 
@@ -352,28 +352,52 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     }
     s += "    }\n";
 
-    if (mode == KM_FILTER && shape.staged) {
+    if (mode == KM_FILTER && (shape.staged || shape.ring)) {
         const StageLayout L = stage_layout(bp, shape);
         snprintf(b, sizeof b, "    static constexpr int NSTAGES = %d, STAGE_BYTES = %d, STAGE_TX = %d;\n", shape.nstages, L.stride, L.tx);
         s += b;
+        if (shape.ring) {
+            snprintf(b, sizeof b, "    static constexpr int TILE_ROWS = %d, NCW = %d, DEFER = %d, LOADS = %d;\n", shape.tile_rows, shape.ncw, shape.defer,
+                     shape.loads);
+            s += b;
+            // one row (lane-strided: a warp step reads 32 consecutive rows, conflict-free) from a stage
+            s += "    static __device__ __forceinline__ void load_row(const unsigned char *stage, int wrow0, int c, Row &row) {\n";
+            for (int i = 0; i < nslots; i++) {
+                const int t = bp.slot_info[i].type;
+                if (t == 2) snprintf(b, sizeof b, "        row.c%d = qe_stage1_bit(stage + %d, wrow0, c);\n", i, L.val_off[i]);
+                else snprintf(b, sizeof b, "        row.c%d = qe_stage1_%s(stage + %d, wrow0, c);\n", i, suffix_of(t), L.val_off[i]);
+                s += b;
+                if (bp.slot_info[i].nullable) {
+                    snprintf(b, sizeof b, "        row.v%d = qe_stage1_bit(stage + %d, wrow0, c);\n", i, L.valid_off[i]);
+                    s += b;
+                }
+            }
+            s += "    }\n";
+        }
         // one thread: a bulk copy per column run of the tile, all signalling the stage's mbarrier
+        const char *bulk = shape.ring ? "qe_bulk_g2s_stream" : "qe_bulk_g2s";
+        const char *pol = shape.ring ? ", policy" : "";
+        if (shape.ring)
+            s += "    static __device__ __forceinline__ void issue(const QeParams &p, qe_i64 row0, qe_u32 stage, qe_u32 mbar, qe_u64 policy) {\n";
+        else
         s += "    static __device__ __forceinline__ void issue(const QeParams &p, qe_i64 row0, qe_u32 stage, qe_u32 mbar) {\n";
         for (int i = 0; i < nslots; i++) {
             const int t = bp.slot_info[i].type;
             if (t == 2)
-                snprintf(b, sizeof b, "        qe_bulk_g2s(stage + %d, (const char *)p.col_values[%d] + (row0 >> 3), %d, mbar);\n",
-                         L.val_off[i], i, L.val_bytes[i]);
+                snprintf(b, sizeof b, "        %s(stage + %d, (const char *)p.col_values[%d] + (row0 >> 3), %d, mbar%s);\n",
+                         bulk, L.val_off[i], i, L.val_bytes[i], pol);
             else
-                snprintf(b, sizeof b, "        qe_bulk_g2s(stage + %d, (const char *)p.col_values[%d] + row0 * %d, %d, mbar);\n",
-                         L.val_off[i], i, t == 4 ? 4 : 8, L.val_bytes[i]);
+                snprintf(b, sizeof b, "        %s(stage + %d, (const char *)p.col_values[%d] + row0 * %d, %d, mbar%s);\n",
+                         bulk, L.val_off[i], i, t == 4 ? 4 : 8, L.val_bytes[i], pol);
             s += b;
             if (bp.slot_info[i].nullable) {
-                snprintf(b, sizeof b, "        qe_bulk_g2s(stage + %d, (const char *)p.col_valid[%d] + (row0 >> 3), %d, mbar);\n",
-                         L.valid_off[i], i, L.valid_bytes);
+                snprintf(b, sizeof b, "        %s(stage + %d, (const char *)p.col_valid[%d] + (row0 >> 3), %d, mbar%s);\n",
+                         bulk, L.valid_off[i], i, L.valid_bytes, pol);
                 s += b;
             }
         }
         s += "    }\n";
+        if (shape.staged) {
         s += "    static __device__ __forceinline__ void load_stage(const unsigned char *stage, int r, Row (&rows)[VEC]) {\n";
         for (int i = 0; i < nslots; i++) {
             const int t = bp.slot_info[i].type;
@@ -396,6 +420,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
             }
         }
         s += "    }\n";
+        }
     }
 
     // ---- eval: RowCallable.invoke for the filter and every projection
@@ -428,6 +453,15 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         for (int k = 0; k < nproj; k++) {
             if (bp.outs[k].type == 2) continue;
             snprintf(b, sizeof b, "        ((%s *)p.out_values[%d])[pos] = o.o%d;\n", ctype_of(bp.outs[k].type), k, k);
+            s += b;
+        }
+        s += "    }\n";
+    }
+    if (mode == KM_FILTER && shape.ring) {
+        s += "    static __device__ __forceinline__ void emit_at(const QeParams &p, qe_u64 base, qe_u32 idx, const Out &o) {\n";
+        for (int k = 0; k < nproj; k++) {
+            if (bp.outs[k].type == 2) continue;
+            snprintf(b, sizeof b, "        ((%s *)p.out_values[%d] + base)[idx] = o.o%d;\n", ctype_of(bp.outs[k].type), k, k);
             s += b;
         }
         s += "    }\n";
@@ -486,12 +520,12 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         s += "    }\n";
     }
     s += "};\n\n";
-    const char *body = mode == KM_FILTER ? (shape.staged ? "qe_filter_staged_body" : shape.pipelined ? "qe_filter_pipelined_body" : "qe_filter_body")
+    const char *body = mode == KM_FILTER ? (shape.ring ? "qe_filter_ring_body" : shape.staged ? "qe_filter_staged_body" : shape.pipelined ? "qe_filter_pipelined_body" : "qe_filter_body")
                      : mode == KM_PROJECT ? "qe_project_body" : "qe_agg_body";
     snprintf(b, sizeof b,
-             "extern \"C\" __global__ void __launch_bounds__(QE_BLOCK, %d) " QE_JIT_ENTRY
+             "extern \"C\" __global__ void __launch_bounds__(%d, %d) " QE_JIT_ENTRY
              "(const __grid_constant__ QeParams p)\n{\n    %s<P>(p);\n}\n",
-             shape.min_blocks, body);
+             mode == KM_FILTER ? shape.block_threads() : 256, shape.min_blocks, body);
     s += b;
     return s;
 }

@@ -25,6 +25,16 @@ struct TileShape {
     bool staged = false;    // filter kernel: columns arrive through cp.async.bulk into shared-memory stages (vec must be 2)
     int nstages = 3;
     bool pipelined = true;  // filter kernel (register-sourced): look-back and scatter deferred by one tile
+    // filter kernel, ring variant (qe_filter_ring_body): persistent warp-specialised CTA around a ring of
+    // shared-memory stages filled by cp.async.bulk; steps / vec are ignored
+    bool ring = false;
+    int tile_rows = 4096;   // rows per tile = rows per stage; a multiple of 32 * ncw and of 128
+    int ncw = 8;            // consumer warps
+    int defer = 2;          // tiles between a tile's evaluation (phase A) and its scatter (phase C)
+    int loads = 0;          // bulk-copy tiles in flight at most (0 = as many as there are free stages)
+
+    int rows_per_tile() const { return ring ? tile_rows : 8 * steps * 32 * vec; }
+    int block_threads() const { return ring ? 32 * (3 + ncw) : 256; }
 };
 
 // bytes of dynamic shared memory the staged filter kernel needs (0 when not staged)

@@ -36,6 +36,10 @@
 
 #include "qe_ops.h"
 
+#ifndef QE_DEBUG_FLAGS
+#define QE_DEBUG_FLAGS 0      // timing experiments only (see qe_filter_body and the ring body)
+#endif
+
 #define QE_BLOCK 256
 #define QE_WARPS 8
 #define QE_FULL_MASK 0xffffffffu
@@ -890,6 +894,25 @@ __device__ __forceinline__ qe_u32 qe_stage_bits(const unsigned char *bitmap, int
     return (w >> (r & 31)) & 3u;
 }
 
+// one row of a staged column (ring variant): lane l of a warp step reads row wrow0 + c + l of the tile;
+// c is a compile-time constant after unrolling, so it folds into the LDS immediate offset
+__device__ __forceinline__ double qe_stage1_f64(const unsigned char *col, int wrow0, int c)
+{
+    return *(const double *)(col + (size_t)(wrow0 + (int)qe_lane()) * 8 + (size_t)c * 8);
+}
+__device__ __forceinline__ qe_i64 qe_stage1_i64(const unsigned char *col, int wrow0, int c)
+{
+    return *(const qe_i64 *)(col + (size_t)(wrow0 + (int)qe_lane()) * 8 + (size_t)c * 8);
+}
+__device__ __forceinline__ qe_i32 qe_stage1_i32(const unsigned char *col, int wrow0, int c)
+{
+    return *(const qe_i32 *)(col + (size_t)(wrow0 + (int)qe_lane()) * 4 + (size_t)c * 4);
+}
+__device__ __forceinline__ bool qe_stage1_bit(const unsigned char *bitmap, int wrow0, int c)
+{
+    return (*(const qe_u32 *)(bitmap + (size_t)(wrow0 >> 5) * 4 + (size_t)(c >> 5) * 4) >> qe_lane()) & 1u;
+}
+
 // K1, staged variant.  Additional members of P:
 //   static constexpr int NSTAGES, STAGE_BYTES (stride of one stage), STAGE_TX (bytes the copies of one stage move);
 //   static void issue(const QeParams&, qe_i64 tile_row0, qe_u32 stage_smem, qe_u32 mbar);   one thread
@@ -969,6 +992,331 @@ __device__ __forceinline__ void qe_filter_staged_body(const QeParams &p)
         const qe_u64 excl = qe_block_lookback(p.tile_state, tile, tile_total, s_lb_sum, s_lb_found);
         if (threadIdx.x == 0 && tile == p.ntiles - 1) *p.out_count = excl + tile_total;
         qe_warp_scatter<P>(p, warp_row0, excl + woff, outs, keep, rank0, step_off);
+    }
+}
+
+// ---- K1, ring variant (the default) ------------------------------------------------
+//
+// One persistent CTA per SM, warp-specialised around a ring of NSTAGES shared-memory
+// stages (a stage = one tile of every referenced column, 16-48 KB):
+//
+//   warp 0      producer   claims tiles through the ticket counter and issues one
+//                          cp.async.bulk per column run into the next free stage
+//   warp 1      publisher  when a tile has been evaluated: sums the per-warp kept-row
+//                          counts and publishes the tile's descriptor (count + 1)
+//   warp 2      look-back  exclusive prefix of each of this CTA's tiles
+//   warps 3..   consumers  phase A (evaluate the filter on a tile from shared memory,
+//                          ballot -> keep-mask words + per-warp counts) and, DEFER
+//                          tiles later, phase C (ordered scatter of the kept rows:
+//                          selection vector + compacted outputs)
+//
+// Why this shape (measured on B200): stable compaction cannot write
+// tile t before every earlier tile has been counted, and on a 148-SM part a
+// descriptor needs an L2 round trip (~500-900 cycles under streaming load) to travel
+// between SMs while a 32 KB tile streams in ~1 500 cycles.  A kernel that holds its
+// tile in registers while it waits stalls the loads; here the tile waits in shared
+// memory, the bulk copies of the next tiles keep running (bytes in flight are bounded
+// by the 227 KB of shared memory, not by registers), and the consumers always have a
+// phase A to run while a prefix is outstanding.
+//
+// Look-back over a persistent grid: tickets are handed out in increasing order, so
+// between two consecutive tiles t' < t of one CTA lie only tiles of other CTAs, and
+//     excl(t) = incl(t') + sum of the counts of tiles t'+1 .. t-1.
+// The look-back warp therefore never hunts for a predecessor with a known prefix: it
+// reads that gap (on average gridDim.x - 1 descriptors, all in flight at once) and
+// adds it to its own running total.  Every predecessor was claimed earlier by a
+// resident CTA, so the spin cannot deadlock.
+//
+// All hand-offs are mbarriers (arrive = release, try_wait = acquire at CTA scope):
+//   full[st]   producer arrive + bulk-copy bytes      -> consumers
+//   claim[st]  producer (tile id known)               -> publisher, look-back
+//   eval[st]   NCW consumer warps (phase A done)      -> publisher, look-back, phase C
+//   pref[st]   look-back (s_excl[st] written)         -> phase C
+//   empty[st]  NCW consumers + publisher + look-back  -> producer
+//
+// Additional members of P:
+//   static constexpr int TILE_ROWS, NCW, NSTAGES, DEFER, LOADS, STAGE_BYTES, STAGE_TX;
+//   static void issue(const QeParams&, qe_i64 tile_row0, qe_u32 stage_smem, qe_u32 mbar, qe_u64 l2_policy);   one thread
+//   static void load_row(const unsigned char *stage, int wrow0, int c, Row&);   row wrow0 + c + lane of the tile (wrow0, c: multiples of 32)
+//   static void emit_at(const QeParams&, qe_u64 base, qe_u32 idx, const Out&);   value outputs at position base + idx
+
+__device__ __forceinline__ void qe_mbar_arrive(qe_u32 mbar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(mbar) : "memory");
+}
+
+__device__ __forceinline__ qe_u32 qe_ld_relaxed_u32(const qe_u32 *p)
+{
+    qe_u32 v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void qe_st_relaxed_u32(qe_u32 *p, qe_u32 v)
+{
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+
+// Phase C of the ring kernel for one warp: kept rows of its slice, in row order, to
+// consecutive output positions starting at wbase.  One store instruction covers one
+// warp step = one contiguous run of the outputs.
+template <class P, int STEPS, bool CHECK_CAP, bool HAS_SEL>
+__device__ __forceinline__ void qe_ring_scatter(const QeParams &p, const unsigned char *stage, int wrow0, qe_u32 first_row,
+                                                qe_u64 wbase, const qe_u32 *masks)
+{
+    const qe_u32 lane = qe_lane();
+    const qe_u32 lt = qe_lanemask_lt();
+    qe_u32 mk[STEPS];
+#pragma unroll
+    for (int s = 0; s < STEPS; s++) mk[s] = masks[s];
+    qe_u32 off = 0;                                           // kept rows of this warp in earlier steps
+#pragma unroll
+    for (int s = 0; s < STEPS; s++) {
+        const qe_u32 m = mk[s];
+        if (m == 0u) continue;                                // warp-uniform
+        const bool kept = (m >> lane) & 1u;
+        const qe_u32 idx = off + __popc(m & lt);
+        typename P::Row row;
+        typename P::Out o;
+        if (P::NBITCOLS > 0 || kept) {
+            P::load_row(stage, wrow0, s * 32, row);
+            (void)P::eval(p, row, o);
+        }
+        if (kept && (!CHECK_CAP || wbase + idx < (qe_u64)p.out_capacity)) {
+            if (HAS_SEL) (p.sel + wbase)[idx] = first_row + (qe_u32)(s * 32);
+            P::emit_at(p, wbase, idx, o);
+        }
+        if (P::NBITCOLS > 0 && (!CHECK_CAP || wbase + off < (qe_u64)p.out_capacity)) {
+            const qe_u32 rk[1] = {idx - off};
+#pragma unroll
+            for (int b = 0; b < P::NBITCOLS; b++) {
+                qe_u32 *bm = P::bitcol(p, b);
+                if (bm) qe_store_bits_compact<1>(bm, wbase + off, rk, kept ? 1u : 0u, P::bit(o, b) ? 1u : 0u);
+            }
+        }
+        off += __popc(m);
+    }
+}
+
+// bulk copy with an L2 evict-first policy: scanned columns are read exactly once, so they should not
+// push the (re-read) tile descriptors or the partially written output lines out of L2
+__device__ __forceinline__ void qe_bulk_g2s_stream(qe_u32 dst_smem, const void *src, qe_u32 bytes, qe_u32 mbar, qe_u64 policy)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 :: "r"(dst_smem), "l"(src), "r"(bytes), "r"(mbar), "l"(policy) : "memory");
+}
+
+__device__ __forceinline__ qe_u64 qe_policy_evict_first()
+{
+    qe_u64 pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+
+__device__ __forceinline__ void qe_prefetch_l2_keep(const void *p)
+{
+    asm volatile("prefetch.global.L2::evict_last [%0];" :: "l"(p));
+}
+
+#define QE_RING_AUX_WARPS 3          // producer, publisher, look-back
+#define QE_RING_LB_PER_LANE 6        // descriptors per lane per look-back round trip (192 per warp)
+
+template <class P>
+__device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
+{
+    constexpr int NST = P::NSTAGES, NCW = P::NCW, TILE = P::TILE_ROWS, DEFER = P::DEFER;
+    constexpr int WROWS = TILE / NCW, STEPS = WROWS / 32;
+    static_assert(WROWS % 32 == 0 && NCW <= 32 && DEFER >= 1 && DEFER < NST, "ring shape");
+
+    extern __shared__ __align__(128) unsigned char qe_dyn_smem[];
+    __shared__ __align__(8) qe_u64 s_full[NST], s_claim[NST], s_eval[NST], s_pref[NST], s_empty[NST];
+    __shared__ qe_u64 s_excl[NST];
+    __shared__ qe_u32 s_tile[NST];
+    __shared__ qe_u32 s_total[NST];
+    __shared__ __align__(16) qe_u32 s_cnt[NST][NCW];
+    __shared__ __align__(16) qe_u32 s_mask[NST][TILE / 32];
+
+    const qe_u32 lane = qe_lane(), warp = qe_warp();
+    qe_u32 *const desc = (qe_u32 *)p.tile_state;             // one 32-bit descriptor per tile: 0 = not counted yet, else count + 1
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int st = 0; st < NST; st++) {
+            qe_mbar_init(qe_smem_addr(&s_full[st]), 1);
+            qe_mbar_init(qe_smem_addr(&s_claim[st]), 1);
+            qe_mbar_init(qe_smem_addr(&s_eval[st]), NCW);
+            qe_mbar_init(qe_smem_addr(&s_pref[st]), 1);
+            qe_mbar_init(qe_smem_addr(&s_empty[st]), NCW + 2);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp == 0) {
+        // ------------------------------------------------------------ producer
+        if (lane == 0) {
+            const qe_u64 policy = qe_policy_evict_first();
+            qe_u32 t = atomicAdd(p.ticket, 1u);
+            for (qe_u32 it = 0;; it++) {
+                const int st = (int)(it % NST);
+                if (it >= NST) qe_mbar_wait(qe_smem_addr(&s_empty[st]), ((it / NST) - 1u) & 1u);
+                // at most LOADS tiles in flight: more only queue up in the memory system, and every
+                // descriptor read of the look-back then waits behind them
+                if (P::LOADS > 0 && it >= (qe_u32)P::LOADS) {
+                    const qe_u32 jt = it - (qe_u32)P::LOADS;
+                    qe_mbar_wait(qe_smem_addr(&s_full[jt % NST]), (jt / NST) & 1u);
+                }
+                s_tile[st] = t;
+                qe_mbar_arrive(qe_smem_addr(&s_claim[st]));
+                if (t >= p.ntiles) {                          // end marker: wakes the consumers, carries no bytes
+                    qe_mbar_arrive(qe_smem_addr(&s_full[st]));
+                    break;
+                }
+                // the tile's descriptor line should be in L2 when it is published and read, NST tiles from now
+                if (!(QE_DEBUG_FLAGS & 32)) qe_prefetch_l2_keep(desc + t);
+                const qe_u32 full = qe_smem_addr(&s_full[st]);
+                qe_mbar_expect_tx(full, (qe_u32)P::STAGE_TX);
+                P::issue(p, (qe_i64)t * TILE, qe_smem_addr(qe_dyn_smem + (size_t)st * P::STAGE_BYTES), full, policy);
+                t = atomicAdd(p.ticket, 1u);                  // next ticket: its round trip overlaps the wait for a free stage
+            }
+        }
+    } else if (warp == 1) {
+        // ----------------------------------------------------------- publisher
+        for (qe_u32 it = 0;; it++) {
+            const int st = (int)(it % NST);
+            const qe_u32 par = (it / NST) & 1u;
+            qe_mbar_wait(qe_smem_addr(&s_claim[st]), par);
+            const qe_u32 t = s_tile[st];
+            if (t >= p.ntiles) break;
+            qe_mbar_wait(qe_smem_addr(&s_eval[st]), par);
+            qe_u32 c = lane < (qe_u32)NCW ? s_cnt[st][lane] : 0u;
+            c = __reduce_add_sync(QE_FULL_MASK, c);
+            if (lane == 0) {
+                qe_st_relaxed_u32(desc + t, c + 1u);
+                qe_mbar_arrive(qe_smem_addr(&s_empty[st]));
+            }
+        }
+    } else if (warp == 2) {
+        // ----------------------------------------------------------- look-back
+        qe_u64 run = 0;                                       // kept rows in tiles [0, lo)
+        qe_u32 lo = 0;
+        for (qe_u32 it = 0;; it++) {
+            const int st = (int)(it % NST);
+            const qe_u32 par = (it / NST) & 1u;
+            qe_mbar_wait(qe_smem_addr(&s_claim[st]), par);
+            const qe_u32 t = s_tile[st];
+            if (t >= p.ntiles) break;
+            // Wait for this CTA's own count first: the grid moves in step, so by then the tiles of the
+            // other CTAs in the gap are counted (or about to be) and the descriptors are read once
+            // instead of being polled for a whole tile time (148 warps polling five cache lines slowed
+            // the very stores they were waiting for: measured 5-12 us per prefix).
+            qe_mbar_wait(qe_smem_addr(&s_eval[st]), par);
+            qe_u32 c = lane < (qe_u32)NCW ? s_cnt[st][lane] : 0u;
+            c = __reduce_add_sync(QE_FULL_MASK, c);
+            // the gap [lo, t): tiles of other CTAs claimed between this CTA's previous tile and this one
+            qe_u32 gap = 0;
+            for (qe_u32 base = lo; base < t; base += 32u * QE_RING_LB_PER_LANE) {
+                qe_u32 d[QE_RING_LB_PER_LANE];
+#pragma unroll
+                for (int k = 0; k < QE_RING_LB_PER_LANE; k++) {   // every read in flight before the first is used
+                    const qe_u32 idx = base + (qe_u32)k * 32u + lane;
+                    d[k] = idx < t ? qe_ld_relaxed_u32(desc + idx) : 1u;
+                }
+#pragma unroll
+                for (int k = 0; k < QE_RING_LB_PER_LANE; k++) {
+                    const qe_u32 idx = base + (qe_u32)k * 32u + lane;
+                    while (d[k] == 0u) {
+                        __nanosleep(64);
+                        d[k] = qe_ld_relaxed_u32(desc + idx);
+                    }
+                    gap += d[k] - 1u;
+                }
+            }
+            gap = __reduce_add_sync(QE_FULL_MASK, gap);
+            const qe_u64 excl = run + gap;
+            if (lane == 0) {
+                s_excl[st] = excl;
+                s_total[st] = c;
+                qe_mbar_arrive(qe_smem_addr(&s_pref[st]));
+                qe_mbar_arrive(qe_smem_addr(&s_empty[st]));
+            }
+            run = excl + c;
+            lo = t + 1u;
+            if (lane == 0 && t == p.ntiles - 1u) *p.out_count = run;
+        }
+    } else {
+        // ----------------------------------------------------------- consumers
+        const int cw = (int)warp - QE_RING_AUX_WARPS;
+        const int wrow0 = cw * WROWS;                         // this warp's slice of every tile
+        int n_valid = 0x7fffffff;                             // iterations that carry a tile (known once the end marker is seen)
+        for (int it = 0;; it++) {
+            if (it < n_valid) {
+                // ---- phase A: evaluate the filter, leave keep masks and counts in shared memory
+                const int st = it % NST;
+                qe_mbar_wait(qe_smem_addr(&s_full[st]), (qe_u32)(it / NST) & 1u);
+                const qe_u32 t = s_tile[st];
+                if (t >= p.ntiles) {
+                    n_valid = it;
+                } else {
+                    const unsigned char *stage = qe_dyn_smem + (size_t)st * P::STAGE_BYTES;
+                    const qe_i64 row0 = (qe_i64)t * TILE;
+                    qe_u32 mk[STEPS];
+                    if (row0 + TILE <= p.nrows) {
+#pragma unroll
+                        for (int s = 0; s < STEPS; s++) {
+                            typename P::Row row;
+                            typename P::Out o;
+                            P::load_row(stage, wrow0, s * 32, row);
+                            mk[s] = __ballot_sync(QE_FULL_MASK, P::eval(p, row, o));
+                        }
+                    } else {                                   // the last tile: rows past the end never pass
+                        const qe_i64 live = p.nrows - row0 - wrow0 - (qe_i64)lane;
+#pragma unroll
+                        for (int s = 0; s < STEPS; s++) {
+                            typename P::Row row;
+                            typename P::Out o;
+                            P::load_row(stage, wrow0, s * 32, row);
+                            mk[s] = __ballot_sync(QE_FULL_MASK, P::eval(p, row, o) && (qe_i64)(s * 32) < live);
+                        }
+                    }
+                    qe_u32 cnt = 0;
+#pragma unroll
+                    for (int s = 0; s < STEPS; s++) cnt += __popc(mk[s]);
+                    if (lane == 0) {
+#pragma unroll
+                        for (int s = 0; s < STEPS; s++) s_mask[st][cw * STEPS + s] = mk[s];
+                        s_cnt[st][cw] = cnt;
+                        qe_mbar_arrive(qe_smem_addr(&s_eval[st]));
+                    }
+                    __syncwarp();
+                }
+            }
+            const int j = it - DEFER;
+            if (j >= 0 && j < n_valid) {
+                // ---- phase C: ordered scatter of tile j, whose prefix has had DEFER tile times to arrive
+                const int st = j % NST;
+                qe_mbar_wait(qe_smem_addr(&s_pref[st]), (qe_u32)(j / NST) & 1u);   // pref follows eval
+                const unsigned char *stage = qe_dyn_smem + (size_t)st * P::STAGE_BYTES;
+                const qe_u32 first_row = p.sel_base + (qe_u32)((qe_i64)s_tile[st] * TILE) + (qe_u32)wrow0 + lane;
+                const qe_u64 excl = s_excl[st];
+                qe_u32 woff = 0;
+#pragma unroll
+                for (int w = 0; w < NCW; w++) woff += w < cw ? s_cnt[st][w] : 0u;
+                const qe_u64 wbase = excl + woff;             // output position of this warp's first kept row
+                const bool fits = excl + s_total[st] <= (qe_u64)p.out_capacity;
+                const qe_u32 *mk = &s_mask[st][cw * STEPS];
+                if (fits) {
+                    if (p.sel) qe_ring_scatter<P, STEPS, false, true>(p, stage, wrow0, first_row, wbase, mk);
+                    else qe_ring_scatter<P, STEPS, false, false>(p, stage, wrow0, first_row, wbase, mk);
+                } else {
+                    if (p.sel) qe_ring_scatter<P, STEPS, true, true>(p, stage, wrow0, first_row, wbase, mk);
+                    else qe_ring_scatter<P, STEPS, true, false>(p, stage, wrow0, first_row, wbase, mk);
+                }
+                __syncwarp();
+                if (lane == 0) qe_mbar_arrive(qe_smem_addr(&s_empty[st]));
+            }
+            if (n_valid != 0x7fffffff && j + 1 >= n_valid) break;
+        }
     }
 }
 

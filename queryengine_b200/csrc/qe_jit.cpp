@@ -123,7 +123,7 @@ bool jit_compile(const std::string &source, std::vector<char> &cubin, std::strin
     return true;
 }
 
-bool jit_load(const std::vector<char> &cubin, const char *entry, size_t dyn_smem, JitKernel &out, std::string &err)
+bool jit_load(const std::vector<char> &cubin, const char *entry, size_t dyn_smem, int block_threads, JitKernel &out, std::string &err)
 {
     cudaError_t e = cudaLibraryLoadData(&out.library, cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0);
     if (e != cudaSuccess) { err = std::string("cudaLibraryLoadData: ") + cudaGetErrorString(e); return false; }
@@ -145,7 +145,7 @@ bool jit_load(const std::vector<char> &cubin, const char *entry, size_t dyn_smem
         }
     }
     int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, (const void *)out.kernel, 256, dyn_smem) == cudaSuccess && n > 0)
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, (const void *)out.kernel, block_threads, dyn_smem) == cudaSuccess && n > 0)
         out.blocks_per_sm = n;
     else
         (void)cudaGetLastError();

@@ -38,7 +38,7 @@ bool jit_compile(const std::string &source, std::vector<char> &cubin, std::strin
                  const std::vector<std::string> &extra_options = std::vector<std::string>());
 
 // Load a cubin on the current device and look up the entry point.
-bool jit_load(const std::vector<char> &cubin, const char *entry, size_t dyn_smem, JitKernel &out, std::string &err);
+bool jit_load(const std::vector<char> &cubin, const char *entry, size_t dyn_smem, int block_threads, JitKernel &out, std::string &err);
 void jit_unload(JitKernel &k);
 
 }  // namespace qe

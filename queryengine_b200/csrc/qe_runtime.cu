@@ -133,7 +133,8 @@ struct qe_ctx {
     Pool pool;
     std::unordered_map<std::string, JitEntry> jit_cache;
     // options
-    int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = 0, opt_stages = 0, opt_debug_flags = 0, opt_pipeline = 1;
+    int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = -1, opt_stages = 0, opt_debug_flags = 0, opt_pipeline = 1;
+    int64_t opt_loads = 0, opt_tile_rows = 0, opt_ncw = 0, opt_defer = 0, opt_stage_kb = 0;
     int64_t launches = 0;
     bool warned_no_nvrtc = false;
     // pinned staging ring for uploads from pageable memory
@@ -252,14 +253,30 @@ extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
         if (value < 0 || value > 32) return fail(QE_ERR_INVALID_ARGUMENT, "grid_per_sm must be in [0, 32]");
         ctx->opt_grid_per_sm = value;
     } else if (k == "staging") {
-        if (value < -1 || value > 1) return fail(QE_ERR_INVALID_ARGUMENT, "staging must be -1 (auto), 0 or 1");
+        if (value < -1 || value > 2) return fail(QE_ERR_INVALID_ARGUMENT, "staging must be -1 (auto), 0, 1 or 2");
         ctx->opt_staging = value;
     } else if (k == "pipeline") {
         ctx->opt_pipeline = value != 0;
+    } else if (k == "tile_rows") {
+        if (value < 0 || value > kPadRows || value % 128) return fail(QE_ERR_INVALID_ARGUMENT, "tile_rows must be 0 (auto) or a multiple of 128 up to 8192");
+        ctx->opt_tile_rows = value;
+    } else if (k == "ncw") {
+        if (value != 0 && value != 4 && value != 8 && value != 12 && value != 16 && value != 20 && value != 24)
+            return fail(QE_ERR_INVALID_ARGUMENT, "ncw must be 0 (auto), 4, 8, 12, 16, 20 or 24");
+        ctx->opt_ncw = value;
+    } else if (k == "defer") {
+        if (value < 0 || value > 6) return fail(QE_ERR_INVALID_ARGUMENT, "defer must be in [0, 6] (0 = auto)");
+        ctx->opt_defer = value;
+    } else if (k == "loads") {
+        if (value < 0 || value > 32) return fail(QE_ERR_INVALID_ARGUMENT, "loads must be in [0, 32] (0 = no limit)");
+        ctx->opt_loads = value;
+    } else if (k == "stage_kb") {
+        if (value < 0 || value > 64) return fail(QE_ERR_INVALID_ARGUMENT, "stage_kb must be in [0, 64] (0 = auto)");
+        ctx->opt_stage_kb = value;
     } else if (k == "debug_flags") {
         ctx->opt_debug_flags = value;                       // timing experiments only (results are wrong)
     } else if (k == "stages") {
-        if (value != 0 && (value < 2 || value > 8)) return fail(QE_ERR_INVALID_ARGUMENT, "stages must be 0 (auto) or 2..8");
+        if (value != 0 && (value < 2 || value > 32)) return fail(QE_ERR_INVALID_ARGUMENT, "stages must be 0 (auto) or 2..32");
         ctx->opt_stages = value;
     } else return fail(QE_ERR_INVALID_ARGUMENT, "unknown option '" + k + "'");
     return QE_OK;
@@ -572,7 +589,7 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
     }
     // Filter kernel: land the columns in shared-memory stages with bulk copies, so the bytes in
     // flight are not bounded by registers and the next tiles load during scan / look-back / scatter.
-    s.staged = mode == qe::KM_FILTER && ctx->opt_staging > 0;
+    s.staged = mode == qe::KM_FILTER && ctx->opt_staging == 1;
     s.pipelined = ctx->opt_pipeline != 0;
     if (s.staged) {
         s.vec = 2;                                             // staged rows are read back with 128-bit LDS
@@ -587,6 +604,27 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         if ((size_t)s.nstages * stage > (220u << 10)) s.staged = false;   // does not fit: register-sourced kernel
     }
     s.min_blocks = 1;
+    // Filter kernel, default: persistent warp-specialised CTA around a ring of bulk-copy stages.
+    s.ring = mode == qe::KM_FILTER && (ctx->opt_staging == -1 || ctx->opt_staging == 2);
+    if (s.ring) {
+        s.ncw = ctx->opt_ncw ? (int)ctx->opt_ncw : 16;
+        const size_t quantum = (size_t)std::max(128, 32 * s.ncw);       // rows: whole warp steps, 16-byte bitmap runs
+        const size_t stage_target = (size_t)(ctx->opt_stage_kb ? ctx->opt_stage_kb : 32) << 10;
+        size_t rows = ctx->opt_tile_rows ? (size_t)ctx->opt_tile_rows : stage_target / row_bytes / quantum * quantum;
+        rows = std::min<size_t>(std::max(rows, quantum), (size_t)kPadRows / quantum * quantum);
+        if (rows % quantum) rows = (rows + quantum - 1) / quantum * quantum;
+        s.tile_rows = (int)rows;
+        s.nstages = 1;
+        const size_t stage = qe::staged_smem_bytes(bp, s);
+        const size_t meta = 64 + (size_t)s.tile_rows / 8 + 4 * (size_t)s.ncw;   // per stage: barriers, keep masks, counts
+        size_t n = ctx->opt_stages ? (size_t)ctx->opt_stages : 16;
+        while (n > 2 && n * (stage + meta) > (224u << 10)) n--;
+        s.nstages = (int)n;
+        s.defer = ctx->opt_defer ? (int)ctx->opt_defer : 2;
+        if (s.defer >= s.nstages) s.defer = s.nstages - 1;
+        s.loads = (int)ctx->opt_loads;
+        if (n * (stage + meta) > (224u << 10) || s.defer < 1) s.ring = false;   // a single tile does not fit: register-sourced kernel
+    }
     return s;
 }
 
@@ -625,9 +663,10 @@ static void serialize_interp(const qe::BoundPipeline &bp, std::vector<uint32_t> 
 static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMode mode, const qe::TileShape &shape,
                           JitEntry **out)
 {
-    char suffix[64];
-    snprintf(suffix, sizeof suffix, "|M%d|S%d|V%d|T%d.%d|D%d|P%d", (int)mode, shape.steps, shape.vec, shape.staged ? 1 : 0,
-             shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0);
+    char suffix[128];
+    snprintf(suffix, sizeof suffix, "|M%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d", (int)mode, shape.steps, shape.vec, shape.staged ? 1 : 0,
+             shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0, shape.ring ? 1 : 0, shape.tile_rows, shape.ncw,
+             shape.defer, shape.loads);
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) { *out = &it->second; return QE_OK; }
@@ -643,7 +682,9 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     JitEntry e;
     e.shape = shape;
     std::string err;
-    if (!qe::jit_load(cubin, QE_JIT_ENTRY, qe::staged_smem_bytes(bp, shape), e.kernel, err)) return fail(QE_ERR_JIT, err);
+    if (!qe::jit_load(cubin, QE_JIT_ENTRY, qe::staged_smem_bytes(bp, shape), mode == qe::KM_FILTER ? shape.block_threads() : QE_BLOCK,
+                      e.kernel, err))
+        return fail(QE_ERR_JIT, err);
     if (getenv("QE_DUMP_JIT"))
         fprintf(stderr, "[qegpu] jit %s: %d regs, %d CTAs/SM\n", key.c_str(), e.kernel.regs, e.kernel.blocks_per_sm);
     auto ins = ctx->jit_cache.emplace(key, e);
@@ -710,7 +751,8 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
         shape.vec = QE_INTERP_VEC;
         blocks_per_sm = qe::interp_blocks_per_sm((int)mode);
     }
-    const int64_t tile_rows = (int64_t)QE_WARPS * shape.steps * 32 * shape.vec;
+    const int64_t tile_rows = shape.rows_per_tile();
+    const int block_threads = use_jit && mode == qe::KM_FILTER ? shape.block_threads() : QE_BLOCK;
     const int64_t ntiles64 = (n + tile_rows - 1) / tile_rows;
     const uint32_t ntiles = (uint32_t)ntiles64;
     if (ctx->opt_grid_per_sm) blocks_per_sm = std::min<int>(blocks_per_sm, (int)ctx->opt_grid_per_sm);
@@ -824,7 +866,7 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
     if (n > 0) {
         if (use_jit) {
             void *args[] = {&p};
-            QE_CUDA(cudaLaunchKernel((const void *)jit->kernel.kernel, dim3(grid), dim3(QE_BLOCK), args, jit->kernel.dyn_smem, ctx->stream));
+            QE_CUDA(cudaLaunchKernel((const void *)jit->kernel.kernel, dim3(grid), dim3(block_threads), args, jit->kernel.dyn_smem, ctx->stream));
         } else {
             QE_CUDA(qe::launch_interp((int)mode, p, grid, ctx->stream));
         }

@@ -75,7 +75,11 @@ Q6_PROJ = fn(Function.MUL, col(1), col(2))
 def test_generated_code_compiles_for_sm100a():
     rc, src, nbytes, err = _generate([(I, False)], fn(Function.CMP_LT, col(0, I), 1e6), [col(0, I)])
     assert rc == 0, err
-    assert "qe_filter_pipelined_body<P>" in src and "((qe_i64)in.c0 < 1000000LL)" in src and nbytes > 1000
+    assert "qe_filter_ring_body<P>" in src and "((qe_i64)in.c0 < 1000000LL)" in src and nbytes > 1000
+    assert "TILE_ROWS = 4096" in src and "row.c0 = qe_stage1_i64(stage + 0, wrow0, c);" in src
+    rc, src, nbytes, err = _generate([(I, False)], fn(Function.CMP_LT, col(0, I), 1e6), [col(0, I)], staging=0)
+    assert rc == 0, err
+    assert "qe_filter_pipelined_body<P>" in src and nbytes > 1000
     rc, src, nbytes, err = _generate([(I, False)], fn(Function.CMP_LT, col(0, I), 1e6), [col(0, I)], staging=1)
     assert rc == 0, err
     assert "qe_bulk_g2s(stage + 0, (const char *)p.col_values[0] + row0 * 8" in src and "qe_filter_staged_body<P>" in src
@@ -92,13 +96,14 @@ def test_generated_code_compiles_for_sm100a():
     # every tile shape the runtime may pick
     for steps in (1, 2, 4, 8):
         for vec in (2, 4):
-            for staging in (0, 1):
+            for staging in (0, 1, 2):
                 rc, src, nbytes, err = _generate([(D, True), (B, True), (T, False)],
                                                  fn(Function.OR, col(1, B), fn(Function.CMP_GE, col(2, T), 9000.0)),
                                                  [fn(Function.IF, col(1, B), col(0), 1.0), col(1, B), col(2, T)],
                                                  steps=steps, vec=vec, staging=staging)
                 assert rc == 0, (steps, vec, staging, err)
                 assert ("qe_filter_staged_body<P>" in src) == (staging == 1)
+                assert ("qe_filter_ring_body<P>" in src) == (staging == 2)
 
 
 def test_type_errors_follow_the_reference_typecheck():

@@ -174,6 +174,34 @@ def test_every_tile_shape(ctx, steps, vec, staging):
     c.close()
 
 
+@pytest.mark.parametrize("stage_kb,ncw,defer,stages", [(0, 0, 0, 0), (4, 4, 1, 2), (8, 8, 1, 3), (16, 16, 3, 5), (48, 8, 2, 4),
+                                                       (2, 12, 2, 16)])
+def test_every_ring_shape(ctx, stage_kb, ncw, defer, stages):
+    """The warp-specialised ring variant of the filter kernel (the default) over its option space."""
+    c = Context(0)
+    c.set_option("staging", 2)
+    for k, v in (("stage_kb", stage_kb), ("ncw", ncw), ("defer", defer), ("stages", stages)):
+        c.set_option(k, v)
+    rng = np.random.default_rng(stage_kb * 100 + ncw)
+    for n in (0, 1, 127, 128, 129, 4095, 4096, 4097, 100003, 1_000_003):
+        v = rng.integers(0, 1000, n).astype(np.int64)
+        t = ColumnarTable(c, [Field("col", I, False)], n)
+        t.upload(0, v)
+        for k in (0.0, 10.0, 500.0, 990.0, 1000.0):
+            res = Pipeline(t, fn(Function.CMP_LT, col(0, I), k), [col(0, I)]).run()
+            want = np.nonzero(v < k)[0].astype(np.uint32)
+            assert res.num_rows == want.size
+            assert np.array_equal(res.selection(), want)
+            assert np.array_equal(res.column(0)[0], v[want])
+            res.close()
+        t.close()
+    spec = random_table(rng, 70001, "DbiT")
+    g = ExprGen(rng, spec.fields)
+    compare_pipeline(c, spec, g.boolean(3), [g.double(4), g.boolean(2), col(2, I), col(3, T)])
+    compare_pipeline(c, spec, g.boolean(4), [col(0), col(1, spec.fields[1].type)])
+    c.close()
+
+
 @pytest.mark.parametrize("interpreter", [False, True])
 def test_aggregates(ctx, interpreter):
     rng = np.random.default_rng(5)
