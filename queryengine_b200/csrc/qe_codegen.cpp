@@ -357,8 +357,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         snprintf(b, sizeof b, "    static constexpr int NSTAGES = %d, STAGE_BYTES = %d, STAGE_TX = %d;\n", shape.nstages, L.stride, L.tx);
         s += b;
         if (shape.ring) {
-            snprintf(b, sizeof b, "    static constexpr int TILE_ROWS = %d, NCW = %d, DEFER = %d, LOADS = %d;\n", shape.tile_rows, shape.ncw, shape.defer,
-                     shape.loads);
+            snprintf(b, sizeof b, "    static constexpr int TILE_ROWS = %d, NCW = %d, NLB = %d, DEFER = %d, LOADS = %d;\n", shape.tile_rows, shape.ncw,
+                     shape.nlb, shape.defer, shape.loads);
             s += b;
             // one row (lane-strided: a warp step reads 32 consecutive rows, conflict-free) from a stage
             s += "    static __device__ __forceinline__ void load_row(const unsigned char *stage, int wrow0, int c, Row &row) {\n";
@@ -458,11 +458,27 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         s += "    }\n";
     }
     if (mode == KM_FILTER && shape.ring) {
-        s += "    static __device__ __forceinline__ void emit_at(const QeParams &p, qe_u64 base, qe_u32 idx, const Out &o) {\n";
+        // per-warp output pointers (advanced to the warp's first output once per tile) + 32-bit indices
+        s += "    struct Ptrs {";
+        bool any = false;
         for (int k = 0; k < nproj; k++) {
             if (bp.outs[k].type == 2) continue;
-            snprintf(b, sizeof b, "        ((%s *)p.out_values[%d] + base)[idx] = o.o%d;\n", ctype_of(bp.outs[k].type), k, k);
-            s += b;
+            snprintf(b, sizeof b, " %s *o%d;", ctype_of(bp.outs[k].type), k); s += b;
+            any = true;
+        }
+        if (!any) s += " int unused;";
+        s += " };\n";
+        s += "    static __device__ __forceinline__ Ptrs out_ptrs(const QeParams &p, qe_u64 base) {\n        Ptrs q;\n";
+        for (int k = 0; k < nproj; k++) {
+            if (bp.outs[k].type == 2) continue;
+            snprintf(b, sizeof b, "        q.o%d = qe_opaque_ptr((%s *)p.out_values[%d] + base);\n", k, ctype_of(bp.outs[k].type), k); s += b;
+        }
+        if (!any) s += "        q.unused = 0;\n";
+        s += "        return q;\n    }\n";
+        s += "    static __device__ __forceinline__ void emit_ptr(const Ptrs &q, qe_u32 idx, const Out &o, bool ok) {\n";
+        for (int k = 0; k < nproj; k++) {
+            if (bp.outs[k].type == 2) continue;
+            snprintf(b, sizeof b, "        qe_stg_if(ok, q.o%d + idx, o.o%d);\n", k, k); s += b;
         }
         s += "    }\n";
     }

@@ -29,12 +29,13 @@ struct TileShape {
     // shared-memory stages filled by cp.async.bulk; steps / vec are ignored
     bool ring = false;
     int tile_rows = 4096;   // rows per tile = rows per stage; a multiple of 32 * ncw and of 128
-    int ncw = 8;            // consumer warps
-    int defer = 2;          // tiles between a tile's evaluation (phase A) and its scatter (phase C)
+    int ncw = 16;           // consumer warps
+    int nlb = 1;            // look-back warps
+    int defer = 3;          // tiles between a tile's evaluation (phase A) and its scatter (phase C)
     int loads = 0;          // bulk-copy tiles in flight at most (0 = as many as there are free stages)
 
     int rows_per_tile() const { return ring ? tile_rows : 8 * steps * 32 * vec; }
-    int block_threads() const { return ring ? 32 * (3 + ncw) : 256; }
+    int block_threads() const { return ring ? 32 * (2 + nlb + ncw) : 256; }
 };
 
 // bytes of dynamic shared memory the staged filter kernel needs (0 when not staged)

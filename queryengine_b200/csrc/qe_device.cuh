@@ -1004,8 +1004,8 @@ __device__ __forceinline__ void qe_filter_staged_body(const QeParams &p)
 //                          cp.async.bulk per column run into the next free stage
 //   warp 1      publisher  when a tile has been evaluated: sums the per-warp kept-row
 //                          counts and publishes the tile's descriptor (count + 1)
-//   warp 2      look-back  exclusive prefix of each of this CTA's tiles
-//   warps 3..   consumers  phase A (evaluate the filter on a tile from shared memory,
+//   warps 2..   look-back  NLB warps: exclusive prefix of each of this CTA's tiles (round robin)
+//   then        consumers  phase A (evaluate the filter on a tile from shared memory,
 //                          ballot -> keep-mask words + per-warp counts) and, DEFER
 //                          tiles later, phase C (ordered scatter of the kept rows:
 //                          selection vector + compacted outputs)
@@ -1035,10 +1035,11 @@ __device__ __forceinline__ void qe_filter_staged_body(const QeParams &p)
 //   empty[st]  NCW consumers + publisher + look-back  -> producer
 //
 // Additional members of P:
-//   static constexpr int TILE_ROWS, NCW, NSTAGES, DEFER, LOADS, STAGE_BYTES, STAGE_TX;
+//   static constexpr int TILE_ROWS, NCW, NLB, NSTAGES, DEFER, LOADS, STAGE_BYTES, STAGE_TX;
 //   static void issue(const QeParams&, qe_i64 tile_row0, qe_u32 stage_smem, qe_u32 mbar, qe_u64 l2_policy);   one thread
 //   static void load_row(const unsigned char *stage, int wrow0, int c, Row&);   row wrow0 + c + lane of the tile (wrow0, c: multiples of 32)
-//   static void emit_at(const QeParams&, qe_u64 base, qe_u32 idx, const Out&);   value outputs at position base + idx
+//   struct Ptrs; static Ptrs out_ptrs(const QeParams&, qe_u64 base);          value output arrays, advanced to position base
+//   static void emit_ptr(const Ptrs&, qe_u32 idx, const Out&, bool ok);       value outputs at position base + idx when ok
 
 __device__ __forceinline__ void qe_mbar_arrive(qe_u32 mbar)
 {
@@ -1057,44 +1058,96 @@ __device__ __forceinline__ void qe_st_relaxed_u32(qe_u32 *p, qe_u32 v)
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
 
+// Predicated stores.  Written as inline PTX so that phase C stays branch-free: left to
+// itself the compiler wraps every warp step in a divergent region (BSSY / BSYNC) and
+// re-derives the addresses inside it.
+__device__ __forceinline__ void qe_stg_if(bool ok, double *a, double v)
+{
+    asm volatile("{ .reg .pred q; setp.ne.u32 q, %0, 0; @q st.global.f64 [%1], %2; }" :: "r"((qe_u32)ok), "l"(a), "d"(v) : "memory");
+}
+__device__ __forceinline__ void qe_stg_if(bool ok, qe_i64 *a, qe_i64 v)
+{
+    asm volatile("{ .reg .pred q; setp.ne.u32 q, %0, 0; @q st.global.s64 [%1], %2; }" :: "r"((qe_u32)ok), "l"(a), "l"(v) : "memory");
+}
+__device__ __forceinline__ void qe_stg_if(bool ok, qe_i32 *a, qe_i32 v)
+{
+    asm volatile("{ .reg .pred q; setp.ne.u32 q, %0, 0; @q st.global.s32 [%1], %2; }" :: "r"((qe_u32)ok), "l"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ void qe_stg_if(bool ok, qe_u32 *a, qe_u32 v)
+{
+    asm volatile("{ .reg .pred q; setp.ne.u32 q, %0, 0; @q st.global.u32 [%1], %2; }" :: "r"((qe_u32)ok), "l"(a), "r"(v) : "memory");
+}
+// keeps a once-per-tile pointer in its register pair (the optimiser otherwise folds the 64-bit
+// base back into every address computation: 6 instructions per store instead of 1)
+template <class T>
+__device__ __forceinline__ T *qe_opaque_ptr(T *q)
+{
+    asm volatile("" : "+l"(q));
+    return q;
+}
+
 // Phase C of the ring kernel for one warp: kept rows of its slice, in row order, to
 // consecutive output positions starting at wbase.  One store instruction covers one
-// warp step = one contiguous run of the outputs.
-template <class P, int STEPS, bool CHECK_CAP, bool HAS_SEL>
-__device__ __forceinline__ void qe_ring_scatter(const QeParams &p, const unsigned char *stage, int wrow0, qe_u32 first_row,
-                                                qe_u64 wbase, const qe_u32 *masks)
+// warp step = one contiguous run of the outputs.  Two code paths, chosen per warp and
+// tile by the number of kept rows: a fully unrolled branch-free one (predicated
+// stores), and for sparse tiles a loop over the steps that kept anything.
+template <class P, bool CHECK_CAP, bool HAS_SEL>
+__device__ __forceinline__ void qe_ring_scatter_step(const QeParams &p, const typename P::Ptrs &ptrs, qe_u32 *selp,
+                                                     const unsigned char *stage, int wrow0, int c, qe_u32 row_id, qe_u64 wbase,
+                                                     qe_u32 cap_left, qe_u32 m, qe_u32 &off)
 {
     const qe_u32 lane = qe_lane();
-    const qe_u32 lt = qe_lanemask_lt();
-    qe_u32 mk[STEPS];
+    const bool kept = (m >> lane) & 1u;
+    const qe_u32 idx = off + __popc(m & qe_lanemask_lt());
+    typename P::Row row;
+    typename P::Out o;
+    P::load_row(stage, wrow0, c, row);
+    (void)P::eval(p, row, o);
+    const bool ok = kept && (!CHECK_CAP || idx < cap_left);
+    if (HAS_SEL) qe_stg_if(ok, selp + idx, row_id);
+    P::emit_ptr(ptrs, idx, o, ok);
+    if (P::NBITCOLS > 0 && (!CHECK_CAP || off < cap_left)) {
+        const qe_u32 rk[1] = {idx - off};
 #pragma unroll
-    for (int s = 0; s < STEPS; s++) mk[s] = masks[s];
+        for (int b = 0; b < P::NBITCOLS; b++) {
+            qe_u32 *bm = P::bitcol(p, b);
+            if (bm) qe_store_bits_compact<1>(bm, wbase + off, rk, kept ? 1u : 0u, P::bit(o, b) ? 1u : 0u);
+        }
+    }
+    off += __popc(m);
+}
+
+template <class P, int STEPS, bool CHECK_CAP, bool HAS_SEL>
+__device__ __forceinline__ void qe_ring_scatter(const QeParams &p, const unsigned char *stage, int wrow0, qe_u32 first_row,
+                                                qe_u64 wbase, const qe_u32 *masks, qe_u32 cnt)
+{
+    const qe_u32 lane = qe_lane();
+    const typename P::Ptrs ptrs = P::out_ptrs(p, wbase);
+    qe_u32 *const selp = HAS_SEL ? qe_opaque_ptr(p.sel + wbase) : (qe_u32 *)0;
+    qe_u32 cap_left = 0xffffffffu;                            // outputs of this warp that still fit (CHECK_CAP only)
+    if (CHECK_CAP) {
+        const qe_u64 cap = (qe_u64)p.out_capacity;
+        cap_left = wbase >= cap ? 0u : (cap - wbase > 0xffffffffull ? 0xffffffffu : (qe_u32)(cap - wbase));
+    }
     qe_u32 off = 0;                                           // kept rows of this warp in earlier steps
+    if (cnt * 4u >= (qe_u32)(STEPS * 32)) {
+        qe_u32 mk[STEPS];
 #pragma unroll
-    for (int s = 0; s < STEPS; s++) {
-        const qe_u32 m = mk[s];
-        if (m == 0u) continue;                                // warp-uniform
-        const bool kept = (m >> lane) & 1u;
-        const qe_u32 idx = off + __popc(m & lt);
-        typename P::Row row;
-        typename P::Out o;
-        if (P::NBITCOLS > 0 || kept) {
-            P::load_row(stage, wrow0, s * 32, row);
-            (void)P::eval(p, row, o);
-        }
-        if (kept && (!CHECK_CAP || wbase + idx < (qe_u64)p.out_capacity)) {
-            if (HAS_SEL) (p.sel + wbase)[idx] = first_row + (qe_u32)(s * 32);
-            P::emit_at(p, wbase, idx, o);
-        }
-        if (P::NBITCOLS > 0 && (!CHECK_CAP || wbase + off < (qe_u64)p.out_capacity)) {
-            const qe_u32 rk[1] = {idx - off};
+        for (int s = 0; s < STEPS; s++) mk[s] = masks[s];
 #pragma unroll
-            for (int b = 0; b < P::NBITCOLS; b++) {
-                qe_u32 *bm = P::bitcol(p, b);
-                if (bm) qe_store_bits_compact<1>(bm, wbase + off, rk, kept ? 1u : 0u, P::bit(o, b) ? 1u : 0u);
-            }
+        for (int s = 0; s < STEPS; s++)
+            qe_ring_scatter_step<P, CHECK_CAP, HAS_SEL>(p, ptrs, selp, stage, wrow0, s * 32, first_row + (qe_u32)(s * 32), wbase,
+                                                        cap_left, mk[s], off);
+    } else {
+        const qe_u32 mine = lane < (qe_u32)STEPS ? masks[lane] : 0u;
+        qe_u32 act = __ballot_sync(QE_FULL_MASK, mine != 0u);
+        while (act) {
+            const int s = __ffs((int)act) - 1;
+            act &= act - 1u;
+            const qe_u32 m = __shfl_sync(QE_FULL_MASK, mine, s);
+            qe_ring_scatter_step<P, CHECK_CAP, HAS_SEL>(p, ptrs, selp, stage, wrow0, s * 32, first_row + (qe_u32)(s * 32), wbase,
+                                                        cap_left, m, off);
         }
-        off += __popc(m);
     }
 }
 
@@ -1118,21 +1171,31 @@ __device__ __forceinline__ void qe_prefetch_l2_keep(const void *p)
     asm volatile("prefetch.global.L2::evict_last [%0];" :: "l"(p));
 }
 
-#define QE_RING_AUX_WARPS 3          // producer, publisher, look-back
 #define QE_RING_LB_PER_LANE 6        // descriptors per lane per look-back round trip (192 per warp)
+
+// phase timing of the ring kernel (QE_DEBUG_FLAGS & 16; tools/phase_timing.py): cycles per CTA in p.debug[cta][16]
+//  0 producer: wait empty   1 producer: wait load throttle   2 producer: tiles
+//  3 look-back warp 0: wait eval   4 first descriptor read   5 re-poll cycles   6 re-polls   7 wait previous prefix   8 gap length
+//  9 consumer warp 0: wait full   10 phase A   11 wait prefix   12 phase C   14 look-back warp 0: first reads that came too early
+#define QE_RT_BEGIN() qe_u64 rt_t0_ = (QE_DEBUG_FLAGS & 16) ? clock64() : 0
+#define QE_RT_ADD(i) do { if (QE_DEBUG_FLAGS & 16) { const qe_u64 n_ = clock64(); rt_acc[i] += n_ - rt_t0_; rt_t0_ = n_; } } while (0)
+#define QE_RT_RESET() do { if (QE_DEBUG_FLAGS & 16) rt_t0_ = clock64(); } while (0)
+#define QE_RT_FLUSH(lo, hi) do { if ((QE_DEBUG_FLAGS & 16) && lane == 0 && blockIdx.x < 2048) { \
+        for (int i_ = (lo); i_ <= (hi); i_++) p.debug[blockIdx.x * 16 + i_] = rt_acc[i_]; } } while (0)
 
 template <class P>
 __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
 {
-    constexpr int NST = P::NSTAGES, NCW = P::NCW, TILE = P::TILE_ROWS, DEFER = P::DEFER;
+    constexpr int NST = P::NSTAGES, NCW = P::NCW, TILE = P::TILE_ROWS, DEFER = P::DEFER, NLB = P::NLB;
     constexpr int WROWS = TILE / NCW, STEPS = WROWS / 32;
-    static_assert(WROWS % 32 == 0 && NCW <= 32 && DEFER >= 1 && DEFER < NST, "ring shape");
+    static_assert(WROWS % 32 == 0 && NCW <= 32 && DEFER >= 1 && DEFER < NST && NLB >= 1 && NLB <= NST, "ring shape");
 
     extern __shared__ __align__(128) unsigned char qe_dyn_smem[];
     __shared__ __align__(8) qe_u64 s_full[NST], s_claim[NST], s_eval[NST], s_pref[NST], s_empty[NST];
-    __shared__ qe_u64 s_excl[NST];
-    __shared__ qe_u32 s_tile[NST];
-    __shared__ qe_u32 s_total[NST];
+    __shared__ qe_u64 s_incl[NST];
+    __shared__ qe_u64 s_wbase[NST][NCW];                      // output position of each consumer warp's first kept row
+    __shared__ qe_u32 s_tile[NST], s_lo[NST], s_row0[NST];
+    __shared__ qe_u32 s_fits[NST];
     __shared__ __align__(16) qe_u32 s_cnt[NST][NCW];
     __shared__ __align__(16) qe_u32 s_mask[NST][TILE / 32];
 
@@ -1157,20 +1220,33 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
         if (lane == 0) {
             const qe_u64 policy = qe_policy_evict_first();
             qe_u32 t = atomicAdd(p.ticket, 1u);
+            qe_u32 lo = 0, ended = 0;
+            qe_u64 rt_acc[16] = {};
+            QE_RT_BEGIN();
             for (qe_u32 it = 0;; it++) {
                 const int st = (int)(it % NST);
+                QE_RT_RESET();
                 if (it >= NST) qe_mbar_wait(qe_smem_addr(&s_empty[st]), ((it / NST) - 1u) & 1u);
+                QE_RT_ADD(0);
                 // at most LOADS tiles in flight: more only queue up in the memory system, and every
                 // descriptor read of the look-back then waits behind them
-                if (P::LOADS > 0 && it >= (qe_u32)P::LOADS) {
+                if (P::LOADS > 0 && it >= (qe_u32)P::LOADS && ended == 0u) {
                     const qe_u32 jt = it - (qe_u32)P::LOADS;
                     qe_mbar_wait(qe_smem_addr(&s_full[jt % NST]), (jt / NST) & 1u);
                 }
+                QE_RT_ADD(1);
+                rt_acc[2] += 1;
                 s_tile[st] = t;
+                s_lo[st] = lo;                                // tiles [lo, t) belong to other CTAs
+                s_row0[st] = p.sel_base + t * (qe_u32)TILE;    // selection-vector value of the tile's first row
+                lo = t + 1u;
                 qe_mbar_arrive(qe_smem_addr(&s_claim[st]));
-                if (t >= p.ntiles) {                          // end marker: wakes the consumers, carries no bytes
-                    qe_mbar_arrive(qe_smem_addr(&s_full[st]));
-                    break;
+                if (t >= p.ntiles) {
+                    // end marker: wakes the consumers (first one only), carries no bytes; every look-back
+                    // warp must meet one on its own round-robin slot, so NLB of them are written
+                    if (ended == 0u) qe_mbar_arrive(qe_smem_addr(&s_full[st]));
+                    if (++ended == (qe_u32)NLB) { QE_RT_FLUSH(0, 2); break; }
+                    continue;
                 }
                 // the tile's descriptor line should be in L2 when it is published and read, NST tiles from now
                 if (!(QE_DEBUG_FLAGS & 32)) qe_prefetch_l2_keep(desc + t);
@@ -1196,23 +1272,31 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                 qe_mbar_arrive(qe_smem_addr(&s_empty[st]));
             }
         }
-    } else if (warp == 2) {
+    } else if (warp < 2u + (qe_u32)NLB) {
         // ----------------------------------------------------------- look-back
-        qe_u64 run = 0;                                       // kept rows in tiles [0, lo)
-        qe_u32 lo = 0;
-        for (qe_u32 it = 0;; it++) {
+        // NLB warps take this CTA's tiles round robin.  A prefix costs one L2 round trip after the
+        // tile's count is visible grid-wide (~1.4 us under streaming load, measured), a 16-32 KB tile
+        // streams in 0.4-0.7 us, so several must be in flight; the gap sums are independent, only the
+        // final add chains through shared memory (s_incl of the previous tile).
+        qe_u64 rt_acc[16] = {};
+        QE_RT_BEGIN();
+        for (qe_u32 it = warp - 2u;; it += (qe_u32)NLB) {
             const int st = (int)(it % NST);
             const qe_u32 par = (it / NST) & 1u;
             qe_mbar_wait(qe_smem_addr(&s_claim[st]), par);
             const qe_u32 t = s_tile[st];
-            if (t >= p.ntiles) break;
+            if (t >= p.ntiles) { if (warp == 2) { QE_RT_FLUSH(3, 8); QE_RT_FLUSH(14, 14); } break; }
+            const qe_u32 lo = s_lo[st];
+            QE_RT_RESET();
             // Wait for this CTA's own count first: the grid moves in step, so by then the tiles of the
             // other CTAs in the gap are counted (or about to be) and the descriptors are read once
             // instead of being polled for a whole tile time (148 warps polling five cache lines slowed
             // the very stores they were waiting for: measured 5-12 us per prefix).
             qe_mbar_wait(qe_smem_addr(&s_eval[st]), par);
-            qe_u32 c = lane < (qe_u32)NCW ? s_cnt[st][lane] : 0u;
-            c = __reduce_add_sync(QE_FULL_MASK, c);
+            QE_RT_ADD(3);
+            rt_acc[8] += t - lo;
+            const qe_u32 mine = lane < (qe_u32)NCW ? s_cnt[st][lane] : 0u;
+            const qe_u32 c = __reduce_add_sync(QE_FULL_MASK, mine);
             // the gap [lo, t): tiles of other CTAs claimed between this CTA's previous tile and this one
             qe_u32 gap = 0;
             for (qe_u32 base = lo; base < t; base += 32u * QE_RING_LB_PER_LANE) {
@@ -1222,38 +1306,72 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                     const qe_u32 idx = base + (qe_u32)k * 32u + lane;
                     d[k] = idx < t ? qe_ld_relaxed_u32(desc + idx) : 1u;
                 }
+                if (QE_DEBUG_FLAGS & 16) {                        // time of the first read = one L2 round trip
+                    bool inval = false;
 #pragma unroll
-                for (int k = 0; k < QE_RING_LB_PER_LANE; k++) {
-                    const qe_u32 idx = base + (qe_u32)k * 32u + lane;
-                    while (d[k] == 0u) {
-                        __nanosleep(64);
-                        d[k] = qe_ld_relaxed_u32(desc + idx);
-                    }
-                    gap += d[k] - 1u;
+                    for (int k = 0; k < QE_RING_LB_PER_LANE; k++) inval |= d[k] == 0u;
+                    if (__any_sync(QE_FULL_MASK, inval)) rt_acc[14] += 1;      // first read came too early
+                    QE_RT_ADD(4);
                 }
+                // Re-read what was not published yet: every missing descriptor again in one go, the warp
+                // stays converged.  No __nanosleep here: on B200 the shortest sleep measured ~1 us (ncu:
+                // two sleeps per tile = the whole 2.3 us tile time), a re-read is its own ~0.5 us back-off.
+                for (;;) {
+                    bool pending = false;
+#pragma unroll
+                    for (int k = 0; k < QE_RING_LB_PER_LANE; k++) pending |= d[k] == 0u;
+                    if (!__any_sync(QE_FULL_MASK, pending)) break;
+                    if (QE_DEBUG_FLAGS & 16) rt_acc[6] += 1;
+#pragma unroll
+                    for (int k = 0; k < QE_RING_LB_PER_LANE; k++) {
+                        const qe_u32 idx = base + (qe_u32)k * 32u + lane;
+                        if (d[k] == 0u) d[k] = qe_ld_relaxed_u32(desc + idx);
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < QE_RING_LB_PER_LANE; k++) gap += d[k] - 1u;
+                QE_RT_ADD(5);
             }
             gap = __reduce_add_sync(QE_FULL_MASK, gap);
-            const qe_u64 excl = run + gap;
+            qe_u64 before = 0;                                // kept rows up to and including this CTA's previous tile
+            if (it > 0) {
+                const qe_u32 jt = it - 1u;
+                qe_mbar_wait(qe_smem_addr(&s_pref[jt % NST]), (jt / NST) & 1u);
+                before = s_incl[jt % NST];
+            }
+            QE_RT_ADD(7);
+            const qe_u64 excl = before + gap;
+            // exclusive scan of the per-warp counts: every consumer warp gets its own base
+            qe_u32 wofs = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const qe_u32 v = __shfl_up_sync(QE_FULL_MASK, wofs, o);
+                if (lane >= (qe_u32)o) wofs += v;
+            }
+            if (lane < (qe_u32)NCW) s_wbase[st][lane] = excl + (wofs - mine);
+            __syncwarp();
             if (lane == 0) {
-                s_excl[st] = excl;
-                s_total[st] = c;
+                s_fits[st] = excl + c <= (qe_u64)p.out_capacity ? 1u : 0u;
+                s_incl[st] = excl + c;
                 qe_mbar_arrive(qe_smem_addr(&s_pref[st]));
                 qe_mbar_arrive(qe_smem_addr(&s_empty[st]));
+                if (t == p.ntiles - 1u) *p.out_count = excl + c;
             }
-            run = excl + c;
-            lo = t + 1u;
-            if (lane == 0 && t == p.ntiles - 1u) *p.out_count = run;
         }
     } else {
         // ----------------------------------------------------------- consumers
-        const int cw = (int)warp - QE_RING_AUX_WARPS;
+        const int cw = (int)warp - (2 + NLB);
         const int wrow0 = cw * WROWS;                         // this warp's slice of every tile
         int n_valid = 0x7fffffff;                             // iterations that carry a tile (known once the end marker is seen)
+        qe_u64 rt_acc[16] = {};
+        QE_RT_BEGIN();
         for (int it = 0;; it++) {
             if (it < n_valid) {
                 // ---- phase A: evaluate the filter, leave keep masks and counts in shared memory
                 const int st = it % NST;
+                QE_RT_RESET();
                 qe_mbar_wait(qe_smem_addr(&s_full[st]), (qe_u32)(it / NST) & 1u);
+                QE_RT_ADD(9);
                 const qe_u32 t = s_tile[st];
                 if (t >= p.ntiles) {
                     n_valid = it;
@@ -1289,33 +1407,35 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                         qe_mbar_arrive(qe_smem_addr(&s_eval[st]));
                     }
                     __syncwarp();
+                    QE_RT_ADD(10);
                 }
             }
             const int j = it - DEFER;
             if (j >= 0 && j < n_valid) {
                 // ---- phase C: ordered scatter of tile j, whose prefix has had DEFER tile times to arrive
                 const int st = j % NST;
+                QE_RT_RESET();
                 qe_mbar_wait(qe_smem_addr(&s_pref[st]), (qe_u32)(j / NST) & 1u);   // pref follows eval
+                QE_RT_ADD(11);
                 const unsigned char *stage = qe_dyn_smem + (size_t)st * P::STAGE_BYTES;
-                const qe_u32 first_row = p.sel_base + (qe_u32)((qe_i64)s_tile[st] * TILE) + (qe_u32)wrow0 + lane;
-                const qe_u64 excl = s_excl[st];
-                qe_u32 woff = 0;
-#pragma unroll
-                for (int w = 0; w < NCW; w++) woff += w < cw ? s_cnt[st][w] : 0u;
-                const qe_u64 wbase = excl + woff;             // output position of this warp's first kept row
-                const bool fits = excl + s_total[st] <= (qe_u64)p.out_capacity;
+                const qe_u32 first_row = s_row0[st] + (qe_u32)wrow0 + lane;
+                const qe_u64 wbase = s_wbase[st][cw];         // output position of this warp's first kept row
+                const qe_u32 cnt = s_cnt[st][cw];
                 const qe_u32 *mk = &s_mask[st][cw * STEPS];
-                if (fits) {
-                    if (p.sel) qe_ring_scatter<P, STEPS, false, true>(p, stage, wrow0, first_row, wbase, mk);
-                    else qe_ring_scatter<P, STEPS, false, false>(p, stage, wrow0, first_row, wbase, mk);
-                } else {
-                    if (p.sel) qe_ring_scatter<P, STEPS, true, true>(p, stage, wrow0, first_row, wbase, mk);
-                    else qe_ring_scatter<P, STEPS, true, false>(p, stage, wrow0, first_row, wbase, mk);
+                if (cnt != 0u) {
+                    if (s_fits[st]) {
+                        if (p.sel) qe_ring_scatter<P, STEPS, false, true>(p, stage, wrow0, first_row, wbase, mk, cnt);
+                        else qe_ring_scatter<P, STEPS, false, false>(p, stage, wrow0, first_row, wbase, mk, cnt);
+                    } else {
+                        if (p.sel) qe_ring_scatter<P, STEPS, true, true>(p, stage, wrow0, first_row, wbase, mk, cnt);
+                        else qe_ring_scatter<P, STEPS, true, false>(p, stage, wrow0, first_row, wbase, mk, cnt);
+                    }
                 }
                 __syncwarp();
+                QE_RT_ADD(12);
                 if (lane == 0) qe_mbar_arrive(qe_smem_addr(&s_empty[st]));
             }
-            if (n_valid != 0x7fffffff && j + 1 >= n_valid) break;
+            if (n_valid != 0x7fffffff && j + 1 >= n_valid) { if (cw == 0) QE_RT_FLUSH(9, 12); break; }
         }
     }
 }

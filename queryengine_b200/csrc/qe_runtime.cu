@@ -134,7 +134,7 @@ struct qe_ctx {
     std::unordered_map<std::string, JitEntry> jit_cache;
     // options
     int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = -1, opt_stages = 0, opt_debug_flags = 0, opt_pipeline = 1;
-    int64_t opt_loads = 0, opt_tile_rows = 0, opt_ncw = 0, opt_defer = 0, opt_stage_kb = 0;
+    int64_t opt_nlb = 0, opt_loads = 0, opt_tile_rows = 0, opt_ncw = 0, opt_defer = 0, opt_stage_kb = 0;
     int64_t launches = 0;
     bool warned_no_nvrtc = false;
     // pinned staging ring for uploads from pageable memory
@@ -265,8 +265,11 @@ extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
             return fail(QE_ERR_INVALID_ARGUMENT, "ncw must be 0 (auto), 4, 8, 12, 16, 20 or 24");
         ctx->opt_ncw = value;
     } else if (k == "defer") {
-        if (value < 0 || value > 6) return fail(QE_ERR_INVALID_ARGUMENT, "defer must be in [0, 6] (0 = auto)");
+        if (value < 0 || value > 30) return fail(QE_ERR_INVALID_ARGUMENT, "defer must be in [0, 30] (0 = auto)");
         ctx->opt_defer = value;
+    } else if (k == "nlb") {
+        if (value < 0 || value > 8) return fail(QE_ERR_INVALID_ARGUMENT, "nlb must be in [0, 8] (0 = auto)");
+        ctx->opt_nlb = value;
     } else if (k == "loads") {
         if (value < 0 || value > 32) return fail(QE_ERR_INVALID_ARGUMENT, "loads must be in [0, 32] (0 = no limit)");
         ctx->opt_loads = value;
@@ -620,9 +623,10 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         size_t n = ctx->opt_stages ? (size_t)ctx->opt_stages : 16;
         while (n > 2 && n * (stage + meta) > (224u << 10)) n--;
         s.nstages = (int)n;
-        s.defer = ctx->opt_defer ? (int)ctx->opt_defer : 2;
+        s.defer = ctx->opt_defer ? (int)ctx->opt_defer : 3;
         if (s.defer >= s.nstages) s.defer = s.nstages - 1;
         s.loads = (int)ctx->opt_loads;
+        s.nlb = std::min(ctx->opt_nlb ? (int)ctx->opt_nlb : 1, s.nstages);   // the end markers need a stage each
         if (n * (stage + meta) > (224u << 10) || s.defer < 1) s.ring = false;   // a single tile does not fit: register-sourced kernel
     }
     return s;
@@ -664,9 +668,9 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
                           JitEntry **out)
 {
     char suffix[128];
-    snprintf(suffix, sizeof suffix, "|M%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d", (int)mode, shape.steps, shape.vec, shape.staged ? 1 : 0,
+    snprintf(suffix, sizeof suffix, "|M%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d.%d", (int)mode, shape.steps, shape.vec, shape.staged ? 1 : 0,
              shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0, shape.ring ? 1 : 0, shape.tile_rows, shape.ncw,
-             shape.defer, shape.loads);
+             shape.defer, shape.loads, shape.nlb);
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) { *out = &it->second; return QE_OK; }

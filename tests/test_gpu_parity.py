@@ -174,13 +174,13 @@ def test_every_tile_shape(ctx, steps, vec, staging):
     c.close()
 
 
-@pytest.mark.parametrize("stage_kb,ncw,defer,stages", [(0, 0, 0, 0), (4, 4, 1, 2), (8, 8, 1, 3), (16, 16, 3, 5), (48, 8, 2, 4),
-                                                       (2, 12, 2, 16)])
-def test_every_ring_shape(ctx, stage_kb, ncw, defer, stages):
+@pytest.mark.parametrize("stage_kb,ncw,defer,stages,nlb", [(0, 0, 0, 0, 0), (4, 4, 1, 2, 1), (8, 8, 1, 3, 3), (16, 16, 3, 5, 2),
+                                                           (48, 8, 2, 4, 4), (2, 12, 9, 16, 8)])
+def test_every_ring_shape(ctx, stage_kb, ncw, defer, stages, nlb):
     """The warp-specialised ring variant of the filter kernel (the default) over its option space."""
     c = Context(0)
     c.set_option("staging", 2)
-    for k, v in (("stage_kb", stage_kb), ("ncw", ncw), ("defer", defer), ("stages", stages)):
+    for k, v in (("stage_kb", stage_kb), ("ncw", ncw), ("defer", defer), ("stages", stages), ("nlb", nlb)):
         c.set_option(k, v)
     rng = np.random.default_rng(stage_kb * 100 + ncw)
     for n in (0, 1, 127, 128, 129, 4095, 4096, 4097, 100003, 1_000_003):
