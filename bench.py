@@ -91,7 +91,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(0.05)
+            self._stop.wait(0.004)
 
     def __enter__(self):
         if self.nv:
@@ -152,7 +152,7 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(np.mean(times)) * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
         "config": workload_config(args.rows, args.gpus),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": f"{sample} rows of the same column, three-filter sweep per step; "
@@ -233,7 +233,7 @@ def timed_steps(torch, ctx, stream, fn_step, steps, dist, device):
     return ms
 
 
-def q6_pipeline(ctx, rows):
+def q6_pipeline(ctx, rows, row_offset=0):
     """BASELINE.json configs[2]: Q6-shaped filter + SUM(extendedprice * discount), four f64 columns."""
     from queryengine_b200 import capi
     from queryengine_b200.ast import AggregationFunction, DataType, Function, col, fn
@@ -241,10 +241,10 @@ def q6_pipeline(ctx, rows):
     D = DataType.DOUBLE
     t = ColumnarTable(ctx, [Field("l_quantity", D), Field("l_extendedprice", D), Field("l_discount", D),
                             Field("l_shipdate", D)], rows)
-    t.generate(0, capi.QE_GEN_UNIFORM_INT, SEED + 1, 1, 50)
-    t.generate(1, capi.QE_GEN_CENTS, SEED + 2, 90000, 10499999)
-    t.generate(2, capi.QE_GEN_CENTS, SEED + 3, 0, 10)
-    t.generate(3, capi.QE_GEN_UNIFORM_INT, SEED + 4, 8036, 10561)
+    t.generate(0, capi.QE_GEN_UNIFORM_INT, SEED + 1, 1, 50, row_offset=row_offset)
+    t.generate(1, capi.QE_GEN_CENTS, SEED + 2, 90000, 10499999, row_offset=row_offset)
+    t.generate(2, capi.QE_GEN_CENTS, SEED + 3, 0, 10, row_offset=row_offset)
+    t.generate(3, capi.QE_GEN_UNIFORM_INT, SEED + 4, 8036, 10561, row_offset=row_offset)
     filt = fn(Function.AND, fn(Function.AND, fn(Function.AND, fn(Function.AND,
               fn(Function.CMP_GE, col(3), 8766.0), fn(Function.CMP_LT, col(3), 9131.0)),
               fn(Function.CMP_GE, col(2), 0.05)), fn(Function.CMP_LE, col(2), 0.07)), fn(Function.CMP_LT, col(0), 24.0))
@@ -394,7 +394,7 @@ def run_ours(args):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic", "config": workload_config(rows, world),
+        "dtype": "int64", "data": "synthetic", "config": workload_config(rows, world),
         "roofline": roofline, "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches),
         "hbm_gb_per_s_aggregate": world * len(SELECTIVITIES) * args.steps * (tot_bytes / len(SELECTIVITIES)) / (ms * 1e-3) / 1e9,
     }
@@ -409,6 +409,29 @@ def run_ours(args):
                 extra[name] = fn_(ctx, torch, stream, n, max(3, args.steps), 3, peak)
             except Exception as e:  # reported, never hidden
                 extra[name] = {"error": repr(e)}
+    if world > 1 and not args.no_extra:
+        # Q6 over SF100 lineitem row-sharded across the ranks: per-rank partial, NCCL all-gather of the partials,
+        # rank-order combine (queryengine_b200/sharding.py) -- the only collective on the path
+        from queryengine_b200 import sharding
+        from queryengine_b200.ast import AggregationFunction
+        lo, hi = sharding.partition(args.q6_rows, world, rank)
+        t6, pipe6 = q6_pipeline(ctx, hi - lo, row_offset=lo)
+        res6 = pipe6.run()
+        for _ in range(3):
+            pipe6.run(res6)
+        m0, n0 = res6.kernel_stats()
+        for _ in range(max(3, args.steps)):
+            pipe6.run(res6)
+        m1, n1 = res6.kernel_stats()
+        total = sharding.sharded_aggregate(res6, [AggregationFunction.SUM], device=device)
+        kms = torch.tensor([(m1 - m0) / max(1, n1 - n0)], dtype=torch.float64, device=device)
+        dist.all_reduce(kms, op=dist.ReduceOp.MAX)
+        extra["q6_sf100_sharded"] = {"rows": args.q6_rows, "partitions": world, "kernel_ms_max_over_ranks": float(kms.item()),
+                                     "rows_per_s": args.q6_rows / (float(kms.item()) * 1e-3),
+                                     "gb_per_s_aggregate": args.q6_rows * 32 / (float(kms.item()) * 1e-3) / 1e9,
+                                     "sum": total[0], "combine": "NCCL all_gather of partials + qe_agg_combine in rank order"}
+        res6.close()
+        t6.close()
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
         v, secs, ckept = cpu_leg(args.cpu_rows, threads)

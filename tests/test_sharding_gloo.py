@@ -1,0 +1,153 @@
+"""Multi-partition host logic (queryengine_b200/sharding.py) on CPU: world_size 2 over gloo.
+
+The per-partition pipeline results are produced by the oracle here (no GPU in this suite); what is under
+test is the partitioning, the all-gather of partial aggregates, the rank-order combine through the C ABI
+(qe_agg_combine needs no device) and the selection-vector rebasing.
+"""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from queryengine_b200 import capi, sharding  # noqa: E402
+from queryengine_b200.ast import AggregationFunction as A, DataType, Function, col, fn  # noqa: E402
+
+D = DataType.DOUBLE
+N = 100_003
+FNS = [A.SUM, A.COUNT, A.MIN, A.MAX, A.AVG]
+
+
+def _table(n=N):
+    rng = np.random.default_rng(7)
+    a = np.round(rng.uniform(-1000, 1000, n), 2)
+    b = rng.integers(0, 11, n).astype(np.float64) / 100.0
+    vb = rng.random(n) > 0.1                       # 10 % nulls in b
+    return a, b, vb
+
+
+def _filter():
+    return fn(Function.AND, fn(Function.CMP_GE, col(0), -250.0), fn(Function.CMP_LT, col(1), 0.07))
+
+
+def _proj():
+    return fn(Function.MUL, col(0), fn(Function.SUB, 1.0, col(1)))
+
+
+def _oracle_rows(a, b, vb, aggregates=None):
+    from oracle_binding import OraclePlan, OracleTable
+    t = OracleTable([D, D], len(a))
+    t.set_column(0, a)
+    t.set_column(1, b, np.packbits(np.asarray(vb, dtype=np.uint8), bitorder="little"))
+    nproj = len(aggregates) if aggregates else 1          # accumulator k consumes projection k
+    return t, OraclePlan(t, [0, 1], _filter(), [_proj()] * nproj, aggregates)
+
+
+def _partial_of_shard(a, b, vb):
+    """What qe_result_agg_partial returns for one partition, computed with the oracle's per-row outputs."""
+    t, plan = _oracle_rows(a, b, vb)
+    n, vals, valid = plan.columns()
+    v = vals[0][valid[0]]
+    s = 0.0
+    for x in v:                                    # sequential, like SumAccumulator (Accumulators.kt:44)
+        s += float(x)
+    if v.size == 0:
+        return capi.AggPartial(0.0, 0, float("inf"), float("-inf"))
+    return capi.AggPartial(s, int(v.size), float(v.min()), float(v.max()))
+
+
+def test_partition_covers_rows_once_and_is_aligned():
+    for n in (0, 1, 127, 128, 129, 1000, N, 6_000_000_000):
+        for world in (1, 2, 3, 4, 8):
+            parts = sharding.partitions(n, world)
+            assert parts[0][0] == 0 and parts[-1][1] == n
+            for (b0, e0), (b1, e1) in zip(parts, parts[1:]):
+                assert e0 == b1 and b0 <= e0
+            assert all(b % sharding.ALIGN == 0 or b == n for b, _ in parts)
+            sizes = [e - b for b, e in parts]
+            assert max(sizes) <= -(-n // world) + sharding.ALIGN
+
+
+def test_single_process_combine_matches_global_oracle():
+    a, b, vb = _table()
+    parts = sharding.partitions(N, 4)
+    by_rank = [[_partial_of_shard(a[lo:hi], b[lo:hi], vb[lo:hi])] * len(FNS) for lo, hi in parts]
+    got = sharding.combine(FNS, by_rank)
+    _, plan = _oracle_rows(a, b, vb, FNS)
+    want = plan.rows()[0]
+    assert got[1] == want[1] and got[2] == want[2] and got[3] == want[3]
+    assert abs(got[0] - want[0]) <= 1e-9 * abs(want[0]) and abs(got[4] - want[4]) <= 1e-9 * abs(want[4])
+    # empty partitions are skipped, an all-empty input is NULL (COUNT is 0)
+    empty = capi.AggPartial(0.0, 0, float("inf"), float("-inf"))
+    assert sharding.combine([A.SUM, A.COUNT, A.MIN], [[empty] * 3, [empty] * 3]) == [None, 0.0, None]
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    try:
+        import torch.distributed as dist
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        a, b, vb = _table()
+        lo, hi = sharding.partition(N, world, rank)
+        mine = [_partial_of_shard(a[lo:hi], b[lo:hi], vb[lo:hi])] * len(FNS)
+        by_rank = sharding.all_gather_partials(mine)
+        got = sharding.combine(FNS, by_rank)
+        # selection vectors: partition-relative + base, concatenated in rank order
+        keep = (a[lo:hi] >= -250.0) & (b[lo:hi] < 0.07) & vb[lo:hi]
+        local = np.nonzero(keep)[0].astype(np.uint32)
+        import torch
+        g = sharding.global_selection(local, lo)
+        sizes = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
+        dist.all_gather(sizes, torch.tensor([g.size], dtype=torch.int64))
+        q.put((rank, got, [int(s.item()) for s in sizes], int(g[0]) if g.size else -1, int(g[-1]) if g.size else -1,
+               [(p.count, p.sum) for p in (r[0] for r in by_rank)]))
+        dist.destroy_process_group()
+    except Exception as e:            # surfaced by the parent
+        q.put((rank, repr(e)))
+
+
+@pytest.mark.timeout(300)
+def test_world_size_2_gloo_all_gather_and_combine():
+    import torch.multiprocessing as mp
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in range(world)]
+    for p in procs:
+        p.join(60)
+    res.sort(key=lambda r: r[0])
+    for r in res:
+        assert len(r) > 2, r
+    a, b, vb = _table()
+    _, plan = _oracle_rows(a, b, vb, FNS)
+    want = plan.rows()[0]
+    for rank, got, sizes, first, last, seen in res:
+        assert got == res[0][1]                                   # every rank derives the same result, bit for bit
+        assert got[1] == want[1] and got[2] == want[2] and got[3] == want[3]
+        assert abs(got[0] - want[0]) <= 1e-9 * abs(want[0])
+        assert sum(sizes) == int(np.count_nonzero((a >= -250.0) & (b < 0.07) & vb))
+        assert seen == res[0][5]                                  # gathered in rank order on every rank
+    keep = (a >= -250.0) & (b < 0.07) & vb
+    sel = np.nonzero(keep)[0]
+    lo1, _ = sharding.partition(N, 2, 1)
+    assert res[0][3] == sel[0] and res[1][4] == sel[-1]
+    assert res[1][3] == sel[sel >= lo1][0]
+    assert sum(res[0][2]) == sel.size
