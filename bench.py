@@ -389,7 +389,7 @@ def run_ours(args):
                 "avg_launch_ms": tot_ms / len(SELECTIVITIES), "per_selectivity": per_sel}
 
     # ---- end to end through the C ABI with host buffers: upload -> filter -> download, every pass
-    e2e = run_e2e(args, torch, ctx, dist, device, rows, world, rank)
+    e2e = run_e2e(args, torch, ctx, dist, device, rows, world, rank, kept)
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
@@ -450,19 +450,26 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def run_e2e(args, torch, ctx, dist, device, rows, world, rank):
+def run_e2e(args, torch, ctx, dist, device, rows, world, rank, kept_full):
+    """The same three-filter sweep through the C ABI with HOST buffers: one qe_pipeline_stream call per step
+    takes the column from pinned host memory (uploaded once per step, in chunks), runs the three filters
+    chunk by chunk and lands every selection vector and compacted column in pinned host memory; uploads,
+    kernels and downloads of neighbouring chunks overlap."""
     from queryengine_b200 import capi
     from queryengine_b200.ast import DataType, col
-    from queryengine_b200.engine import ColumnarTable, Field, Pipeline
+    from queryengine_b200.engine import ColumnarTable, Field, Pipeline, stream_pipelines
     I64 = DataType.INT64
     e2e_rows = min(rows, args.e2e_rows) if args.e2e_rows else rows
-    budget = int(host_memory_available() * 0.5) // max(1, world if world <= 8 else 8)
-    e2e_rows = max(1 << 20, min(e2e_rows, budget // 20 // (1 << 20) * (1 << 20)))
+    frac = sum(k / rows for k in kept_full)                           # kept rows per input row over the sweep
+    bytes_per_row = 8 + 12 * frac * 1.02 + 1
+    budget = int(host_memory_available() * 0.6) // max(1, min(world, 8))
+    e2e_rows = max(1 << 20, min(e2e_rows, int(budget / bytes_per_row) // (1 << 20) * (1 << 20)))
+    caps = [int(k / rows * e2e_rows * 1.02) + 4096 for k in kept_full]
     bufs = []
     try:
         h_in = PinnedBuffer(e2e_rows * 8); bufs.append(h_in)
-        h_sel = PinnedBuffer(e2e_rows * 4); bufs.append(h_sel)
-        h_val = PinnedBuffer(e2e_rows * 8); bufs.append(h_val)
+        h_sel = [PinnedBuffer(c * 4) for c in caps]; bufs += h_sel
+        h_val = [PinnedBuffer(c * 8) for c in caps]; bufs += h_val
     except capi.QeError:
         for b in bufs:
             b.free()
@@ -474,34 +481,39 @@ def run_e2e(args, torch, ctx, dist, device, rows, world, rank):
     dense = Pipeline(t, None, [col(0, I64, "col")]).run()
     capi.check(capi.lib().qe_result_column(dense.handle, 0, h_in.ptr, None))
     dense.close()
-    pipes = [Pipeline(t, filter_expr(s), [col(0, I64, "col")]) for s in SELECTIVITIES]
+    pipes = [Pipeline(t, filter_expr(s), [col(0, I64, "col")], out_capacity_rows=c) for s, c in zip(SELECTIVITIES, caps)]
     results = [None] * len(pipes)
     kept = [0] * len(pipes)
 
-    def one_pass(i):
-        t.upload_raw(0, h_in.ptr.value, None, 0, e2e_rows)           # host -> HBM (pinned, async)
-        results[i] = pipes[i].run(results[i])
-        kept[i] = results[i].num_rows                                # waits for the kernel
-        capi.check(capi.lib().qe_result_selection(results[i].handle, h_sel.ptr))
-        capi.check(capi.lib().qe_result_column(results[i].handle, 0, h_val.ptr, None))
+    def one_step():
+        res = stream_pipelines(t, pipes, [h_in.ptr.value], chunk_rows=args.e2e_chunk_rows, results=results,
+                               host_selection=[b.ptr.value for b in h_sel],
+                               host_out_values=[[b.ptr.value] for b in h_val])
+        for i, r in enumerate(res):
+            results[i] = r
+            kept[i] = r.num_rows                                     # d2h read of the step's result sizes
 
-    for i in range(len(pipes)):
-        one_pass(i)                                                  # warm-up
+    one_step()                                                       # warm-up
     steps = max(1, min(args.steps, args.e2e_steps))
     if dist is not None:
         dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(steps):
-        for i in range(len(pipes)):
-            one_pass(i)
+        one_step()
     torch.cuda.synchronize()
     secs = time.perf_counter() - t0
     if dist is not None:
         tt = torch.tensor([secs], dtype=torch.float64, device=device)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         secs = float(tt.item())
-    h2d = len(pipes) * e2e_rows * 8
+    # spot check of what landed in host memory: first kept row of the 50 % filter
+    import ctypes as C
+    first_sel = C.cast(h_sel[1].ptr, C.POINTER(C.c_uint32))[0]
+    first_val = C.cast(h_val[1].ptr, C.POINTER(C.c_int64))[0]
+    src_val = C.cast(h_in.ptr, C.POINTER(C.c_int64))[first_sel]
+    assert first_val == src_val and first_val < int(0.5 * 2 ** 40), "streamed output does not match the host column"
+    h2d = e2e_rows * 8
     d2h = sum(k * 12 + 8 for k in kept)
     for r in results:
         r.close()
@@ -510,8 +522,10 @@ def run_e2e(args, torch, ctx, dist, device, rows, world, rank):
         b.free()
     return {"value": world * len(pipes) * e2e_rows * steps / secs, "unit": UNIT, "rows_per_gpu": e2e_rows, "steps": steps,
             "ms_per_step": secs / steps * 1e3, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-            "what": "per filter pass: qe_table_upload from pinned host memory, qe_pipeline_run, "
-                    "qe_result_selection + qe_result_column into pinned host memory"}
+            "chunk_rows": args.e2e_chunk_rows,
+            "what": "per step one qe_pipeline_stream call: the column is copied from pinned host memory once (in chunks), "
+                    "the three filters run chunk by chunk, selection vectors + compacted columns land in pinned host "
+                    "memory; uploads, kernels and downloads overlap on three streams"}
 
 
 def main():
@@ -524,6 +538,7 @@ def main():
     ap.add_argument("--cpu-rows", type=int, default=40_000_000, help="rows of the bounded CPU sample")
     ap.add_argument("--e2e-rows", type=int, default=0, help="rows per GPU for the end-to-end leg (0 = same as --rows)")
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-chunk-rows", type=int, default=1 << 25, help="rows per chunk of the streamed end-to-end leg")
     ap.add_argument("--q6-rows", type=int, default=600_037_902)
     ap.add_argument("--tree-rows", type=int, default=1_000_000_000)
     ap.add_argument("--no-extra", action="store_true")

@@ -118,13 +118,15 @@ typedef struct qe_pipeline_desc {
     int32_t nagg;                      /* 0, or == nproj */
     int64_t row_begin;                 /* batch = rows [row_begin, row_end); row_begin % 128 == 0 */
     int64_t row_end;                   /* -1 = to the end of the table */
-    int64_t out_capacity_rows;         /* rows the compacted outputs may hold; 0 = worst case (all rows) */
+    int64_t out_capacity_rows;         /* rows the outputs may hold; 0 = worst case (all rows of this batch) */
     uint32_t flags;                    /* QE_RUN_* */
 } qe_pipeline_desc;
 
 enum {
     QE_RUN_NO_SELECTION = 1u << 0,     /* do not materialise the selection vector */
-    QE_RUN_INTERPRETER  = 1u << 1      /* use the generic interpreter kernels instead of generated code */
+    QE_RUN_INTERPRETER  = 1u << 1,     /* use the generic interpreter kernels instead of generated code */
+    QE_RUN_APPEND       = 1u << 2      /* *result holds earlier batches of the same pipeline: append this batch's rows
+                                          (order preserved; capacity is the first run's out_capacity_rows) */
 };
 
 /* ---- context: one CUDA device, one stream, a device memory pool ------------ */
@@ -190,6 +192,25 @@ QE_API int qe_pipeline_run(qe_ctx *ctx, const qe_table *table,
                            qe_result **result);
 QE_API int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_pipeline_desc *desc,
                               qe_result **result);
+
+/* ---- streaming: host columns in, host results out, chunk by chunk -----------
+ * Stands in for the same subtree when the table starts in host memory (the reference's MemoryTable
+ * always does, M/data/MemoryTable.kt:7): uploads, kernels and downloads of neighbouring row-range
+ * chunks overlap on three streams.  Host buffers should be pinned (qe_host_alloc) for the copies to
+ * be asynchronous.  Returns when every copy has completed; the results also stay readable through
+ * qe_result_* as after qe_pipeline_run.  Filter and projection pipelines only. */
+typedef struct qe_stream_desc {
+    int64_t chunk_rows;                          /* rows per chunk, a multiple of 128; 0 = 32 Mi */
+    const void *const *host_values;              /* [table columns] source of each column (as qe_table_upload), NULL entry = already resident */
+    const uint8_t *const *host_validity;         /* [table columns] Arrow bitmaps, or NULL */
+    int32_t npipelines;
+    const qe_pipeline_desc *pipelines;           /* row_begin / row_end / QE_RUN_APPEND are set by the library */
+    qe_result **results;                         /* [npipelines] in / out, as for qe_pipeline_run_ex */
+    uint32_t *const *host_selection;             /* [npipelines] destination of the selection vectors; NULL or NULL entries = not wanted */
+    void *const *const *host_out_values;         /* [npipelines][nproj] destinations of the output columns */
+    uint8_t *const *const *host_out_validity;    /* [npipelines][nproj] destinations of the validity bitmaps, or NULL */
+} qe_stream_desc;
+QE_API int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_desc *desc);
 
 /* ---- results ------------------------------------------------------------- */
 /* rows the pipeline emitted (kept rows; 1 for an aggregation).  Waits for the run. */

@@ -23,6 +23,7 @@ QE_ERR_STATE = 7
 
 QE_RUN_NO_SELECTION = 1
 QE_RUN_INTERPRETER = 2
+QE_RUN_APPEND = 4
 
 QE_GEN_UNIFORM_U40 = 0
 QE_GEN_UNIFORM_INT = 1
@@ -60,6 +61,20 @@ class PipelineDesc(C.Structure):
     ]
 
 
+class StreamDesc(C.Structure):
+    _fields_ = [
+        ("chunk_rows", C.c_int64),
+        ("host_values", C.POINTER(C.c_void_p)),
+        ("host_validity", C.POINTER(C.c_void_p)),
+        ("npipelines", C.c_int32),
+        ("pipelines", C.POINTER(PipelineDesc)),
+        ("results", C.POINTER(C.c_void_p)),
+        ("host_selection", C.POINTER(C.c_void_p)),
+        ("host_out_values", C.POINTER(C.POINTER(C.c_void_p))),
+        ("host_out_validity", C.POINTER(C.POINTER(C.c_void_p))),
+    ]
+
+
 # every symbol include/qegpu.h declares: name -> (restype, argtypes)
 _vp = C.c_void_p
 SYMBOLS = {
@@ -80,6 +95,7 @@ SYMBOLS = {
     "qe_table_destroy": (C.c_int, [_vp]),
     "qe_pipeline_run": (C.c_int, [_vp, _vp, _vp, C.POINTER(_vp), C.c_int, C.POINTER(C.c_int32), C.c_int, C.POINTER(_vp)]),
     "qe_pipeline_run_ex": (C.c_int, [_vp, _vp, C.POINTER(PipelineDesc), C.POINTER(_vp)]),
+    "qe_pipeline_stream": (C.c_int, [_vp, _vp, C.POINTER(StreamDesc)]),
     "qe_result_num_rows": (C.c_int, [_vp, C.POINTER(C.c_int64)]),
     "qe_result_num_columns": (C.c_int, [_vp, C.POINTER(C.c_int)]),
     "qe_result_column_type": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),

@@ -75,6 +75,7 @@ struct QeParams {
     qe_u64       *tile_state;                 // decoupled-lookback descriptors, one per tile, zeroed per run
     qe_u32       *ticket;                     // dynamic tile counter, zeroed per run
     qe_u64       *out_count;                  // number of rows kept
+    const qe_u64 *out_base;                   // append mode: rows already in the outputs (device word), 0 = none
     double       *agg_partials;               // [gridDim.x][QE_MAX_AGGS][4] = sum, count (bits), min, max
     const qe_u32 *iprog;                      // interpreter only: serialized pipeline (qe_interp.cuh)
     qe_u64       *debug;                      // [4096][8] per-CTA phase cycle counters (QE_DEBUG_FLAGS & 16)
@@ -668,6 +669,7 @@ __device__ __forceinline__ void qe_filter_body(const QeParams &p)
     __shared__ qe_u32 s_lb_found[QE_WARPS];
 
     const qe_u32 lane = qe_lane(), warp = qe_warp();
+    const qe_u64 base0 = p.out_base ? *p.out_base : 0ull;      // append mode: rows of earlier batches
 
 #ifndef QE_DEBUG_FLAGS
 #define QE_DEBUG_FLAGS 0      // timing experiments only: 1 no look-back, 2 static tiles, 4 no scatter, 8 warp look-back
@@ -727,6 +729,7 @@ __device__ __forceinline__ void qe_filter_body(const QeParams &p)
             excl = qe_block_lookback(p.tile_state, tile, tile_total, s_lb_sum, s_lb_found);
         }
         QE_TICK(3);
+        excl += base0;
         if (threadIdx.x == 0 && tile == p.ntiles - 1) *p.out_count = excl + tile_total;
         if (!(QE_DEBUG_FLAGS & 4)) qe_warp_scatter<P>(p, warp_row0, excl + woff, outs, keep, rank0, step_off);
         QE_TICK(4);
@@ -786,7 +789,8 @@ __device__ __forceinline__ void qe_filter_pipelined_body(const QeParams &p)
         }
         if (have_prev) {
             // the previous tile: prefix (its predecessors published long ago) and ordered scatter
-            const qe_u64 excl = qe_block_lookback<false>(p.tile_state, prev_tile, prev_total, s_lb_sum, s_lb_found);
+            const qe_u64 excl = (p.out_base ? *p.out_base : 0ull) +
+                                qe_block_lookback<false>(p.tile_state, prev_tile, prev_total, s_lb_sum, s_lb_found);
             if (threadIdx.x == 0 && prev_tile == p.ntiles - 1) *p.out_count = excl + prev_total;
             const qe_i64 prev_row0 = (qe_i64)prev_tile * TILE + (qe_i64)warp * WARP_ROWS;
             qe_warp_scatter<P>(p, prev_row0, excl + prev_woff, prev_outs, prev_keep, prev_rank0, prev_step_off);
@@ -989,7 +993,7 @@ __device__ __forceinline__ void qe_filter_staged_body(const QeParams &p)
             woff += (qe_u32)w < warp ? c : 0u;
             tile_total += c;
         }
-        const qe_u64 excl = qe_block_lookback(p.tile_state, tile, tile_total, s_lb_sum, s_lb_found);
+        const qe_u64 excl = (p.out_base ? *p.out_base : 0ull) + qe_block_lookback(p.tile_state, tile, tile_total, s_lb_sum, s_lb_found);
         if (threadIdx.x == 0 && tile == p.ntiles - 1) *p.out_count = excl + tile_total;
         qe_warp_scatter<P>(p, warp_row0, excl + woff, outs, keep, rank0, step_off);
     }
@@ -1280,6 +1284,7 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
         // final add chains through shared memory (s_incl of the previous tile).
         qe_u64 rt_acc[16] = {};
         QE_RT_BEGIN();
+        const qe_u64 base0 = p.out_base ? *p.out_base : 0ull;  // append mode: rows of earlier batches
         for (qe_u32 it = warp - 2u;; it += (qe_u32)NLB) {
             const int st = (int)(it % NST);
             const qe_u32 par = (it / NST) & 1u;
@@ -1333,7 +1338,7 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                 QE_RT_ADD(5);
             }
             gap = __reduce_add_sync(QE_FULL_MASK, gap);
-            qe_u64 before = 0;                                // kept rows up to and including this CTA's previous tile
+            qe_u64 before = base0;                            // kept rows up to and including this CTA's previous tile
             if (it > 0) {
                 const qe_u32 jt = it - 1u;
                 qe_mbar_wait(qe_smem_addr(&s_pref[jt % NST]), (jt / NST) & 1u);

@@ -130,6 +130,7 @@ struct qe_ctx {
     int device = 0;
     int num_sms = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t h2d = nullptr, d2h = nullptr;   // copy streams of qe_pipeline_stream (created on first use)
     Pool pool;
     std::unordered_map<std::string, JitEntry> jit_cache;
     // options
@@ -222,6 +223,8 @@ extern "C" int qe_ctx_destroy(qe_ctx *ctx)
         if (ctx->staging_free[i]) cudaEventDestroy(ctx->staging_free[i]);
     }
     ctx->pool.destroy();
+    if (ctx->h2d) cudaStreamDestroy(ctx->h2d);
+    if (ctx->d2h) cudaStreamDestroy(ctx->d2h);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return QE_OK;
@@ -766,7 +769,13 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
     // ---- result buffers (reused when the caller passes the previous result back)
     qe_result *r = *result;
     if (r && r->ctx != ctx) return fail(QE_ERR_INVALID_ARGUMENT, "result belongs to another context");
-    if (r && r->pending) { QE_CUDA(cudaEventSynchronize(r->ev_done)); r->pending = false; }
+    const bool append = (d->flags & QE_RUN_APPEND) != 0;
+    if (append) {
+        if (mode == qe::KM_AGG) return fail(QE_ERR_UNSUPPORTED, "QE_RUN_APPEND: aggregations are combined with qe_agg_combine instead");
+        if (!r || r->mode != (int)mode || r->cols.size() != bp.outs.size() || !r->ctl.ptr)
+            return fail(QE_ERR_STATE, "QE_RUN_APPEND needs the result of an earlier run of the same pipeline");
+    }
+    if (r && r->pending && !append) { QE_CUDA(cudaEventSynchronize(r->ev_done)); r->pending = false; }
     if (r) fold_timing(r);
     if (!r) {
         r = new qe_result();
@@ -782,12 +791,22 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
         ~Cleanup() { if (armed && *slot != r) qe_result_destroy(r); }
     } cleanup{r, result, true};
 
+    const int64_t emitted_before = append ? r->batch_rows : 0;      // dense outputs: rows already in the result
+    if (append && mode == qe::KM_PROJECT) {
+        if (emitted_before % 128) return fail(QE_ERR_INVALID_ARGUMENT, "QE_RUN_APPEND: earlier batches must be multiples of 128 rows");
+        if (emitted_before + ntiles64 * tile_rows > r->capacity)
+            return fail(QE_ERR_CAPACITY, "QE_RUN_APPEND: the first run's out_capacity_rows does not cover this batch");
+    }
     r->mode = (int)mode;
     r->used_jit = use_jit;
-    r->batch_rows = n;
+    r->batch_rows = emitted_before + n;
     r->agg_fns = bp.agg_fns;
-    const int64_t capacity = mode == qe::KM_FILTER ? (d->out_capacity_rows > 0 ? std::min(d->out_capacity_rows, n) : n)
-                           : mode == qe::KM_PROJECT ? ntiles64 * tile_rows : 0;
+    // capacity is fixed by the first run (out_capacity_rows may exceed the batch: later batches are appended)
+    const int64_t capacity = append ? r->capacity
+                           : mode == qe::KM_FILTER ? (d->out_capacity_rows > 0 ? d->out_capacity_rows : n)
+                           : mode == qe::KM_PROJECT ? std::max(ntiles64 * tile_rows,
+                                                               (d->out_capacity_rows + kPadRows - 1) / kPadRows * kPadRows + kPadRows)
+                           : 0;
     r->capacity = capacity;
     if (r->cols.size() != bp.outs.size()) {
         for (ResultColumn &c : r->cols) { release(ctx, c.values); release(ctx, c.valid); }
@@ -816,12 +835,14 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
             c.has_validity = bp.outs[k].has_validity;
             const size_t vbytes = c.type == QE_TYPE_BOOLEAN ? bitmap_bytes : (size_t)std::max<int64_t>(capacity, 1) * type_width(c.type);
             if ((rc = ensure(ctx, c.values, vbytes))) return rc;
-            p.out_values[k] = c.values.ptr;
+            // dense outputs of an appended batch start where the earlier batches ended
+            const size_t dense_off = mode == qe::KM_PROJECT ? (size_t)emitted_before : 0;
+            p.out_values[k] = (char *)c.values.ptr + (c.type == QE_TYPE_BOOLEAN ? dense_off / 8 : dense_off * type_width(c.type));
             if (c.has_validity) {
                 if ((rc = ensure(ctx, c.valid, bitmap_bytes))) return rc;
-                p.out_valid[k] = (qe_u32 *)c.valid.ptr;
+                p.out_valid[k] = (qe_u32 *)((char *)c.valid.ptr + dense_off / 8);
             }
-            if (mode == qe::KM_FILTER) {      // compacted bit columns are OR-ed into: start from zero
+            if (mode == qe::KM_FILTER && !append) {      // compacted bit columns are OR-ed into: start from zero
                 if (c.type == QE_TYPE_BOOLEAN) QE_CUDA(cudaMemsetAsync(c.values.ptr, 0, bitmap_bytes, ctx->stream));
                 if (c.has_validity) QE_CUDA(cudaMemsetAsync(c.valid.ptr, 0, bitmap_bytes, ctx->stream));
             }
@@ -838,13 +859,28 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
     } else if (mode != qe::KM_FILTER) {
         release(ctx, r->sel);
     }
-    // control block: [0] kept-row count (u64)  [8] ticket (u32)  [16...] tile descriptors
-    const size_t ctl_bytes = 16 + (mode == qe::KM_FILTER ? (size_t)ntiles * 8 : 0);
+    // control block: [0] kept-row count (u64)  [8] ticket (u32)  [16] append base (u64)  [32...] tile descriptors
+    const size_t ctl_bytes = 32 + (mode == qe::KM_FILTER ? (size_t)ntiles * 8 : 0);
+    if (append && r->ctl.bytes < ctl_bytes) {                 // grow, keeping the running count
+        DevBuf bigger;
+        if ((rc = ensure(ctx, bigger, ctl_bytes))) return rc;
+        QE_CUDA(cudaMemcpyAsync(bigger.ptr, r->ctl.ptr, 32, cudaMemcpyDeviceToDevice, ctx->stream));
+        release(ctx, r->ctl);                                  // stream-ordered: reused only by later work of this stream
+        r->ctl = bigger;
+    }
     if ((rc = ensure(ctx, r->ctl, ctl_bytes))) return rc;
-    QE_CUDA(cudaMemsetAsync(r->ctl.ptr, 0, ctl_bytes, ctx->stream));
+    if (append) {
+        // base <- count of the earlier batches; ticket and descriptors start from zero again
+        QE_CUDA(cudaMemcpyAsync((char *)r->ctl.ptr + 16, r->ctl.ptr, 8, cudaMemcpyDeviceToDevice, ctx->stream));
+        QE_CUDA(cudaMemsetAsync((char *)r->ctl.ptr + 8, 0, 8, ctx->stream));
+        if (ctl_bytes > 32) QE_CUDA(cudaMemsetAsync((char *)r->ctl.ptr + 32, 0, ctl_bytes - 32, ctx->stream));
+        p.out_base = (const qe_u64 *)((char *)r->ctl.ptr + 16);
+    } else {
+        QE_CUDA(cudaMemsetAsync(r->ctl.ptr, 0, ctl_bytes, ctx->stream));
+    }
     p.out_count = (qe_u64 *)r->ctl.ptr;
     p.ticket = (qe_u32 *)((char *)r->ctl.ptr + 8);
-    p.tile_state = (qe_u64 *)((char *)r->ctl.ptr + 16);
+    p.tile_state = (qe_u64 *)((char *)r->ctl.ptr + 32);
     if (mode == qe::KM_AGG) {
         if ((rc = ensure(ctx, r->partials, (size_t)grid * QE_MAX_AGGS * 4 * sizeof(double)))) return rc;
         if ((rc = ensure(ctx, r->final_aggs, QE_MAX_AGGS * 4 * sizeof(double)))) return rc;
@@ -1132,6 +1168,161 @@ extern "C" int qe_result_debug_counters(qe_result *r, uint64_t *dst, size_t n)
 }
 
 extern "C" int qe_result_used_jit(const qe_result *r) { return r && r->used_jit ? 1 : 0; }
+
+// --------------------------------------------------------------- streaming
+// Host columns in, host results out, in row-range chunks: the upload of chunk c+1 (copy engine, h2d
+// stream), the kernels of chunk c (compute stream) and the download of the rows chunk c-1 produced
+// (other copy engine, d2h stream) run at the same time, so a scan that starts and ends in host memory
+// is bound by the busier PCIe direction instead of by the sum of both plus the kernels.  Every chunk
+// after the first is run with QE_RUN_APPEND, so the device-side results are the same as one run over
+// the whole table.
+
+namespace {
+
+struct StreamSinkState {
+    int64_t rows_done = 0;      // rows already downloaded
+};
+
+int download_range(qe_ctx *ctx, qe_result *r, int q, const qe_stream_desc *sd, int64_t from, int64_t to)
+{
+    if (to <= from) return QE_OK;
+    if (sd->host_selection && sd->host_selection[q] && r->sel.ptr)
+        QE_CUDA(cudaMemcpyAsync(sd->host_selection[q] + from, (const uint32_t *)r->sel.ptr + from, (size_t)(to - from) * 4,
+                                cudaMemcpyDeviceToHost, ctx->d2h));
+    for (size_t k = 0; k < r->cols.size(); k++) {
+        const ResultColumn &c = r->cols[k];
+        void *hv = sd->host_out_values && sd->host_out_values[q] ? sd->host_out_values[q][k] : nullptr;
+        uint8_t *hn = sd->host_out_validity && sd->host_out_validity[q] ? sd->host_out_validity[q][k] : nullptr;
+        const size_t b0 = (size_t)(from / 8), b1 = (size_t)((to + 7) / 8);     // bitmaps: whole bytes, the shared
+        if (hv) {                                                               // boundary byte is copied again later
+            if (c.type == QE_TYPE_BOOLEAN)
+                QE_CUDA(cudaMemcpyAsync((char *)hv + b0, (const char *)c.values.ptr + b0, b1 - b0, cudaMemcpyDeviceToHost, ctx->d2h));
+            else
+                QE_CUDA(cudaMemcpyAsync((char *)hv + (size_t)from * type_width(c.type),
+                                        (const char *)c.values.ptr + (size_t)from * type_width(c.type),
+                                        (size_t)(to - from) * type_width(c.type), cudaMemcpyDeviceToHost, ctx->d2h));
+        }
+        if (hn) {
+            if (c.has_validity)
+                QE_CUDA(cudaMemcpyAsync(hn + b0, (const char *)c.valid.ptr + b0, b1 - b0, cudaMemcpyDeviceToHost, ctx->d2h));
+            else if (to > from) {                                               // statically non-null: all ones
+                for (int64_t i = from; i < to && (i % 8); i++) hn[i / 8] |= (uint8_t)(1u << (i % 8));
+                const int64_t a = (from + 7) / 8 * 8;
+                if (to > a) {
+                    memset(hn + a / 8, 0xff, (size_t)((to - a) / 8));
+                    if ((to - a) % 8) hn[to / 8] = (uint8_t)((1u << (to % 8)) - 1u);
+                }
+            }
+        }
+    }
+    return QE_OK;
+}
+
+}  // namespace
+
+extern "C" int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_desc *sd)
+{
+    if (!ctx || !table || !sd || !sd->pipelines || !sd->results || sd->npipelines <= 0)
+        return fail(QE_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (table->ctx != ctx) return fail(QE_ERR_INVALID_ARGUMENT, "table belongs to another context");
+    if (sd->npipelines > 16) return fail(QE_ERR_UNSUPPORTED, "at most 16 pipelines per stream call");
+    int64_t chunk = sd->chunk_rows > 0 ? sd->chunk_rows : (int64_t)32 << 20;
+    if (chunk % 128) return fail(QE_ERR_INVALID_ARGUMENT, "chunk_rows must be a multiple of 128");
+    DeviceGuard g(ctx->device);
+    if (!ctx->h2d) QE_CUDA(cudaStreamCreateWithFlags(&ctx->h2d, cudaStreamNonBlocking));
+    if (!ctx->d2h) QE_CUDA(cudaStreamCreateWithFlags(&ctx->d2h, cudaStreamNonBlocking));
+    const int np = sd->npipelines;
+    const int64_t n = table->nrows;
+    const int nchunks = (int)std::max<int64_t>(1, (n + chunk - 1) / chunk);
+
+    unsigned long long *counts = nullptr;                      // pinned: kept rows after chunk c of pipeline q
+    QE_CUDA(cudaHostAlloc((void **)&counts, sizeof(unsigned long long) * (size_t)nchunks * np, cudaHostAllocDefault));
+    std::vector<cudaEvent_t> ev_up(nchunks, nullptr), ev_run((size_t)nchunks * np, nullptr);
+    std::vector<StreamSinkState> sink(np);
+    int rc = QE_OK;
+    auto cleanup = [&]() {
+        cudaStreamSynchronize(ctx->h2d);
+        cudaStreamSynchronize(ctx->stream);
+        cudaStreamSynchronize(ctx->d2h);
+        for (cudaEvent_t e : ev_up) if (e) cudaEventDestroy(e);
+        for (cudaEvent_t e : ev_run) if (e) cudaEventDestroy(e);
+        cudaFreeHost(counts);
+    };
+#define QE_STREAM_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { rc = fail_cuda(#call, e__); cleanup(); return rc; } } while (0)
+
+    // earlier work on the compute stream (generators, uploads through qe_table_upload) comes first
+    cudaEvent_t ev_start = nullptr;
+    QE_STREAM_CUDA(cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming));
+    ev_up.push_back(ev_start);                                 // destroyed with the others
+    QE_STREAM_CUDA(cudaEventRecord(ev_start, ctx->stream));
+    QE_STREAM_CUDA(cudaStreamWaitEvent(ctx->h2d, ev_start, 0));
+
+    auto drain = [&](int c) -> int {                           // download what chunk c added, pipeline by pipeline
+        for (int q = 0; q < np; q++) {
+            cudaError_t e = cudaEventSynchronize(ev_run[(size_t)c * np + q]);
+            if (e != cudaSuccess) return fail_cuda("cudaEventSynchronize", e);
+            qe_result *r = sd->results[q];
+            int64_t upto = r->mode == qe::KM_PROJECT ? std::min<int64_t>((int64_t)(c + 1) * chunk, n)
+                                                     : (int64_t)counts[(size_t)c * np + q];
+            upto = std::min(upto, r->capacity);
+            int drc = download_range(ctx, r, q, sd, sink[q].rows_done, upto);
+            if (drc) return drc;
+            sink[q].rows_done = std::max(sink[q].rows_done, upto);
+        }
+        return QE_OK;
+    };
+
+    for (int c = 0; c < nchunks; c++) {
+        const int64_t r0 = (int64_t)c * chunk, r1 = std::min(n, r0 + chunk);
+        // ---- upload chunk c
+        for (size_t col = 0; col < table->cols.size(); col++) {
+            const qe_col_desc &cd = table->cols[col];
+            const void *hv = sd->host_values ? sd->host_values[col] : nullptr;
+            const uint8_t *hn = sd->host_validity ? sd->host_validity[col] : nullptr;
+            if (hv && r1 > r0) {
+                if (cd.type == QE_TYPE_BOOLEAN)
+                    QE_STREAM_CUDA(cudaMemcpyAsync((char *)table->values[col] + r0 / 8, (const char *)hv + r0 / 8,
+                                                   (size_t)((r1 - r0 + 7) / 8), cudaMemcpyHostToDevice, ctx->h2d));
+                else
+                    QE_STREAM_CUDA(cudaMemcpyAsync((char *)table->values[col] + (size_t)r0 * type_width(cd.type),
+                                                   (const char *)hv + (size_t)r0 * type_width(cd.type),
+                                                   (size_t)(r1 - r0) * type_width(cd.type), cudaMemcpyHostToDevice, ctx->h2d));
+            }
+            if (hn && cd.nullable && r1 > r0)
+                QE_STREAM_CUDA(cudaMemcpyAsync((char *)table->valid[col] + r0 / 8, hn + r0 / 8, (size_t)((r1 - r0 + 7) / 8),
+                                               cudaMemcpyHostToDevice, ctx->h2d));
+        }
+        QE_STREAM_CUDA(cudaEventCreateWithFlags(&ev_up[c], cudaEventDisableTiming));
+        QE_STREAM_CUDA(cudaEventRecord(ev_up[c], ctx->h2d));
+        QE_STREAM_CUDA(cudaStreamWaitEvent(ctx->stream, ev_up[c], 0));
+        // ---- run every pipeline over chunk c
+        for (int q = 0; q < np; q++) {
+            qe_pipeline_desc d = sd->pipelines[q];
+            d.row_begin = r0;
+            d.row_end = r1;
+            d.flags = (d.flags & ~(uint32_t)QE_RUN_APPEND) | (c > 0 ? (uint32_t)QE_RUN_APPEND : 0u);
+            if (d.out_capacity_rows <= 0) d.out_capacity_rows = n;
+            rc = qe_pipeline_run_ex(ctx, table, &d, &sd->results[q]);
+            if (rc) { cleanup(); return rc; }
+            qe_result *r = sd->results[q];
+            if (r->mode == qe::KM_AGG) { cleanup(); return fail(QE_ERR_UNSUPPORTED, "qe_pipeline_stream: aggregations are not streamed"); }
+            QE_STREAM_CUDA(cudaMemcpyAsync(&counts[(size_t)c * np + q], r->ctl.ptr, sizeof(unsigned long long),
+                                           cudaMemcpyDeviceToHost, ctx->stream));
+            QE_STREAM_CUDA(cudaEventCreateWithFlags(&ev_run[(size_t)c * np + q], cudaEventDisableTiming));
+            QE_STREAM_CUDA(cudaEventRecord(ev_run[(size_t)c * np + q], ctx->stream));
+        }
+        // ---- while chunk c runs, download what chunk c-1 produced
+        if (c > 0 && (rc = drain(c - 1))) { cleanup(); return rc; }
+    }
+    if ((rc = drain(nchunks - 1))) { cleanup(); return rc; }
+#undef QE_STREAM_CUDA
+    cleanup();
+    for (int q = 0; q < np; q++) {                             // the runs are complete: make the results readable
+        qe_result *r = sd->results[q];
+        r->pending = false;                                     // all three streams were synchronised in cleanup()
+    }
+    return QE_OK;
+}
 
 // ------------------------------------------------------------ diagnostics
 // Bind a pipeline against a schema, generate its CUDA source and optionally

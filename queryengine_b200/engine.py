@@ -286,6 +286,25 @@ class Pipeline:
         self._proj_arr = (C.c_void_p * max(1, len(self.projs)))(*[p.handle for p in self.projs])
         self._agg_arr = (C.c_int32 * max(1, len(self.aggs)))(*self.aggs)
 
+    def desc(self, row_begin: int = 0, row_end: int = -1, append: bool = False) -> "capi.PipelineDesc":
+        d = capi.PipelineDesc()
+        d.filter = self.filter.handle if self.filter else None
+        d.proj = self._proj_arr
+        d.nproj = len(self.projs)
+        d.agg_fns = self._agg_arr
+        d.nagg = len(self.aggs)
+        d.row_begin = row_begin
+        d.row_end = row_end
+        d.out_capacity_rows = self.out_capacity_rows
+        d.flags = self.flags | (capi.QE_RUN_APPEND if append else 0)
+        return d
+
+    def run_append(self, result: PipelineResult, row_begin: int, row_end: int) -> PipelineResult:
+        """Run one more row-range batch and append its rows to `result` (QE_RUN_APPEND)."""
+        d = self.desc(row_begin, row_end, append=True)
+        capi.check(capi.lib().qe_pipeline_run_ex(self.ctx.handle, self.table.handle, C.byref(d), C.byref(result.handle)))
+        return result
+
     def run(self, result: Optional[PipelineResult] = None, row_begin: int = 0, row_end: int = -1) -> PipelineResult:
         """Enqueue the pipeline on the context's stream; accessors of the result wait for it."""
         r = result or PipelineResult(self.ctx)
@@ -301,6 +320,65 @@ class Pipeline:
         d.flags = self.flags
         capi.check(capi.lib().qe_pipeline_run_ex(self.ctx.handle, self.table.handle, C.byref(d), C.byref(r.handle)))
         return r
+
+
+def stream_pipelines(table: ColumnarTable, pipelines: Sequence[Pipeline], host_values: Sequence[Optional[int]],
+                     host_validity: Optional[Sequence[Optional[int]]] = None, chunk_rows: int = 0,
+                     results: Optional[List[Optional[PipelineResult]]] = None,
+                     host_selection: Optional[Sequence[Optional[int]]] = None,
+                     host_out_values: Optional[Sequence[Sequence[Optional[int]]]] = None,
+                     host_out_validity: Optional[Sequence[Sequence[Optional[int]]]] = None) -> List[PipelineResult]:
+    """qe_pipeline_stream: host columns in (addresses of caller-owned, ideally pinned buffers), host results
+    out, chunk by chunk with uploads, kernels and downloads overlapped.  Returns the (complete) results."""
+    ctx = table.ctx
+    np_ = len(pipelines)
+    res = [(results[q] if results and results[q] is not None else PipelineResult(ctx)) for q in range(np_)]
+    ncols = len(table.fields)
+
+    def ptr_array(vals, n):
+        arr = (C.c_void_p * max(1, n))()
+        for i in range(n):
+            arr[i] = vals[i] if vals is not None and i < len(vals) and vals[i] else None
+        return arr
+
+    sd = capi.StreamDesc()
+    sd.chunk_rows = chunk_rows
+    hv = ptr_array(host_values, ncols)
+    sd.host_values = hv
+    hn = ptr_array(host_validity, ncols) if host_validity is not None else None
+    if hn is not None:
+        sd.host_validity = hn
+    sd.npipelines = np_
+    descs = (capi.PipelineDesc * np_)(*[p.desc() for p in pipelines])
+    sd.pipelines = descs
+    handles = (C.c_void_p * np_)(*[r.handle.value for r in res])
+    sd.results = handles
+    hs = ptr_array(host_selection, np_) if host_selection is not None else None
+    if hs is not None:
+        sd.host_selection = hs
+    keep = []
+
+    def ptr_matrix(rows):
+        outer = (C.POINTER(C.c_void_p) * np_)()
+        for q in range(np_):
+            n = len(pipelines[q].projs)
+            inner = ptr_array(rows[q] if rows[q] is not None else None, n)
+            keep.append(inner)
+            outer[q] = C.cast(inner, C.POINTER(C.c_void_p))
+        return outer
+
+    if host_out_values is not None:
+        ov = ptr_matrix(host_out_values)
+        sd.host_out_values = ov
+    if host_out_validity is not None:
+        on = ptr_matrix(host_out_validity)
+        sd.host_out_validity = on
+    try:
+        capi.check(capi.lib().qe_pipeline_stream(ctx.handle, table.handle, C.byref(sd)))
+    finally:
+        for q in range(np_):
+            res[q].handle = C.c_void_p(handles[q])
+    return res
 
 
 class GpuPipelineOperator:

@@ -331,3 +331,83 @@ def test_large_scan_properties(ctx):
         res.close()
         res2.close()
     t.close()
+
+
+@pytest.mark.parametrize("interpreter", [False, True])
+def test_append_batches_equal_one_run(ctx, interpreter):
+    """QE_RUN_APPEND: row-range batches appended into one result = the whole table in one run (values, selection,
+    compacted validity / boolean bitmaps; dense projections too)."""
+    rng = np.random.default_rng(77)
+    spec = random_table(rng, 50_000, "DbiT")
+    g = ExprGen(rng, spec.fields)
+    t = spec.gpu(ctx)
+    filt = g.boolean(3)
+    projs = [g.double(4), g.boolean(2), col(2, I), col(3, T)]
+    for f in (filt, None):
+        whole = Pipeline(t, f, projs, interpreter=interpreter).run()
+        pipe = Pipeline(t, f, projs, interpreter=interpreter, out_capacity_rows=spec.nrows)
+        bounds = [0, 128, 128, 4224, 20096, 20096 + 8192, spec.nrows]
+        res = pipe.run(row_begin=0, row_end=bounds[1])
+        for lo, hi in zip(bounds[1:], bounds[2:]):
+            res = pipe.run_append(res, lo, hi)
+        assert res.num_rows == whole.num_rows
+        if f is not None:
+            assert np.array_equal(res.selection(), whole.selection())
+        for k in range(len(projs)):
+            a, av = res.column(k)
+            b, bv = whole.column(k)
+            assert np.array_equal(av, bv)
+            a, b = np.asarray(a)[bv], np.asarray(b)[bv]
+            assert f64_equal(a, b).all() if a.dtype == np.float64 else np.array_equal(a, b)
+        res.close()
+        whole.close()
+    t.close()
+
+
+@pytest.mark.parametrize("chunk", [128, 4096, 1 << 16])
+def test_stream_host_in_host_out(ctx, chunk):
+    """qe_pipeline_stream: chunked upload / run / download equals upload + run + read back."""
+    from queryengine_b200.engine import stream_pipelines
+    rng = np.random.default_rng(chunk)
+    n = 200_003
+    v = rng.integers(0, 1000, n).astype(np.int64)
+    d = rng.normal(size=n)
+    dv = rng.random(n) > 0.2
+    fields = [Field("i", I, False), Field("d", D, True)]
+    ref_t = ColumnarTable.from_arrays(ctx, fields, [v, d], [None, dv])
+    filt = fn(Function.CMP_LT, col(0, I), 400.0)
+    projs = [col(0, I), fn(Function.MUL, col(1), 2.0)]
+    whole = Pipeline(ref_t, filt, projs).run()
+    dense = Pipeline(ref_t, None, [fn(Function.ADD, col(1), 1.0)]).run()
+    want_n = whole.num_rows
+    # streamed: the table starts empty, host buffers are plain numpy arrays (pageable is allowed, pinned is faster)
+    t = ColumnarTable(ctx, fields, n)
+    vbits = np.packbits(dv.astype(np.uint8), bitorder="little")
+    sel = np.zeros(n, np.uint32)
+    o0 = np.zeros(n, np.int64)
+    o1 = np.zeros(n, np.float64)
+    o1v = np.zeros((n + 7) // 8, np.uint8)
+    o2 = np.zeros(n, np.float64)
+    o2v = np.zeros((n + 7) // 8, np.uint8)
+    pipes = [Pipeline(t, filt, projs), Pipeline(t, None, [fn(Function.ADD, col(1), 1.0)])]
+    res = stream_pipelines(t, pipes, [v.ctypes.data, d.ctypes.data], [None, vbits.ctypes.data], chunk_rows=chunk,
+                           host_selection=[sel.ctypes.data, None],
+                           host_out_values=[[o0.ctypes.data, o1.ctypes.data], [o2.ctypes.data]],
+                           host_out_validity=[[None, o1v.ctypes.data], [o2v.ctypes.data]])
+    assert res[0].num_rows == want_n and res[1].num_rows == n
+    assert np.array_equal(sel[:want_n], whole.selection())
+    w0, _ = whole.column(0)
+    w1, w1v = whole.column(1)
+    assert np.array_equal(o0[:want_n], w0)
+    got1v = np.unpackbits(o1v, bitorder="little")[:want_n].astype(bool)
+    assert np.array_equal(got1v, w1v)
+    assert np.array_equal(o1[:want_n][w1v], np.asarray(w1)[w1v])
+    dd, ddv = dense.column(0)
+    got2v = np.unpackbits(o2v, bitorder="little")[:n].astype(bool)
+    assert np.array_equal(got2v, ddv) and np.array_equal(o2[ddv], np.asarray(dd)[ddv])
+    # the device-side results are complete as well
+    assert np.array_equal(res[0].selection(), whole.selection())
+    for r in res + [whole, dense]:
+        r.close()
+    t.close()
+    ref_t.close()
