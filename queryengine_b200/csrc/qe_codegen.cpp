@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <vector>
 
 namespace qe {
@@ -21,6 +22,11 @@ struct SV {                  // one entry of the compile-time operand stack
 struct Gen {
     std::string body;
     int ntmp = 0;
+    // common subexpressions: (function, operand names) -> the temporary that already holds the result.
+    // The reference evaluates a repeated subtree every time it meets it (it has no DAG); the functions
+    // are pure, so evaluating once is indistinguishable -- and a shared subtree with a divide or a MOD
+    // in it is most of the work of a row.
+    std::map<std::string, SV> memo;
 
     std::string tmp(const char *prefix)
     {
@@ -122,6 +128,18 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
     std::vector<SV> st;
     for (const Instr &in : e.code) {
         SV r;
+        std::string key;
+        if (in.op <= OP_CMP_NE) {                   // a function of the operands on top of the stack
+            const int ar = op_arity(in.op);
+            key = std::to_string((int)in.op);
+            for (size_t i = st.size() - (size_t)ar; i < st.size(); i++) key += "|" + st[i].val + "?" + st[i].valid;
+            auto hit = g.memo.find(key);
+            if (hit != g.memo.end()) {
+                st.resize(st.size() - (size_t)ar);
+                st.push_back(hit->second);
+                continue;
+            }
+        }
         switch (in.op) {
         case OP_LOAD_COL: {
             const int slot = (int)in.arg;
@@ -221,6 +239,7 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
             break;
         }
         }
+        if (!key.empty()) g.memo[key] = r;
         st.push_back(r);
     }
     return st.back();

@@ -411,3 +411,34 @@ def test_stream_host_in_host_out(ctx, chunk):
         r.close()
     t.close()
     ref_t.close()
+
+
+@pytest.mark.parametrize("interpreter", [False, True])
+def test_mod_fast_path_is_bit_exact(ctx, interpreter):
+    """MOD = JVM DREM = C fmod (M/evaluator/Interpreter.kt:100).  The device code takes an exact
+    three-instruction path when the quotient fits 53 bits and the library loop otherwise: both sides of
+    that switch, signed zeros, infinities, NaN, denormals and quotients next to integers."""
+    rng = np.random.default_rng(123)
+    n = 200_000
+    mant = rng.random(n) + 1.0
+    a = mant * 2.0 ** rng.integers(-40, 80, n) * rng.choice([-1.0, 1.0], n)
+    b = (rng.random(n) + 1.0) * 2.0 ** rng.integers(-40, 40, n) * rng.choice([-1.0, 1.0], n)
+    # exact multiples and near-multiples: quotient an integer, or one ulp off either side
+    k = rng.integers(1, 1 << 30, n // 4).astype(np.float64)
+    bb = np.round(rng.random(n // 4) * 1000 + 1, 3)
+    a[: n // 4] = k * bb
+    b[: n // 4] = bb
+    a[n // 4: n // 4 + 1000] = np.nextafter(a[:1000], np.inf)
+    b[n // 4: n // 4 + 1000] = b[:1000]
+    special = np.array([0.0, -0.0, np.inf, -np.inf, np.nan, 5e-324, -5e-324, 2.2250738585072014e-308, 1.7976931348623157e308,
+                        1.0, -1.0, 7.0, 2.0 ** 53, 2.0 ** 53 + 2, 2.0 ** 52 + 1, 3.0, 0.1, 1e-300, 1e300])
+    sa, sb = np.meshgrid(special, special)
+    m = sa.size
+    a[-m:] = sa.ravel()
+    b[-m:] = sb.ravel()
+    # quotients around 2^53: the switch between the two paths
+    a[-m - 2000:-m] = (2.0 ** 53 + rng.integers(-1000, 1000, 2000)) * 3.0
+    b[-m - 2000:-m] = 3.0
+    spec = TableSpec([Field("a", D, False), Field("b", D, False)], [a, b], [None, None])
+    compare_pipeline(ctx, spec, None, [fn(Function.MOD, col(0), col(1)), fn(Function.MOD, col(0), 7.0),
+                                       fn(Function.MOD, col(1), col(0))], interpreter=interpreter)
