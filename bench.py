@@ -270,6 +270,50 @@ def extra_q6(ctx, torch, stream, rows, steps, warmup, peak):
     return out
 
 
+def sf_filter_pipeline(ctx, rows, row_offset=0, capacity_frac=0.30):
+    """BASELINE.json configs[4]: multi-column AND/OR filter + two projections over lineitem-shaped columns
+    (qty, extendedprice, discount, tax, shipdate; all f64), one row-range partition."""
+    from queryengine_b200 import capi
+    from queryengine_b200.ast import DataType, Function, col, fn
+    from queryengine_b200.engine import ColumnarTable, Field, Pipeline
+    D = DataType.DOUBLE
+    t = ColumnarTable(ctx, [Field("l_quantity", D), Field("l_extendedprice", D), Field("l_discount", D), Field("l_tax", D),
+                            Field("l_shipdate", D)], rows)
+    t.generate(0, capi.QE_GEN_UNIFORM_INT, SEED + 1, 1, 50, row_offset=row_offset)
+    t.generate(1, capi.QE_GEN_CENTS, SEED + 2, 90000, 10499999, row_offset=row_offset)
+    t.generate(2, capi.QE_GEN_CENTS, SEED + 3, 0, 10, row_offset=row_offset)
+    t.generate(3, capi.QE_GEN_CENTS, SEED + 5, 0, 8, row_offset=row_offset)
+    t.generate(4, capi.QE_GEN_UNIFORM_INT, SEED + 4, 8036, 10561, row_offset=row_offset)
+    qty, ep, disc, tax, sd = (col(i) for i in range(5))
+    filt = fn(Function.OR,
+              fn(Function.AND, fn(Function.AND, fn(Function.CMP_GE, sd, 8766.0), fn(Function.CMP_LT, sd, 9131.0)),
+                 fn(Function.CMP_LT, qty, 24.0)),
+              fn(Function.AND, fn(Function.CMP_GE, disc, 0.05), fn(Function.CMP_LE, tax, 0.02)))
+    net = fn(Function.MUL, ep, fn(Function.SUB, 1.0, disc))
+    gross = fn(Function.MUL, fn(Function.MUL, ep, fn(Function.SUB, 1.0, disc)), fn(Function.ADD, 1.0, tax))
+    return t, Pipeline(t, filt, [net, gross], out_capacity_rows=int(rows * capacity_frac) + 4096)
+
+
+def extra_sf_filter(ctx, rows, steps, warmup, peak, row_offset=0):
+    t, pipe = sf_filter_pipeline(ctx, rows, row_offset)
+    res = pipe.run()
+    for _ in range(warmup):
+        pipe.run(res)
+    ms0, runs0 = res.kernel_stats()
+    for _ in range(steps):
+        pipe.run(res)
+    ms1, runs1 = res.kernel_stats()
+    kms = (ms1 - ms0) / max(1, runs1 - runs0)
+    kept = res.num_rows
+    nbytes = rows * 40.0 + kept * 20.0
+    out = {"rows": rows, "kept": kept, "selectivity": kept / rows, "kernel_ms": kms, "rows_per_s": rows / (kms * 1e-3),
+           "gb_per_s": nbytes / (kms * 1e-3) / 1e9, "frac_of_peak": nbytes / (kms * 1e-3) / 1e9 / peak,
+           "algorithmic_bytes_per_row": 40 + 20 * kept / rows, "jit": res.used_jit}
+    res.close()
+    t.close()
+    return out
+
+
 def tree_expr():
     """The depth-8 nullable arithmetic tree of BASELINE.json configs[3] (fixed here, evaluated by the oracle in tests)."""
     from queryengine_b200.ast import Function, col, fn
@@ -409,6 +453,10 @@ def run_ours(args):
                 extra[name] = fn_(ctx, torch, stream, n, max(3, args.steps), 3, peak)
             except Exception as e:  # reported, never hidden
                 extra[name] = {"error": repr(e)}
+        try:      # configs[4] on one partition (SF1000 / 6: what one of 6 GPUs would hold)
+            extra["lineitem_filter_2proj_1e9"] = extra_sf_filter(ctx, args.sf_rows, max(3, args.steps), 3, peak)
+        except Exception as e:
+            extra["lineitem_filter_2proj_1e9"] = {"error": repr(e)}
     if world > 1 and not args.no_extra:
         # Q6 over SF100 lineitem row-sharded across the ranks: per-rank partial, NCCL all-gather of the partials,
         # rank-order combine (queryengine_b200/sharding.py) -- the only collective on the path
@@ -432,6 +480,26 @@ def run_ours(args):
                                      "sum": total[0], "combine": "NCCL all_gather of partials + qe_agg_combine in rank order"}
         res6.close()
         t6.close()
+        # configs[4]: SF1000 lineitem (5 999 989 709 rows) row-sharded over the ranks, no collective at all
+        from queryengine_b200 import sharding as sh
+        total = 5_999_989_709
+        lo, hi = sh.partition(total, world, rank)
+        free_b, _tot = torch.cuda.mem_get_info()
+        fit = int(free_b * 0.85 / (40 + 0.30 * 20)) // 4096 * 4096      # rows this GPU can hold with its outputs
+        nloc = min(hi - lo, fit, 0xfffff000)
+        try:
+            e = extra_sf_filter(ctx, nloc, max(3, args.steps), 3, peak, row_offset=lo)
+            v = torch.tensor([e["kernel_ms"], float(nloc), float(e["kept"])], dtype=torch.float64, device=device)
+            vmax = v.clone(); dist.all_reduce(vmax, op=dist.ReduceOp.MAX)
+            vsum = v.clone(); dist.all_reduce(vsum, op=dist.ReduceOp.SUM)
+            rows_all, kept_all, kms = float(vsum[1].item()), float(vsum[2].item()), float(vmax[0].item())
+            extra["lineitem_sf1000_sharded"] = {
+                "rows_total_sf1000": total, "rows_processed": int(rows_all), "partitions": world, "kept": int(kept_all),
+                "reduced": rows_all < total, "kernel_ms_max_over_ranks": kms, "rows_per_s": rows_all / (kms * 1e-3),
+                "gb_per_s_aggregate": (rows_all * 40 + kept_all * 20) / (kms * 1e-3) / 1e9,
+                "frac_of_aggregate_peak": (rows_all * 40 + kept_all * 20) / (kms * 1e-3) / 1e9 / (peak * world)}
+        except Exception as e:
+            extra["lineitem_sf1000_sharded"] = {"error": repr(e)}
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
         v, secs, ckept = cpu_leg(args.cpu_rows, threads)
@@ -541,6 +609,7 @@ def main():
     ap.add_argument("--e2e-chunk-rows", type=int, default=1 << 25, help="rows per chunk of the streamed end-to-end leg")
     ap.add_argument("--q6-rows", type=int, default=600_037_902)
     ap.add_argument("--tree-rows", type=int, default=1_000_000_000)
+    ap.add_argument("--sf-rows", type=int, default=1_000_000_000, help="rows of the single-partition configs[4] extra")
     ap.add_argument("--no-extra", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--allow-interpreter", action="store_true")
