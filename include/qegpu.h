@@ -48,17 +48,22 @@ typedef enum qe_status {
     QE_ERR_INVALID_ARGUMENT = 1,
     QE_ERR_PROGRAM = 2,        /* malformed program or operand types the reference's TypeCheck rejects */
     QE_ERR_CUDA = 3,
-    QE_ERR_UNSUPPORTED = 4,    /* e.g. STRING expressions (not on the GPU path yet) */
+    QE_ERR_UNSUPPORTED = 4,    /* e.g. ANY / ALL aggregates, more columns than QE_MAX_PIPELINE_COLUMNS */
     QE_ERR_CAPACITY = 5,       /* more rows passed the filter than out_capacity_rows */
     QE_ERR_JIT = 6,
     QE_ERR_STATE = 7
 } qe_status;
 
-/* Physical column types.  DOUBLE and BOOLEAN are the reference's DataType
+/* Physical column types.  STRING, DOUBLE and BOOLEAN are the reference's DataType
  * members (M/data/Schema.kt:3-5, same ordinals); INT64 and DATE32 are
- * extensions that widen exactly to DOUBLE when loaded (|x| < 2^53). */
+ * extensions that widen exactly to DOUBLE when loaded (|x| < 2^53).
+ * STRING columns hold dictionary codes: the caller interns every string of a
+ * context (column values AND literals) in ONE dictionary, so that equal codes
+ * <=> equal strings.  That is all the reference's type checker lets a query do
+ * with strings: CMP_EQ / CMP_NE, IF branches, bare columns, COUNT and group keys
+ * (M/evaluator/TypeCheck.kt:65-71,86-94,118-120). */
 typedef enum qe_type {
-    QE_TYPE_STRING = 0,        /* reserved, not supported on this path */
+    QE_TYPE_STRING = 0,        /* int32_t[n] dictionary codes */
     QE_TYPE_DOUBLE = 1,        /* double[n] */
     QE_TYPE_BOOLEAN = 2,       /* bitmap, LSB first */
     QE_TYPE_INT64 = 3,         /* int64_t[n] */
@@ -81,11 +86,13 @@ typedef enum qe_agg_fn {
  *   QE_OP_CONST_F64 NumericLiteralExpression; the next two words are the low
  *                   and high halves of the IEEE-754 bits
  *   QE_OP_CONST_BOOL BooleanLiteralExpression; argument = 0 / 1
+ *   QE_OP_CONST_STR StringLiteralExpression; the next word is its dictionary code (int32)
  */
 enum {
     QE_OP_LOAD_COL = 32,
     QE_OP_CONST_F64 = 33,
-    QE_OP_CONST_BOOL = 34
+    QE_OP_CONST_BOOL = 34,
+    QE_OP_CONST_STR = 35
 };
 #define QE_MAX_PROGRAM_WORDS 1024
 #define QE_MAX_STACK 32

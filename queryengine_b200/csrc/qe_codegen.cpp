@@ -143,8 +143,8 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
         switch (in.op) {
         case OP_LOAD_COL: {
             const int slot = (int)in.arg;
-            r.t = (bp.slot_info[slot].type == 2) ? VT_BOOL : VT_F64;
-            r.val = slot_value(bp, slot);
+            r.t = bp.slot_info[slot].type == 2 ? VT_BOOL : bp.slot_info[slot].type == 0 ? VT_STR : VT_F64;
+            r.val = slot_value(bp, slot);              // STRING: the dictionary code itself (qe_i32)
             char b[32];
             if (bp.slot_info[slot].type == 3 || bp.slot_info[slot].type == 4) {
                 snprintf(b, sizeof b, "in.c%d", slot);
@@ -159,6 +159,9 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
             break;
         case OP_CONST_BOOL:
             r.t = VT_BOOL; r.val = in.arg ? "true" : "false"; r.valid = "true";
+            break;
+        case OP_CONST_STR:                          // StringLiteralExpression as its dictionary code
+            r.t = VT_STR; r.val = "((qe_i32)" + std::to_string(in.code) + ")"; r.valid = "true";
             break;
         case OP_UNARY_PLUS: {                       // M/evaluator/Interpreter.kt:94
             r = st.back(); st.pop_back(); r.is_const = false; r.raw_int.clear();
@@ -190,7 +193,7 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
             SV a = st.back(); st.pop_back();
             r.t = VT_BOOL; r.valid = and_valid(a.valid, b.valid); r.val = g.tmp("t");
             std::string rhs;
-            if (a.t == VT_BOOL) {                   // Boolean equality, TypeCheck.kt:65-71
+            if (a.t == VT_BOOL || a.t == VT_STR) {  // Boolean / String equality (TypeCheck.kt:65-71); equal codes <=> equal strings
                 rhs = std::string("(") + a.val + (in.op == OP_CMP_EQ ? " == " : " != ") + b.val + ")";
             } else if (int_literal_ok(b) && !a.raw_int.empty()) {
                 rhs = int_compare(in.op, a.raw_int, b.k);
@@ -226,7 +229,7 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
             SV t = st.back(); st.pop_back();
             SV c = st.back(); st.pop_back();
             r.t = t.t; r.val = g.tmp("t");
-            g.line(std::string("const ") + (r.t == VT_F64 ? "double " : "bool ") + r.val + " = " + c.val + " ? " + t.val +
+            g.line(std::string("const ") + (r.t == VT_F64 ? "double " : r.t == VT_STR ? "qe_i32 " : "bool ") + r.val + " = " + c.val + " ? " + t.val +
                    " : " + f.val + ";");
             std::string branch_valid = (t.valid == "true" && f.valid == "true")
                                            ? "true" : "(" + c.val + " ? " + t.valid + " : " + f.valid + ")";
@@ -270,7 +273,7 @@ StageLayout stage_layout(const BoundPipeline &bp, const TileShape &shape)
     int off = 0;
     L.valid_bytes = tile / 8;
     for (const ColumnInfo &c : bp.slot_info) {
-        const int w = c.type == 2 ? 0 : (c.type == 4 ? 4 : 8);
+        const int w = c.type == 2 ? 0 : ((c.type == 4 || c.type == 0) ? 4 : 8);
         const int bytes = w ? tile * w : tile / 8;
         L.val_off.push_back(off);
         L.val_bytes.push_back(bytes);
@@ -407,7 +410,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                          bulk, L.val_off[i], i, L.val_bytes[i], pol);
             else
                 snprintf(b, sizeof b, "        %s(stage + %d, (const char *)p.col_values[%d] + row0 * %d, %d, mbar%s);\n",
-                         bulk, L.val_off[i], i, t == 4 ? 4 : 8, L.val_bytes[i], pol);
+                         bulk, L.val_off[i], i, (t == 4 || t == 0) ? 4 : 8, L.val_bytes[i], pol);
             s += b;
             if (bp.slot_info[i].nullable) {
                 snprintf(b, sizeof b, "        %s(stage + %d, (const char *)p.col_valid[%d] + (row0 >> 3), %d, mbar%s);\n",

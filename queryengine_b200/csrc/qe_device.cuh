@@ -49,6 +49,7 @@
 #define QE_MAX_AGGS 8
 
 // physical column types (values match include/qegpu.h)
+#define QE_T_STR 0      /* dictionary codes, int32 */
 #define QE_T_F64 1
 #define QE_T_BOOL 2
 #define QE_T_I64 3

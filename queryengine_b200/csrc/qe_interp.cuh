@@ -12,7 +12,9 @@
 //   [20 + k]  out k:   type | has_validity << 8 | (identity_slot + 1) << 16   (8 entries)
 //   [28 + k]  aggregate function of projection k                 (8 entries)
 //   [36 ...]  programs: filter (if any) then projections, each  len, word[len]
-//             word = opcode | arg << 8 ; CONST_F64 is followed by two payload words
+//             word = opcode | arg << 8 ; CONST_F64 is followed by two payload words, CONST_STR by one
+// STRING values (dictionary codes, int32) travel on the double stack: the widening is exact and
+// equality of the doubles is equality of the codes.
 #ifndef QE_INTERP_CUH
 #define QE_INTERP_CUH
 
@@ -51,7 +53,7 @@ static __device__ __noinline__ QeInterpValue qe_interp_run(const QeParams &p, co
             const void *col = p.col_values[arg];
             if (type == QE_T_F64) f = ((const double *)col)[r];
             else if (type == QE_T_I64) f = qe_i64_to_f64(((const qe_i64 *)col)[r]);
-            else if (type == QE_T_DATE32) f = qe_i32_to_f64(((const qe_i32 *)col)[r]);
+            else if (type == QE_T_DATE32 || type == QE_T_STR) f = qe_i32_to_f64(((const qe_i32 *)col)[r]);
             else bv = (((const qe_u32 *)col)[r >> 5] >> ((qe_u32)r & 31u)) & 1u;
             sf[sp] = f;
             sb = (sb & ~(1u << sp)) | ((bv ? 1u : 0u) << sp);
@@ -61,6 +63,11 @@ static __device__ __noinline__ QeInterpValue qe_interp_run(const QeParams &p, co
             const qe_u64 bits = (qe_u64)code[pc + 1] | ((qe_u64)code[pc + 2] << 32);
             pc += 2;
             sf[sp] = qe_bits_f64((qe_i64)bits);
+            sv |= 1u << sp;
+            sp++;
+        } else if (op == 35u) {                                 // CONST_STR
+            pc += 1;
+            sf[sp] = qe_i32_to_f64((qe_i32)code[pc]);
             sv |= 1u << sp;
             sp++;
         } else if (op == 34u) {                                 // CONST_BOOL
@@ -175,6 +182,7 @@ struct QeInterpProgram {
         if (type == QE_T_F64) ((double *)p.out_values[k])[pos] = f;
         else if (type == QE_T_I64) ((qe_i64 *)p.out_values[k])[pos] = qe_f64_bits(f);
         else if (type == QE_T_DATE32) ((qe_i32 *)p.out_values[k])[pos] = (qe_i32)qe_f64_bits(f);
+        else if (type == QE_T_STR) ((qe_i32 *)p.out_values[k])[pos] = (qe_i32)f;
     }
 
     static __device__ void emit(const QeParams &p, qe_u64 pos, const Out &o)

@@ -95,7 +95,7 @@ __global__ void qe_generate_kernel(void *values, qe_u32 *validity, int type, int
         const double v = qe_gen_value(kind, seed, g, p0, p1);
         if (type == QE_T_F64) ((double *)values)[r] = v;
         else if (type == QE_T_I64) ((qe_i64 *)values)[r] = (qe_i64)v;
-        else if (type == QE_T_DATE32) ((qe_i32 *)values)[r] = (qe_i32)v;
+        else if (type == QE_T_DATE32 || type == QE_T_STR) ((qe_i32 *)values)[r] = (qe_i32)v;
         else bbits |= (((qe_u64)v) & 1ull ? 1u : 0u) << j;
         const bool valid = qe_splitmix64(~seed ^ (g * 0x9e3779b97f4a7c15ull)) >= null_threshold || null_rate <= 0.0;
         vbits |= (valid ? 1u : 0u) << j;

@@ -16,6 +16,7 @@ const char *op_name(int op)
     if (op == OP_LOAD_COL) return "LOAD_COL";
     if (op == OP_CONST_F64) return "CONST_F64";
     if (op == OP_CONST_BOOL) return "CONST_BOOL";
+    if (op == OP_CONST_STR) return "CONST_STR";
     return "?";
 }
 
@@ -25,7 +26,7 @@ int op_arity(int op)
     switch (op) {
     case OP_IF: return 3;
     case OP_NOT: case OP_UNARY_MINUS: case OP_UNARY_PLUS: return 1;
-    case OP_LOAD_COL: case OP_CONST_F64: case OP_CONST_BOOL: return 0;
+    case OP_LOAD_COL: case OP_CONST_F64: case OP_CONST_BOOL: case OP_CONST_STR: return 0;
     default: return (op >= 0 && op < 17) ? 2 : -1;
     }
 }
@@ -52,6 +53,11 @@ bool parse_program(const uint32_t *words, size_t n, Program &out, std::string &e
             memcpy(&in.k, &bits, sizeof bits);
             pc += 2;
         }
+        if (in.op == OP_CONST_STR) {
+            if (pc + 1 >= n) { err = "CONST_STR truncated"; return false; }
+            in.code = (int32_t)words[pc + 1];
+            pc += 1;
+        }
         if (in.op == OP_CONST_BOOL && in.arg > 1) { err = "CONST_BOOL argument must be 0 or 1"; return false; }
         if (depth < ar) {
             err = std::string("stack underflow at ") + op_name(in.op); return false;
@@ -69,7 +75,7 @@ namespace {
 
 struct TV { VType t; bool nullable; };
 
-const char *vt_name(VType t) { return t == VT_F64 ? "DOUBLE" : t == VT_BOOL ? "BOOLEAN" : "?"; }
+const char *vt_name(VType t) { return t == VT_F64 ? "DOUBLE" : t == VT_BOOL ? "BOOLEAN" : t == VT_STR ? "STRING" : "?"; }
 
 std::string invalid_types(int op, const TV *a, int n)
 {
@@ -84,6 +90,7 @@ VType value_type_of_column(int qtype)
     switch (qtype) {
     case 1: case 3: case 4: return VT_F64;    // DOUBLE, INT64, DATE32 (widened on load)
     case 2: return VT_BOOL;
+    case 0: return VT_STR;                    // dictionary codes
     default: return VT_NONE;
     }
 }
@@ -102,7 +109,7 @@ static int bind_expr(const std::vector<ColumnInfo> &schema, const Program &p, Bo
             if (in.arg >= schema.size()) { err = "column index out of range"; return 2; }
             const ColumnInfo &ci = schema[in.arg];
             const VType t = value_type_of_column(ci.type);
-            if (t == VT_NONE) { err = "STRING columns are not supported on the GPU path"; return 4; }
+            if (t == VT_NONE) { err = "unknown column type"; return 1; }
             int slot = -1;
             for (size_t s = 0; s < bp.slot_table_col.size(); s++)
                 if (bp.slot_table_col[s] == (int)in.arg) slot = (int)s;
@@ -118,6 +125,7 @@ static int bind_expr(const std::vector<ColumnInfo> &schema, const Program &p, Bo
         }
         case OP_CONST_F64: st.push_back({VT_F64, false}); break;
         case OP_CONST_BOOL: st.push_back({VT_BOOL, false}); break;
+        case OP_CONST_STR: st.push_back({VT_STR, false}); break;
         default: {
             const int ar = op_arity(in.op);
             TV a[3];
@@ -138,7 +146,8 @@ static int bind_expr(const std::vector<ColumnInfo> &schema, const Program &p, Bo
                 break;
             case OP_CMP_EQ: case OP_CMP_NE:                               // TypeCheck.kt:65-71
                 if (a[0].t != a[1].t) { err = invalid_types(in.op, a, ar); return 2; }
-                in.arg = a[0].t == VT_BOOL ? 1u : 0u;     // Boolean equality (read by the interpreter kernels)
+                in.arg = a[0].t == VT_BOOL ? 1u : 0u;     // Boolean equality (read by the interpreter kernels); STRING
+                                                          // codes compare like numbers
                 r = {VT_BOOL, a[0].nullable || a[1].nullable};
                 break;
             case OP_CMP_LT: case OP_CMP_LE: case OP_CMP_GE: case OP_CMP_GT:   // TypeCheck.kt:72-78
@@ -188,7 +197,7 @@ int bind_pipeline(const std::vector<ColumnInfo> &schema,
         if (rc) return rc;
         BoundOutput bo;
         if (be.identity_slot >= 0) bo.type = out.slot_info[be.identity_slot].type;   // bare column keeps its physical type
-        else bo.type = be.type == VT_F64 ? 1 : 2;
+        else bo.type = be.type == VT_F64 ? 1 : be.type == VT_BOOL ? 2 : 0;
         bo.has_validity = be.nullable;
         out.proj.push_back(be);
         out.outs.push_back(bo);
@@ -214,7 +223,8 @@ std::string BoundPipeline::signature() const
         for (const Instr &in : e.code) {
             uint64_t kb;
             memcpy(&kb, &in.k, sizeof kb);
-            snprintf(b, sizeof b, "%u.%u.%llx,", in.op, in.arg, (unsigned long long)(in.op == OP_CONST_F64 ? kb : 0));
+            snprintf(b, sizeof b, "%u.%u.%llx,", in.op, in.arg,
+                     (unsigned long long)(in.op == OP_CONST_F64 ? kb : in.op == OP_CONST_STR ? (uint64_t)(uint32_t)in.code : 0));
             s += b;
         }
         s += ';';

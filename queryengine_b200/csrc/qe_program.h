@@ -21,17 +21,20 @@ enum Op : uint8_t {
     OP_AND = 0, OP_OR, OP_IF, OP_NOT, OP_UNARY_MINUS, OP_UNARY_PLUS,
     OP_MUL, OP_DIV, OP_MOD, OP_ADD, OP_SUB,
     OP_CMP_LT, OP_CMP_LE, OP_CMP_GE, OP_CMP_GT, OP_CMP_EQ, OP_CMP_NE,
-    OP_LOAD_COL = 32, OP_CONST_F64 = 33, OP_CONST_BOOL = 34
+    OP_LOAD_COL = 32, OP_CONST_F64 = 33, OP_CONST_BOOL = 34, OP_CONST_STR = 35
 };
 
 const char *op_name(int op);
 int op_arity(int op);          // -1 for unknown opcodes
 
-enum VType : uint8_t { VT_NONE = 0, VT_F64 = 1, VT_BOOL = 2 };   // == reference DataType ordinals
+// VT_F64 / VT_BOOL == reference DataType ordinals; VT_STR is a STRING held as its dictionary code (int32):
+// equal codes <=> equal strings, as long as one dictionary encodes every STRING column and literal of a context
+enum VType : uint8_t { VT_NONE = 0, VT_F64 = 1, VT_BOOL = 2, VT_STR = 3 };
 
 struct Instr {
     uint8_t op = 0;
     uint32_t arg = 0;          // LOAD_COL: column (table index before binding, slot after); CONST_BOOL: 0/1
+    int32_t code = 0;          // CONST_STR: dictionary code of the StringLiteralExpression
     double k = 0.0;            // CONST_F64
 };
 

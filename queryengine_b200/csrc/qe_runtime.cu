@@ -161,7 +161,7 @@ static size_t type_width(int type)
 {
     switch (type) {
     case QE_TYPE_DOUBLE: case QE_TYPE_INT64: return 8;
-    case QE_TYPE_DATE32: return 4;
+    case QE_TYPE_DATE32: case QE_TYPE_STRING: return 4;      // STRING = int32 dictionary codes
     default: return 0;    // BOOLEAN: bitmap
     }
 }
@@ -337,8 +337,7 @@ extern "C" int qe_table_create(qe_ctx *ctx, int ncols, const qe_col_desc *cols, 
     if (nrows < 0 || nrows > 0xffffffffLL)
         return fail(QE_ERR_INVALID_ARGUMENT, "nrows must fit the 32-bit selection vector (shard larger tables by row range)");
     for (int c = 0; c < ncols; c++) {
-        if (cols[c].type == QE_TYPE_STRING) return fail(QE_ERR_UNSUPPORTED, "STRING columns are not supported on the GPU path");
-        if (cols[c].type < 1 || cols[c].type > 4) return fail(QE_ERR_INVALID_ARGUMENT, "unknown column type");
+        if (cols[c].type < 0 || cols[c].type > 4) return fail(QE_ERR_INVALID_ARGUMENT, "unknown column type");
     }
     DeviceGuard g(ctx->device);
     qe_table *t = new qe_table();
@@ -665,6 +664,7 @@ static void serialize_interp(const qe::BoundPipeline &bp, std::vector<uint32_t> 
                 w.push_back((uint32_t)bits);
                 w.push_back((uint32_t)(bits >> 32));
             }
+            if (in.op == qe::OP_CONST_STR) w.push_back((uint32_t)in.code);
         }
         w[at] = (uint32_t)(w.size() - at - 1);
     };

@@ -24,7 +24,43 @@ from . import capi
 from .ast import AggregationFunction, ColumnExpression, DataType, Expression
 from .program import serialize
 
-_NP_OF = {DataType.DOUBLE: np.float64, DataType.INT64: np.int64, DataType.DATE32: np.int32}
+_NP_OF = {DataType.DOUBLE: np.float64, DataType.INT64: np.int64, DataType.DATE32: np.int32, DataType.STRING: np.int32}
+
+
+class StringDictionary:
+    """String <-> int32 code, one per Context.  STRING columns live in HBM as codes and string literals
+    are serialized as codes of the SAME dictionary, so equal codes <=> equal strings -- which is all the
+    reference lets a query do with strings (CMP_EQ / CMP_NE, IF branches, group keys, COUNT:
+    .../evaluator/TypeCheck.kt:65-71,86-94,118-120).  Codes are handed out in first-seen order."""
+
+    def __init__(self):
+        self._code = {}
+        self._strings: List[str] = []
+
+    def __len__(self) -> int:
+        return len(self._strings)
+
+    def encode(self, s: str) -> int:
+        c = self._code.get(s)
+        if c is None:
+            c = len(self._strings)
+            self._code[s] = c
+            self._strings.append(s)
+        return c
+
+    def encode_column(self, values: Sequence[Optional[str]]):
+        """list of str / None -> (int32 codes, bool validity mask)"""
+        codes = np.zeros(len(values), np.int32)
+        valid = np.ones(len(values), bool)
+        for i, s in enumerate(values):
+            if s is None:
+                valid[i] = False
+            else:
+                codes[i] = self.encode(s)
+        return codes, valid
+
+    def decode(self, code: int) -> str:
+        return self._strings[int(code)]
 
 
 def pack_bits(mask) -> np.ndarray:
@@ -43,6 +79,7 @@ class Context:
         self.handle = C.c_void_p()
         capi.check(capi.lib().qe_ctx_create(device, C.byref(self.handle)))
         self.device = device
+        self.dictionary = StringDictionary()
 
     def set_option(self, key: str, value: int) -> None:
         capi.check(capi.lib().qe_ctx_set_option(self.handle, key.encode(), int(value)))
@@ -76,7 +113,7 @@ class Program:
     def __init__(self, ctx: Context, expr: Expression):
         self.ctx = ctx
         self.expr = expr
-        self.words = serialize(expr)
+        self.words = serialize(expr, ctx.dictionary)
         self.handle = C.c_void_p()
         capi.check(capi.lib().qe_program_create(ctx.handle, self.words.ctypes.data, self.words.size, C.byref(self.handle)))
 
@@ -123,6 +160,12 @@ class ColumnarTable:
     def upload(self, col: int, values, valid_mask=None, row0: int = 0) -> None:
         """values: array of the column's type (bool array for BOOLEAN); valid_mask: bool array or None."""
         f = self.fields[col]
+        if f.type == DataType.STRING and not isinstance(values, np.ndarray):
+            values, smask = self.ctx.dictionary.encode_column(values)      # str / None -> codes
+            if valid_mask is None and not smask.all():
+                valid_mask = smask
+            elif valid_mask is not None:
+                valid_mask = np.asarray(valid_mask, dtype=bool) & smask
         if f.type == DataType.BOOLEAN:
             n = len(values)
             data = pack_bits(values)
@@ -418,8 +461,10 @@ class GpuPipelineOperator:
             if self.aggregates:
                 vals = [self._result.agg(k) for k in range(len(self.aggregates))]
                 self._cols = [(np.array([0.0 if v is None else v]), np.array([v is not None])) for v in vals]
+                self._types = [DataType.DOUBLE] * len(vals)
             else:
                 self._cols = [self._result.column(k) for k in range(self._result.num_columns)]
+                self._types = [self._result.column_type(k)[0] for k in range(self._result.num_columns)]
         return self._cols
 
     def next(self):
@@ -436,6 +481,8 @@ class GpuPipelineOperator:
                 row.append(None)
             elif vals.dtype == np.bool_:
                 row.append(bool(vals[i]))
+            elif self._types[k] == DataType.STRING:
+                row.append(self.pipeline.ctx.dictionary.decode(vals[i]))
             elif self.aggregates and self.aggregates[k] == AggregationFunction.COUNT:
                 row.append(int(vals[i]))                       # CountAccumulator.finish() is an Int
             else:

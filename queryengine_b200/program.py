@@ -25,13 +25,14 @@ from .ast import (
 OP_LOAD_COL = 32
 OP_CONST_F64 = 33
 OP_CONST_BOOL = 34
+OP_CONST_STR = 35
 
 
 class UnsupportedExpression(Exception):
-    """The expression cannot run on the GPU path (e.g. STRING literals)."""
+    """The expression cannot run on the GPU path (e.g. a STRING literal without a dictionary)."""
 
 
-def _emit(e: Expression, out: List[int]) -> None:
+def _emit(e: Expression, out: List[int], dictionary=None) -> None:
     if isinstance(e, ColumnExpression):
         if e.index < 0 or e.index >= (1 << 24):
             raise ValueError("column index out of range")
@@ -42,10 +43,14 @@ def _emit(e: Expression, out: List[int]) -> None:
     elif isinstance(e, BooleanLiteralExpression):
         out.append(OP_CONST_BOOL | ((1 if e.value else 0) << 8))
     elif isinstance(e, StringLiteralExpression):
-        raise UnsupportedExpression("STRING expressions are not on the GPU path")
+        # StringLiteralExpression (.../ast/Expressions.kt:29-33) as the code of the context's dictionary:
+        # the same dictionary encodes the STRING columns, so equal codes <=> equal strings
+        if dictionary is None:
+            raise UnsupportedExpression("STRING literals need the context's StringDictionary")
+        out += [OP_CONST_STR, dictionary.encode(e.value) & 0xFFFFFFFF]
     elif isinstance(e, FunctionExpression):
         for o in e.operands:
-            _emit(o, out)
+            _emit(o, out, dictionary)
         out.append(int(e.function))
     else:
         # IdentifierExpression must be resolved before evaluation
@@ -53,7 +58,7 @@ def _emit(e: Expression, out: List[int]) -> None:
         raise TypeError(f"unexpected node {type(e).__name__} during evaluation")
 
 
-def serialize(e: Expression) -> np.ndarray:
+def serialize(e: Expression, dictionary=None) -> np.ndarray:
     words: List[int] = []
-    _emit(e, words)
+    _emit(e, words, dictionary)
     return np.asarray(words, dtype=np.uint32)

@@ -44,16 +44,16 @@ def test_serializer_postfix_words():
     assert np.array([w[2], w[3]], dtype=np.uint32).view(np.float64)[0] == 5.0
     assert list(serialize(lit(True))) == [34 | (1 << 8)]
     with pytest.raises(UnsupportedExpression):
-        serialize(StringLiteralExpression("t"))
+        serialize(StringLiteralExpression("t"))          # no dictionary given
     with pytest.raises(ValueError):
         FunctionExpression(Function.ADD, [lit(1.0)])
 
 
-def _generate(schema, filter_, projs, aggs=(), steps=0, vec=0, compile_=True, staging=-1):
+def _generate(schema, filter_, projs, aggs=(), steps=0, vec=0, compile_=True, staging=-1, dictionary=None):
     L = capi.lib()
     descs = (capi.ColDesc * len(schema))(*[capi.ColDesc(int(t), 1 if n else 0) for t, n in schema])
     exprs = ([filter_] if filter_ is not None else []) + list(projs)
-    words = [serialize(e) for e in exprs]
+    words = [serialize(e, dictionary) for e in exprs]
     ptrs = (C.c_void_p * len(words))(*[w.ctypes.data for w in words])
     lens = (C.c_size_t * len(words))(*[w.size for w in words])
     aggarr = (C.c_int32 * max(1, len(aggs)))(*[int(a) for a in aggs])
@@ -196,3 +196,34 @@ print("ok", nbytes)
 """
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
     assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
+
+
+def test_string_dictionary_codes_in_programs_and_generated_code():
+    # STRING = dictionary codes: the reference's TypeCheck lets strings into CMP_EQ / CMP_NE, IF branches,
+    # bare columns and COUNT only (M/evaluator/TypeCheck.kt:65-71,86-94,118-120)
+    from queryengine_b200.engine import StringDictionary
+    S = DataType.STRING
+    d = StringDictionary()
+    assert [d.encode(x) for x in ("t", "f", "t", "")] == [0, 1, 0, 2] and d.decode(1) == "f" and len(d) == 3
+    codes, valid = d.encode_column(["f", None, "zz"])
+    assert list(codes) == [1, 0, 3] and list(valid) == [True, False, True]
+    assert list(serialize(StringLiteralExpression("f"), d)) == [35, 1]
+    # T/evaluator/CompilerTest.kt:104-120: IF(cond, "t", "f") compiles to a select between two codes
+    e = FunctionExpression(Function.IF, [ColumnExpression("cond", 0, B), StringLiteralExpression("t"), StringLiteralExpression("f")], S)
+    rc, src, nbytes, err = _generate([(B, True)], None, [e], dictionary=d)
+    assert rc == 0, err
+    assert "const qe_i32 t0 = in.c0 ? ((qe_i32)0) : ((qe_i32)1);" in src and "qe_i32 o0;" in src and nbytes > 1000
+    # string equality against a literal and between columns, in the ring filter, with a compacted STRING output
+    f = fn(Function.OR, fn(Function.CMP_EQ, col(0, S), StringLiteralExpression("zz")), fn(Function.CMP_NE, col(0, S), col(1, S)))
+    rc, src, nbytes, err = _generate([(S, True), (S, False)], f, [col(1, S)], dictionary=d)
+    assert rc == 0, err
+    assert "(in.c0 == ((qe_i32)3))" in src and "(in.c0 != in.c1)" in src and "qe_stage1_i32" in src and "qe_filter_ring_body<P>" in src
+    # what TypeCheck rejects is rejected here with its message
+    for bad in (fn(Function.CMP_LT, col(0, S), col(1, S)), fn(Function.ADD, col(0, S), 1.0),
+                fn(Function.CMP_EQ, col(0, S), 1.0), fn(Function.IF, lit(True), col(0, S), 1.0), fn(Function.NOT, col(0, S))):
+        rc, _, _, err = _generate([(S, True), (S, False)], None, [bad], compile_=False, dictionary=d)
+        assert rc == capi.QE_ERR_PROGRAM and "STRING" in err, err
+    rc, _, _, err = _generate([(S, True)], None, [col(0, S)], [AggregationFunction.COUNT], dictionary=d)
+    assert rc == 0, err
+    rc, _, _, err = _generate([(S, True)], None, [col(0, S)], [AggregationFunction.MIN], compile_=False, dictionary=d)
+    assert rc == capi.QE_ERR_PROGRAM

@@ -13,7 +13,7 @@ from parity import TableSpec, compare_aggregation, compare_pipeline, f64_equal, 
 from queryengine_b200 import capi
 from queryengine_b200.ast import (
     AggregationFunction, BooleanLiteralExpression, ColumnExpression, DataType, Function, FunctionExpression,
-    NumericLiteralExpression, col, fn, lit,
+    NumericLiteralExpression, StringLiteralExpression, col, fn, lit,
 )
 from queryengine_b200.engine import ColumnarTable, Context, Field, GpuPipelineOperator, Pipeline
 
@@ -36,6 +36,8 @@ def _rows_table(ctx, fields, rows):
         valid.append(np.array([v is not None for v in vals]))
         if f.type == B:
             cols.append(np.array([bool(v) for v in vals]))
+        elif f.type == DataType.STRING:
+            cols.append(vals)                       # str / None: dictionary-encoded by ColumnarTable.upload
         else:
             cols.append(np.array([0.0 if v is None else v for v in vals], dtype=np.float64))
     return ColumnarTable.from_arrays(ctx, fields, cols, valid)
@@ -442,3 +444,61 @@ def test_mod_fast_path_is_bit_exact(ctx, interpreter):
     spec = TableSpec([Field("a", D, False), Field("b", D, False)], [a, b], [None, None])
     compare_pipeline(ctx, spec, None, [fn(Function.MOD, col(0), col(1)), fn(Function.MOD, col(0), 7.0),
                                        fn(Function.MOD, col(1), col(0))], interpreter=interpreter)
+
+
+# ---------------------------------------------------------------- STRING columns as dictionary codes
+
+S = DataType.STRING
+
+
+@pytest.mark.parametrize("interpreter", [False, True])
+def test_compilertest_if_with_string_literals_golden(ctx, interpreter):
+    # T/evaluator/CompilerTest.kt:104-120, as written there: IF(cond, "t", "f") over true / false / null
+    e = FunctionExpression(Function.IF, [ColumnExpression("cond", 0, B), StringLiteralExpression("t"),
+                                         StringLiteralExpression("f")], S)
+    assert _eval_rows(ctx, [Field("cond", B, True)], [[True], [False], [None]], e, interpreter) == ["t", "f", None]
+
+
+def _string_table(rng, n):
+    vocab = ["a", "b", "B", "", "lineitem", "R", "N", "\u00e4\u00f6", "a "]
+    s0 = [None if rng.random() < 0.2 else vocab[int(rng.integers(len(vocab)))] for _ in range(n)]
+    s1 = [vocab[int(rng.integers(4))] for _ in range(n)]
+    x = np.round(rng.uniform(-10, 10, n), 1)
+    b = rng.random(n) < 0.5
+    bv = rng.random(n) < 0.9
+    rows = [[s0[i], s1[i], float(x[i]), (bool(b[i]) if bv[i] else None)] for i in range(n)]
+    fields = [Field("s0", S, True), Field("s1", S, False), Field("x", D, False), Field("b", B, True)]
+    return fields, rows
+
+
+@pytest.mark.parametrize("interpreter", [False, True])
+@pytest.mark.parametrize("nrows", [0, 1, 777, 20000])
+def test_string_equality_if_and_filter_match_the_oracle(ctx, nrows, interpreter):
+    from oracle_binding import OraclePlan, OracleTable
+    rng = np.random.default_rng(100 + nrows)
+    fields, rows = _string_table(rng, nrows)
+    s0, s1, x, b = col(0, S), col(1, S), col(2), col(3, B)
+    lit_s = StringLiteralExpression
+    projs = [
+        fn(Function.CMP_EQ, s0, s1),
+        fn(Function.CMP_NE, s0, lit_s("b")),
+        fn(Function.IF, fn(Function.CMP_LT, x, 0.0), s0, lit_s("neg")),
+        fn(Function.IF, fn(Function.CMP_EQ, s0, s1), s1, fn(Function.IF, b, lit_s("never seen in a column"), s0)),
+        s0, s1,
+        fn(Function.CMP_EQ, lit_s("a"), lit_s("a")),
+    ]
+    filters = [None,
+               fn(Function.OR, fn(Function.CMP_EQ, s0, lit_s("a")), fn(Function.CMP_NE, s1, s0)),
+               fn(Function.AND, fn(Function.CMP_NE, s0, lit_s("")), b)]
+    otable = OracleTable.from_rows([f.type for f in fields], rows) if nrows else None
+    t = _rows_table(ctx, fields, rows) if nrows else ColumnarTable(ctx, fields, 0)
+    for f in filters:
+        got = GpuPipelineOperator(t, f, projs, None, interpreter=interpreter).map()
+        want = OraclePlan(otable, [0, 1, 2, 3], filter=f, projections=projs).rows() if nrows else []
+        assert got == want, (f, next((g, w) for g, w in zip(got, want) if g != w) if len(got) == len(want) else (len(got), len(want)))
+    # COUNT over a STRING expression skips nulls (GlobalAggregationOperator.kt:16-21, TypeCheck.kt:118-120)
+    if nrows:
+        got = GpuPipelineOperator(t, filters[2], [projs[2], s0], [A.COUNT, A.COUNT], interpreter=interpreter).map()
+        want = OraclePlan(otable, [0, 1, 2, 3], filter=filters[2], projections=[projs[2], s0], aggregates=[A.COUNT, A.COUNT]).rows()
+        assert got == want
+    t.close()
