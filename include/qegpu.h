@@ -219,6 +219,41 @@ typedef struct qe_stream_desc {
 } qe_stream_desc;
 QE_API int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_desc *desc);
 
+/* ---- group-by: stands in for Scan -> [Filter] -> Projection -> GroupByAggregationOperator
+ *      (M/operator/GroupByAggregationOperator.kt:21-75; the plan RewriteAggregates builds,
+ *      M/evaluator/RewriteAggregates.kt:18-49: every non-aggregate select expression is a key).
+ *      A row's key is the tuple of its `keys` values; keys compare like the reference's boxed
+ *      values (Double.equals: NaN == NaN, -0.0 != 0.0; null is a key value like any other; STRING
+ *      by dictionary code).  Accumulator k of a group takes `inputs[k]`, nulls skipped.  The
+ *      result has one row per group, in order of first appearance (LinkedHashMap), with the
+ *      nkeys key columns first and then the nagg aggregates (DOUBLE; NULL as finish() would
+ *      return null); read it with qe_result_num_rows / qe_result_column.  The call is
+ *      synchronous.  Few groups (what fits a CTA's shared memory) accumulate in
+ *      per-thread private copies and are combined in a fixed order, so results are reproducible;
+ *      otherwise global atomics are used (SUM / AVG then depend on the order of additions,
+ *      within the tolerance stated for SUM).  Needs NVRTC. */
+typedef struct qe_groupby_desc {
+    const qe_program *filter;          /* may be NULL */
+    const qe_program *const *keys;     /* group key expressions */
+    int32_t nkeys;                     /* 0..8 */
+    const qe_program *const *inputs;   /* aggregate input expressions */
+    const int32_t *agg_fns;            /* qe_agg_fn of each input */
+    int32_t nagg;                      /* nkeys + nagg <= 16 */
+    int64_t row_begin;                 /* rows [row_begin, row_end); row_begin % 128 == 0 */
+    int64_t row_end;                   /* -1 = to the end of the table */
+    int64_t max_groups;                /* capacity of the group table; 0 = 65536.  QE_ERR_CAPACITY when exceeded */
+    uint32_t flags;                    /* QE_GROUPBY_* */
+} qe_groupby_desc;
+enum {
+    QE_GROUPBY_ATOMIC = 1u << 0        /* skip the private-accumulator variant */
+};
+QE_API int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_groupby_desc *desc, qe_result **result);
+/* per-group partial aggregates and first rows, for combining row-range partitions by key on the host */
+QE_API int qe_result_group_partial(qe_result *result, int64_t group, int k, qe_agg_partial *out);
+QE_API int qe_result_group_first_rows(qe_result *result, int64_t *dst);
+/* 0: private accumulators (reproducible), 1: global atomics, -1: not a group-by result */
+QE_API int qe_result_group_variant(const qe_result *result);
+
 /* ---- results ------------------------------------------------------------- */
 /* rows the pipeline emitted (kept rows; 1 for an aggregation).  Waits for the run. */
 QE_API int qe_result_num_rows(qe_result *result, int64_t *nrows);
@@ -258,6 +293,12 @@ QE_API int qe_debug_generate(const qe_col_desc *cols, int ncols,
                              int has_filter, int nproj, const int32_t *agg_fns, int nagg,
                              int steps, int vec, int staging, int compile,
                              char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes);
+
+/* Same for a group-by: programs = [filter,] nkeys key programs, nagg aggregate inputs; atomic: which variant. */
+QE_API int qe_debug_generate_groupby(const qe_col_desc *cols, int ncols,
+                                     const uint32_t *const *programs, const size_t *nwords,
+                                     int has_filter, int nkeys, const int32_t *agg_fns, int nagg, int atomic, int compile,
+                                     char *src_buf, size_t src_cap, size_t *cubin_bytes);
 
 QE_API const char *qe_last_error(void);
 QE_API const char *qe_version(void);

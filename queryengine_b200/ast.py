@@ -147,6 +147,19 @@ class FunctionExpression(Expression):
             raise ValueError(f"{self.function.name} takes {self.function.arity} operands, got {len(self.operands)}")
 
 
+@dataclass(frozen=True)
+class AggregationFunctionExpression(Expression):
+    """AggregationFunctionExpression(function, operands) (Expressions.kt:47-57); one operand."""
+    function: AggregationFunction
+    operands: Tuple[Expression, ...]
+
+    def __init__(self, function: AggregationFunction, operands: Sequence[Expression]):
+        object.__setattr__(self, "function", AggregationFunction(function))
+        object.__setattr__(self, "operands", tuple(operands))
+        if len(self.operands) != 1:
+            raise ValueError("aggregation functions take one operand")
+
+
 # ---- small construction helpers used by tests and the bench harness -------
 
 def col(index: int, dtype: DataType = DataType.DOUBLE, name: Optional[str] = None) -> ColumnExpression:
@@ -163,6 +176,10 @@ def lit(v) -> Expression:
 
 def fn(function: Function, *ops) -> FunctionExpression:
     return FunctionExpression(function, [o if isinstance(o, Expression) else lit(o) for o in ops])
+
+
+def agg(function: AggregationFunction, operand) -> AggregationFunctionExpression:
+    return AggregationFunctionExpression(function, [operand if isinstance(operand, Expression) else lit(operand)])
 
 
 def walk(e: Expression):

@@ -24,6 +24,7 @@ QE_ERR_STATE = 7
 QE_RUN_NO_SELECTION = 1
 QE_RUN_INTERPRETER = 2
 QE_RUN_APPEND = 4
+QE_GROUPBY_ATOMIC = 1
 
 QE_GEN_UNIFORM_U40 = 0
 QE_GEN_UNIFORM_INT = 1
@@ -57,6 +58,21 @@ class PipelineDesc(C.Structure):
         ("row_begin", C.c_int64),
         ("row_end", C.c_int64),
         ("out_capacity_rows", C.c_int64),
+        ("flags", C.c_uint32),
+    ]
+
+
+class GroupByDesc(C.Structure):
+    _fields_ = [
+        ("filter", C.c_void_p),
+        ("keys", C.POINTER(C.c_void_p)),
+        ("nkeys", C.c_int32),
+        ("inputs", C.POINTER(C.c_void_p)),
+        ("agg_fns", C.POINTER(C.c_int32)),
+        ("nagg", C.c_int32),
+        ("row_begin", C.c_int64),
+        ("row_end", C.c_int64),
+        ("max_groups", C.c_int64),
         ("flags", C.c_uint32),
     ]
 
@@ -113,6 +129,13 @@ SYMBOLS = {
     "qe_debug_generate": (C.c_int, [C.POINTER(ColDesc), C.c_int, C.POINTER(_vp), C.POINTER(C.c_size_t), C.c_int, C.c_int,
                                     C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "qe_debug_generate_groupby": (C.c_int, [C.POINTER(ColDesc), C.c_int, C.POINTER(_vp), C.POINTER(C.c_size_t), C.c_int, C.c_int,
+                                            C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_size_t,
+                                            C.POINTER(C.c_size_t)]),
+    "qe_groupby_run": (C.c_int, [_vp, _vp, C.POINTER(GroupByDesc), C.POINTER(_vp)]),
+    "qe_result_group_partial": (C.c_int, [_vp, C.c_int64, C.c_int, C.POINTER(AggPartial)]),
+    "qe_result_group_first_rows": (C.c_int, [_vp, _vp]),
+    "qe_result_group_variant": (C.c_int, [_vp]),
     "qe_last_error": (C.c_char_p, []),
     "qe_version": (C.c_char_p, []),
 }

@@ -1,6 +1,7 @@
 // qe_codegen.cpp -- see qe_codegen.h
 #include "qe_codegen.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -299,6 +300,34 @@ size_t staged_smem_bytes(const BoundPipeline &bp, const TileShape &shape)
     return (size_t)stage_layout(bp, shape).stride * (size_t)shape.nstages;
 }
 
+GroupPlan plan_groupby(const BoundPipeline &bp)
+{
+    GroupPlan g;
+    g.nkeys = bp.group_keys > 0 ? bp.group_keys : 0;
+    auto word = [&](int kind, unsigned long long init) {
+        g.kind.push_back(kind);
+        g.init.push_back(init);
+        return (int)g.kind.size() - 1;
+    };
+    word(4, ~0ULL);                          // first row: min over u64
+    word(1, 0);                              // rows of the group
+    for (size_t k = 0; k < bp.agg_fns.size(); k++) {
+        const int fn = bp.agg_fns[k];
+        int vw = -1;
+        if (fn == 2 || fn == 4) vw = word(0, 0);                                   // SUM / AVG: 0.0, Accumulators.kt:40,93
+        else if (fn == 0) vw = word(2, 0x7ff0000000000000ULL);                     // MIN: +Infinity, :57
+        else if (fn == 1) vw = word(3, 0xfff0000000000000ULL);                     // MAX: -Infinity, :75
+        g.val_word.push_back(vw);
+        g.cnt_word.push_back(bp.proj[(size_t)g.nkeys + k].nullable ? word(1, 0) : 1);
+    }
+    g.nwords = (int)g.kind.size();
+    const size_t per_group = (size_t)g.nwords * 256u * 8u;
+    g.lmax = (int)std::min<size_t>(64, (200u << 10) / per_group);
+    g.cslots = 2;
+    while (g.cslots < 2 * g.lmax) g.cslots *= 2;
+    return g;
+}
+
 std::string generate_source(const BoundPipeline &bp, KernelMode mode, const TileShape &shape)
 {
     std::string s;
@@ -311,7 +340,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     // bit columns of the outputs (validity bitmaps and BOOLEAN values)
     struct BitCol { std::string ptr, bit; };
     std::vector<BitCol> bitcols;
-    if (mode != KM_AGG) {
+    const bool is_group = mode == KM_GROUPBY_PRIVATE || mode == KM_GROUPBY_ATOMIC;
+    if (mode != KM_AGG && !is_group) {
         for (int k = 0; k < nproj; k++) {
             if (bp.outs[k].has_validity) {
                 snprintf(b, sizeof b, "p.out_valid[%d]", k);
@@ -516,7 +546,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         }
         s += "    }\n";
     }
-    if (mode != KM_AGG) {
+    if (mode != KM_AGG && !is_group) {
         s += "    static __device__ __forceinline__ qe_u32 *bitcol(const QeParams &p, int b) {\n        switch (b) {\n";
         for (size_t i = 0; i < bitcols.size(); i++) {
             snprintf(b, sizeof b, "        case %d: return ", (int)i); s += b; s += bitcols[i].ptr + ";\n";
@@ -557,9 +587,96 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         }
         s += "    }\n";
     }
+    if (is_group) {
+        // GroupByAggregationOperator.open (M/operator/GroupByAggregationOperator.kt:21-48): key = the first
+        // NKEYS values of the row, accumulator i takes value NKEYS + i, nulls are skipped
+        const GroupPlan gp = plan_groupby(bp);
+        snprintf(b, sizeof b, "    static constexpr int NKEYS = %d, NWORDS = %d, LMAX = %d, CSLOTS = %d;\n", gp.nkeys > 0 ? gp.nkeys : 1,
+                 gp.nwords, gp.lmax > 0 ? gp.lmax : 1, gp.cslots);
+        s += b;
+        s += "    static __device__ __forceinline__ void key_pack(const Out &o, qe_u64 (&k)[NKEYS], qe_u32 &nulls) {\n        nulls = 0u;\n";
+        if (gp.nkeys == 0) s += "        k[0] = 0ull;\n";
+        for (int i = 0; i < gp.nkeys; i++) {
+            const int t = bp.outs[i].type;
+            if (t == 1) snprintf(b, sizeof b, "        k[%d] = qe_key_f64(o.o%d);\n", i, i);
+            else if (t == 2) snprintf(b, sizeof b, "        k[%d] = o.o%d ? 1ull : 0ull;\n", i, i);
+            else snprintf(b, sizeof b, "        k[%d] = (qe_u64)(qe_i64)o.o%d;\n", i, i);
+            s += b;
+            if (bp.proj[i].nullable) {
+                snprintf(b, sizeof b, "        if (!o.n%d) { k[%d] = 0ull; nulls |= %uu; }\n", i, i, 1u << i);
+                s += b;
+            }
+        }
+        s += "    }\n";
+        s += "    static __device__ __forceinline__ qe_u64 word_init(int w) {\n        switch (w) {\n";
+        for (int w = 0; w < gp.nwords; w++) {
+            snprintf(b, sizeof b, "        case %d: return 0x%llxull;\n", w, gp.init[w]); s += b;
+        }
+        s += "        }\n        return 0ull;\n    }\n";
+        s += "    static __device__ __forceinline__ int word_kind(int w) {\n        switch (w) {\n";
+        for (int w = 0; w < gp.nwords; w++) {
+            snprintf(b, sizeof b, "        case %d: return %d;\n", w, gp.kind[w]); s += b;
+        }
+        s += "        }\n        return 1;\n    }\n";
+        // value and validity of aggregate input j
+        auto agg_val = [&](int j) {
+            const int k = gp.nkeys + j;
+            char v[64];
+            if (bp.outs[k].type == 1) snprintf(v, sizeof v, "o.o%d", k);
+            else if (bp.outs[k].type == 3) snprintf(v, sizeof v, "qe_i64_to_f64(o.o%d)", k);
+            else if (bp.outs[k].type == 4) snprintf(v, sizeof v, "qe_i32_to_f64(o.o%d)", k);
+            else snprintf(v, sizeof v, "0.0");
+            return std::string(v);
+        };
+        for (int variant = 0; variant < 2; variant++) {
+            const bool atomic = variant == 1;
+            s += atomic ? "    static __device__ __forceinline__ void acc_atomic(qe_u64 *a, const Out &o, qe_u64 row) {\n"
+                        : "    static __device__ __forceinline__ void acc_private(qe_u64 *a, const Out &o, qe_u64 row) {\n"
+                          "        constexpr size_t WS = (size_t)LMAX * QE_BLOCK;\n";
+            auto at = [&](int w) {
+                char a[48];
+                if (atomic) snprintf(a, sizeof a, "a + %d", w);
+                else snprintf(a, sizeof a, "a[%d * WS]", w);
+                return std::string(a);
+            };
+            if (atomic) {
+                s += "        atomicMin((unsigned long long *)a, (unsigned long long)row);\n";
+                s += "        atomicAdd((unsigned long long *)(a + 1), 1ull);\n";
+            } else {
+                s += "        a[0] = row < a[0] ? row : a[0];\n";
+                s += "        a[WS] += 1ull;\n";
+            }
+            for (size_t j = 0; j < bp.agg_fns.size(); j++) {
+                const int fn = bp.agg_fns[j];
+                const int k = gp.nkeys + (int)j;
+                const int vw = gp.val_word[j], cw = gp.cnt_word[j];
+                std::string guard;
+                if (bp.proj[k].nullable) { snprintf(b, sizeof b, "if (o.n%d) ", k); guard = b; }
+                std::string stmts;
+                const std::string v = agg_val((int)j);
+                if (vw >= 0) {
+                    if (atomic) {
+                        if (fn == 2 || fn == 4) stmts += "atomicAdd((double *)(" + at(vw) + "), " + v + "); ";
+                        else if (fn == 0) stmts += "qe_atomic_min_f64(" + at(vw) + ", " + v + "); ";
+                        else stmts += "qe_atomic_max_f64(" + at(vw) + ", " + v + "); ";
+                    } else {
+                        const char *f = (fn == 2 || fn == 4) ? "qe_add" : fn == 0 ? "qe_math_min" : "qe_math_max";
+                        stmts += at(vw) + " = (qe_u64)qe_f64_bits(" + f + "(qe_bits_f64((qe_i64)" + at(vw) + "), " + v + ")); ";
+                    }
+                }
+                if (cw != 1) {
+                    if (atomic) stmts += "atomicAdd((unsigned long long *)(" + at(cw) + "), 1ull); ";
+                    else stmts += at(cw) + " += 1ull; ";
+                }
+                if (!stmts.empty()) s += "        " + guard + "{ " + stmts + "}\n";
+            }
+            s += "    }\n";
+        }
+    }
     s += "};\n\n";
     const char *body = mode == KM_FILTER ? (shape.ring ? "qe_filter_ring_body" : shape.staged ? "qe_filter_staged_body" : shape.pipelined ? "qe_filter_pipelined_body" : "qe_filter_body")
-                     : mode == KM_PROJECT ? "qe_project_body" : "qe_agg_body";
+                     : mode == KM_PROJECT ? "qe_project_body" : mode == KM_AGG ? "qe_agg_body"
+                     : mode == KM_GROUPBY_PRIVATE ? "qe_groupby_private_body" : "qe_groupby_atomic_body";
     snprintf(b, sizeof b,
              "extern \"C\" __global__ void __launch_bounds__(%d, %d) " QE_JIT_ENTRY
              "(const __grid_constant__ QeParams p)\n{\n    %s<P>(p);\n}\n",

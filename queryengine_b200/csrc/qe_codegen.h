@@ -11,12 +11,26 @@
 #define QE_CODEGEN_H
 
 #include <string>
+#include <vector>
 
 #include "qe_program.h"
 
 namespace qe {
 
-enum KernelMode { KM_FILTER = 0, KM_PROJECT = 1, KM_AGG = 2 };
+enum KernelMode { KM_FILTER = 0, KM_PROJECT = 1, KM_AGG = 2, KM_GROUPBY_PRIVATE = 3, KM_GROUPBY_ATOMIC = 4 };
+
+// Accumulator words of one group (qe_device.cuh, "group-by"): word 0 = first row (min), word 1 = rows of the
+// group, then per aggregate a value word (SUM / AVG / MIN / MAX) and, when its input can be null, its own
+// count of non-null inputs (otherwise the group's row count is that count).
+struct GroupPlan {
+    int nkeys = 0, nwords = 0;
+    std::vector<int> kind;                 // QE_GK_* of every word
+    std::vector<unsigned long long> init;  // initial bits of every word
+    std::vector<int> val_word, cnt_word;   // per aggregate; val_word = -1 for COUNT
+    int lmax = 0, cslots = 0;              // private variant: groups per CTA that fit shared memory, key-cache slots
+    size_t private_smem() const { return (size_t)nwords * (size_t)lmax * 256u * 8u; }
+};
+GroupPlan plan_groupby(const BoundPipeline &bp);
 
 struct TileShape {
     int steps = 2;          // steps per warp per tile

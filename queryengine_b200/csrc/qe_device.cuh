@@ -84,6 +84,16 @@ struct QeParams {
     qe_i64        out_capacity;               // rows the compacted outputs can hold
     qe_u32        ntiles;
     qe_u32        sel_base;                   // table row index of the batch's first row
+    // group-by (qe_groupby_*_body): open-addressing table of the groups seen so far, in HBM
+    qe_u32       *g_state;                    // [slots] 0 empty, 1 key being written, 2 ready
+    qe_u64       *g_keys;                     // [slots][NKEYS] canonical key bits
+    qe_u32       *g_nulls;                    // [slots] bit i: key i is null
+    qe_u64       *g_acc;                      // [slots][NWORDS] accumulator words (word 0 = first row, word 1 = rows)
+    qe_u32       *g_ctl;                      // [0] groups claimed  [1] overflow flags (1 private capacity, 2 table capacity)
+    qe_u64       *g_part;                     // private variant: [grid][LMAX][NWORDS] per-CTA partial accumulators
+    qe_u32       *g_part_slot;                // private variant: [grid][1 + LMAX]: local groups, then the table slot of each
+    qe_u32        g_slot_mask;                // slots - 1 (a power of two)
+    qe_u32        g_max_groups;
 };
 
 // ---------------------------------------------------------------- memory ops
@@ -1511,6 +1521,288 @@ __device__ __forceinline__ void qe_agg_body(const QeParams &p)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) kept += __shfl_down_sync(QE_FULL_MASK, kept, o);
     if (qe_lane() == 0 && kept) atomicAdd((unsigned long long *)p.out_count, (unsigned long long)kept);
+}
+
+// ------------------------------------------------------------------ group-by
+// GroupByAggregationOperator (M/operator/GroupByAggregationOperator.kt:21-75): a LinkedHashMap from the
+// key columns of a row (boxed values compared with contentEquals: Double.equals, so NaN == NaN and
+// -0.0 != 0.0; null is a key value like any other) to one Accumulator per aggregate; nulls are skipped
+// (:38-43); rows come out in order of first appearance.
+//
+// Here: the groups live in an open-addressing table in HBM (g_state / g_keys / g_nulls), keyed by the
+// canonical bits of the key values.  Accumulators are 8-byte words; word 0 is the smallest row index of the
+// group (first appearance), word 1 its row count, then what the aggregates need.  Two kernel bodies:
+//   qe_groupby_private_body  few groups: every THREAD owns a private copy of the accumulator words of up
+//                            to LMAX groups in shared memory (no atomics, no conflicts: lane-consecutive
+//                            words), a shared-memory key cache maps key -> local group; a fixed-order
+//                            reduce per CTA and a fixed-order merge over the CTAs follow, so the result
+//                            does not depend on scheduling.
+//   qe_groupby_atomic_body   any number of groups: global atomics on g_acc (SUM order not reproducible).
+// What a group-by program P adds to load / eval:
+//   static constexpr int NKEYS, NWORDS, LMAX, CSLOTS;
+//   static void key_pack(const Out&, qe_u64 (&k)[NKEYS], qe_u32 &nulls);
+//   static qe_u64 word_init(int w);  static int word_kind(int w);
+//   static void acc_private(qe_u64 *a, const Out&, qe_u64 row);    word w of this thread's copy at a[w * LMAX * QE_BLOCK]
+//   static void acc_atomic(qe_u64 *a, const Out&, qe_u64 row);     word w at a[w]
+#define QE_GK_ADD_F64 0
+#define QE_GK_ADD_I64 1
+#define QE_GK_MIN_F64 2
+#define QE_GK_MAX_F64 3
+#define QE_GK_MIN_U64 4
+
+// Double.equals / hashCode compare doubleToLongBits: one NaN, and -0.0 differs from 0.0
+__device__ __forceinline__ qe_u64 qe_key_f64(double x)
+{
+    return x != x ? 0x7ff8000000000000ULL : (qe_u64)qe_f64_bits(x);
+}
+
+__device__ __forceinline__ qe_u64 qe_group_combine(int kind, qe_u64 a, qe_u64 b)
+{
+    switch (kind) {
+    case QE_GK_ADD_F64: return (qe_u64)qe_f64_bits(qe_add(qe_bits_f64((qe_i64)a), qe_bits_f64((qe_i64)b)));
+    case QE_GK_ADD_I64: return a + b;
+    case QE_GK_MIN_F64: return (qe_u64)qe_f64_bits(qe_math_min(qe_bits_f64((qe_i64)a), qe_bits_f64((qe_i64)b)));
+    case QE_GK_MAX_F64: return (qe_u64)qe_f64_bits(qe_math_max(qe_bits_f64((qe_i64)a), qe_bits_f64((qe_i64)b)));
+    default:            return a < b ? a : b;
+    }
+}
+
+template <int NKEYS>
+__device__ __forceinline__ qe_u32 qe_group_hash(const qe_u64 (&k)[NKEYS], qe_u32 nulls)
+{
+    qe_u64 h = 0x9e3779b97f4a7c15ULL ^ (qe_u64)nulls;
+#pragma unroll
+    for (int i = 0; i < NKEYS; i++) {
+        h = (h ^ k[i]) * 0xff51afd7ed558ccdULL;
+        h ^= h >> 32;
+    }
+    return (qe_u32)h;
+}
+
+__device__ __forceinline__ qe_u32 qe_ld_acquire_u32(const qe_u32 *p)
+{
+    qe_u32 v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void qe_st_release_u32(qe_u32 *p, qe_u32 v)
+{
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Slot of the key in the global table, inserting it if it is new.  -1: the table is full.
+// Shape of the loop: no thread leaves it from inside the branch that holds a half-written slot -- every
+// lane runs to the end of the iteration, so a lane that waits for a slot owned by another lane of its own
+// warp cannot keep that lane from finishing (the usual intra-warp spin-lock hazard).  Spins are bounded:
+// a run that hits the bound is discarded through the overflow flags instead of hanging the device.
+template <int NKEYS>
+__device__ __noinline__ int qe_group_global_slot(const QeParams &p, const qe_u64 (&k)[NKEYS], qe_u32 nulls, qe_u32 h)
+{
+    qe_u32 s = h & p.g_slot_mask;
+    qe_u32 probe = 0, spins = 0;
+    int found = -2;
+    while (found == -2) {
+        const qe_u32 st = qe_ld_acquire_u32(p.g_state + s);
+        if (st == 2u) {
+            bool same = p.g_nulls[s] == nulls;
+#pragma unroll
+            for (int i = 0; i < NKEYS; i++) same = same && p.g_keys[(size_t)s * NKEYS + i] == k[i];
+            if (same) {
+                found = (int)s;
+            } else {
+                s = (s + 1u) & p.g_slot_mask;
+                if (++probe > p.g_slot_mask) found = -1;
+            }
+        } else if (st == 0u) {
+            if (atomicCAS(p.g_state + s, 0u, 1u) == 0u) {
+                if (atomicAdd(p.g_ctl, 1u) >= p.g_max_groups) atomicOr(p.g_ctl + 1, 2u);   // over the limit: the run is discarded
+#pragma unroll
+                for (int i = 0; i < NKEYS; i++) p.g_keys[(size_t)s * NKEYS + i] = k[i];
+                p.g_nulls[s] = nulls;
+                qe_st_release_u32(p.g_state + s, 2u);
+                found = (int)s;
+            }
+        } else if (++spins > (1u << 24)) {
+            found = -1;                                       // the key of this slot never got published
+        }
+    }
+    if (found < 0) atomicOr(p.g_ctl + 1, 2u);
+    return found;
+}
+
+template <class P>
+__device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
+{
+    constexpr int STEPS = P::STEPS, VEC = P::VEC, NKEYS = P::NKEYS, NWORDS = P::NWORDS, LMAX = P::LMAX, CS = P::CSLOTS;
+    constexpr int WARP_ROWS = STEPS * 32 * VEC;
+    constexpr int TILE = QE_WARPS * WARP_ROWS;
+    extern __shared__ __align__(16) unsigned char qe_gsmem[];
+    qe_u64 *s_acc = (qe_u64 *)qe_gsmem;                       // [NWORDS][LMAX][QE_BLOCK]
+    __shared__ qe_u64 c_keys[CS][NKEYS];
+    __shared__ qe_u32 c_nulls[CS];
+    __shared__ int c_local[CS];
+    __shared__ qe_u32 c_state[CS];
+    __shared__ qe_u32 l_slot[LMAX];
+    __shared__ qe_u32 s_nlocal, s_over;
+    const qe_u32 warp = qe_warp(), lane = qe_lane(), tid = threadIdx.x;
+
+    for (int i = (int)tid; i < CS; i += QE_BLOCK) c_state[i] = 0u;
+    if (tid == 0) { s_nlocal = 0u; s_over = 0u; }
+#pragma unroll 1
+    for (int w = 0; w < NWORDS; w++) {
+        const qe_u64 init = P::word_init(w);
+#pragma unroll 1
+        for (int l = 0; l < LMAX; l++) s_acc[((size_t)w * LMAX + l) * QE_BLOCK + tid] = init;
+    }
+    __syncthreads();
+
+    for (qe_u32 tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+        const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
+        typename P::Out outs[STEPS][VEC];
+        qe_u32 keep[STEPS], inb[STEPS];
+        qe_tile_eval<P>(p, warp_row0, outs, keep, inb);
+#pragma unroll
+        for (int s = 0; s < STEPS; s++) {
+#pragma unroll
+            for (int j = 0; j < VEC; j++) {
+                if (!((keep[s] >> j) & 1u)) continue;
+                qe_u64 k[NKEYS];
+                qe_u32 nulls;
+                P::key_pack(outs[s][j], k, nulls);
+                // ---- key -> local group, through the CTA's key cache (same loop shape as qe_group_global_slot)
+                int l = -1;
+                const qe_u32 h = qe_group_hash<NKEYS>(k, nulls);
+                qe_u32 c = h & (qe_u32)(CS - 1);
+                int probe = 0;
+                qe_u32 spins = 0;
+                bool done = false;
+                while (!done) {
+                    const qe_u32 st = *(volatile qe_u32 *)&c_state[c];
+                    if (*(volatile qe_u32 *)&s_over) {
+                        done = true;                          // the run is discarded anyway
+                    } else if (st == 2u) {
+                        bool same = c_nulls[c] == nulls;
+#pragma unroll
+                        for (int i = 0; i < NKEYS; i++) same = same && c_keys[c][i] == k[i];
+                        if (same) {
+                            l = c_local[c];
+                            done = true;
+                        } else {
+                            c = (c + 1u) & (qe_u32)(CS - 1);
+                            if (++probe >= CS) { *(volatile qe_u32 *)&s_over = 1u; done = true; }
+                        }
+                    } else if (st == 0u) {
+                        if (atomicCAS(&c_state[c], 0u, 1u) == 0u) {
+#pragma unroll
+                            for (int i = 0; i < NKEYS; i++) c_keys[c][i] = k[i];
+                            c_nulls[c] = nulls;
+                            int nl = (int)atomicAdd(&s_nlocal, 1u);
+                            if (nl >= LMAX) {
+                                *(volatile qe_u32 *)&s_over = 1u;
+                                nl = -1;
+                            } else {
+                                const int gs = qe_group_global_slot<NKEYS>(p, k, nulls, h);
+                                l_slot[nl] = gs < 0 ? 0xffffffffu : (qe_u32)gs;
+                            }
+                            c_local[c] = nl;
+                            __threadfence_block();
+                            *(volatile qe_u32 *)&c_state[c] = 2u;
+                            l = nl;
+                            done = true;
+                        }
+                    } else if (++spins > (1u << 24)) {
+                        *(volatile qe_u32 *)&s_over = 1u;
+                        done = true;
+                    }
+                }
+                if (l >= 0) {
+                    const qe_u64 row = (qe_u64)p.sel_base + (qe_u64)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j);
+                    P::acc_private(s_acc + (size_t)l * QE_BLOCK + tid, outs[s][j], row);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    // ---- fixed-order reduce of the 256 private copies: (group, word) pairs round-robin over the warps
+    const int nlocal = (int)(s_nlocal < (qe_u32)LMAX ? s_nlocal : (qe_u32)LMAX);
+    for (int idx = (int)warp; idx < nlocal * NWORDS; idx += QE_WARPS) {
+        const int l = idx / NWORDS, w = idx - l * NWORDS;
+        const int kind = P::word_kind(w);
+        const qe_u64 *src = s_acc + ((size_t)w * LMAX + l) * QE_BLOCK;
+        qe_u64 v = src[lane];
+#pragma unroll
+        for (int q = 1; q < QE_WARPS; q++) v = qe_group_combine(kind, v, src[lane + 32 * q]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const qe_u64 b = (qe_u64)__shfl_down_sync(QE_FULL_MASK, (unsigned long long)v, o);
+            v = qe_group_combine(kind, v, b);
+        }
+        if (lane == 0) p.g_part[((size_t)blockIdx.x * LMAX + l) * NWORDS + w] = v;
+    }
+    qe_u32 *ps = p.g_part_slot + (size_t)blockIdx.x * (1 + LMAX);
+    if (tid == 0) {
+        ps[0] = (qe_u32)nlocal;
+        if (s_over) atomicOr(p.g_ctl + 1, 1u);
+    }
+    if ((int)tid < nlocal) ps[1 + tid] = l_slot[tid];
+}
+
+template <class P>
+__device__ __forceinline__ void qe_groupby_atomic_body(const QeParams &p)
+{
+    constexpr int STEPS = P::STEPS, VEC = P::VEC, NKEYS = P::NKEYS, NWORDS = P::NWORDS;
+    constexpr int WARP_ROWS = STEPS * 32 * VEC;
+    constexpr int TILE = QE_WARPS * WARP_ROWS;
+    const qe_u32 warp = qe_warp(), lane = qe_lane();
+    for (qe_u32 tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+        const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
+        typename P::Out outs[STEPS][VEC];
+        qe_u32 keep[STEPS], inb[STEPS];
+        qe_tile_eval<P>(p, warp_row0, outs, keep, inb);
+#pragma unroll
+        for (int s = 0; s < STEPS; s++) {
+#pragma unroll
+            for (int j = 0; j < VEC; j++) {
+                if (!((keep[s] >> j) & 1u)) continue;
+                qe_u64 k[NKEYS];
+                qe_u32 nulls;
+                P::key_pack(outs[s][j], k, nulls);
+                const int gs = qe_group_global_slot<NKEYS>(p, k, nulls, qe_group_hash<NKEYS>(k, nulls));
+                if (gs >= 0) {
+                    const qe_u64 row = (qe_u64)p.sel_base + (qe_u64)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j);
+                    P::acc_atomic(p.g_acc + (size_t)gs * NWORDS, outs[s][j], row);
+                }
+            }
+        }
+    }
+}
+
+// atomics on accumulator words with the accumulators' semantics (Math.min / Math.max: NaN wins, -0.0 < 0.0)
+__device__ __forceinline__ void qe_atomic_min_f64(qe_u64 *a, double v)
+{
+    unsigned long long old = *(volatile unsigned long long *)a;
+    for (;;) {
+        const double cur = qe_bits_f64((qe_i64)old);
+        const double nv = qe_math_min(cur, v);
+        if ((unsigned long long)qe_f64_bits(nv) == old) return;
+        const unsigned long long seen = atomicCAS((unsigned long long *)a, old, (unsigned long long)qe_f64_bits(nv));
+        if (seen == old) return;
+        old = seen;
+    }
+}
+
+__device__ __forceinline__ void qe_atomic_max_f64(qe_u64 *a, double v)
+{
+    unsigned long long old = *(volatile unsigned long long *)a;
+    for (;;) {
+        const double cur = qe_bits_f64((qe_i64)old);
+        const double nv = qe_math_max(cur, v);
+        if ((unsigned long long)qe_f64_bits(nv) == old) return;
+        const unsigned long long seen = atomicCAS((unsigned long long *)a, old, (unsigned long long)qe_f64_bits(nv));
+        if (seen == old) return;
+        old = seen;
+    }
 }
 
 #endif  // QE_DEVICE_CUH

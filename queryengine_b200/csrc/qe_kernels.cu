@@ -104,6 +104,53 @@ __global__ void qe_generate_kernel(void *values, qe_u32 *validity, int type, int
     if (validity) validity[word] = vbits;
 }
 
+
+// ---- group-by helpers (the main kernels are generated; see "group-by" in qe_device.cuh)
+
+// every slot empty, every accumulator word at its initial value
+__global__ void qe_groupby_init_kernel(qe_u32 *state, qe_u64 *acc, qe_u32 *ctl, qe_i64 nslots, qe::GroupWords gw)
+{
+    const qe_i64 i = (qe_i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) { ctl[0] = 0u; ctl[1] = 0u; ctl[2] = 0u; ctl[3] = 0u; }
+    if (i >= nslots) return;
+    state[i] = 0u;
+    for (int w = 0; w < gw.nwords; w++) acc[i * gw.nwords + w] = gw.init[w];
+}
+
+// Private variant: fold the per-CTA partials into the table, CTA 0 first, then CTA 1, ... (one CTA of threads;
+// within one source CTA the local groups map to distinct slots, so there are no conflicts and the order of
+// the additions into a slot is the CTA order: reproducible).
+__global__ void qe_groupby_merge_kernel(const qe_u64 *part, const qe_u32 *part_slot, qe_u64 *acc, int nctas, int lmax,
+                                        qe::GroupWords gw)
+{
+    for (int c = 0; c < nctas; c++) {
+        const qe_u32 *ps = part_slot + (size_t)c * (1 + lmax);
+        const int n = (int)ps[0];
+        for (int idx = (int)threadIdx.x; idx < n * gw.nwords; idx += (int)blockDim.x) {
+            const int l = idx / gw.nwords, w = idx - l * gw.nwords;
+            const qe_u32 slot = ps[1 + l];
+            if (slot == 0xffffffffu) continue;
+            qe_u64 *dst = acc + (size_t)slot * gw.nwords + w;
+            *dst = qe_group_combine(gw.kind[w], *dst, part[((size_t)c * lmax + l) * gw.nwords + w]);
+        }
+        __syncthreads();
+    }
+}
+
+// compact the occupied slots into records [acc words][key words][nulls], in no particular order
+__global__ void qe_groupby_collect_kernel(const qe_u32 *state, const qe_u64 *keys, const qe_u32 *nulls, const qe_u64 *acc,
+                                          qe_i64 nslots, int nkeys, int nwords, qe_u64 *records, qe_u32 *ctl, qe_u32 capacity)
+{
+    const qe_i64 i = (qe_i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nslots || state[i] != 2u) return;
+    const qe_u32 at = atomicAdd(ctl + 2, 1u);
+    if (at >= capacity) return;
+    qe_u64 *r = records + (size_t)at * (nwords + nkeys + 1);
+    for (int w = 0; w < nwords; w++) r[w] = acc[i * nwords + w];
+    for (int k = 0; k < nkeys; k++) r[nwords + k] = keys[i * nkeys + k];
+    r[nwords + nkeys] = nulls[i];
+}
+
 }  // namespace
 
 namespace qe {
@@ -130,6 +177,30 @@ int interp_blocks_per_sm(int mode)
 cudaError_t launch_agg_final(const double *partials, int nblocks, int nagg, double *out, cudaStream_t stream)
 {
     qe_agg_final_kernel<<<1, QE_BLOCK, 0, stream>>>(partials, nblocks, nagg, out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_groupby_init(uint32_t *state, uint64_t *acc, uint32_t *ctl, int64_t nslots, const GroupWords &gw, cudaStream_t stream)
+{
+    const int block = 256;
+    qe_groupby_init_kernel<<<(unsigned)((nslots + block - 1) / block), block, 0, stream>>>(state, (qe_u64 *)acc, ctl, (qe_i64)nslots, gw);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_groupby_merge(const uint64_t *part, const uint32_t *part_slot, uint64_t *acc, int nctas, int lmax,
+                                 const GroupWords &gw, cudaStream_t stream)
+{
+    qe_groupby_merge_kernel<<<1, 256, 0, stream>>>((const qe_u64 *)part, part_slot, (qe_u64 *)acc, nctas, lmax, gw);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_groupby_collect(const uint32_t *state, const uint64_t *keys, const uint32_t *nulls, const uint64_t *acc,
+                                   int64_t nslots, int nkeys, int nwords, uint64_t *records, uint32_t *ctl, uint32_t capacity,
+                                   cudaStream_t stream)
+{
+    const int block = 256;
+    qe_groupby_collect_kernel<<<(unsigned)((nslots + block - 1) / block), block, 0, stream>>>(
+        state, (const qe_u64 *)keys, nulls, (const qe_u64 *)acc, (qe_i64)nslots, nkeys, nwords, (qe_u64 *)records, ctl, capacity);
     return cudaGetLastError();
 }
 

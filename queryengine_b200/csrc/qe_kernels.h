@@ -13,10 +13,24 @@ struct QeParams;
 
 namespace qe {
 
+// accumulator words of a group-by (GroupPlan of qe_codegen.h), by value into the helper kernels
+struct GroupWords {
+    int nwords;
+    unsigned char kind[48];
+    unsigned long long init[48];
+};
+
 // mode: 0 filter, 1 project, 2 aggregate (== KernelMode)
 cudaError_t launch_interp(int mode, const QeParams &p, int grid, cudaStream_t stream);
 int interp_blocks_per_sm(int mode);
 cudaError_t launch_agg_final(const double *partials, int nblocks, int nagg, double *out, cudaStream_t stream);
+// group-by helpers: ctl = [0] groups claimed [1] overflow flags [2] records collected [3] spare
+cudaError_t launch_groupby_init(uint32_t *state, uint64_t *acc, uint32_t *ctl, int64_t nslots, const GroupWords &gw, cudaStream_t stream);
+cudaError_t launch_groupby_merge(const uint64_t *part, const uint32_t *part_slot, uint64_t *acc, int nctas, int lmax,
+                                 const GroupWords &gw, cudaStream_t stream);
+cudaError_t launch_groupby_collect(const uint32_t *state, const uint64_t *keys, const uint32_t *nulls, const uint64_t *acc,
+                                   int64_t nslots, int nkeys, int nwords, uint64_t *records, uint32_t *ctl, uint32_t capacity,
+                                   cudaStream_t stream);
 cudaError_t launch_generate(void *values, uint32_t *validity, int type, int kind, uint64_t seed, double p0, double p1,
                             double null_rate, int64_t row_offset, int64_t nrows, cudaStream_t stream);
 

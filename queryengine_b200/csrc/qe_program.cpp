@@ -176,12 +176,20 @@ static int bind_expr(const std::vector<ColumnInfo> &schema, const Program &p, Bo
 
 int bind_pipeline(const std::vector<ColumnInfo> &schema,
                   const Program *filter, const std::vector<const Program *> &proj,
-                  const std::vector<int> &agg_fns, BoundPipeline &out, std::string &err)
+                  const std::vector<int> &agg_fns, BoundPipeline &out, std::string &err, int group_keys)
 {
     out = BoundPipeline();
-    if (proj.size() > 8) { err = "more than QE_MAX_PROJECTIONS projections"; return 4; }
-    if (!agg_fns.empty() && agg_fns.size() != proj.size()) {
-        err = "each aggregate consumes one projection: nagg must equal nproj"; return 1;
+    out.group_keys = group_keys;
+    const size_t nkeys = group_keys > 0 ? (size_t)group_keys : 0;
+    if (group_keys >= 0) {
+        if (proj.size() > 16) { err = "more than 16 group keys + aggregate inputs"; return 4; }
+        if (nkeys > 8 || nkeys > proj.size()) { err = "bad number of group keys"; return 1; }
+        if (agg_fns.size() != proj.size() - nkeys) { err = "one aggregate function per projection after the keys"; return 1; }
+    } else {
+        if (proj.size() > 8) { err = "more than QE_MAX_PROJECTIONS projections"; return 4; }
+        if (!agg_fns.empty() && agg_fns.size() != proj.size()) {
+            err = "each aggregate consumes one projection: nagg must equal nproj"; return 1;
+        }
     }
     if (!filter && proj.empty()) { err = "pipeline has neither filter nor projection"; return 1; }
     if (filter) {
@@ -207,7 +215,7 @@ int bind_pipeline(const std::vector<ColumnInfo> &schema,
         if (fn == 5 || fn == 6) { err = "ANY / ALL aggregates are not implemented (as in the reference)"; return 4; }
         if (fn < 0 || fn > 4) { err = "unknown aggregation function"; return 1; }
         // M/evaluator/TypeCheck.kt:110-120: MIN/MAX/SUM/AVG need DOUBLE, COUNT takes anything
-        if (fn != 3 && out.proj[k].type != VT_F64) {
+        if (fn != 3 && out.proj[nkeys + k].type != VT_F64) {
             err = "Invalid operand types for aggregation: DOUBLE expected"; return 2;
         }
         out.agg_fns.push_back(fn);
@@ -237,6 +245,7 @@ std::string BoundPipeline::signature() const
     for (const BoundExpr &e : proj) put_expr(e);
     s += "|A";
     for (int f : agg_fns) { snprintf(b, sizeof b, "%d,", f); s += b; }
+    if (group_keys >= 0) { snprintf(b, sizeof b, "|G%d", group_keys); s += b; }
     return s;
 }
 

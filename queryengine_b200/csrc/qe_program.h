@@ -71,15 +71,17 @@ struct BoundPipeline {
     BoundExpr filter;
     std::vector<BoundExpr> proj;
     std::vector<BoundOutput> outs;         // one per projection
-    std::vector<int> agg_fns;              // empty, or one per projection
+    std::vector<int> agg_fns;              // empty, or one per projection (group-by: one per projection after the keys)
+    int group_keys = -1;                   // >= 0: GroupByAggregationOperator, the first group_keys projections are the key
     // everything that changes the generated code, as a cache key
     std::string signature() const;
 };
 
 // status: 0 ok, 2 program/type error, 4 unsupported, 1 invalid argument (values of qe_status)
+// group_keys >= 0 binds a group-by: proj = keys then aggregate inputs (up to 16 in all), agg_fns one per input
 int bind_pipeline(const std::vector<ColumnInfo> &schema,
                   const Program *filter, const std::vector<const Program *> &proj,
-                  const std::vector<int> &agg_fns, BoundPipeline &out, std::string &err);
+                  const std::vector<int> &agg_fns, BoundPipeline &out, std::string &err, int group_keys = -1);
 
 }  // namespace qe
 #endif

@@ -515,7 +515,16 @@ struct qe_result {
     bool timed = false;                 // ev_begin / ev_end hold a run not yet folded into the totals
     double total_kernel_ms = 0.0;       // device time of the main kernel over all runs into this result
     int64_t kernel_runs = 0;
+    // group-by: the table of groups on the device, and the finished rows (one per group) on the host
+    DevBuf g_state, g_keys, g_nulls, g_acc, g_ctl, g_part, g_part_slot, g_records;
+    std::vector<std::vector<uint8_t>> h_values, h_valid;    // per output column: values in the column's layout, Arrow bitmap
+    int64_t h_rows = 0;
+    int g_nkeys = 0, g_variant = 0;                         // variant: 0 private accumulators, 1 global atomics
+    std::vector<qe_agg_partial> g_partials;                 // [group][aggregate]
+    std::vector<int64_t> g_first_row;                       // [group] table row of the group's first appearance
 };
+
+static bool is_groupby(const qe_result *r) { return r->mode == qe::KM_GROUPBY_PRIVATE || r->mode == qe::KM_GROUPBY_ATOMIC; }
 
 // Fold the last run's kernel time into the totals (the run must have completed).
 static void fold_timing(qe_result *r)
@@ -558,6 +567,8 @@ extern "C" int qe_result_destroy(qe_result *r)
     for (ResultColumn &c : r->cols) { release(r->ctx, c.values); release(r->ctx, c.valid); }
     release(r->ctx, r->sel);
     release(r->ctx, r->ctl);
+    for (DevBuf *b : {&r->g_state, &r->g_keys, &r->g_nulls, &r->g_acc, &r->g_ctl, &r->g_part, &r->g_part_slot, &r->g_records})
+        release(r->ctx, *b);
     release(r->ctx, r->partials);
     release(r->ctx, r->final_aggs);
     release(r->ctx, r->debug);
@@ -673,7 +684,7 @@ static void serialize_interp(const qe::BoundPipeline &bp, std::vector<uint32_t> 
 }
 
 static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMode mode, const qe::TileShape &shape,
-                          JitEntry **out)
+                          JitEntry **out, size_t dyn_smem = 0)
 {
     char suffix[128];
     snprintf(suffix, sizeof suffix, "|M%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d.%d", (int)mode, shape.steps, shape.vec, shape.staged ? 1 : 0,
@@ -694,7 +705,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     JitEntry e;
     e.shape = shape;
     std::string err;
-    if (!qe::jit_load(cubin, QE_JIT_ENTRY, qe::staged_smem_bytes(bp, shape), mode == qe::KM_FILTER ? shape.block_threads() : QE_BLOCK,
+    if (!qe::jit_load(cubin, QE_JIT_ENTRY, dyn_smem ? dyn_smem : qe::staged_smem_bytes(bp, shape), mode == qe::KM_FILTER ? shape.block_threads() : QE_BLOCK,
                       e.kernel, err))
         return fail(QE_ERR_JIT, err);
     if (getenv("QE_DUMP_JIT"))
@@ -963,6 +974,274 @@ extern "C" int qe_pipeline_run(qe_ctx *ctx, const qe_table *table, const qe_prog
     return qe_pipeline_run_ex(ctx, table, &d, result);
 }
 
+
+// ------------------------------------------------------------------ group-by
+// Stands in for Scan -> [Filter] -> Projection(keys + aggregate inputs) -> GroupByAggregationOperator
+// (M/evaluator/Planner.kt:46-58, M/operator/GroupByAggregationOperator.kt:21-75).  Synchronous: the groups
+// are few compared with the rows, they are finished (Accumulator.finish) and ordered by first appearance
+// (LinkedHashMap iteration order) on the host.
+
+static void finish_agg(int fn, const qe_agg_partial &p, double *value, int *is_null);
+
+static int groupby_finish(qe_ctx *ctx, qe_result *r, const qe::BoundPipeline &bp, const qe::GroupPlan &gp, int64_t ngroups)
+{
+    const int nkeys = gp.nkeys, nagg = (int)bp.agg_fns.size(), nwords = gp.nwords;
+    const size_t rec = (size_t)nwords + (size_t)nkeys + 1;
+    std::vector<uint64_t> records((size_t)ngroups * rec);
+    if (ngroups > 0) {
+        QE_CUDA(cudaMemcpyAsync(records.data(), r->g_records.ptr, records.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        QE_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    std::vector<int64_t> order((size_t)ngroups);
+    for (int64_t i = 0; i < ngroups; i++) order[(size_t)i] = i;
+    std::sort(order.begin(), order.end(), [&](int64_t a, int64_t b) { return records[(size_t)a * rec] < records[(size_t)b * rec]; });
+
+    const int ncols = nkeys + nagg;
+    r->h_rows = ngroups;
+    r->h_values.assign((size_t)ncols, std::vector<uint8_t>());
+    r->h_valid.assign((size_t)ncols, std::vector<uint8_t>());
+    r->g_partials.assign((size_t)ngroups * (size_t)std::max(nagg, 1), qe_agg_partial());
+    r->g_first_row.assign((size_t)ngroups, 0);
+    const size_t vbytes = (size_t)((ngroups + 7) / 8);
+    for (int c = 0; c < ncols; c++) {
+        const int type = r->cols[(size_t)c].type;
+        r->h_values[(size_t)c].assign(type == QE_TYPE_BOOLEAN ? vbytes : (size_t)ngroups * type_width(type), 0);
+        r->h_valid[(size_t)c].assign(vbytes, 0);
+    }
+    for (int64_t g = 0; g < ngroups; g++) {
+        const uint64_t *w = &records[(size_t)order[(size_t)g] * rec];
+        r->g_first_row[(size_t)g] = (int64_t)w[0];
+        const uint32_t nulls = (uint32_t)w[nwords + nkeys];
+        for (int k = 0; k < nkeys; k++) {
+            if ((nulls >> k) & 1u) continue;                    // null key: validity bit stays 0, value 0
+            r->h_valid[(size_t)k][(size_t)(g / 8)] |= (uint8_t)(1u << (g % 8));
+            const uint64_t bits = w[nwords + k];
+            uint8_t *dst = r->h_values[(size_t)k].data();
+            switch (r->cols[(size_t)k].type) {
+            case QE_TYPE_BOOLEAN: if (bits) dst[g / 8] |= (uint8_t)(1u << (g % 8)); break;
+            case QE_TYPE_DOUBLE: case QE_TYPE_INT64: memcpy(dst + (size_t)g * 8, &bits, 8); break;
+            default: { const int32_t v = (int32_t)(int64_t)bits; memcpy(dst + (size_t)g * 4, &v, 4); break; }
+            }
+        }
+        for (int j = 0; j < nagg; j++) {
+            qe_agg_partial p;
+            p.sum = 0.0;
+            p.min = 0.0;
+            p.max = 0.0;
+            p.count = (int64_t)w[gp.cnt_word[(size_t)j]];
+            const int fn = bp.agg_fns[(size_t)j];
+            if (gp.val_word[(size_t)j] >= 0) {
+                double v;
+                memcpy(&v, &w[gp.val_word[(size_t)j]], 8);
+                if (fn == QE_AGG_FN_MIN) p.min = v;
+                else if (fn == QE_AGG_FN_MAX) p.max = v;
+                else p.sum = v;
+            }
+            r->g_partials[(size_t)g * (size_t)nagg + (size_t)j] = p;
+            double value = 0.0;
+            int is_null = 0;
+            finish_agg(fn, p, &value, &is_null);
+            if (!is_null) {
+                memcpy(r->h_values[(size_t)(nkeys + j)].data() + (size_t)g * 8, &value, 8);
+                r->h_valid[(size_t)(nkeys + j)][(size_t)(g / 8)] |= (uint8_t)(1u << (g % 8));
+            }
+        }
+    }
+    return QE_OK;
+}
+
+
+extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_groupby_desc *d, qe_result **result)
+{
+    if (!ctx || !table || !d || !result) return fail(QE_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (table->ctx != ctx) return fail(QE_ERR_INVALID_ARGUMENT, "table belongs to another context");
+    if (d->nkeys < 0 || d->nagg < 0 || d->nkeys + d->nagg <= 0) return fail(QE_ERR_INVALID_ARGUMENT, "bad key / aggregate count");
+    if ((d->nkeys && !d->keys) || (d->nagg && (!d->inputs || !d->agg_fns))) return fail(QE_ERR_INVALID_ARGUMENT, "NULL key / input list");
+    DeviceGuard g(ctx->device);
+
+    std::vector<qe::ColumnInfo> schema(table->cols.size());
+    for (size_t c = 0; c < table->cols.size(); c++) {
+        schema[c].type = table->cols[c].type;
+        schema[c].nullable = table->cols[c].nullable != 0;
+    }
+    std::vector<const qe::Program *> proj;
+    for (int k = 0; k < d->nkeys; k++) {
+        if (!d->keys[k]) return fail(QE_ERR_INVALID_ARGUMENT, "NULL key program");
+        proj.push_back(&d->keys[k]->prog);
+    }
+    for (int k = 0; k < d->nagg; k++) {
+        if (!d->inputs[k]) return fail(QE_ERR_INVALID_ARGUMENT, "NULL aggregate input program");
+        proj.push_back(&d->inputs[k]->prog);
+    }
+    std::vector<int> aggs(d->agg_fns, d->agg_fns + d->nagg);
+    qe::BoundPipeline bp;
+    std::string err;
+    int rc = qe::bind_pipeline(schema, d->filter ? &d->filter->prog : nullptr, proj, aggs, bp, err, d->nkeys);
+    if (rc) return fail(rc, err);
+    const qe::GroupPlan gp = qe::plan_groupby(bp);
+    if (gp.nwords > 48) return fail(QE_ERR_UNSUPPORTED, "too many accumulator words");
+
+    const int64_t row_begin = d->row_begin;
+    const int64_t row_end = d->row_end < 0 ? table->nrows : d->row_end;
+    if (row_begin < 0 || row_end < row_begin || row_end > table->nrows) return fail(QE_ERR_INVALID_ARGUMENT, "bad row range");
+    if (row_begin % 128) return fail(QE_ERR_INVALID_ARGUMENT, "row_begin must be a multiple of 128");
+    const int64_t n = row_end - row_begin;
+
+    std::string why;
+    if (!qe::jit_available(&why)) return fail(QE_ERR_JIT, "group-by needs NVRTC (generated code only): " + why);
+
+    const int64_t max_groups = d->max_groups > 0 ? d->max_groups : 65536;
+    if (max_groups > (1ll << 28)) return fail(QE_ERR_INVALID_ARGUMENT, "max_groups too large");
+    int64_t nslots = 1024;
+    while (nslots < 2 * max_groups) nslots *= 2;
+
+    qe_result *r = *result;
+    if (r && r->ctx != ctx) return fail(QE_ERR_INVALID_ARGUMENT, "result belongs to another context");
+    if (r && r->pending) { QE_CUDA(cudaEventSynchronize(r->ev_done)); r->pending = false; }
+    if (r) fold_timing(r);
+    if (!r) {
+        r = new qe_result();
+        r->ctx = ctx;
+        cudaError_t e = cudaHostAlloc((void **)&r->host, sizeof(ResultHost), cudaHostAllocDefault);
+        if (e == cudaSuccess) e = cudaEventCreate(&r->ev_begin);
+        if (e == cudaSuccess) e = cudaEventCreate(&r->ev_end);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&r->ev_done, cudaEventDisableTiming);
+        if (e != cudaSuccess) { qe_result_destroy(r); return fail_cuda("result setup", e); }
+    }
+    struct Cleanup {
+        qe_result *r; qe_result **slot; bool armed;
+        ~Cleanup() { if (armed && *slot != r) qe_result_destroy(r); }
+    } cleanup{r, result, true};
+
+    for (ResultColumn &c : r->cols) { release(ctx, c.values); release(ctx, c.valid); }
+    r->cols.assign(bp.outs.size(), ResultColumn());
+    for (size_t k = 0; k < bp.outs.size(); k++) {
+        r->cols[k].type = k < (size_t)gp.nkeys ? bp.outs[k].type : QE_TYPE_DOUBLE;
+        r->cols[k].has_validity = true;
+    }
+    r->agg_fns = bp.agg_fns;
+    r->g_nkeys = gp.nkeys;
+    r->batch_rows = n;
+    r->capacity = 0;
+    r->used_jit = true;
+    r->h_rows = 0;
+
+    qe::GroupWords gw;
+    memset(&gw, 0, sizeof gw);
+    gw.nwords = gp.nwords;
+    for (int w = 0; w < gp.nwords; w++) { gw.kind[w] = (unsigned char)gp.kind[(size_t)w]; gw.init[w] = gp.init[(size_t)w]; }
+
+    const int nk = std::max(gp.nkeys, 1);
+    if ((rc = ensure(ctx, r->g_state, (size_t)nslots * 4))) return rc;
+    if ((rc = ensure(ctx, r->g_keys, (size_t)nslots * (size_t)nk * 8))) return rc;
+    if ((rc = ensure(ctx, r->g_nulls, (size_t)nslots * 4))) return rc;
+    if ((rc = ensure(ctx, r->g_acc, (size_t)nslots * (size_t)gp.nwords * 8))) return rc;
+    if ((rc = ensure(ctx, r->g_ctl, 16))) return rc;
+
+    QeParams p;
+    memset(&p, 0, sizeof p);
+    for (size_t s = 0; s < bp.slot_table_col.size(); s++) {
+        const int c = bp.slot_table_col[s];
+        const int type = table->cols[c].type;
+        if (type == QE_TYPE_BOOLEAN) p.col_values[s] = (const char *)table->values[c] + row_begin / 8;
+        else p.col_values[s] = (const char *)table->values[c] + (size_t)row_begin * type_width(type);
+        p.col_valid[s] = table->valid[c] ? table->valid[c] + row_begin / 32 : nullptr;
+    }
+    p.nrows = n;
+    p.sel_base = (uint32_t)row_begin;
+    p.g_state = (qe_u32 *)r->g_state.ptr;
+    p.g_keys = (qe_u64 *)r->g_keys.ptr;
+    p.g_nulls = (qe_u32 *)r->g_nulls.ptr;
+    p.g_acc = (qe_u64 *)r->g_acc.ptr;
+    p.g_ctl = (qe_u32 *)r->g_ctl.ptr;
+    p.g_slot_mask = (qe_u32)(nslots - 1);
+    p.g_max_groups = (qe_u32)max_groups;
+
+    uint32_t ctl[4] = {0, 0, 0, 0};
+    bool atomic = (d->flags & QE_GROUPBY_ATOMIC) != 0 || gp.lmax < 1;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        const qe::KernelMode mode = atomic ? qe::KM_GROUPBY_ATOMIC : qe::KM_GROUPBY_PRIVATE;
+        qe::TileShape shape = choose_shape(ctx, bp, mode);
+        JitEntry *jit = nullptr;
+        if ((rc = get_jit_kernel(ctx, bp, mode, shape, &jit, atomic ? 0 : gp.private_smem()))) return rc;
+        const int64_t tile_rows = shape.rows_per_tile();
+        const int64_t ntiles64 = (n + tile_rows - 1) / tile_rows;
+        int blocks_per_sm = jit->kernel.blocks_per_sm;
+        if (ctx->opt_grid_per_sm) blocks_per_sm = std::min<int>(blocks_per_sm, (int)ctx->opt_grid_per_sm);
+        const int grid = (int)std::min<int64_t>(std::max<int64_t>(ntiles64, 1), (int64_t)ctx->num_sms * blocks_per_sm);
+        p.ntiles = (uint32_t)ntiles64;
+        if (!atomic) {
+            if ((rc = ensure(ctx, r->g_part, (size_t)grid * (size_t)gp.lmax * (size_t)gp.nwords * 8))) return rc;
+            if ((rc = ensure(ctx, r->g_part_slot, (size_t)grid * (size_t)(1 + gp.lmax) * 4))) return rc;
+            p.g_part = (qe_u64 *)r->g_part.ptr;
+            p.g_part_slot = (qe_u32 *)r->g_part_slot.ptr;
+        }
+        r->mode = (int)mode;
+        r->g_variant = atomic ? 1 : 0;
+        QE_CUDA(qe::launch_groupby_init((uint32_t *)r->g_state.ptr, (uint64_t *)r->g_acc.ptr, (uint32_t *)r->g_ctl.ptr, nslots, gw, ctx->stream));
+        ctx->launches++;
+        QE_CUDA(cudaEventRecord(r->ev_begin, ctx->stream));
+        if (n > 0) {
+            void *args[] = {&p};
+            QE_CUDA(cudaLaunchKernel((const void *)jit->kernel.kernel, dim3(grid), dim3(QE_BLOCK), args, jit->kernel.dyn_smem, ctx->stream));
+            ctx->launches++;
+        }
+        QE_CUDA(cudaEventRecord(r->ev_end, ctx->stream));
+        r->timed = true;
+        if (n > 0 && !atomic) {
+            QE_CUDA(qe::launch_groupby_merge((const uint64_t *)r->g_part.ptr, (const uint32_t *)r->g_part_slot.ptr, (uint64_t *)r->g_acc.ptr,
+                                             grid, gp.lmax, gw, ctx->stream));
+            ctx->launches++;
+        }
+        QE_CUDA(cudaMemcpyAsync(ctl, r->g_ctl.ptr, sizeof ctl, cudaMemcpyDeviceToHost, ctx->stream));
+        QE_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctl[1] & 2u)
+            return fail(QE_ERR_CAPACITY, "more than max_groups (" + std::to_string(max_groups) + ") groups; rerun with a larger max_groups");
+        if (!(ctl[1] & 1u)) break;
+        if (atomic) return fail(QE_ERR_STATE, "group-by: unexpected overflow flag");
+        fold_timing(r);          // the discarded attempt still ran: keep its time in the totals
+        atomic = true;           // a CTA met more groups than fit its shared memory: global atomics instead
+    }
+    const int64_t ngroups = ctl[0];
+    if (ngroups > 0) {
+        if ((rc = ensure(ctx, r->g_records, (size_t)ngroups * (size_t)(gp.nwords + gp.nkeys + 1) * 8))) return rc;
+        QE_CUDA(qe::launch_groupby_collect((const uint32_t *)r->g_state.ptr, (const uint64_t *)r->g_keys.ptr, (const uint32_t *)r->g_nulls.ptr,
+                                           (const uint64_t *)r->g_acc.ptr, nslots, gp.nkeys, gp.nwords, (uint64_t *)r->g_records.ptr,
+                                           (uint32_t *)r->g_ctl.ptr, (uint32_t)ngroups, ctx->stream));
+        ctx->launches++;
+    }
+    if ((rc = groupby_finish(ctx, r, bp, gp, ngroups))) return rc;
+    QE_CUDA(cudaEventRecord(r->ev_done, ctx->stream));
+    r->pending = false;
+    r->host->count = (unsigned long long)ngroups;
+    cleanup.armed = false;
+    *result = r;
+    return QE_OK;
+}
+
+extern "C" int qe_result_group_partial(qe_result *r, int64_t group, int k, qe_agg_partial *out)
+{
+    if (!r || !out) return fail(QE_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (!is_groupby(r)) return fail(QE_ERR_STATE, "this result is not a group-by");
+    const int nagg = (int)r->agg_fns.size();
+    if (group < 0 || group >= r->h_rows || k < 0 || k >= nagg) return fail(QE_ERR_INVALID_ARGUMENT, "group / aggregate index out of range");
+    *out = r->g_partials[(size_t)group * (size_t)nagg + (size_t)k];
+    return QE_OK;
+}
+
+extern "C" int qe_result_group_first_rows(qe_result *r, int64_t *dst)
+{
+    if (!r || !dst) return fail(QE_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (!is_groupby(r)) return fail(QE_ERR_STATE, "this result is not a group-by");
+    for (int64_t g = 0; g < r->h_rows; g++) dst[g] = r->g_first_row[(size_t)g];
+    return QE_OK;
+}
+
+extern "C" int qe_result_group_variant(const qe_result *r)
+{
+    return r && is_groupby(r) ? r->g_variant : -1;
+}
+
 // ------------------------------------------------------- result accessors
 
 static int wait_result(qe_result *r)
@@ -978,6 +1257,7 @@ static int wait_result(qe_result *r)
 
 static int64_t emitted_rows(const qe_result *r)
 {
+    if (is_groupby(r)) return r->h_rows;
     if (r->mode == qe::KM_AGG) return 1;
     if (r->mode == qe::KM_PROJECT) return r->batch_rows;
     return (int64_t)r->host->count;
@@ -1035,6 +1315,11 @@ extern "C" int qe_result_column(qe_result *r, int k, void *dst_values, uint8_t *
         return QE_OK;
     }
     if (n == 0) return QE_OK;
+    if (is_groupby(r)) {                       // finished on the host by qe_groupby_run
+        if (dst_values) memcpy(dst_values, r->h_values[k].data(), r->h_values[k].size());
+        if (dst_validity) memcpy(dst_validity, r->h_valid[k].data(), r->h_valid[k].size());
+        return QE_OK;
+    }
     if (dst_values) {
         const size_t bytes = c.type == QE_TYPE_BOOLEAN ? (size_t)((n + 7) / 8) : (size_t)n * type_width(c.type);
         QE_CUDA(cudaMemcpyAsync(dst_values, c.values.ptr, bytes, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1333,11 +1618,10 @@ extern "C" int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_
 // Bind a pipeline against a schema, generate its CUDA source and optionally
 // compile it with NVRTC.  Needs no GPU: used by the CPU-side tests and for
 // inspecting the generated code (SASS via cuobjdump on the returned cubin).
-extern "C" int qe_debug_generate(const qe_col_desc *cols, int ncols,
-                                 const uint32_t *const *programs, const size_t *nwords,
-                                 int has_filter, int nproj, const int32_t *agg_fns, int nagg,
-                                 int steps, int vec, int staging, int compile,
-                                 char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes)
+static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *const *programs, const size_t *nwords,
+                          int has_filter, int nproj, const int32_t *agg_fns, int nagg, int group_keys, int atomic,
+                          int steps, int vec, int staging, int compile,
+                          char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes)
 {
     if (!cols || ncols <= 0 || !programs || !nwords) return fail(QE_ERR_INVALID_ARGUMENT, "NULL argument");
     std::vector<qe::ColumnInfo> schema(ncols);
@@ -1352,9 +1636,10 @@ extern "C" int qe_debug_generate(const qe_col_desc *cols, int ncols,
     std::vector<int> aggs;
     if (nagg > 0) aggs.assign(agg_fns, agg_fns + nagg);
     qe::BoundPipeline bp;
-    int rc = qe::bind_pipeline(schema, has_filter ? &progs[0] : nullptr, proj, aggs, bp, err);
+    int rc = qe::bind_pipeline(schema, has_filter ? &progs[0] : nullptr, proj, aggs, bp, err, group_keys);
     if (rc) return fail(rc, err);
-    const qe::KernelMode mode = !bp.agg_fns.empty() ? qe::KM_AGG : bp.has_filter ? qe::KM_FILTER : qe::KM_PROJECT;
+    const qe::KernelMode mode = group_keys >= 0 ? (atomic ? qe::KM_GROUPBY_ATOMIC : qe::KM_GROUPBY_PRIVATE)
+                              : !bp.agg_fns.empty() ? qe::KM_AGG : bp.has_filter ? qe::KM_FILTER : qe::KM_PROJECT;
     qe_ctx dummy;
     dummy.opt_steps = steps;
     dummy.opt_vec = vec;
@@ -1375,4 +1660,24 @@ extern "C" int qe_debug_generate(const qe_col_desc *cols, int ncols,
         if (cubin_buf && cubin_cap >= cubin.size()) memcpy(cubin_buf, cubin.data(), cubin.size());
     }
     return QE_OK;
+}
+
+extern "C" int qe_debug_generate(const qe_col_desc *cols, int ncols,
+                                 const uint32_t *const *programs, const size_t *nwords,
+                                 int has_filter, int nproj, const int32_t *agg_fns, int nagg,
+                                 int steps, int vec, int staging, int compile,
+                                 char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes)
+{
+    return debug_generate(cols, ncols, programs, nwords, has_filter, nproj, agg_fns, nagg, -1, 0, steps, vec, staging, compile,
+                          src_buf, src_cap, cubin_buf, cubin_cap, cubin_bytes);
+}
+
+extern "C" int qe_debug_generate_groupby(const qe_col_desc *cols, int ncols,
+                                         const uint32_t *const *programs, const size_t *nwords,
+                                         int has_filter, int nkeys, const int32_t *agg_fns, int nagg, int atomic, int compile,
+                                         char *src_buf, size_t src_cap, size_t *cubin_bytes)
+{
+    if (nkeys < 0 || nagg < 0) return fail(QE_ERR_INVALID_ARGUMENT, "bad key / aggregate count");
+    return debug_generate(cols, ncols, programs, nwords, has_filter, nkeys + nagg, agg_fns, nagg, nkeys, atomic, 0, 0, -1, compile,
+                          src_buf, src_cap, nullptr, 0, cubin_bytes);
 }

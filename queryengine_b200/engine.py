@@ -21,7 +21,7 @@ from typing import List, Optional, Sequence
 import numpy as np
 
 from . import capi
-from .ast import AggregationFunction, ColumnExpression, DataType, Expression
+from .ast import AggregationFunction, AggregationFunctionExpression, ColumnExpression, DataType, Expression
 from .program import serialize
 
 _NP_OF = {DataType.DOUBLE: np.float64, DataType.INT64: np.int64, DataType.DATE32: np.int32, DataType.STRING: np.int32}
@@ -495,6 +495,131 @@ class GpuPipelineOperator:
 
     def map(self, mapper=lambda r: r) -> List:
         """Operator.map (.../operator/Operators.kt:25-32): open, pull until null, close."""
+        out = []
+        self.open()
+        try:
+            while True:
+                r = self.next()
+                if r is None:
+                    break
+                out.append(mapper(r))
+        finally:
+            self.close()
+        return out
+
+
+class GroupByPipeline:
+    """A bound Scan -> [Filter] -> Projection(keys + inputs) -> GroupByAggregation subtree (qe_groupby_run)."""
+
+    def __init__(self, table: ColumnarTable, filter: Optional[Expression], keys: Sequence[Expression],
+                 inputs: Sequence[Expression], aggregates: Sequence[AggregationFunction],
+                 max_groups: int = 0, atomic: bool = False):
+        self.table = table
+        self.ctx = table.ctx
+        self.filter = Program(self.ctx, filter) if filter is not None else None
+        self.keys = [Program(self.ctx, e) for e in keys]
+        self.inputs = [Program(self.ctx, e) for e in inputs]
+        self.aggs = [int(a) for a in aggregates]
+        if len(self.aggs) != len(self.inputs):
+            raise ValueError("one aggregation function per input")
+        self.max_groups = max_groups
+        self.flags = capi.QE_GROUPBY_ATOMIC if atomic else 0
+        self._key_arr = (C.c_void_p * max(1, len(self.keys)))(*[p.handle for p in self.keys])
+        self._in_arr = (C.c_void_p * max(1, len(self.inputs)))(*[p.handle for p in self.inputs])
+        self._agg_arr = (C.c_int32 * max(1, len(self.aggs)))(*self.aggs)
+
+    def run(self, result: Optional[PipelineResult] = None, row_begin: int = 0, row_end: int = -1) -> PipelineResult:
+        r = result or PipelineResult(self.ctx)
+        d = capi.GroupByDesc()
+        d.filter = self.filter.handle if self.filter else None
+        d.keys = self._key_arr
+        d.nkeys = len(self.keys)
+        d.inputs = self._in_arr
+        d.agg_fns = self._agg_arr
+        d.nagg = len(self.aggs)
+        d.row_begin = row_begin
+        d.row_end = row_end
+        d.max_groups = self.max_groups
+        d.flags = self.flags
+        capi.check(capi.lib().qe_groupby_run(self.ctx.handle, self.table.handle, C.byref(d), C.byref(r.handle)))
+        return r
+
+
+def rewrite_aggregates(select: Sequence[Expression]):
+    """rewriteAggregates for one projection (.../evaluator/RewriteAggregates.kt:18-49): every select
+    expression without an aggregate is a group key (in select order), every aggregate's operand an
+    accumulator input.  Returns (keys, inputs, functions, finish) where finish[i] is the column of the
+    aggregation's output row (keys first, then aggregates) that select expression i reads.  Only bare
+    aggregates are handled here; expressions OVER aggregates stay with the caller (they run on the
+    handful of result rows)."""
+    keys = [e for e in select if not isinstance(e, AggregationFunctionExpression)]
+    inputs, fns, finish = [], [], []
+    ki = 0
+    for e in select:
+        if isinstance(e, AggregationFunctionExpression):
+            finish.append(len(keys) + len(inputs))
+            inputs.append(e.operands[0])
+            fns.append(e.function)
+        else:
+            finish.append(ki)
+            ki += 1
+    return keys, inputs, fns, finish
+
+
+class GpuGroupByOperator:
+    """Operator for ProjectionOperator(GroupByAggregationOperator(ProjectionOperator([FilterOperator(] scan [)]))):
+    `select` mixes key expressions and AggregationFunctionExpressions like a SELECT list
+    (.../operator/GroupByAggregationOperator.kt:21-75).  Rows come out in order of first appearance."""
+
+    def __init__(self, table: ColumnarTable, filter: Optional[Expression], select: Sequence[Expression],
+                 max_groups: int = 0, atomic: bool = False):
+        self.select = list(select)
+        keys, inputs, fns, self.finish = rewrite_aggregates(self.select)
+        self.fns = fns
+        self.nkeys = len(keys)
+        self.pipeline = GroupByPipeline(table, filter, keys, inputs, fns, max_groups=max_groups, atomic=atomic)
+        self._result: Optional[PipelineResult] = None
+        self._rows: Optional[List[list]] = None
+        self._idx = 0
+
+    def open(self) -> None:
+        self._result = self.pipeline.run(self._result)
+        res = self._result
+        n = res.num_rows
+        cols = [res.column(k) for k in range(res.num_columns)]
+        types = [res.column_type(k)[0] for k in range(res.num_columns)]
+        dictionary = self.pipeline.ctx.dictionary
+        rows = []
+        for i in range(n):
+            full = []
+            for k, (vals, valid) in enumerate(cols):
+                if not valid[i]:
+                    full.append(None)
+                elif types[k] == DataType.BOOLEAN:
+                    full.append(bool(vals[i]))
+                elif types[k] == DataType.STRING:
+                    full.append(dictionary.decode(vals[i]))
+                elif k >= self.nkeys and self.fns[k - self.nkeys] == AggregationFunction.COUNT:
+                    full.append(int(vals[i]))                  # CountAccumulator.finish() is an Int
+                else:
+                    full.append(float(vals[i]))
+            rows.append([full[c] for c in self.finish])
+        self._rows = rows
+        self._idx = 0
+
+    def next(self):
+        if self._rows is None:
+            raise RuntimeError("Operator not opened")
+        if self._idx >= len(self._rows):
+            return None
+        self._idx += 1
+        return self._rows[self._idx - 1]
+
+    def close(self) -> None:
+        self._rows = None
+        self._idx = 0
+
+    def map(self, mapper=lambda r: r) -> List:
         out = []
         self.open()
         try:
