@@ -325,6 +325,52 @@ def tree_expr():
               fn(Function.SUB, fn(Function.UNARY_MINUS, inner), fn(Function.MUL, d, 0.25)))
 
 
+def q1_pipeline(ctx, rows, row_offset=0, atomic=False):
+    """TPC-H Q1 shape: group by two low-cardinality STRING keys (dictionary codes), eight
+    aggregates, a date filter that keeps ~96 % of the rows.  48 bytes per row are read."""
+    from queryengine_b200 import capi
+    from queryengine_b200.ast import AggregationFunction as A, DataType, Function, col, fn
+    from queryengine_b200.engine import ColumnarTable, Field, GroupByPipeline
+    D, S = DataType.DOUBLE, DataType.STRING
+    t = ColumnarTable(ctx, [Field("l_returnflag", S), Field("l_linestatus", S), Field("l_quantity", D), Field("l_extendedprice", D),
+                            Field("l_discount", D), Field("l_tax", D), Field("l_shipdate", D)], rows)
+    t.generate(0, capi.QE_GEN_UNIFORM_INT, SEED + 7, 0, 2, row_offset=row_offset)       # codes of 'A' 'N' 'R'
+    t.generate(1, capi.QE_GEN_UNIFORM_INT, SEED + 8, 3, 4, row_offset=row_offset)       # codes of 'F' 'O'
+    t.generate(2, capi.QE_GEN_UNIFORM_INT, SEED + 1, 1, 50, row_offset=row_offset)
+    t.generate(3, capi.QE_GEN_CENTS, SEED + 2, 90000, 10499999, row_offset=row_offset)
+    t.generate(4, capi.QE_GEN_CENTS, SEED + 3, 0, 10, row_offset=row_offset)
+    t.generate(5, capi.QE_GEN_CENTS, SEED + 5, 0, 8, row_offset=row_offset)
+    t.generate(6, capi.QE_GEN_UNIFORM_INT, SEED + 4, 8036, 10561, row_offset=row_offset)
+    rf, ls, qty, ep, disc, tax, sd = col(0, S), col(1, S), col(2), col(3), col(4), col(5), col(6)
+    net = fn(Function.MUL, ep, fn(Function.SUB, 1.0, disc))
+    gross = fn(Function.MUL, net, fn(Function.ADD, 1.0, tax))
+    pipe = GroupByPipeline(t, fn(Function.CMP_LE, sd, 10471.0), [rf, ls], [qty, ep, net, gross, qty, ep, disc, rf],
+                           [A.SUM, A.SUM, A.SUM, A.SUM, A.AVG, A.AVG, A.AVG, A.COUNT], atomic=atomic)
+    return t, pipe
+
+
+def extra_q1(ctx, rows, steps, warmup, peak):
+    from queryengine_b200 import capi
+    t, pipe = q1_pipeline(ctx, rows)
+    res = pipe.run()
+    for _ in range(warmup):
+        pipe.run(res)
+    ms0, runs0 = res.kernel_stats()
+    for _ in range(steps):
+        pipe.run(res)
+    ms1, runs1 = res.kernel_stats()
+    kms = (ms1 - ms0) / max(1, runs1 - runs0)
+    groups = res.num_rows
+    counts = res.column(9)[0]
+    out = {"rows": rows, "groups": groups, "kernel_ms": kms, "rows_per_s": rows / (kms * 1e-3),
+           "gb_per_s": rows * 48 / (kms * 1e-3) / 1e9, "frac_of_peak": rows * 48 / (kms * 1e-3) / 1e9 / peak,
+           "algorithmic_bytes_per_row": 48, "selectivity": float(counts.sum()) / rows,
+           "variant": "private" if capi.lib().qe_result_group_variant(res.handle) == 0 else "atomic"}
+    res.close()
+    t.close()
+    return out
+
+
 def extra_tree(ctx, torch, stream, rows, steps, warmup, peak):
     """BASELINE.json configs[3]: nullable f64 arithmetic tree (depth 8) with validity bitmaps, dense projection."""
     from queryengine_b200 import capi
@@ -457,6 +503,10 @@ def run_ours(args):
             extra["lineitem_filter_2proj_1e9"] = extra_sf_filter(ctx, args.sf_rows, max(3, args.steps), 3, peak)
         except Exception as e:
             extra["lineitem_filter_2proj_1e9"] = {"error": repr(e)}
+        try:      # group-by, TPC-H Q1 shape over SF100 lineitem
+            extra["q1_groupby_sf100"] = extra_q1(ctx, args.q6_rows, max(3, args.steps), 3, peak)
+        except Exception as e:
+            extra["q1_groupby_sf100"] = {"error": repr(e)}
     if world > 1 and not args.no_extra:
         # Q6 over SF100 lineitem row-sharded across the ranks: per-rank partial, NCCL all-gather of the partials,
         # rank-order combine (queryengine_b200/sharding.py) -- the only collective on the path

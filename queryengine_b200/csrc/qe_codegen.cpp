@@ -322,9 +322,17 @@ GroupPlan plan_groupby(const BoundPipeline &bp)
     }
     g.nwords = (int)g.kind.size();
     const size_t per_group = (size_t)g.nwords * 256u * 8u;
-    g.lmax = (int)std::min<size_t>(64, (200u << 10) / per_group);
-    g.cslots = 2;
-    while (g.cslots < 2 * g.lmax) g.cslots *= 2;
+    // shared memory of the private variant: LMAX groups of thread-private words + the key cache (>= 32 slots
+    // per group, so that nearly every key sits in its first probe slot and the per-row path is straight-line
+    // code; at most 1024 slots), together under 220 KB
+    const int nk = g.nkeys > 0 ? g.nkeys : 1;
+    for (g.lmax = (int)std::min<size_t>(64, (216u << 10) / per_group); g.lmax >= 1; g.lmax--) {
+        g.cslots = 64;
+        while (g.cslots < 32 * g.lmax && g.cslots < 1024) g.cslots *= 2;
+        const size_t cache = (size_t)g.cslots * (8u * (size_t)nk + 12u) + 4u * (size_t)g.lmax + 64u;
+        if ((size_t)g.lmax * per_group + cache <= (220u << 10)) break;
+    }
+    if (g.lmax < 1) { g.lmax = 0; g.cslots = 64; }
     return g;
 }
 

@@ -1570,11 +1570,16 @@ __device__ __forceinline__ qe_u64 qe_group_combine(int kind, qe_u64 a, qe_u64 b)
 template <int NKEYS>
 __device__ __forceinline__ qe_u32 qe_group_hash(const qe_u64 (&k)[NKEYS], qe_u32 nulls)
 {
+    // The high bits must come DOWN before the multiply: small-integer doubles differ only in their top ~12
+    // bits, and a multiply alone never moves those into the low bits the table index is taken from
+    // (measured: every key in one probe chain).
     qe_u64 h = 0x9e3779b97f4a7c15ULL ^ (qe_u64)nulls;
 #pragma unroll
     for (int i = 0; i < NKEYS; i++) {
-        h = (h ^ k[i]) * 0xff51afd7ed558ccdULL;
+        h ^= k[i];
         h ^= h >> 32;
+        h *= 0xff51afd7ed558ccdULL;
+        h ^= h >> 29;
     }
     return (qe_u32)h;
 }
@@ -1631,6 +1636,71 @@ __device__ __noinline__ int qe_group_global_slot(const QeParams &p, const qe_u64
     return found;
 }
 
+// The CTA's key cache of the private variant: key -> local group (index of the thread-private accumulators).
+// Sized so that nearly every key sits in its first probe slot (CS >= 32 x LMAX): the per-row path is then
+// straight-line code, the probing loop below runs for new and for displaced keys only.
+template <int NKEYS, int CS, int LMAX>
+struct QeGroupCache {
+    qe_u64 keys[CS][NKEYS];
+    qe_u32 nulls[CS];
+    int local[CS];
+    qe_u32 state[CS];           // 0 empty, 1 being written, 2 ready
+    qe_u32 slot[LMAX];          // table slot of every local group
+    qe_u32 nlocal, over;
+};
+
+template <int NKEYS, int CS, int LMAX>
+__device__ __noinline__ int qe_group_local_slow(const QeParams &p, QeGroupCache<NKEYS, CS, LMAX> *gcp, const qe_u64 (&k)[NKEYS],
+                                                qe_u32 nulls, qe_u32 h)
+{
+    volatile QeGroupCache<NKEYS, CS, LMAX> &gc = *gcp;
+    int l = -1;
+    qe_u32 c = h & (qe_u32)(CS - 1);
+    int probe = 0;
+    qe_u32 spins = 0;
+    bool done = false;
+    while (!done) {                                           // same loop shape as qe_group_global_slot
+        const qe_u32 st = gc.state[c];
+        if (gc.over) {
+            done = true;                                      // the run is discarded anyway
+        } else if (st == 2u) {
+            bool same = gc.nulls[c] == nulls;
+#pragma unroll
+            for (int i = 0; i < NKEYS; i++) same = same && gc.keys[c][i] == k[i];
+            if (same) {
+                l = gc.local[c];
+                done = true;
+            } else {
+                c = (c + 1u) & (qe_u32)(CS - 1);
+                if (++probe >= CS) { gc.over = 1u; done = true; }
+            }
+        } else if (st == 0u) {
+            if (atomicCAS(&gcp->state[c], 0u, 1u) == 0u) {
+#pragma unroll
+                for (int i = 0; i < NKEYS; i++) gc.keys[c][i] = k[i];
+                gc.nulls[c] = nulls;
+                int nl = (int)atomicAdd(&gcp->nlocal, 1u);
+                if (nl >= LMAX) {
+                    gc.over = 1u;
+                    nl = -1;
+                } else {
+                    const int gs = qe_group_global_slot<NKEYS>(p, k, nulls, h);
+                    gc.slot[nl] = gs < 0 ? 0xffffffffu : (qe_u32)gs;
+                }
+                gc.local[c] = nl;
+                __threadfence_block();
+                gc.state[c] = 2u;
+                l = nl;
+                done = true;
+            }
+        } else if (++spins > (1u << 24)) {
+            gc.over = 1u;
+            done = true;
+        }
+    }
+    return l;
+}
+
 template <class P>
 __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
 {
@@ -1639,16 +1709,11 @@ __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
     constexpr int TILE = QE_WARPS * WARP_ROWS;
     extern __shared__ __align__(16) unsigned char qe_gsmem[];
     qe_u64 *s_acc = (qe_u64 *)qe_gsmem;                       // [NWORDS][LMAX][QE_BLOCK]
-    __shared__ qe_u64 c_keys[CS][NKEYS];
-    __shared__ qe_u32 c_nulls[CS];
-    __shared__ int c_local[CS];
-    __shared__ qe_u32 c_state[CS];
-    __shared__ qe_u32 l_slot[LMAX];
-    __shared__ qe_u32 s_nlocal, s_over;
+    __shared__ QeGroupCache<NKEYS, CS, LMAX> gc;
     const qe_u32 warp = qe_warp(), lane = qe_lane(), tid = threadIdx.x;
 
-    for (int i = (int)tid; i < CS; i += QE_BLOCK) c_state[i] = 0u;
-    if (tid == 0) { s_nlocal = 0u; s_over = 0u; }
+    for (int i = (int)tid; i < CS; i += QE_BLOCK) gc.state[i] = 0u;
+    if (tid == 0) { gc.nlocal = 0u; gc.over = 0u; }
 #pragma unroll 1
     for (int w = 0; w < NWORDS; w++) {
         const qe_u64 init = P::word_init(w);
@@ -1670,52 +1735,16 @@ __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
                 qe_u64 k[NKEYS];
                 qe_u32 nulls;
                 P::key_pack(outs[s][j], k, nulls);
-                // ---- key -> local group, through the CTA's key cache (same loop shape as qe_group_global_slot)
-                int l = -1;
                 const qe_u32 h = qe_group_hash<NKEYS>(k, nulls);
-                qe_u32 c = h & (qe_u32)(CS - 1);
-                int probe = 0;
-                qe_u32 spins = 0;
-                bool done = false;
-                while (!done) {
-                    const qe_u32 st = *(volatile qe_u32 *)&c_state[c];
-                    if (*(volatile qe_u32 *)&s_over) {
-                        done = true;                          // the run is discarded anyway
-                    } else if (st == 2u) {
-                        bool same = c_nulls[c] == nulls;
+                const qe_u32 c = h & (qe_u32)(CS - 1);
+                // first probe, straight-line: volatile keeps the four reads in this order (state first)
+                const volatile QeGroupCache<NKEYS, CS, LMAX> &vc = gc;
+                bool hit = vc.state[c] == 2u;
+                hit = hit && vc.nulls[c] == nulls;
 #pragma unroll
-                        for (int i = 0; i < NKEYS; i++) same = same && c_keys[c][i] == k[i];
-                        if (same) {
-                            l = c_local[c];
-                            done = true;
-                        } else {
-                            c = (c + 1u) & (qe_u32)(CS - 1);
-                            if (++probe >= CS) { *(volatile qe_u32 *)&s_over = 1u; done = true; }
-                        }
-                    } else if (st == 0u) {
-                        if (atomicCAS(&c_state[c], 0u, 1u) == 0u) {
-#pragma unroll
-                            for (int i = 0; i < NKEYS; i++) c_keys[c][i] = k[i];
-                            c_nulls[c] = nulls;
-                            int nl = (int)atomicAdd(&s_nlocal, 1u);
-                            if (nl >= LMAX) {
-                                *(volatile qe_u32 *)&s_over = 1u;
-                                nl = -1;
-                            } else {
-                                const int gs = qe_group_global_slot<NKEYS>(p, k, nulls, h);
-                                l_slot[nl] = gs < 0 ? 0xffffffffu : (qe_u32)gs;
-                            }
-                            c_local[c] = nl;
-                            __threadfence_block();
-                            *(volatile qe_u32 *)&c_state[c] = 2u;
-                            l = nl;
-                            done = true;
-                        }
-                    } else if (++spins > (1u << 24)) {
-                        *(volatile qe_u32 *)&s_over = 1u;
-                        done = true;
-                    }
-                }
+                for (int i = 0; i < NKEYS; i++) hit = hit && vc.keys[c][i] == k[i];
+                int l = vc.local[c];
+                if (!hit) l = qe_group_local_slow<NKEYS, CS, LMAX>(p, &gc, k, nulls, h);
                 if (l >= 0) {
                     const qe_u64 row = (qe_u64)p.sel_base + (qe_u64)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j);
                     P::acc_private(s_acc + (size_t)l * QE_BLOCK + tid, outs[s][j], row);
@@ -1725,7 +1754,7 @@ __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
     }
     __syncthreads();
     // ---- fixed-order reduce of the 256 private copies: (group, word) pairs round-robin over the warps
-    const int nlocal = (int)(s_nlocal < (qe_u32)LMAX ? s_nlocal : (qe_u32)LMAX);
+    const int nlocal = (int)(gc.nlocal < (qe_u32)LMAX ? gc.nlocal : (qe_u32)LMAX);
     for (int idx = (int)warp; idx < nlocal * NWORDS; idx += QE_WARPS) {
         const int l = idx / NWORDS, w = idx - l * NWORDS;
         const int kind = P::word_kind(w);
@@ -1743,9 +1772,9 @@ __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
     qe_u32 *ps = p.g_part_slot + (size_t)blockIdx.x * (1 + LMAX);
     if (tid == 0) {
         ps[0] = (qe_u32)nlocal;
-        if (s_over) atomicOr(p.g_ctl + 1, 1u);
+        if (gc.over) atomicOr(p.g_ctl + 1, 1u);
     }
-    if ((int)tid < nlocal) ps[1 + tid] = l_slot[tid];
+    if ((int)tid < nlocal) ps[1 + tid] = gc.slot[tid];
 }
 
 template <class P>
