@@ -648,7 +648,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                 return std::string(a);
             };
             if (atomic) {
-                s += "        atomicMin((unsigned long long *)a, (unsigned long long)row);\n";
+                // first row: after the first few rows of a group nothing is smaller any more -- look before the atomic
+                s += "        if (row < *(volatile qe_u64 *)a) atomicMin((unsigned long long *)a, (unsigned long long)row);\n";
                 s += "        atomicAdd((unsigned long long *)(a + 1), 1ull);\n";
             } else {
                 s += "        a[0] = row < a[0] ? row : a[0];\n";

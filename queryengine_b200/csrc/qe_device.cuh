@@ -1722,11 +1722,26 @@ __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
     }
     __syncthreads();
 
+    // Only 8 warps fit beside the accumulators, so the loads of the NEXT tile are issued before this tile is
+    // evaluated and accumulated (register double buffer): the memory latency hides behind the shared-memory
+    // read-modify-write chains instead of adding to them.
+    typename P::Row rows[STEPS][VEC];
+    if (blockIdx.x < p.ntiles) {
+#pragma unroll
+        for (int s = 0; s < STEPS; s++)
+            P::load(p, (qe_i64)blockIdx.x * TILE + (qe_i64)warp * WARP_ROWS + (qe_i64)s * 32 * VEC + lane * VEC, rows[s]);
+    }
     for (qe_u32 tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
         const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
+        typename P::Row next[STEPS][VEC];
+        // the column allocations are padded by whole tiles, but not by a whole grid of them: clamp
+        const qe_u32 ntile = tile + gridDim.x < p.ntiles ? tile + gridDim.x : tile;
+#pragma unroll
+        for (int s = 0; s < STEPS; s++)
+            P::load(p, (qe_i64)ntile * TILE + (qe_i64)warp * WARP_ROWS + (qe_i64)s * 32 * VEC + lane * VEC, next[s]);
         typename P::Out outs[STEPS][VEC];
-        qe_u32 keep[STEPS], inb[STEPS];
-        qe_tile_eval<P>(p, warp_row0, outs, keep, inb);
+        qe_u32 keep[STEPS];
+        qe_rows_eval<P>(p, warp_row0, rows, outs, keep);
 #pragma unroll
         for (int s = 0; s < STEPS; s++) {
 #pragma unroll
@@ -1751,6 +1766,10 @@ __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
                 }
             }
         }
+#pragma unroll
+        for (int s = 0; s < STEPS; s++)
+#pragma unroll
+            for (int j = 0; j < VEC; j++) rows[s][j] = next[s][j];
     }
     __syncthreads();
     // ---- fixed-order reduce of the 256 private copies: (group, word) pairs round-robin over the warps
