@@ -101,3 +101,84 @@ def sharded_aggregate(result, fns: Sequence[AggregationFunction], device=None, g
     """This rank's aggregation result (PipelineResult of its partition) -> the global aggregates on every rank."""
     mine = [result.agg_partial(k) for k in range(len(fns))]
     return combine(fns, all_gather_partials(mine, device=device, group=group))
+
+
+# ---------------------------------------------------------------- group-by across partitions
+# GroupByAggregationOperator over a row-range sharded table: every rank groups its own rows (qe_groupby_run),
+# the per-group partials (a handful of rows) are all-gathered as Python objects and merged BY KEY on every
+# rank: partials folded in rank order (qe_agg_combine, as for the global aggregates), groups ordered by the
+# smallest global row index at which they appear -- the order a single scan of the whole table would have
+# produced (LinkedHashMap insertion order, .../operator/GroupByAggregationOperator.kt:22,29-36).
+
+def _key_id(v):
+    """Hashable identity of one key value with the reference's equality: Double.equals semantics (all NaNs
+    equal, -0.0 != 0.0), null a value of its own."""
+    if isinstance(v, float):
+        if v != v:
+            return ("f", "nan")
+        return ("f", np.array([v], dtype=np.float64).view(np.uint64)[0].item())
+    return (type(v).__name__, v)
+
+
+def group_partials(result, nkeys: int, fns: Sequence[AggregationFunction], dictionary, row_offset: int = 0):
+    """This rank's groups out of a qe_groupby_run result: [(keys, first_row_global, [(sum, count, min, max)])].
+    STRING keys are decoded (dictionary codes are private to a process)."""
+    import ctypes as C
+    from .ast import DataType
+    n = result.num_rows
+    cols = [result.column(k) for k in range(nkeys)]
+    types = [result.column_type(k)[0] for k in range(nkeys)]
+    first = np.zeros(max(n, 1), np.int64)
+    capi.check(capi.lib().qe_result_group_first_rows(result.handle, first.ctypes.data))
+    out = []
+    for g in range(n):
+        key = []
+        for k in range(nkeys):
+            vals, valid = cols[k]
+            if not valid[g]:
+                key.append(None)
+            elif types[k] == DataType.STRING:
+                key.append(dictionary.decode(vals[g]))
+            elif types[k] == DataType.BOOLEAN:
+                key.append(bool(vals[g]))
+            else:
+                key.append(float(vals[g]))
+        parts = []
+        for j in range(len(fns)):
+            p = capi.AggPartial()
+            capi.check(capi.lib().qe_result_group_partial(result.handle, g, j, C.byref(p)))
+            parts.append((p.sum, p.count, p.min, p.max))
+        out.append((tuple(key), int(first[g]) + int(row_offset), parts))
+    return out
+
+
+def combine_groups(fns: Sequence[AggregationFunction], by_rank) -> List[list]:
+    """Merge per-rank group lists (rank order) into the rows of the whole table: [key..., finish()...]."""
+    merged = {}
+    for rank_groups in by_rank:
+        for key, first, parts in rank_groups:
+            kid = tuple(_key_id(v) for v in key)
+            e = merged.get(kid)
+            if e is None:
+                merged[kid] = [key, first, [[p] for p in parts]]
+            else:
+                e[1] = min(e[1], first)
+                for j, p in enumerate(parts):
+                    e[2][j].append(p)
+    rows = []
+    for key, first, parts in sorted(merged.values(), key=lambda e: e[1]):
+        finished = combine(fns, [[capi.AggPartial(*p[r]) for p in parts] for r in range(len(parts[0]))]) if parts else []
+        rows.append(list(key) + [int(v) if (v is not None and fn == AggregationFunction.COUNT) else v
+                                 for v, fn in zip(finished, fns)])
+    return rows
+
+
+def sharded_groupby(result, nkeys: int, fns: Sequence[AggregationFunction], dictionary, row_offset: int, group=None) -> List[list]:
+    """This rank's group-by result -> the rows of the whole table, on every rank."""
+    import torch.distributed as dist
+    mine = group_partials(result, nkeys, fns, dictionary, row_offset)
+    if not (dist.is_available() and dist.is_initialized()):
+        return combine_groups(fns, [mine])
+    gathered = [None] * dist.get_world_size(group)
+    dist.all_gather_object(gathered, mine, group=group)
+    return combine_groups(fns, gathered)

@@ -192,3 +192,28 @@ def test_private_variant_is_reproducible_and_reports_partials(ctx):
     capi.check(capi.lib().qe_result_group_partial(r2.handle, 0, 0, C.byref(p)))
     assert p.count == int(a[2][0]) and p.sum == a[1][0]
     r1.close(); r2.close(); t.close()
+
+
+def test_row_range_partitions_merge_to_the_whole_table_result(ctx):
+    # two partitions of one table grouped separately (what two GPUs would do), merged by key on the host
+    from queryengine_b200 import sharding
+    rng = np.random.default_rng(21)
+    rows = _random_rows(rng, 6000, 1, 3)
+    for r in rows:
+        r[3] = float(int(r[3]))                              # integer-valued terms: every summation order is exact
+    s, b, k, x, y = (col(i, f.type) for i, f in enumerate(FIELDS))
+    fns = [A.SUM, A.COUNT, A.MIN, A.MAX]
+    t = _gpu_table(ctx, FIELDS, rows)
+    pipe = GroupByPipeline(t, fn(Function.CMP_GT, x, -90.0), [s, k], [x, y, x, x], fns)
+    whole = sharding.combine_groups(fns, [sharding.group_partials(pipe.run(), 2, fns, ctx.dictionary)])
+    parts = []
+    for lo, hi in ((0, 2432), (2432, 6000)):
+        parts.append(sharding.group_partials(pipe.run(row_begin=lo, row_end=hi), 2, fns, ctx.dictionary))
+    merged = sharding.combine_groups(fns, parts)
+    assert len(whole) == len(merged) and len(whole) > 10
+    for w, m in zip(whole, merged):
+        assert all(_same(a, c) for a, c in zip(w, m)), (w, m)
+    op = GpuGroupByOperator(t, fn(Function.CMP_GT, x, -90.0), [s, k, agg(A.SUM, x), agg(A.COUNT, y), agg(A.MIN, x), agg(A.MAX, x)])
+    for w, m in zip(op.map(), merged):
+        assert all(_same(a, c) for a, c in zip(w, m)), (w, m)
+    t.close()

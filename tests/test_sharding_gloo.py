@@ -151,3 +151,91 @@ def test_world_size_2_gloo_all_gather_and_combine():
     assert res[0][3] == sel[0] and res[1][4] == sel[-1]
     assert res[1][3] == sel[sel >= lo1][0]
     assert sum(res[0][2]) == sel.size
+
+
+# ---------------------------------------------------------------- group-by across partitions
+
+def _group_rows():
+    rng = np.random.default_rng(11)
+    n = 4000
+    flag = [None if rng.random() < 0.1 else ["A", "N", "R"][int(rng.integers(3))] for _ in range(n)]
+    k = [[0.0, -0.0, float("nan"), 2.0][int(rng.integers(4))] for _ in range(n)]
+    x = [None if rng.random() < 0.2 else float(int(rng.integers(-100, 100))) for _ in range(n)]
+    return [[flag[i], k[i], x[i]] for i in range(n)]
+
+
+def _shard_groups(rows, lo, hi):
+    """What sharding.group_partials returns for rows [lo, hi): computed here with plain Python (no GPU in this suite)."""
+    groups = {}
+    for i in range(lo, hi):
+        flag, k, x = rows[i]
+        kid = (sharding._key_id(flag), sharding._key_id(k))
+        g = groups.setdefault(kid, [(flag, k), i, [0.0, 0, float("inf"), float("-inf")]])
+        if x is not None:
+            a = g[2]
+            a[0] += x; a[1] += 1; a[2] = min(a[2], x); a[3] = max(a[3], x)
+    return [(key, first, [tuple(a)] * 4) for key, first, a in groups.values()]
+
+
+GFNS = [A.SUM, A.COUNT, A.MIN, A.MAX]
+
+
+def _oracle_groups(rows):
+    from oracle_binding import OraclePlan, OracleTable
+    S = DataType.STRING
+    t = OracleTable.from_rows([S, D, D], rows)
+    from queryengine_b200.ast import col as c
+    return OraclePlan(t, [0, 1, 2], projections=[c(0, S), c(1), c(2), c(2), c(2), c(2)], aggregates=GFNS, group_count=2).rows()
+
+
+def _rows_equal(got, want):
+    import math
+    assert len(got) == len(want), (len(got), len(want))
+    for g, w in zip(got, want):
+        for a, b in zip(g, w):
+            if isinstance(a, float) and isinstance(b, float):
+                assert (math.isnan(a) and math.isnan(b)) or (a == b and math.copysign(1, a) == math.copysign(1, b)), (g, w)
+            else:
+                assert a == b, (g, w)
+
+
+def test_group_partials_merge_by_key_in_first_appearance_order():
+    rows = _group_rows()
+    parts = sharding.partitions(len(rows), 3)
+    by_rank = [_shard_groups(rows, lo, hi) for lo, hi in parts]
+    _rows_equal(sharding.combine_groups(GFNS, by_rank), _oracle_groups(rows))      # integer-valued x: sums are exact
+
+
+def _group_worker(rank, world, port, q):
+    try:
+        import torch.distributed as dist
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        rows = _group_rows()
+        lo, hi = sharding.partition(len(rows), world, rank)
+        gathered = [None] * world
+        dist.all_gather_object(gathered, _shard_groups(rows, lo, hi))
+        q.put((rank, sharding.combine_groups(GFNS, gathered)))
+        dist.destroy_process_group()
+    except Exception as e:
+        q.put((rank, repr(e)))
+
+
+@pytest.mark.timeout(300)
+def test_world_size_2_gloo_groupby_merge():
+    import torch.multiprocessing as mp
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_group_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=240) for _ in range(world)], key=lambda r: r[0])
+    for p in procs:
+        p.join(60)
+    want = _oracle_groups(_group_rows())
+    for rank, got in res:
+        assert isinstance(got, list), got
+        _rows_equal(got, want)
