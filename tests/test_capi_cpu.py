@@ -227,3 +227,18 @@ def test_string_dictionary_codes_in_programs_and_generated_code():
     assert rc == 0, err
     rc, _, _, err = _generate([(S, True)], None, [col(0, S)], [AggregationFunction.MIN], compile_=False, dictionary=d)
     assert rc == capi.QE_ERR_PROGRAM
+
+
+def test_jni_shim_matches_the_c_abi():
+    # bindings/jni/qegpu_jni.c cannot be built here (no JDK): check its syntax and its use of every qe_* entry
+    # point against include/qegpu.h with the stand-in jni.h
+    import subprocess
+    r = subprocess.run(["gcc", "-fsyntax-only", "-Wall", "-Werror", "-Wno-unused-parameter",
+                        "-I", os.path.join(ROOT, "bindings", "jni", "jni_stub"), "-I", os.path.join(ROOT, "include"),
+                        os.path.join(ROOT, "bindings", "jni", "qegpu_jni.c")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    kt = open(os.path.join(ROOT, "bindings", "kotlin", "net", "jhorstmann", "queryengine", "gpu", "QeGpu.kt")).read()
+    c = open(os.path.join(ROOT, "bindings", "jni", "qegpu_jni.c")).read()
+    declared = set(re.findall(r"external fun (\w+)\(", kt))
+    defined = set(re.findall(r"QE_JNI\((\w+)\)\(", c))
+    assert declared == defined and len(declared) >= 15, declared ^ defined
