@@ -253,6 +253,8 @@ QE_API int qe_result_group_partial(qe_result *result, int64_t group, int k, qe_a
 QE_API int qe_result_group_first_rows(qe_result *result, int64_t *dst);
 /* 0: private accumulators (reproducible), 1: global atomics, -1: not a group-by result */
 QE_API int qe_result_group_variant(const qe_result *result);
+/* threads per CTA of the variant that produced the result (private: 512 when the groups fit, else 256) */
+QE_API int qe_result_group_threads(const qe_result *result);
 
 /* ---- results ------------------------------------------------------------- */
 /* rows the pipeline emitted (kept rows; 1 for an aggregation).  Waits for the run. */

@@ -136,6 +136,7 @@ SYMBOLS = {
     "qe_result_group_partial": (C.c_int, [_vp, C.c_int64, C.c_int, C.POINTER(AggPartial)]),
     "qe_result_group_first_rows": (C.c_int, [_vp, _vp]),
     "qe_result_group_variant": (C.c_int, [_vp]),
+    "qe_result_group_threads": (C.c_int, [_vp]),
     "qe_last_error": (C.c_char_p, []),
     "qe_version": (C.c_char_p, []),
 }

@@ -300,28 +300,51 @@ size_t staged_smem_bytes(const BoundPipeline &bp, const TileShape &shape)
     return (size_t)stage_layout(bp, shape).stride * (size_t)shape.nstages;
 }
 
-GroupPlan plan_groupby(const BoundPipeline &bp)
+GroupPlan plan_groupby(const BoundPipeline &bp, int threads)
 {
     GroupPlan g;
+    g.threads = threads;
     g.nkeys = bp.group_keys > 0 ? bp.group_keys : 0;
     auto word = [&](int kind, unsigned long long init) {
         g.kind.push_back(kind);
         g.init.push_back(init);
         return (int)g.kind.size() - 1;
     };
-    word(4, ~0ULL);                          // first row: min over u64
-    word(1, 0);                              // rows of the group
+    word(5, 0xffffffff00000000ULL);          // first row (min, high half) | rows of the group (sum, low half)
+    // Aggregates over the same input expression share words: SUM(x) and AVG(x) one sum, and every aggregate of
+    // a nullable x one count (TPC-H Q1: sum(qty), avg(qty), sum(price), avg(price) -> two sum words, not four).
+    auto expr_sig = [&](const BoundExpr &e) {
+        std::string sg;
+        char t[48];
+        for (const Instr &in : e.code) {
+            unsigned long long kb;
+            memcpy(&kb, &in.k, sizeof kb);
+            snprintf(t, sizeof t, "%u.%u.%llx.%d,", in.op, in.arg, in.op == OP_CONST_F64 ? kb : 0ULL, in.op == OP_CONST_STR ? in.code : 0);
+            sg += t;
+        }
+        return sg;
+    };
+    std::map<std::string, int> shared;
     for (size_t k = 0; k < bp.agg_fns.size(); k++) {
         const int fn = bp.agg_fns[k];
+        const BoundExpr &in = bp.proj[(size_t)g.nkeys + k];
+        const std::string sg = expr_sig(in);
+        auto shared_word = [&](const std::string &what, int kind, unsigned long long init) {
+            auto it = shared.find(what + sg);
+            if (it != shared.end()) return it->second;
+            const int w = word(kind, init);
+            shared[what + sg] = w;
+            return w;
+        };
         int vw = -1;
-        if (fn == 2 || fn == 4) vw = word(0, 0);                                   // SUM / AVG: 0.0, Accumulators.kt:40,93
-        else if (fn == 0) vw = word(2, 0x7ff0000000000000ULL);                     // MIN: +Infinity, :57
-        else if (fn == 1) vw = word(3, 0xfff0000000000000ULL);                     // MAX: -Infinity, :75
+        if (fn == 2 || fn == 4) vw = shared_word("sum|", 0, 0);                                    // SUM / AVG: 0.0, Accumulators.kt:40,93
+        else if (fn == 0) vw = shared_word("min|", 2, 0x7ff0000000000000ULL);                      // MIN: +Infinity, :57
+        else if (fn == 1) vw = shared_word("max|", 3, 0xfff0000000000000ULL);                      // MAX: -Infinity, :75
         g.val_word.push_back(vw);
-        g.cnt_word.push_back(bp.proj[(size_t)g.nkeys + k].nullable ? word(1, 0) : 1);
+        g.cnt_word.push_back(in.nullable ? shared_word("cnt|", 1, 0) : -1);
     }
     g.nwords = (int)g.kind.size();
-    const size_t per_group = (size_t)g.nwords * 256u * 8u;
+    const size_t per_group = (size_t)g.nwords * (size_t)threads * 8u;
     // shared memory of the private variant: LMAX groups of thread-private words + the key cache (>= 32 slots
     // per group, so that nearly every key sits in its first probe slot and the per-row path is straight-line
     // code; at most 1024 slots), together under 220 KB
@@ -598,9 +621,9 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     if (is_group) {
         // GroupByAggregationOperator.open (M/operator/GroupByAggregationOperator.kt:21-48): key = the first
         // NKEYS values of the row, accumulator i takes value NKEYS + i, nulls are skipped
-        const GroupPlan gp = plan_groupby(bp);
-        snprintf(b, sizeof b, "    static constexpr int NKEYS = %d, NWORDS = %d, LMAX = %d, CSLOTS = %d;\n", gp.nkeys > 0 ? gp.nkeys : 1,
-                 gp.nwords, gp.lmax > 0 ? gp.lmax : 1, gp.cslots);
+        const GroupPlan gp = plan_groupby(bp, shape.gthreads);
+        snprintf(b, sizeof b, "    static constexpr int NKEYS = %d, NWORDS = %d, LMAX = %d, CSLOTS = %d, GTHREADS = %d;\n", gp.nkeys > 0 ? gp.nkeys : 1,
+                 gp.nwords, gp.lmax > 0 ? gp.lmax : 1, gp.cslots, gp.threads);
         s += b;
         s += "    static __device__ __forceinline__ void key_pack(const Out &o, qe_u64 (&k)[NKEYS], qe_u32 &nulls) {\n        nulls = 0u;\n";
         if (gp.nkeys == 0) s += "        k[0] = 0ull;\n";
@@ -640,7 +663,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
             const bool atomic = variant == 1;
             s += atomic ? "    static __device__ __forceinline__ void acc_atomic(qe_u64 *a, const Out &o, qe_u64 row) {\n"
                         : "    static __device__ __forceinline__ void acc_private(qe_u64 *a, const Out &o, qe_u64 row) {\n"
-                          "        constexpr size_t WS = (size_t)LMAX * QE_BLOCK;\n";
+                          "        constexpr size_t WS = (size_t)LMAX * GTHREADS;\n";
             auto at = [&](int w) {
                 char a[48];
                 if (atomic) snprintf(a, sizeof a, "a + %d", w);
@@ -648,13 +671,15 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                 return std::string(a);
             };
             if (atomic) {
-                // first row: after the first few rows of a group nothing is smaller any more -- look before the atomic
-                s += "        if (row < *(volatile qe_u64 *)a) atomicMin((unsigned long long *)a, (unsigned long long)row);\n";
-                s += "        atomicAdd((unsigned long long *)(a + 1), 1ull);\n";
+                // word 0, little endian: rows in the low half, first row in the high half.  After the first few rows
+                // of a group nothing is smaller any more -- look before the atomic.
+                s += "        if ((qe_u32)row < ((volatile qe_u32 *)a)[1]) atomicMin(((unsigned int *)a) + 1, (unsigned int)row);\n";
+                s += "        atomicAdd((unsigned int *)a, 1u);\n";
             } else {
-                s += "        a[0] = row < a[0] ? row : a[0];\n";
-                s += "        a[WS] += 1ull;\n";
+                s += "        { const qe_u64 w0 = a[0]; const qe_u64 f = w0 >> 32;\n"
+                     "          a[0] = ((row < f ? row : f) << 32) | ((w0 + 1ull) & 0xffffffffull); }\n";
             }
+            std::vector<bool> done((size_t)gp.nwords, false);   // a shared word is updated by the first aggregate that uses it
             for (size_t j = 0; j < bp.agg_fns.size(); j++) {
                 const int fn = bp.agg_fns[j];
                 const int k = gp.nkeys + (int)j;
@@ -663,7 +688,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                 if (bp.proj[k].nullable) { snprintf(b, sizeof b, "if (o.n%d) ", k); guard = b; }
                 std::string stmts;
                 const std::string v = agg_val((int)j);
-                if (vw >= 0) {
+                if (vw >= 0 && !done[(size_t)vw]) {
+                    done[(size_t)vw] = true;
                     if (atomic) {
                         if (fn == 2 || fn == 4) stmts += "atomicAdd((double *)(" + at(vw) + "), " + v + "); ";
                         else if (fn == 0) stmts += "qe_atomic_min_f64(" + at(vw) + ", " + v + "); ";
@@ -673,7 +699,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                         stmts += at(vw) + " = (qe_u64)qe_f64_bits(" + f + "(qe_bits_f64((qe_i64)" + at(vw) + "), " + v + ")); ";
                     }
                 }
-                if (cw != 1) {
+                if (cw >= 0 && !done[(size_t)cw]) {
+                    done[(size_t)cw] = true;
                     if (atomic) stmts += "atomicAdd((unsigned long long *)(" + at(cw) + "), 1ull); ";
                     else stmts += at(cw) + " += 1ull; ";
                 }
@@ -689,7 +716,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     snprintf(b, sizeof b,
              "extern \"C\" __global__ void __launch_bounds__(%d, %d) " QE_JIT_ENTRY
              "(const __grid_constant__ QeParams p)\n{\n    %s<P>(p);\n}\n",
-             mode == KM_FILTER ? shape.block_threads() : 256, shape.min_blocks, body);
+             mode == KM_FILTER ? shape.block_threads() : mode == KM_GROUPBY_PRIVATE ? shape.gthreads : 256, shape.min_blocks, body);
     s += b;
     return s;
 }

@@ -19,18 +19,19 @@ namespace qe {
 
 enum KernelMode { KM_FILTER = 0, KM_PROJECT = 1, KM_AGG = 2, KM_GROUPBY_PRIVATE = 3, KM_GROUPBY_ATOMIC = 4 };
 
-// Accumulator words of one group (qe_device.cuh, "group-by"): word 0 = first row (min), word 1 = rows of the
-// group, then per aggregate a value word (SUM / AVG / MIN / MAX) and, when its input can be null, its own
-// count of non-null inputs (otherwise the group's row count is that count).
+// Accumulator words of one group (qe_device.cuh, "group-by"): word 0 = first row << 32 | rows of the group,
+// then per aggregate a value word (SUM / AVG / MIN / MAX) and, when its input can be null, its own count of
+// non-null inputs (otherwise the group's row count is that count: cnt_word = -1).
 struct GroupPlan {
     int nkeys = 0, nwords = 0;
     std::vector<int> kind;                 // QE_GK_* of every word
     std::vector<unsigned long long> init;  // initial bits of every word
     std::vector<int> val_word, cnt_word;   // per aggregate; val_word = -1 for COUNT
+    int threads = 256;                     // private variant: threads per CTA (512 when enough groups still fit)
     int lmax = 0, cslots = 0;              // private variant: groups per CTA that fit shared memory, key-cache slots
-    size_t private_smem() const { return (size_t)nwords * (size_t)lmax * 256u * 8u; }
+    size_t private_smem() const { return (size_t)nwords * (size_t)lmax * (size_t)threads * 8u; }
 };
-GroupPlan plan_groupby(const BoundPipeline &bp);
+GroupPlan plan_groupby(const BoundPipeline &bp, int threads = 256);
 
 struct TileShape {
     int steps = 2;          // steps per warp per tile
@@ -47,8 +48,9 @@ struct TileShape {
     int nlb = 1;            // look-back warps
     int defer = 3;          // tiles between a tile's evaluation (phase A) and its scatter (phase C)
     int loads = 0;          // bulk-copy tiles in flight at most (0 = as many as there are free stages)
+    int gthreads = 256;     // group-by, private variant: threads per CTA (256 or 512)
 
-    int rows_per_tile() const { return ring ? tile_rows : 8 * steps * 32 * vec; }
+    int rows_per_tile() const { return ring ? tile_rows : (gthreads / 32) * steps * 32 * vec; }
     int block_threads() const { return ring ? 32 * (2 + nlb + ncw) : 256; }
 };
 

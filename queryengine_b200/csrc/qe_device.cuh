@@ -88,7 +88,7 @@ struct QeParams {
     qe_u32       *g_state;                    // [slots] 0 empty, 1 key being written, 2 ready
     qe_u64       *g_keys;                     // [slots][NKEYS] canonical key bits
     qe_u32       *g_nulls;                    // [slots] bit i: key i is null
-    qe_u64       *g_acc;                      // [slots][NWORDS] accumulator words (word 0 = first row, word 1 = rows)
+    qe_u64       *g_acc;                      // [slots][NWORDS] accumulator words (word 0 = first row << 32 | rows)
     qe_u32       *g_ctl;                      // [0] groups claimed  [1] overflow flags (1 private capacity, 2 table capacity)
     qe_u64       *g_part;                     // private variant: [grid][LMAX][NWORDS] per-CTA partial accumulators
     qe_u32       *g_part_slot;                // private variant: [grid][1 + LMAX]: local groups, then the table slot of each
@@ -1530,8 +1530,9 @@ __device__ __forceinline__ void qe_agg_body(const QeParams &p)
 // (:38-43); rows come out in order of first appearance.
 //
 // Here: the groups live in an open-addressing table in HBM (g_state / g_keys / g_nulls), keyed by the
-// canonical bits of the key values.  Accumulators are 8-byte words; word 0 is the smallest row index of the
-// group (first appearance), word 1 its row count, then what the aggregates need.  Two kernel bodies:
+// canonical bits of the key values.  Accumulators are 8-byte words; word 0 holds the smallest row index of the
+// group (first appearance) in its high half and the group's row count in its low half (a table has < 2^32
+// rows), then come the words the aggregates need.  Two kernel bodies:
 //   qe_groupby_private_body  few groups: every THREAD owns a private copy of the accumulator words of up
 //                            to LMAX groups in shared memory (no atomics, no conflicts: lane-consecutive
 //                            words), a shared-memory key cache maps key -> local group; a fixed-order
@@ -1542,13 +1543,15 @@ __device__ __forceinline__ void qe_agg_body(const QeParams &p)
 //   static constexpr int NKEYS, NWORDS, LMAX, CSLOTS;
 //   static void key_pack(const Out&, qe_u64 (&k)[NKEYS], qe_u32 &nulls);
 //   static qe_u64 word_init(int w);  static int word_kind(int w);
-//   static void acc_private(qe_u64 *a, const Out&, qe_u64 row);    word w of this thread's copy at a[w * LMAX * QE_BLOCK]
+//   static constexpr int GTHREADS;                                 private variant: threads per CTA (256 or 512)
+//   static void acc_private(qe_u64 *a, const Out&, qe_u64 row);    word w of this thread's copy at a[w * LMAX * GTHREADS]
 //   static void acc_atomic(qe_u64 *a, const Out&, qe_u64 row);     word w at a[w]
 #define QE_GK_ADD_F64 0
 #define QE_GK_ADD_I64 1
 #define QE_GK_MIN_F64 2
 #define QE_GK_MAX_F64 3
 #define QE_GK_MIN_U64 4
+#define QE_GK_FIRST_ROWS 5     /* word 0: first row (u32, min) << 32 | rows of the group (u32, sum); a table has < 2^32 rows */
 
 // Double.equals / hashCode compare doubleToLongBits: one NaN, and -0.0 differs from 0.0
 __device__ __forceinline__ qe_u64 qe_key_f64(double x)
@@ -1563,6 +1566,10 @@ __device__ __forceinline__ qe_u64 qe_group_combine(int kind, qe_u64 a, qe_u64 b)
     case QE_GK_ADD_I64: return a + b;
     case QE_GK_MIN_F64: return (qe_u64)qe_f64_bits(qe_math_min(qe_bits_f64((qe_i64)a), qe_bits_f64((qe_i64)b)));
     case QE_GK_MAX_F64: return (qe_u64)qe_f64_bits(qe_math_max(qe_bits_f64((qe_i64)a), qe_bits_f64((qe_i64)b)));
+    case QE_GK_FIRST_ROWS: {
+        const qe_u64 fa = a >> 32, fb = b >> 32;
+        return ((fa < fb ? fa : fb) << 32) | ((a + b) & 0xffffffffULL);
+    }
     default:            return a < b ? a : b;
     }
 }
@@ -1705,20 +1712,21 @@ template <class P>
 __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
 {
     constexpr int STEPS = P::STEPS, VEC = P::VEC, NKEYS = P::NKEYS, NWORDS = P::NWORDS, LMAX = P::LMAX, CS = P::CSLOTS;
+    constexpr int GT = P::GTHREADS, GW = GT / 32;             // threads / warps per CTA: 512 / 16 when the groups fit, else 256 / 8
     constexpr int WARP_ROWS = STEPS * 32 * VEC;
-    constexpr int TILE = QE_WARPS * WARP_ROWS;
+    constexpr int TILE = GW * WARP_ROWS;
     extern __shared__ __align__(16) unsigned char qe_gsmem[];
-    qe_u64 *s_acc = (qe_u64 *)qe_gsmem;                       // [NWORDS][LMAX][QE_BLOCK]
+    qe_u64 *s_acc = (qe_u64 *)qe_gsmem;                       // [NWORDS][LMAX][GT]
     __shared__ QeGroupCache<NKEYS, CS, LMAX> gc;
     const qe_u32 warp = qe_warp(), lane = qe_lane(), tid = threadIdx.x;
 
-    for (int i = (int)tid; i < CS; i += QE_BLOCK) gc.state[i] = 0u;
+    for (int i = (int)tid; i < CS; i += GT) gc.state[i] = 0u;
     if (tid == 0) { gc.nlocal = 0u; gc.over = 0u; }
 #pragma unroll 1
     for (int w = 0; w < NWORDS; w++) {
         const qe_u64 init = P::word_init(w);
 #pragma unroll 1
-        for (int l = 0; l < LMAX; l++) s_acc[((size_t)w * LMAX + l) * QE_BLOCK + tid] = init;
+        for (int l = 0; l < LMAX; l++) s_acc[((size_t)w * LMAX + l) * GT + tid] = init;
     }
     __syncthreads();
 
@@ -1762,7 +1770,7 @@ __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
                 if (!hit) l = qe_group_local_slow<NKEYS, CS, LMAX>(p, &gc, k, nulls, h);
                 if (l >= 0) {
                     const qe_u64 row = (qe_u64)p.sel_base + (qe_u64)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j);
-                    P::acc_private(s_acc + (size_t)l * QE_BLOCK + tid, outs[s][j], row);
+                    P::acc_private(s_acc + (size_t)l * GT + tid, outs[s][j], row);
                 }
             }
         }
@@ -1772,15 +1780,15 @@ __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
             for (int j = 0; j < VEC; j++) rows[s][j] = next[s][j];
     }
     __syncthreads();
-    // ---- fixed-order reduce of the 256 private copies: (group, word) pairs round-robin over the warps
+    // ---- fixed-order reduce of the GT private copies: (group, word) pairs round-robin over the warps
     const int nlocal = (int)(gc.nlocal < (qe_u32)LMAX ? gc.nlocal : (qe_u32)LMAX);
-    for (int idx = (int)warp; idx < nlocal * NWORDS; idx += QE_WARPS) {
+    for (int idx = (int)warp; idx < nlocal * NWORDS; idx += GW) {
         const int l = idx / NWORDS, w = idx - l * NWORDS;
         const int kind = P::word_kind(w);
-        const qe_u64 *src = s_acc + ((size_t)w * LMAX + l) * QE_BLOCK;
+        const qe_u64 *src = s_acc + ((size_t)w * LMAX + l) * GT;
         qe_u64 v = src[lane];
 #pragma unroll
-        for (int q = 1; q < QE_WARPS; q++) v = qe_group_combine(kind, v, src[lane + 32 * q]);
+        for (int q = 1; q < GW; q++) v = qe_group_combine(kind, v, src[lane + 32 * q]);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             const qe_u64 b = (qe_u64)__shfl_down_sync(QE_FULL_MASK, (unsigned long long)v, o);

@@ -519,8 +519,9 @@ struct qe_result {
     DevBuf g_state, g_keys, g_nulls, g_acc, g_ctl, g_part, g_part_slot, g_records;
     std::vector<std::vector<uint8_t>> h_values, h_valid;    // per output column: values in the column's layout, Arrow bitmap
     int64_t h_rows = 0;
-    int g_nkeys = 0, g_variant = 0;                         // variant: 0 private accumulators, 1 global atomics
+    int g_nkeys = 0, g_variant = 0, g_threads = 0;          // variant: 0 private accumulators, 1 global atomics
     std::string g_overflowed;                               // signature of the group-by whose private variant overflowed here
+    int g_level = 0;                                        // ... and the variant to start with next time (0: 512 threads, 1: 256, 2: atomics)
     std::vector<qe_agg_partial> g_partials;                 // [group][aggregate]
     std::vector<int64_t> g_first_row;                       // [group] table row of the group's first appearance
 };
@@ -691,9 +692,9 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
                           JitEntry **out, size_t dyn_smem = 0)
 {
     char suffix[128];
-    snprintf(suffix, sizeof suffix, "|M%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d.%d", (int)mode, shape.steps, shape.vec, shape.staged ? 1 : 0,
+    snprintf(suffix, sizeof suffix, "|M%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d.%d|G%d", (int)mode, shape.steps, shape.vec, shape.staged ? 1 : 0,
              shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0, shape.ring ? 1 : 0, shape.tile_rows, shape.ncw,
-             shape.defer, shape.loads, shape.nlb);
+             shape.defer, shape.loads, shape.nlb, shape.gthreads);
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) { *out = &it->second; return QE_OK; }
@@ -709,7 +710,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     JitEntry e;
     e.shape = shape;
     std::string err;
-    if (!qe::jit_load(cubin, QE_JIT_ENTRY, dyn_smem ? dyn_smem : qe::staged_smem_bytes(bp, shape), mode == qe::KM_FILTER ? shape.block_threads() : QE_BLOCK,
+    if (!qe::jit_load(cubin, QE_JIT_ENTRY, dyn_smem ? dyn_smem : qe::staged_smem_bytes(bp, shape), mode == qe::KM_FILTER ? shape.block_threads() : mode == qe::KM_GROUPBY_PRIVATE ? shape.gthreads : QE_BLOCK,
                       e.kernel, err))
         return fail(QE_ERR_JIT, err);
     if (getenv("QE_DUMP_JIT"))
@@ -998,6 +999,7 @@ static int groupby_finish(qe_ctx *ctx, qe_result *r, const qe::BoundPipeline &bp
     }
     std::vector<int64_t> order((size_t)ngroups);
     for (int64_t i = 0; i < ngroups; i++) order[(size_t)i] = i;
+    // word 0 = first row << 32 | rows: ordering by the whole word orders by first row (first rows are distinct)
     std::sort(order.begin(), order.end(), [&](int64_t a, int64_t b) { return records[(size_t)a * rec] < records[(size_t)b * rec]; });
 
     const int ncols = nkeys + nagg;
@@ -1014,7 +1016,7 @@ static int groupby_finish(qe_ctx *ctx, qe_result *r, const qe::BoundPipeline &bp
     }
     for (int64_t g = 0; g < ngroups; g++) {
         const uint64_t *w = &records[(size_t)order[(size_t)g] * rec];
-        r->g_first_row[(size_t)g] = (int64_t)w[0];
+        r->g_first_row[(size_t)g] = (int64_t)(w[0] >> 32);
         const uint32_t nulls = (uint32_t)w[nwords + nkeys];
         for (int k = 0; k < nkeys; k++) {
             if ((nulls >> k) & 1u) continue;                    // null key: validity bit stays 0, value 0
@@ -1032,7 +1034,7 @@ static int groupby_finish(qe_ctx *ctx, qe_result *r, const qe::BoundPipeline &bp
             p.sum = 0.0;
             p.min = 0.0;
             p.max = 0.0;
-            p.count = (int64_t)w[gp.cnt_word[(size_t)j]];
+            p.count = gp.cnt_word[(size_t)j] < 0 ? (int64_t)(w[0] & 0xffffffffULL) : (int64_t)w[gp.cnt_word[(size_t)j]];
             const int fn = bp.agg_fns[(size_t)j];
             if (gp.val_word[(size_t)j] >= 0) {
                 double v;
@@ -1082,7 +1084,10 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     std::string err;
     int rc = qe::bind_pipeline(schema, d->filter ? &d->filter->prog : nullptr, proj, aggs, bp, err, d->nkeys);
     if (rc) return fail(rc, err);
-    const qe::GroupPlan gp = qe::plan_groupby(bp);
+    // Variants, tried in this order until one holds every group a CTA meets: private accumulators with 512 threads
+    // (16 warps per SM hide the shared-memory and HBM latencies; half as many groups fit), with 256 threads, atomics.
+    const qe::GroupPlan gp512 = qe::plan_groupby(bp, 512);
+    const qe::GroupPlan gp = qe::plan_groupby(bp, 256);
     if (gp.nwords > 48) return fail(QE_ERR_UNSUPPORTED, "too many accumulator words");
 
     const int64_t row_begin = d->row_begin;
@@ -1162,14 +1167,26 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     p.g_max_groups = (qe_u32)max_groups;
 
     uint32_t ctl[4] = {0, 0, 0, 0};
-    // a result that is reused remembers that this group-by has more groups than the private variant holds
+    // a result that is reused remembers which variants this group-by has overflowed
     const std::string sig = bp.signature();
-    bool atomic = (d->flags & QE_GROUPBY_ATOMIC) != 0 || gp.lmax < 1 || r->g_overflowed == sig;
-    for (int attempt = 0; attempt < 2; attempt++) {
+    int level = r->g_overflowed == sig ? r->g_level : 0;
+    if (d->flags & QE_GROUPBY_ATOMIC) level = 2;
+    for (;; level++) {
+        if (level == 0 && gp512.lmax < 2) continue;
+        if (level == 1 && (gp.lmax < 1 || gp.lmax <= gp512.lmax)) continue;
+        const bool atomic = level >= 2;
+        const qe::GroupPlan &plan = level == 0 ? gp512 : gp;
         const qe::KernelMode mode = atomic ? qe::KM_GROUPBY_ATOMIC : qe::KM_GROUPBY_PRIVATE;
         qe::TileShape shape = choose_shape(ctx, bp, mode);
+        if (!atomic) {
+            shape.gthreads = plan.threads;
+            if (plan.threads == 512 && !ctx->opt_steps && !ctx->opt_vec) {      // measured best for 16- and 48-byte rows
+                shape.steps = 1;
+                shape.vec = qe::jit_wide_loads_supported() ? 4 : 2;
+            }
+        }
         JitEntry *jit = nullptr;
-        if ((rc = get_jit_kernel(ctx, bp, mode, shape, &jit, atomic ? 0 : gp.private_smem()))) return rc;
+        if ((rc = get_jit_kernel(ctx, bp, mode, shape, &jit, atomic ? 0 : plan.private_smem()))) return rc;
         const int64_t tile_rows = shape.rows_per_tile();
         const int64_t ntiles64 = (n + tile_rows - 1) / tile_rows;
         int blocks_per_sm = jit->kernel.blocks_per_sm;
@@ -1177,26 +1194,28 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
         const int grid = (int)std::min<int64_t>(std::max<int64_t>(ntiles64, 1), (int64_t)ctx->num_sms * blocks_per_sm);
         p.ntiles = (uint32_t)ntiles64;
         if (!atomic) {
-            if ((rc = ensure(ctx, r->g_part, (size_t)grid * (size_t)gp.lmax * (size_t)gp.nwords * 8))) return rc;
-            if ((rc = ensure(ctx, r->g_part_slot, (size_t)grid * (size_t)(1 + gp.lmax) * 4))) return rc;
+            if ((rc = ensure(ctx, r->g_part, (size_t)grid * (size_t)plan.lmax * (size_t)plan.nwords * 8))) return rc;
+            if ((rc = ensure(ctx, r->g_part_slot, (size_t)grid * (size_t)(1 + plan.lmax) * 4))) return rc;
             p.g_part = (qe_u64 *)r->g_part.ptr;
             p.g_part_slot = (qe_u32 *)r->g_part_slot.ptr;
         }
         r->mode = (int)mode;
         r->g_variant = atomic ? 1 : 0;
+        r->g_threads = atomic ? QE_BLOCK : plan.threads;
         QE_CUDA(qe::launch_groupby_init((uint32_t *)r->g_state.ptr, (uint64_t *)r->g_acc.ptr, (uint32_t *)r->g_ctl.ptr, nslots, gw, ctx->stream));
         ctx->launches++;
         QE_CUDA(cudaEventRecord(r->ev_begin, ctx->stream));
         if (n > 0) {
             void *args[] = {&p};
-            QE_CUDA(cudaLaunchKernel((const void *)jit->kernel.kernel, dim3(grid), dim3(QE_BLOCK), args, jit->kernel.dyn_smem, ctx->stream));
+            QE_CUDA(cudaLaunchKernel((const void *)jit->kernel.kernel, dim3(grid), dim3(atomic ? QE_BLOCK : plan.threads), args,
+                                     jit->kernel.dyn_smem, ctx->stream));
             ctx->launches++;
         }
         QE_CUDA(cudaEventRecord(r->ev_end, ctx->stream));
         r->timed = true;
         if (n > 0 && !atomic) {
             QE_CUDA(qe::launch_groupby_merge((const uint64_t *)r->g_part.ptr, (const uint32_t *)r->g_part_slot.ptr, (uint64_t *)r->g_acc.ptr,
-                                             grid, gp.lmax, gw, ctx->stream));
+                                             grid, plan.lmax, gw, ctx->stream));
             ctx->launches++;
         }
         QE_CUDA(cudaMemcpyAsync(ctl, r->g_ctl.ptr, sizeof ctl, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1206,8 +1225,8 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
         if (!(ctl[1] & 1u)) break;
         if (atomic) return fail(QE_ERR_STATE, "group-by: unexpected overflow flag");
         fold_timing(r);          // the discarded attempt still ran: keep its time in the totals
-        atomic = true;           // a CTA met more groups than fit its shared memory: global atomics instead
-        r->g_overflowed = sig;
+        r->g_overflowed = sig;   // a CTA met more groups than fit its shared memory: next variant
+        r->g_level = level + 1;
     }
     const int64_t ngroups = ctl[0];
     if (ngroups > 0) {
@@ -1247,6 +1266,11 @@ extern "C" int qe_result_group_first_rows(qe_result *r, int64_t *dst)
 extern "C" int qe_result_group_variant(const qe_result *r)
 {
     return r && is_groupby(r) ? r->g_variant : -1;
+}
+
+extern "C" int qe_result_group_threads(const qe_result *r)
+{
+    return r && is_groupby(r) ? r->g_threads : -1;
 }
 
 // ------------------------------------------------------- result accessors
