@@ -230,8 +230,9 @@ QE_API int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_desc
  *      return null); read it with qe_result_num_rows / qe_result_column.  The call is
  *      synchronous.  Few groups (what fits a CTA's shared memory) accumulate in
  *      per-thread private copies and are combined in a fixed order, so results are reproducible;
- *      otherwise global atomics are used (SUM / AVG then depend on the order of additions,
- *      within the tolerance stated for SUM).  Needs NVRTC. */
+ *      more groups share one copy per CTA (shared-memory atomics), still more use global atomics
+ *      (SUM / AVG then depend on the order of additions, within the tolerance stated for SUM).
+ *      Needs NVRTC. */
 typedef struct qe_groupby_desc {
     const qe_program *filter;          /* may be NULL */
     const qe_program *const *keys;     /* group key expressions */
@@ -245,13 +246,14 @@ typedef struct qe_groupby_desc {
     uint32_t flags;                    /* QE_GROUPBY_* */
 } qe_groupby_desc;
 enum {
-    QE_GROUPBY_ATOMIC = 1u << 0        /* skip the private-accumulator variant */
+    QE_GROUPBY_ATOMIC = 1u << 0,       /* go straight to global atomics */
+    QE_GROUPBY_SHARED = 1u << 1        /* skip the private-accumulator variants: start with one shared-memory copy per CTA */
 };
 QE_API int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_groupby_desc *desc, qe_result **result);
 /* per-group partial aggregates and first rows, for combining row-range partitions by key on the host */
 QE_API int qe_result_group_partial(qe_result *result, int64_t group, int k, qe_agg_partial *out);
 QE_API int qe_result_group_first_rows(qe_result *result, int64_t *dst);
-/* 0: private accumulators (reproducible), 1: global atomics, -1: not a group-by result */
+/* 0: private accumulators (reproducible), 2: one shared-memory copy per CTA, 1: global atomics, -1: not a group-by result */
 QE_API int qe_result_group_variant(const qe_result *result);
 /* threads per CTA of the variant that produced the result (private: 512 when the groups fit, else 256) */
 QE_API int qe_result_group_threads(const qe_result *result);
@@ -296,7 +298,7 @@ QE_API int qe_debug_generate(const qe_col_desc *cols, int ncols,
                              int steps, int vec, int staging, int compile,
                              char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes);
 
-/* Same for a group-by: programs = [filter,] nkeys key programs, nagg aggregate inputs; atomic: which variant. */
+/* Same for a group-by: programs = [filter,] nkeys key programs, nagg aggregate inputs; atomic: 0 private, 1 global atomics, 2 CTA-shared. */
 QE_API int qe_debug_generate_groupby(const qe_col_desc *cols, int ncols,
                                      const uint32_t *const *programs, const size_t *nwords,
                                      int has_filter, int nkeys, const int32_t *agg_fns, int nagg, int atomic, int compile,

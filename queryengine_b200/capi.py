@@ -25,6 +25,7 @@ QE_RUN_NO_SELECTION = 1
 QE_RUN_INTERPRETER = 2
 QE_RUN_APPEND = 4
 QE_GROUPBY_ATOMIC = 1
+QE_GROUPBY_SHARED = 2
 
 QE_GEN_UNIFORM_U40 = 0
 QE_GEN_UNIFORM_INT = 1

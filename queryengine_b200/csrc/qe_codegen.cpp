@@ -300,6 +300,13 @@ size_t staged_smem_bytes(const BoundPipeline &bp, const TileShape &shape)
     return (size_t)stage_layout(bp, shape).stride * (size_t)shape.nstages;
 }
 
+size_t GroupPlan::shared_smem() const
+{
+    // QeGroupCache<NKEYS, CS, LMAX> of qe_device.cuh: keys, nulls, local, state per slot; slot per group; two words
+    const size_t nk = nkeys > 0 ? (size_t)nkeys : 1;
+    return (size_t)slmax * (size_t)nwords * 8u + (size_t)scslots * (8u * nk + 12u) + 4u * (size_t)slmax + 16u;
+}
+
 GroupPlan plan_groupby(const BoundPipeline &bp, int threads)
 {
     GroupPlan g;
@@ -356,6 +363,12 @@ GroupPlan plan_groupby(const BoundPipeline &bp, int threads)
         if ((size_t)g.lmax * per_group + cache <= (220u << 10)) break;
     }
     if (g.lmax < 1) { g.lmax = 0; g.cslots = 64; }
+    // shared variant: one copy of the words per CTA + a key cache of 4 slots per group, all in dynamic shared memory
+    for (g.slmax = 8192; g.slmax >= 64; g.slmax /= 2) {
+        g.scslots = 4 * g.slmax;
+        if (g.shared_smem() <= (208u << 10)) break;
+    }
+    if (g.slmax < 64) { g.slmax = 0; g.scslots = 64; }
     return g;
 }
 
@@ -371,7 +384,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     // bit columns of the outputs (validity bitmaps and BOOLEAN values)
     struct BitCol { std::string ptr, bit; };
     std::vector<BitCol> bitcols;
-    const bool is_group = mode == KM_GROUPBY_PRIVATE || mode == KM_GROUPBY_ATOMIC;
+    const bool is_group = mode == KM_GROUPBY_PRIVATE || mode == KM_GROUPBY_ATOMIC || mode == KM_GROUPBY_SHARED;
     if (mode != KM_AGG && !is_group) {
         for (int k = 0; k < nproj; k++) {
             if (bp.outs[k].has_validity) {
@@ -625,6 +638,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         snprintf(b, sizeof b, "    static constexpr int NKEYS = %d, NWORDS = %d, LMAX = %d, CSLOTS = %d, GTHREADS = %d;\n", gp.nkeys > 0 ? gp.nkeys : 1,
                  gp.nwords, gp.lmax > 0 ? gp.lmax : 1, gp.cslots, gp.threads);
         s += b;
+        snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d;\n", gp.slmax > 0 ? gp.slmax : 64, gp.scslots);
+        s += b;
         s += "    static __device__ __forceinline__ void key_pack(const Out &o, qe_u64 (&k)[NKEYS], qe_u32 &nulls) {\n        nulls = 0u;\n";
         if (gp.nkeys == 0) s += "        k[0] = 0ull;\n";
         for (int i = 0; i < gp.nkeys; i++) {
@@ -701,7 +716,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                 }
                 if (cw >= 0 && !done[(size_t)cw]) {
                     done[(size_t)cw] = true;
-                    if (atomic) stmts += "atomicAdd((unsigned long long *)(" + at(cw) + "), 1ull); ";
+                    // a table has < 2^32 rows: the count fits the low half, and 32-bit adds are native in shared memory too
+                    if (atomic) stmts += "atomicAdd((unsigned int *)(" + at(cw) + "), 1u); ";
                     else stmts += at(cw) + " += 1ull; ";
                 }
                 if (!stmts.empty()) s += "        " + guard + "{ " + stmts + "}\n";
@@ -712,11 +728,12 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     s += "};\n\n";
     const char *body = mode == KM_FILTER ? (shape.ring ? "qe_filter_ring_body" : shape.staged ? "qe_filter_staged_body" : shape.pipelined ? "qe_filter_pipelined_body" : "qe_filter_body")
                      : mode == KM_PROJECT ? "qe_project_body" : mode == KM_AGG ? "qe_agg_body"
-                     : mode == KM_GROUPBY_PRIVATE ? "qe_groupby_private_body" : "qe_groupby_atomic_body";
+                     : mode == KM_GROUPBY_PRIVATE ? "qe_groupby_private_body"
+                     : mode == KM_GROUPBY_SHARED ? "qe_groupby_shared_body" : "qe_groupby_atomic_body";
     snprintf(b, sizeof b,
              "extern \"C\" __global__ void __launch_bounds__(%d, %d) " QE_JIT_ENTRY
              "(const __grid_constant__ QeParams p)\n{\n    %s<P>(p);\n}\n",
-             mode == KM_FILTER ? shape.block_threads() : mode == KM_GROUPBY_PRIVATE ? shape.gthreads : 256, shape.min_blocks, body);
+             mode == KM_FILTER ? shape.block_threads() : (mode == KM_GROUPBY_PRIVATE || mode == KM_GROUPBY_SHARED) ? shape.gthreads : 256, shape.min_blocks, body);
     s += b;
     return s;
 }

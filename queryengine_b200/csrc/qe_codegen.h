@@ -17,7 +17,7 @@
 
 namespace qe {
 
-enum KernelMode { KM_FILTER = 0, KM_PROJECT = 1, KM_AGG = 2, KM_GROUPBY_PRIVATE = 3, KM_GROUPBY_ATOMIC = 4 };
+enum KernelMode { KM_FILTER = 0, KM_PROJECT = 1, KM_AGG = 2, KM_GROUPBY_PRIVATE = 3, KM_GROUPBY_ATOMIC = 4, KM_GROUPBY_SHARED = 5 };
 
 // Accumulator words of one group (qe_device.cuh, "group-by"): word 0 = first row << 32 | rows of the group,
 // then per aggregate a value word (SUM / AVG / MIN / MAX) and, when its input can be null, its own count of
@@ -30,6 +30,8 @@ struct GroupPlan {
     int threads = 256;                     // private variant: threads per CTA (512 when enough groups still fit)
     int lmax = 0, cslots = 0;              // private variant: groups per CTA that fit shared memory, key-cache slots
     size_t private_smem() const { return (size_t)nwords * (size_t)lmax * (size_t)threads * 8u; }
+    int slmax = 0, scslots = 0;            // shared variant: groups per CTA (one copy of the words), key-cache slots
+    size_t shared_smem() const;            // accumulators + key cache, all dynamic
 };
 GroupPlan plan_groupby(const BoundPipeline &bp, int threads = 256);
 

@@ -1804,6 +1804,85 @@ __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
     if ((int)tid < nlocal) ps[1 + tid] = gc.slot[tid];
 }
 
+// Middle variant: more groups than the private copies hold, few enough for ONE copy of the accumulators per CTA
+// in shared memory (SLMAX groups, hundreds to thousands).  Rows update it with shared-memory atomics (native
+// 32-bit for the first-row / row-count word and the counts, compare-and-swap loops for the f64 words), which
+// keeps the traffic off the L2 atomic units the global variant saturates.  The CTA's copy is flushed as a
+// partial and merged in CTA order like the private variant's; within a CTA the order of the additions into a
+// SUM is not reproducible.
+template <class P>
+__device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
+{
+    constexpr int STEPS = P::STEPS, VEC = P::VEC, NKEYS = P::NKEYS, NWORDS = P::NWORDS, LMAX = P::SLMAX, CS = P::SCSLOTS;
+    constexpr int GT = P::GTHREADS, GW = GT / 32;
+    constexpr int WARP_ROWS = STEPS * 32 * VEC;
+    constexpr int TILE = GW * WARP_ROWS;
+    typedef QeGroupCache<NKEYS, CS, LMAX> Cache;
+    extern __shared__ __align__(16) unsigned char qe_gsmem[];
+    qe_u64 *s_acc = (qe_u64 *)qe_gsmem;                       // [LMAX][NWORDS]
+    Cache &gc = *(Cache *)(qe_gsmem + (size_t)LMAX * NWORDS * 8);
+    const qe_u32 warp = qe_warp(), lane = qe_lane(), tid = threadIdx.x;
+
+    for (int i = (int)tid; i < CS; i += GT) gc.state[i] = 0u;
+    if (tid == 0) { gc.nlocal = 0u; gc.over = 0u; }
+    for (int i = (int)tid; i < LMAX * NWORDS; i += GT) s_acc[i] = P::word_init(i % NWORDS);
+    __syncthreads();
+
+    typename P::Row rows[STEPS][VEC];
+    if (blockIdx.x < p.ntiles) {
+#pragma unroll
+        for (int s = 0; s < STEPS; s++)
+            P::load(p, (qe_i64)blockIdx.x * TILE + (qe_i64)warp * WARP_ROWS + (qe_i64)s * 32 * VEC + lane * VEC, rows[s]);
+    }
+    for (qe_u32 tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+        const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
+        typename P::Row next[STEPS][VEC];
+        const qe_u32 ntile = tile + gridDim.x < p.ntiles ? tile + gridDim.x : tile;
+#pragma unroll
+        for (int s = 0; s < STEPS; s++)
+            P::load(p, (qe_i64)ntile * TILE + (qe_i64)warp * WARP_ROWS + (qe_i64)s * 32 * VEC + lane * VEC, next[s]);
+        typename P::Out outs[STEPS][VEC];
+        qe_u32 keep[STEPS];
+        qe_rows_eval<P>(p, warp_row0, rows, outs, keep);
+#pragma unroll
+        for (int s = 0; s < STEPS; s++) {
+#pragma unroll
+            for (int j = 0; j < VEC; j++) {
+                if (!((keep[s] >> j) & 1u)) continue;
+                qe_u64 k[NKEYS];
+                qe_u32 nulls;
+                P::key_pack(outs[s][j], k, nulls);
+                const qe_u32 h = qe_group_hash<NKEYS>(k, nulls);
+                const qe_u32 c = h & (qe_u32)(CS - 1);
+                const volatile Cache &vc = gc;
+                bool hit = vc.state[c] == 2u;
+                hit = hit && vc.nulls[c] == nulls;
+#pragma unroll
+                for (int i = 0; i < NKEYS; i++) hit = hit && vc.keys[c][i] == k[i];
+                int l = vc.local[c];
+                if (!hit) l = qe_group_local_slow<NKEYS, CS, LMAX>(p, &gc, k, nulls, h);
+                if (l >= 0) {
+                    const qe_u64 row = (qe_u64)p.sel_base + (qe_u64)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j);
+                    P::acc_atomic(s_acc + (size_t)l * NWORDS, outs[s][j], row);
+                }
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < STEPS; s++)
+#pragma unroll
+            for (int j = 0; j < VEC; j++) rows[s][j] = next[s][j];
+    }
+    __syncthreads();
+    const int nlocal = (int)(gc.nlocal < (qe_u32)LMAX ? gc.nlocal : (qe_u32)LMAX);
+    for (int i = (int)tid; i < nlocal * NWORDS; i += GT) p.g_part[(size_t)blockIdx.x * LMAX * NWORDS + i] = s_acc[i];
+    qe_u32 *ps = p.g_part_slot + (size_t)blockIdx.x * (1 + LMAX);
+    if (tid == 0) {
+        ps[0] = (qe_u32)nlocal;
+        if (gc.over) atomicOr(p.g_ctl + 1, 1u);
+    }
+    for (int i = (int)tid; i < nlocal; i += GT) ps[1 + i] = gc.slot[i];
+}
+
 template <class P>
 __device__ __forceinline__ void qe_groupby_atomic_body(const QeParams &p)
 {

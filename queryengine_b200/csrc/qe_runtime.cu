@@ -519,14 +519,18 @@ struct qe_result {
     DevBuf g_state, g_keys, g_nulls, g_acc, g_ctl, g_part, g_part_slot, g_records;
     std::vector<std::vector<uint8_t>> h_values, h_valid;    // per output column: values in the column's layout, Arrow bitmap
     int64_t h_rows = 0;
-    int g_nkeys = 0, g_variant = 0, g_threads = 0;          // variant: 0 private accumulators, 1 global atomics
+    int g_nkeys = 0, g_variant = 0, g_threads = 0;          // variant: 0 private accumulators, 1 global atomics, 2 CTA-shared
     std::string g_overflowed;                               // signature of the group-by whose private variant overflowed here
-    int g_level = 0;                                        // ... and the variant to start with next time (0: 512 threads, 1: 256, 2: atomics)
+    int g_level = 0;                                        // ... and the variant to start with next time (0: private 512 threads,
+                                                            // 1: private 256, 2: CTA-shared accumulators, 3: global atomics)
     std::vector<qe_agg_partial> g_partials;                 // [group][aggregate]
     std::vector<int64_t> g_first_row;                       // [group] table row of the group's first appearance
 };
 
-static bool is_groupby(const qe_result *r) { return r->mode == qe::KM_GROUPBY_PRIVATE || r->mode == qe::KM_GROUPBY_ATOMIC; }
+static bool is_groupby(const qe_result *r)
+{
+    return r->mode == qe::KM_GROUPBY_PRIVATE || r->mode == qe::KM_GROUPBY_ATOMIC || r->mode == qe::KM_GROUPBY_SHARED;
+}
 
 // Fold the last run's kernel time into the totals (the run must have completed).
 static void fold_timing(qe_result *r)
@@ -710,7 +714,8 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     JitEntry e;
     e.shape = shape;
     std::string err;
-    if (!qe::jit_load(cubin, QE_JIT_ENTRY, dyn_smem ? dyn_smem : qe::staged_smem_bytes(bp, shape), mode == qe::KM_FILTER ? shape.block_threads() : mode == qe::KM_GROUPBY_PRIVATE ? shape.gthreads : QE_BLOCK,
+    if (!qe::jit_load(cubin, QE_JIT_ENTRY, dyn_smem ? dyn_smem : qe::staged_smem_bytes(bp, shape), mode == qe::KM_FILTER ? shape.block_threads()
+                      : (mode == qe::KM_GROUPBY_PRIVATE || mode == qe::KM_GROUPBY_SHARED) ? shape.gthreads : QE_BLOCK,
                       e.kernel, err))
         return fail(QE_ERR_JIT, err);
     if (getenv("QE_DUMP_JIT"))
@@ -1170,13 +1175,16 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     // a result that is reused remembers which variants this group-by has overflowed
     const std::string sig = bp.signature();
     int level = r->g_overflowed == sig ? r->g_level : 0;
-    if (d->flags & QE_GROUPBY_ATOMIC) level = 2;
+    if (d->flags & QE_GROUPBY_ATOMIC) level = 3;
+    else if (d->flags & QE_GROUPBY_SHARED) level = std::max(level, 2);
     for (;; level++) {
         if (level == 0 && gp512.lmax < 2) continue;
         if (level == 1 && (gp.lmax < 1 || gp.lmax <= gp512.lmax)) continue;
-        const bool atomic = level >= 2;
-        const qe::GroupPlan &plan = level == 0 ? gp512 : gp;
-        const qe::KernelMode mode = atomic ? qe::KM_GROUPBY_ATOMIC : qe::KM_GROUPBY_PRIVATE;
+        if (level == 2 && gp512.slmax < 64) continue;
+        const bool atomic = level >= 3, shared = level == 2;
+        const qe::GroupPlan &plan = (level == 0 || level == 2) ? gp512 : gp;
+        const qe::KernelMode mode = atomic ? qe::KM_GROUPBY_ATOMIC : shared ? qe::KM_GROUPBY_SHARED : qe::KM_GROUPBY_PRIVATE;
+        const int part_groups = shared ? plan.slmax : plan.lmax;
         qe::TileShape shape = choose_shape(ctx, bp, mode);
         if (!atomic) {
             shape.gthreads = plan.threads;
@@ -1186,7 +1194,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
             }
         }
         JitEntry *jit = nullptr;
-        if ((rc = get_jit_kernel(ctx, bp, mode, shape, &jit, atomic ? 0 : plan.private_smem()))) return rc;
+        if ((rc = get_jit_kernel(ctx, bp, mode, shape, &jit, atomic ? 0 : shared ? plan.shared_smem() : plan.private_smem()))) return rc;
         const int64_t tile_rows = shape.rows_per_tile();
         const int64_t ntiles64 = (n + tile_rows - 1) / tile_rows;
         int blocks_per_sm = jit->kernel.blocks_per_sm;
@@ -1194,13 +1202,13 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
         const int grid = (int)std::min<int64_t>(std::max<int64_t>(ntiles64, 1), (int64_t)ctx->num_sms * blocks_per_sm);
         p.ntiles = (uint32_t)ntiles64;
         if (!atomic) {
-            if ((rc = ensure(ctx, r->g_part, (size_t)grid * (size_t)plan.lmax * (size_t)plan.nwords * 8))) return rc;
-            if ((rc = ensure(ctx, r->g_part_slot, (size_t)grid * (size_t)(1 + plan.lmax) * 4))) return rc;
+            if ((rc = ensure(ctx, r->g_part, (size_t)grid * (size_t)part_groups * (size_t)plan.nwords * 8))) return rc;
+            if ((rc = ensure(ctx, r->g_part_slot, (size_t)grid * (size_t)(1 + part_groups) * 4))) return rc;
             p.g_part = (qe_u64 *)r->g_part.ptr;
             p.g_part_slot = (qe_u32 *)r->g_part_slot.ptr;
         }
         r->mode = (int)mode;
-        r->g_variant = atomic ? 1 : 0;
+        r->g_variant = atomic ? 1 : shared ? 2 : 0;
         r->g_threads = atomic ? QE_BLOCK : plan.threads;
         QE_CUDA(qe::launch_groupby_init((uint32_t *)r->g_state.ptr, (uint64_t *)r->g_acc.ptr, (uint32_t *)r->g_ctl.ptr, nslots, gw, ctx->stream));
         ctx->launches++;
@@ -1215,7 +1223,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
         r->timed = true;
         if (n > 0 && !atomic) {
             QE_CUDA(qe::launch_groupby_merge((const uint64_t *)r->g_part.ptr, (const uint32_t *)r->g_part_slot.ptr, (uint64_t *)r->g_acc.ptr,
-                                             grid, plan.lmax, gw, ctx->stream));
+                                             grid, part_groups, gw, ctx->stream));
             ctx->launches++;
         }
         QE_CUDA(cudaMemcpyAsync(ctl, r->g_ctl.ptr, sizeof ctl, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1669,13 +1677,14 @@ static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *co
     qe::BoundPipeline bp;
     int rc = qe::bind_pipeline(schema, has_filter ? &progs[0] : nullptr, proj, aggs, bp, err, group_keys);
     if (rc) return fail(rc, err);
-    const qe::KernelMode mode = group_keys >= 0 ? (atomic ? qe::KM_GROUPBY_ATOMIC : qe::KM_GROUPBY_PRIVATE)
+    const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : atomic == 2 ? qe::KM_GROUPBY_SHARED : qe::KM_GROUPBY_PRIVATE)
                               : !bp.agg_fns.empty() ? qe::KM_AGG : bp.has_filter ? qe::KM_FILTER : qe::KM_PROJECT;
     qe_ctx dummy;
     dummy.opt_steps = steps;
     dummy.opt_vec = vec;
     dummy.opt_staging = staging;
-    const qe::TileShape shape = choose_shape(&dummy, bp, mode);
+    qe::TileShape shape = choose_shape(&dummy, bp, mode);
+    if (mode == qe::KM_GROUPBY_SHARED) { shape.gthreads = 512; shape.steps = 1; shape.vec = qe::jit_wide_loads_supported() ? 4 : 2; }
     const std::string src = qe::generate_source(bp, mode, shape);
     if (src_buf && src_cap) {
         const size_t n = std::min(src_cap - 1, src.size());

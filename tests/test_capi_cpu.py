@@ -242,3 +242,32 @@ def test_jni_shim_matches_the_c_abi():
     declared = set(re.findall(r"external fun (\w+)\(", kt))
     defined = set(re.findall(r"QE_JNI\((\w+)\)\(", c))
     assert declared == defined and len(declared) >= 15, declared ^ defined
+
+
+def test_groupby_code_of_every_variant_compiles():
+    # TPC-H Q1 shape: two STRING keys, eight aggregates, a filter (GroupByAggregationOperator.kt:21-75)
+    from queryengine_b200.engine import StringDictionary
+    S = DataType.STRING
+    A = AggregationFunction
+    d = StringDictionary()
+    schema = [(S, False), (S, True), (D, False), (D, False), (D, True), (D, False), (D, False)]
+    rf, ls, qty, ep, disc, tax, sd = [col(i, t) for i, (t, _) in enumerate(schema)]
+    net = fn(Function.MUL, ep, fn(Function.SUB, 1.0, disc))
+    exprs = [fn(Function.CMP_LE, sd, 10471.0), rf, ls, qty, ep, net, fn(Function.MUL, net, fn(Function.ADD, 1.0, tax)), qty, ep, disc, rf]
+    aggs = [A.SUM, A.SUM, A.SUM, A.MIN, A.AVG, A.AVG, A.MAX, A.COUNT]
+    L = capi.lib()
+    descs = (capi.ColDesc * len(schema))(*[capi.ColDesc(int(t), 1 if n else 0) for t, n in schema])
+    words = [serialize(e, d) for e in exprs]
+    ptrs = (C.c_void_p * len(words))(*[w.ctypes.data for w in words])
+    lens = (C.c_size_t * len(words))(*[w.size for w in words])
+    aggarr = (C.c_int32 * len(aggs))(*[int(a) for a in aggs])
+    for variant, body in ((0, "qe_groupby_private_body<P>"), (2, "qe_groupby_shared_body<P>"), (1, "qe_groupby_atomic_body<P>")):
+        src = C.create_string_buffer(1 << 17)
+        nb = C.c_size_t(0)
+        rc = L.qe_debug_generate_groupby(descs, len(schema), ptrs, lens, 1, 2, aggarr, len(aggs), variant, 1, src, len(src), C.byref(nb))
+        assert rc == 0, L.qe_last_error().decode()
+        text = src.value.decode()
+        assert body in text and nb.value > 10000
+        # SUM(qty) and AVG(qty) share one sum word, SUM(ep) and AVG(ep) another: 1 + 2 + (net: sum + count) + (gross: min + count) + (disc: max, count shared with net? no: own) ...
+        assert "NKEYS = 2" in text and "k[1] = 0ull; nulls |= 2u;" in text
+        assert text.count("a[2 * WS] = ") == 1 if variant == 0 else True

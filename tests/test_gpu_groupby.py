@@ -85,11 +85,15 @@ FIELDS = [Field("s", S, True), Field("b", B, True), Field("k", D, True), Field("
 def _check_against_oracle(ctx, rows, keys, inputs, fns, filter_, atomic, expect_variant=None, max_groups=0):
     nkeys = len(keys)
     t = _gpu_table(ctx, FIELDS, rows)
-    pipe = GroupByPipeline(t, filter_, keys, inputs, fns, atomic=atomic, max_groups=max_groups)
+    shared = atomic == "shared"
+    atomic = atomic is True
+    pipe = GroupByPipeline(t, filter_, keys, inputs, fns, atomic=atomic, shared=shared, max_groups=max_groups)
     res = pipe.run()
     if expect_variant is not None:
         assert capi.lib().qe_result_group_variant(res.handle) == expect_variant
-    op = GpuGroupByOperator(t, filter_, list(keys) + [agg(f, e) for f, e in zip(fns, inputs)], atomic=atomic, max_groups=max_groups)
+    elif atomic or shared:
+        assert capi.lib().qe_result_group_variant(res.handle) == (1 if atomic else 2)
+    op = GpuGroupByOperator(t, filter_, list(keys) + [agg(f, e) for f, e in zip(fns, inputs)], atomic=atomic, shared=shared, max_groups=max_groups)
     got = op.map()
     if not rows:
         assert got == []
@@ -137,7 +141,7 @@ def _check_against_oracle(ctx, rows, keys, inputs, fns, filter_, atomic, expect_
     return got
 
 
-@pytest.mark.parametrize("atomic", [False, True])
+@pytest.mark.parametrize("atomic", [False, "shared", True])
 @pytest.mark.parametrize("nrows", [0, 1, 300, 20000])
 def test_groupby_matches_oracle_keys_order_and_aggregates(ctx, nrows, atomic):
     rng = np.random.default_rng(7 + nrows)
@@ -159,8 +163,14 @@ def test_many_groups_fall_back_to_atomics_and_capacity_is_checked(ctx):
     n = 30000
     rows = [[None, None, float(int(rng.integers(5000))), float(np.round(rng.uniform(-10, 10), 1)), None] for _ in range(n)]
     k, x = col(2), col(3)
-    got = _check_against_oracle(ctx, rows, [k], [x, x], [A.SUM, A.COUNT], None, False, expect_variant=1)
+    # 5000 groups: no private variant holds them; a CTA of this small table meets only a few hundred, so the
+    # CTA-shared variant takes over (a CTA that met more than its shared memory holds would fall back to atomics)
+    got = _check_against_oracle(ctx, rows, [k], [x, x], [A.SUM, A.COUNT], None, False, expect_variant=2)
     assert len(got) == len({r[2] for r in rows})
+    # ~1000 groups: more than the private copies hold, one shared-memory copy per CTA takes them
+    rows1k = [[r[0], r[1], float(int(r[2]) % 1000), r[3], r[4]] for r in rows]
+    got = _check_against_oracle(ctx, rows1k, [k], [x, x, x], [A.SUM, A.COUNT, A.MIN], None, False, expect_variant=2)
+    assert len(got) == 1000
     t = _gpu_table(ctx, FIELDS, rows)
     with pytest.raises(capi.QeError) as e:
         GroupByPipeline(t, None, [k], [x], [A.SUM], max_groups=1000).run()
