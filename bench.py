@@ -334,8 +334,10 @@ def q1_pipeline(ctx, rows, row_offset=0, atomic=False):
     D, S = DataType.DOUBLE, DataType.STRING
     t = ColumnarTable(ctx, [Field("l_returnflag", S), Field("l_linestatus", S), Field("l_quantity", D), Field("l_extendedprice", D),
                             Field("l_discount", D), Field("l_tax", D), Field("l_shipdate", D)], rows)
-    t.generate(0, capi.QE_GEN_UNIFORM_INT, SEED + 7, 0, 2, row_offset=row_offset)       # codes of 'A' 'N' 'R'
-    t.generate(1, capi.QE_GEN_UNIFORM_INT, SEED + 8, 3, 4, row_offset=row_offset)       # codes of 'F' 'O'
+    codes = [ctx.dictionary.encode(v) for v in ("A", "N", "R", "F", "O")]              # the flags' dictionary codes
+    assert codes[1] == codes[0] + 1 and codes[2] == codes[0] + 2 and codes[4] == codes[3] + 1
+    t.generate(0, capi.QE_GEN_UNIFORM_INT, SEED + 7, codes[0], codes[2], row_offset=row_offset)
+    t.generate(1, capi.QE_GEN_UNIFORM_INT, SEED + 8, codes[3], codes[4], row_offset=row_offset)
     t.generate(2, capi.QE_GEN_UNIFORM_INT, SEED + 1, 1, 50, row_offset=row_offset)
     t.generate(3, capi.QE_GEN_CENTS, SEED + 2, 90000, 10499999, row_offset=row_offset)
     t.generate(4, capi.QE_GEN_CENTS, SEED + 3, 0, 10, row_offset=row_offset)
@@ -531,6 +533,33 @@ def run_ours(args):
                                      "sum": total[0], "combine": "NCCL all_gather of partials + qe_agg_combine in rank order"}
         res6.close()
         t6.close()
+        # TPC-H Q1 shape row-sharded: every rank groups its rows, the per-group partials are all-gathered and merged
+        # by key in rank order (sharding.sharded_groupby)
+        try:
+            from queryengine_b200 import capi as _capi
+            from queryengine_b200.ast import AggregationFunction as _A
+            t1, pipe1 = q1_pipeline(ctx, hi - lo, row_offset=lo)
+            res1 = pipe1.run()
+            for _ in range(3):
+                pipe1.run(res1)
+            m0, n0 = res1.kernel_stats()
+            for _ in range(max(3, args.steps)):
+                pipe1.run(res1)
+            m1, n1 = res1.kernel_stats()
+            fns1 = [_A.SUM, _A.SUM, _A.SUM, _A.SUM, _A.AVG, _A.AVG, _A.AVG, _A.COUNT]
+            rows1 = sharding.sharded_groupby(res1, 2, fns1, ctx.dictionary, lo)
+            kms = torch.tensor([(m1 - m0) / max(1, n1 - n0)], dtype=torch.float64, device=device)
+            dist.all_reduce(kms, op=dist.ReduceOp.MAX)
+            extra["q1_groupby_sf100_sharded"] = {
+                "rows": args.q6_rows, "partitions": world, "groups": len(rows1), "kernel_ms_max_over_ranks": float(kms.item()),
+                "rows_per_s": args.q6_rows / (float(kms.item()) * 1e-3),
+                "gb_per_s_aggregate": args.q6_rows * 48 / (float(kms.item()) * 1e-3) / 1e9,
+                "count_total": int(sum(r[-1] for r in rows1)),
+                "combine": "all_gather_object of per-group partials + merge by key, partials in rank order"}
+            res1.close()
+            t1.close()
+        except Exception as e:
+            extra["q1_groupby_sf100_sharded"] = {"error": repr(e)}
         # configs[4]: SF1000 lineitem (5 999 989 709 rows) row-sharded over the ranks, no collective at all
         from queryengine_b200 import sharding as sh
         total = 5_999_989_709
