@@ -414,6 +414,8 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
+    all_cpus = os.sched_getaffinity(0)
+    numa = bind_to_gpu_numa_node(local_rank)
     dist = None
     if world > 1:
         import torch.distributed as dist_mod
@@ -488,7 +490,7 @@ def run_ours(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "int64", "data": "synthetic", "config": workload_config(rows, world),
-        "roofline": roofline, "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches),
+        "roofline": roofline, "clocks": clocks.summary(), "e2e": dict(e2e, cpus_bound_near_gpu=numa), "gpu_launches": int(launches),
         "hbm_gb_per_s_aggregate": world * len(SELECTIVITIES) * args.steps * (tot_bytes / len(SELECTIVITIES)) / (ms * 1e-3) / 1e9,
     }
     for r in results:
@@ -580,6 +582,7 @@ def run_ours(args):
                 "frac_of_aggregate_peak": (rows_all * 40 + kept_all * 20) / (kms * 1e-3) / 1e9 / (peak * world)}
         except Exception as e:
             extra["lineitem_sf1000_sharded"] = {"error": repr(e)}
+    os.sched_setaffinity(0, all_cpus)          # the CPU baseline below uses every host core
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
         v, secs, ckept = cpu_leg(args.cpu_rows, threads)
@@ -596,6 +599,26 @@ def run_ours(args):
         print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
+
+
+def bind_to_gpu_numa_node(index):
+    """Pin this rank's threads to the CPUs next to its GPU (NVML's ideal affinity) before any pinned host buffer is
+    allocated, so that the end-to-end leg's staging memory sits on the GPU's NUMA node: with one rank per GPU the
+    copies of eight ranks otherwise cross the socket interconnect.  Returns the CPU count bound to, or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
 
 
 def run_e2e(args, torch, ctx, dist, device, rows, world, rank, kept_full):
