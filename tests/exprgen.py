@@ -5,9 +5,10 @@ import numpy as np
 
 from queryengine_b200.ast import (
     BooleanLiteralExpression, ColumnExpression, DataType, Expression, Function, FunctionExpression,
-    NumericLiteralExpression,
+    NumericLiteralExpression, StringLiteralExpression,
 )
 
+STRINGS = ["a", "b", "", "lineitem", "N", "never in a column"]
 LITERALS = [0.0, -0.0, 1.0, -1.0, 2.0, 0.5, 7.0, 100.0, -3.25, float("inf"), float("nan"), 1e-3, 24.0]
 
 
@@ -16,6 +17,7 @@ class ExprGen:
         self.rng = rng
         self.dcols = [i for i, f in enumerate(fields) if f.type in (DataType.DOUBLE, DataType.INT64, DataType.DATE32)]
         self.bcols = [i for i, f in enumerate(fields) if f.type == DataType.BOOLEAN]
+        self.scols = [i for i, f in enumerate(fields) if f.type == DataType.STRING]
         self.fields = fields
 
     def _col(self, i) -> ColumnExpression:
@@ -36,8 +38,20 @@ class ExprGen:
             return FunctionExpression(f, [self.double(depth - 1)])
         return FunctionExpression(Function.IF, [self.boolean(depth - 1), self.double(depth - 1), self.double(depth - 1)])
 
+    def string(self, depth: int) -> Expression:
+        """STRING-typed trees: columns, literals, IF (all the reference's TypeCheck allows, TypeCheck.kt:86-94)."""
+        r = self.rng
+        if depth <= 0 or r.random() < 0.4:
+            if self.scols and r.random() < 0.7:
+                return self._col(int(r.choice(self.scols)))
+            return StringLiteralExpression(STRINGS[int(r.integers(len(STRINGS)))])
+        return FunctionExpression(Function.IF, [self.boolean(depth - 1), self.string(depth - 1), self.string(depth - 1)])
+
     def boolean(self, depth: int) -> Expression:
         r = self.rng
+        if self.scols and depth > 0 and r.random() < 0.2:      # string equality, TypeCheck.kt:65-71
+            f = Function.CMP_EQ if r.random() < 0.5 else Function.CMP_NE
+            return FunctionExpression(f, [self.string(depth - 1), self.string(depth - 1)])
         if depth <= 0 or r.random() < 0.1:
             if self.bcols and r.random() < 0.8:
                 return self._col(int(r.choice(self.bcols)))

@@ -502,3 +502,40 @@ def test_string_equality_if_and_filter_match_the_oracle(ctx, nrows, interpreter)
         want = OraclePlan(otable, [0, 1, 2, 3], filter=filters[2], projections=[projs[2], s0], aggregates=[A.COUNT, A.COUNT]).rows()
         assert got == want
     t.close()
+
+
+def _row_values_equal(a, b):
+    import math
+    if isinstance(a, float) and isinstance(b, float):
+        return (math.isnan(a) and math.isnan(b)) or (a == b and math.copysign(1.0, a) == math.copysign(1.0, b))
+    return a == b and type(a) == type(b)
+
+
+@pytest.mark.parametrize("interpreter", [False, True])
+@pytest.mark.parametrize("seed", range(8))
+def test_random_trees_with_string_columns(ctx, seed, interpreter):
+    """Random well-typed trees over DOUBLE / BOOLEAN / STRING columns (string equality, IF over strings, strings
+    inside filters): rows out of the GPU operator == rows out of the oracle, which evaluates real strings."""
+    from exprgen import STRINGS
+    from oracle_binding import OraclePlan, OracleTable
+    rng = np.random.default_rng(4000 + seed)
+    n = int(rng.integers(1, 4000))
+    fields = [Field("d0", D, False), Field("d1", D, True), Field("b0", B, True), Field("s0", S, True), Field("s1", S, False)]
+    vocab = STRINGS[:5] + ["x"]
+    rows = []
+    for _ in range(n):
+        rows.append([float(np.round(rng.uniform(-5, 5), 1)) if rng.random() < 0.9 else float(rng.choice([np.nan, -0.0, np.inf])),
+                     None if rng.random() < 0.2 else float(int(rng.integers(-3, 4))),
+                     None if rng.random() < 0.2 else bool(rng.random() < 0.5),
+                     None if rng.random() < 0.2 else vocab[int(rng.integers(len(vocab)))],
+                     vocab[int(rng.integers(3))]])
+    g = ExprGen(rng, fields)
+    filt = g.boolean(4) if seed % 3 else None
+    projs = [g.string(3), g.boolean(4), g.double(4), g.string(2)]
+    t = _rows_table(ctx, fields, rows)
+    got = GpuPipelineOperator(t, filt, projs, None, interpreter=interpreter).map()
+    want = OraclePlan(OracleTable.from_rows([f.type for f in fields], rows), list(range(len(fields))), filter=filt, projections=projs).rows()
+    assert len(got) == len(want)
+    for i, (g_, w_) in enumerate(zip(got, want)):
+        assert all(_row_values_equal(a, b) for a, b in zip(g_, w_)), (i, g_, w_)
+    t.close()
