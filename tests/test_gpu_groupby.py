@@ -227,3 +227,24 @@ def test_row_range_partitions_merge_to_the_whole_table_result(ctx):
     for w, m in zip(op.map(), merged):
         assert all(_same(a, c) for a, c in zip(w, m)), (w, m)
     t.close()
+
+
+def test_int64_and_date32_key_columns(ctx):
+    # INT64 / DATE32 have no reference counterpart: the oracle sees their exact f64 widening
+    I, T = DataType.INT64, DataType.DATE32
+    rng = np.random.default_rng(77)
+    n = 10007
+    ki = rng.integers(-3, 4, n).astype(np.int64) * (1 << 40)
+    kd = rng.integers(9000, 9004, n).astype(np.int32)
+    vd = rng.random(n) < 0.9
+    x = np.round(rng.uniform(0, 10, n), 0)
+    fields = [Field("ki", I, False), Field("kd", T, True), Field("x", D, False)]
+    t = ColumnarTable.from_arrays(ctx, fields, [ki, kd, x], [None, vd, None])
+    got = GpuGroupByOperator(t, None, [col(0, I), col(1, T), agg(A.SUM, col(2)), agg(A.COUNT, col(2))]).map()
+    ot = OracleTable([D, D, D], n)
+    ot.set_column(0, ki.astype(np.float64))
+    ot.set_column(1, kd.astype(np.float64), np.packbits(vd.astype(np.uint8), bitorder="little"))
+    ot.set_column(2, x)
+    want = OraclePlan(ot, [0, 1, 2], projections=[col(0), col(1), col(2), col(2)], aggregates=[A.SUM, A.COUNT], group_count=2).rows()
+    assert got == want and len(got) == 7 * 5
+    t.close()
