@@ -150,7 +150,7 @@ bool jit_load(const std::vector<char> &cubin, const char *entry, size_t dyn_smem
     else
         (void)cudaGetLastError();
     cudaFuncAttributes fa;
-    if (cudaFuncGetAttributes(&fa, (const void *)out.kernel) == cudaSuccess) out.regs = fa.numRegs;
+    if (cudaFuncGetAttributes(&fa, (const void *)out.kernel) == cudaSuccess) { out.regs = fa.numRegs; out.local_bytes = fa.localSizeBytes; }
     else (void)cudaGetLastError();
     return true;
 }

@@ -22,6 +22,7 @@ struct JitKernel {
     cudaKernel_t kernel = nullptr;
     int blocks_per_sm = 1;
     int regs = 0;
+    size_t local_bytes = 0; // per-thread local memory (register spills)
     size_t dyn_smem = 0;    // dynamic shared memory per CTA
 };
 
