@@ -205,7 +205,9 @@ QE_API int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_pipel
  * always does, M/data/MemoryTable.kt:7): uploads, kernels and downloads of neighbouring row-range
  * chunks overlap on three streams.  Host buffers should be pinned (qe_host_alloc) for the copies to
  * be asynchronous.  Returns when every copy has completed; the results also stay readable through
- * qe_result_* as after qe_pipeline_run.  Filter and projection pipelines only. */
+ * qe_result_* as after qe_pipeline_run.  Filter, projection and global-aggregation pipelines: an
+ * aggregation treats every chunk as a partition and folds the chunks' partials in chunk order
+ * (read it with qe_result_agg / qe_result_agg_partial). */
 typedef struct qe_stream_desc {
     int64_t chunk_rows;                          /* rows per chunk, a multiple of 128; 0 = 32 Mi */
     const void *const *host_values;              /* [table columns] source of each column (as qe_table_upload), NULL entry = already resident */

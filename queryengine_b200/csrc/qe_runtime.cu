@@ -1578,6 +1578,10 @@ extern "C" int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_
 
     unsigned long long *counts = nullptr;                      // pinned: kept rows after chunk c of pipeline q
     QE_CUDA(cudaHostAlloc((void **)&counts, sizeof(unsigned long long) * (size_t)nchunks * np, cudaHostAllocDefault));
+    // aggregations: the partials of every chunk (pinned), combined in chunk order when all chunks are done
+    double *chunk_aggs = nullptr;                              // [chunk][pipeline][QE_MAX_AGGS][4]
+    const size_t agg_stride = (size_t)QE_MAX_AGGS * 4;
+    QE_CUDA(cudaHostAlloc((void **)&chunk_aggs, sizeof(double) * agg_stride * (size_t)nchunks * np, cudaHostAllocDefault));
     std::vector<cudaEvent_t> ev_up(nchunks, nullptr), ev_run((size_t)nchunks * np, nullptr);
     std::vector<StreamSinkState> sink(np);
     int rc = QE_OK;
@@ -1588,6 +1592,8 @@ extern "C" int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_
         for (cudaEvent_t e : ev_up) if (e) cudaEventDestroy(e);
         for (cudaEvent_t e : ev_run) if (e) cudaEventDestroy(e);
         cudaFreeHost(counts);
+        cudaFreeHost(chunk_aggs);
+        chunk_aggs = nullptr;
     };
 #define QE_STREAM_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { rc = fail_cuda(#call, e__); cleanup(); return rc; } } while (0)
 
@@ -1603,6 +1609,7 @@ extern "C" int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_
             cudaError_t e = cudaEventSynchronize(ev_run[(size_t)c * np + q]);
             if (e != cudaSuccess) return fail_cuda("cudaEventSynchronize", e);
             qe_result *r = sd->results[q];
+            if (r->mode == qe::KM_AGG) continue;                // nothing to download per chunk
             int64_t upto = r->mode == qe::KM_PROJECT ? std::min<int64_t>((int64_t)(c + 1) * chunk, n)
                                                      : (int64_t)counts[(size_t)c * np + q];
             upto = std::min(upto, r->capacity);
@@ -1641,12 +1648,18 @@ extern "C" int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_
             qe_pipeline_desc d = sd->pipelines[q];
             d.row_begin = r0;
             d.row_end = r1;
-            d.flags = (d.flags & ~(uint32_t)QE_RUN_APPEND) | (c > 0 ? (uint32_t)QE_RUN_APPEND : 0u);
+            const bool is_agg = d.nagg > 0;
+            d.flags = (d.flags & ~(uint32_t)QE_RUN_APPEND) | ((c > 0 && !is_agg) ? (uint32_t)QE_RUN_APPEND : 0u);
             if (d.out_capacity_rows <= 0) d.out_capacity_rows = n;
             rc = qe_pipeline_run_ex(ctx, table, &d, &sd->results[q]);
             if (rc) { cleanup(); return rc; }
             qe_result *r = sd->results[q];
-            if (r->mode == qe::KM_AGG) { cleanup(); return fail(QE_ERR_UNSUPPORTED, "qe_pipeline_stream: aggregations are not streamed"); }
+            if (r->mode == qe::KM_AGG) {
+                // every chunk is one partition: keep its partials (GlobalAggregationOperator over a row range)
+                double *dst = chunk_aggs + ((size_t)c * np + q) * agg_stride;
+                if (r1 > r0) QE_STREAM_CUDA(cudaMemcpyAsync(dst, r->final_aggs.ptr, sizeof(double) * agg_stride, cudaMemcpyDeviceToHost, ctx->stream));
+                else memset(dst, 0, sizeof(double) * agg_stride);
+            }
             QE_STREAM_CUDA(cudaMemcpyAsync(&counts[(size_t)c * np + q], r->ctl.ptr, sizeof(unsigned long long),
                                            cudaMemcpyDeviceToHost, ctx->stream));
             QE_STREAM_CUDA(cudaEventCreateWithFlags(&ev_run[(size_t)c * np + q], cudaEventDisableTiming));
@@ -1657,6 +1670,31 @@ extern "C" int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_
     }
     if ((rc = drain(nchunks - 1))) { cleanup(); return rc; }
 #undef QE_STREAM_CUDA
+    cudaStreamSynchronize(ctx->stream);
+    for (int q = 0; q < np; q++) {
+        qe_result *r = sd->results[q];
+        if (r->mode != qe::KM_AGG) continue;
+        // partials of the chunks folded in chunk order (as qe_agg_combine folds partitions in rank order)
+        for (size_t k = 0; k < r->agg_fns.size(); k++) {
+            double sum = 0.0, mn = qe_bits_f64((qe_i64)0x7ff0000000000000LL), mx = qe_bits_f64((qe_i64)0xfff0000000000000ULL);
+            int64_t count = 0;
+            for (int c = 0; c < nchunks; c++) {
+                const double *src = chunk_aggs + ((size_t)c * np + q) * agg_stride + k * 4;
+                int64_t cnt;
+                memcpy(&cnt, &src[1], sizeof cnt);
+                if (cnt == 0) continue;
+                count += cnt;
+                sum += src[0];
+                mn = qe_math_min(mn, src[2]);
+                mx = qe_math_max(mx, src[3]);
+            }
+            r->host->agg[k][0] = sum;
+            memcpy(&r->host->agg[k][1], &count, sizeof count);
+            r->host->agg[k][2] = mn;
+            r->host->agg[k][3] = mx;
+        }
+        r->batch_rows = n;
+    }
     cleanup();
     for (int q = 0; q < np; q++) {                             // the runs are complete: make the results readable
         qe_result *r = sd->results[q];

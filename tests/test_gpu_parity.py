@@ -539,3 +539,38 @@ def test_random_trees_with_string_columns(ctx, seed, interpreter):
     for i, (g_, w_) in enumerate(zip(got, want)):
         assert all(_row_values_equal(a, b) for a, b in zip(g_, w_)), (i, g_, w_)
     t.close()
+
+
+@pytest.mark.parametrize("chunk", [4096, 65536, 1 << 20])
+def test_stream_aggregation_folds_chunk_partials(ctx, chunk):
+    """qe_pipeline_stream with a GlobalAggregation pipeline: every chunk is a partition, partials folded in chunk
+    order -- COUNT / MIN / MAX identical to the one-shot run, SUM exact on integer-valued terms; a filter pipeline
+    rides along in the same call."""
+    from queryengine_b200.engine import stream_pipelines
+    rng = np.random.default_rng(chunk + 1)
+    n = 300_007
+    q = rng.integers(0, 50, n).astype(np.float64)
+    x = rng.integers(-1000, 1000, n).astype(np.float64)
+    xv = rng.random(n) > 0.3
+    fields = [Field("q", D, False), Field("x", D, True)]
+    ref_t = ColumnarTable.from_arrays(ctx, fields, [q, x], [None, xv])
+    filt = fn(Function.CMP_LT, col(0), 24.0)
+    projs = [fn(Function.MUL, col(0), col(1)), col(1), col(1), col(1), col(0)]
+    fns = [A.SUM, A.COUNT, A.MIN, A.MAX, A.AVG]
+    whole = Pipeline(ref_t, filt, projs, fns).run()
+    t = ColumnarTable(ctx, fields, n)
+    xbits = np.packbits(xv.astype(np.uint8), bitorder="little")
+    sel = np.zeros(n, np.uint32)
+    pipes = [Pipeline(t, filt, projs, fns), Pipeline(t, filt, [col(0)])]
+    res = stream_pipelines(t, pipes, [q.ctypes.data, x.ctypes.data], [None, xbits.ctypes.data], chunk_rows=chunk,
+                           host_selection=[None, sel.ctypes.data], host_out_values=[None, [None]], host_out_validity=[None, [None]])
+    for k in range(len(fns)):
+        assert res[0].agg(k) == whole.agg(k), (fns[k], res[0].agg(k), whole.agg(k))
+    keep = q < 24.0
+    assert res[0].agg(1) == float(np.count_nonzero(keep & xv))
+    assert res[0].agg(0) == float(np.sum((q * x)[keep & xv]))
+    assert res[1].num_rows == int(keep.sum()) and np.array_equal(sel[:res[1].num_rows], np.nonzero(keep)[0])
+    for r in res + [whole]:
+        r.close()
+    t.close()
+    ref_t.close()
