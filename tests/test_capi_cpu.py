@@ -271,3 +271,30 @@ def test_groupby_code_of_every_variant_compiles():
         # SUM(qty) and AVG(qty) share one sum word, SUM(ep) and AVG(ep) another: 1 + 2 + (net: sum + count) + (gross: min + count) + (disc: max, count shared with net? no: own) ...
         assert "NKEYS = 2" in text and "k[1] = 0ull; nulls |= 2u;" in text
         assert text.count("a[2 * WS] = ") == 1 if variant == 0 else True
+
+
+def test_malformed_programs_are_rejected_not_crashed():
+    # random word streams through the parser / binder (no GPU needed): every outcome is a status code
+    L = capi.lib()
+    rng = np.random.default_rng(99)
+    schema = [(D, True), (B, False), (DataType.STRING, True), (I, False)]
+    descs = (capi.ColDesc * len(schema))(*[capi.ColDesc(int(t), 1 if n else 0) for t, n in schema])
+    ops = list(range(17)) + [32, 33, 34, 35, 36, 99, 255]
+    seen = set()
+    for trial in range(3000):
+        n = int(rng.integers(1, 24))
+        w = np.zeros(n, np.uint32)
+        for i in range(n):
+            op = ops[int(rng.integers(len(ops)))]
+            arg = int(rng.integers(0, 6)) if rng.random() < 0.9 else int(rng.integers(0, 1 << 24))
+            w[i] = op | (arg << 8)
+        ptrs = (C.c_void_p * 1)(w.ctypes.data)
+        lens = (C.c_size_t * 1)(w.size)
+        aggarr = (C.c_int32 * 1)(0)
+        nb = C.c_size_t(0)
+        rc = L.qe_debug_generate(descs, len(schema), ptrs, lens, 0, 1, aggarr, 0, 0, 0, -1, 0, None, 0, None, 0, C.byref(nb))
+        seen.add(rc)
+        assert rc in (capi.QE_OK, capi.QE_ERR_PROGRAM, capi.QE_ERR_INVALID_ARGUMENT, capi.QE_ERR_UNSUPPORTED), (rc, list(w))
+        rc = L.qe_debug_generate_groupby(descs, len(schema), ptrs, lens, 0, 1, aggarr, 0, int(rng.integers(3)), 0, None, 0, C.byref(nb))
+        assert rc in (capi.QE_OK, capi.QE_ERR_PROGRAM, capi.QE_ERR_INVALID_ARGUMENT, capi.QE_ERR_UNSUPPORTED), (rc, list(w))
+    assert capi.QE_OK in seen and capi.QE_ERR_PROGRAM in seen
