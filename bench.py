@@ -477,7 +477,7 @@ def run_ours(args):
             traffic = json.load(open(tp)).get("filter_sweep_dram_bytes_per_launch")
         except Exception:
             traffic = None
-    roofline = {"bound": "hbm", "kernel": "qe_kernel (generated filter+compaction, qe_filter_ring_body)", "achieved": achieved,
+    roofline = {"bound": "hbm", "kernel": "qe_filter_ring_kernel (generated filter + compaction, body qe_filter_ring_body)", "achieved": achieved,
                 "peak": peak, "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak,
                 "frac_of_nominal_8000": achieved / 8000.0, "traffic": traffic,
                 "algorithmic_bytes_per_launch": tot_bytes / len(SELECTIVITIES),

@@ -731,11 +731,25 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                      : mode == KM_GROUPBY_PRIVATE ? "qe_groupby_private_body"
                      : mode == KM_GROUPBY_SHARED ? "qe_groupby_shared_body" : "qe_groupby_atomic_body";
     snprintf(b, sizeof b,
-             "extern \"C\" __global__ void __launch_bounds__(%d, %d) " QE_JIT_ENTRY
+             "extern \"C\" __global__ void __launch_bounds__(%d, %d) %s"
              "(const __grid_constant__ QeParams p)\n{\n    %s<P>(p);\n}\n",
-             mode == KM_FILTER ? shape.block_threads() : (mode == KM_GROUPBY_PRIVATE || mode == KM_GROUPBY_SHARED) ? shape.gthreads : 256, shape.min_blocks, body);
+             mode == KM_FILTER ? shape.block_threads() : (mode == KM_GROUPBY_PRIVATE || mode == KM_GROUPBY_SHARED) ? shape.gthreads : 256, shape.min_blocks,
+             jit_entry_name(mode, shape), body);
     s += b;
     return s;
+}
+
+const char *jit_entry_name(KernelMode mode, const TileShape &shape)
+{
+    switch (mode) {
+    case KM_FILTER: return shape.ring ? "qe_filter_ring_kernel" : shape.staged ? "qe_filter_staged_kernel"
+                         : shape.pipelined ? "qe_filter_pipelined_kernel" : "qe_filter_kernel";
+    case KM_PROJECT: return "qe_project_kernel";
+    case KM_AGG: return "qe_agg_kernel";
+    case KM_GROUPBY_PRIVATE: return "qe_groupby_private_kernel";
+    case KM_GROUPBY_SHARED: return "qe_groupby_shared_kernel";
+    default: return "qe_groupby_atomic_kernel";
+    }
 }
 
 }  // namespace qe

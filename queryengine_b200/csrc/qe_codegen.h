@@ -59,8 +59,9 @@ struct TileShape {
 // bytes of dynamic shared memory the staged filter kernel needs (0 when not staged)
 size_t staged_smem_bytes(const BoundPipeline &bp, const TileShape &shape);
 
-// name of the generated entry point
-#define QE_JIT_ENTRY "qe_kernel"
+// name of the generated entry point: one per kernel body, so that a profiler's launch list says which
+// kernel of DESIGN.md section 4 a launch was (qe_filter_ring_kernel, qe_project_kernel, qe_agg_kernel, ...)
+const char *jit_entry_name(KernelMode mode, const TileShape &shape);
 
 std::string generate_source(const BoundPipeline &bp, KernelMode mode, const TileShape &shape);
 

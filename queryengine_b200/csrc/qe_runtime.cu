@@ -718,7 +718,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     JitEntry e;
     e.shape = shape;
     std::string err;
-    if (!qe::jit_load(cubin, QE_JIT_ENTRY, dyn_smem ? dyn_smem : qe::staged_smem_bytes(bp, shape), mode == qe::KM_FILTER ? shape.block_threads()
+    if (!qe::jit_load(cubin, qe::jit_entry_name(mode, shape), dyn_smem ? dyn_smem : qe::staged_smem_bytes(bp, shape), mode == qe::KM_FILTER ? shape.block_threads()
                       : (mode == qe::KM_GROUPBY_PRIVATE || mode == qe::KM_GROUPBY_SHARED) ? shape.gthreads : QE_BLOCK,
                       e.kernel, err))
         return fail(QE_ERR_JIT, err);

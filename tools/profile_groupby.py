@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""One group-by launch for ncu (development tool):  ncu --set full -k qe_kernel ... python tools/profile_groupby.py --card 32"""
+"""One group-by launch for ncu (development tool):  ncu --set full -k qe_groupby_private_kernel ... python tools/profile_groupby.py --card 32"""
 import argparse, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)

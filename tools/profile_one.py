@@ -15,7 +15,7 @@ from queryengine_b200.ast import DataType, Function, col, fn  # noqa: E402
 from queryengine_b200.engine import ColumnarTable, Context, Field, Pipeline  # noqa: E402
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--what", default="filter", choices=["filter", "tree", "q6"])
+ap.add_argument("--what", default="filter", choices=["filter", "tree", "q6", "sf", "q1"])
 ap.add_argument("--sel", type=float, default=0.5)
 ap.add_argument("--rows", type=int, default=1_000_000_000)
 ap.add_argument("--reps", type=int, default=3)
@@ -36,6 +36,12 @@ elif args.what == "tree":
     for c, rate in enumerate((0.0, 0.01, 0.10, 0.50)):
         t.generate(c, capi.QE_GEN_UNIFORM_REAL, 52 + c, -1000.0, 1000.0, null_rate=rate)
     pipe = Pipeline(t, None, [bench.tree_expr()])
+elif args.what == "sf":
+    import bench
+    t, pipe = bench.sf_filter_pipeline(ctx, args.rows)
+elif args.what == "q1":
+    import bench
+    t, pipe = bench.q1_pipeline(ctx, args.rows)
 else:
     import bench
     t, pipe = bench.q6_pipeline(ctx, args.rows)
