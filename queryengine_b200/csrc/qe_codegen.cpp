@@ -457,7 +457,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                      shape.nlb, shape.defer, shape.loads);
             s += b;
             // one row (lane-strided: a warp step reads 32 consecutive rows, conflict-free) from a stage
-            s += "    static __device__ __forceinline__ void load_row(const unsigned char *stage, int wrow0, int c, Row &row) {\n";
+            s += "    static __device__ __forceinline__ void load_row(qe_u32 stage, int wrow0, int c, Row &row) {\n";
             for (int i = 0; i < nslots; i++) {
                 const int t = bp.slot_info[i].type;
                 if (t == 2) snprintf(b, sizeof b, "        row.c%d = qe_stage1_bit(stage + %d, wrow0, c);\n", i, L.val_off[i]);

@@ -928,6 +928,69 @@ __device__ __forceinline__ bool qe_stage1_bit(const unsigned char *bitmap, int w
     return (*(const qe_u32 *)(bitmap + (size_t)(wrow0 >> 5) * 4 + (size_t)(c >> 5) * 4) >> qe_lane()) & 1u;
 }
 
+// the same through a 32-bit shared-window address (ring variant): the kernel keeps ONE opaque base in a
+// register and every shared access is base + constant.  With C++ pointers to __shared__ objects nvcc
+// re-derives each address inside the loop (MOV window base, VIADD offset, S2R SR_CgaCtaId, LEA): three S2R
+// and ~30 address instructions per consumer warp and tile, measured as `wait` / short-scoreboard stalls.
+__device__ __forceinline__ double qe_stage1_f64(qe_u32 col, int wrow0, int c)
+{
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(col + (qe_u32)(wrow0 + (int)qe_lane()) * 8u + (qe_u32)c * 8u));
+    return v;
+}
+__device__ __forceinline__ qe_i64 qe_stage1_i64(qe_u32 col, int wrow0, int c)
+{
+    qe_i64 v;
+    asm volatile("ld.shared.s64 %0, [%1];" : "=l"(v) : "r"(col + (qe_u32)(wrow0 + (int)qe_lane()) * 8u + (qe_u32)c * 8u));
+    return v;
+}
+__device__ __forceinline__ qe_i32 qe_stage1_i32(qe_u32 col, int wrow0, int c)
+{
+    qe_i32 v;
+    asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(col + (qe_u32)(wrow0 + (int)qe_lane()) * 4u + (qe_u32)c * 4u));
+    return v;
+}
+__device__ __forceinline__ bool qe_stage1_bit(qe_u32 bitmap, int wrow0, int c)
+{
+    qe_u32 w;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(bitmap + (qe_u32)(wrow0 >> 5) * 4u + (qe_u32)(c >> 5) * 4u));
+    return (w >> qe_lane()) & 1u;
+}
+
+__device__ __forceinline__ qe_u32 qe_lds_u32(qe_u32 a)
+{
+    qe_u32 v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ qe_u64 qe_lds_u64(qe_u32 a)
+{
+    qe_u64 v;
+    asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void qe_lds_u32x4(qe_u32 a, qe_u32 &x, qe_u32 &y, qe_u32 &z, qe_u32 &w)
+{
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(x), "=r"(y), "=r"(z), "=r"(w) : "r"(a) : "memory");
+}
+__device__ __forceinline__ void qe_sts_u32(qe_u32 a, qe_u32 v)
+{
+    asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ void qe_sts_u64(qe_u32 a, qe_u64 v)
+{
+    asm volatile("st.shared.u64 [%0], %1;" :: "r"(a), "l"(v) : "memory");
+}
+__device__ __forceinline__ void qe_sts_u32x4(qe_u32 a, qe_u32 x, qe_u32 y, qe_u32 z, qe_u32 w)
+{
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" :: "r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
+__device__ __forceinline__ qe_u32 qe_opaque_u32(qe_u32 x)
+{
+    asm volatile("" : "+r"(x));
+    return x;
+}
+
 // K1, staged variant.  Additional members of P:
 //   static constexpr int NSTAGES, STAGE_BYTES (stride of one stage), STAGE_TX (bytes the copies of one stage move);
 //   static void issue(const QeParams&, qe_i64 tile_row0, qe_u32 stage_smem, qe_u32 mbar);   one thread
@@ -1108,7 +1171,7 @@ __device__ __forceinline__ T *qe_opaque_ptr(T *q)
 // stores), and for sparse tiles a loop over the steps that kept anything.
 template <class P, bool CHECK_CAP, bool HAS_SEL>
 __device__ __forceinline__ void qe_ring_scatter_step(const QeParams &p, const typename P::Ptrs &ptrs, qe_u32 *selp,
-                                                     const unsigned char *stage, int wrow0, int c, qe_u32 row_id, qe_u64 wbase,
+                                                     qe_u32 stage, int wrow0, int c, qe_u32 row_id, qe_u64 wbase,
                                                      qe_u32 cap_left, qe_u32 m, qe_u32 &off)
 {
     const qe_u32 lane = qe_lane();
@@ -1133,9 +1196,10 @@ __device__ __forceinline__ void qe_ring_scatter_step(const QeParams &p, const ty
 }
 
 template <class P, int STEPS, bool CHECK_CAP, bool HAS_SEL>
-__device__ __forceinline__ void qe_ring_scatter(const QeParams &p, const unsigned char *stage, int wrow0, qe_u32 first_row,
-                                                qe_u64 wbase, const qe_u32 *masks, qe_u32 cnt)
+__device__ __forceinline__ void qe_ring_scatter(const QeParams &p, qe_u32 stage, int wrow0, qe_u32 first_row,
+                                                qe_u64 wbase, qe_u32 masks, qe_u32 cnt)
 {
+    // stage, masks: shared-window addresses of the tile's stage and of this warp's STEPS keep-mask words
     const qe_u32 lane = qe_lane();
     const typename P::Ptrs ptrs = P::out_ptrs(p, wbase);
     qe_u32 *const selp = HAS_SEL ? qe_opaque_ptr(p.sel + wbase) : (qe_u32 *)0;
@@ -1147,14 +1211,19 @@ __device__ __forceinline__ void qe_ring_scatter(const QeParams &p, const unsigne
     qe_u32 off = 0;                                           // kept rows of this warp in earlier steps
     if (cnt * 4u >= (qe_u32)(STEPS * 32)) {
         qe_u32 mk[STEPS];
+        if (STEPS % 4 == 0) {
 #pragma unroll
-        for (int s = 0; s < STEPS; s++) mk[s] = masks[s];
+            for (int s = 0; s < STEPS; s += 4) qe_lds_u32x4(masks + (qe_u32)s * 4u, mk[s], mk[s + 1], mk[s + 2], mk[s + 3]);
+        } else {
+#pragma unroll
+            for (int s = 0; s < STEPS; s++) mk[s] = qe_lds_u32(masks + (qe_u32)s * 4u);
+        }
 #pragma unroll
         for (int s = 0; s < STEPS; s++)
             qe_ring_scatter_step<P, CHECK_CAP, HAS_SEL>(p, ptrs, selp, stage, wrow0, s * 32, first_row + (qe_u32)(s * 32), wbase,
                                                         cap_left, mk[s], off);
     } else {
-        const qe_u32 mine = lane < (qe_u32)STEPS ? masks[lane] : 0u;
+        const qe_u32 mine = lane < (qe_u32)STEPS ? qe_lds_u32(masks + lane * 4u) : 0u;
         qe_u32 act = __ballot_sync(QE_FULL_MASK, mine != 0u);
         while (act) {
             const int s = __ffs((int)act) - 1;
@@ -1205,30 +1274,39 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
     constexpr int WROWS = TILE / NCW, STEPS = WROWS / 32;
     static_assert(WROWS % 32 == 0 && NCW <= 32 && DEFER >= 1 && DEFER < NST && NLB >= 1 && NLB <= NST, "ring shape");
 
+    // control block, addressed as (one opaque 32-bit shared-window base) + constant: see qe_stage1_*(qe_u32, ...)
+    constexpr qe_u32 O_FULL = 0, O_CLAIM = 8 * NST, O_EVAL = 16 * NST, O_PREF = 24 * NST, O_EMPTY = 32 * NST;   // mbarriers [NST]
+    constexpr qe_u32 O_INCL = 40 * NST;                       // u64 [NST]: kept rows up to and including the tile
+    constexpr qe_u32 O_WBASE = 48 * NST;                      // u64 [NST][NCW]: output position of each consumer warp's first kept row
+    constexpr qe_u32 O_TILE = O_WBASE + 8 * NST * NCW;        // u32 [NST] each: tile, lo, row0, fits
+    constexpr qe_u32 O_LO = O_TILE + 4 * NST, O_ROW0 = O_LO + 4 * NST, O_FITS = O_ROW0 + 4 * NST;
+    constexpr qe_u32 O_CNT = (O_FITS + 4 * NST + 15u) & ~15u; // u32 [NST][NCW]
+    constexpr qe_u32 O_MASK = (O_CNT + 4 * NST * NCW + 15u) & ~15u;   // u32 [NST][TILE / 32]
+    constexpr qe_u32 CTL_BYTES = O_MASK + 4 * NST * (TILE / 32);
+
     extern __shared__ __align__(128) unsigned char qe_dyn_smem[];
-    __shared__ __align__(8) qe_u64 s_full[NST], s_claim[NST], s_eval[NST], s_pref[NST], s_empty[NST];
-    __shared__ qe_u64 s_incl[NST];
-    __shared__ qe_u64 s_wbase[NST][NCW];                      // output position of each consumer warp's first kept row
-    __shared__ qe_u32 s_tile[NST], s_lo[NST], s_row0[NST];
-    __shared__ qe_u32 s_fits[NST];
-    __shared__ __align__(16) qe_u32 s_cnt[NST][NCW];
-    __shared__ __align__(16) qe_u32 s_mask[NST][TILE / 32];
+    __shared__ __align__(16) unsigned char s_ctl[CTL_BYTES];
 
     const qe_u32 lane = qe_lane(), warp = qe_warp();
     qe_u32 *const desc = (qe_u32 *)p.tile_state;             // one 32-bit descriptor per tile: 0 = not counted yet, else count + 1
+    const qe_u32 cb = qe_opaque_u32(qe_smem_addr(s_ctl));
+    const qe_u32 dyn = qe_opaque_u32(qe_smem_addr(qe_dyn_smem));
 
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int st = 0; st < NST; st++) {
-            qe_mbar_init(qe_smem_addr(&s_full[st]), 1);
-            qe_mbar_init(qe_smem_addr(&s_claim[st]), 1);
-            qe_mbar_init(qe_smem_addr(&s_eval[st]), NCW);
-            qe_mbar_init(qe_smem_addr(&s_pref[st]), 1);
-            qe_mbar_init(qe_smem_addr(&s_empty[st]), NCW + 2);
+            qe_mbar_init(cb + O_FULL + 8u * st, 1);
+            qe_mbar_init(cb + O_CLAIM + 8u * st, 1);
+            qe_mbar_init(cb + O_EVAL + 8u * st, NCW);
+            qe_mbar_init(cb + O_PREF + 8u * st, 1);
+            qe_mbar_init(cb + O_EMPTY + 8u * st, NCW + 2);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+
+    // every role walks the stages round robin: st = it % NST and par = (it / NST) & 1 are carried, not divided out
+#define QE_RING_NEXT(st_, par_, by_) do { st_ += (by_); if (st_ >= (qe_u32)NST) { st_ -= (qe_u32)NST; par_ ^= 1u; } } while (0)
 
     if (warp == 0) {
         // ------------------------------------------------------------ producer
@@ -1239,79 +1317,79 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
             qe_u64 rt_acc[16] = {};
             QE_RT_BEGIN();
             for (qe_u32 it = 0;; it++) {
-                const int st = (int)(it % NST);
+                const qe_u32 st = it % NST;
                 QE_RT_RESET();
-                if (it >= NST) qe_mbar_wait(qe_smem_addr(&s_empty[st]), ((it / NST) - 1u) & 1u);
+                if (it >= NST) qe_mbar_wait(cb + O_EMPTY + 8u * st, ((it / NST) - 1u) & 1u);
                 QE_RT_ADD(0);
                 // at most LOADS tiles in flight: more only queue up in the memory system, and every
                 // descriptor read of the look-back then waits behind them
                 if (P::LOADS > 0 && it >= (qe_u32)P::LOADS && ended == 0u) {
                     const qe_u32 jt = it - (qe_u32)P::LOADS;
-                    qe_mbar_wait(qe_smem_addr(&s_full[jt % NST]), (jt / NST) & 1u);
+                    qe_mbar_wait(cb + O_FULL + 8u * (jt % NST), (jt / NST) & 1u);
                 }
                 QE_RT_ADD(1);
                 rt_acc[2] += 1;
-                s_tile[st] = t;
-                s_lo[st] = lo;                                // tiles [lo, t) belong to other CTAs
-                s_row0[st] = p.sel_base + t * (qe_u32)TILE;    // selection-vector value of the tile's first row
+                qe_sts_u32(cb + O_TILE + 4u * st, t);
+                qe_sts_u32(cb + O_LO + 4u * st, lo);           // tiles [lo, t) belong to other CTAs
+                qe_sts_u32(cb + O_ROW0 + 4u * st, p.sel_base + t * (qe_u32)TILE);   // selection-vector value of the tile's first row
                 lo = t + 1u;
-                qe_mbar_arrive(qe_smem_addr(&s_claim[st]));
+                qe_mbar_arrive(cb + O_CLAIM + 8u * st);
                 if (t >= p.ntiles) {
                     // end marker: wakes the consumers (first one only), carries no bytes; every look-back
                     // warp must meet one on its own round-robin slot, so NLB of them are written
-                    if (ended == 0u) qe_mbar_arrive(qe_smem_addr(&s_full[st]));
+                    if (ended == 0u) qe_mbar_arrive(cb + O_FULL + 8u * st);
                     if (++ended == (qe_u32)NLB) { QE_RT_FLUSH(0, 2); break; }
                     continue;
                 }
                 // the tile's descriptor line should be in L2 when it is published and read, NST tiles from now
                 if (!(QE_DEBUG_FLAGS & 32)) qe_prefetch_l2_keep(desc + t);
-                const qe_u32 full = qe_smem_addr(&s_full[st]);
+                const qe_u32 full = cb + O_FULL + 8u * st;
                 qe_mbar_expect_tx(full, (qe_u32)P::STAGE_TX);
-                P::issue(p, (qe_i64)t * TILE, qe_smem_addr(qe_dyn_smem + (size_t)st * P::STAGE_BYTES), full, policy);
+                P::issue(p, (qe_i64)t * TILE, dyn + st * (qe_u32)P::STAGE_BYTES, full, policy);
                 t = atomicAdd(p.ticket, 1u);                  // next ticket: its round trip overlaps the wait for a free stage
             }
         }
     } else if (warp == 1) {
         // ----------------------------------------------------------- publisher
-        for (qe_u32 it = 0;; it++) {
-            const int st = (int)(it % NST);
-            const qe_u32 par = (it / NST) & 1u;
-            qe_mbar_wait(qe_smem_addr(&s_claim[st]), par);
-            const qe_u32 t = s_tile[st];
+        qe_u32 st = 0, par = 0;
+        for (;;) {
+            qe_mbar_wait(cb + O_CLAIM + 8u * st, par);
+            const qe_u32 t = qe_lds_u32(cb + O_TILE + 4u * st);
             if (t >= p.ntiles) break;
-            qe_mbar_wait(qe_smem_addr(&s_eval[st]), par);
-            qe_u32 c = lane < (qe_u32)NCW ? s_cnt[st][lane] : 0u;
+            qe_mbar_wait(cb + O_EVAL + 8u * st, par);
+            qe_u32 c = lane < (qe_u32)NCW ? qe_lds_u32(cb + O_CNT + 4u * ((qe_u32)NCW * st + lane)) : 0u;
             c = __reduce_add_sync(QE_FULL_MASK, c);
             if (lane == 0) {
                 qe_st_relaxed_u32(desc + t, c + 1u);
-                qe_mbar_arrive(qe_smem_addr(&s_empty[st]));
+                qe_mbar_arrive(cb + O_EMPTY + 8u * st);
             }
+            QE_RING_NEXT(st, par, 1u);
         }
     } else if (warp < 2u + (qe_u32)NLB) {
         // ----------------------------------------------------------- look-back
         // NLB warps take this CTA's tiles round robin.  A prefix costs one L2 round trip after the
         // tile's count is visible grid-wide (~1.4 us under streaming load, measured), a 16-32 KB tile
         // streams in 0.4-0.7 us, so several must be in flight; the gap sums are independent, only the
-        // final add chains through shared memory (s_incl of the previous tile).
+        // final add chains through shared memory (the inclusive count of the previous tile).
         qe_u64 rt_acc[16] = {};
         QE_RT_BEGIN();
         const qe_u64 base0 = p.out_base ? *p.out_base : 0ull;  // append mode: rows of earlier batches
         for (qe_u32 it = warp - 2u;; it += (qe_u32)NLB) {
-            const int st = (int)(it % NST);
+            const qe_u32 st = it % NST;
             const qe_u32 par = (it / NST) & 1u;
-            qe_mbar_wait(qe_smem_addr(&s_claim[st]), par);
-            const qe_u32 t = s_tile[st];
+            qe_mbar_wait(cb + O_CLAIM + 8u * st, par);
+            const qe_u32 t = qe_lds_u32(cb + O_TILE + 4u * st);
             if (t >= p.ntiles) { if (warp == 2) { QE_RT_FLUSH(3, 8); QE_RT_FLUSH(14, 14); } break; }
-            const qe_u32 lo = s_lo[st];
+            const qe_u32 lo = qe_lds_u32(cb + O_LO + 4u * st);
             QE_RT_RESET();
             // Wait for this CTA's own count first: the grid moves in step, so by then the tiles of the
             // other CTAs in the gap are counted (or about to be) and the descriptors are read once
             // instead of being polled for a whole tile time (148 warps polling five cache lines slowed
             // the very stores they were waiting for: measured 5-12 us per prefix).
-            qe_mbar_wait(qe_smem_addr(&s_eval[st]), par);
+            qe_mbar_wait(cb + O_EVAL + 8u * st, par);
             QE_RT_ADD(3);
             rt_acc[8] += t - lo;
-            const qe_u32 mine = lane < (qe_u32)NCW ? s_cnt[st][lane] : 0u;
+            const qe_u32 mine = lane < (qe_u32)NCW ? qe_lds_u32(cb + O_CNT + 4u * ((qe_u32)NCW * st + lane)) : 0u;
             const qe_u32 c = __reduce_add_sync(QE_FULL_MASK, mine);
             // the gap [lo, t): tiles of other CTAs claimed between this CTA's previous tile and this one
             qe_u32 gap = 0;
@@ -1352,8 +1430,8 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
             qe_u64 before = base0;                            // kept rows up to and including this CTA's previous tile
             if (it > 0) {
                 const qe_u32 jt = it - 1u;
-                qe_mbar_wait(qe_smem_addr(&s_pref[jt % NST]), (jt / NST) & 1u);
-                before = s_incl[jt % NST];
+                qe_mbar_wait(cb + O_PREF + 8u * (jt % NST), (jt / NST) & 1u);
+                before = qe_lds_u64(cb + O_INCL + 8u * (jt % NST));
             }
             QE_RT_ADD(7);
             const qe_u64 excl = before + gap;
@@ -1364,35 +1442,36 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                 const qe_u32 v = __shfl_up_sync(QE_FULL_MASK, wofs, o);
                 if (lane >= (qe_u32)o) wofs += v;
             }
-            if (lane < (qe_u32)NCW) s_wbase[st][lane] = excl + (wofs - mine);
+            if (lane < (qe_u32)NCW) qe_sts_u64(cb + O_WBASE + 8u * ((qe_u32)NCW * st + lane), excl + (wofs - mine));
             __syncwarp();
             if (lane == 0) {
-                s_fits[st] = excl + c <= (qe_u64)p.out_capacity ? 1u : 0u;
-                s_incl[st] = excl + c;
-                qe_mbar_arrive(qe_smem_addr(&s_pref[st]));
-                qe_mbar_arrive(qe_smem_addr(&s_empty[st]));
+                qe_sts_u32(cb + O_FITS + 4u * st, excl + c <= (qe_u64)p.out_capacity ? 1u : 0u);
+                qe_sts_u64(cb + O_INCL + 8u * st, excl + c);
+                qe_mbar_arrive(cb + O_PREF + 8u * st);
+                qe_mbar_arrive(cb + O_EMPTY + 8u * st);
                 if (t == p.ntiles - 1u) *p.out_count = excl + c;
             }
         }
     } else {
         // ----------------------------------------------------------- consumers
-        const int cw = (int)warp - (2 + NLB);
-        const int wrow0 = cw * WROWS;                         // this warp's slice of every tile
+        const qe_u32 cw = warp - (2u + (qe_u32)NLB);
+        const int wrow0 = (int)cw * WROWS;                    // this warp's slice of every tile
         int n_valid = 0x7fffffff;                             // iterations that carry a tile (known once the end marker is seen)
+        qe_u32 st_a = 0, par_a = 0;                           // stage / parity of phase A's tile (iteration it)
+        qe_u32 st_c = 0, par_c = 0;                           // ... of phase C's tile (iteration it - DEFER)
         qe_u64 rt_acc[16] = {};
         QE_RT_BEGIN();
         for (int it = 0;; it++) {
             if (it < n_valid) {
                 // ---- phase A: evaluate the filter, leave keep masks and counts in shared memory
-                const int st = it % NST;
                 QE_RT_RESET();
-                qe_mbar_wait(qe_smem_addr(&s_full[st]), (qe_u32)(it / NST) & 1u);
+                qe_mbar_wait(cb + O_FULL + 8u * st_a, par_a);
                 QE_RT_ADD(9);
-                const qe_u32 t = s_tile[st];
+                const qe_u32 t = qe_lds_u32(cb + O_TILE + 4u * st_a);
                 if (t >= p.ntiles) {
                     n_valid = it;
                 } else {
-                    const unsigned char *stage = qe_dyn_smem + (size_t)st * P::STAGE_BYTES;
+                    const qe_u32 stage = dyn + st_a * (qe_u32)P::STAGE_BYTES;
                     const qe_i64 row0 = (qe_i64)t * TILE;
                     qe_u32 mk[STEPS];
                     if (row0 + TILE <= p.nrows) {
@@ -1417,29 +1496,35 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
 #pragma unroll
                     for (int s = 0; s < STEPS; s++) cnt += __popc(mk[s]);
                     if (lane == 0) {
+                        const qe_u32 ma = cb + O_MASK + 4u * ((qe_u32)(TILE / 32) * st_a + cw * (qe_u32)STEPS);
+                        if (STEPS % 4 == 0) {
 #pragma unroll
-                        for (int s = 0; s < STEPS; s++) s_mask[st][cw * STEPS + s] = mk[s];
-                        s_cnt[st][cw] = cnt;
-                        qe_mbar_arrive(qe_smem_addr(&s_eval[st]));
+                            for (int s = 0; s < STEPS; s += 4) qe_sts_u32x4(ma + 4u * s, mk[s], mk[s + 1], mk[s + 2], mk[s + 3]);
+                        } else {
+#pragma unroll
+                            for (int s = 0; s < STEPS; s++) qe_sts_u32(ma + 4u * s, mk[s]);
+                        }
+                        qe_sts_u32(cb + O_CNT + 4u * ((qe_u32)NCW * st_a + cw), cnt);
+                        qe_mbar_arrive(cb + O_EVAL + 8u * st_a);
                     }
                     __syncwarp();
                     QE_RT_ADD(10);
                 }
+                QE_RING_NEXT(st_a, par_a, 1u);
             }
             const int j = it - DEFER;
             if (j >= 0 && j < n_valid) {
                 // ---- phase C: ordered scatter of tile j, whose prefix has had DEFER tile times to arrive
-                const int st = j % NST;
                 QE_RT_RESET();
-                qe_mbar_wait(qe_smem_addr(&s_pref[st]), (qe_u32)(j / NST) & 1u);   // pref follows eval
+                qe_mbar_wait(cb + O_PREF + 8u * st_c, par_c);                      // pref follows eval
                 QE_RT_ADD(11);
-                const unsigned char *stage = qe_dyn_smem + (size_t)st * P::STAGE_BYTES;
-                const qe_u32 first_row = s_row0[st] + (qe_u32)wrow0 + lane;
-                const qe_u64 wbase = s_wbase[st][cw];         // output position of this warp's first kept row
-                const qe_u32 cnt = s_cnt[st][cw];
-                const qe_u32 *mk = &s_mask[st][cw * STEPS];
+                const qe_u32 cnt = qe_lds_u32(cb + O_CNT + 4u * ((qe_u32)NCW * st_c + cw));
                 if (cnt != 0u) {
-                    if (s_fits[st]) {
+                    const qe_u32 stage = dyn + st_c * (qe_u32)P::STAGE_BYTES;
+                    const qe_u32 first_row = qe_lds_u32(cb + O_ROW0 + 4u * st_c) + (qe_u32)wrow0 + lane;
+                    const qe_u64 wbase = qe_lds_u64(cb + O_WBASE + 8u * ((qe_u32)NCW * st_c + cw));   // output position of this warp's first kept row
+                    const qe_u32 mk = cb + O_MASK + 4u * ((qe_u32)(TILE / 32) * st_c + cw * (qe_u32)STEPS);
+                    if (qe_lds_u32(cb + O_FITS + 4u * st_c)) {
                         if (p.sel) qe_ring_scatter<P, STEPS, false, true>(p, stage, wrow0, first_row, wbase, mk, cnt);
                         else qe_ring_scatter<P, STEPS, false, false>(p, stage, wrow0, first_row, wbase, mk, cnt);
                     } else {
@@ -1449,11 +1534,13 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                 }
                 __syncwarp();
                 QE_RT_ADD(12);
-                if (lane == 0) qe_mbar_arrive(qe_smem_addr(&s_empty[st]));
+                if (lane == 0) qe_mbar_arrive(cb + O_EMPTY + 8u * st_c);
+                QE_RING_NEXT(st_c, par_c, 1u);
             }
             if (n_valid != 0x7fffffff && j + 1 >= n_valid) { if (cw == 0) QE_RT_FLUSH(9, 12); break; }
         }
     }
+#undef QE_RING_NEXT
 }
 
 template <class P>
