@@ -268,8 +268,8 @@ extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
         if (value < 0 || value > kPadRows || value % 128) return fail(QE_ERR_INVALID_ARGUMENT, "tile_rows must be 0 (auto) or a multiple of 128 up to 8192");
         ctx->opt_tile_rows = value;
     } else if (k == "ncw") {
-        if (value != 0 && value != 4 && value != 8 && value != 12 && value != 16 && value != 20 && value != 24)
-            return fail(QE_ERR_INVALID_ARGUMENT, "ncw must be 0 (auto), 4, 8, 12, 16, 20 or 24");
+        if (value < 0 || value > 28 || value % 4)
+            return fail(QE_ERR_INVALID_ARGUMENT, "ncw must be 0 (auto) or a multiple of 4 up to 28");
         ctx->opt_ncw = value;
     } else if (k == "defer") {
         if (value < 0 || value > 30) return fail(QE_ERR_INVALID_ARGUMENT, "defer must be in [0, 30] (0 = auto)");
@@ -636,7 +636,10 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
     // Filter kernel, default: persistent warp-specialised CTA around a ring of bulk-copy stages.
     s.ring = mode == qe::KM_FILTER && (ctx->opt_staging == -1 || ctx->opt_staging == 2);
     if (s.ring) {
-        s.ncw = ctx->opt_ncw ? (int)ctx->opt_ncw : 16;
+        // consumer warps: 16, or 20 for a single 8-byte column -- at low selectivity that kernel is bound by
+        // issue slots and latency, not by HBM (1 %: 1.45 ms with 16 warps, 1.31 with 20 or 24; 99 %: 2.98 / 3.00 /
+        // 3.02); 40-byte rows lose with more warps (6.9 ms with 16, 7.7 with 24): profiles/r01_sweep_06_*.jsonl
+        s.ncw = ctx->opt_ncw ? (int)ctx->opt_ncw : (row_bytes <= 8 ? 20 : 16);
         const size_t quantum = (size_t)std::max(128, 32 * s.ncw);       // rows: whole warp steps, 16-byte bitmap runs
         const size_t stage_target = (size_t)(ctx->opt_stage_kb ? ctx->opt_stage_kb : 32) << 10;
         // One look-back per tile costs ~1500 cycles whatever the tile holds, so a tile must carry >= ~32 KB for
