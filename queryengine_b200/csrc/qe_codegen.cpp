@@ -296,7 +296,7 @@ StageLayout stage_layout(const BoundPipeline &bp, const TileShape &shape)
 
 size_t staged_smem_bytes(const BoundPipeline &bp, const TileShape &shape)
 {
-    if (!shape.staged && !shape.ring) return 0;
+    if (!shape.staged && !shape.ring && !shape.greg) return 0;
     return (size_t)stage_layout(bp, shape).stride * (size_t)shape.nstages;
 }
 
@@ -369,6 +369,19 @@ GroupPlan plan_groupby(const BoundPipeline &bp, int threads)
         if (g.shared_smem() <= (208u << 10)) break;
     }
     if (g.slmax < 64) { g.slmax = 0; g.scslots = 64; }
+    // register variant: per group two 32-bit registers (first row, rows) + two per further word; ~96 registers
+    // of accumulators leave room for the row and the expression temporaries under the 152 a 416-thread CTA gets
+    const int reg_per_group = 2 + 2 * (g.nwords - 1);
+    g.rmax = std::min(16, 96 / reg_per_group);
+    // ... and it pays only where the row is wide enough for the issue slots: a row costs about
+    // 100 + RMAX * (4 + words) instructions (every group's words are touched, predicated), and at the HBM rate an
+    // SM has ~5.7 issue slots per row byte (measured: Q1 shape, 48-byte rows, 6 words, RMAX 8: 5.8 ms against 7.3
+    // for the private variant; SUM, COUNT over 16-byte rows: 8.1 ms against 2.0)
+    int row_bytes = 0;
+    for (const ColumnInfo &c : bp.slot_info) row_bytes += c.type == 2 ? 1 : ((c.type == 4 || c.type == 0) ? 4 : 8);
+    const int fit = (5 * row_bytes - 100) / (4 + g.nwords);
+    g.rmax = std::min(g.rmax, fit);
+    if (g.rmax < 4) g.rmax = 0;
     return g;
 }
 
@@ -384,7 +397,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     // bit columns of the outputs (validity bitmaps and BOOLEAN values)
     struct BitCol { std::string ptr, bit; };
     std::vector<BitCol> bitcols;
-    const bool is_group = mode == KM_GROUPBY_PRIVATE || mode == KM_GROUPBY_ATOMIC || mode == KM_GROUPBY_SHARED;
+    const bool is_group = mode == KM_GROUPBY_PRIVATE || mode == KM_GROUPBY_ATOMIC || mode == KM_GROUPBY_SHARED || mode == KM_GROUPBY_REG;
     if (mode != KM_AGG && !is_group) {
         for (int k = 0; k < nproj; k++) {
             if (bp.outs[k].has_validity) {
@@ -448,11 +461,12 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     }
     s += "    }\n";
 
-    if (mode == KM_FILTER && (shape.staged || shape.ring)) {
+    if ((mode == KM_FILTER && (shape.staged || shape.ring)) || (mode == KM_GROUPBY_REG && shape.greg)) {
+        const bool ringlike = shape.ring || shape.greg;
         const StageLayout L = stage_layout(bp, shape);
         snprintf(b, sizeof b, "    static constexpr int NSTAGES = %d, STAGE_BYTES = %d, STAGE_TX = %d;\n", shape.nstages, L.stride, L.tx);
         s += b;
-        if (shape.ring) {
+        if (ringlike) {
             snprintf(b, sizeof b, "    static constexpr int TILE_ROWS = %d, NCW = %d, NLB = %d, DEFER = %d, LOADS = %d;\n", shape.tile_rows, shape.ncw,
                      shape.nlb, shape.defer, shape.loads);
             s += b;
@@ -471,9 +485,9 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
             s += "    }\n";
         }
         // one thread: a bulk copy per column run of the tile, all signalling the stage's mbarrier
-        const char *bulk = shape.ring ? "qe_bulk_g2s_stream" : "qe_bulk_g2s";
-        const char *pol = shape.ring ? ", policy" : "";
-        if (shape.ring)
+        const char *bulk = ringlike ? "qe_bulk_g2s_stream" : "qe_bulk_g2s";
+        const char *pol = ringlike ? ", policy" : "";
+        if (ringlike)
             s += "    static __device__ __forceinline__ void issue(const QeParams &p, qe_i64 row0, qe_u32 stage, qe_u32 mbar, qe_u64 policy) {\n";
         else
         s += "    static __device__ __forceinline__ void issue(const QeParams &p, qe_i64 row0, qe_u32 stage, qe_u32 mbar) {\n";
@@ -640,6 +654,12 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         s += b;
         snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d;\n", gp.slmax > 0 ? gp.slmax : 64, gp.scslots);
         s += b;
+        {
+            int rcs = 64;
+            while (rcs < 32 * gp.rmax) rcs *= 2;
+            snprintf(b, sizeof b, "    static constexpr int RMAX = %d, RCSLOTS = %d;\n", gp.rmax > 0 ? gp.rmax : 1, rcs);
+            s += b;
+        }
         s += "    static __device__ __forceinline__ void key_pack(const Out &o, qe_u64 (&k)[NKEYS], qe_u32 &nulls) {\n        nulls = 0u;\n";
         if (gp.nkeys == 0) s += "        k[0] = 0ull;\n";
         for (int i = 0; i < gp.nkeys; i++) {
@@ -674,14 +694,22 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
             else snprintf(v, sizeof v, "0.0");
             return std::string(v);
         };
-        for (int variant = 0; variant < 2; variant++) {
-            const bool atomic = variant == 1;
+        for (int variant = 0; variant < 4; variant++) {
+            // 0 private (shared-memory words), 1 global atomics, 2 registers with selects, 3 registers with DFMA by a
+            // 0.0 / 1.0 mask (finite inputs only: inf * 0.0 would poison the other groups; all_finite() guards it)
+            const bool atomic = variant == 1, regs = variant >= 2, rfma = variant == 3;
+            // register variant: called for every g in [0, RMAX), branch-free -- every update is a predicated
+            // instruction or a select on (l == g).  (As `if (l == g) update` the compiler built a divergent switch:
+            // every group met by the warp ran as its own branch, ~140 cycles per group and warp step.)
             s += atomic ? "    static __device__ __forceinline__ void acc_atomic(qe_u64 *a, const Out &o, qe_u64 row) {\n"
+               : rfma ? "    static __device__ __forceinline__ void acc_regs_fma(qe_u32 &first, qe_u32 &rows, qe_u64 (&a)[NWORDS], const Out &o, qe_u32 row, int l, int g) {\n"
+               : regs ? "    static __device__ __forceinline__ void acc_regs(qe_u32 &first, qe_u32 &rows, qe_u64 (&a)[NWORDS], const Out &o, qe_u32 row, int l, int g) {\n"
                         : "    static __device__ __forceinline__ void acc_private(qe_u64 *a, const Out &o, qe_u64 row) {\n"
                           "        constexpr size_t WS = (size_t)LMAX * GTHREADS;\n";
             auto at = [&](int w) {
                 char a[48];
                 if (atomic) snprintf(a, sizeof a, "a + %d", w);
+                else if (regs) snprintf(a, sizeof a, "a[%d]", w);
                 else snprintf(a, sizeof a, "a[%d * WS]", w);
                 return std::string(a);
             };
@@ -690,6 +718,11 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                 // of a group nothing is smaller any more -- look before the atomic.
                 s += "        if ((qe_u32)row < ((volatile qe_u32 *)a)[1]) atomicMin(((unsigned int *)a) + 1, (unsigned int)row);\n";
                 s += "        atomicAdd((unsigned int *)a, 1u);\n";
+            } else if (regs) {
+                // a thread meets its rows in ascending order, but min() keeps this independent of that
+                s += "        const bool m = l == g;\n"
+                     "        first = min(first, m ? row : 0xffffffffu);\n        rows += m ? 1u : 0u;\n";
+                if (rfma) s += "        const double mg = m ? 1.0 : 0.0;\n";
             } else {
                 s += "        { const qe_u64 w0 = a[0]; const qe_u64 f = w0 >> 32;\n"
                      "          a[0] = ((row < f ? row : f) << 32) | ((w0 + 1ull) & 0xffffffffull); }\n";
@@ -703,6 +736,29 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                 if (bp.proj[k].nullable) { snprintf(b, sizeof b, "if (o.n%d) ", k); guard = b; }
                 std::string stmts;
                 const std::string v = agg_val((int)j);
+                if (regs) {
+                    // l of this aggregate: -1 when its input is null (nulls are skipped, Accumulators.kt)
+                    std::string lj = "l";
+                    if (bp.proj[k].nullable) { snprintf(b, sizeof b, "(o.n%d ? l : -1)", k); lj = b; }
+                    if (vw >= 0 && !done[(size_t)vw]) {
+                        done[(size_t)vw] = true;
+                        if ((fn == 2 || fn == 4) && rfma) {
+                            std::string mj = "mg";
+                            if (bp.proj[k].nullable) { snprintf(b, sizeof b, "((o.n%d && m) ? 1.0 : 0.0)", k); mj = b; }
+                            stmts += at(vw) + " = (qe_u64)qe_f64_bits(fma(" + v + ", " + mj + ", qe_bits_f64((qe_i64)" + at(vw) + "))); ";
+                        } else {
+                            const char *f = (fn == 2 || fn == 4) ? "qe_add" : fn == 0 ? "qe_math_min" : "qe_math_max";
+                            stmts += at(vw) + " = (" + lj + " == g) ? (qe_u64)qe_f64_bits(" + f +
+                                     "(qe_bits_f64((qe_i64)" + at(vw) + "), " + v + ")) : " + at(vw) + "; ";
+                        }
+                    }
+                    if (cw >= 0 && !done[(size_t)cw]) {
+                        done[(size_t)cw] = true;
+                        stmts += at(cw) + " += (" + lj + " == g) ? 1ull : 0ull; ";
+                    }
+                    if (!stmts.empty()) s += "        " + stmts + "\n";
+                    continue;
+                }
                 if (vw >= 0 && !done[(size_t)vw]) {
                     done[(size_t)vw] = true;
                     if (atomic) {
@@ -724,16 +780,30 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
             }
             s += "    }\n";
         }
+        // every SUM / AVG input of the row is finite (whether null or not: a null's value bits are arbitrary)
+        s += "    static __device__ __forceinline__ bool all_finite(const Out &o) {\n        bool f = true;\n";
+        {
+            std::vector<bool> seen((size_t)gp.nwords, false);
+            for (size_t j = 0; j < bp.agg_fns.size(); j++) {
+                const int fn = bp.agg_fns[j], vw = gp.val_word[j];
+                if ((fn != 2 && fn != 4) || vw < 0 || seen[(size_t)vw]) continue;
+                seen[(size_t)vw] = true;
+                s += "        f = f && (((qe_u32)(qe_f64_bits(" + agg_val((int)j) + ") >> 32) & 0x7ff00000u) != 0x7ff00000u);\n";
+            }
+        }
+        s += "        return f;\n    }\n";
     }
     s += "};\n\n";
     const char *body = mode == KM_FILTER ? (shape.ring ? "qe_filter_ring_body" : shape.staged ? "qe_filter_staged_body" : shape.pipelined ? "qe_filter_pipelined_body" : "qe_filter_body")
                      : mode == KM_PROJECT ? "qe_project_body" : mode == KM_AGG ? "qe_agg_body"
                      : mode == KM_GROUPBY_PRIVATE ? "qe_groupby_private_body"
+                     : mode == KM_GROUPBY_REG ? "qe_groupby_reg_body"
                      : mode == KM_GROUPBY_SHARED ? "qe_groupby_shared_body" : "qe_groupby_atomic_body";
     snprintf(b, sizeof b,
              "extern \"C\" __global__ void __launch_bounds__(%d, %d) %s"
              "(const __grid_constant__ QeParams p)\n{\n    %s<P>(p);\n}\n",
-             mode == KM_FILTER ? shape.block_threads() : (mode == KM_GROUPBY_PRIVATE || mode == KM_GROUPBY_SHARED) ? shape.gthreads : 256, shape.min_blocks,
+             (mode == KM_FILTER || mode == KM_GROUPBY_REG) ? shape.block_threads()
+                 : (mode == KM_GROUPBY_PRIVATE || mode == KM_GROUPBY_SHARED) ? shape.gthreads : 256, shape.min_blocks,
              jit_entry_name(mode, shape), body);
     s += b;
     return s;
@@ -748,6 +818,7 @@ const char *jit_entry_name(KernelMode mode, const TileShape &shape)
     case KM_AGG: return "qe_agg_kernel";
     case KM_GROUPBY_PRIVATE: return "qe_groupby_private_kernel";
     case KM_GROUPBY_SHARED: return "qe_groupby_shared_kernel";
+    case KM_GROUPBY_REG: return "qe_groupby_reg_kernel";
     default: return "qe_groupby_atomic_kernel";
     }
 }

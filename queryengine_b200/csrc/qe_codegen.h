@@ -17,7 +17,8 @@
 
 namespace qe {
 
-enum KernelMode { KM_FILTER = 0, KM_PROJECT = 1, KM_AGG = 2, KM_GROUPBY_PRIVATE = 3, KM_GROUPBY_ATOMIC = 4, KM_GROUPBY_SHARED = 5 };
+enum KernelMode { KM_FILTER = 0, KM_PROJECT = 1, KM_AGG = 2, KM_GROUPBY_PRIVATE = 3, KM_GROUPBY_ATOMIC = 4, KM_GROUPBY_SHARED = 5,
+                  KM_GROUPBY_REG = 6 };
 
 // Accumulator words of one group (qe_device.cuh, "group-by"): word 0 = first row << 32 | rows of the group,
 // then per aggregate a value word (SUM / AVG / MIN / MAX) and, when its input can be null, its own count of
@@ -32,6 +33,7 @@ struct GroupPlan {
     size_t private_smem() const { return (size_t)nwords * (size_t)lmax * (size_t)threads * 8u; }
     int slmax = 0, scslots = 0;            // shared variant: groups per CTA (one copy of the words), key-cache slots
     size_t shared_smem() const;            // accumulators + key cache, all dynamic
+    int rmax = 0;                          // register variant: groups per CTA whose accumulators every thread keeps in registers (0: not applicable)
 };
 GroupPlan plan_groupby(const BoundPipeline &bp, int threads = 256);
 
@@ -51,9 +53,12 @@ struct TileShape {
     int defer = 3;          // tiles between a tile's evaluation (phase A) and its scatter (phase C)
     int loads = 0;          // bulk-copy tiles in flight at most (0 = as many as there are free stages)
     int gthreads = 256;     // group-by, private variant: threads per CTA (256 or 512)
+    // group-by, register variant (qe_groupby_reg_body): the same ring of bulk-copy stages (tile_rows, ncw, nstages),
+    // one producer warp + ncw consumer warps, no look-back
+    bool greg = false;
 
-    int rows_per_tile() const { return ring ? tile_rows : (gthreads / 32) * steps * 32 * vec; }
-    int block_threads() const { return ring ? 32 * (2 + nlb + ncw) : 256; }
+    int rows_per_tile() const { return (ring || greg) ? tile_rows : (gthreads / 32) * steps * 32 * vec; }
+    int block_threads() const { return greg ? 32 * (1 + ncw) : ring ? 32 * (2 + nlb + ncw) : 256; }
 };
 
 // bytes of dynamic shared memory the staged filter kernel needs (0 when not staged)

@@ -1896,6 +1896,170 @@ __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
     if ((int)tid < nlocal) ps[1 + tid] = gc.slot[tid];
 }
 
+// Register variant: at most RMAX groups (2-16, by accumulator width), every consumer THREAD keeps the words of all
+// of them in registers and a row updates them with predicated instructions (`if (local == g) ...`, unrolled over
+// g): no shared-memory read-modify-write chain per row, which is what bounds the private variant (ncu: short
+// scoreboard 5.0 stalled warps per issue, LSU wavefronts 59 % of peak, 47 % of DRAM peak on the Q1 shape).  With
+// the accumulators out of shared memory, shared memory holds a ring of bulk-copy stages like the filter kernel's:
+// one producer warp (cp.async.bulk per column run, static tile -> CTA assignment so that the summation order
+// depends on the grid only), NCW consumer warps, full / empty mbarriers, no look-back (nothing is ordered).
+// Ends like the private variant: registers to shared memory as [word][group][thread], fixed-order reduce, one
+// partial per CTA for qe_groupby_merge_kernel.  More than RMAX groups -> overflow flag, the caller moves on to the
+// private variant; the flag is raised as soon as it is seen and every producer stops issuing tiles.
+template <class P>
+__device__ __forceinline__ void qe_groupby_reg_body(const QeParams &p)
+{
+    constexpr int NST = P::NSTAGES, NCW = P::NCW, TILE = P::TILE_ROWS, NKEYS = P::NKEYS, NWORDS = P::NWORDS, RMAX = P::RMAX, CS = P::RCSLOTS;
+    constexpr int WROWS = TILE / NCW, STEPS = WROWS / 32, GT = NCW * 32;
+    static_assert(WROWS % 32 == 0 && NCW >= 1 && NCW <= 31 && NST >= 2, "register group-by shape");
+    static_assert((size_t)NWORDS * RMAX * GT * 8 <= (size_t)NST * P::STAGE_BYTES, "the final reduce reuses the stages");
+
+    extern __shared__ __align__(128) unsigned char qe_dyn_smem[];
+    __shared__ __align__(8) qe_u64 s_bar[2 * NST];            // full[NST], empty[NST]
+    __shared__ qe_u32 s_tile[NST];
+    __shared__ QeGroupCache<NKEYS, CS, RMAX> gc;
+    const qe_u32 warp = qe_warp(), lane = qe_lane(), tid = threadIdx.x;
+    const qe_u32 bar = qe_opaque_u32(qe_smem_addr(s_bar));
+    const qe_u32 dyn = qe_opaque_u32(qe_smem_addr(qe_dyn_smem));
+    const qe_u32 tl = qe_opaque_u32(qe_smem_addr(s_tile));
+
+    for (int i = (int)tid; i < CS; i += (int)blockDim.x) gc.state[i] = 0u;
+    if (tid == 0) {
+        gc.nlocal = 0u;
+        gc.over = 0u;
+#pragma unroll
+        for (int st = 0; st < NST; st++) {
+            qe_mbar_init(bar + 8u * st, 1);
+            qe_mbar_init(bar + 8u * (NST + st), NCW);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    qe_u32 rfirst[RMAX], rrows[RMAX];
+    qe_u64 racc[RMAX][NWORDS];
+#pragma unroll
+    for (int g = 0; g < RMAX; g++) {
+        rfirst[g] = 0xffffffffu;
+        rrows[g] = 0u;
+#pragma unroll
+        for (int w = 0; w < NWORDS; w++) racc[g][w] = P::word_init(w);
+    }
+
+    if (warp == 0) {
+        // ------------------------------------------------------------ producer
+        if (lane == 0) {
+            const qe_u64 policy = qe_policy_evict_first();
+            qe_u32 st = 0, par = 0;
+            for (qe_u32 it = 0;; it++) {
+                if (it >= (qe_u32)NST) qe_mbar_wait(bar + 8u * (NST + st), par ^ 1u);
+                qe_u32 t = blockIdx.x + it * gridDim.x;
+                if (t < p.ntiles && (qe_ld_relaxed_u32(p.g_ctl + 1) & 1u)) t = p.ntiles;   // some CTA overflowed: the run is discarded
+                qe_sts_u32(tl + 4u * st, t);
+                const qe_u32 full = bar + 8u * st;
+                if (t >= p.ntiles) {                          // end marker
+                    qe_mbar_arrive(full);
+                    break;
+                }
+                qe_mbar_expect_tx(full, (qe_u32)P::STAGE_TX);
+                P::issue(p, (qe_i64)t * TILE, dyn + st * (qe_u32)P::STAGE_BYTES, full, policy);
+                if (++st == (qe_u32)NST) { st = 0; par ^= 1u; }
+            }
+        }
+    } else {
+        // ----------------------------------------------------------- consumers
+        const qe_u32 cw = warp - 1u;
+        const int wrow0 = (int)cw * WROWS;
+        qe_u32 st = 0, par = 0;
+        bool flagged = false;
+        for (;;) {
+            qe_mbar_wait(bar + 8u * st, par);
+            const qe_u32 t = qe_lds_u32(tl + 4u * st);
+            if (t >= p.ntiles) break;
+            const qe_u32 stage = dyn + st * (qe_u32)P::STAGE_BYTES;
+            const volatile QeGroupCache<NKEYS, CS, RMAX> &vc = gc;
+            if (!vc.over) {
+                const qe_i64 live = p.nrows - (qe_i64)t * TILE - wrow0 - (qe_i64)lane;   // rows of this lane's column that exist
+#pragma unroll
+                for (int s = 0; s < STEPS; s++) {
+                    typename P::Row row;
+                    typename P::Out o;
+                    P::load_row(stage, wrow0, s * 32, row);
+                    const bool keep = P::eval(p, row, o) && (qe_i64)(s * 32) < live;
+                    int l = -1;
+                    if (keep) {
+                        qe_u64 k[NKEYS];
+                        qe_u32 nulls;
+                        P::key_pack(o, k, nulls);
+                        const qe_u32 h = qe_group_hash<NKEYS>(k, nulls);
+                        const qe_u32 c = h & (qe_u32)(CS - 1);
+                        // first probe, straight-line: volatile keeps the reads in this order (state first)
+                        bool hit = vc.state[c] == 2u;
+                        hit = hit && vc.nulls[c] == nulls;
+#pragma unroll
+                        for (int i = 0; i < NKEYS; i++) hit = hit && vc.keys[c][i] == k[i];
+                        l = vc.local[c];
+                        if (!hit) l = qe_group_local_slow<NKEYS, CS, RMAX>(p, &gc, k, nulls, h);
+                    }
+                    const qe_u32 rowid = p.sel_base + t * (qe_u32)TILE + (qe_u32)(wrow0 + s * 32) + lane;
+                    // SUM words: one DFMA by a 0.0 / 1.0 mask per group and word (bit-identical to the add: v * 1.0
+                    // is v, v * 0.0 is a zero of either sign and leaves a sum that started at +0.0 unchanged) --
+                    // unless an input is Inf / NaN, whose product with 0.0 would poison the other groups: selects then
+                    if (P::all_finite(o)) {
+#pragma unroll
+                        for (int g = 0; g < RMAX; g++) P::acc_regs_fma(rfirst[g], rrows[g], racc[g], o, rowid, l, g);
+                    } else {
+#pragma unroll
+                        for (int g = 0; g < RMAX; g++) P::acc_regs(rfirst[g], rrows[g], racc[g], o, rowid, l, g);
+                    }
+                }
+            } else if (!flagged && cw == 0 && lane == 0) {
+                atomicOr(p.g_ctl + 1, 1u);                    // tell every producer now
+                flagged = true;
+            }
+            __syncwarp();
+            if (lane == 0) qe_mbar_arrive(bar + 8u * (NST + st));
+            if (++st == (qe_u32)NST) { st = 0; par ^= 1u; }
+        }
+    }
+    __syncthreads();                                          // every stage has been read: the stages become the reduce buffer
+    qe_u64 *s_acc = (qe_u64 *)qe_dyn_smem;                    // [NWORDS][RMAX][GT]
+    if (warp > 0) {
+        const qe_u32 ct = tid - 32u;
+#pragma unroll
+        for (int g = 0; g < RMAX; g++) {
+            s_acc[((size_t)0 * RMAX + g) * GT + ct] = ((qe_u64)rfirst[g] << 32) | (qe_u64)rrows[g];
+#pragma unroll
+            for (int w = 1; w < NWORDS; w++) s_acc[((size_t)w * RMAX + g) * GT + ct] = racc[g][w];
+        }
+    }
+    __syncthreads();
+    // ---- fixed-order reduce of the GT thread copies: (group, word) pairs round-robin over the consumer warps
+    const int nlocal = (int)(gc.nlocal < (qe_u32)RMAX ? gc.nlocal : (qe_u32)RMAX);
+    if (warp > 0) {
+        for (int idx = (int)warp - 1; idx < nlocal * NWORDS; idx += NCW) {
+            const int l = idx / NWORDS, w = idx - l * NWORDS;
+            const int kind = P::word_kind(w);
+            const qe_u64 *src = s_acc + ((size_t)w * RMAX + l) * GT;
+            qe_u64 v = src[lane];
+#pragma unroll
+            for (int q = 1; q < NCW; q++) v = qe_group_combine(kind, v, src[lane + 32 * q]);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const qe_u64 b = (qe_u64)__shfl_down_sync(QE_FULL_MASK, (unsigned long long)v, o);
+                v = qe_group_combine(kind, v, b);
+            }
+            if (lane == 0) p.g_part[((size_t)blockIdx.x * RMAX + l) * NWORDS + w] = v;
+        }
+    }
+    qe_u32 *ps = p.g_part_slot + (size_t)blockIdx.x * (1 + RMAX);
+    if (tid == 0) {
+        ps[0] = (qe_u32)nlocal;
+        if (gc.over) atomicOr(p.g_ctl + 1, 1u);
+    }
+    if ((int)tid < nlocal) ps[1 + tid] = gc.slot[tid];
+}
+
 // Middle variant: more groups than the private copies hold, few enough for ONE copy of the accumulators per CTA
 // in shared memory (SLMAX groups, hundreds to thousands).  Rows update it with shared-memory atomics (native
 // 32-bit for the first-row / row-count word and the counts, compare-and-swap loops for the f64 words), which

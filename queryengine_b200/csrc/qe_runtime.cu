@@ -134,7 +134,7 @@ struct qe_ctx {
     Pool pool;
     std::unordered_map<std::string, JitEntry> jit_cache;
     // options
-    int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = -1, opt_stages = 0, opt_debug_flags = 0, opt_pipeline = 1;
+    int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = -1, opt_stages = 0, opt_debug_flags = 0, opt_pipeline = 1, opt_groupby_registers = 1;
     int64_t opt_min_blocks = 0;
     int64_t opt_nlb = 0, opt_loads = 0, opt_tile_rows = 0, opt_ncw = 0, opt_defer = 0, opt_stage_kb = 0;
     int64_t launches = 0;
@@ -264,12 +264,14 @@ extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
         ctx->opt_min_blocks = value;
     } else if (k == "pipeline") {
         ctx->opt_pipeline = value != 0;
+    } else if (k == "groupby_registers") {
+        ctx->opt_groupby_registers = value != 0;             // 0: group-by starts with the private (shared-memory) variant
     } else if (k == "tile_rows") {
         if (value < 0 || value > kPadRows || value % 128) return fail(QE_ERR_INVALID_ARGUMENT, "tile_rows must be 0 (auto) or a multiple of 128 up to 8192");
         ctx->opt_tile_rows = value;
     } else if (k == "ncw") {
-        if (value < 0 || value > 28 || value % 4)
-            return fail(QE_ERR_INVALID_ARGUMENT, "ncw must be 0 (auto) or a multiple of 4 up to 28");
+        if (value < 0 || value > 28 || (value % 4 && value != 11))
+            return fail(QE_ERR_INVALID_ARGUMENT, "ncw must be 0 (auto), a multiple of 4 up to 28, or 11 (group-by register variant)");
         ctx->opt_ncw = value;
     } else if (k == "defer") {
         if (value < 0 || value > 30) return fail(QE_ERR_INVALID_ARGUMENT, "defer must be in [0, 30] (0 = auto)");
@@ -523,7 +525,7 @@ struct qe_result {
     DevBuf g_state, g_keys, g_nulls, g_acc, g_ctl, g_part, g_part_slot, g_records;
     std::vector<std::vector<uint8_t>> h_values, h_valid;    // per output column: values in the column's layout, Arrow bitmap
     int64_t h_rows = 0;
-    int g_nkeys = 0, g_variant = 0, g_threads = 0;          // variant: 0 private accumulators, 1 global atomics, 2 CTA-shared
+    int g_nkeys = 0, g_variant = 0, g_threads = 0;          // variant: 0 private accumulators, 1 global atomics, 2 CTA-shared, 3 registers
     std::string g_overflowed;                               // signature of the group-by whose private variant overflowed here
     int g_level = 0;                                        // ... and the variant to start with next time (0: private 512 threads,
                                                             // 1: private 256, 2: CTA-shared accumulators, 3: global atomics)
@@ -533,7 +535,8 @@ struct qe_result {
 
 static bool is_groupby(const qe_result *r)
 {
-    return r->mode == qe::KM_GROUPBY_PRIVATE || r->mode == qe::KM_GROUPBY_ATOMIC || r->mode == qe::KM_GROUPBY_SHARED;
+    return r->mode == qe::KM_GROUPBY_PRIVATE || r->mode == qe::KM_GROUPBY_ATOMIC || r->mode == qe::KM_GROUPBY_SHARED ||
+           r->mode == qe::KM_GROUPBY_REG;
 }
 
 // Fold the last run's kernel time into the totals (the run must have completed).
@@ -663,6 +666,29 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         s.nlb = std::min(ctx->opt_nlb ? (int)ctx->opt_nlb : 1, s.nstages);   // the end markers need a stage each
         if (n * (stage + meta) > (224u << 10) || s.defer < 1) s.ring = false;   // a single tile does not fit: register-sourced kernel
     }
+    // Group-by, register variant: the same ring of stages, one producer warp + ncw consumer warps, no look-back.
+    if (mode == qe::KM_GROUPBY_REG) {
+        s.greg = true;
+        // Registers are allocated per four warps: 1 + 11 warps get 168 registers per thread, 13-16 warps 128 (which
+        // spills the accumulators).  Eleven consumer warps need tiles of 1408 rows (whole warp steps and 16-byte
+        // runs of every column and bitmap); when three such stages do not fit, eight warps and 256-row quanta.
+        s.ncw = ctx->opt_ncw ? (int)ctx->opt_ncw : 11;
+        if (s.ncw == 11 && 3 * 1408 * row_bytes > (200u << 10)) s.ncw = 8;
+        const size_t quantum = s.ncw == 11 ? 1408 : (size_t)std::max(128, 32 * s.ncw);
+        const size_t stage_target = (size_t)(ctx->opt_stage_kb ? ctx->opt_stage_kb : 32) << 10;
+        size_t rows = stage_target / row_bytes / quantum * quantum;
+        if (rows * row_bytes < stage_target && (rows + quantum) * row_bytes <= (44u << 10)) rows += quantum;
+        if (ctx->opt_tile_rows) rows = (size_t)ctx->opt_tile_rows;
+        rows = std::min<size_t>(std::max(rows, quantum), (size_t)kPadRows / quantum * quantum);
+        if (rows % quantum) rows = (rows + quantum - 1) / quantum * quantum;
+        s.tile_rows = (int)rows;
+        s.nstages = 1;
+        const size_t stage = qe::staged_smem_bytes(bp, s);
+        size_t n = ctx->opt_stages ? (size_t)ctx->opt_stages : 8;
+        while (n > 2 && n * stage > (208u << 10)) n--;         // the key cache and the barriers are static shared memory
+        s.nstages = (int)n;
+        if (n * stage > (208u << 10)) s.greg = false;
+    }
     return s;
 }
 
@@ -705,7 +731,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     char suffix[128];
     snprintf(suffix, sizeof suffix, "|M%d|B%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d.%d|G%d", (int)mode, shape.min_blocks, shape.steps, shape.vec, shape.staged ? 1 : 0,
              shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0, shape.ring ? 1 : 0, shape.tile_rows, shape.ncw,
-             shape.defer, shape.loads, shape.nlb, shape.gthreads);
+             shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 : 0));
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) { *out = &it->second; return QE_OK; }
@@ -721,7 +747,8 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     JitEntry e;
     e.shape = shape;
     std::string err;
-    if (!qe::jit_load(cubin, qe::jit_entry_name(mode, shape), dyn_smem ? dyn_smem : qe::staged_smem_bytes(bp, shape), mode == qe::KM_FILTER ? shape.block_threads()
+    if (!qe::jit_load(cubin, qe::jit_entry_name(mode, shape), dyn_smem ? dyn_smem : qe::staged_smem_bytes(bp, shape),
+                      (mode == qe::KM_FILTER || mode == qe::KM_GROUPBY_REG) ? shape.block_threads()
                       : (mode == qe::KM_GROUPBY_PRIVATE || mode == qe::KM_GROUPBY_SHARED) ? shape.gthreads : QE_BLOCK,
                       e.kernel, err))
         return fail(QE_ERR_JIT, err);
@@ -1189,19 +1216,28 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     uint32_t ctl[4] = {0, 0, 0, 0};
     // a result that is reused remembers which variants this group-by has overflowed
     const std::string sig = bp.signature();
+    // levels: 0 registers, 1 private 512 threads, 2 private 256 threads, 3 CTA-shared, 4 global atomics
     int level = r->g_overflowed == sig ? r->g_level : 0;
-    if (d->flags & QE_GROUPBY_ATOMIC) level = 3;
-    else if (d->flags & QE_GROUPBY_SHARED) level = std::max(level, 2);
+    if (d->flags & QE_GROUPBY_ATOMIC) level = 4;
+    else if (d->flags & QE_GROUPBY_SHARED) level = std::max(level, 3);
     for (;; level++) {
-        if (level == 0 && gp512.lmax < 2) continue;
-        if (level == 1 && (gp.lmax < 1 || gp.lmax <= gp512.lmax)) continue;
-        if (level == 2 && gp512.slmax < 64) continue;
-        const bool atomic = level >= 3, shared = level == 2;
-        const qe::GroupPlan &plan = (level == 0 || level == 2) ? gp512 : gp;
-        const qe::KernelMode mode = atomic ? qe::KM_GROUPBY_ATOMIC : shared ? qe::KM_GROUPBY_SHARED : qe::KM_GROUPBY_PRIVATE;
-        const int part_groups = shared ? plan.slmax : plan.lmax;
-        qe::TileShape shape = choose_shape(ctx, bp, mode);
-        if (!atomic) {
+        const bool regs = level == 0;
+        qe::TileShape reg_shape;
+        if (regs) {
+            if (!ctx->opt_groupby_registers || gp.rmax < 2) continue;
+            reg_shape = choose_shape(ctx, bp, qe::KM_GROUPBY_REG);
+            // the final reduce lays the thread copies out over the stages
+            if (!reg_shape.greg || (size_t)gp.nwords * (size_t)gp.rmax * (size_t)reg_shape.ncw * 32u * 8u > qe::staged_smem_bytes(bp, reg_shape)) continue;
+        }
+        if (level == 1 && gp512.lmax < 2) continue;
+        if (level == 2 && (gp.lmax < 1 || gp.lmax <= gp512.lmax)) continue;
+        if (level == 3 && gp512.slmax < 64) continue;
+        const bool atomic = level >= 4, shared = level == 3;
+        const qe::GroupPlan &plan = (level == 1 || level == 3) ? gp512 : gp;
+        const qe::KernelMode mode = regs ? qe::KM_GROUPBY_REG : atomic ? qe::KM_GROUPBY_ATOMIC : shared ? qe::KM_GROUPBY_SHARED : qe::KM_GROUPBY_PRIVATE;
+        const int part_groups = regs ? plan.rmax : shared ? plan.slmax : plan.lmax;
+        qe::TileShape shape = regs ? reg_shape : choose_shape(ctx, bp, mode);
+        if (!atomic && !regs) {
             shape.gthreads = plan.threads;
             if (plan.threads == 512 && !ctx->opt_steps && !ctx->opt_vec) {      // measured best for 16- and 48-byte rows
                 shape.steps = 1;
@@ -1209,7 +1245,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
             }
         }
         JitEntry *jit = nullptr;
-        if ((rc = get_jit_kernel(ctx, bp, mode, shape, &jit, atomic ? 0 : shared ? plan.shared_smem() : plan.private_smem()))) return rc;
+        if ((rc = get_jit_kernel(ctx, bp, mode, shape, &jit, (atomic || regs) ? 0 : shared ? plan.shared_smem() : plan.private_smem()))) return rc;
         const int64_t tile_rows = shape.rows_per_tile();
         const int64_t ntiles64 = (n + tile_rows - 1) / tile_rows;
         int blocks_per_sm = jit->kernel.blocks_per_sm;
@@ -1223,14 +1259,15 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
             p.g_part_slot = (qe_u32 *)r->g_part_slot.ptr;
         }
         r->mode = (int)mode;
-        r->g_variant = atomic ? 1 : shared ? 2 : 0;
-        r->g_threads = atomic ? QE_BLOCK : plan.threads;
+        r->g_variant = regs ? 3 : atomic ? 1 : shared ? 2 : 0;
+        const int threads = regs ? shape.block_threads() : atomic ? QE_BLOCK : plan.threads;
+        r->g_threads = threads;
         QE_CUDA(qe::launch_groupby_init((uint32_t *)r->g_state.ptr, (uint64_t *)r->g_acc.ptr, (uint32_t *)r->g_ctl.ptr, nslots, gw, ctx->stream));
         ctx->launches++;
         QE_CUDA(cudaEventRecord(r->ev_begin, ctx->stream));
         if (n > 0) {
             void *args[] = {&p};
-            QE_CUDA(cudaLaunchKernel((const void *)jit->kernel.kernel, dim3(grid), dim3(atomic ? QE_BLOCK : plan.threads), args,
+            QE_CUDA(cudaLaunchKernel((const void *)jit->kernel.kernel, dim3(grid), dim3(threads), args,
                                      jit->kernel.dyn_smem, ctx->stream));
             ctx->launches++;
         }
@@ -1730,7 +1767,7 @@ static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *co
     qe::BoundPipeline bp;
     int rc = qe::bind_pipeline(schema, has_filter ? &progs[0] : nullptr, proj, aggs, bp, err, group_keys);
     if (rc) return fail(rc, err);
-    const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : atomic == 2 ? qe::KM_GROUPBY_SHARED : qe::KM_GROUPBY_PRIVATE)
+    const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : atomic == 2 ? qe::KM_GROUPBY_SHARED : atomic == 3 ? qe::KM_GROUPBY_REG : qe::KM_GROUPBY_PRIVATE)
                               : !bp.agg_fns.empty() ? qe::KM_AGG : bp.has_filter ? qe::KM_FILTER : qe::KM_PROJECT;
     qe_ctx dummy;
     dummy.opt_steps = steps;

@@ -45,15 +45,19 @@ def _gpu_table(ctx, fields, rows):
     return ColumnarTable.from_arrays(ctx, fields, cols, valid)
 
 
-@pytest.mark.parametrize("atomic", [False, True])
+@pytest.mark.parametrize("atomic", [False, "private", True])
 def test_querytest_group_by_multiple_columns_golden(ctx, atomic):
     # T/evaluator/QueryTest.kt:14-32, as written there: SELECT bar, SUM(num), foo FROM table
     fields = [Field("foo", S, True), Field("bar", S, True), Field("num", D, True)]
     rows = [["a", "A", 1.0], ["a", "B", 2.0], ["a", "B", 3.0], ["b", "B", 4.0], ["b", "B", None], ["c", None, None]]
     t = _gpu_table(ctx, fields, rows)
-    op = GpuGroupByOperator(t, None, [col(1, S), agg(A.SUM, col(2)), col(0, S)], atomic=atomic)
-    assert op.map() == [["A", 1.0, "a"], ["B", 5.0, "a"], ["B", 4.0, "b"], [None, None, "c"]]
-    assert op.map() == [["A", 1.0, "a"], ["B", 5.0, "a"], ["B", 4.0, "b"], [None, None, "c"]]      # re-open
+    ctx.set_option("groupby_registers", 0 if atomic == "private" else 1)
+    try:
+        op = GpuGroupByOperator(t, None, [col(1, S), agg(A.SUM, col(2)), col(0, S)], atomic=atomic is True)
+        assert op.map() == [["A", 1.0, "a"], ["B", 5.0, "a"], ["B", 4.0, "b"], [None, None, "c"]]
+        assert op.map() == [["A", 1.0, "a"], ["B", 5.0, "a"], ["B", 4.0, "b"], [None, None, "c"]]      # re-open
+    finally:
+        ctx.set_option("groupby_registers", 1)
     t.close()
 
 
@@ -82,8 +86,15 @@ def _random_rows(rng, n, nstr, cardinality):
 FIELDS = [Field("s", S, True), Field("b", B, True), Field("k", D, True), Field("x", D, False), Field("y", D, True)]
 
 
-def _check_against_oracle(ctx, rows, keys, inputs, fns, filter_, atomic, expect_variant=None, max_groups=0):
+def _check_against_oracle(ctx, rows, keys, inputs, fns, filter_, atomic, expect_variant=None, max_groups=0, fields=None):
+    if atomic == "private":                   # start with the shared-memory private variant instead of the register one
+        ctx.set_option("groupby_registers", 0)
+        try:
+            return _check_against_oracle(ctx, rows, keys, inputs, fns, filter_, False, expect_variant, max_groups, fields)
+        finally:
+            ctx.set_option("groupby_registers", 1)
     nkeys = len(keys)
+    FIELDS = fields if fields is not None else globals()["FIELDS"]
     t = _gpu_table(ctx, FIELDS, rows)
     shared = atomic == "shared"
     atomic = atomic is True
@@ -141,7 +152,7 @@ def _check_against_oracle(ctx, rows, keys, inputs, fns, filter_, atomic, expect_
     return got
 
 
-@pytest.mark.parametrize("atomic", [False, "shared", True])
+@pytest.mark.parametrize("atomic", [False, "private", "shared", True])
 @pytest.mark.parametrize("nrows", [0, 1, 300, 20000])
 def test_groupby_matches_oracle_keys_order_and_aggregates(ctx, nrows, atomic):
     rng = np.random.default_rng(7 + nrows)
@@ -156,6 +167,29 @@ def test_groupby_matches_oracle_keys_order_and_aggregates(ctx, nrows, atomic):
                           [fn(Function.MUL, x, y)], [A.SUM], fn(Function.CMP_NE, s, StringLiteralExpression("g1")), atomic)
     # no keys at all: one group (when any row arrives)
     _check_against_oracle(ctx, rows, [], [x, y], [A.SUM, A.COUNT], None, atomic) if nrows else None
+
+
+@pytest.mark.parametrize("nrows", [1, 5000, 40000])
+def test_register_variant_with_nulls_and_non_finite_inputs(ctx, nrows):
+    # wide rows and few groups: the register variant (3).  SUM words are updated with a DFMA by a 0.0 / 1.0 mask, which
+    # is only valid for finite inputs -- rows carrying Inf / NaN (null or not) must take the select path and must not
+    # leak into the other groups
+    fields = [Field("k", D, True), Field("x", D, True), Field("y", D, True), Field("z", D, False), Field("w", D, False),
+              Field("s", S, False)]
+    rng = np.random.default_rng(100 + nrows)
+    specials = [float("inf"), float("-inf"), float("nan")]
+    rows = []
+    for i in range(nrows):
+        k = None if rng.random() < 0.1 else float(rng.integers(0, 3))
+        x = specials[int(rng.integers(3))] if (k == 2.0 and rng.random() < 0.01) else (None if rng.random() < 0.2 else float(np.round(rng.uniform(-100, 100), 2)))
+        y = None if rng.random() < 0.3 else float(rng.uniform(-1e6, 1e6))
+        z = float("inf") if (k == 1.0 and i % 977 == 5) else float(rng.integers(-1000, 1000))
+        rows.append([k, x, y, z, float(rng.integers(0, 100)), "f%d" % int(rng.integers(2))])
+    k, x, y, z, w, s = (col(i, f.type) for i, f in enumerate(fields))
+    _check_against_oracle(ctx, rows, [k], [x, x, x, y, y, z, w, s], [A.SUM, A.AVG, A.MIN, A.MAX, A.COUNT, A.SUM, A.SUM, A.COUNT], None, False,
+                          expect_variant=3, fields=fields)
+    _check_against_oracle(ctx, rows, [k], [x, z, w, fn(Function.MUL, z, w)], [A.SUM, A.SUM, A.AVG, A.SUM], fn(Function.CMP_GE, w, 10.0), False,
+                          expect_variant=3, fields=fields)
 
 
 def test_many_groups_fall_back_to_atomics_and_capacity_is_checked(ctx):
@@ -178,15 +212,28 @@ def test_many_groups_fall_back_to_atomics_and_capacity_is_checked(ctx):
     t.close()
 
 
-def test_private_variant_is_reproducible_and_reports_partials(ctx):
+@pytest.mark.parametrize("registers", [1, 0])
+def test_private_variant_is_reproducible_and_reports_partials(ctx, registers):
+    # few groups: accumulators in registers (variant 3) by default, thread-private shared-memory copies (variant 0)
+    # when that is switched off; both reduce in a fixed order
+    ctx.set_option("groupby_registers", registers)
+    try:
+        _reproducible(ctx, 3 if registers else 0)
+    finally:
+        ctx.set_option("groupby_registers", 1)
+
+
+def _reproducible(ctx, expect_variant):
     n = 2_000_000
-    fields = [Field("g", D, False), Field("x", D, False)]
+    # 40-byte rows, five words per group: wide enough for the register variant's cost rule (plan_groupby)
+    fields = [Field("g", D, False)] + [Field(c, D, False) for c in "xyzw"]
     t = ColumnarTable(ctx, fields, n)
     t.generate(0, capi.QE_GEN_UNIFORM_INT, 11, 0, 5)
-    t.generate(1, capi.QE_GEN_UNIFORM_REAL, 12, -1.0, 1.0)
-    pipe = GroupByPipeline(t, None, [col(0)], [col(1), col(1)], [A.SUM, A.COUNT])
+    for c in range(1, 5):
+        t.generate(c, capi.QE_GEN_UNIFORM_REAL, 11 + c, -1.0, 1.0)
+    pipe = GroupByPipeline(t, None, [col(0)], [col(1), col(1), col(2), col(3), col(4)], [A.SUM, A.COUNT, A.SUM, A.SUM, A.SUM])
     r1 = pipe.run()
-    assert capi.lib().qe_result_group_variant(r1.handle) == 0
+    assert capi.lib().qe_result_group_variant(r1.handle) == expect_variant
     a = [r1.column(k)[0].copy() for k in range(3)]
     r2 = pipe.run()
     b = [r2.column(k)[0].copy() for k in range(3)]
