@@ -648,7 +648,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     if (is_group) {
         // GroupByAggregationOperator.open (M/operator/GroupByAggregationOperator.kt:21-48): key = the first
         // NKEYS values of the row, accumulator i takes value NKEYS + i, nulls are skipped
-        const GroupPlan gp = plan_groupby(bp, shape.gthreads);
+        GroupPlan gp = plan_groupby(bp, shape.gthreads);
+        if (shape.rmax_hint > 0 && shape.rmax_hint < gp.rmax) gp.rmax = shape.rmax_hint;
         snprintf(b, sizeof b, "    static constexpr int NKEYS = %d, NWORDS = %d, LMAX = %d, CSLOTS = %d, GTHREADS = %d;\n", gp.nkeys > 0 ? gp.nkeys : 1,
                  gp.nwords, gp.lmax > 0 ? gp.lmax : 1, gp.cslots, gp.threads);
         s += b;

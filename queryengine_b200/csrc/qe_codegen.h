@@ -56,6 +56,7 @@ struct TileShape {
     // group-by, register variant (qe_groupby_reg_body): the same ring of bulk-copy stages (tile_rows, ncw, nstages),
     // one producer warp + ncw consumer warps, no look-back
     bool greg = false;
+    int rmax_hint = 0;      // register variant: compile for this many groups instead of the plan's maximum (0: the maximum)
 
     int rows_per_tile() const { return (ring || greg) ? tile_rows : (gthreads / 32) * steps * 32 * vec; }
     int block_threads() const { return greg ? 32 * (1 + ncw) : ring ? 32 * (2 + nlb + ncw) : 256; }

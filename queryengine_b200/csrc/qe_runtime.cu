@@ -526,6 +526,8 @@ struct qe_result {
     std::vector<std::vector<uint8_t>> h_values, h_valid;    // per output column: values in the column's layout, Arrow bitmap
     int64_t h_rows = 0;
     int g_nkeys = 0, g_variant = 0, g_threads = 0;          // variant: 0 private accumulators, 1 global atomics, 2 CTA-shared, 3 registers
+    std::string g_seen_sig;                                 // signature of the last group-by that completed into this result ...
+    int g_seen_groups = 0;                                  // ... and how many groups it found (sizes the register variant next time)
     std::string g_overflowed;                               // signature of the group-by whose private variant overflowed here
     int g_level = 0;                                        // ... and the variant to start with next time (0: private 512 threads,
                                                             // 1: private 256, 2: CTA-shared accumulators, 3: global atomics)
@@ -731,7 +733,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     char suffix[128];
     snprintf(suffix, sizeof suffix, "|M%d|B%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d.%d|G%d", (int)mode, shape.min_blocks, shape.steps, shape.vec, shape.staged ? 1 : 0,
              shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0, shape.ring ? 1 : 0, shape.tile_rows, shape.ncw,
-             shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 : 0));
+             shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0));
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) { *out = &it->second; return QE_OK; }
@@ -1220,14 +1222,19 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     int level = r->g_overflowed == sig ? r->g_level : 0;
     if (d->flags & QE_GROUPBY_ATOMIC) level = 4;
     else if (d->flags & QE_GROUPBY_SHARED) level = std::max(level, 3);
+    // register variant: every group's words are touched for every row, so compile for the group count the same
+    // group-by found last time (a reused result remembers it); more groups than that -> once more with the maximum
+    int rmax_use = gp.rmax;
+    if (r->g_seen_sig == sig && r->g_seen_groups > 0) rmax_use = std::min(gp.rmax, std::max(4, r->g_seen_groups));
     for (;; level++) {
         const bool regs = level == 0;
         qe::TileShape reg_shape;
         if (regs) {
             if (!ctx->opt_groupby_registers || gp.rmax < 2) continue;
             reg_shape = choose_shape(ctx, bp, qe::KM_GROUPBY_REG);
+            reg_shape.rmax_hint = rmax_use;
             // the final reduce lays the thread copies out over the stages
-            if (!reg_shape.greg || (size_t)gp.nwords * (size_t)gp.rmax * (size_t)reg_shape.ncw * 32u * 8u > qe::staged_smem_bytes(bp, reg_shape)) continue;
+            if (!reg_shape.greg || (size_t)gp.nwords * (size_t)rmax_use * (size_t)reg_shape.ncw * 32u * 8u > qe::staged_smem_bytes(bp, reg_shape)) continue;
         }
         if (level == 1 && gp512.lmax < 2) continue;
         if (level == 2 && (gp.lmax < 1 || gp.lmax <= gp512.lmax)) continue;
@@ -1235,7 +1242,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
         const bool atomic = level >= 4, shared = level == 3;
         const qe::GroupPlan &plan = (level == 1 || level == 3) ? gp512 : gp;
         const qe::KernelMode mode = regs ? qe::KM_GROUPBY_REG : atomic ? qe::KM_GROUPBY_ATOMIC : shared ? qe::KM_GROUPBY_SHARED : qe::KM_GROUPBY_PRIVATE;
-        const int part_groups = regs ? plan.rmax : shared ? plan.slmax : plan.lmax;
+        const int part_groups = regs ? rmax_use : shared ? plan.slmax : plan.lmax;
         qe::TileShape shape = regs ? reg_shape : choose_shape(ctx, bp, mode);
         if (!atomic && !regs) {
             shape.gthreads = plan.threads;
@@ -1285,10 +1292,17 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
         if (!(ctl[1] & 1u)) break;
         if (atomic) return fail(QE_ERR_STATE, "group-by: unexpected overflow flag");
         fold_timing(r);          // the discarded attempt still ran: keep its time in the totals
+        if (regs && rmax_use < gp.rmax) {                      // more groups than last time: the same variant at full size
+            rmax_use = gp.rmax;
+            level--;
+            continue;
+        }
         r->g_overflowed = sig;   // a CTA met more groups than fit its shared memory: next variant
         r->g_level = level + 1;
     }
     const int64_t ngroups = ctl[0];
+    r->g_seen_sig = sig;
+    r->g_seen_groups = (int)std::min<int64_t>(ngroups, 1 << 20);
     if (ngroups > 0) {
         if ((rc = ensure(ctx, r->g_records, (size_t)ngroups * (size_t)(gp.nwords + gp.nkeys + 1) * 8))) return rc;
         QE_CUDA(qe::launch_groupby_collect((const uint32_t *)r->g_state.ptr, (const uint64_t *)r->g_keys.ptr, (const uint32_t *)r->g_nulls.ptr,
