@@ -1980,37 +1980,53 @@ __device__ __forceinline__ void qe_groupby_reg_body(const QeParams &p)
             const volatile QeGroupCache<NKEYS, CS, RMAX> &vc = gc;
             if (!vc.over) {
                 const qe_i64 live = p.nrows - (qe_i64)t * TILE - wrow0 - (qe_i64)lane;   // rows of this lane's column that exist
+                // Three passes over the warp's STEPS rows, each straight-line code, so that the shared-memory reads of
+                // all steps are in flight together (three warps per scheduler cannot hide a per-row chain of
+                // evaluate -> probe -> compare -> update): (1) evaluate and probe the key cache once, every read
+                // unconditional, (2) the rare misses -- new or displaced keys -- take the probing loop, (3) update.
+                typename P::Out o[STEPS];
+                int l[STEPS];
+                qe_u32 miss = 0;
 #pragma unroll
                 for (int s = 0; s < STEPS; s++) {
                     typename P::Row row;
-                    typename P::Out o;
                     P::load_row(stage, wrow0, s * 32, row);
-                    const bool keep = P::eval(p, row, o) && (qe_i64)(s * 32) < live;
-                    int l = -1;
-                    if (keep) {
+                    const bool keep = P::eval(p, row, o[s]) && (qe_i64)(s * 32) < live;
+                    qe_u64 k[NKEYS];
+                    qe_u32 nulls;
+                    P::key_pack(o[s], k, nulls);
+                    const qe_u32 c = qe_group_hash<NKEYS>(k, nulls) & (qe_u32)(CS - 1);
+                    // state first: a slot seen ready (2) never changes again, and a thread's shared-memory reads complete in order
+                    bool hit = vc.state[c] == 2u;
+                    hit &= vc.nulls[c] == nulls;
+#pragma unroll
+                    for (int i = 0; i < NKEYS; i++) hit &= vc.keys[c][i] == k[i];
+                    const int lc = vc.local[c];
+                    l[s] = (keep && hit) ? lc : -1;
+                    miss |= (keep && !hit) ? (1u << s) : 0u;
+                }
+                if (miss) {
+#pragma unroll
+                    for (int s = 0; s < STEPS; s++) {
+                        if (!((miss >> s) & 1u)) continue;
                         qe_u64 k[NKEYS];
                         qe_u32 nulls;
-                        P::key_pack(o, k, nulls);
-                        const qe_u32 h = qe_group_hash<NKEYS>(k, nulls);
-                        const qe_u32 c = h & (qe_u32)(CS - 1);
-                        // first probe, straight-line: volatile keeps the reads in this order (state first)
-                        bool hit = vc.state[c] == 2u;
-                        hit = hit && vc.nulls[c] == nulls;
-#pragma unroll
-                        for (int i = 0; i < NKEYS; i++) hit = hit && vc.keys[c][i] == k[i];
-                        l = vc.local[c];
-                        if (!hit) l = qe_group_local_slow<NKEYS, CS, RMAX>(p, &gc, k, nulls, h);
+                        P::key_pack(o[s], k, nulls);
+                        l[s] = qe_group_local_slow<NKEYS, CS, RMAX>(p, &gc, k, nulls, qe_group_hash<NKEYS>(k, nulls));
                     }
+                }
+#pragma unroll
+                for (int s = 0; s < STEPS; s++) {
                     const qe_u32 rowid = p.sel_base + t * (qe_u32)TILE + (qe_u32)(wrow0 + s * 32) + lane;
                     // SUM words: one DFMA by a 0.0 / 1.0 mask per group and word (bit-identical to the add: v * 1.0
                     // is v, v * 0.0 is a zero of either sign and leaves a sum that started at +0.0 unchanged) --
                     // unless an input is Inf / NaN, whose product with 0.0 would poison the other groups: selects then
-                    if (P::all_finite(o)) {
+                    if (P::all_finite(o[s])) {
 #pragma unroll
-                        for (int g = 0; g < RMAX; g++) P::acc_regs_fma(rfirst[g], rrows[g], racc[g], o, rowid, l, g);
+                        for (int g = 0; g < RMAX; g++) P::acc_regs_fma(rfirst[g], rrows[g], racc[g], o[s], rowid, l[s], g);
                     } else {
 #pragma unroll
-                        for (int g = 0; g < RMAX; g++) P::acc_regs(rfirst[g], rrows[g], racc[g], o, rowid, l, g);
+                        for (int g = 0; g < RMAX; g++) P::acc_regs(rfirst[g], rrows[g], racc[g], o[s], rowid, l[s], g);
                     }
                 }
             } else if (!flagged && cw == 0 && lane == 0) {
