@@ -373,6 +373,7 @@ GroupPlan plan_groupby(const BoundPipeline &bp, int threads)
     // of accumulators leave room for the row and the expression temporaries under the 152 a 416-thread CTA gets
     const int reg_per_group = 2 + 2 * (g.nwords - 1);
     g.rmax = std::min(16, 96 / reg_per_group);
+    g.rmax_regs = g.rmax < 2 ? 0 : g.rmax;
     // ... and it pays only where the row is wide enough for the issue slots: a row costs about
     // 100 + RMAX * (4 + words) instructions (every group's words are touched, predicated), and at the HBM rate an
     // SM has ~5.7 issue slots per row byte (measured: Q1 shape, 48-byte rows, 6 words, RMAX 8: 5.8 ms against 7.3
@@ -649,7 +650,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         // GroupByAggregationOperator.open (M/operator/GroupByAggregationOperator.kt:21-48): key = the first
         // NKEYS values of the row, accumulator i takes value NKEYS + i, nulls are skipped
         GroupPlan gp = plan_groupby(bp, shape.gthreads);
-        if (shape.rmax_hint > 0 && shape.rmax_hint < gp.rmax) gp.rmax = shape.rmax_hint;
+        if (shape.rmax_hint > 0) gp.rmax = std::min(shape.rmax_hint, gp.rmax_regs);
         snprintf(b, sizeof b, "    static constexpr int NKEYS = %d, NWORDS = %d, LMAX = %d, CSLOTS = %d, GTHREADS = %d;\n", gp.nkeys > 0 ? gp.nkeys : 1,
                  gp.nwords, gp.lmax > 0 ? gp.lmax : 1, gp.cslots, gp.threads);
         s += b;

@@ -34,6 +34,7 @@ struct GroupPlan {
     int slmax = 0, scslots = 0;            // shared variant: groups per CTA (one copy of the words), key-cache slots
     size_t shared_smem() const;            // accumulators + key cache, all dynamic
     int rmax = 0;                          // register variant: groups per CTA whose accumulators every thread keeps in registers (0: not applicable)
+    int rmax_regs = 0;                     // ... by the register budget alone, without the cost rule
 };
 GroupPlan plan_groupby(const BoundPipeline &bp, int threads = 256);
 

@@ -265,7 +265,8 @@ extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
     } else if (k == "pipeline") {
         ctx->opt_pipeline = value != 0;
     } else if (k == "groupby_registers") {
-        ctx->opt_groupby_registers = value != 0;             // 0: group-by starts with the private (shared-memory) variant
+        if (value < 0 || value > 2) return fail(QE_ERR_INVALID_ARGUMENT, "groupby_registers must be 0 (off), 1 (by the cost rule) or 2 (whenever the registers suffice)");
+        ctx->opt_groupby_registers = value;                  // 0: group-by starts with the private (shared-memory) variant
     } else if (k == "tile_rows") {
         if (value < 0 || value > kPadRows || value % 128) return fail(QE_ERR_INVALID_ARGUMENT, "tile_rows must be 0 (auto) or a multiple of 128 up to 8192");
         ctx->opt_tile_rows = value;
@@ -1224,13 +1225,14 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     else if (d->flags & QE_GROUPBY_SHARED) level = std::max(level, 3);
     // register variant: every group's words are touched for every row, so compile for the group count the same
     // group-by found last time (a reused result remembers it); more groups than that -> once more with the maximum
-    int rmax_use = gp.rmax;
-    if (r->g_seen_sig == sig && r->g_seen_groups > 0) rmax_use = std::min(gp.rmax, std::max(4, r->g_seen_groups));
+    const int rmax_full = ctx->opt_groupby_registers == 2 ? gp.rmax_regs : gp.rmax;
+    int rmax_use = rmax_full;
+    if (r->g_seen_sig == sig && r->g_seen_groups > 0) rmax_use = std::min(rmax_full, std::max(4, r->g_seen_groups));
     for (;; level++) {
         const bool regs = level == 0;
         qe::TileShape reg_shape;
         if (regs) {
-            if (!ctx->opt_groupby_registers || gp.rmax < 2) continue;
+            if (!ctx->opt_groupby_registers || rmax_full < 2) continue;
             reg_shape = choose_shape(ctx, bp, qe::KM_GROUPBY_REG);
             reg_shape.rmax_hint = rmax_use;
             // the final reduce lays the thread copies out over the stages
@@ -1292,8 +1294,8 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
         if (!(ctl[1] & 1u)) break;
         if (atomic) return fail(QE_ERR_STATE, "group-by: unexpected overflow flag");
         fold_timing(r);          // the discarded attempt still ran: keep its time in the totals
-        if (regs && rmax_use < gp.rmax) {                      // more groups than last time: the same variant at full size
-            rmax_use = gp.rmax;
+        if (regs && rmax_use < rmax_full) {                    // more groups than last time: the same variant at full size
+            rmax_use = rmax_full;
             level--;
             continue;
         }
