@@ -2140,23 +2140,46 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
         typename P::Out outs[STEPS][VEC];
         qe_u32 keep[STEPS];
         qe_rows_eval<P>(p, warp_row0, rows, outs, keep);
+        // probes of all rows first (unconditional reads, all in flight together), misses second, updates third
+        const volatile Cache &vc = gc;
+        int lg[STEPS][VEC];
+        qe_u32 miss = 0;
 #pragma unroll
         for (int s = 0; s < STEPS; s++) {
 #pragma unroll
             for (int j = 0; j < VEC; j++) {
-                if (!((keep[s] >> j) & 1u)) continue;
+                const bool kept = (keep[s] >> j) & 1u;
                 qe_u64 k[NKEYS];
                 qe_u32 nulls;
                 P::key_pack(outs[s][j], k, nulls);
-                const qe_u32 h = qe_group_hash<NKEYS>(k, nulls);
-                const qe_u32 c = h & (qe_u32)(CS - 1);
-                const volatile Cache &vc = gc;
+                const qe_u32 c = qe_group_hash<NKEYS>(k, nulls) & (qe_u32)(CS - 1);
                 bool hit = vc.state[c] == 2u;
-                hit = hit && vc.nulls[c] == nulls;
+                hit &= vc.nulls[c] == nulls;
 #pragma unroll
-                for (int i = 0; i < NKEYS; i++) hit = hit && vc.keys[c][i] == k[i];
-                int l = vc.local[c];
-                if (!hit) l = qe_group_local_slow<NKEYS, CS, LMAX>(p, &gc, k, nulls, h);
+                for (int i = 0; i < NKEYS; i++) hit &= vc.keys[c][i] == k[i];
+                const int lc = vc.local[c];
+                lg[s][j] = (kept && hit) ? lc : -1;
+                miss |= (kept && !hit) ? (1u << (s * VEC + j)) : 0u;
+            }
+        }
+        if (miss) {
+#pragma unroll
+            for (int s = 0; s < STEPS; s++) {
+#pragma unroll
+                for (int j = 0; j < VEC; j++) {
+                    if (!((miss >> (s * VEC + j)) & 1u)) continue;
+                    qe_u64 k[NKEYS];
+                    qe_u32 nulls;
+                    P::key_pack(outs[s][j], k, nulls);
+                    lg[s][j] = qe_group_local_slow<NKEYS, CS, LMAX>(p, &gc, k, nulls, qe_group_hash<NKEYS>(k, nulls));
+                }
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < STEPS; s++) {
+#pragma unroll
+            for (int j = 0; j < VEC; j++) {
+                const int l = lg[s][j];
                 if (l >= 0) {
                     const qe_u64 row = (qe_u64)p.sel_base + (qe_u64)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j);
                     P::acc_atomic(s_acc + (size_t)l * NWORDS, outs[s][j], row);
