@@ -18,4 +18,4 @@ run filter_s099 qe_filter_ring_kernel --what filter --sel 0.99
 run q6_agg qe_agg_kernel --what q6 --rows 600037902
 run tree_project qe_project_kernel --what tree
 run sf_filter_2proj qe_filter_ring_kernel --what sf
-run q1_groupby qe_groupby_private_kernel --what q1 --rows 600037902
+run q1_groupby qe_groupby_reg_kernel --what q1 --rows 600037902
