@@ -146,7 +146,9 @@ QE_API void *qe_ctx_stream(qe_ctx *ctx);
  * "grid_per_sm" (0 = auto), "staging" (filter kernel variant: -1 auto = 2; 0 register-sourced; 1 bulk-copy stages,
  * look-back in line; 2 warp-specialised ring of bulk-copy stages with deferred scatter), "stages" (0 = auto, 2..32),
  * ring variant: "stage_kb" (bytes of column data per stage, 0 = auto), "tile_rows" (0 = auto), "ncw" (consumer
- * warps, 0 = auto), "defer" (tiles between evaluation and scatter, 0 = auto) */
+ * warps, 0 = auto: 20 for a single 8-byte column, else 16), "defer" (tiles between evaluation and scatter, 0 = auto);
+ * group-by: "groupby_registers" (1 default: accumulators in registers when the cost rule allows; 0 never; 2 whenever
+ * the registers suffice) */
 QE_API int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value);
 /* kernels launched by this context so far */
 QE_API int64_t qe_ctx_launch_count(const qe_ctx *ctx);

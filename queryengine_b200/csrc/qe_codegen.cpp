@@ -186,6 +186,14 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
             const char *f = in.op == OP_ADD ? "qe_add" : in.op == OP_SUB ? "qe_sub" : in.op == OP_MUL ? "qe_mul"
                           : in.op == OP_DIV ? "qe_div" : "qe_mod";
             r.t = VT_F64; r.valid = and_valid(a.valid, b.valid); r.val = g.tmp("t");
+            if (in.op == OP_MOD && b.is_const && !a.is_const) {
+                // literal divisor: multiply by its reciprocal instead of dividing (qe_mod_k); both must be normal
+                const double kk = std::fabs(b.k), inv = 1.0 / kk;
+                if (kk >= 0x1p-1000 && kk <= 0x1p1000 && std::isfinite(inv)) {
+                    g.line("const double " + r.val + " = qe_mod_k(" + a.val + ", " + b.val + ", " + f64_literal(kk) + ", " + f64_literal(inv) + ");");
+                    break;
+                }
+            }
             g.line("const double " + r.val + " = " + f + "(" + a.val + ", " + b.val + ");");
             break;
         }

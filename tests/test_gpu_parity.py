@@ -446,6 +446,32 @@ def test_mod_fast_path_is_bit_exact(ctx, interpreter):
                                        fn(Function.MOD, col(1), col(0))], interpreter=interpreter)
 
 
+@pytest.mark.parametrize("k", [7.0, -7.0, 0.1, 3.0, 1e-3, 1e10, -2.5, 3.0 * 2.0 ** -20, 1.0, 2.0 ** -600, 2.0 ** 600, 0.7,
+                               1e-320, 2.0 ** 1010, 0.0, float("inf"), float("nan")])
+def test_mod_by_a_literal_is_bit_exact(ctx, k):
+    """`MOD(x, literal)`: the generated code multiplies by the literal's reciprocal and corrects the quotient
+    (qe_mod_k); dividends on and next to multiples of k, quotients up to and beyond the 2^51 switch to the general
+    path, signed zeros, infinities, NaN, denormals; divisors the fast path must refuse (denormal, huge, 0, Inf, NaN)."""
+    rng = np.random.default_rng(321)
+    n = 300_000
+    kk = abs(k) if np.isfinite(k) and k != 0.0 else 1.0
+    a = (rng.random(n) + 1.0) * 2.0 ** rng.integers(-60, 80, n) * rng.choice([-1.0, 1.0], n)
+    with np.errstate(over="ignore", invalid="ignore"):
+        q = rng.integers(0, 1 << 40, n // 3).astype(np.float64)
+        mult = q * kk                                           # (nearly) exact multiples, then one ulp either side
+        a[: n // 3] = mult * rng.choice([-1.0, 1.0], n // 3)
+        a[n // 3: n // 3 + 30000] = np.nextafter(mult[:30000], np.inf)
+        a[n // 3 + 30000: n // 3 + 60000] = np.nextafter(mult[:30000], -np.inf)
+        big = (2.0 ** 51 + rng.integers(-2000, 2000, 4000)) * kk  # quotients around the 2^51 switch
+        a[-5000:-1000] = big * rng.choice([-1.0, 1.0], 4000)
+    special = np.array([0.0, -0.0, np.inf, -np.inf, np.nan, 5e-324, -5e-324, 2.2250738585072014e-308, 1.7976931348623157e308,
+                        kk, -kk, np.nextafter(kk, 0.0), np.nextafter(kk, np.inf), 2 * kk, 0.5 * kk, 2.0 ** 53, 2.0 ** 53 + 2, 1e300])
+    a[-special.size:] = special
+    a = np.where(np.isfinite(a) | np.isnan(a) | np.isinf(a), a, 0.0)
+    spec = TableSpec([Field("a", D, False)], [a], [None])
+    compare_pipeline(ctx, spec, None, [fn(Function.MOD, col(0), k), fn(Function.ADD, fn(Function.MOD, fn(Function.MUL, col(0), 3.0), k), 1.0)])
+
+
 # ---------------------------------------------------------------- STRING columns as dictionary codes (SURVEY.md 8f next-3)
 
 S = DataType.STRING
