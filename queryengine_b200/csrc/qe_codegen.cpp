@@ -304,7 +304,7 @@ StageLayout stage_layout(const BoundPipeline &bp, const TileShape &shape)
 
 size_t staged_smem_bytes(const BoundPipeline &bp, const TileShape &shape)
 {
-    if (!shape.staged && !shape.ring && !shape.greg) return 0;
+    if (!shape.staged && !shape.ring && !shape.greg && !shape.pring) return 0;
     return (size_t)stage_layout(bp, shape).stride * (size_t)shape.nstages;
 }
 
@@ -470,8 +470,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     }
     s += "    }\n";
 
-    if ((mode == KM_FILTER && (shape.staged || shape.ring)) || (mode == KM_GROUPBY_REG && shape.greg)) {
-        const bool ringlike = shape.ring || shape.greg;
+    if ((mode == KM_FILTER && (shape.staged || shape.ring)) || (mode == KM_GROUPBY_REG && shape.greg) || (mode == KM_PROJECT && shape.pring)) {
+        const bool ringlike = shape.ring || shape.greg || shape.pring;
         const StageLayout L = stage_layout(bp, shape);
         snprintf(b, sizeof b, "    static constexpr int NSTAGES = %d, STAGE_BYTES = %d, STAGE_TX = %d;\n", shape.nstages, L.stride, L.tx);
         s += b;
@@ -567,7 +567,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     }
     s += "    }\n";
 
-    if (mode == KM_FILTER) {
+    if (mode == KM_FILTER || (mode == KM_PROJECT && shape.pring)) {
         s += "    static __device__ __forceinline__ void emit(const QeParams &p, qe_u64 pos, const Out &o) {\n";
         for (int k = 0; k < nproj; k++) {
             if (bp.outs[k].type == 2) continue;
@@ -805,14 +805,14 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     }
     s += "};\n\n";
     const char *body = mode == KM_FILTER ? (shape.ring ? "qe_filter_ring_body" : shape.staged ? "qe_filter_staged_body" : shape.pipelined ? "qe_filter_pipelined_body" : "qe_filter_body")
-                     : mode == KM_PROJECT ? "qe_project_body" : mode == KM_AGG ? "qe_agg_body"
+                     : mode == KM_PROJECT ? (shape.pring ? "qe_project_ring_body" : "qe_project_body") : mode == KM_AGG ? "qe_agg_body"
                      : mode == KM_GROUPBY_PRIVATE ? "qe_groupby_private_body"
                      : mode == KM_GROUPBY_REG ? "qe_groupby_reg_body"
                      : mode == KM_GROUPBY_SHARED ? "qe_groupby_shared_body" : "qe_groupby_atomic_body";
     snprintf(b, sizeof b,
              "extern \"C\" __global__ void __launch_bounds__(%d, %d) %s"
              "(const __grid_constant__ QeParams p)\n{\n    %s<P>(p);\n}\n",
-             (mode == KM_FILTER || mode == KM_GROUPBY_REG) ? shape.block_threads()
+             (mode == KM_FILTER || mode == KM_GROUPBY_REG || (mode == KM_PROJECT && shape.pring)) ? shape.block_threads()
                  : (mode == KM_GROUPBY_PRIVATE || mode == KM_GROUPBY_SHARED) ? shape.gthreads : 256, shape.min_blocks,
              jit_entry_name(mode, shape), body);
     s += b;
@@ -824,7 +824,7 @@ const char *jit_entry_name(KernelMode mode, const TileShape &shape)
     switch (mode) {
     case KM_FILTER: return shape.ring ? "qe_filter_ring_kernel" : shape.staged ? "qe_filter_staged_kernel"
                          : shape.pipelined ? "qe_filter_pipelined_kernel" : "qe_filter_kernel";
-    case KM_PROJECT: return "qe_project_kernel";
+    case KM_PROJECT: return shape.pring ? "qe_project_ring_kernel" : "qe_project_kernel";
     case KM_AGG: return "qe_agg_kernel";
     case KM_GROUPBY_PRIVATE: return "qe_groupby_private_kernel";
     case KM_GROUPBY_SHARED: return "qe_groupby_shared_kernel";

@@ -57,10 +57,12 @@ struct TileShape {
     // group-by, register variant (qe_groupby_reg_body): the same ring of bulk-copy stages (tile_rows, ncw, nstages),
     // one producer warp + ncw consumer warps, no look-back
     bool greg = false;
+    // dense projection through the same ring of stages (qe_project_ring_body): one producer warp + ncw consumer warps
+    bool pring = false;
     int rmax_hint = 0;      // register variant: compile for this many groups instead of the plan's maximum (0: the maximum)
 
-    int rows_per_tile() const { return (ring || greg) ? tile_rows : (gthreads / 32) * steps * 32 * vec; }
-    int block_threads() const { return greg ? 32 * (1 + ncw) : ring ? 32 * (2 + nlb + ncw) : 256; }
+    int rows_per_tile() const { return (ring || greg || pring) ? tile_rows : (gthreads / 32) * steps * 32 * vec; }
+    int block_threads() const { return (greg || pring) ? 32 * (1 + ncw) : ring ? 32 * (2 + nlb + ncw) : 256; }
 };
 
 // bytes of dynamic shared memory the staged filter kernel needs (0 when not staged)

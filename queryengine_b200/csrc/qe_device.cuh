@@ -1580,6 +1580,86 @@ __device__ __forceinline__ void qe_project_body(const QeParams &p)
     if (blockIdx.x == 0 && threadIdx.x == 0) *p.out_count = (qe_u64)p.nrows;
 }
 
+// K2, ring variant: the columns of a tile arrive in shared-memory stages by bulk copy (one producer warp, static
+// tile -> CTA assignment), NCW consumer warps evaluate one row per lane and step from shared memory and store the
+// dense outputs (one coalesced 256-byte store per 8-byte output and warp step, validity / BOOLEAN words by ballot).
+// The bytes in flight are bounded by shared memory instead of by the registers of four small CTAs.
+template <class P>
+__device__ __forceinline__ void qe_project_ring_body(const QeParams &p)
+{
+    constexpr int NST = P::NSTAGES, NCW = P::NCW, TILE = P::TILE_ROWS;
+    constexpr int WROWS = TILE / NCW, STEPS = WROWS / 32;
+    static_assert(WROWS % 32 == 0 && NCW >= 1 && NCW <= 31 && NST >= 2, "projection ring shape");
+
+    extern __shared__ __align__(128) unsigned char qe_dyn_smem[];
+    __shared__ __align__(8) qe_u64 s_bar[2 * NST];            // full[NST], empty[NST]
+    __shared__ qe_u32 s_tile[NST];
+    const qe_u32 warp = qe_warp(), lane = qe_lane();
+    const qe_u32 bar = qe_opaque_u32(qe_smem_addr(s_bar));
+    const qe_u32 dyn = qe_opaque_u32(qe_smem_addr(qe_dyn_smem));
+    const qe_u32 tl = qe_opaque_u32(qe_smem_addr(s_tile));
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int st = 0; st < NST; st++) {
+            qe_mbar_init(bar + 8u * st, 1);
+            qe_mbar_init(bar + 8u * (NST + st), NCW);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp == 0) {
+        if (lane == 0) {
+            const qe_u64 policy = qe_policy_evict_first();
+            qe_u32 st = 0, par = 0;
+            for (qe_u32 it = 0;; it++) {
+                if (it >= (qe_u32)NST) qe_mbar_wait(bar + 8u * (NST + st), par ^ 1u);
+                const qe_u32 t = blockIdx.x + it * gridDim.x;
+                qe_sts_u32(tl + 4u * st, t);
+                const qe_u32 full = bar + 8u * st;
+                if (t >= p.ntiles) {                          // end marker
+                    qe_mbar_arrive(full);
+                    break;
+                }
+                qe_mbar_expect_tx(full, (qe_u32)P::STAGE_TX);
+                P::issue(p, (qe_i64)t * TILE, dyn + st * (qe_u32)P::STAGE_BYTES, full, policy);
+                if (++st == (qe_u32)NST) { st = 0; par ^= 1u; }
+            }
+        }
+    } else {
+        const qe_u32 cw = warp - 1u;
+        const int wrow0 = (int)cw * WROWS;
+        qe_u32 st = 0, par = 0;
+        for (;;) {
+            qe_mbar_wait(bar + 8u * st, par);
+            const qe_u32 t = qe_lds_u32(tl + 4u * st);
+            if (t >= p.ntiles) break;
+            const qe_u32 stage = dyn + st * (qe_u32)P::STAGE_BYTES;
+            const qe_i64 row0 = (qe_i64)t * TILE + wrow0;     // first row of this warp's slice
+#pragma unroll
+            for (int s = 0; s < STEPS; s++) {
+                typename P::Row row;
+                typename P::Out o;
+                P::load_row(stage, wrow0, s * 32, row);
+                (void)P::eval(p, row, o);
+                const qe_i64 r = row0 + s * 32 + (qe_i64)lane;
+                const bool inb = r < p.nrows;
+                if (inb) P::emit(p, (qe_u64)r, o);
+#pragma unroll
+                for (int b = 0; b < P::NBITCOLS; b++) {
+                    qe_u32 *bm = P::bitcol(p, b);
+                    const qe_u32 w = __ballot_sync(QE_FULL_MASK, inb && P::bit(o, b));
+                    if (bm && lane == 0) bm[(row0 + s * 32) >> 5] = w;
+                }
+            }
+            __syncwarp();
+            if (lane == 0) qe_mbar_arrive(bar + 8u * (NST + st));
+            if (++st == (qe_u32)NST) { st = 0; par ^= 1u; }
+        }
+    }
+}
+
 template <class P>
 __device__ __forceinline__ void qe_agg_body(const QeParams &p)
 {

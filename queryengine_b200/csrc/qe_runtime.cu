@@ -669,6 +669,27 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         s.nlb = std::min(ctx->opt_nlb ? (int)ctx->opt_nlb : 1, s.nstages);   // the end markers need a stage each
         if (n * (stage + meta) > (224u << 10) || s.defer < 1) s.ring = false;   // a single tile does not fit: register-sourced kernel
     }
+    // Dense projection through the same ring of stages (one producer warp + 16 consumer warps): on request only
+    // ("staging" = 2).  Measured equal to the grid-stride kernel on the nullable tree (6.54 against 6.51 ms per
+    // 10^9 rows, both at the DRAM rate of an 80 % read / 20 % write mix), so the simpler kernel stays the default.
+    if (mode == qe::KM_PROJECT && ctx->opt_staging == 2 && !ctx->opt_steps && !ctx->opt_vec) {
+        s.pring = true;
+        s.ncw = ctx->opt_ncw ? (int)ctx->opt_ncw : 16;
+        const size_t quantum = (size_t)std::max(128, 32 * s.ncw);
+        const size_t stage_target = (size_t)(ctx->opt_stage_kb ? ctx->opt_stage_kb : 32) << 10;
+        size_t rows = stage_target / row_bytes / quantum * quantum;
+        if (rows * row_bytes < stage_target && (rows + quantum) * row_bytes <= (44u << 10)) rows += quantum;
+        if (ctx->opt_tile_rows) rows = (size_t)ctx->opt_tile_rows;
+        rows = std::min<size_t>(std::max(rows, quantum), (size_t)kPadRows / quantum * quantum);
+        if (rows % quantum) rows = (rows + quantum - 1) / quantum * quantum;
+        s.tile_rows = (int)rows;
+        s.nstages = 1;
+        const size_t stage = qe::staged_smem_bytes(bp, s);
+        size_t n = ctx->opt_stages ? (size_t)ctx->opt_stages : 8;
+        while (n > 2 && n * stage > (216u << 10)) n--;
+        s.nstages = (int)n;
+        if (n * stage > (216u << 10) || s.ncw % 4 || bp.slot_info.empty()) s.pring = false;   // does not fit (or reads no column): grid-stride kernel
+    }
     // Group-by, register variant: the same ring of stages, one producer warp + ncw consumer warps, no look-back.
     if (mode == qe::KM_GROUPBY_REG) {
         s.greg = true;
@@ -734,7 +755,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     char suffix[128];
     snprintf(suffix, sizeof suffix, "|M%d|B%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d.%d|G%d", (int)mode, shape.min_blocks, shape.steps, shape.vec, shape.staged ? 1 : 0,
              shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0, shape.ring ? 1 : 0, shape.tile_rows, shape.ncw,
-             shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0));
+             shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0) + (shape.pring ? 200000 : 0));
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) { *out = &it->second; return QE_OK; }
@@ -751,7 +772,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     e.shape = shape;
     std::string err;
     if (!qe::jit_load(cubin, qe::jit_entry_name(mode, shape), dyn_smem ? dyn_smem : qe::staged_smem_bytes(bp, shape),
-                      (mode == qe::KM_FILTER || mode == qe::KM_GROUPBY_REG) ? shape.block_threads()
+                      (mode == qe::KM_FILTER || mode == qe::KM_GROUPBY_REG || shape.pring) ? shape.block_threads()
                       : (mode == qe::KM_GROUPBY_PRIVATE || mode == qe::KM_GROUPBY_SHARED) ? shape.gthreads : QE_BLOCK,
                       e.kernel, err))
         return fail(QE_ERR_JIT, err);
@@ -815,7 +836,7 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
         shape = choose_shape(ctx, bp, mode);
         // Dense projection: four CTAs per SM (64 registers) hide the latency of the FP64 divide / MOD sequences better
         // than three (measured on the nullable tree: 6.83 -> 6.34 ms); kept only when the tighter bound does not spill.
-        if (mode == qe::KM_PROJECT && !ctx->opt_min_blocks) {
+        if (mode == qe::KM_PROJECT && !ctx->opt_min_blocks && !shape.pring) {
             qe::TileShape tight = shape;
             tight.min_blocks = 4;
             JitEntry *cand = nullptr;
@@ -830,7 +851,7 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
         blocks_per_sm = qe::interp_blocks_per_sm((int)mode);
     }
     const int64_t tile_rows = shape.rows_per_tile();
-    const int block_threads = use_jit && mode == qe::KM_FILTER ? shape.block_threads() : QE_BLOCK;
+    const int block_threads = use_jit && (mode == qe::KM_FILTER || shape.pring) ? shape.block_threads() : QE_BLOCK;
     const int64_t ntiles64 = (n + tile_rows - 1) / tile_rows;
     const uint32_t ntiles = (uint32_t)ntiles64;
     if (ctx->opt_grid_per_sm) blocks_per_sm = std::min<int>(blocks_per_sm, (int)ctx->opt_grid_per_sm);

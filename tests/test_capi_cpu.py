@@ -76,7 +76,7 @@ def test_generated_code_compiles_for_sm100a():
     rc, src, nbytes, err = _generate([(I, False)], fn(Function.CMP_LT, col(0, I), 1e6), [col(0, I)])
     assert rc == 0, err
     assert "qe_filter_ring_body<P>" in src and "((qe_i64)in.c0 < 1000000LL)" in src and nbytes > 1000
-    assert "TILE_ROWS = 4096" in src and "row.c0 = qe_stage1_i64(stage + 0, wrow0, c);" in src
+    assert "TILE_ROWS = 4480" in src and "NCW = 20" in src and "row.c0 = qe_stage1_i64(stage + 0, wrow0, c);" in src
     rc, src, nbytes, err = _generate([(I, False)], fn(Function.CMP_LT, col(0, I), 1e6), [col(0, I)], staging=0)
     assert rc == 0, err
     assert "qe_filter_pipelined_body<P>" in src and nbytes > 1000
@@ -92,7 +92,10 @@ def test_generated_code_compiles_for_sm100a():
                  fn(Function.SUB, fn(Function.MOD, col(2), 7.0), fn(Function.UNARY_MINUS, col(1)))))
     rc, src, nbytes, err = _generate([(D, False), (D, True), (D, True), (D, True)], None, [tree])
     assert rc == 0, err
-    assert "qe_project_body<P>" in src and "NBITCOLS = 1" in src
+    assert "qe_project_body<P>" in src and "NBITCOLS = 1" in src and "qe_mod_k(" in src
+    rc, src, nbytes, err = _generate([(D, False), (D, True), (D, True), (D, True)], None, [tree], staging=2)
+    assert rc == 0, err
+    assert "qe_project_ring_body<P>" in src and "qe_project_ring_kernel" in src
     # every tile shape the runtime may pick
     for steps in (1, 2, 4, 8):
         for vec in (2, 4):

@@ -176,6 +176,21 @@ def test_every_tile_shape(ctx, steps, vec, staging):
     c.close()
 
 
+@pytest.mark.parametrize("ncw,stage_kb,nrows", [(0, 0, 30011), (4, 4, 1), (8, 16, 4096), (20, 0, 100003), (12, 48, 65536)])
+def test_dense_projection_through_the_ring_of_stages(ctx, ncw, stage_kb, nrows):
+    """qe_project_ring_kernel ("staging" = 2 without a filter): bulk-copied stages, one row per lane and step, dense
+    value stores and validity / BOOLEAN words by ballot; every column type, nullable inputs, ragged tails."""
+    c = Context(0)
+    c.set_option("staging", 2)
+    c.set_option("ncw", ncw)
+    c.set_option("stage_kb", stage_kb)
+    rng = np.random.default_rng(77 + ncw)
+    spec = random_table(rng, nrows, "DbiTdB")
+    g = ExprGen(rng, spec.fields)
+    compare_pipeline(c, spec, None, [g.double(5), g.boolean(3), col(2, I), col(3, T), g.double(3), col(1, B)])
+    c.close()
+
+
 @pytest.mark.parametrize("stage_kb,ncw,defer,stages,nlb", [(0, 0, 0, 0, 0), (4, 4, 1, 2, 1), (8, 8, 1, 3, 3), (16, 16, 3, 5, 2),
                                                            (48, 8, 2, 4, 4), (2, 12, 9, 16, 8)])
 def test_every_ring_shape(ctx, stage_kb, ncw, defer, stages, nlb):
