@@ -315,7 +315,13 @@ size_t GroupPlan::shared_smem() const
     return (size_t)slmax * (size_t)nwords * 8u + (size_t)scslots * (8u * nk + 12u) + 4u * (size_t)slmax + 16u;
 }
 
-GroupPlan plan_groupby(const BoundPipeline &bp, int threads)
+size_t GroupPlan::shared_smem32() const
+{
+    const size_t nk = nkeys > 0 ? (size_t)nkeys : 1;
+    return (size_t)slmax32 * (size_t)nwords * 8u * 32u + (size_t)scslots32 * (8u * nk + 12u) + 4u * (size_t)slmax32 + 16u;
+}
+
+GroupPlan plan_groupby(const BoundPipeline &bp, int threads, int lane_acc_kb)
 {
     GroupPlan g;
     g.threads = threads;
@@ -377,6 +383,19 @@ GroupPlan plan_groupby(const BoundPipeline &bp, int threads)
         if (g.shared_smem() <= (208u << 10)) break;
     }
     if (g.slmax < 64) { g.slmax = 0; g.scslots = 64; }
+    // lane-private copies: 32 x the accumulator bytes, 8 key-cache slots per group
+    // Key cache: >= 16 slots per group.  With 8 (256 groups in 2 048 slots) a sixth of the keys sat past their first
+    // slot and the probing loop those rows take made the kernel 6-18 x slower (SUM + COUNT over 16-byte rows: 2.2 ms
+    // with 128 groups, 13.8 / 24.8 / 40.8 ms with 160 / 192 / 256); with 16 the same 160 groups take 2.25 ms.  A
+    // straight-line second probe did not help.  `lane_acc_kb` caps the bytes of the copies (experiments; 0 = no cap).
+    const size_t lane_cap = (size_t)(lane_acc_kb > 0 ? lane_acc_kb : 200) << 10;
+    g.slmax32 = (int)std::min<size_t>(1024, lane_cap / ((size_t)g.nwords * 8u * 32u));
+    for (; g.slmax32 >= 16; g.slmax32--) {
+        g.scslots32 = 64;
+        while (g.scslots32 < 16 * g.slmax32) g.scslots32 *= 2;
+        if (g.shared_smem32() <= (208u << 10)) break;
+    }
+    if (g.slmax32 < 16) { g.slmax32 = 0; g.scslots32 = 64; }
     // register variant: per group two 32-bit registers (first row, rows) + two per further word; ~96 registers
     // of accumulators leave room for the row and the expression temporaries under the 152 a 416-thread CTA gets
     const int reg_per_group = 2 + 2 * (g.nwords - 1);
@@ -657,12 +676,15 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     if (is_group) {
         // GroupByAggregationOperator.open (M/operator/GroupByAggregationOperator.kt:21-48): key = the first
         // NKEYS values of the row, accumulator i takes value NKEYS + i, nulls are skipped
-        GroupPlan gp = plan_groupby(bp, shape.gthreads);
+        GroupPlan gp = plan_groupby(bp, shape.gthreads, shape.lane_acc_kb);
         if (shape.rmax_hint > 0) gp.rmax = std::min(shape.rmax_hint, gp.rmax_regs);
         snprintf(b, sizeof b, "    static constexpr int NKEYS = %d, NWORDS = %d, LMAX = %d, CSLOTS = %d, GTHREADS = %d;\n", gp.nkeys > 0 ? gp.nkeys : 1,
                  gp.nwords, gp.lmax > 0 ? gp.lmax : 1, gp.cslots, gp.threads);
         s += b;
-        snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d;\n", gp.slmax > 0 ? gp.slmax : 64, gp.scslots);
+        if (shape.scopies == 32)
+            snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = 32;\n", gp.slmax32 > 0 ? gp.slmax32 : 32, gp.scslots32);
+        else
+            snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = 1;\n", gp.slmax > 0 ? gp.slmax : 64, gp.scslots);
         s += b;
         {
             int rcs = 64;
@@ -711,14 +733,14 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
             // register variant: called for every g in [0, RMAX), branch-free -- every update is a predicated
             // instruction or a select on (l == g).  (As `if (l == g) update` the compiler built a divergent switch:
             // every group met by the warp ran as its own branch, ~140 cycles per group and warp step.)
-            s += atomic ? "    static __device__ __forceinline__ void acc_atomic(qe_u64 *a, const Out &o, qe_u64 row) {\n"
+            s += atomic ? "    template <int AS> static __device__ __forceinline__ void acc_atomic(qe_u64 *a, const Out &o, qe_u64 row) {\n"
                : rfma ? "    static __device__ __forceinline__ void acc_regs_fma(qe_u32 &first, qe_u32 &rows, qe_u64 (&a)[NWORDS], const Out &o, qe_u32 row, int l, int g) {\n"
                : regs ? "    static __device__ __forceinline__ void acc_regs(qe_u32 &first, qe_u32 &rows, qe_u64 (&a)[NWORDS], const Out &o, qe_u32 row, int l, int g) {\n"
                         : "    static __device__ __forceinline__ void acc_private(qe_u64 *a, const Out &o, qe_u64 row) {\n"
                           "        constexpr size_t WS = (size_t)LMAX * GTHREADS;\n";
             auto at = [&](int w) {
                 char a[48];
-                if (atomic) snprintf(a, sizeof a, "a + %d", w);
+                if (atomic) snprintf(a, sizeof a, "a + %d * AS", w);
                 else if (regs) snprintf(a, sizeof a, "a[%d]", w);
                 else snprintf(a, sizeof a, "a[%d * WS]", w);
                 return std::string(a);
@@ -827,7 +849,7 @@ const char *jit_entry_name(KernelMode mode, const TileShape &shape)
     case KM_PROJECT: return shape.pring ? "qe_project_ring_kernel" : "qe_project_kernel";
     case KM_AGG: return "qe_agg_kernel";
     case KM_GROUPBY_PRIVATE: return "qe_groupby_private_kernel";
-    case KM_GROUPBY_SHARED: return "qe_groupby_shared_kernel";
+    case KM_GROUPBY_SHARED: return shape.scopies == 32 ? "qe_groupby_lane_kernel" : "qe_groupby_shared_kernel";
     case KM_GROUPBY_REG: return "qe_groupby_reg_kernel";
     default: return "qe_groupby_atomic_kernel";
     }

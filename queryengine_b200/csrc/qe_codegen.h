@@ -33,10 +33,12 @@ struct GroupPlan {
     size_t private_smem() const { return (size_t)nwords * (size_t)lmax * (size_t)threads * 8u; }
     int slmax = 0, scslots = 0;            // shared variant: groups per CTA (one copy of the words), key-cache slots
     size_t shared_smem() const;            // accumulators + key cache, all dynamic
+    int slmax32 = 0, scslots32 = 0;        // the same with one copy of the words per LANE (32 per CTA): contention / 32
+    size_t shared_smem32() const;
     int rmax = 0;                          // register variant: groups per CTA whose accumulators every thread keeps in registers (0: not applicable)
     int rmax_regs = 0;                     // ... by the register budget alone, without the cost rule
 };
-GroupPlan plan_groupby(const BoundPipeline &bp, int threads = 256);
+GroupPlan plan_groupby(const BoundPipeline &bp, int threads = 256, int lane_acc_kb = 0);
 
 struct TileShape {
     int steps = 2;          // steps per warp per tile
@@ -59,6 +61,8 @@ struct TileShape {
     bool greg = false;
     // dense projection through the same ring of stages (qe_project_ring_body): one producer warp + ncw consumer warps
     bool pring = false;
+    int lane_acc_kb = 0;    // group-by, lane copies: cap on the KB of the copies (0 = none, see plan_groupby)
+    int scopies = 1;        // group-by, CTA-shared variant: copies of the accumulator words per CTA (1, or 32 = one per lane)
     int rmax_hint = 0;      // register variant: compile for this many groups instead of the plan's maximum (0: the maximum)
 
     int rows_per_tile() const { return (ring || greg || pring) ? tile_rows : (gthreads / 32) * steps * 32 * vec; }

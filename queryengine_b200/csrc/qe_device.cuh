@@ -1717,7 +1717,7 @@ __device__ __forceinline__ void qe_agg_body(const QeParams &p)
 //   static qe_u64 word_init(int w);  static int word_kind(int w);
 //   static constexpr int GTHREADS;                                 private variant: threads per CTA (256 or 512)
 //   static void acc_private(qe_u64 *a, const Out&, qe_u64 row);    word w of this thread's copy at a[w * LMAX * GTHREADS]
-//   static void acc_atomic(qe_u64 *a, const Out&, qe_u64 row);     word w at a[w]
+//   template <int AS> static void acc_atomic(qe_u64 *a, const Out&, qe_u64 row);     word w at a[w * AS]
 #define QE_GK_ADD_F64 0
 #define QE_GK_ADD_I64 1
 #define QE_GK_MIN_F64 2
@@ -2193,15 +2193,19 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
     constexpr int GT = P::GTHREADS, GW = GT / 32;
     constexpr int WARP_ROWS = STEPS * 32 * VEC;
     constexpr int TILE = GW * WARP_ROWS;
+    // COPIES = 32 ("lane" kernel): one copy of the words per LANE index, shared by the lanes of that index in all
+    // warps ([group][word][lane]: lane-consecutive, conflict-free).  The same atomics, but two threads meet on a
+    // word only when they have the same lane AND the same group: the CAS loops of the f64 words hardly ever retry.
+    constexpr int COPIES = P::SCOPIES;
     typedef QeGroupCache<NKEYS, CS, LMAX> Cache;
     extern __shared__ __align__(16) unsigned char qe_gsmem[];
-    qe_u64 *s_acc = (qe_u64 *)qe_gsmem;                       // [LMAX][NWORDS]
-    Cache &gc = *(Cache *)(qe_gsmem + (size_t)LMAX * NWORDS * 8);
+    qe_u64 *s_acc = (qe_u64 *)qe_gsmem;                       // [LMAX][NWORDS][COPIES]
+    Cache &gc = *(Cache *)(qe_gsmem + (size_t)LMAX * NWORDS * COPIES * 8);
     const qe_u32 warp = qe_warp(), lane = qe_lane(), tid = threadIdx.x;
 
     for (int i = (int)tid; i < CS; i += GT) gc.state[i] = 0u;
     if (tid == 0) { gc.nlocal = 0u; gc.over = 0u; }
-    for (int i = (int)tid; i < LMAX * NWORDS; i += GT) s_acc[i] = P::word_init(i % NWORDS);
+    for (int i = (int)tid; i < LMAX * NWORDS * COPIES; i += GT) s_acc[i] = P::word_init((i / COPIES) % NWORDS);
     __syncthreads();
 
     typename P::Row rows[STEPS][VEC];
@@ -2262,7 +2266,7 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
                 const int l = lg[s][j];
                 if (l >= 0) {
                     const qe_u64 row = (qe_u64)p.sel_base + (qe_u64)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j);
-                    P::acc_atomic(s_acc + (size_t)l * NWORDS, outs[s][j], row);
+                    P::template acc_atomic<COPIES>(s_acc + (size_t)l * NWORDS * COPIES + (COPIES > 1 ? lane : 0u), outs[s][j], row);
                 }
             }
         }
@@ -2273,7 +2277,14 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
     }
     __syncthreads();
     const int nlocal = (int)(gc.nlocal < (qe_u32)LMAX ? gc.nlocal : (qe_u32)LMAX);
-    for (int i = (int)tid; i < nlocal * NWORDS; i += GT) p.g_part[(size_t)blockIdx.x * LMAX * NWORDS + i] = s_acc[i];
+    for (int i = (int)tid; i < nlocal * NWORDS; i += GT) {
+        qe_u64 v = s_acc[(size_t)i * COPIES];
+        if (COPIES > 1) {                                     // the lane copies in lane order
+            const int kind = P::word_kind(i % NWORDS);
+            for (int c = 1; c < COPIES; c++) v = qe_group_combine(kind, v, s_acc[(size_t)i * COPIES + c]);
+        }
+        p.g_part[(size_t)blockIdx.x * LMAX * NWORDS + i] = v;
+    }
     qe_u32 *ps = p.g_part_slot + (size_t)blockIdx.x * (1 + LMAX);
     if (tid == 0) {
         ps[0] = (qe_u32)nlocal;
@@ -2305,7 +2316,7 @@ __device__ __forceinline__ void qe_groupby_atomic_body(const QeParams &p)
                 const int gs = qe_group_global_slot<NKEYS>(p, k, nulls, qe_group_hash<NKEYS>(k, nulls));
                 if (gs >= 0) {
                     const qe_u64 row = (qe_u64)p.sel_base + (qe_u64)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j);
-                    P::acc_atomic(p.g_acc + (size_t)gs * NWORDS, outs[s][j], row);
+                    P::template acc_atomic<1>(p.g_acc + (size_t)gs * NWORDS, outs[s][j], row);
                 }
             }
         }

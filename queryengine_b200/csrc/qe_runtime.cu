@@ -134,7 +134,7 @@ struct qe_ctx {
     Pool pool;
     std::unordered_map<std::string, JitEntry> jit_cache;
     // options
-    int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = -1, opt_stages = 0, opt_debug_flags = 0, opt_pipeline = 1, opt_groupby_registers = 1;
+    int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = -1, opt_stages = 0, opt_debug_flags = 0, opt_pipeline = 1, opt_groupby_registers = 1, opt_groupby_lanes = 1, opt_lane_acc_kb = 0;
     int64_t opt_min_blocks = 0;
     int64_t opt_nlb = 0, opt_loads = 0, opt_tile_rows = 0, opt_ncw = 0, opt_defer = 0, opt_stage_kb = 0;
     int64_t launches = 0;
@@ -264,6 +264,11 @@ extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
         ctx->opt_min_blocks = value;
     } else if (k == "pipeline") {
         ctx->opt_pipeline = value != 0;
+    } else if (k == "lane_acc_kb") {
+        if (value < 0 || value > 200) return fail(QE_ERR_INVALID_ARGUMENT, "lane_acc_kb must be in [0, 200] (0 = no cap)");
+        ctx->opt_lane_acc_kb = value;
+    } else if (k == "groupby_lanes") {
+        ctx->opt_groupby_lanes = value != 0;                 // 0: skip the lane-copies variant (32 copies per CTA)
     } else if (k == "groupby_registers") {
         if (value < 0 || value > 2) return fail(QE_ERR_INVALID_ARGUMENT, "groupby_registers must be 0 (off), 1 (by the cost rule) or 2 (whenever the registers suffice)");
         ctx->opt_groupby_registers = value;                  // 0: group-by starts with the private (shared-memory) variant
@@ -526,7 +531,7 @@ struct qe_result {
     DevBuf g_state, g_keys, g_nulls, g_acc, g_ctl, g_part, g_part_slot, g_records;
     std::vector<std::vector<uint8_t>> h_values, h_valid;    // per output column: values in the column's layout, Arrow bitmap
     int64_t h_rows = 0;
-    int g_nkeys = 0, g_variant = 0, g_threads = 0;          // variant: 0 private accumulators, 1 global atomics, 2 CTA-shared, 3 registers
+    int g_nkeys = 0, g_variant = 0, g_threads = 0;          // variant: 0 private accumulators, 1 global atomics, 2 CTA-shared, 3 registers, 4 lane copies
     std::string g_seen_sig;                                 // signature of the last group-by that completed into this result ...
     int g_seen_groups = 0;                                  // ... and how many groups it found (sizes the register variant next time)
     std::string g_overflowed;                               // signature of the group-by whose private variant overflowed here
@@ -755,7 +760,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     char suffix[128];
     snprintf(suffix, sizeof suffix, "|M%d|B%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d.%d|G%d", (int)mode, shape.min_blocks, shape.steps, shape.vec, shape.staged ? 1 : 0,
              shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0, shape.ring ? 1 : 0, shape.tile_rows, shape.ncw,
-             shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0) + (shape.pring ? 200000 : 0));
+             shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0) + (shape.pring ? 200000 : 0) + (shape.scopies == 32 ? 400000 + 1000000 * shape.lane_acc_kb : 0));
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) { *out = &it->second; return QE_OK; }
@@ -1157,7 +1162,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     if (rc) return fail(rc, err);
     // Variants, tried in this order until one holds every group a CTA meets: private accumulators with 512 threads
     // (16 warps per SM hide the shared-memory and HBM latencies; half as many groups fit), with 256 threads, atomics.
-    const qe::GroupPlan gp512 = qe::plan_groupby(bp, 512);
+    const qe::GroupPlan gp512 = qe::plan_groupby(bp, 512, (int)ctx->opt_lane_acc_kb);
     const qe::GroupPlan gp = qe::plan_groupby(bp, 256);
     if (gp.nwords > 48) return fail(QE_ERR_UNSUPPORTED, "too many accumulator words");
 
@@ -1240,9 +1245,10 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     uint32_t ctl[4] = {0, 0, 0, 0};
     // a result that is reused remembers which variants this group-by has overflowed
     const std::string sig = bp.signature();
-    // levels: 0 registers, 1 private 512 threads, 2 private 256 threads, 3 CTA-shared, 4 global atomics
+    // levels: 0 registers, 1 private 512 threads, 2 private 256 threads, 3 lane copies (32 per CTA), 4 CTA-shared (one
+    // copy), 5 global atomics
     int level = r->g_overflowed == sig ? r->g_level : 0;
-    if (d->flags & QE_GROUPBY_ATOMIC) level = 4;
+    if (d->flags & QE_GROUPBY_ATOMIC) level = 5;
     else if (d->flags & QE_GROUPBY_SHARED) level = std::max(level, 3);
     // register variant: every group's words are touched for every row, so compile for the group count the same
     // group-by found last time (a reused result remembers it); more groups than that -> once more with the maximum
@@ -1261,12 +1267,15 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
         }
         if (level == 1 && gp512.lmax < 2) continue;
         if (level == 2 && (gp.lmax < 1 || gp.lmax <= gp512.lmax)) continue;
-        if (level == 3 && gp512.slmax < 64) continue;
-        const bool atomic = level >= 4, shared = level == 3;
-        const qe::GroupPlan &plan = (level == 1 || level == 3) ? gp512 : gp;
+        if (level == 3 && (gp512.slmax32 < 16 || !ctx->opt_groupby_lanes)) continue;
+        if (level == 4 && gp512.slmax < 64) continue;
+        const bool atomic = level >= 5, shared = level == 3 || level == 4, lanes = level == 3;
+        const qe::GroupPlan &plan = (level == 1 || shared) ? gp512 : gp;
         const qe::KernelMode mode = regs ? qe::KM_GROUPBY_REG : atomic ? qe::KM_GROUPBY_ATOMIC : shared ? qe::KM_GROUPBY_SHARED : qe::KM_GROUPBY_PRIVATE;
-        const int part_groups = regs ? rmax_use : shared ? plan.slmax : plan.lmax;
+        const int part_groups = regs ? rmax_use : lanes ? plan.slmax32 : shared ? plan.slmax : plan.lmax;
         qe::TileShape shape = regs ? reg_shape : choose_shape(ctx, bp, mode);
+        shape.scopies = lanes ? 32 : 1;
+        shape.lane_acc_kb = (int)ctx->opt_lane_acc_kb;
         if (!atomic && !regs) {
             shape.gthreads = plan.threads;
             if (plan.threads == 512 && !ctx->opt_steps && !ctx->opt_vec) {      // measured best for 16- and 48-byte rows
@@ -1275,7 +1284,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
             }
         }
         JitEntry *jit = nullptr;
-        if ((rc = get_jit_kernel(ctx, bp, mode, shape, &jit, (atomic || regs) ? 0 : shared ? plan.shared_smem() : plan.private_smem()))) return rc;
+        if ((rc = get_jit_kernel(ctx, bp, mode, shape, &jit, (atomic || regs) ? 0 : lanes ? plan.shared_smem32() : shared ? plan.shared_smem() : plan.private_smem()))) return rc;
         const int64_t tile_rows = shape.rows_per_tile();
         const int64_t ntiles64 = (n + tile_rows - 1) / tile_rows;
         int blocks_per_sm = jit->kernel.blocks_per_sm;
@@ -1289,7 +1298,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
             p.g_part_slot = (qe_u32 *)r->g_part_slot.ptr;
         }
         r->mode = (int)mode;
-        r->g_variant = regs ? 3 : atomic ? 1 : shared ? 2 : 0;
+        r->g_variant = regs ? 3 : atomic ? 1 : lanes ? 4 : shared ? 2 : 0;
         const int threads = regs ? shape.block_threads() : atomic ? QE_BLOCK : plan.threads;
         r->g_threads = threads;
         QE_CUDA(qe::launch_groupby_init((uint32_t *)r->g_state.ptr, (uint64_t *)r->g_acc.ptr, (uint32_t *)r->g_ctl.ptr, nslots, gw, ctx->stream));
@@ -1804,14 +1813,14 @@ static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *co
     qe::BoundPipeline bp;
     int rc = qe::bind_pipeline(schema, has_filter ? &progs[0] : nullptr, proj, aggs, bp, err, group_keys);
     if (rc) return fail(rc, err);
-    const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : atomic == 2 ? qe::KM_GROUPBY_SHARED : atomic == 3 ? qe::KM_GROUPBY_REG : qe::KM_GROUPBY_PRIVATE)
+    const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : (atomic == 2 || atomic == 4) ? qe::KM_GROUPBY_SHARED : atomic == 3 ? qe::KM_GROUPBY_REG : qe::KM_GROUPBY_PRIVATE)
                               : !bp.agg_fns.empty() ? qe::KM_AGG : bp.has_filter ? qe::KM_FILTER : qe::KM_PROJECT;
     qe_ctx dummy;
     dummy.opt_steps = steps;
     dummy.opt_vec = vec;
     dummy.opt_staging = staging;
     qe::TileShape shape = choose_shape(&dummy, bp, mode);
-    if (mode == qe::KM_GROUPBY_SHARED) { shape.gthreads = 512; shape.steps = 1; shape.vec = qe::jit_wide_loads_supported() ? 4 : 2; }
+    if (mode == qe::KM_GROUPBY_SHARED) { shape.gthreads = 512; shape.steps = 1; shape.vec = qe::jit_wide_loads_supported() ? 4 : 2; shape.scopies = atomic == 4 ? 32 : 1; }
     const std::string src = qe::generate_source(bp, mode, shape);
     if (src_buf && src_cap) {
         const size_t n = std::min(src_cap - 1, src.size());

@@ -101,9 +101,10 @@ def _check_against_oracle(ctx, rows, keys, inputs, fns, filter_, atomic, expect_
     pipe = GroupByPipeline(t, filter_, keys, inputs, fns, atomic=atomic, shared=shared, max_groups=max_groups)
     res = pipe.run()
     if expect_variant is not None:
-        assert capi.lib().qe_result_group_variant(res.handle) == expect_variant
+        allowed = expect_variant if isinstance(expect_variant, tuple) else (expect_variant,)
+        assert capi.lib().qe_result_group_variant(res.handle) in allowed
     elif atomic or shared:
-        assert capi.lib().qe_result_group_variant(res.handle) == (1 if atomic else 2)
+        assert capi.lib().qe_result_group_variant(res.handle) in ((1,) if atomic else (2, 4))
     op = GpuGroupByOperator(t, filter_, list(keys) + [agg(f, e) for f, e in zip(fns, inputs)], atomic=atomic, shared=shared, max_groups=max_groups)
     got = op.map()
     if not rows:
@@ -199,17 +200,36 @@ def test_many_groups_fall_back_to_atomics_and_capacity_is_checked(ctx):
     k, x = col(2), col(3)
     # 5000 groups: no private variant holds them; a CTA of this small table meets only a few hundred, so the
     # CTA-shared variant takes over (a CTA that met more than its shared memory holds would fall back to atomics)
-    got = _check_against_oracle(ctx, rows, [k], [x, x], [A.SUM, A.COUNT], None, False, expect_variant=2)
+    got = _check_against_oracle(ctx, rows, [k], [x, x], [A.SUM, A.COUNT], None, False, expect_variant=(2, 4))
     assert len(got) == len({r[2] for r in rows})
     # ~1000 groups: more than the private copies hold, one shared-memory copy per CTA takes them
     rows1k = [[r[0], r[1], float(int(r[2]) % 1000), r[3], r[4]] for r in rows]
-    got = _check_against_oracle(ctx, rows1k, [k], [x, x, x], [A.SUM, A.COUNT, A.MIN], None, False, expect_variant=2)
+    got = _check_against_oracle(ctx, rows1k, [k], [x, x, x], [A.SUM, A.COUNT, A.MIN], None, False, expect_variant=(2, 4))
     assert len(got) == 1000
     t = _gpu_table(ctx, FIELDS, rows)
     with pytest.raises(capi.QeError) as e:
         GroupByPipeline(t, None, [k], [x], [A.SUM], max_groups=1000).run()
     assert "max_groups" in str(e.value)
     t.close()
+
+
+@pytest.mark.parametrize("ngroups", [30, 60])
+def test_lane_copies_variant_for_tens_to_hundreds_of_groups(ctx, ngroups):
+    # more groups than the thread-private copies hold, few enough for one copy per lane index (variant 4); then the same
+    # query with that variant switched off (one copy per CTA, variant 2): same groups, same order
+    rng = np.random.default_rng(50 + ngroups)
+    n = 40000
+    rows = [[("s%d" % int(rng.integers(3))) if rng.random() > 0.05 else None, None, float(int(rng.integers(ngroups // 3))),
+             float(np.round(rng.uniform(-10, 10), 1)), None if rng.random() < 0.2 else float(rng.uniform(-1e3, 1e3))] for _ in range(n)]
+    s, k, x, y = col(0, S), col(2), col(3), col(4)
+    # three words per group (first row | rows, sum of x, count of y): up to 85 groups within the 64 KB of lane copies
+    got = _check_against_oracle(ctx, rows, [s, k], [x, y, x], [A.SUM, A.COUNT, A.AVG], None, False, expect_variant=4)
+    ctx.set_option("groupby_lanes", 0)
+    try:
+        got2 = _check_against_oracle(ctx, rows, [s, k], [x, y, x], [A.SUM, A.COUNT, A.AVG], None, False, expect_variant=2)
+    finally:
+        ctx.set_option("groupby_lanes", 1)
+    assert [g[:2] for g in got] == [g[:2] for g in got2]
 
 
 @pytest.mark.parametrize("registers", [1, 0])
