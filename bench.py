@@ -374,6 +374,41 @@ def extra_q1(ctx, rows, steps, warmup, peak):
     return out
 
 
+def extra_f64_column(ctx, rows, steps, warmup, peak):
+    """configs[1] with the column held as f64 -- the reference's own numeric type (M/data/Schema.kt:3-5):
+    the same values, the same `col < k` sweep, selection vector + compacted f64 column."""
+    from queryengine_b200 import capi
+    from queryengine_b200.ast import DataType, Function, col, fn
+    from queryengine_b200.engine import ColumnarTable, Field, Pipeline
+    D = DataType.DOUBLE
+    t = ColumnarTable(ctx, [Field("col", D, False)], rows)
+    t.generate(0, capi.QE_GEN_UNIFORM_U40, SEED)
+    out = {"rows": rows, "per_selectivity": []}
+    tot_ms = tot_bytes = 0.0
+    for s_ in (0.01, 0.5, 0.99):
+        pipe = Pipeline(t, fn(Function.CMP_LT, col(0, D, "col"), float(int(s_ * 2 ** 40))), [col(0, D, "col")])
+        res = pipe.run()
+        for _ in range(warmup):
+            pipe.run(res)
+        ms0, runs0 = res.kernel_stats()
+        for _ in range(steps):
+            pipe.run(res)
+        ms1, runs1 = res.kernel_stats()
+        kms = (ms1 - ms0) / max(1, runs1 - runs0)
+        kept = res.num_rows
+        nbytes = 8.0 * rows + 12.0 * kept
+        out["per_selectivity"].append({"selectivity": s_, "kept": kept, "kernel_ms": kms, "gb_per_s": nbytes / (kms * 1e-3) / 1e9,
+                                       "frac_of_peak": nbytes / (kms * 1e-3) / 1e9 / peak})
+        tot_ms += kms
+        tot_bytes += nbytes
+        res.close()
+    out["rows_per_s"] = 3 * rows / (tot_ms * 1e-3)
+    out["gb_per_s"] = tot_bytes / (tot_ms * 1e-3) / 1e9
+    out["frac_of_peak"] = out["gb_per_s"] / peak
+    t.close()
+    return out
+
+
 def extra_tree(ctx, torch, stream, rows, steps, warmup, peak):
     """BASELINE.json configs[3]: nullable f64 arithmetic tree (depth 8) with validity bitmaps, dense projection."""
     from queryengine_b200 import capi
@@ -504,6 +539,10 @@ def run_ours(args):
                 extra[name] = fn_(ctx, torch, stream, n, max(3, args.steps), 3, peak)
             except Exception as e:  # reported, never hidden
                 extra[name] = {"error": repr(e)}
+        try:      # configs[1] with the column held as f64, the reference's own type
+            extra["single_f64_column_1e9"] = extra_f64_column(ctx, args.rows, max(3, args.steps), 3, peak)
+        except Exception as e:
+            extra["single_f64_column_1e9"] = {"error": repr(e)}
         try:      # configs[4] on one partition (SF1000 / 6: what one of 6 GPUs would hold)
             extra["lineitem_filter_2proj_1e9"] = extra_sf_filter(ctx, args.sf_rows, max(3, args.steps), 3, peak)
         except Exception as e:

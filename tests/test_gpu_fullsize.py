@@ -66,23 +66,27 @@ def _bits(torch, ptr, row0, n):
     return ((by[:, None] >> sh[None, :]) & 1).bool().reshape(-1)[:n]
 
 
-def test_config_b_single_column_filter_1e9(ctx, torch_mod):
-    """configs[1]: one int64 column, 10^9 rows, `col < k` at 1 / 50 / 99 %: selection vector and compacted column."""
+@pytest.mark.parametrize("held_as", ["int64", "f64"])
+def test_config_b_single_column_filter_1e9(ctx, torch_mod, held_as):
+    """configs[1]: one column, 10^9 rows, `col < k` at 1 / 50 / 99 %: selection vector and compacted column.  The column is
+    held as int64 (BASELINE.json) and as f64, the reference's own numeric type: same values."""
     torch = torch_mod
     n = 1_000_000_000
-    t = ColumnarTable(ctx, [Field("col", I, False)], n)
+    ctype = I if held_as == "int64" else DataType.DOUBLE
+    t = ColumnarTable(ctx, [Field("col", ctype, False)], n)
     t.generate(0, capi.QE_GEN_UNIFORM_U40, 42)
     ctx.synchronize()
-    column = dev(torch, t.device_ptr(0, 0), n, "<i8")
-    total = int(column.sum())                                              # int64 wrap-around sum
+    column = dev(torch, t.device_ptr(0, 0), n, "<i8" if held_as == "int64" else "<f8")
+    bits = column.view(torch.int64)
+    total = int(bits.sum())                                                # int64 wrap-around sum of the value bits
     for s in (0.01, 0.5, 0.99):
         k = int(s * 2 ** 40)
-        res = Pipeline(t, fn(Function.CMP_LT, col(0, I), float(k)), [col(0, I)]).run()
+        res = Pipeline(t, fn(Function.CMP_LT, col(0, ctype), float(k)), [col(0, ctype)]).run()
         m = res.num_rows
         assert res.used_jit and abs(m / n - s) < 1e-4
         ctx.synchronize()
         sel = dev(torch, res.device_ptr(0, 2), m, "<i4")                   # row ids < 2^31
-        vals = dev(torch, res.device_ptr(0, 0), m, "<i8")
+        vals = dev(torch, res.device_ptr(0, 0), m, "<i8")                  # value bits
         # the independent restatement, chunk by chunk: nonzero(col < k) and col[those rows]
         done = 0
         for r0 in range(0, n, CHUNK):
@@ -90,19 +94,19 @@ def test_config_b_single_column_filter_1e9(ctx, torch_mod):
             idx = torch.nonzero(c < k).reshape(-1)
             got = sel[done:done + idx.numel()]
             assert got.numel() == idx.numel() and bool((got.long() == idx + r0).all())
-            assert bool((vals[done:done + idx.numel()] == c[idx]).all())
+            assert bool((vals[done:done + idx.numel()] == bits[r0:r0 + CHUNK][idx]).all())
             done += idx.numel()
             del idx, got
         assert done == m
         # size-independent properties
         assert bool((sel[1:] > sel[:-1]).all())                            # ascending, unique
-        assert bool((vals < k).all())
-        res2 = Pipeline(t, fn(Function.CMP_GE, col(0, I), float(k)), [col(0, I)]).run()
+        assert bool((vals.view(column.dtype) < k).all())
+        res2 = Pipeline(t, fn(Function.CMP_GE, col(0, ctype), float(k)), [col(0, ctype)]).run()
         m2 = res2.num_rows
         ctx.synchronize()
         assert m + m2 == n                                                 # complement keeps exactly the rest
         vals2 = dev(torch, res2.device_ptr(0, 0), m2, "<i8")
-        assert int(vals.sum()) + int(vals2.sum()) - total in (0, 2 ** 64, -2 ** 64)   # checksum of checksums
+        assert (int(vals.sum()) + int(vals2.sum()) - total) % 2 ** 64 == 0   # checksum of checksums
         torch.cuda.synchronize()
         res.close()
         res2.close()
