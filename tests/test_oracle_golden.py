@@ -221,3 +221,25 @@ def test_accumulators_spec():
     plan = OraclePlan(nan_t, [0], projections=[c, c], aggregates=[A.MIN, A.MAX])
     (mn, mx), = plan.rows()
     assert math.isnan(mn) and math.isnan(mx)          # Math.min/max propagate NaN
+
+
+def test_jdk_published_known_answers():
+    """The JLS / Javadoc examples for the primitives the reference delegates to the JDK (tests/jdk_vectors.py)."""
+    import jdk_vectors as J
+    D = DataType.DOUBLE
+    a, b = ColumnExpression("a", 0, D), ColumnExpression("b", 1, D)
+    for name, x, y, want in J.ARITHMETIC:
+        for mode in MODES:
+            got = compile_expression(FunctionExpression(Function[name], [a, b]), mode)([x, y])
+            assert J.same(got, want), (name, x, y, got, want, mode)
+    for name, x, y, want in J.COMPARISONS:
+        modes = MODES if name in ("CMP_EQ", "CMP_NE") else (Mode.INTERPRETER, Mode.BYTECODE_COMPILER)   # ClosureCompiler is IEEE on <,<=,>=,>
+        for mode in modes:
+            got = compile_expression(FunctionExpression(Function[name], [a, b]), mode)([x, y])
+            assert got is want, (name, x, y, got, want, mode)
+    A = AggregationFunction
+    c = ColumnExpression("x", 0, D)
+    for values, mn, mx in J.MIN_MAX:
+        table = OracleTable.from_rows([D], [[v] for v in values])
+        (gmn, gmx), = OraclePlan(table, [0], projections=[c, c], aggregates=[A.MIN, A.MAX]).rows()
+        assert J.same(gmn, mn) and J.same(gmx, mx), (values, gmn, gmx)
