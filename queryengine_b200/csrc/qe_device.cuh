@@ -1912,6 +1912,11 @@ __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
             P::load(p, (qe_i64)blockIdx.x * TILE + (qe_i64)warp * WARP_ROWS + (qe_i64)s * 32 * VEC + lane * VEC, rows[s]);
     }
     for (qe_u32 tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+        // more groups than this variant holds, here or in another CTA: the run is discarded, stop reading
+        if (((const volatile qe_u32 &)gc.over) != 0u || (qe_ld_relaxed_u32(p.g_ctl + 1) & 1u)) {
+            if (((const volatile qe_u32 &)gc.over) != 0u && lane == 0) atomicOr(p.g_ctl + 1, 1u);
+            break;
+        }
         const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
         typename P::Row next[STEPS][VEC];
         // the column allocations are padded by whole tiles, but not by a whole grid of them: clamp
@@ -2215,6 +2220,11 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
             P::load(p, (qe_i64)blockIdx.x * TILE + (qe_i64)warp * WARP_ROWS + (qe_i64)s * 32 * VEC + lane * VEC, rows[s]);
     }
     for (qe_u32 tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+        // more groups than this variant holds, here or in another CTA: the run is discarded, stop reading
+        if (((const volatile qe_u32 &)gc.over) != 0u || (qe_ld_relaxed_u32(p.g_ctl + 1) & 1u)) {
+            if (((const volatile qe_u32 &)gc.over) != 0u && lane == 0) atomicOr(p.g_ctl + 1, 1u);
+            break;
+        }
         const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
         typename P::Row next[STEPS][VEC];
         const qe_u32 ntile = tile + gridDim.x < p.ntiles ? tile + gridDim.x : tile;
