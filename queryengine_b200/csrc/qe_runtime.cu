@@ -518,6 +518,8 @@ struct qe_result {
     bool used_jit = false;
     int64_t batch_rows = 0;
     int64_t capacity = 0;
+    std::string f_sig;                  // filter runs: signature of the last pipeline run into this result ...
+    double f_sel = -1.0;                // ... and the selectivity it measured (kept / rows; -1 unknown)
     std::vector<ResultColumn> cols;
     std::vector<int> agg_fns;
     DevBuf sel, ctl, partials, final_aggs, debug;
@@ -603,7 +605,7 @@ extern "C" int qe_result_destroy(qe_result *r)
 
 // ---------------------------------------------------------------- pipeline
 
-static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMode mode)
+static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMode mode, double sel_hint = -1.0)
 {
     // Aim for ~128 bytes of column data in flight per thread: enough 16/32-byte
     // requests outstanding to cover HBM latency at 8+ warps per scheduler,
@@ -650,7 +652,9 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         // consumer warps: 16, or 20 for a single 8-byte column -- at low selectivity that kernel is bound by
         // issue slots and latency, not by HBM (1 %: 1.45 ms with 16 warps, 1.31 with 20 or 24; 99 %: 2.98 / 3.00 /
         // 3.02); 40-byte rows lose with more warps (6.9 ms with 16, 7.7 with 24): profiles/r01_sweep_06_*.jsonl
-        s.ncw = ctx->opt_ncw ? (int)ctx->opt_ncw : (row_bytes <= 8 ? 20 : 16);
+        // ... unless the same pipeline kept more than 40 % of its rows the last time it ran into this result: from there
+        // on the kernel is bound by HBM and 16 warps are the faster shape (99 %: 2.98 against 3.00-3.04 ms)
+        s.ncw = ctx->opt_ncw ? (int)ctx->opt_ncw : ((row_bytes <= 8 && !(sel_hint > 0.4)) ? 20 : 16);
         const size_t quantum = (size_t)std::max(128, 32 * s.ncw);       // rows: whole warp steps, 16-byte bitmap runs
         const size_t stage_target = (size_t)(ctx->opt_stage_kb ? ctx->opt_stage_kb : 32) << 10;
         // One look-back per tile costs ~1500 cycles whatever the tile holds, so a tile must carry >= ~32 KB for
@@ -838,7 +842,16 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
     JitEntry *jit = nullptr;
     int blocks_per_sm = 1;
     if (use_jit) {
-        shape = choose_shape(ctx, bp, mode);
+        // a reused result knows the selectivity of its last run (waiting for that run is what a reuse does anyway)
+        double sel_hint = -1.0;
+        if (qe_result *prev = *result; prev && prev->ctx == ctx && mode == qe::KM_FILTER && prev->mode == (int)mode &&
+                                       !(d->flags & QE_RUN_APPEND) && prev->f_sig == bp.signature()) {
+            if (prev->pending) { QE_CUDA(cudaEventSynchronize(prev->ev_done)); prev->pending = false; }
+            if (prev->batch_rows > 0 && (int64_t)prev->host->count <= prev->capacity)
+                prev->f_sel = (double)prev->host->count / (double)prev->batch_rows;
+            sel_hint = prev->f_sel;
+        }
+        shape = choose_shape(ctx, bp, mode, sel_hint);
         // Dense projection: four CTAs per SM (64 registers) hide the latency of the FP64 divide / MOD sequences better
         // than three (measured on the nullable tree: 6.83 -> 6.34 ms); kept only when the tighter bound does not spill.
         if (mode == qe::KM_PROJECT && !ctx->opt_min_blocks && !shape.pring) {
@@ -895,6 +908,7 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
             return fail(QE_ERR_CAPACITY, "QE_RUN_APPEND: the first run's out_capacity_rows does not cover this batch");
     }
     r->mode = (int)mode;
+    if (mode == qe::KM_FILTER) { const std::string sg = bp.signature(); if (r->f_sig != sg) { r->f_sig = sg; r->f_sel = -1.0; } }
     r->used_jit = use_jit;
     r->batch_rows = emitted_before + n;
     r->agg_fns = bp.agg_fns;
