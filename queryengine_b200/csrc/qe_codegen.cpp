@@ -321,6 +321,12 @@ size_t GroupPlan::shared_smem32() const
     return (size_t)slmax32 * (size_t)nwords * 8u * 32u + (size_t)scslots32 * (8u * nk + 12u) + 4u * (size_t)slmax32 + 16u;
 }
 
+size_t GroupPlan::shared_smem8() const
+{
+    const size_t nk = nkeys > 0 ? (size_t)nkeys : 1;
+    return (size_t)slmax8 * (size_t)nwords * 8u * 8u + (size_t)scslots8 * (8u * nk + 12u) + 4u * (size_t)slmax8 + 16u;
+}
+
 GroupPlan plan_groupby(const BoundPipeline &bp, int threads, int lane_acc_kb)
 {
     GroupPlan g;
@@ -396,6 +402,12 @@ GroupPlan plan_groupby(const BoundPipeline &bp, int threads, int lane_acc_kb)
         if (g.shared_smem32() <= (208u << 10)) break;
     }
     if (g.slmax32 < 16) { g.slmax32 = 0; g.scslots32 = 64; }
+    for (g.slmax8 = 2048; g.slmax8 >= 64; g.slmax8--) {
+        g.scslots8 = 64;
+        while (g.scslots8 < 16 * g.slmax8) g.scslots8 *= 2;
+        if (g.shared_smem8() <= (208u << 10)) break;
+    }
+    if (g.slmax8 < 64 || g.slmax8 <= g.slmax32) { g.slmax8 = 0; g.scslots8 = 64; }
     // register variant: per group two 32-bit registers (first row, rows) + two per further word; ~96 registers
     // of accumulators leave room for the row and the expression temporaries under the 152 a 416-thread CTA gets
     const int reg_per_group = 2 + 2 * (g.nwords - 1);
@@ -683,6 +695,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         s += b;
         if (shape.scopies == 32)
             snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = 32;\n", gp.slmax32 > 0 ? gp.slmax32 : 32, gp.scslots32);
+        else if (shape.scopies == 8)
+            snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = 8;\n", gp.slmax8 > 0 ? gp.slmax8 : 64, gp.scslots8);
         else
             snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = 1;\n", gp.slmax > 0 ? gp.slmax : 64, gp.scslots);
         s += b;
@@ -849,7 +863,7 @@ const char *jit_entry_name(KernelMode mode, const TileShape &shape)
     case KM_PROJECT: return shape.pring ? "qe_project_ring_kernel" : "qe_project_kernel";
     case KM_AGG: return "qe_agg_kernel";
     case KM_GROUPBY_PRIVATE: return "qe_groupby_private_kernel";
-    case KM_GROUPBY_SHARED: return shape.scopies == 32 ? "qe_groupby_lane_kernel" : "qe_groupby_shared_kernel";
+    case KM_GROUPBY_SHARED: return shape.scopies == 32 ? "qe_groupby_lane_kernel" : shape.scopies == 8 ? "qe_groupby_lane8_kernel" : "qe_groupby_shared_kernel";
     case KM_GROUPBY_REG: return "qe_groupby_reg_kernel";
     default: return "qe_groupby_atomic_kernel";
     }

@@ -1912,11 +1912,6 @@ __device__ __forceinline__ void qe_groupby_private_body(const QeParams &p)
             P::load(p, (qe_i64)blockIdx.x * TILE + (qe_i64)warp * WARP_ROWS + (qe_i64)s * 32 * VEC + lane * VEC, rows[s]);
     }
     for (qe_u32 tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
-        // more groups than this variant holds, here or in another CTA: the run is discarded, stop reading
-        if (((const volatile qe_u32 &)gc.over) != 0u || (qe_ld_relaxed_u32(p.g_ctl + 1) & 1u)) {
-            if (((const volatile qe_u32 &)gc.over) != 0u && lane == 0) atomicOr(p.g_ctl + 1, 1u);
-            break;
-        }
         const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
         typename P::Row next[STEPS][VEC];
         // the column allocations are padded by whole tiles, but not by a whole grid of them: clamp
@@ -2198,6 +2193,7 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
     constexpr int GT = P::GTHREADS, GW = GT / 32;
     constexpr int WARP_ROWS = STEPS * 32 * VEC;
     constexpr int TILE = GW * WARP_ROWS;
+    // COPIES = 8: one copy per (lane & 7) -- four lanes of a warp and their peers in all warps share it; more groups fit.
     // COPIES = 32 ("lane" kernel): one copy of the words per LANE index, shared by the lanes of that index in all
     // warps ([group][word][lane]: lane-consecutive, conflict-free).  The same atomics, but two threads meet on a
     // word only when they have the same lane AND the same group: the CAS loops of the f64 words hardly ever retry.
@@ -2219,9 +2215,13 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
         for (int s = 0; s < STEPS; s++)
             P::load(p, (qe_i64)blockIdx.x * TILE + (qe_i64)warp * WARP_ROWS + (qe_i64)s * 32 * VEC + lane * VEC, rows[s]);
     }
+    qe_u32 over_poll = 0;
     for (qe_u32 tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
-        // more groups than this variant holds, here or in another CTA: the run is discarded, stop reading
-        if (((const volatile qe_u32 &)gc.over) != 0u || (qe_ld_relaxed_u32(p.g_ctl + 1) & 1u)) {
+        // more groups than this variant holds, here or in another CTA: the run is discarded, stop reading.  Looked at
+        // every 32nd tile only: the global flag is an L2 round trip in front of a tile of a few rows per thread (checked
+        // every tile it cost the lane-copies kernel 20 %: 2.2 -> 2.7 ms).
+        if ((++over_poll & 31u) == 0u &&
+            (((const volatile qe_u32 &)gc.over) != 0u || (qe_ld_relaxed_u32(p.g_ctl + 1) & 1u))) {
             if (((const volatile qe_u32 &)gc.over) != 0u && lane == 0) atomicOr(p.g_ctl + 1, 1u);
             break;
         }
@@ -2276,7 +2276,7 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
                 const int l = lg[s][j];
                 if (l >= 0) {
                     const qe_u64 row = (qe_u64)p.sel_base + (qe_u64)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j);
-                    P::template acc_atomic<COPIES>(s_acc + (size_t)l * NWORDS * COPIES + (COPIES > 1 ? lane : 0u), outs[s][j], row);
+                    P::template acc_atomic<COPIES>(s_acc + (size_t)l * NWORDS * COPIES + (lane & (qe_u32)(COPIES - 1)), outs[s][j], row);
                 }
             }
         }

@@ -533,7 +533,7 @@ struct qe_result {
     DevBuf g_state, g_keys, g_nulls, g_acc, g_ctl, g_part, g_part_slot, g_records;
     std::vector<std::vector<uint8_t>> h_values, h_valid;    // per output column: values in the column's layout, Arrow bitmap
     int64_t h_rows = 0;
-    int g_nkeys = 0, g_variant = 0, g_threads = 0;          // variant: 0 private accumulators, 1 global atomics, 2 CTA-shared, 3 registers, 4 lane copies
+    int g_nkeys = 0, g_variant = 0, g_threads = 0;          // variant: 0 private accumulators, 1 global atomics, 2 CTA-shared, 3 registers, 4 lane copies, 5 eight copies
     std::string g_seen_sig;                                 // signature of the last group-by that completed into this result ...
     int g_seen_groups = 0;                                  // ... and how many groups it found (sizes the register variant next time)
     std::string g_overflowed;                               // signature of the group-by whose private variant overflowed here
@@ -764,7 +764,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     char suffix[128];
     snprintf(suffix, sizeof suffix, "|M%d|B%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d.%d|G%d", (int)mode, shape.min_blocks, shape.steps, shape.vec, shape.staged ? 1 : 0,
              shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0, shape.ring ? 1 : 0, shape.tile_rows, shape.ncw,
-             shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0) + (shape.pring ? 200000 : 0) + (shape.scopies == 32 ? 400000 + 1000000 * shape.lane_acc_kb : 0));
+             shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0) + (shape.pring ? 200000 : 0) + (shape.scopies == 32 ? 400000 + 1000000 * shape.lane_acc_kb : shape.scopies == 8 ? 800000 : 0));
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) { *out = &it->second; return QE_OK; }
@@ -1259,10 +1259,10 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     uint32_t ctl[4] = {0, 0, 0, 0};
     // a result that is reused remembers which variants this group-by has overflowed
     const std::string sig = bp.signature();
-    // levels: 0 registers, 1 private 512 threads, 2 private 256 threads, 3 lane copies (32 per CTA), 4 CTA-shared (one
-    // copy), 5 global atomics
+    // levels: 0 registers, 1 private 512 threads, 2 private 256 threads, 3 lane copies (32 per CTA), 4 eight copies,
+    // 5 CTA-shared (one copy), 6 global atomics
     int level = r->g_overflowed == sig ? r->g_level : 0;
-    if (d->flags & QE_GROUPBY_ATOMIC) level = 5;
+    if (d->flags & QE_GROUPBY_ATOMIC) level = 6;
     else if (d->flags & QE_GROUPBY_SHARED) level = std::max(level, 3);
     // register variant: every group's words are touched for every row, so compile for the group count the same
     // group-by found last time (a reused result remembers it); more groups than that -> once more with the maximum
@@ -1285,13 +1285,14 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
         // rows: 2.2 ms against 2.5 ms at 32-48 groups) and hold more groups
         if (level == 2 && gp.nwords <= 3 && ctx->opt_groupby_lanes && gp512.slmax32 >= gp.lmax) continue;
         if (level == 3 && (gp512.slmax32 < 16 || !ctx->opt_groupby_lanes)) continue;
-        if (level == 4 && gp512.slmax < 64) continue;
-        const bool atomic = level >= 5, shared = level == 3 || level == 4, lanes = level == 3;
+        if (level == 4 && (gp512.slmax8 < 64 || !ctx->opt_groupby_lanes)) continue;
+        if (level == 5 && gp512.slmax < 64) continue;
+        const bool atomic = level >= 6, shared = level >= 3 && level <= 5, lanes = level == 3, lanes8 = level == 4;
         const qe::GroupPlan &plan = (level == 1 || shared) ? gp512 : gp;
         const qe::KernelMode mode = regs ? qe::KM_GROUPBY_REG : atomic ? qe::KM_GROUPBY_ATOMIC : shared ? qe::KM_GROUPBY_SHARED : qe::KM_GROUPBY_PRIVATE;
-        const int part_groups = regs ? rmax_use : lanes ? plan.slmax32 : shared ? plan.slmax : plan.lmax;
+        const int part_groups = regs ? rmax_use : lanes ? plan.slmax32 : lanes8 ? plan.slmax8 : shared ? plan.slmax : plan.lmax;
         qe::TileShape shape = regs ? reg_shape : choose_shape(ctx, bp, mode);
-        shape.scopies = lanes ? 32 : 1;
+        shape.scopies = lanes ? 32 : lanes8 ? 8 : 1;
         shape.lane_acc_kb = (int)ctx->opt_lane_acc_kb;
         if (!atomic && !regs) {
             shape.gthreads = plan.threads;
@@ -1301,7 +1302,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
             }
         }
         JitEntry *jit = nullptr;
-        if ((rc = get_jit_kernel(ctx, bp, mode, shape, &jit, (atomic || regs) ? 0 : lanes ? plan.shared_smem32() : shared ? plan.shared_smem() : plan.private_smem()))) return rc;
+        if ((rc = get_jit_kernel(ctx, bp, mode, shape, &jit, (atomic || regs) ? 0 : lanes ? plan.shared_smem32() : lanes8 ? plan.shared_smem8() : shared ? plan.shared_smem() : plan.private_smem()))) return rc;
         const int64_t tile_rows = shape.rows_per_tile();
         const int64_t ntiles64 = (n + tile_rows - 1) / tile_rows;
         int blocks_per_sm = jit->kernel.blocks_per_sm;
@@ -1315,7 +1316,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
             p.g_part_slot = (qe_u32 *)r->g_part_slot.ptr;
         }
         r->mode = (int)mode;
-        r->g_variant = regs ? 3 : atomic ? 1 : lanes ? 4 : shared ? 2 : 0;
+        r->g_variant = regs ? 3 : atomic ? 1 : lanes ? 4 : lanes8 ? 5 : shared ? 2 : 0;
         const int threads = regs ? shape.block_threads() : atomic ? QE_BLOCK : plan.threads;
         r->g_threads = threads;
         QE_CUDA(qe::launch_groupby_init((uint32_t *)r->g_state.ptr, (uint64_t *)r->g_acc.ptr, (uint32_t *)r->g_ctl.ptr, nslots, gw, ctx->stream));
@@ -1830,14 +1831,14 @@ static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *co
     qe::BoundPipeline bp;
     int rc = qe::bind_pipeline(schema, has_filter ? &progs[0] : nullptr, proj, aggs, bp, err, group_keys);
     if (rc) return fail(rc, err);
-    const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : (atomic == 2 || atomic == 4) ? qe::KM_GROUPBY_SHARED : atomic == 3 ? qe::KM_GROUPBY_REG : qe::KM_GROUPBY_PRIVATE)
+    const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : (atomic == 2 || atomic == 4 || atomic == 5) ? qe::KM_GROUPBY_SHARED : atomic == 3 ? qe::KM_GROUPBY_REG : qe::KM_GROUPBY_PRIVATE)
                               : !bp.agg_fns.empty() ? qe::KM_AGG : bp.has_filter ? qe::KM_FILTER : qe::KM_PROJECT;
     qe_ctx dummy;
     dummy.opt_steps = steps;
     dummy.opt_vec = vec;
     dummy.opt_staging = staging;
     qe::TileShape shape = choose_shape(&dummy, bp, mode);
-    if (mode == qe::KM_GROUPBY_SHARED) { shape.gthreads = 512; shape.steps = 1; shape.vec = qe::jit_wide_loads_supported() ? 4 : 2; shape.scopies = atomic == 4 ? 32 : 1; }
+    if (mode == qe::KM_GROUPBY_SHARED) { shape.gthreads = 512; shape.steps = 1; shape.vec = qe::jit_wide_loads_supported() ? 4 : 2; shape.scopies = atomic == 4 ? 32 : atomic == 5 ? 8 : 1; }
     const std::string src = qe::generate_source(bp, mode, shape);
     if (src_buf && src_cap) {
         const size_t n = std::min(src_cap - 1, src.size());

@@ -104,7 +104,7 @@ def _check_against_oracle(ctx, rows, keys, inputs, fns, filter_, atomic, expect_
         allowed = expect_variant if isinstance(expect_variant, tuple) else (expect_variant,)
         assert capi.lib().qe_result_group_variant(res.handle) in allowed
     elif atomic or shared:
-        assert capi.lib().qe_result_group_variant(res.handle) in ((1,) if atomic else (2, 4))
+        assert capi.lib().qe_result_group_variant(res.handle) in ((1,) if atomic else (2, 4, 5))
     op = GpuGroupByOperator(t, filter_, list(keys) + [agg(f, e) for f, e in zip(fns, inputs)], atomic=atomic, shared=shared, max_groups=max_groups)
     got = op.map()
     if not rows:
@@ -193,6 +193,17 @@ def test_register_variant_with_nulls_and_non_finite_inputs(ctx, nrows):
                           expect_variant=3, fields=fields)
 
 
+def test_eight_copies_variant_for_hundreds_of_groups(ctx):
+    # more groups than the lane copies hold (85 with three words), few enough for eight copies per CTA (variant 5)
+    rng = np.random.default_rng(808)
+    n = 60000
+    rows = [[None, bool(rng.random() < 0.5) if rng.random() > 0.1 else None, float(int(rng.integers(60))),
+             float(np.round(rng.uniform(-10, 10), 1)), None if rng.random() < 0.2 else float(rng.uniform(-1e3, 1e3))] for _ in range(n)]
+    b, k, x, y = col(1, B), col(2), col(3), col(4)
+    got = _check_against_oracle(ctx, rows, [b, k], [x, y, x], [A.SUM, A.COUNT, A.AVG], None, False, expect_variant=5)
+    assert len(got) == len({(r[1], r[2]) for r in rows})
+
+
 def test_many_groups_fall_back_to_atomics_and_capacity_is_checked(ctx):
     rng = np.random.default_rng(3)
     n = 30000
@@ -200,11 +211,11 @@ def test_many_groups_fall_back_to_atomics_and_capacity_is_checked(ctx):
     k, x = col(2), col(3)
     # 5000 groups: no private variant holds them; a CTA of this small table meets only a few hundred, so the
     # CTA-shared variant takes over (a CTA that met more than its shared memory holds would fall back to atomics)
-    got = _check_against_oracle(ctx, rows, [k], [x, x], [A.SUM, A.COUNT], None, False, expect_variant=(2, 4))
+    got = _check_against_oracle(ctx, rows, [k], [x, x], [A.SUM, A.COUNT], None, False, expect_variant=(2, 4, 5))
     assert len(got) == len({r[2] for r in rows})
     # ~1000 groups: more than the private copies hold, one shared-memory copy per CTA takes them
     rows1k = [[r[0], r[1], float(int(r[2]) % 1000), r[3], r[4]] for r in rows]
-    got = _check_against_oracle(ctx, rows1k, [k], [x, x, x], [A.SUM, A.COUNT, A.MIN], None, False, expect_variant=(2, 4))
+    got = _check_against_oracle(ctx, rows1k, [k], [x, x, x], [A.SUM, A.COUNT, A.MIN], None, False, expect_variant=(2, 4, 5))
     assert len(got) == 1000
     t = _gpu_table(ctx, FIELDS, rows)
     with pytest.raises(capi.QeError) as e:

@@ -42,7 +42,7 @@ def timed(pipe, reps):
 for atomic in (False, True):
     t, pipe = bench.q1_pipeline(ctx, args.rows, atomic=atomic)
     ms, v, g = timed(pipe, args.reps)
-    print(json.dumps({"what": "q1", "rows": args.rows, "variant": ["private", "atomic", "shared", "registers", "lanes"][v], "groups": g[0], "threads": g[1], "kernel_ms": round(ms, 3),
+    print(json.dumps({"what": "q1", "rows": args.rows, "variant": ["private", "atomic", "shared", "registers", "lanes", "lanes8"][v], "groups": g[0], "threads": g[1], "kernel_ms": round(ms, 3),
                       "gb_per_s": round(args.rows * 48 / ms / 1e6, 1), "frac": round(args.rows * 48 / ms / 1e6 / peak, 3)}), flush=True)
     t.close()
 D = DataType.DOUBLE
@@ -52,6 +52,6 @@ for card in (int(c) for c in args.cards.split(",")):
     t.generate(0, capi.QE_GEN_UNIFORM_INT, 6, 0, card - 1)
     pipe = GroupByPipeline(t, None, [col(0)], [col(1), col(1)], [A.SUM, A.COUNT], max_groups=max(65536, 2 * card))
     ms, v, g = timed(pipe, args.reps)
-    print(json.dumps({"what": "sum_count_by_k", "cardinality": card, "variant": ["private", "atomic", "shared", "registers", "lanes"][v], "groups": g[0], "threads": g[1],
+    print(json.dumps({"what": "sum_count_by_k", "cardinality": card, "variant": ["private", "atomic", "shared", "registers", "lanes", "lanes8"][v], "groups": g[0], "threads": g[1],
                       "kernel_ms": round(ms, 3), "gb_per_s": round(args.rows * 16 / ms / 1e6, 1),
                       "frac": round(args.rows * 16 / ms / 1e6 / peak, 3)}), flush=True)
