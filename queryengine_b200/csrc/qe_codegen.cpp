@@ -409,7 +409,7 @@ GroupPlan plan_groupby(const BoundPipeline &bp, int threads, int lane_acc_kb)
     }
     if (g.slmax8 < 64 || g.slmax8 <= g.slmax32) { g.slmax8 = 0; g.scslots8 = 64; }
     // register variant: per group two 32-bit registers (first row, rows) + two per further word; ~96 registers
-    // of accumulators leave room for the row and the expression temporaries under the 152 a 416-thread CTA gets
+    // of accumulators leave room for the row and the expression temporaries under the 168 a 384-thread CTA (1 producer + 11 consumer warps) gets
     const int reg_per_group = 2 + 2 * (g.nwords - 1);
     g.rmax = std::min(16, 96 / reg_per_group);
     g.rmax_regs = g.rmax < 2 ? 0 : g.rmax;
