@@ -127,13 +127,20 @@ typedef struct qe_pipeline_desc {
     int64_t row_end;                   /* -1 = to the end of the table */
     int64_t out_capacity_rows;         /* rows the outputs may hold; 0 = worst case (all rows of this batch) */
     uint32_t flags;                    /* QE_RUN_* */
+    int64_t sel_offset;                /* added to the table row index in the selection vector (0 normally; a batch that
+                                          holds rows [g, g+n) of a larger table at rows [s, s+n) of this one passes g - s);
+                                          row + sel_offset must fit 32 bits */
 } qe_pipeline_desc;
 
 enum {
     QE_RUN_NO_SELECTION = 1u << 0,     /* do not materialise the selection vector */
     QE_RUN_INTERPRETER  = 1u << 1,     /* use the generic interpreter kernels instead of generated code */
-    QE_RUN_APPEND       = 1u << 2      /* *result holds earlier batches of the same pipeline: append this batch's rows
+    QE_RUN_APPEND       = 1u << 2,     /* *result holds earlier batches of the same pipeline: append this batch's rows
                                           (order preserved; capacity is the first run's out_capacity_rows) */
+    QE_RUN_NO_VALUES    = 1u << 3      /* filter pipelines: the selection vector is the whole output -- the projections are
+                                          neither evaluated nor written.  For callers that hold the table themselves
+                                          (the reference's MemoryTable is in host memory, M/data/MemoryTable.kt:7, and
+                                          FilterOperator returns the very row it was given, M/operator/FilterOperator.kt:20-22) */
 };
 
 /* ---- context: one CUDA device, one stream, a device memory pool ------------ */
@@ -152,6 +159,14 @@ QE_API void *qe_ctx_stream(qe_ctx *ctx);
 QE_API int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value);
 /* kernels launched by this context so far */
 QE_API int64_t qe_ctx_launch_count(const qe_ctx *ctx);
+/* give the device memory the context's pool holds but does not use back to the driver */
+QE_API int qe_ctx_trim(qe_ctx *ctx);
+
+/* Where compiled pipelines came from, process-wide (stands in for the compile-once-per-expression of
+ * M/evaluator/BytecodeCompiler.kt:134-175): lookups served from [0] memory, [1] the ahead-of-time table baked into
+ * the library, [2] the on-disk cache ($QE_CACHE_DIR, else $XDG_CACHE_HOME/qegpu, else $HOME/.cache/qegpu; "off"
+ * disables it), [3] compiled by NVRTC; [4] = milliseconds spent in NVRTC, [5] = entries of the ahead-of-time table. */
+QE_API int qe_jit_stats(double out[6]);
 
 /* pinned host memory for staging-free uploads / downloads */
 QE_API int qe_host_alloc(size_t bytes, void **out);
@@ -204,23 +219,54 @@ QE_API int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_pipel
 
 /* ---- streaming: host columns in, host results out, chunk by chunk -----------
  * Stands in for the same subtree when the table starts in host memory (the reference's MemoryTable
- * always does, M/data/MemoryTable.kt:7): uploads, kernels and downloads of neighbouring row-range
- * chunks overlap on three streams.  Host buffers should be pinned (qe_host_alloc) for the copies to
- * be asynchronous.  Returns when every copy has completed; the results also stay readable through
- * qe_result_* as after qe_pipeline_run.  Filter, projection and global-aggregation pipelines: an
- * aggregation treats every chunk as a partition and folds the chunks' partials in chunk order
- * (read it with qe_result_agg / qe_result_agg_partial). */
+ * always does, M/data/MemoryTable.kt:7) or is larger than the device (MemorySourceOperator scans a table of
+ * any size, M/operator/MemorySourceOperator.kt:18-36): uploads, kernels and downloads of neighbouring
+ * row-range chunks overlap on three streams.  Host buffers should be pinned (qe_host_alloc) for the copies
+ * to be asynchronous.  Returns when every copy has completed.
+ *
+ * Two modes:
+ *   resident (total_rows == 0)   `table` holds the whole table; chunk c is uploaded to its own rows and every
+ *       chunk appends to the same device-side result (QE_RUN_APPEND), which stays readable through qe_result_*
+ *       as after qe_pipeline_run.
+ *   bounded (total_rows > 0)     `table` is a window of table.nrows / chunk_rows (>= 2) chunk slots used round
+ *       robin; total_rows may exceed both the device memory and 2^32.  Every chunk writes into one of as many
+ *       output buffer sets (worst case: a chunk's rows each), which is downloaded to its place in the caller's
+ *       host buffers and reused.  Afterwards qe_result_num_rows / qe_result_agg* / qe_result_kernel_stats work
+ *       on results[q]; the rows themselves are in the host buffers only (qe_result_column: QE_ERR_STATE).
+ *       pipelines[q].out_capacity_rows = rows host_selection[q] / host_out_values[q] can hold (0 = total_rows);
+ *       QE_ERR_CAPACITY when a filter keeps more.
+ * Selection vectors hold global row indices; with QE_STREAM_CHUNK_RELATIVE (required beyond 2^32 rows) they
+ * hold the index inside the chunk, and chunk_kept says which output positions belong to which chunk:
+ * global row of output i = chunk * chunk_rows + sel[i] for chunk_kept[q][chunk-1] <= i < chunk_kept[q][chunk].
+ * Aggregations: every chunk contributes its super-tile partials to one list, folded in row order at the end --
+ * with chunk_rows a multiple of QE_AGG_SUPER_ROWS the result is bit-identical to one run over the resident
+ * table (read it with qe_result_agg / qe_result_agg_partial). */
+typedef struct qe_stream_gen {           /* synthetic source of one column, as qe_table_generate */
+    int32_t kind;                        /* QE_GEN_*, or -1: not generated */
+    uint64_t seed;
+    double p0, p1, null_rate;
+} qe_stream_gen;
 typedef struct qe_stream_desc {
     int64_t chunk_rows;                          /* rows per chunk, a multiple of 128; 0 = 32 Mi */
     const void *const *host_values;              /* [table columns] source of each column (as qe_table_upload), NULL entry = already resident */
     const uint8_t *const *host_validity;         /* [table columns] Arrow bitmaps, or NULL */
     int32_t npipelines;
-    const qe_pipeline_desc *pipelines;           /* row_begin / row_end / QE_RUN_APPEND are set by the library */
+    const qe_pipeline_desc *pipelines;           /* row_begin / row_end / sel_offset / QE_RUN_APPEND are set by the library */
     qe_result **results;                         /* [npipelines] in / out, as for qe_pipeline_run_ex */
     uint32_t *const *host_selection;             /* [npipelines] destination of the selection vectors; NULL or NULL entries = not wanted */
     void *const *const *host_out_values;         /* [npipelines][nproj] destinations of the output columns */
     uint8_t *const *const *host_out_validity;    /* [npipelines][nproj] destinations of the validity bitmaps, or NULL */
+    int64_t total_rows;                          /* 0: resident mode; > 0: bounded mode, rows of the whole (host) table */
+    uint32_t flags;                              /* QE_STREAM_* */
+    const qe_stream_gen *gen;                    /* [table columns] or NULL: columns generated on the device chunk by chunk
+                                                    from the global row index gen_row_offset + row (benchmarks of tables no
+                                                    host could hold) */
+    int64_t gen_row_offset;
+    int64_t *const *chunk_kept;                  /* [npipelines][chunks] out, or NULL: rows kept up to and including each chunk */
 } qe_stream_desc;
+enum {
+    QE_STREAM_CHUNK_RELATIVE = 1u << 0           /* selection vectors count from the first row of their chunk */
+};
 QE_API int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_desc *desc);
 
 /* ---- group-by: stands in for Scan -> [Filter] -> Projection -> GroupByAggregationOperator
@@ -279,6 +325,13 @@ QE_API int qe_result_selection(qe_result *result, uint32_t *dst);
 /* finish() of accumulator k (M/evaluator/Accumulators.kt:21-107); COUNT is returned as a double */
 QE_API int qe_result_agg(qe_result *result, int k, double *value, int *is_null);
 QE_API int qe_result_agg_partial(qe_result *result, int k, qe_agg_partial *out);
+/* The partials of aggregate k per super-tile of QE_AGG_SUPER_ROWS rows, in row order (at most `capacity` are written,
+ * *n receives how many there are).  A sum is formed in a fixed shape over the ROW INDEX -- rows of a 16 384-row
+ * sub-tile in a fixed order, 64 sub-tiles per super-tile in a fixed tree, super-tiles one by one in ascending order --
+ * so qe_agg_combine over the concatenated lists of all partitions gives the same bits for any number of partitions
+ * or streamed chunks whose boundaries are multiples of QE_AGG_SUPER_ROWS. */
+#define QE_AGG_SUPER_ROWS 1048576
+QE_API int qe_result_agg_partials(qe_result *result, int k, qe_agg_partial *dst, int64_t capacity, int64_t *n);
 /* device addresses of the result buffers: which = 0 values, 1 validity, 2 selection vector (k ignored) */
 QE_API void *qe_result_device_ptr(qe_result *result, int k, int which);
 /* device time of the main kernel of the last run that produced this result, in milliseconds */
@@ -293,6 +346,56 @@ QE_API int qe_result_destroy(qe_result *result);
 
 /* Combine per-partition partials in array order (deterministic) and finish. */
 QE_API int qe_agg_combine(int agg_fn, const qe_agg_partial *partials, int n, double *value, int *is_null);
+
+/* ---- several GPUs, one process ------------------------------------------------
+ * The reference is one process that builds one plan (M/Main.kt:11-19, M/evaluator/Planner.kt:30); a JVM adapter
+ * cannot call torch.distributed.  A qe_mgpu owns one context per device and one worker thread per context; a table is
+ * split into contiguous row ranges (partition boundaries are multiples of QE_AGG_SUPER_ROWS, so SUM / AVG do not depend
+ * on the number of devices), every call fans out to all devices at once and joins.  Filter / projection outputs stay
+ * on their device ("gathered per partition": concatenating the partitions in order is the reference's scan order,
+ * M/operator/FilterOperator.kt:17-22); the only exchange is the partial aggregates, which every device leaves in
+ * pinned host memory and the calling thread folds in partition order (GlobalAggregationOperator.kt:10-25,
+ * Accumulators.kt:38-54) -- for one process that is cheaper than a collective, see DESIGN.md.  Group-by results are
+ * merged by key on the host (fixed-width records, partials in partition order, groups ordered by first row).
+ * Programs are host objects: one created with any context of the group (qe_mgpu_ctx) runs on all of them.  STRING
+ * columns of all partitions must use ONE dictionary. */
+typedef struct qe_mgpu qe_mgpu;
+typedef struct qe_mtable qe_mtable;
+typedef struct qe_mresult qe_mresult;
+
+QE_API int qe_mgpu_create(const int *devices, int ndevices, qe_mgpu **out);
+QE_API int qe_mgpu_destroy(qe_mgpu *m);
+QE_API int qe_mgpu_num_devices(const qe_mgpu *m);
+QE_API qe_ctx *qe_mgpu_ctx(qe_mgpu *m, int part);
+QE_API int qe_mgpu_set_option(qe_mgpu *m, const char *key, int64_t value);      /* on every context */
+/* rows [*begin, *end) of partition `part` of an nrows-row table over `nparts` partitions */
+QE_API int qe_partition_rows(int64_t nrows, int nparts, int part, int64_t *begin, int64_t *end);
+
+QE_API int qe_mtable_create(qe_mgpu *m, int ncols, const qe_col_desc *cols, int64_t nrows, qe_mtable **out);
+/* whole column from host memory; every device copies its row range, all at the same time */
+QE_API int qe_mtable_upload(qe_mtable *t, int col, const void *values, const uint8_t *validity);
+/* synthetic column from the global row index (as qe_table_generate with row_offset = the partition's first row) */
+QE_API int qe_mtable_generate(qe_mtable *t, int col, int kind, uint64_t seed, double p0, double p1, double null_rate);
+QE_API qe_table *qe_mtable_part(qe_mtable *t, int part);
+QE_API int qe_mtable_destroy(qe_mtable *t);
+
+/* desc->row_begin / row_end must be 0 / -1 (the whole table); out_capacity_rows applies to every partition */
+QE_API int qe_mgpu_pipeline_run(qe_mgpu *m, const qe_mtable *t, const qe_pipeline_desc *desc, qe_mresult **result);
+QE_API int qe_mgpu_groupby_run(qe_mgpu *m, const qe_mtable *t, const qe_groupby_desc *desc, qe_mresult **result);
+/* descs[part] describes the stream of partition `part` (host pointers already offset to its first row);
+ * qe_pipeline_stream runs on every device at the same time */
+QE_API int qe_mgpu_pipeline_stream(qe_mgpu *m, qe_mtable *t, const qe_stream_desc *descs);
+
+QE_API int qe_mresult_num_rows(qe_mresult *r, int64_t *nrows);                  /* all partitions (groups after the merge) */
+QE_API int qe_mresult_num_columns(const qe_mresult *r, int *ncols);
+QE_API qe_result *qe_mresult_part(qe_mresult *r, int part);
+QE_API int qe_mresult_part_rows(qe_mresult *r, int part, int64_t *nrows);
+/* partitions concatenated in order; values / validity as qe_result_column */
+QE_API int qe_mresult_column(qe_mresult *r, int k, void *dst_values, uint8_t *dst_validity);
+/* global row indices (the partition's first row added), 64-bit */
+QE_API int qe_mresult_selection(qe_mresult *r, uint64_t *dst);
+QE_API int qe_mresult_agg(qe_mresult *r, int k, double *value, int *is_null);
+QE_API int qe_mresult_destroy(qe_mresult *r);
 
 /* Diagnostics, no GPU needed: bind `programs` (filter first when has_filter,
  * then nproj projections) against a schema, write the generated CUDA source
@@ -310,6 +413,26 @@ QE_API int qe_debug_generate_groupby(const qe_col_desc *cols, int ncols,
                                      const uint32_t *const *programs, const size_t *nwords,
                                      int has_filter, int nkeys, const int32_t *agg_fns, int nagg, int atomic, int compile,
                                      char *src_buf, size_t src_cap, size_t *cubin_bytes);
+
+/* Ahead-of-time compilation, no GPU needed: compile the kernel a run of this pipeline would ask for (context options at
+ * their defaults) through the cubin caches, so that it lands in $QE_CACHE_DIR; queryengine_b200/build.py bakes the
+ * files into the library.  programs = [filter,] projections -- or, with group_keys >= 0, [filter,] keys then aggregate
+ * inputs (nproj = keys + inputs; the register variant of the group-by).  key_out receives the 32-digit cache key. */
+typedef struct qe_aot_desc {
+    const qe_col_desc *cols;
+    int32_t ncols;
+    const uint32_t *const *programs;
+    const size_t *nwords;
+    int32_t has_filter, nproj;
+    const int32_t *agg_fns;
+    int32_t nagg;
+    int32_t group_keys;                /* -1: not a group-by */
+    double sel_hint;                   /* filter: selectivity the same query measured on its previous run, or -1 */
+    int32_t min_blocks;                /* dense projection: 4 = the variant tried first, 0 = the fallback */
+    int32_t seen_groups;               /* group-by: groups the same query found on its previous run, or 0 */
+    uint32_t run_flags;                /* QE_RUN_NO_VALUES */
+} qe_aot_desc;
+QE_API int qe_aot_compile(const qe_aot_desc *desc, char key_out[33], int *origin);
 
 QE_API const char *qe_last_error(void);
 QE_API const char *qe_version(void);

@@ -24,6 +24,9 @@ QE_ERR_STATE = 7
 QE_RUN_NO_SELECTION = 1
 QE_RUN_INTERPRETER = 2
 QE_RUN_APPEND = 4
+QE_RUN_NO_VALUES = 8
+QE_STREAM_CHUNK_RELATIVE = 1
+QE_AGG_SUPER_ROWS = 1 << 20
 QE_GROUPBY_ATOMIC = 1
 QE_GROUPBY_SHARED = 2
 
@@ -60,6 +63,7 @@ class PipelineDesc(C.Structure):
         ("row_end", C.c_int64),
         ("out_capacity_rows", C.c_int64),
         ("flags", C.c_uint32),
+        ("sel_offset", C.c_int64),
     ]
 
 
@@ -78,6 +82,10 @@ class GroupByDesc(C.Structure):
     ]
 
 
+class StreamGen(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("seed", C.c_uint64), ("p0", C.c_double), ("p1", C.c_double), ("null_rate", C.c_double)]
+
+
 class StreamDesc(C.Structure):
     _fields_ = [
         ("chunk_rows", C.c_int64),
@@ -89,6 +97,29 @@ class StreamDesc(C.Structure):
         ("host_selection", C.POINTER(C.c_void_p)),
         ("host_out_values", C.POINTER(C.POINTER(C.c_void_p))),
         ("host_out_validity", C.POINTER(C.POINTER(C.c_void_p))),
+        ("total_rows", C.c_int64),
+        ("flags", C.c_uint32),
+        ("gen", C.POINTER(StreamGen)),
+        ("gen_row_offset", C.c_int64),
+        ("chunk_kept", C.POINTER(C.POINTER(C.c_int64))),
+    ]
+
+
+class AotDesc(C.Structure):
+    _fields_ = [
+        ("cols", C.POINTER(ColDesc)),
+        ("ncols", C.c_int32),
+        ("programs", C.POINTER(C.c_void_p)),
+        ("nwords", C.POINTER(C.c_size_t)),
+        ("has_filter", C.c_int32),
+        ("nproj", C.c_int32),
+        ("agg_fns", C.POINTER(C.c_int32)),
+        ("nagg", C.c_int32),
+        ("group_keys", C.c_int32),
+        ("sel_hint", C.c_double),
+        ("min_blocks", C.c_int32),
+        ("seen_groups", C.c_int32),
+        ("run_flags", C.c_uint32),
     ]
 
 
@@ -138,6 +169,32 @@ SYMBOLS = {
     "qe_result_group_first_rows": (C.c_int, [_vp, _vp]),
     "qe_result_group_variant": (C.c_int, [_vp]),
     "qe_result_group_threads": (C.c_int, [_vp]),
+    "qe_ctx_trim": (C.c_int, [_vp]),
+    "qe_jit_stats": (C.c_int, [C.POINTER(C.c_double)]),
+    "qe_result_agg_partials": (C.c_int, [_vp, C.c_int, C.POINTER(AggPartial), C.c_int64, C.POINTER(C.c_int64)]),
+    "qe_aot_compile": (C.c_int, [C.POINTER(AotDesc), C.c_char_p, C.POINTER(C.c_int)]),
+    "qe_partition_rows": (C.c_int, [C.c_int64, C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "qe_mgpu_create": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(_vp)]),
+    "qe_mgpu_destroy": (C.c_int, [_vp]),
+    "qe_mgpu_num_devices": (C.c_int, [_vp]),
+    "qe_mgpu_ctx": (_vp, [_vp, C.c_int]),
+    "qe_mgpu_set_option": (C.c_int, [_vp, C.c_char_p, C.c_int64]),
+    "qe_mtable_create": (C.c_int, [_vp, C.c_int, C.POINTER(ColDesc), C.c_int64, C.POINTER(_vp)]),
+    "qe_mtable_upload": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "qe_mtable_generate": (C.c_int, [_vp, C.c_int, C.c_int, C.c_uint64, C.c_double, C.c_double, C.c_double]),
+    "qe_mtable_part": (_vp, [_vp, C.c_int]),
+    "qe_mtable_destroy": (C.c_int, [_vp]),
+    "qe_mgpu_pipeline_run": (C.c_int, [_vp, _vp, C.POINTER(PipelineDesc), C.POINTER(_vp)]),
+    "qe_mgpu_groupby_run": (C.c_int, [_vp, _vp, C.POINTER(GroupByDesc), C.POINTER(_vp)]),
+    "qe_mgpu_pipeline_stream": (C.c_int, [_vp, _vp, C.POINTER(StreamDesc)]),
+    "qe_mresult_num_rows": (C.c_int, [_vp, C.POINTER(C.c_int64)]),
+    "qe_mresult_num_columns": (C.c_int, [_vp, C.POINTER(C.c_int)]),
+    "qe_mresult_part": (_vp, [_vp, C.c_int]),
+    "qe_mresult_part_rows": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_int64)]),
+    "qe_mresult_column": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "qe_mresult_selection": (C.c_int, [_vp, _vp]),
+    "qe_mresult_agg": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
+    "qe_mresult_destroy": (C.c_int, [_vp]),
     "qe_last_error": (C.c_char_p, []),
     "qe_version": (C.c_char_p, []),
 }

@@ -18,6 +18,7 @@ struct SV {                  // one entry of the compile-time operand stack
     bool is_const = false;
     double k = 0.0;
     std::string raw_int;     // non-empty: the value is a bare INT64 / DATE32 column, this is its integer payload
+    int lit = -1;            // is_const: slot of the literal in QeParams::lit_* (-1: the value is embedded in the code)
 };
 
 struct Gen {
@@ -101,22 +102,31 @@ bool int_literal_ok(const SV &s)
     return s.is_const && s.k == s.k && std::fabs(s.k) < 4.0e18 && !(s.k == 0.0 && std::signbit(s.k));
 }
 
-std::string int_compare(int op, const std::string &x, double k)
+// floor(k) / ceil(k) come from the kernel parameters (the host computes them per run, fill of QeParams::lit_lo /
+// lit_hi) unless the literal had no parameter slot left; only `integral` -- part of the literal's class -- shapes the code.
+std::string int_compare(int op, const std::string &x, const SV &lit)
 {
-    const long long lo = (long long)std::floor(k), hi = (long long)std::ceil(k);
-    const bool integral = lo == hi;
-    char b[96];
+    const double k = lit.k;
+    const bool integral = std::floor(k) == std::ceil(k);
+    char lo[48], hi[48], b[160];
+    if (lit.lit >= 0) {
+        snprintf(lo, sizeof lo, "p.lit_lo[%d]", lit.lit);
+        snprintf(hi, sizeof hi, "p.lit_hi[%d]", lit.lit);
+    } else {
+        snprintf(lo, sizeof lo, "%lldLL", (long long)std::floor(k));
+        snprintf(hi, sizeof hi, "%lldLL", (long long)std::ceil(k));
+    }
     switch (op) {
-    case OP_CMP_LT: snprintf(b, sizeof b, "((qe_i64)%s < %lldLL)", x.c_str(), hi); break;
-    case OP_CMP_LE: snprintf(b, sizeof b, "((qe_i64)%s <= %lldLL)", x.c_str(), lo); break;
-    case OP_CMP_GE: snprintf(b, sizeof b, "((qe_i64)%s >= %lldLL)", x.c_str(), hi); break;
-    case OP_CMP_GT: snprintf(b, sizeof b, "((qe_i64)%s > %lldLL)", x.c_str(), lo); break;
+    case OP_CMP_LT: snprintf(b, sizeof b, "((qe_i64)%s < %s)", x.c_str(), hi); break;
+    case OP_CMP_LE: snprintf(b, sizeof b, "((qe_i64)%s <= %s)", x.c_str(), lo); break;
+    case OP_CMP_GE: snprintf(b, sizeof b, "((qe_i64)%s >= %s)", x.c_str(), hi); break;
+    case OP_CMP_GT: snprintf(b, sizeof b, "((qe_i64)%s > %s)", x.c_str(), lo); break;
     case OP_CMP_EQ:
-        if (integral) snprintf(b, sizeof b, "((qe_i64)%s == %lldLL)", x.c_str(), lo);
+        if (integral) snprintf(b, sizeof b, "((qe_i64)%s == %s)", x.c_str(), lo);
         else snprintf(b, sizeof b, "false");
         break;
     default:
-        if (integral) snprintf(b, sizeof b, "((qe_i64)%s != %lldLL)", x.c_str(), lo);
+        if (integral) snprintf(b, sizeof b, "((qe_i64)%s != %s)", x.c_str(), lo);
         else snprintf(b, sizeof b, "true");
         break;
     }
@@ -155,17 +165,19 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
             r.valid = bp.slot_info[slot].nullable ? b : "true";
             break;
         }
-        case OP_CONST_F64:
-            r.t = VT_F64; r.val = f64_literal(in.k); r.valid = "true"; r.is_const = true; r.k = in.k;
+        case OP_CONST_F64:                          // value from the kernel parameters: one kernel for every literal of a class
+            r.t = VT_F64; r.valid = "true"; r.is_const = true; r.k = in.k; r.lit = in.lit;
+            r.val = in.lit >= 0 ? "p.lit_f64[" + std::to_string(in.lit) + "]" : f64_literal(in.k);
             break;
         case OP_CONST_BOOL:
             r.t = VT_BOOL; r.val = in.arg ? "true" : "false"; r.valid = "true";
             break;
         case OP_CONST_STR:                          // StringLiteralExpression as its dictionary code
-            r.t = VT_STR; r.val = "((qe_i32)" + std::to_string(in.code) + ")"; r.valid = "true";
+            r.t = VT_STR; r.valid = "true";
+            r.val = in.lit >= 0 ? "((qe_i32)p.lit_lo[" + std::to_string(in.lit) + "])" : "((qe_i32)" + std::to_string(in.code) + ")";
             break;
         case OP_UNARY_PLUS: {                       // M/evaluator/Interpreter.kt:94
-            r = st.back(); st.pop_back(); r.is_const = false; r.raw_int.clear();
+            r = st.back(); st.pop_back(); r.is_const = false; r.lit = -1; r.raw_int.clear();
             break;
         }
         case OP_UNARY_MINUS: {                      // Interpreter.kt:95
@@ -189,8 +201,10 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
             if (in.op == OP_MOD && b.is_const && !a.is_const) {
                 // literal divisor: multiply by its reciprocal instead of dividing (qe_mod_k); both must be normal
                 const double kk = std::fabs(b.k), inv = 1.0 / kk;
-                if (kk >= 0x1p-1000 && kk <= 0x1p1000 && std::isfinite(inv)) {
-                    g.line("const double " + r.val + " = qe_mod_k(" + a.val + ", " + b.val + ", " + f64_literal(kk) + ", " + f64_literal(inv) + ");");
+                if (kk >= 0x1p-1000 && kk <= 0x1p1000 && std::isfinite(inv)) {     // == Literal::mod_ok()
+                    const std::string skk = b.lit >= 0 ? "p.lit_abs[" + std::to_string(b.lit) + "]" : f64_literal(kk);
+                    const std::string sinv = b.lit >= 0 ? "p.lit_inv[" + std::to_string(b.lit) + "]" : f64_literal(inv);
+                    g.line("const double " + r.val + " = qe_mod_k(" + a.val + ", " + b.val + ", " + skk + ", " + sinv + ");");
                     break;
                 }
             }
@@ -205,9 +219,9 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
             if (a.t == VT_BOOL || a.t == VT_STR) {  // Boolean / String equality (TypeCheck.kt:65-71); equal codes <=> equal strings
                 rhs = std::string("(") + a.val + (in.op == OP_CMP_EQ ? " == " : " != ") + b.val + ")";
             } else if (int_literal_ok(b) && !a.raw_int.empty()) {
-                rhs = int_compare(in.op, a.raw_int, b.k);
+                rhs = int_compare(in.op, a.raw_int, b);
             } else if (int_literal_ok(a) && !b.raw_int.empty()) {
-                rhs = int_compare(cmp_swapped(in.op), b.raw_int, a.k);
+                rhs = int_compare(cmp_swapped(in.op), b.raw_int, a);
             } else if (plain_literal(b) && !a.is_const) {
                 rhs = std::string(cmp_fn(in.op)) + "_k(" + a.val + ", " + b.val + ")";
             } else if (plain_literal(a) && !b.is_const) {
@@ -677,10 +691,10 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
             s += b; s += val + ", " + on + ");\n";
         }
         s += "    }\n";
-        s += "    static __device__ __forceinline__ void acc_store(const QeParams &p, Accs &a, QeAcc *slot) {\n";
+        s += "    static __device__ __forceinline__ void acc_store(const QeParams &p, Accs &a, QeAcc *slot, qe_i64 part) {\n";
         for (size_t k = 0; k < bp.agg_fns.size(); k++) {
-            snprintf(b, sizeof b, "        qe_acc_block_reduce_store<%d>(a.a%d, slot, p.agg_partials, %d);\n", bp.agg_fns[k],
-                     (int)k, (int)k);
+            snprintf(b, sizeof b, "        qe_acc_block_reduce_store<%d>(a.a%d, slot, p.agg_partials, part, %d, %d);\n", bp.agg_fns[k],
+                     (int)k, (int)bp.agg_fns.size(), (int)k);
             s += b;
         }
         s += "    }\n";

@@ -47,6 +47,15 @@
 #define QE_MAX_COLS 16      // referenced scan columns per pipeline
 #define QE_MAX_OUTS 8       // projection outputs per pipeline
 #define QE_MAX_AGGS 8
+#define QE_MAX_LITS 24      // literal parameter slots per pipeline (qe_program.h)
+
+// Global aggregation is folded in a fixed shape over the ROW INDEX, not over the grid: every CTA owns whole
+// sub-tiles of QE_AGG_SUB_ROWS rows (one partial each), QE_AGG_SUPER_ROWS / QE_AGG_SUB_ROWS consecutive sub-tile
+// partials are folded by one warp in a fixed tree (qe_agg_final_kernel), and the super-tile partials are added up in
+// ascending row order on the host.  SUM / AVG therefore do not depend on the grid size, on the number of streamed
+// chunks or on the number of GPUs, as long as every partition / chunk starts at a multiple of QE_AGG_SUPER_ROWS.
+#define QE_AGG_SUB_ROWS 16384
+#define QE_AGG_SUPER_ROWS 1048576
 
 // physical column types (values match include/qegpu.h)
 #define QE_T_STR 0      /* dictionary codes, int32 */
@@ -77,7 +86,9 @@ struct QeParams {
     qe_u32       *ticket;                     // dynamic tile counter, zeroed per run
     qe_u64       *out_count;                  // number of rows kept
     const qe_u64 *out_base;                   // append mode: rows already in the outputs (device word), 0 = none
-    double       *agg_partials;               // [gridDim.x][QE_MAX_AGGS][4] = sum, count (bits), min, max
+    qe_u64        out_base_mask;              // bits of *out_base that offset this run's outputs: all ones = append to one
+                                              // buffer; 7 = a streamed chunk with buffers of its own keeps the bit phase only
+    double       *agg_partials;               // [sub-tiles][aggregates][4] = sum, count (bits), min, max
     const qe_u32 *iprog;                      // interpreter only: serialized pipeline (qe_interp.cuh)
     qe_u64       *debug;                      // [4096][8] per-CTA phase cycle counters (QE_DEBUG_FLAGS & 16)
     qe_i64        nrows;                      // rows in this batch
@@ -94,7 +105,17 @@ struct QeParams {
     qe_u32       *g_part_slot;                // private variant: [grid][1 + LMAX]: local groups, then the table slot of each
     qe_u32        g_slot_mask;                // slots - 1 (a power of two)
     qe_u32        g_max_groups;
+    // literals of the expression trees (generated code reads the values from here: one kernel per literal CLASS)
+    double        lit_f64[QE_MAX_LITS];       // NumericLiteralExpression values
+    qe_i64        lit_lo[QE_MAX_LITS];        // floor(k) for integer-domain comparisons; dictionary code of a string literal
+    qe_i64        lit_hi[QE_MAX_LITS];        // ceil(k)
+    double        lit_abs[QE_MAX_LITS];       // |k|      (MOD by a literal, qe_mod_k)
+    double        lit_inv[QE_MAX_LITS];       // 1 / |k|
 };
+
+// rows already in the outputs before this run (append mode), and the part of it that offsets this run's positions
+__device__ __forceinline__ qe_u64 qe_out_base_full(const QeParams &p) { return p.out_base ? *p.out_base : 0ull; }
+
 
 // ---------------------------------------------------------------- memory ops
 
@@ -474,7 +495,7 @@ __device__ __forceinline__ void qe_acc_warp_reduce(QeAcc &a)
 // Block reduce in fixed order (lane tree, then warps 0..7 sequentially) and
 // write this CTA's partial.  `slot` is a [QE_WARPS] shared array.
 template <int FN>
-__device__ __forceinline__ void qe_acc_block_reduce_store(QeAcc a, QeAcc *slot, double *partials, int k)
+__device__ __forceinline__ void qe_acc_block_reduce_store(QeAcc a, QeAcc *slot, double *partials, qe_i64 part, int nagg, int k)
 {
     qe_acc_warp_reduce<FN>(a);
     __syncthreads();
@@ -483,7 +504,7 @@ __device__ __forceinline__ void qe_acc_block_reduce_store(QeAcc a, QeAcc *slot, 
     if (threadIdx.x == 0) {
         QeAcc t = slot[0];
         for (int w = 1; w < QE_WARPS; w++) qe_acc_merge<FN>(t, slot[w]);
-        double *dst = partials + ((qe_i64)blockIdx.x * QE_MAX_AGGS + k) * 4;
+        double *dst = partials + (part * nagg + k) * 4;
         dst[0] = t.sum;
         dst[1] = qe_bits_f64(t.count);
         dst[2] = t.mn;
@@ -503,7 +524,7 @@ __device__ __forceinline__ void qe_acc_merge_all(QeAcc &a, const QeAcc &b)
 }
 
 // Same block reduce as qe_acc_block_reduce_store, all four fields.
-__device__ __forceinline__ void qe_acc_block_reduce_store_all(QeAcc a, QeAcc *slot, double *partials, int k)
+__device__ __forceinline__ void qe_acc_block_reduce_store_all(QeAcc a, QeAcc *slot, double *partials, qe_i64 part, int nagg, int k)
 {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -520,7 +541,7 @@ __device__ __forceinline__ void qe_acc_block_reduce_store_all(QeAcc a, QeAcc *sl
     if (threadIdx.x == 0) {
         QeAcc t = slot[0];
         for (int w = 1; w < QE_WARPS; w++) qe_acc_merge_all(t, slot[w]);
-        double *dst = partials + ((qe_i64)blockIdx.x * QE_MAX_AGGS + k) * 4;
+        double *dst = partials + (part * nagg + k) * 4;
         dst[0] = t.sum;
         dst[1] = qe_bits_f64(t.count);
         dst[2] = t.mn;
@@ -680,7 +701,7 @@ __device__ __forceinline__ void qe_filter_body(const QeParams &p)
     __shared__ qe_u32 s_lb_found[QE_WARPS];
 
     const qe_u32 lane = qe_lane(), warp = qe_warp();
-    const qe_u64 base0 = p.out_base ? *p.out_base : 0ull;      // append mode: rows of earlier batches
+    const qe_u64 base0 = qe_out_base_full(p) & p.out_base_mask;      // append mode: rows of earlier batches
 
 #ifndef QE_DEBUG_FLAGS
 #define QE_DEBUG_FLAGS 0      // timing experiments only: 1 no look-back, 2 static tiles, 4 no scatter, 8 warp look-back
@@ -741,7 +762,7 @@ __device__ __forceinline__ void qe_filter_body(const QeParams &p)
         }
         QE_TICK(3);
         excl += base0;
-        if (threadIdx.x == 0 && tile == p.ntiles - 1) *p.out_count = excl + tile_total;
+        if (threadIdx.x == 0 && tile == p.ntiles - 1) *p.out_count = (qe_out_base_full(p) & ~p.out_base_mask) + excl + tile_total;
         if (!(QE_DEBUG_FLAGS & 4)) qe_warp_scatter<P>(p, warp_row0, excl + woff, outs, keep, rank0, step_off);
         QE_TICK(4);
     }
@@ -800,9 +821,9 @@ __device__ __forceinline__ void qe_filter_pipelined_body(const QeParams &p)
         }
         if (have_prev) {
             // the previous tile: prefix (its predecessors published long ago) and ordered scatter
-            const qe_u64 excl = (p.out_base ? *p.out_base : 0ull) +
+            const qe_u64 excl = (qe_out_base_full(p) & p.out_base_mask) +
                                 qe_block_lookback<false>(p.tile_state, prev_tile, prev_total, s_lb_sum, s_lb_found);
-            if (threadIdx.x == 0 && prev_tile == p.ntiles - 1) *p.out_count = excl + prev_total;
+            if (threadIdx.x == 0 && prev_tile == p.ntiles - 1) *p.out_count = (qe_out_base_full(p) & ~p.out_base_mask) + excl + prev_total;
             const qe_i64 prev_row0 = (qe_i64)prev_tile * TILE + (qe_i64)warp * WARP_ROWS;
             qe_warp_scatter<P>(p, prev_row0, excl + prev_woff, prev_outs, prev_keep, prev_rank0, prev_step_off);
         }
@@ -1067,8 +1088,8 @@ __device__ __forceinline__ void qe_filter_staged_body(const QeParams &p)
             woff += (qe_u32)w < warp ? c : 0u;
             tile_total += c;
         }
-        const qe_u64 excl = (p.out_base ? *p.out_base : 0ull) + qe_block_lookback(p.tile_state, tile, tile_total, s_lb_sum, s_lb_found);
-        if (threadIdx.x == 0 && tile == p.ntiles - 1) *p.out_count = excl + tile_total;
+        const qe_u64 excl = (qe_out_base_full(p) & p.out_base_mask) + qe_block_lookback(p.tile_state, tile, tile_total, s_lb_sum, s_lb_found);
+        if (threadIdx.x == 0 && tile == p.ntiles - 1) *p.out_count = (qe_out_base_full(p) & ~p.out_base_mask) + excl + tile_total;
         qe_warp_scatter<P>(p, warp_row0, excl + woff, outs, keep, rank0, step_off);
     }
 }
@@ -1378,7 +1399,8 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
         // final add chains through shared memory (the inclusive count of the previous tile).
         qe_u64 rt_acc[16] = {};
         QE_RT_BEGIN();
-        const qe_u64 base0 = p.out_base ? *p.out_base : 0ull;  // append mode: rows of earlier batches
+        const qe_u64 base_full = qe_out_base_full(p);          // append mode: rows of earlier batches
+        const qe_u64 base0 = base_full & p.out_base_mask;
         for (qe_u32 it = warp - 2u;; it += (qe_u32)NLB) {
             const qe_u32 st = it % NST;
             const qe_u32 par = (it / NST) & 1u;
@@ -1454,7 +1476,7 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                 qe_sts_u64(cb + O_INCL + 8u * st, excl + c);
                 qe_mbar_arrive(cb + O_PREF + 8u * st);
                 qe_mbar_arrive(cb + O_EMPTY + 8u * st);
-                if (t == p.ntiles - 1u) *p.out_count = excl + c;
+                if (t == p.ntiles - 1u) *p.out_count = (base_full & ~p.out_base_mask) + excl + c;   // stays the running total
             }
         }
     } else {
@@ -1666,29 +1688,39 @@ __device__ __forceinline__ void qe_agg_body(const QeParams &p)
     constexpr int STEPS = P::STEPS, VEC = P::VEC;
     constexpr int WARP_ROWS = STEPS * 32 * VEC;
     constexpr int TILE = QE_WARPS * WARP_ROWS;
+    constexpr int TPS = QE_AGG_SUB_ROWS / TILE;               // tiles per sub-tile
+    static_assert(QE_AGG_SUB_ROWS % TILE == 0 && TPS >= 1, "a sub-tile is a whole number of tiles");
     __shared__ QeAcc s_slot[QE_WARPS];
     const qe_u32 warp = qe_warp();
 
-    typename P::Accs accs;
-    P::acc_init(accs);
     qe_i64 kept = 0;
-    // static tile -> CTA assignment: the summation order depends only on the grid size
-    for (qe_u32 tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
-        const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
-        typename P::Out outs[STEPS][VEC];
-        qe_u32 keep[STEPS], inb[STEPS];
-        qe_tile_eval<P>(p, warp_row0, outs, keep, inb);
+    const qe_u32 nsub = (p.ntiles + (qe_u32)TPS - 1u) / (qe_u32)TPS;
+    // One partial per sub-tile of QE_AGG_SUB_ROWS rows, folded in an order that depends on the tile shape only: a
+    // thread adds its rows of the sub-tile's tiles in ascending order, then the fixed lane tree and the warps 0..7
+    // in sequence.  Which CTA takes which sub-tile does not matter (the partial is stored by sub-tile index), so
+    // neither the grid size nor the partitioning of the table changes a SUM.
+    for (qe_u32 sub = blockIdx.x; sub < nsub; sub += gridDim.x) {
+        typename P::Accs accs;
+        P::acc_init(accs);
+        const qe_u32 t0 = sub * (qe_u32)TPS;
+        const qe_u32 t1 = t0 + (qe_u32)TPS < p.ntiles ? t0 + (qe_u32)TPS : p.ntiles;
+        for (qe_u32 tile = t0; tile < t1; tile++) {
+            const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
+            typename P::Out outs[STEPS][VEC];
+            qe_u32 keep[STEPS], inb[STEPS];
+            qe_tile_eval<P>(p, warp_row0, outs, keep, inb);
 #pragma unroll
-        for (int s = 0; s < STEPS; s++) {
+            for (int s = 0; s < STEPS; s++) {
 #pragma unroll
-            for (int j = 0; j < VEC; j++) {
-                const bool k = (keep[s] >> j) & 1u;
-                P::acc_add(p, accs, outs[s][j], k);
-                kept += k ? 1 : 0;
+                for (int j = 0; j < VEC; j++) {
+                    const bool k = (keep[s] >> j) & 1u;
+                    P::acc_add(p, accs, outs[s][j], k);
+                    kept += k ? 1 : 0;
+                }
             }
         }
+        P::acc_store(p, accs, s_slot, (qe_i64)sub);
     }
-    P::acc_store(p, accs, s_slot);
     // rows that reached the aggregation (diagnostic; the result row count is 1)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) kept += __shfl_down_sync(QE_FULL_MASK, kept, o);

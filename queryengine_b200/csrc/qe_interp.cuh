@@ -236,10 +236,10 @@ struct QeInterpProgram {
         }
     }
 
-    static __device__ void acc_store(const QeParams &p, Accs &a, QeAcc *slot)
+    static __device__ void acc_store(const QeParams &p, Accs &a, QeAcc *slot, qe_i64 part)
     {
         const int nagg = (int)p.iprog[2];
-        for (int k = 0; k < nagg; k++) qe_acc_block_reduce_store_all(a.a[k], slot, p.agg_partials, k);
+        for (int k = 0; k < nagg; k++) qe_acc_block_reduce_store_all(a.a[k], slot, p.agg_partials, part, nagg, k);
     }
 };
 

@@ -33,6 +33,8 @@ Nvrtc &nvrtc()
     static Nvrtc n;
     static std::once_flag once;
     std::call_once(once, [] {
+        // tests / deployments without a compiler: behave as if libnvrtc were missing (AOT and disk cubins still load)
+        if (const char *off = getenv("QE_DISABLE_NVRTC"); off && *off && *off != '0') { n.why = "NVRTC disabled by QE_DISABLE_NVRTC"; return; }
         // Absolute paths of the toolkit first: a bare soname would resolve to whatever libnvrtc the
         // process already has loaded (PyTorch bundles an older one whose ptxas lacks the 256-bit
         // loads of sm_100), and loading by path gets the toolkit's own copy beside it.
@@ -74,8 +76,9 @@ bool jit_available(std::string *why)
 bool jit_wide_loads_supported()
 {
     Nvrtc &n = nvrtc();
-    // ld.global.v4.f64 / .v4.b64 (LDG.E.256) needs PTX ISA 8.8 = CUDA 12.9
-    return n.handle && (n.major > 12 || (n.major == 12 && n.minor >= 9));
+    // ld.global.v4.f64 / .v4.b64 (LDG.E.256) needs PTX ISA 8.8 = CUDA 12.9.  Without any NVRTC the shapes of the
+    // ahead-of-time cubins apply (built with the toolkit's 12.9), so the answer is yes.
+    return !n.handle || n.major > 12 || (n.major == 12 && n.minor >= 9);
 }
 
 std::string jit_version()

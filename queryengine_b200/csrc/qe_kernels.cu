@@ -28,25 +28,49 @@ __global__ void __launch_bounds__(QE_BLOCK) qe_interp_agg_kernel(const __grid_co
     qe_agg_body<InterpProgram>(p);
 }
 
-// One block.  Thread t folds CTAs t, t+256, ... in order, then the fixed block
-// tree: the result depends only on the number of partials.
-__global__ void __launch_bounds__(QE_BLOCK) qe_agg_final_kernel(const double *partials, int nblocks, int nagg, double *out)
+// Second level of the fixed-shape aggregation (QE_AGG_SUPER_ROWS in qe_device.cuh): one warp per super-tile folds
+// its 64 consecutive sub-tile partials -- lane l takes sub-tiles 2l and 2l+1, then the lane tree.  A missing
+// sub-tile (past the end of the batch) is the identity; x + 0.0 is exact and a partial sum is never -0.0 (sums
+// start at +0.0, M/evaluator/Accumulators.kt:40), so padding does not change a bit.
+__global__ void __launch_bounds__(QE_BLOCK) qe_agg_final_kernel(const double *sub, qe_i64 nsub, int nagg, double *out)
 {
-    __shared__ QeAcc s_slot[QE_WARPS];
+    constexpr int SPS = QE_AGG_SUPER_ROWS / QE_AGG_SUB_ROWS;
+    static_assert(SPS == 64, "one warp folds two sub-tiles per lane");
+    const qe_i64 super = (qe_i64)blockIdx.x * QE_WARPS + qe_warp();
+    if (super * SPS >= nsub) return;
+    const qe_u32 lane = qe_lane();
     for (int k = 0; k < nagg; k++) {
         QeAcc a;
         qe_acc_init(a);
-        for (int b = threadIdx.x; b < nblocks; b += QE_BLOCK) {
-            const double *src = partials + ((qe_i64)b * QE_MAX_AGGS + k) * 4;
-            QeAcc x;
-            x.sum = src[0];
-            x.count = qe_f64_bits(src[1]);
-            x.mn = src[2];
-            x.mx = src[3];
-            qe_acc_merge_all(a, x);
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const qe_i64 i = super * SPS + 2 * (qe_i64)lane + h;
+            if (i < nsub) {
+                const double *src = sub + (i * nagg + k) * 4;
+                QeAcc x;
+                x.sum = src[0];
+                x.count = qe_f64_bits(src[1]);
+                x.mn = src[2];
+                x.mx = src[3];
+                qe_acc_merge_all(a, x);
+            }
         }
-        // blockIdx.x == 0, so the helper writes slot k of "CTA 0" of `out`
-        qe_acc_block_reduce_store_all(a, s_slot, out, k);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            QeAcc b;
+            b.count = qe_shfl_down_i64(a.count, o);
+            b.sum = qe_shfl_down_f64(a.sum, o);
+            b.mn = qe_shfl_down_f64(a.mn, o);
+            b.mx = qe_shfl_down_f64(a.mx, o);
+            qe_acc_merge_all(a, b);
+        }
+        if (lane == 0) {
+            double *dst = out + (super * nagg + k) * 4;
+            dst[0] = a.sum;
+            dst[1] = qe_bits_f64(a.count);
+            dst[2] = a.mn;
+            dst[3] = a.mx;
+        }
     }
 }
 
@@ -174,9 +198,12 @@ int interp_blocks_per_sm(int mode)
     return n;
 }
 
-cudaError_t launch_agg_final(const double *partials, int nblocks, int nagg, double *out, cudaStream_t stream)
+cudaError_t launch_agg_final(const double *sub_partials, int64_t nsub, int nagg, double *super_partials, cudaStream_t stream)
 {
-    qe_agg_final_kernel<<<1, QE_BLOCK, 0, stream>>>(partials, nblocks, nagg, out);
+    const int64_t sps = QE_AGG_SUPER_ROWS / QE_AGG_SUB_ROWS;
+    const int64_t nsuper = (nsub + sps - 1) / sps;
+    if (nsuper <= 0) return cudaSuccess;
+    qe_agg_final_kernel<<<(unsigned)((nsuper + QE_WARPS - 1) / QE_WARPS), QE_BLOCK, 0, stream>>>(sub_partials, (qe_i64)nsub, nagg, super_partials);
     return cudaGetLastError();
 }
 

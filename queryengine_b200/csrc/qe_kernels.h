@@ -23,7 +23,8 @@ struct GroupWords {
 // mode: 0 filter, 1 project, 2 aggregate (== KernelMode)
 cudaError_t launch_interp(int mode, const QeParams &p, int grid, cudaStream_t stream);
 int interp_blocks_per_sm(int mode);
-cudaError_t launch_agg_final(const double *partials, int nblocks, int nagg, double *out, cudaStream_t stream);
+// folds [nsub][nagg][4] sub-tile partials into [ceil(nsub / 64)][nagg][4] super-tile partials (fixed tree per super-tile)
+cudaError_t launch_agg_final(const double *sub_partials, int64_t nsub, int nagg, double *super_partials, cudaStream_t stream);
 // group-by helpers: ctl = [0] groups claimed [1] overflow flags [2] records collected [3] spare
 cudaError_t launch_groupby_init(uint32_t *state, uint64_t *acc, uint32_t *ctl, int64_t nslots, const GroupWords &gw, cudaStream_t stream);
 cudaError_t launch_groupby_merge(const uint64_t *part, const uint32_t *part_slot, uint64_t *acc, int nctas, int lmax,

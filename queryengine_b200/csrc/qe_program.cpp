@@ -1,6 +1,7 @@
 // qe_program.cpp -- see qe_program.h
 #include "qe_program.h"
 
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 
@@ -73,7 +74,9 @@ bool parse_program(const uint32_t *words, size_t n, Program &out, std::string &e
 
 namespace {
 
-struct TV { VType t; bool nullable; };
+// type and nullability of a stack entry, plus what the code generator's special cases look at: is it a literal
+// (index of its CONST instruction) or a bare INT64 / DATE32 column
+struct TV { VType t; bool nullable; int const_at = -1; bool raw_int = false; };
 
 const char *vt_name(VType t) { return t == VT_F64 ? "DOUBLE" : t == VT_BOOL ? "BOOLEAN" : t == VT_STR ? "STRING" : "?"; }
 
@@ -120,10 +123,10 @@ static int bind_expr(const std::vector<ColumnInfo> &schema, const Program &p, Bo
                 bp.slot_info.push_back(ci);
             }
             in.arg = (uint32_t)slot;
-            st.push_back({t, ci.nullable});
+            st.push_back({t, ci.nullable, -1, ci.type == 3 || ci.type == 4});
             break;
         }
-        case OP_CONST_F64: st.push_back({VT_F64, false}); break;
+        case OP_CONST_F64: st.push_back({VT_F64, false, (int)out.code.size(), false}); break;
         case OP_CONST_BOOL: st.push_back({VT_BOOL, false}); break;
         case OP_CONST_STR: st.push_back({VT_STR, false}); break;
         default: {
@@ -139,6 +142,7 @@ static int bind_expr(const std::vector<ColumnInfo> &schema, const Program &p, Bo
             case OP_ADD: case OP_SUB: case OP_MUL: case OP_DIV: case OP_MOD:
                 if (a[0].t != VT_F64 || a[1].t != VT_F64) { err = invalid_types(in.op, a, ar); return 2; }
                 r = {VT_F64, a[0].nullable || a[1].nullable};
+                if (in.op == OP_MOD && a[1].const_at >= 0 && a[0].const_at < 0) out.code[(size_t)a[1].const_at].lit_need |= LIT_MOD;
                 break;
             case OP_NOT:                                                  // TypeCheck.kt:58-64
                 if (a[0].t != VT_BOOL) { err = invalid_types(in.op, a, ar); return 2; }
@@ -146,12 +150,16 @@ static int bind_expr(const std::vector<ColumnInfo> &schema, const Program &p, Bo
                 break;
             case OP_CMP_EQ: case OP_CMP_NE:                               // TypeCheck.kt:65-71
                 if (a[0].t != a[1].t) { err = invalid_types(in.op, a, ar); return 2; }
+                for (int i = 0; i < 2 && a[0].t == VT_F64; i++)
+                    if (a[i].const_at >= 0) out.code[(size_t)a[i].const_at].lit_need |= LIT_PLAIN | (a[1 - i].raw_int ? LIT_INT : 0u);
                 in.arg = a[0].t == VT_BOOL ? 1u : 0u;     // Boolean equality (read by the interpreter kernels); STRING
                                                           // codes compare like numbers
                 r = {VT_BOOL, a[0].nullable || a[1].nullable};
                 break;
             case OP_CMP_LT: case OP_CMP_LE: case OP_CMP_GE: case OP_CMP_GT:   // TypeCheck.kt:72-78
                 if (a[0].t != VT_F64 || a[1].t != VT_F64) { err = invalid_types(in.op, a, ar); return 2; }
+                for (int i = 0; i < 2; i++)
+                    if (a[i].const_at >= 0) out.code[(size_t)a[i].const_at].lit_need |= LIT_PLAIN | (a[1 - i].raw_int ? LIT_INT : 0u);
                 r = {VT_BOOL, a[0].nullable || a[1].nullable};
                 break;
             case OP_AND: case OP_OR:                                      // TypeCheck.kt:79-85, intent
@@ -172,6 +180,49 @@ static int bind_expr(const std::vector<ColumnInfo> &schema, const Program &p, Bo
     out.nullable = st.back().nullable;
     if (out.code.size() == 1 && out.code[0].op == OP_LOAD_COL) out.identity_slot = (int)out.code[0].arg;
     return 0;
+}
+
+bool Literal::plain() const { return !is_str && k == k && k != 0.0; }
+bool Literal::int_ok() const { return !is_str && k == k && std::fabs(k) < 4.0e18 && !(k == 0.0 && std::signbit(k)); }
+bool Literal::integral() const { return int_ok() && std::floor(k) == std::ceil(k); }
+bool Literal::mod_ok() const
+{
+    if (is_str || !(k == k)) return false;
+    const double kk = std::fabs(k);
+    return kk >= 0x1p-1000 && kk <= 0x1p1000 && std::isfinite(1.0 / kk);
+}
+
+// Number the distinct literals of the pipeline in order of first appearance.  Equal values share a slot, so
+// repeated subtrees still print identically and the code generator's common-subexpression table finds them.
+static void assign_literals(BoundPipeline &bp)
+{
+    auto visit = [&](BoundExpr &e) {
+        for (Instr &in : e.code) {
+            if (in.op != OP_CONST_F64 && in.op != OP_CONST_STR) continue;
+            const bool str = in.op == OP_CONST_STR;
+            uint64_t bits;
+            memcpy(&bits, &in.k, sizeof bits);
+            int slot = -1;
+            for (size_t i = 0; i < bp.lits.size() && slot < 0; i++) {
+                const Literal &l = bp.lits[i];
+                uint64_t lb;
+                memcpy(&lb, &l.k, sizeof lb);
+                if (l.is_str == str && (str ? l.code == in.code : lb == bits)) slot = (int)i;
+            }
+            if (slot < 0 && bp.lits.size() < QE_MAX_LITS) {
+                Literal l;
+                l.is_str = str;
+                l.k = str ? 0.0 : in.k;
+                l.code = str ? in.code : 0;
+                slot = (int)bp.lits.size();
+                bp.lits.push_back(l);
+            }
+            in.lit = slot;
+            if (slot >= 0) bp.lits[(size_t)slot].need |= in.lit_need;
+        }
+    };
+    if (bp.has_filter) visit(bp.filter);
+    for (BoundExpr &e : bp.proj) visit(e);
 }
 
 int bind_pipeline(const std::vector<ColumnInfo> &schema,
@@ -220,6 +271,7 @@ int bind_pipeline(const std::vector<ColumnInfo> &schema,
         }
         out.agg_fns.push_back(fn);
     }
+    assign_literals(out);
     return 0;
 }
 
@@ -231,8 +283,11 @@ std::string BoundPipeline::signature() const
         for (const Instr &in : e.code) {
             uint64_t kb;
             memcpy(&kb, &in.k, sizeof kb);
-            snprintf(b, sizeof b, "%u.%u.%llx,", in.op, in.arg,
-                     (unsigned long long)(in.op == OP_CONST_F64 ? kb : in.op == OP_CONST_STR ? (uint64_t)(uint32_t)in.code : 0));
+            if ((in.op == OP_CONST_F64 || in.op == OP_CONST_STR) && in.lit >= 0)      // a parameter: slot + class, not the value
+                snprintf(b, sizeof b, "%u.L%d.%x,", in.op, in.lit, lits[(size_t)in.lit].flags());
+            else
+                snprintf(b, sizeof b, "%u.%u.%llx,", in.op, in.arg,
+                         (unsigned long long)(in.op == OP_CONST_F64 ? kb : in.op == OP_CONST_STR ? (uint64_t)(uint32_t)in.code : 0));
             s += b;
         }
         s += ';';

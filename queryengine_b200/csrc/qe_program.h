@@ -36,7 +36,26 @@ struct Instr {
     uint32_t arg = 0;          // LOAD_COL: column (table index before binding, slot after); CONST_BOOL: 0/1
     int32_t code = 0;          // CONST_STR: dictionary code of the StringLiteralExpression
     double k = 0.0;            // CONST_F64
+    int lit = -1;              // CONST_F64 / CONST_STR after binding: slot of BoundPipeline::lits (-1: embedded in the code)
+    unsigned lit_need = 0;     // CONST_F64: which class flags of the literal the code generator looks at for THIS use
 };
+
+// A literal of a bound pipeline.  Generated kernels read literal VALUES from the kernel parameters
+// (QeParams::lit_*), so `col < 10` and `col < 11` are one kernel; only the literal's CLASS -- the handful of
+// properties the code generator branches on -- is part of the pipeline signature.
+#define QE_MAX_LITS 24
+struct Literal {
+    bool is_str = false;
+    double k = 0.0;            // NumericLiteralExpression
+    int32_t code = 0;          // StringLiteralExpression: dictionary code
+    bool plain() const;        // neither NaN nor a zero: Double.compare agrees with the IEEE comparison (qe_cmp_*_k)
+    bool int_ok() const;       // usable against a bare INT64 / DATE32 column in the integer domain (finite, in range, not -0.0)
+    bool integral() const;     // ... and floor(k) == ceil(k)
+    bool mod_ok() const;       // |k| and 1 / |k| are normal: MOD by reciprocal multiply (qe_mod_k)
+    unsigned need = 0;         // union of the uses' lit_need: only these flags are part of the signature
+    unsigned flags() const { return is_str ? 16u : ((plain() ? 1u : 0u) | (int_ok() ? 2u : 0u) | (integral() ? 4u : 0u) | (mod_ok() ? 8u : 0u)) & need; }
+};
+enum { LIT_PLAIN = 1u, LIT_INT = 2u | 4u, LIT_MOD = 8u };
 
 struct Program {
     std::vector<uint32_t> words;
@@ -73,6 +92,7 @@ struct BoundPipeline {
     std::vector<BoundOutput> outs;         // one per projection
     std::vector<int> agg_fns;              // empty, or one per projection (group-by: one per projection after the keys)
     int group_keys = -1;                   // >= 0: GroupByAggregationOperator, the first group_keys projections are the key
+    std::vector<Literal> lits;             // distinct literals in order of first appearance (at most QE_MAX_LITS; the rest stay embedded)
     // everything that changes the generated code, as a cache key
     std::string signature() const;
 };

@@ -9,9 +9,11 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <list>
 #include <map>
 #include <mutex>
 #include <string>
@@ -20,13 +22,15 @@
 
 #include "../../include/qegpu.h"
 #include "qe_codegen.h"
+#include "qe_cubin_cache.h"
 #include "qe_device.cuh"
+#include "qe_internal.h"
 #include "qe_interp.cuh"
 #include "qe_jit.h"
 #include "qe_kernels.h"
 #include "qe_program.h"
 
-#define QE_VERSION_STRING "0.1.0"
+#define QE_VERSION_STRING "0.2.0"
 
 // Column allocations are padded so that any tile shape (<= 8192 rows) starting
 // at any 128-aligned batch offset can be loaded without bounds checks.
@@ -42,6 +46,8 @@ static int fail(int code, const std::string &msg)
     tls_error = msg;
     return code;
 }
+
+int qe_fail(int code, const std::string &msg) { return fail(code, msg); }
 
 static int fail_cuda(const char *what, cudaError_t e)
 {
@@ -124,6 +130,7 @@ struct Pool {
 struct JitEntry {
     qe::JitKernel kernel;
     qe::TileShape shape;
+    std::list<std::string>::iterator lru;      // position in qe_ctx::jit_lru
 };
 
 struct qe_ctx {
@@ -132,7 +139,12 @@ struct qe_ctx {
     cudaStream_t stream = nullptr;
     cudaStream_t h2d = nullptr, d2h = nullptr;   // copy streams of qe_pipeline_stream (created on first use)
     Pool pool;
+    // kernels loaded on this device, by pipeline signature + tile shape; least recently used first in jit_lru.
+    // (The compiled cubins themselves live in the process-wide store of qe_cubin_cache.cpp.)
     std::unordered_map<std::string, JitEntry> jit_cache;
+    std::list<std::string> jit_lru;
+    int64_t opt_jit_cache_entries = 128;
+    int64_t jit_loads = 0;                       // cudaLibraryLoadData calls (cold or evicted kernels)
     // options
     int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = -1, opt_stages = 0, opt_debug_flags = 0, opt_pipeline = 1, opt_groupby_registers = 1, opt_groupby_lanes = 1, opt_lane_acc_kb = 0;
     int64_t opt_min_blocks = 0;
@@ -296,11 +308,33 @@ extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
     } else if (k == "stages") {
         if (value != 0 && (value < 2 || value > 32)) return fail(QE_ERR_INVALID_ARGUMENT, "stages must be 0 (auto) or 2..32");
         ctx->opt_stages = value;
+    } else if (k == "jit_cache_entries") {
+        if (value < 1 || value > 65536) return fail(QE_ERR_INVALID_ARGUMENT, "jit_cache_entries must be in [1, 65536]");
+        ctx->opt_jit_cache_entries = value;
     } else return fail(QE_ERR_INVALID_ARGUMENT, "unknown option '" + k + "'");
     return QE_OK;
 }
 
 extern "C" int64_t qe_ctx_launch_count(const qe_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int qe_ctx_trim(qe_ctx *ctx)
+{
+    if (!ctx) return fail(QE_ERR_INVALID_ARGUMENT, "ctx is NULL");
+    DeviceGuard g(ctx->device);
+    QE_CUDA(cudaStreamSynchronize(ctx->stream));             // freed blocks may still be in use by enqueued work
+    ctx->pool.release_cached();
+    return QE_OK;
+}
+
+extern "C" int qe_jit_stats(double out[6])
+{
+    if (!out) return fail(QE_ERR_INVALID_ARGUMENT, "out is NULL");
+    const qe::CubinStats st = qe::cubin_stats();
+    for (int i = 0; i < 4; i++) out[i] = (double)st.hits[i];
+    out[4] = st.compile_ms;
+    out[5] = (double)qe::kAotCount;
+    return QE_OK;
+}
 
 extern "C" int qe_host_alloc(size_t bytes, void **out)
 {
@@ -526,6 +560,14 @@ struct qe_result {
     ResultHost *host = nullptr;         // pinned
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_done = nullptr;
     bool pending = false;
+    bool chained = false;               // a chunk of a bounded qe_pipeline_stream: host->count is the running total of the stream
+    bool streamed = false;              // outputs went to the caller's host buffers chunk by chunk; none are held on the device
+    // aggregation: super-tile partials [n_super][aggregates][4] (pinned), folded in row order on first access
+    double *h_super = nullptr;
+    size_t h_super_cap = 0;             // doubles
+    int64_t n_super = 0;
+    bool agg_folded = true;
+    std::vector<qe_result *> ring;      // bounded streaming: further output buffer sets, owned by this result
     bool timed = false;                 // ev_begin / ev_end hold a run not yet folded into the totals
     double total_kernel_ms = 0.0;       // device time of the main kernel over all runs into this result
     int64_t kernel_runs = 0;
@@ -582,11 +624,58 @@ static void release(qe_ctx *ctx, DevBuf &b)
     b.bytes = 0;
 }
 
+static int ensure_host_super(qe_result *r, size_t doubles)
+{
+    if (r->h_super && r->h_super_cap >= doubles) return QE_OK;
+    if (r->h_super) {
+        if (r->pending) { QE_CUDA(cudaEventSynchronize(r->ev_done)); r->pending = false; }   // a copy into it may be in flight
+        cudaFreeHost(r->h_super);
+    }
+    r->h_super = nullptr;
+    r->h_super_cap = 0;
+    const size_t cap = std::max<size_t>(doubles, 1024);
+    QE_CUDA(cudaHostAlloc((void **)&r->h_super, cap * sizeof(double), cudaHostAllocDefault));
+    memset(r->h_super, 0, cap * sizeof(double));              // count 0 = no contribution
+    r->h_super_cap = cap;
+    return QE_OK;
+}
+
+// Third level of the fixed-shape aggregation: the super-tile partials in ascending row order, one addition each
+// (the reference adds row by row in this order, M/evaluator/Accumulators.kt:44; here the rows of a super-tile arrive
+// pre-added in a fixed tree).  qe_agg_combine over the concatenated lists of several partitions does the same.
+static void fold_aggs(qe_result *r)
+{
+    if (r->mode != qe::KM_AGG || r->agg_folded) return;
+    const size_t nagg = r->agg_fns.size();
+    for (size_t k = 0; k < nagg && k < QE_MAX_AGGS; k++) {
+        double sum = 0.0, mn = qe_bits_f64((qe_i64)0x7ff0000000000000LL), mx = qe_bits_f64((qe_i64)0xfff0000000000000ULL);
+        int64_t count = 0;
+        for (int64_t s = 0; s < r->n_super; s++) {
+            const double *src = r->h_super + ((size_t)s * nagg + k) * 4;
+            int64_t cnt;
+            memcpy(&cnt, &src[1], sizeof cnt);
+            if (cnt == 0) continue;
+            count += cnt;
+            sum += src[0];
+            mn = qe_math_min(mn, src[2]);
+            mx = qe_math_max(mx, src[3]);
+        }
+        r->host->agg[k][0] = sum;
+        memcpy(&r->host->agg[k][1], &count, sizeof count);
+        r->host->agg[k][2] = mn;
+        r->host->agg[k][3] = mx;
+    }
+    r->agg_folded = true;
+}
+
 extern "C" int qe_result_destroy(qe_result *r)
 {
     if (!r) return QE_OK;
     DeviceGuard g(r->ctx->device);
     if (r->pending) cudaEventSynchronize(r->ev_done);
+    for (qe_result *m : r->ring) qe_result_destroy(m);
+    r->ring.clear();
+    if (r->h_super) cudaFreeHost(r->h_super);
     for (ResultColumn &c : r->cols) { release(r->ctx, c.values); release(r->ctx, c.valid); }
     release(r->ctx, r->sel);
     release(r->ctx, r->ctl);
@@ -758,6 +847,9 @@ static void serialize_interp(const qe::BoundPipeline &bp, std::vector<uint32_t> 
     for (const qe::BoundExpr &e : bp.proj) put(e);
 }
 
+// Generated kernel for (pipeline, mode, tile shape) on this context's device.  Returns QE_OK, QE_ERR_JIT when the
+// compilation or the load failed, or -1 when the cubin is in no cache and there is no NVRTC to make it (the caller
+// then runs the interpreter kernels).
 static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMode mode, const qe::TileShape &shape,
                           JitEntry **out, size_t dyn_smem = 0)
 {
@@ -767,32 +859,90 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
              shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0) + (shape.pring ? 200000 : 0) + (shape.scopies == 32 ? 400000 + 1000000 * shape.lane_acc_kb : shape.scopies == 8 ? 800000 : 0));
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
-    if (it != ctx->jit_cache.end()) { *out = &it->second; return QE_OK; }
+    if (it != ctx->jit_cache.end()) {
+        ctx->jit_lru.splice(ctx->jit_lru.end(), ctx->jit_lru, it->second.lru);      // most recently used
+        *out = &it->second;
+        return QE_OK;
+    }
     const std::string src = qe::generate_source(bp, mode, shape);
-    std::vector<char> cubin;
-    std::string log;
     std::vector<std::string> extra;
     if (ctx->opt_debug_flags) extra.push_back("-DQE_DEBUG_FLAGS=" + std::to_string(ctx->opt_debug_flags));
-    if (!qe::jit_compile(src, cubin, log, extra)) {
+    qe::CubinRef cubin;
+    std::string log;
+    int origin = 0;
+    const int crc = qe::cubin_get(src, extra, cubin, &origin, log);
+    if (crc < 0) { tls_error = "no cached kernel for this pipeline and no compiler: " + log; return -1; }
+    if (crc) {
         if (getenv("QE_DUMP_JIT")) fprintf(stderr, "%s\n", src.c_str());
         return fail(QE_ERR_JIT, "compiling the generated pipeline failed: " + log);
+    }
+    // bounded: the least recently used kernels are unloaded (nothing of theirs may still be running)
+    while ((int64_t)ctx->jit_cache.size() >= ctx->opt_jit_cache_entries && !ctx->jit_lru.empty()) {
+        cudaStreamSynchronize(ctx->stream);
+        auto victim = ctx->jit_cache.find(ctx->jit_lru.front());
+        if (victim != ctx->jit_cache.end()) {
+            qe::jit_unload(victim->second.kernel);
+            ctx->jit_cache.erase(victim);
+        }
+        ctx->jit_lru.pop_front();
     }
     JitEntry e;
     e.shape = shape;
     std::string err;
-    if (!qe::jit_load(cubin, qe::jit_entry_name(mode, shape), dyn_smem ? dyn_smem : qe::staged_smem_bytes(bp, shape),
+    if (!qe::jit_load(*cubin, qe::jit_entry_name(mode, shape), dyn_smem ? dyn_smem : qe::staged_smem_bytes(bp, shape),
                       (mode == qe::KM_FILTER || mode == qe::KM_GROUPBY_REG || shape.pring) ? shape.block_threads()
                       : (mode == qe::KM_GROUPBY_PRIVATE || mode == qe::KM_GROUPBY_SHARED) ? shape.gthreads : QE_BLOCK,
                       e.kernel, err))
         return fail(QE_ERR_JIT, err);
+    ctx->jit_loads++;
     if (getenv("QE_DUMP_JIT"))
-        fprintf(stderr, "[qegpu] jit %s: %d regs, %d CTAs/SM\n", key.c_str(), e.kernel.regs, e.kernel.blocks_per_sm);
+        fprintf(stderr, "[qegpu] kernel %s: origin %d (0 memory, 1 aot, 2 disk, 3 nvrtc), %d regs, %d CTAs/SM\n", key.c_str(), origin,
+                e.kernel.regs, e.kernel.blocks_per_sm);
+    ctx->jit_lru.push_back(key);
+    e.lru = std::prev(ctx->jit_lru.end());
     auto ins = ctx->jit_cache.emplace(key, e);
     *out = &ins.first->second;
     return QE_OK;
 }
 
-extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_pipeline_desc *d, qe_result **result)
+// literal values of the bound pipeline -> kernel parameters (see Literal in qe_program.h)
+static void fill_literals(const qe::BoundPipeline &bp, QeParams &p)
+{
+    for (size_t i = 0; i < bp.lits.size() && i < QE_MAX_LITS; i++) {
+        const qe::Literal &l = bp.lits[i];
+        if (l.is_str) { p.lit_lo[i] = l.code; p.lit_hi[i] = l.code; continue; }
+        p.lit_f64[i] = l.k;
+        if (l.int_ok()) { p.lit_lo[i] = (long long)std::floor(l.k); p.lit_hi[i] = (long long)std::ceil(l.k); }
+        if (l.mod_ok()) { p.lit_abs[i] = std::fabs(l.k); p.lit_inv[i] = 1.0 / std::fabs(l.k); }
+    }
+}
+
+// signature + literal values: "the same query", for the hints a reused result carries from its last run
+static std::string query_key(const qe::BoundPipeline &bp)
+{
+    std::string s = bp.signature() + "|L";
+    char b[24];
+    for (const qe::Literal &l : bp.lits) {
+        unsigned long long bits;
+        memcpy(&bits, &l.k, sizeof bits);
+        snprintf(b, sizeof b, "%llx.%d,", bits, l.code);
+        s += b;
+    }
+    return s;
+}
+
+// What qe_pipeline_stream adds to a run (not part of the ABI).
+struct RunExtra {
+    const qe_u64 *chain_base = nullptr;   // bounded streaming: device word holding the rows kept by the earlier chunks; this
+                                          // run writes into buffers of its own and keeps only the bit phase (out_base_mask 7)
+    bool chained = false;
+    int64_t super_offset = 0;             // aggregation: where this chunk's super-tile partials go in the host list ...
+    int64_t super_total = 0;              // ... and the length of the whole list (0: this run alone)
+};
+
+static int ensure_host_super(qe_result *r, size_t doubles);
+
+static int run_pipeline(qe_ctx *ctx, const qe_table *table, const qe_pipeline_desc *d, qe_result **result, const RunExtra *extra)
 {
     if (!ctx || !table || !d || !result) return fail(QE_ERR_INVALID_ARGUMENT, "NULL argument");
     if (table->ctx != ctx) return fail(QE_ERR_INVALID_ARGUMENT, "table belongs to another context");
@@ -806,8 +956,12 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
         schema[c].type = table->cols[c].type;
         schema[c].nullable = table->cols[c].nullable != 0;
     }
+    // QE_RUN_NO_VALUES: the caller holds the table (MemoryTable lives in host memory, M/data/MemoryTable.kt:7) and
+    // FilterOperator hands back the very row it was given (M/operator/FilterOperator.kt:20-22), so the selection
+    // vector alone is its output: the projections are neither evaluated nor written
+    const bool no_values = (d->flags & QE_RUN_NO_VALUES) && d->filter && d->nagg == 0;
     std::vector<const qe::Program *> proj;
-    for (int k = 0; k < d->nproj; k++) {
+    for (int k = 0; k < d->nproj && !no_values; k++) {
         if (!d->proj || !d->proj[k]) return fail(QE_ERR_INVALID_ARGUMENT, "NULL projection program");
         proj.push_back(&d->proj[k]->prog);
     }
@@ -825,45 +979,55 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
     if (row_begin < 0 || row_end < row_begin || row_end > table->nrows) return fail(QE_ERR_INVALID_ARGUMENT, "bad row range");
     if (row_begin % 128) return fail(QE_ERR_INVALID_ARGUMENT, "row_begin must be a multiple of 128");
     const int64_t n = row_end - row_begin;
+    if (mode == qe::KM_FILTER && !(d->flags & QE_RUN_NO_SELECTION) &&
+        (row_begin + d->sel_offset < 0 || row_end + d->sel_offset > 0x100000000LL))
+        return fail(QE_ERR_INVALID_ARGUMENT, "selection vector values (row + sel_offset) must fit 32 bits");
 
-    // ---- kernel: generated code, or the interpreter
+    // ---- kernel: generated code (from the caches or NVRTC), or the interpreter
     bool use_jit = ctx->opt_jit != 0 && !(d->flags & QE_RUN_INTERPRETER);
-    if (use_jit) {
-        std::string why;
-        if (!qe::jit_available(&why)) {
-            if (!ctx->warned_no_nvrtc) {
-                fprintf(stderr, "[qegpu] warning: %s; using the interpreter kernels (slower, still on the GPU)\n", why.c_str());
-                ctx->warned_no_nvrtc = true;
-            }
-            use_jit = false;
-        }
-    }
     qe::TileShape shape;
     JitEntry *jit = nullptr;
     int blocks_per_sm = 1;
+    const std::string qkey = mode == qe::KM_FILTER ? query_key(bp) : std::string();
     if (use_jit) {
         // a reused result knows the selectivity of its last run (waiting for that run is what a reuse does anyway)
         double sel_hint = -1.0;
         if (qe_result *prev = *result; prev && prev->ctx == ctx && mode == qe::KM_FILTER && prev->mode == (int)mode &&
-                                       !(d->flags & QE_RUN_APPEND) && prev->f_sig == bp.signature()) {
+                                       !(d->flags & QE_RUN_APPEND) && !(extra && extra->chained) && prev->f_sig == qkey) {
             if (prev->pending) { QE_CUDA(cudaEventSynchronize(prev->ev_done)); prev->pending = false; }
             if (prev->batch_rows > 0 && (int64_t)prev->host->count <= prev->capacity)
                 prev->f_sel = (double)prev->host->count / (double)prev->batch_rows;
             sel_hint = prev->f_sel;
+        } else if (qe_result *prev = *result; prev && prev->f_sig == qkey) {
+            sel_hint = prev->f_sel;                           // appended / chained chunks keep the shape of the first
         }
         shape = choose_shape(ctx, bp, mode, sel_hint);
         // Dense projection: four CTAs per SM (64 registers) hide the latency of the FP64 divide / MOD sequences better
         // than three (measured on the nullable tree: 6.83 -> 6.34 ms); kept only when the tighter bound does not spill.
+        rc = QE_OK;
         if (mode == qe::KM_PROJECT && !ctx->opt_min_blocks && !shape.pring) {
             qe::TileShape tight = shape;
             tight.min_blocks = 4;
             JitEntry *cand = nullptr;
-            if (get_jit_kernel(ctx, bp, mode, tight, &cand) == QE_OK && cand->kernel.local_bytes == 0) shape = tight;
+            rc = get_jit_kernel(ctx, bp, mode, tight, &cand);
+            if (rc == QE_OK && cand->kernel.local_bytes == 0) { shape = tight; jit = cand; }
+            else if (rc > 0) return rc;
         }
-        rc = get_jit_kernel(ctx, bp, mode, shape, &jit);
-        if (rc) return rc;
-        blocks_per_sm = jit->kernel.blocks_per_sm;
-    } else {
+        if (!jit && rc >= 0) rc = get_jit_kernel(ctx, bp, mode, shape, &jit);
+        if (rc > 0) return rc;
+        if (rc < 0) {                                          // no compiler and not in the AOT table / disk cache
+            if (!ctx->warned_no_nvrtc) {
+                fprintf(stderr, "[qegpu] warning: %s; using the interpreter kernels (slower, still on the GPU)\n", tls_error.c_str());
+                ctx->warned_no_nvrtc = true;
+            }
+            use_jit = false;
+            jit = nullptr;
+        } else {
+            blocks_per_sm = jit->kernel.blocks_per_sm;
+        }
+    }
+    if (!use_jit) {
+        shape = qe::TileShape();
         shape.steps = QE_INTERP_STEPS;
         shape.vec = QE_INTERP_VEC;
         blocks_per_sm = qe::interp_blocks_per_sm((int)mode);
@@ -874,7 +1038,11 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
     const uint32_t ntiles = (uint32_t)ntiles64;
     if (ctx->opt_grid_per_sm) blocks_per_sm = std::min<int>(blocks_per_sm, (int)ctx->opt_grid_per_sm);
     if (mode == qe::KM_AGG) blocks_per_sm = std::min(blocks_per_sm, 8);
-    int grid = (int)std::min<int64_t>(std::max<int64_t>(ntiles64, 1), (int64_t)ctx->num_sms * blocks_per_sm);
+    // aggregation: CTAs take whole sub-tiles of QE_AGG_SUB_ROWS rows (qe_agg_body)
+    if (mode == qe::KM_AGG && (QE_AGG_SUB_ROWS % tile_rows)) return fail(QE_ERR_STATE, "aggregation tile does not divide a sub-tile");
+    const int64_t nsub = mode == qe::KM_AGG ? (ntiles64 + QE_AGG_SUB_ROWS / tile_rows - 1) / (QE_AGG_SUB_ROWS / tile_rows) : 0;
+    const int64_t nsuper = (nsub + QE_AGG_SUPER_ROWS / QE_AGG_SUB_ROWS - 1) / (QE_AGG_SUPER_ROWS / QE_AGG_SUB_ROWS);
+    int grid = (int)std::min<int64_t>(std::max<int64_t>(mode == qe::KM_AGG ? nsub : ntiles64, 1), (int64_t)ctx->num_sms * blocks_per_sm);
 
     // ---- result buffers (reused when the caller passes the previous result back)
     qe_result *r = *result;
@@ -885,7 +1053,8 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
         if (!r || r->mode != (int)mode || r->cols.size() != bp.outs.size() || !r->ctl.ptr)
             return fail(QE_ERR_STATE, "QE_RUN_APPEND needs the result of an earlier run of the same pipeline");
     }
-    if (r && r->pending && !append) { QE_CUDA(cudaEventSynchronize(r->ev_done)); r->pending = false; }
+    const bool keep_pending = append || (extra && mode == qe::KM_AGG && extra->super_offset > 0);   // later chunk of one stream call
+    if (r && r->pending && !keep_pending) { QE_CUDA(cudaEventSynchronize(r->ev_done)); r->pending = false; }
     if (r) fold_timing(r);
     if (!r) {
         r = new qe_result();
@@ -908,10 +1077,12 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
             return fail(QE_ERR_CAPACITY, "QE_RUN_APPEND: the first run's out_capacity_rows does not cover this batch");
     }
     r->mode = (int)mode;
-    if (mode == qe::KM_FILTER) { const std::string sg = bp.signature(); if (r->f_sig != sg) { r->f_sig = sg; r->f_sel = -1.0; } }
+    if (mode == qe::KM_FILTER && r->f_sig != qkey) { r->f_sig = qkey; r->f_sel = -1.0; }
     r->used_jit = use_jit;
     r->batch_rows = emitted_before + n;
     r->agg_fns = bp.agg_fns;
+    r->chained = extra && extra->chained;
+    r->streamed = false;
     // capacity is fixed by the first run (out_capacity_rows may exceed the batch: later batches are appended)
     const int64_t capacity = append ? r->capacity
                            : mode == qe::KM_FILTER ? (d->out_capacity_rows > 0 ? d->out_capacity_rows : n)
@@ -935,8 +1106,10 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
     }
     p.nrows = n;
     p.ntiles = ntiles;
-    p.sel_base = (uint32_t)row_begin;
+    p.sel_base = (uint32_t)(row_begin + d->sel_offset);
     p.out_capacity = capacity;
+    p.out_base_mask = ~0ull;
+    fill_literals(bp, p);
 
     const size_t bitmap_bytes = (size_t)((capacity + 31) / 32 + 16) * 4;
     if (mode != qe::KM_AGG) {
@@ -967,8 +1140,8 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
     if (mode == qe::KM_FILTER && !(d->flags & QE_RUN_NO_SELECTION)) {
         if ((rc = ensure(ctx, r->sel, (size_t)std::max<int64_t>(capacity, 1) * 4))) return rc;
         p.sel = (qe_u32 *)r->sel.ptr;
-    } else if (mode != qe::KM_FILTER) {
-        release(ctx, r->sel);
+    } else if (!append) {
+        release(ctx, r->sel);                       // no selection vector this time: an earlier run's must not be readable
     }
     // control block: [0] kept-row count (u64)  [8] ticket (u32)  [16] append base (u64)  [32...] tile descriptors
     const size_t ctl_bytes = 32 + (mode == qe::KM_FILTER ? (size_t)ntiles * 8 : 0);
@@ -988,13 +1161,31 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
         p.out_base = (const qe_u64 *)((char *)r->ctl.ptr + 16);
     } else {
         QE_CUDA(cudaMemsetAsync(r->ctl.ptr, 0, ctl_bytes, ctx->stream));
+        if (extra && extra->chained && mode == qe::KM_FILTER) {
+            // a streamed chunk with buffers of its own: positions start at (rows kept so far) & 7, so that compacted bit
+            // columns keep their phase and the chunks' bytes can be laid end to end on the host; the kept-row count the
+            // kernel leaves in ctl[0] is still the running total
+            if (extra->chain_base) {
+                QE_CUDA(cudaMemcpyAsync((char *)r->ctl.ptr + 16, extra->chain_base, 8, cudaMemcpyDeviceToDevice, ctx->stream));
+                QE_CUDA(cudaMemcpyAsync(r->ctl.ptr, extra->chain_base, 8, cudaMemcpyDeviceToDevice, ctx->stream));   // n == 0: the total stands
+                p.out_base = (const qe_u64 *)((char *)r->ctl.ptr + 16);
+            }
+            p.out_base_mask = 7ull;
+        }
     }
     p.out_count = (qe_u64 *)r->ctl.ptr;
     p.ticket = (qe_u32 *)((char *)r->ctl.ptr + 8);
     p.tile_state = (qe_u64 *)((char *)r->ctl.ptr + 32);
+    const int nagg = (int)bp.agg_fns.size();
+    const int64_t super_off = extra ? extra->super_offset : 0;
     if (mode == qe::KM_AGG) {
-        if ((rc = ensure(ctx, r->partials, (size_t)grid * QE_MAX_AGGS * 4 * sizeof(double)))) return rc;
-        if ((rc = ensure(ctx, r->final_aggs, QE_MAX_AGGS * 4 * sizeof(double)))) return rc;
+        if ((rc = ensure(ctx, r->partials, (size_t)std::max<int64_t>(nsub, 1) * (size_t)nagg * 4 * sizeof(double)))) return rc;
+        if ((rc = ensure(ctx, r->final_aggs, (size_t)std::max<int64_t>(nsuper, 1) * (size_t)nagg * 4 * sizeof(double)))) return rc;
+        const int64_t total = extra && extra->super_total > 0 ? extra->super_total : nsuper;
+        if (super_off + nsuper > total) return fail(QE_ERR_STATE, "super-tile partial list too short");
+        if ((rc = ensure_host_super(r, (size_t)std::max<int64_t>(total, 1) * (size_t)nagg * 4))) return rc;
+        r->n_super = super_off + nsuper;
+        r->agg_folded = false;
         p.agg_partials = (double *)r->partials.ptr;
     }
     if (ctx->opt_debug_flags & 16) {
@@ -1024,20 +1215,12 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
         ctx->launches++;
     }
     QE_CUDA(cudaEventRecord(r->ev_end, ctx->stream));
-    if (mode == qe::KM_AGG) {
-        if (n > 0) {
-            QE_CUDA(qe::launch_agg_final((const double *)r->partials.ptr, grid, (int)bp.agg_fns.size(),
-                                         (double *)r->final_aggs.ptr, ctx->stream));
-            ctx->launches++;
-            QE_CUDA(cudaMemcpyAsync(r->host->agg, r->final_aggs.ptr, sizeof r->host->agg, cudaMemcpyDeviceToHost, ctx->stream));
-        } else {
-            for (int k = 0; k < QE_MAX_AGGS; k++) {
-                r->host->agg[k][0] = 0.0;
-                r->host->agg[k][1] = 0.0;      // count bits = 0
-                r->host->agg[k][2] = 0.0;
-                r->host->agg[k][3] = 0.0;
-            }
-        }
+    if (mode == qe::KM_AGG && n > 0) {
+        // second level of the fixed-shape fold on the device, the (few) super-tile partials to the host list
+        QE_CUDA(qe::launch_agg_final((const double *)r->partials.ptr, nsub, nagg, (double *)r->final_aggs.ptr, ctx->stream));
+        ctx->launches++;
+        QE_CUDA(cudaMemcpyAsync(r->h_super + (size_t)super_off * (size_t)nagg * 4, r->final_aggs.ptr,
+                                (size_t)nsuper * (size_t)nagg * 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     }
     QE_CUDA(cudaMemcpyAsync(&r->host->count, r->ctl.ptr, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
     QE_CUDA(cudaEventRecord(r->ev_done, ctx->stream));
@@ -1051,6 +1234,11 @@ extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_p
     cleanup.armed = false;
     *result = r;
     return QE_OK;
+}
+
+extern "C" int qe_pipeline_run_ex(qe_ctx *ctx, const qe_table *table, const qe_pipeline_desc *d, qe_result **result)
+{
+    return run_pipeline(ctx, table, d, result, nullptr);
 }
 
 extern "C" int qe_pipeline_run(qe_ctx *ctx, const qe_table *table, const qe_program *filter,
@@ -1186,9 +1374,6 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     if (row_begin % 128) return fail(QE_ERR_INVALID_ARGUMENT, "row_begin must be a multiple of 128");
     const int64_t n = row_end - row_begin;
 
-    std::string why;
-    if (!qe::jit_available(&why)) return fail(QE_ERR_JIT, "group-by needs NVRTC (generated code only): " + why);
-
     const int64_t max_groups = d->max_groups > 0 ? d->max_groups : 65536;
     if (max_groups > (1ll << 28)) return fail(QE_ERR_INVALID_ARGUMENT, "max_groups too large");
     int64_t nslots = 1024;
@@ -1255,10 +1440,12 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     p.g_ctl = (qe_u32 *)r->g_ctl.ptr;
     p.g_slot_mask = (qe_u32)(nslots - 1);
     p.g_max_groups = (qe_u32)max_groups;
+    p.out_base_mask = ~0ull;
+    fill_literals(bp, p);
 
     uint32_t ctl[4] = {0, 0, 0, 0};
     // a result that is reused remembers which variants this group-by has overflowed
-    const std::string sig = bp.signature();
+    const std::string sig = query_key(bp);
     // levels: 0 registers, 1 private 512 threads, 2 private 256 threads, 3 lane copies (32 per CTA), 4 eight copies,
     // 5 CTA-shared (one copy), 6 global atomics
     int level = r->g_overflowed == sig ? r->g_level : 0;
@@ -1301,8 +1488,14 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
                 shape.vec = qe::jit_wide_loads_supported() ? 4 : 2;
             }
         }
+        // a tile (and the prefetch of the next one) must stay inside the padding of the column allocations
+        if (shape.rows_per_tile() > kPadRows)
+            return fail(QE_ERR_INVALID_ARGUMENT, "group-by tile of " + std::to_string(shape.rows_per_tile()) + " rows (threads / 32 * steps * 32 * vec) exceeds " +
+                                                 std::to_string(kPadRows) + ": lower the \"steps\" / \"vec\" options");
         JitEntry *jit = nullptr;
-        if ((rc = get_jit_kernel(ctx, bp, mode, shape, &jit, (atomic || regs) ? 0 : lanes ? plan.shared_smem32() : lanes8 ? plan.shared_smem8() : shared ? plan.shared_smem() : plan.private_smem()))) return rc;
+        rc = get_jit_kernel(ctx, bp, mode, shape, &jit, (atomic || regs) ? 0 : lanes ? plan.shared_smem32() : lanes8 ? plan.shared_smem8() : shared ? plan.shared_smem() : plan.private_smem());
+        if (rc < 0) return fail(QE_ERR_JIT, "group-by needs generated code: " + tls_error);
+        if (rc) return rc;
         const int64_t tile_rows = shape.rows_per_tile();
         const int64_t ntiles64 = (n + tile_rows - 1) / tile_rows;
         int blocks_per_sm = jit->kernel.blocks_per_sm;
@@ -1407,6 +1600,7 @@ static int wait_result(qe_result *r)
         QE_CUDA(cudaEventSynchronize(r->ev_done));
         r->pending = false;
     }
+    fold_aggs(r);
     return QE_OK;
 }
 
@@ -1423,7 +1617,7 @@ extern "C" int qe_result_num_rows(qe_result *r, int64_t *nrows)
     int rc = wait_result(r);
     if (rc) return rc;
     if (nrows) *nrows = emitted_rows(r);
-    if (r->mode == qe::KM_FILTER && (int64_t)r->host->count > r->capacity) {
+    if (r->mode == qe::KM_FILTER && !r->chained && !r->streamed && (int64_t)r->host->count > r->capacity) {
         return fail(QE_ERR_CAPACITY, "filter kept " + std::to_string(r->host->count) + " rows but out_capacity_rows is " +
                                      std::to_string(r->capacity) + "; rerun with a larger capacity");
     }
@@ -1457,6 +1651,7 @@ extern "C" int qe_result_column(qe_result *r, int k, void *dst_values, uint8_t *
     int rc = qe_result_num_rows(r, &n);
     if (rc) return rc;
     if (k < 0 || k >= (int)r->cols.size()) return fail(QE_ERR_INVALID_ARGUMENT, "column index out of range");
+    if (r->streamed) return fail(QE_ERR_STATE, "streamed result: the rows are in the host buffers given to qe_pipeline_stream");
     qe_ctx *ctx = r->ctx;
     DeviceGuard g(ctx->device);
     const ResultColumn &c = r->cols[k];
@@ -1495,6 +1690,7 @@ extern "C" int qe_result_selection(qe_result *r, uint32_t *dst)
     int rc = qe_result_num_rows(r, &n);
     if (rc) return rc;
     if (r->mode != qe::KM_FILTER || !r->sel.ptr) return fail(QE_ERR_STATE, "this result has no selection vector");
+    if (r->streamed) return fail(QE_ERR_STATE, "streamed result: the selection vector is in the host buffer given to qe_pipeline_stream");
     if (!dst) return fail(QE_ERR_INVALID_ARGUMENT, "dst is NULL");
     if (n == 0) return QE_OK;
     DeviceGuard g(r->ctx->device);
@@ -1523,6 +1719,25 @@ extern "C" int qe_result_agg_partial(qe_result *r, int k, qe_agg_partial *out)
     if (r->batch_rows == 0) {
         out->count = 0;
         out->sum = 0.0;
+    }
+    return QE_OK;
+}
+
+extern "C" int qe_result_agg_partials(qe_result *r, int k, qe_agg_partial *dst, int64_t capacity, int64_t *n)
+{
+    int rc = wait_result(r);
+    if (rc) return rc;
+    if (r->mode != qe::KM_AGG) return fail(QE_ERR_STATE, "this result is not an aggregation");
+    const size_t nagg = r->agg_fns.size();
+    if (k < 0 || k >= (int)nagg) return fail(QE_ERR_INVALID_ARGUMENT, "aggregate index out of range");
+    const int64_t have = r->batch_rows == 0 ? 0 : r->n_super;
+    if (n) *n = have;
+    for (int64_t s = 0; dst && s < have && s < capacity; s++) {
+        const double *src = r->h_super + ((size_t)s * nagg + (size_t)k) * 4;
+        dst[s].sum = src[0];
+        memcpy(&dst[s].count, &src[1], sizeof dst[s].count);
+        dst[s].min = src[2];
+        dst[s].max = src[3];
     }
     return QE_OK;
 }
@@ -1575,7 +1790,7 @@ extern "C" int qe_agg_combine(int agg_fn, const qe_agg_partial *partials, int n,
 
 extern "C" void *qe_result_device_ptr(qe_result *r, int k, int which)
 {
-    if (!r) return nullptr;
+    if (!r || r->streamed) return nullptr;
     if (which == 2) return r->sel.ptr;
     if (k < 0 || k >= (int)r->cols.size()) return nullptr;
     return which == 0 ? r->cols[k].values.ptr : r->cols[k].valid.ptr;
@@ -1597,8 +1812,15 @@ extern "C" int qe_result_kernel_stats(qe_result *r, double *total_ms, int64_t *r
     if (rc) return rc;
     DeviceGuard g(r->ctx->device);
     fold_timing(r);
-    if (total_ms) *total_ms = r->total_kernel_ms;
-    if (runs) *runs = r->kernel_runs;
+    double ms = r->total_kernel_ms;
+    int64_t nr = r->kernel_runs;
+    for (qe_result *m : r->ring) {                             // bounded streaming: the other output buffer sets ran chunks too
+        fold_timing(m);
+        ms += m->total_kernel_ms;
+        nr += m->kernel_runs;
+    }
+    if (total_ms) *total_ms = ms;
+    if (runs) *runs = nr;
     return QE_OK;
 }
 
@@ -1618,39 +1840,89 @@ extern "C" int qe_result_used_jit(const qe_result *r) { return r && r->used_jit 
 // Host columns in, host results out, in row-range chunks: the upload of chunk c+1 (copy engine, h2d
 // stream), the kernels of chunk c (compute stream) and the download of the rows chunk c-1 produced
 // (other copy engine, d2h stream) run at the same time, so a scan that starts and ends in host memory
-// is bound by the busier PCIe direction instead of by the sum of both plus the kernels.  Every chunk
-// after the first is run with QE_RUN_APPEND, so the device-side results are the same as one run over
-// the whole table.
+// is bound by the busier PCIe direction instead of by the sum of both plus the kernels.
+//   resident mode: every chunk after the first runs with QE_RUN_APPEND, the device-side results are the
+//     same as one run over the whole table.
+//   bounded mode: the table is a ring of chunk slots and every pipeline has as many output buffer sets;
+//     a chunk's kernel starts its output positions at (rows kept so far) & 7, so compacted bit columns keep
+//     their phase and the chunks' bytes are laid end to end in the caller's buffers (the one byte two chunks
+//     share goes through a scratch byte and is OR-ed in at the end).
 
 namespace {
 
-struct StreamSinkState {
-    int64_t rows_done = 0;      // rows already downloaded
+struct ByteFix { uint8_t *dst; size_t scratch; };
+
+struct StreamState {
+    qe_ctx *ctx = nullptr;
+    std::vector<cudaEvent_t> events;
+    unsigned long long *counts = nullptr;      // pinned: rows kept up to and including chunk c, per pipeline
+    uint8_t *scratch = nullptr;                // pinned: first bytes of bit columns that share a byte with the chunk before
+    size_t scratch_used = 0, scratch_cap = 0;
+    std::vector<ByteFix> fixes;
+    ~StreamState()
+    {
+        if (ctx) {
+            if (ctx->h2d) cudaStreamSynchronize(ctx->h2d);
+            cudaStreamSynchronize(ctx->stream);
+            if (ctx->d2h) cudaStreamSynchronize(ctx->d2h);
+        }
+        for (cudaEvent_t e : events) if (e) cudaEventDestroy(e);
+        if (counts) cudaFreeHost(counts);
+        if (scratch) cudaFreeHost(scratch);
+    }
+    cudaError_t new_event(cudaEvent_t *e)
+    {
+        cudaError_t rc = cudaEventCreateWithFlags(e, cudaEventDisableTiming);
+        if (rc == cudaSuccess) events.push_back(*e);
+        return rc;
+    }
 };
 
-int download_range(qe_ctx *ctx, qe_result *r, int q, const qe_stream_desc *sd, int64_t from, int64_t to)
+// bits [from, to) of a host bitmap <- bits [src_from, ...) of a device bitmap, src_from == from (mod 8).
+// `own_first_byte`: the device byte holding bit src_from has no bits of earlier chunks (bounded mode), so it must be
+// OR-ed into the host byte instead of replacing it.
+int download_bits(StreamState &st, uint8_t *host, const void *dev, int64_t from, int64_t to, int64_t src_from, bool own_first_byte)
 {
     if (to <= from) return QE_OK;
+    size_t hb = (size_t)(from / 8), db = (size_t)(src_from / 8);
+    size_t nb = (size_t)((to + 7) / 8) - hb;
+    if (own_first_byte && (from % 8)) {
+        if (st.scratch_used >= st.scratch_cap) return fail(QE_ERR_STATE, "stream scratch exhausted");
+        QE_CUDA(cudaMemcpyAsync(st.scratch + st.scratch_used, (const char *)dev + db, 1, cudaMemcpyDeviceToHost, st.ctx->d2h));
+        st.fixes.push_back(ByteFix{host + hb, st.scratch_used++});
+        hb++; db++; nb--;
+    }
+    if (nb) QE_CUDA(cudaMemcpyAsync(host + hb, (const char *)dev + db, nb, cudaMemcpyDeviceToHost, st.ctx->d2h));
+    return QE_OK;
+}
+
+// output rows [from, to) of pipeline q, which sit at position src_from of `r`'s device buffers, to the caller's buffers
+int download_range(StreamState &st, const qe_result *r, int q, const qe_stream_desc *sd, int64_t from, int64_t to, int64_t src_from,
+                   bool own_first_byte)
+{
+    if (to <= from) return QE_OK;
+    qe_ctx *ctx = st.ctx;
     if (sd->host_selection && sd->host_selection[q] && r->sel.ptr)
-        QE_CUDA(cudaMemcpyAsync(sd->host_selection[q] + from, (const uint32_t *)r->sel.ptr + from, (size_t)(to - from) * 4,
+        QE_CUDA(cudaMemcpyAsync(sd->host_selection[q] + from, (const uint32_t *)r->sel.ptr + src_from, (size_t)(to - from) * 4,
                                 cudaMemcpyDeviceToHost, ctx->d2h));
     for (size_t k = 0; k < r->cols.size(); k++) {
         const ResultColumn &c = r->cols[k];
         void *hv = sd->host_out_values && sd->host_out_values[q] ? sd->host_out_values[q][k] : nullptr;
         uint8_t *hn = sd->host_out_validity && sd->host_out_validity[q] ? sd->host_out_validity[q][k] : nullptr;
-        const size_t b0 = (size_t)(from / 8), b1 = (size_t)((to + 7) / 8);     // bitmaps: whole bytes, the shared
-        if (hv) {                                                               // boundary byte is copied again later
+        int rc = QE_OK;
+        if (hv) {
             if (c.type == QE_TYPE_BOOLEAN)
-                QE_CUDA(cudaMemcpyAsync((char *)hv + b0, (const char *)c.values.ptr + b0, b1 - b0, cudaMemcpyDeviceToHost, ctx->d2h));
+                rc = download_bits(st, (uint8_t *)hv, c.values.ptr, from, to, src_from, own_first_byte);
             else
                 QE_CUDA(cudaMemcpyAsync((char *)hv + (size_t)from * type_width(c.type),
-                                        (const char *)c.values.ptr + (size_t)from * type_width(c.type),
+                                        (const char *)c.values.ptr + (size_t)src_from * type_width(c.type),
                                         (size_t)(to - from) * type_width(c.type), cudaMemcpyDeviceToHost, ctx->d2h));
+            if (rc) return rc;
         }
         if (hn) {
-            if (c.has_validity)
-                QE_CUDA(cudaMemcpyAsync(hn + b0, (const char *)c.valid.ptr + b0, b1 - b0, cudaMemcpyDeviceToHost, ctx->d2h));
-            else if (to > from) {                                               // statically non-null: all ones
+            if (c.has_validity) {
+                if ((rc = download_bits(st, hn, c.valid.ptr, from, to, src_from, own_first_byte))) return rc;
+            } else {                                                            // statically non-null: all ones
                 for (int64_t i = from; i < to && (i % 8); i++) hn[i / 8] |= (uint8_t)(1u << (i % 8));
                 const int64_t a = (from + 7) / 8 * 8;
                 if (to > a) {
@@ -1671,138 +1943,171 @@ extern "C" int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_
         return fail(QE_ERR_INVALID_ARGUMENT, "NULL argument");
     if (table->ctx != ctx) return fail(QE_ERR_INVALID_ARGUMENT, "table belongs to another context");
     if (sd->npipelines > 16) return fail(QE_ERR_UNSUPPORTED, "at most 16 pipelines per stream call");
-    int64_t chunk = sd->chunk_rows > 0 ? sd->chunk_rows : (int64_t)32 << 20;
+    const int64_t chunk = sd->chunk_rows > 0 ? sd->chunk_rows : (int64_t)32 << 20;
     if (chunk % 128) return fail(QE_ERR_INVALID_ARGUMENT, "chunk_rows must be a multiple of 128");
+    if (sd->total_rows < 0) return fail(QE_ERR_INVALID_ARGUMENT, "total_rows must not be negative");
+    const bool bounded = sd->total_rows > 0;
+    const bool relative = (sd->flags & QE_STREAM_CHUNK_RELATIVE) != 0;
+    const int np = sd->npipelines;
+    const int64_t n = bounded ? sd->total_rows : table->nrows;
+    int nslots = 1;
+    if (bounded) {
+        const int64_t fit = table->nrows / chunk;
+        if (fit < 2) return fail(QE_ERR_INVALID_ARGUMENT, "bounded streaming: the table must hold at least two chunks (nrows >= 2 * chunk_rows)");
+        nslots = (int)std::min<int64_t>(fit, 3);
+    }
+    if (chunk > 0xffffffffLL) return fail(QE_ERR_INVALID_ARGUMENT, "chunk_rows must fit 32 bits");
+    const int64_t nchunks = std::max<int64_t>(1, (n + chunk - 1) / chunk);
+    if (nchunks > (1 << 20)) return fail(QE_ERR_INVALID_ARGUMENT, "more than 2^20 chunks: use a larger chunk_rows");
+    for (int q = 0; q < np; q++) {
+        const qe_pipeline_desc &d = sd->pipelines[q];
+        if (n > 0x100000000LL && !relative && d.filter && d.nagg == 0 && !(d.flags & QE_RUN_NO_SELECTION))
+            return fail(QE_ERR_INVALID_ARGUMENT, "more than 2^32 rows: selection vectors need QE_STREAM_CHUNK_RELATIVE");
+    }
+    const int64_t spc = (chunk + QE_AGG_SUPER_ROWS - 1) / QE_AGG_SUPER_ROWS;       // super-tile partials per chunk
     DeviceGuard g(ctx->device);
     if (!ctx->h2d) QE_CUDA(cudaStreamCreateWithFlags(&ctx->h2d, cudaStreamNonBlocking));
     if (!ctx->d2h) QE_CUDA(cudaStreamCreateWithFlags(&ctx->d2h, cudaStreamNonBlocking));
-    const int np = sd->npipelines;
-    const int64_t n = table->nrows;
-    const int nchunks = (int)std::max<int64_t>(1, (n + chunk - 1) / chunk);
 
-    unsigned long long *counts = nullptr;                      // pinned: kept rows after chunk c of pipeline q
-    QE_CUDA(cudaHostAlloc((void **)&counts, sizeof(unsigned long long) * (size_t)nchunks * np, cudaHostAllocDefault));
-    // aggregations: the partials of every chunk (pinned), combined in chunk order when all chunks are done
-    double *chunk_aggs = nullptr;                              // [chunk][pipeline][QE_MAX_AGGS][4]
-    const size_t agg_stride = (size_t)QE_MAX_AGGS * 4;
-    QE_CUDA(cudaHostAlloc((void **)&chunk_aggs, sizeof(double) * agg_stride * (size_t)nchunks * np, cudaHostAllocDefault));
-    std::vector<cudaEvent_t> ev_up(nchunks, nullptr), ev_run((size_t)nchunks * np, nullptr);
-    std::vector<StreamSinkState> sink(np);
-    int rc = QE_OK;
-    auto cleanup = [&]() {
-        cudaStreamSynchronize(ctx->h2d);
-        cudaStreamSynchronize(ctx->stream);
-        cudaStreamSynchronize(ctx->d2h);
-        for (cudaEvent_t e : ev_up) if (e) cudaEventDestroy(e);
-        for (cudaEvent_t e : ev_run) if (e) cudaEventDestroy(e);
-        cudaFreeHost(counts);
-        cudaFreeHost(chunk_aggs);
-        chunk_aggs = nullptr;
+    StreamState st;
+    st.ctx = ctx;
+    QE_CUDA(cudaHostAlloc((void **)&st.counts, sizeof(unsigned long long) * (size_t)nchunks * np, cudaHostAllocDefault));
+    st.scratch_cap = bounded ? (size_t)nchunks * (size_t)np * 2 * QE_MAX_PROJECTIONS + 16 : 16;
+    QE_CUDA(cudaHostAlloc((void **)&st.scratch, st.scratch_cap, cudaHostAllocDefault));
+    std::vector<cudaEvent_t> ev_up((size_t)nchunks, nullptr), ev_run((size_t)nchunks, nullptr), ev_dl((size_t)nchunks, nullptr);
+    // bounded mode: output buffer sets of pipeline q, [0] = results[q] itself, the others are owned by it
+    std::vector<std::vector<qe_result *>> ring((size_t)np, std::vector<qe_result *>((size_t)nslots, nullptr));
+    for (int q = 0; q < np; q++) {
+        qe_result *r = sd->results[q];
+        if (r && r->ctx != ctx) return fail(QE_ERR_INVALID_ARGUMENT, "result belongs to another context");
+        if (r && r->pending) { QE_CUDA(cudaEventSynchronize(r->ev_done)); r->pending = false; }
+        for (int j = 1; r && j < nslots && (size_t)(j - 1) < r->ring.size(); j++) ring[(size_t)q][(size_t)j] = r->ring[(size_t)(j - 1)];
+    }
+    auto slot_result = [&](int q, int64_t c) -> qe_result *& {
+        const size_t j = bounded ? (size_t)(c % nslots) : 0;
+        return j == 0 ? sd->results[q] : ring[(size_t)q][j];
     };
-#define QE_STREAM_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { rc = fail_cuda(#call, e__); cleanup(); return rc; } } while (0)
 
     // earlier work on the compute stream (generators, uploads through qe_table_upload) comes first
     cudaEvent_t ev_start = nullptr;
-    QE_STREAM_CUDA(cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming));
-    ev_up.push_back(ev_start);                                 // destroyed with the others
-    QE_STREAM_CUDA(cudaEventRecord(ev_start, ctx->stream));
-    QE_STREAM_CUDA(cudaStreamWaitEvent(ctx->h2d, ev_start, 0));
+    QE_CUDA(st.new_event(&ev_start));
+    QE_CUDA(cudaEventRecord(ev_start, ctx->stream));
+    QE_CUDA(cudaStreamWaitEvent(ctx->h2d, ev_start, 0));
 
-    auto drain = [&](int c) -> int {                           // download what chunk c added, pipeline by pipeline
+    int rc = QE_OK;
+    auto drain = [&](int64_t c) -> int {                       // download what chunk c added, pipeline by pipeline
+        QE_CUDA(cudaEventSynchronize(ev_run[(size_t)c]));
+        const int64_t r0 = c * chunk, r1 = std::min(n, r0 + chunk);
         for (int q = 0; q < np; q++) {
-            cudaError_t e = cudaEventSynchronize(ev_run[(size_t)c * np + q]);
-            if (e != cudaSuccess) return fail_cuda("cudaEventSynchronize", e);
-            qe_result *r = sd->results[q];
-            if (r->mode == qe::KM_AGG) continue;                // nothing to download per chunk
-            int64_t upto = r->mode == qe::KM_PROJECT ? std::min<int64_t>((int64_t)(c + 1) * chunk, n)
-                                                     : (int64_t)counts[(size_t)c * np + q];
-            upto = std::min(upto, r->capacity);
-            int drc = download_range(ctx, r, q, sd, sink[q].rows_done, upto);
+            const qe_pipeline_desc &d = sd->pipelines[q];
+            if (d.nagg > 0) continue;                           // nothing to download per chunk
+            const qe_result *src = slot_result(q, c);
+            const bool dense = src->mode == qe::KM_PROJECT;
+            const int64_t kb = dense ? r0 : (c > 0 ? (int64_t)st.counts[(size_t)(c - 1) * np + q] : 0);
+            int64_t ka = dense ? r1 : (int64_t)st.counts[(size_t)c * np + q];
+            if (sd->chunk_kept && sd->chunk_kept[q]) sd->chunk_kept[q][c] = ka;
+            if (bounded) {
+                const int64_t cap = d.out_capacity_rows > 0 ? d.out_capacity_rows : n;
+                if (ka > cap) return fail(QE_ERR_CAPACITY, "filter kept " + std::to_string(ka) + " rows but out_capacity_rows is " + std::to_string(cap));
+            } else {
+                ka = std::min(ka, src->capacity);               // qe_result_num_rows reports the overflow
+            }
+            const int drc = download_range(st, src, q, sd, kb, ka, bounded ? (dense ? 0 : (kb & 7)) : kb, bounded && !dense);
             if (drc) return drc;
-            sink[q].rows_done = std::max(sink[q].rows_done, upto);
         }
+        QE_CUDA(st.new_event(&ev_dl[(size_t)c]));
+        QE_CUDA(cudaEventRecord(ev_dl[(size_t)c], ctx->d2h));
         return QE_OK;
     };
 
-    for (int c = 0; c < nchunks; c++) {
-        const int64_t r0 = (int64_t)c * chunk, r1 = std::min(n, r0 + chunk);
-        // ---- upload chunk c
-        for (size_t col = 0; col < table->cols.size(); col++) {
+    for (int64_t c = 0; c < nchunks; c++) {
+        const int64_t r0 = c * chunk, r1 = std::min(n, r0 + chunk), nc = r1 - r0;
+        const int64_t base_row = bounded ? (c % nslots) * chunk : r0;          // where the chunk lives in `table`
+        // ---- upload (or generate) chunk c
+        if (bounded && c >= nslots) QE_CUDA(cudaStreamWaitEvent(ctx->h2d, ev_run[(size_t)(c - nslots)], 0));   // the slot's last reader
+        for (size_t col = 0; col < table->cols.size() && nc > 0; col++) {
             const qe_col_desc &cd = table->cols[col];
             const void *hv = sd->host_values ? sd->host_values[col] : nullptr;
             const uint8_t *hn = sd->host_validity ? sd->host_validity[col] : nullptr;
-            if (hv && r1 > r0) {
-                if (cd.type == QE_TYPE_BOOLEAN)
-                    QE_STREAM_CUDA(cudaMemcpyAsync((char *)table->values[col] + r0 / 8, (const char *)hv + r0 / 8,
-                                                   (size_t)((r1 - r0 + 7) / 8), cudaMemcpyHostToDevice, ctx->h2d));
-                else
-                    QE_STREAM_CUDA(cudaMemcpyAsync((char *)table->values[col] + (size_t)r0 * type_width(cd.type),
-                                                   (const char *)hv + (size_t)r0 * type_width(cd.type),
-                                                   (size_t)(r1 - r0) * type_width(cd.type), cudaMemcpyHostToDevice, ctx->h2d));
+            const size_t w = type_width(cd.type);
+            if (sd->gen && sd->gen[col].kind >= 0) {
+                const qe_stream_gen &gs = sd->gen[col];
+                if (gs.kind > 4) return fail(QE_ERR_INVALID_ARGUMENT, "unknown generator kind");
+                void *dv = cd.type == QE_TYPE_BOOLEAN ? (void *)((char *)table->values[col] + base_row / 8)
+                                                      : (void *)((char *)table->values[col] + (size_t)base_row * w);
+                QE_CUDA(qe::launch_generate(dv, table->valid[col] ? table->valid[col] + base_row / 32 : nullptr, cd.type, gs.kind, gs.seed,
+                                            gs.p0, gs.p1, cd.nullable ? gs.null_rate : 0.0, sd->gen_row_offset + r0, nc, ctx->stream));
+                ctx->launches++;
+                continue;
             }
-            if (hn && cd.nullable && r1 > r0)
-                QE_STREAM_CUDA(cudaMemcpyAsync((char *)table->valid[col] + r0 / 8, hn + r0 / 8, (size_t)((r1 - r0 + 7) / 8),
-                                               cudaMemcpyHostToDevice, ctx->h2d));
+            if (hv) {
+                if (cd.type == QE_TYPE_BOOLEAN)
+                    QE_CUDA(cudaMemcpyAsync((char *)table->values[col] + base_row / 8, (const char *)hv + r0 / 8,
+                                            (size_t)((nc + 7) / 8), cudaMemcpyHostToDevice, ctx->h2d));
+                else
+                    QE_CUDA(cudaMemcpyAsync((char *)table->values[col] + (size_t)base_row * w, (const char *)hv + (size_t)r0 * w,
+                                            (size_t)nc * w, cudaMemcpyHostToDevice, ctx->h2d));
+            }
+            if (hn && cd.nullable)
+                QE_CUDA(cudaMemcpyAsync((char *)table->valid[col] + base_row / 8, hn + r0 / 8, (size_t)((nc + 7) / 8),
+                                        cudaMemcpyHostToDevice, ctx->h2d));
         }
-        QE_STREAM_CUDA(cudaEventCreateWithFlags(&ev_up[c], cudaEventDisableTiming));
-        QE_STREAM_CUDA(cudaEventRecord(ev_up[c], ctx->h2d));
-        QE_STREAM_CUDA(cudaStreamWaitEvent(ctx->stream, ev_up[c], 0));
+        QE_CUDA(st.new_event(&ev_up[(size_t)c]));
+        QE_CUDA(cudaEventRecord(ev_up[(size_t)c], ctx->h2d));
+        QE_CUDA(cudaStreamWaitEvent(ctx->stream, ev_up[(size_t)c], 0));
+        // the output buffer set this chunk writes must have been downloaded
+        if (bounded && c >= nslots) QE_CUDA(cudaStreamWaitEvent(ctx->stream, ev_dl[(size_t)(c - nslots)], 0));
         // ---- run every pipeline over chunk c
         for (int q = 0; q < np; q++) {
             qe_pipeline_desc d = sd->pipelines[q];
-            d.row_begin = r0;
-            d.row_end = r1;
+            d.row_begin = base_row;
+            d.row_end = base_row + nc;
+            d.sel_offset = (relative ? 0 : r0) - base_row;
+            d.flags &= ~(uint32_t)QE_RUN_APPEND;
             const bool is_agg = d.nagg > 0;
-            d.flags = (d.flags & ~(uint32_t)QE_RUN_APPEND) | ((c > 0 && !is_agg) ? (uint32_t)QE_RUN_APPEND : 0u);
-            if (d.out_capacity_rows <= 0) d.out_capacity_rows = n;
-            rc = qe_pipeline_run_ex(ctx, table, &d, &sd->results[q]);
-            if (rc) { cleanup(); return rc; }
-            qe_result *r = sd->results[q];
-            if (r->mode == qe::KM_AGG) {
-                // every chunk is one partition: keep its partials (GlobalAggregationOperator over a row range)
-                double *dst = chunk_aggs + ((size_t)c * np + q) * agg_stride;
-                if (r1 > r0) QE_STREAM_CUDA(cudaMemcpyAsync(dst, r->final_aggs.ptr, sizeof(double) * agg_stride, cudaMemcpyDeviceToHost, ctx->stream));
-                else memset(dst, 0, sizeof(double) * agg_stride);
+            RunExtra extra;
+            qe_result **slot = &sd->results[q];
+            if (is_agg) {
+                extra.super_offset = c * spc;
+                extra.super_total = nchunks * spc;
+            } else if (bounded) {
+                slot = &slot_result(q, c);
+                extra.chained = true;
+                extra.chain_base = c > 0 ? (const qe_u64 *)slot_result(q, c - 1)->ctl.ptr : nullptr;
+                d.out_capacity_rows = nc + 8;
+            } else {
+                if (c > 0) d.flags |= (uint32_t)QE_RUN_APPEND;
+                if (d.out_capacity_rows <= 0) d.out_capacity_rows = n;
             }
-            QE_STREAM_CUDA(cudaMemcpyAsync(&counts[(size_t)c * np + q], r->ctl.ptr, sizeof(unsigned long long),
-                                           cudaMemcpyDeviceToHost, ctx->stream));
-            QE_STREAM_CUDA(cudaEventCreateWithFlags(&ev_run[(size_t)c * np + q], cudaEventDisableTiming));
-            QE_STREAM_CUDA(cudaEventRecord(ev_run[(size_t)c * np + q], ctx->stream));
+            const bool fresh = *slot == nullptr;
+            if ((rc = run_pipeline(ctx, table, &d, slot, &extra))) return rc;
+            qe_result *r = *slot;
+            if (fresh && slot != &sd->results[q]) sd->results[q]->ring.push_back(r);      // owned by the pipeline's result
+            QE_CUDA(cudaMemcpyAsync(&st.counts[(size_t)c * np + q], r->ctl.ptr, sizeof(unsigned long long),
+                                    cudaMemcpyDeviceToHost, ctx->stream));
         }
+        QE_CUDA(st.new_event(&ev_run[(size_t)c]));
+        QE_CUDA(cudaEventRecord(ev_run[(size_t)c], ctx->stream));
         // ---- while chunk c runs, download what chunk c-1 produced
-        if (c > 0 && (rc = drain(c - 1))) { cleanup(); return rc; }
+        if (c > 0 && (rc = drain(c - 1))) return rc;
     }
-    if ((rc = drain(nchunks - 1))) { cleanup(); return rc; }
-#undef QE_STREAM_CUDA
-    cudaStreamSynchronize(ctx->stream);
-    for (int q = 0; q < np; q++) {
-        qe_result *r = sd->results[q];
-        if (r->mode != qe::KM_AGG) continue;
-        // partials of the chunks folded in chunk order (as qe_agg_combine folds partitions in rank order)
-        for (size_t k = 0; k < r->agg_fns.size(); k++) {
-            double sum = 0.0, mn = qe_bits_f64((qe_i64)0x7ff0000000000000LL), mx = qe_bits_f64((qe_i64)0xfff0000000000000ULL);
-            int64_t count = 0;
-            for (int c = 0; c < nchunks; c++) {
-                const double *src = chunk_aggs + ((size_t)c * np + q) * agg_stride + k * 4;
-                int64_t cnt;
-                memcpy(&cnt, &src[1], sizeof cnt);
-                if (cnt == 0) continue;
-                count += cnt;
-                sum += src[0];
-                mn = qe_math_min(mn, src[2]);
-                mx = qe_math_max(mx, src[3]);
-            }
-            r->host->agg[k][0] = sum;
-            memcpy(&r->host->agg[k][1], &count, sizeof count);
-            r->host->agg[k][2] = mn;
-            r->host->agg[k][3] = mx;
-        }
-        r->batch_rows = n;
-    }
-    cleanup();
+    if ((rc = drain(nchunks - 1))) return rc;
+    QE_CUDA(cudaStreamSynchronize(ctx->h2d));
+    QE_CUDA(cudaStreamSynchronize(ctx->stream));
+    QE_CUDA(cudaStreamSynchronize(ctx->d2h));
+    for (const ByteFix &f : st.fixes) *f.dst |= st.scratch[f.scratch];
     for (int q = 0; q < np; q++) {                             // the runs are complete: make the results readable
         qe_result *r = sd->results[q];
-        r->pending = false;                                     // all three streams were synchronised in cleanup()
+        r->pending = false;
+        for (qe_result *m : r->ring) m->pending = false;
+        if (r->mode == qe::KM_AGG) {
+            r->batch_rows = n;                                  // n_super: the last chunk's run left the length of the whole list
+            r->agg_folded = false;
+        } else if (bounded) {
+            r->streamed = true;
+            r->batch_rows = n;
+            r->host->count = r->mode == qe::KM_PROJECT ? (unsigned long long)n : st.counts[(size_t)(nchunks - 1) * np + q];
+        }
     }
     return QE_OK;
 }
@@ -1811,10 +2116,20 @@ extern "C" int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_
 // Bind a pipeline against a schema, generate its CUDA source and optionally
 // compile it with NVRTC.  Needs no GPU: used by the CPU-side tests and for
 // inspecting the generated code (SASS via cuobjdump on the returned cubin).
+struct DebugOpts {
+    int steps = 0, vec = 0, staging = -1;
+    double sel_hint = -1.0;       // filter: selectivity the same query measured last time
+    int min_blocks = 0;           // dense projection: 4 = the tight variant tried first
+    int seen_groups = 0;          // group-by, register variant: groups found last time
+    uint32_t run_flags = 0;       // QE_RUN_NO_VALUES
+    bool runtime_shapes = false;  // group-by: the shape qe_groupby_run would launch (register variant only)
+};
+
 static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *const *programs, const size_t *nwords,
                           int has_filter, int nproj, const int32_t *agg_fns, int nagg, int group_keys, int atomic,
-                          int steps, int vec, int staging, int compile,
-                          char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes)
+                          const DebugOpts &o, int compile,
+                          char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes,
+                          char *key_out = nullptr, int *origin_out = nullptr)
 {
     if (!cols || ncols <= 0 || !programs || !nwords) return fail(QE_ERR_INVALID_ARGUMENT, "NULL argument");
     std::vector<qe::ColumnInfo> schema(ncols);
@@ -1824,8 +2139,9 @@ static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *co
     std::string err;
     for (int i = 0; i < nprog; i++)
         if (!qe::parse_program(programs[i], nwords[i], progs[i], err)) return fail(QE_ERR_PROGRAM, err);
+    const bool no_values = (o.run_flags & QE_RUN_NO_VALUES) && has_filter && nagg == 0 && group_keys < 0;
     std::vector<const qe::Program *> proj;
-    for (int k = 0; k < nproj; k++) proj.push_back(&progs[(has_filter ? 1 : 0) + k]);
+    for (int k = 0; k < nproj && !no_values; k++) proj.push_back(&progs[(has_filter ? 1 : 0) + k]);
     std::vector<int> aggs;
     if (nagg > 0) aggs.assign(agg_fns, agg_fns + nagg);
     qe::BoundPipeline bp;
@@ -1834,11 +2150,18 @@ static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *co
     const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : (atomic == 2 || atomic == 4 || atomic == 5) ? qe::KM_GROUPBY_SHARED : atomic == 3 ? qe::KM_GROUPBY_REG : qe::KM_GROUPBY_PRIVATE)
                               : !bp.agg_fns.empty() ? qe::KM_AGG : bp.has_filter ? qe::KM_FILTER : qe::KM_PROJECT;
     qe_ctx dummy;
-    dummy.opt_steps = steps;
-    dummy.opt_vec = vec;
-    dummy.opt_staging = staging;
-    qe::TileShape shape = choose_shape(&dummy, bp, mode);
+    dummy.opt_steps = o.steps;
+    dummy.opt_vec = o.vec;
+    dummy.opt_staging = o.staging;
+    qe::TileShape shape = choose_shape(&dummy, bp, mode, o.sel_hint);
+    if (o.min_blocks > 0) shape.min_blocks = o.min_blocks;
     if (mode == qe::KM_GROUPBY_SHARED) { shape.gthreads = 512; shape.steps = 1; shape.vec = qe::jit_wide_loads_supported() ? 4 : 2; shape.scopies = atomic == 4 ? 32 : atomic == 5 ? 8 : 1; }
+    if (mode == qe::KM_GROUPBY_REG && o.runtime_shapes) {       // as qe_groupby_run, level 0
+        const qe::GroupPlan gp = qe::plan_groupby(bp, 256);
+        if (gp.rmax < 2 || !shape.greg) return fail(QE_ERR_UNSUPPORTED, "the register variant does not apply to this group-by");
+        shape.rmax_hint = o.seen_groups > 0 ? std::min(gp.rmax, std::max(4, o.seen_groups)) : gp.rmax;
+        shape.scopies = 1;
+    }
     const std::string src = qe::generate_source(bp, mode, shape);
     if (src_buf && src_cap) {
         const size_t n = std::min(src_cap - 1, src.size());
@@ -1846,12 +2169,19 @@ static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *co
         src_buf[n] = 0;
     }
     if (cubin_bytes) *cubin_bytes = 0;
+    if (key_out) {
+        const std::string key = qe::cubin_key(src, std::vector<std::string>());
+        memcpy(key_out, key.c_str(), std::min<size_t>(key.size() + 1, 33));
+    }
     if (compile) {
-        std::vector<char> cubin;
+        qe::CubinRef cubin;
         std::string log;
-        if (!qe::jit_compile(src, cubin, log)) return fail(QE_ERR_JIT, log);
-        if (cubin_bytes) *cubin_bytes = cubin.size();
-        if (cubin_buf && cubin_cap >= cubin.size()) memcpy(cubin_buf, cubin.data(), cubin.size());
+        int origin = 0;
+        const int crc = qe::cubin_get(src, std::vector<std::string>(), cubin, &origin, log);
+        if (crc) return fail(QE_ERR_JIT, log);
+        if (origin_out) *origin_out = origin;
+        if (cubin_bytes) *cubin_bytes = cubin->size();
+        if (cubin_buf && cubin_cap >= cubin->size()) memcpy(cubin_buf, cubin->data(), cubin->size());
     }
     return QE_OK;
 }
@@ -1862,7 +2192,11 @@ extern "C" int qe_debug_generate(const qe_col_desc *cols, int ncols,
                                  int steps, int vec, int staging, int compile,
                                  char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes)
 {
-    return debug_generate(cols, ncols, programs, nwords, has_filter, nproj, agg_fns, nagg, -1, 0, steps, vec, staging, compile,
+    DebugOpts o;
+    o.steps = steps;
+    o.vec = vec;
+    o.staging = staging;
+    return debug_generate(cols, ncols, programs, nwords, has_filter, nproj, agg_fns, nagg, -1, 0, o, compile,
                           src_buf, src_cap, cubin_buf, cubin_cap, cubin_bytes);
 }
 
@@ -1872,6 +2206,23 @@ extern "C" int qe_debug_generate_groupby(const qe_col_desc *cols, int ncols,
                                          char *src_buf, size_t src_cap, size_t *cubin_bytes)
 {
     if (nkeys < 0 || nagg < 0) return fail(QE_ERR_INVALID_ARGUMENT, "bad key / aggregate count");
-    return debug_generate(cols, ncols, programs, nwords, has_filter, nkeys + nagg, agg_fns, nagg, nkeys, atomic, 0, 0, -1, compile,
+    return debug_generate(cols, ncols, programs, nwords, has_filter, nkeys + nagg, agg_fns, nagg, nkeys, atomic, DebugOpts(), compile,
                           src_buf, src_cap, nullptr, 0, cubin_bytes);
+}
+
+// Ahead-of-time compilation (no GPU needed): the kernel qe_pipeline_run_ex / qe_groupby_run would ask for, with the
+// context options at their defaults, is generated and compiled through the cubin caches -- i.e. it lands in
+// $QE_CACHE_DIR, from where queryengine_b200/build.py bakes it into the library (qe_aot_table.cpp).
+extern "C" int qe_aot_compile(const qe_aot_desc *d, char key_out[33], int *origin)
+{
+    if (!d) return fail(QE_ERR_INVALID_ARGUMENT, "desc is NULL");
+    DebugOpts o;
+    o.sel_hint = d->sel_hint;
+    o.min_blocks = d->min_blocks;
+    o.seen_groups = d->seen_groups;
+    o.run_flags = d->run_flags;
+    o.runtime_shapes = true;
+    const bool group = d->group_keys >= 0;
+    return debug_generate(d->cols, d->ncols, d->programs, d->nwords, d->has_filter, d->nproj, d->agg_fns, d->nagg,
+                          group ? d->group_keys : -1, group ? 3 : 0, o, 1, nullptr, 0, nullptr, 0, nullptr, key_out, origin);
 }

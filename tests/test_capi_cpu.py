@@ -75,7 +75,8 @@ Q6_PROJ = fn(Function.MUL, col(1), col(2))
 def test_generated_code_compiles_for_sm100a():
     rc, src, nbytes, err = _generate([(I, False)], fn(Function.CMP_LT, col(0, I), 1e6), [col(0, I)])
     assert rc == 0, err
-    assert "qe_filter_ring_body<P>" in src and "((qe_i64)in.c0 < 1000000LL)" in src and nbytes > 1000
+    # the literal is a kernel parameter: the code names its slot, not its value
+    assert "qe_filter_ring_body<P>" in src and "((qe_i64)in.c0 < p.lit_hi[0])" in src and nbytes > 1000
     assert "TILE_ROWS = 4480" in src and "NCW = 20" in src and "row.c0 = qe_stage1_i64(stage + 0, wrow0, c);" in src
     rc, src, nbytes, err = _generate([(I, False)], fn(Function.CMP_LT, col(0, I), 1e6), [col(0, I)], staging=0)
     assert rc == 0, err
@@ -107,6 +108,92 @@ def test_generated_code_compiles_for_sm100a():
                 assert rc == 0, (steps, vec, staging, err)
                 assert ("qe_filter_staged_body<P>" in src) == (staging == 1)
                 assert ("qe_filter_ring_body<P>" in src) == (staging == 2)
+
+
+def test_literals_are_kernel_parameters():
+    """`col < 10` and `col < 11` are ONE kernel (the cache key held the literal bits): the generated source
+    and therefore the cubin cache key depend on the literal's class only -- NaN / zero / integral / MOD-able."""
+    def src_of(schema, filt, projs, **kw):
+        rc, src, _, err = _generate(schema, filt, projs, compile_=False, **kw)
+        assert rc == 0, err
+        return src
+    a = src_of([(I, False)], fn(Function.CMP_LT, col(0, I), 10.0), [col(0, I)])
+    b = src_of([(I, False)], fn(Function.CMP_LT, col(0, I), 11.0), [col(0, I)])
+    assert a == b and "10" not in a.split("struct P")[1].split("eval(")[1].split("return")[0]
+    # another class -> another kernel: a non-integral literal against an integer column folds EQ to `false`
+    c = src_of([(I, False)], fn(Function.CMP_EQ, col(0, I), 10.0), [col(0, I)])
+    d = src_of([(I, False)], fn(Function.CMP_EQ, col(0, I), 10.5), [col(0, I)])
+    assert c != d and "== p.lit_lo[0]" in c and "= false;" in d
+    # f64 columns: a plain literal takes the one-instruction comparison, NaN and zeros the total-order one
+    e = src_of([(D, False)], fn(Function.CMP_LT, col(0), 3.0), [col(0)])
+    f = src_of([(D, False)], fn(Function.CMP_LT, col(0), 4.5), [col(0)])
+    g = src_of([(D, False)], fn(Function.CMP_LT, col(0), 0.0), [col(0)])
+    h = src_of([(D, False)], fn(Function.CMP_LT, col(0), float("nan")), [col(0)])
+    assert e == f and "qe_cmp_lt_k(in.c0, p.lit_f64[0])" in e
+    assert "qe_cmp_lt(in.c0, p.lit_f64[0])" in g and "qe_cmp_lt(in.c0, p.lit_f64[0])" in h
+    # equal literals share a slot, so a repeated subtree is still evaluated once (common subexpressions)
+    sub = fn(Function.MOD, fn(Function.MUL, col(0), 0.5), 7.0)
+    t = src_of([(D, False)], None, [fn(Function.ADD, sub, sub)])
+    assert t.count("qe_mod_k(") == 1 and "p.lit_abs[1]" in t and "p.lit_inv[1]" in t
+    # more distinct literals than parameter slots: the rest stay in the code
+    e2 = col(0)
+    for i in range(30):
+        e2 = fn(Function.ADD, e2, float(i) + 0.25)
+    u = src_of([(D, False)], None, [e2])
+    assert "p.lit_f64[23]" in u and "p.lit_f64[24]" not in u and "qe_bits_f64((qe_i64)0x" in u
+    # string literals: the dictionary code is a parameter as well
+    from queryengine_b200.engine import StringDictionary
+    dic = StringDictionary()
+    S = DataType.STRING
+    s1 = src_of([(S, True)], fn(Function.CMP_EQ, col(0, S), lit("a")), [col(0, S)], dictionary=dic)
+    s2 = src_of([(S, True)], fn(Function.CMP_EQ, col(0, S), lit("another")), [col(0, S)], dictionary=dic)
+    assert s1 == s2 and "(qe_i32)p.lit_lo[0]" in s1
+
+
+def test_cubin_cache_memory_disk_and_aot(tmp_path):
+    """A compiled pipeline comes from memory, from the ahead-of-time table baked into the library, from
+    $QE_CACHE_DIR, or -- last -- from NVRTC (qe_cubin_cache.h).  Run in fresh processes: the caches are per process."""
+    import subprocess
+    import sys
+    code = r"""
+import ctypes as C, sys
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+from queryengine_b200 import capi, workloads as W
+from queryengine_b200.aot import compile_one
+from queryengine_b200.ast import DataType, Function, col, fn
+st = (C.c_double * 6)()
+def stats():
+    capi.check(capi.lib().qe_jit_stats(st)); return [int(x) for x in st[:4]] + [st[4], int(st[5])]
+# a BASELINE pipeline: in the ahead-of-time table (any literal: values are parameters)
+compile_one("aot", W.single_column_schema(), W.single_column_filter(0.123), [col(0, DataType.INT64, "col")])
+s1 = stats()
+# not a BASELINE pipeline: disk cache or NVRTC
+D = DataType.DOUBLE
+odd = fn(Function.CMP_GT, fn(Function.SUB, col(0), col(1)), 17.0)
+compile_one("odd", [("a", D, True), ("b", D, False)], odd, [col(1)])
+s2 = stats()
+compile_one("odd again", [("a", D, True), ("b", D, False)], odd, [col(1)])
+s3 = stats()
+print("STATS", s1, s2, s3)
+""" % (ROOT, os.path.join(ROOT, "tests"))
+    env = dict(os.environ, QE_CACHE_DIR=str(tmp_path / "cache"))
+
+    def run(extra_env=None):
+        out = subprocess.run([sys.executable, "-c", code], env=dict(env, **(extra_env or {})), capture_output=True, text=True, check=True).stdout
+        s1, s2, s3 = eval(out.split("STATS", 1)[1].strip().replace("] [", "], ["))
+        return s1, s2, s3
+
+    s1, s2, s3 = run()
+    assert s1[5] >= 10                                         # entries of the ahead-of-time table
+    assert s1[:4] == [0, 1, 0, 0]                              # BASELINE pipeline: from the table, no compiler involved
+    assert s2[:4] == [0, 1, 0, 1] and s2[4] > 0                # first process: NVRTC, written to the cache directory
+    assert s3[:4] == [1, 1, 0, 1]                              # again in the same process: memory
+    assert len(list((tmp_path / "cache").glob("*.cubin"))) == 1
+    s1, s2, s3 = run()
+    assert s2[:4] == [0, 1, 1, 0] and s2[4] == 0               # second process: from disk, NVRTC never ran
+    # without any compiler the ahead-of-time and disk entries still serve
+    s1, s2, s3 = run({"QE_DISABLE_NVRTC": "1"})
+    assert s1[:4] == [0, 1, 0, 0] and s2[:4] == [0, 1, 1, 0]
 
 
 def test_type_errors_follow_the_reference_typecheck():
@@ -215,12 +302,13 @@ def test_string_dictionary_codes_in_programs_and_generated_code():
     e = FunctionExpression(Function.IF, [ColumnExpression("cond", 0, B), StringLiteralExpression("t"), StringLiteralExpression("f")], S)
     rc, src, nbytes, err = _generate([(B, True)], None, [e], dictionary=d)
     assert rc == 0, err
-    assert "const qe_i32 t0 = in.c0 ? ((qe_i32)0) : ((qe_i32)1);" in src and "qe_i32 o0;" in src and nbytes > 1000
+    # (the codes themselves are kernel parameters: lit_lo[slot])
+    assert "const qe_i32 t0 = in.c0 ? ((qe_i32)p.lit_lo[0]) : ((qe_i32)p.lit_lo[1]);" in src and "qe_i32 o0;" in src and nbytes > 1000
     # string equality against a literal and between columns, in the ring filter, with a compacted STRING output
     f = fn(Function.OR, fn(Function.CMP_EQ, col(0, S), StringLiteralExpression("zz")), fn(Function.CMP_NE, col(0, S), col(1, S)))
     rc, src, nbytes, err = _generate([(S, True), (S, False)], f, [col(1, S)], dictionary=d)
     assert rc == 0, err
-    assert "(in.c0 == ((qe_i32)3))" in src and "(in.c0 != in.c1)" in src and "qe_stage1_i32" in src and "qe_filter_ring_body<P>" in src
+    assert "(in.c0 == ((qe_i32)p.lit_lo[0]))" in src and "(in.c0 != in.c1)" in src and "qe_stage1_i32" in src and "qe_filter_ring_body<P>" in src
     # what TypeCheck rejects is rejected here with its message
     for bad in (fn(Function.CMP_LT, col(0, S), col(1, S)), fn(Function.ADD, col(0, S), 1.0),
                 fn(Function.CMP_EQ, col(0, S), 1.0), fn(Function.IF, lit(True), col(0, S), 1.0), fn(Function.NOT, col(0, S))):
