@@ -162,6 +162,10 @@ QE_API int64_t qe_ctx_launch_count(const qe_ctx *ctx);
 /* give the device memory the context's pool holds but does not use back to the driver */
 QE_API int qe_ctx_trim(qe_ctx *ctx);
 
+/* HBM yardsticks with the pipelines' own access shapes: kind 0 reads `bytes`, 1 copies `bytes` (read + write), 2 writes
+ * `bytes`; best device time of `reps` passes.  bench.py's roofline denominators for a launch's read / write mix. */
+QE_API int qe_yardstick(qe_ctx *ctx, int kind, int64_t bytes, int reps, float *best_ms);
+
 /* Where compiled pipelines came from, process-wide (stands in for the compile-once-per-expression of
  * M/evaluator/BytecodeCompiler.kt:134-175): lookups served from [0] memory, [1] the ahead-of-time table baked into
  * the library, [2] the on-disk cache ($QE_CACHE_DIR, else $XDG_CACHE_HOME/qegpu, else $HOME/.cache/qegpu; "off"
@@ -385,6 +389,23 @@ QE_API int qe_mgpu_groupby_run(qe_mgpu *m, const qe_mtable *t, const qe_groupby_
 /* descs[part] describes the stream of partition `part` (host pointers already offset to its first row);
  * qe_pipeline_stream runs on every device at the same time */
 QE_API int qe_mgpu_pipeline_stream(qe_mgpu *m, qe_mtable *t, const qe_stream_desc *descs);
+
+/* Merge the groups of several row-range partitions by key (what qe_mgpu_groupby_run does after the devices have
+ * finished; also for callers that gathered the partitions' groups some other way, e.g. one process per GPU and an
+ * all-gather of these arrays).  Keys are compared by their value bits (as qe_result_column returns them, widened to
+ * 64 bits; NaN keys are canonical) and null flags; partials of one group are folded in partition order; groups come
+ * out ordered by their smallest first_row -- the order one scan of the whole table would have met them in.
+ * out_* arrays hold `capacity` groups: out_keys / out_key_null [g][nkeys], out_values / out_null [g][nagg]. */
+typedef struct qe_group_part {
+    int64_t ngroups;
+    const uint64_t *keys;              /* [ngroups][nkeys] value bits */
+    const uint8_t *key_null;           /* [ngroups][nkeys] 1 = the key value is null */
+    const int64_t *first_row;          /* [ngroups] GLOBAL row of the group's first appearance */
+    const qe_agg_partial *partials;    /* [ngroups][nagg] */
+} qe_group_part;
+QE_API int qe_groupby_merge(const qe_group_part *parts, int nparts, int nkeys, const int32_t *agg_fns, int nagg,
+                            int64_t capacity, uint64_t *out_keys, uint8_t *out_key_null, int64_t *out_first_row,
+                            double *out_values, uint8_t *out_null, int64_t *out_ngroups);
 
 QE_API int qe_mresult_num_rows(qe_mresult *r, int64_t *nrows);                  /* all partitions (groups after the merge) */
 QE_API int qe_mresult_num_columns(const qe_mresult *r, int *ncols);

@@ -105,6 +105,11 @@ class StreamDesc(C.Structure):
     ]
 
 
+class GroupPart(C.Structure):
+    _fields_ = [("ngroups", C.c_int64), ("keys", C.c_void_p), ("key_null", C.c_void_p), ("first_row", C.c_void_p),
+                ("partials", C.c_void_p)]
+
+
 class AotDesc(C.Structure):
     _fields_ = [
         ("cols", C.POINTER(ColDesc)),
@@ -171,6 +176,7 @@ SYMBOLS = {
     "qe_result_group_threads": (C.c_int, [_vp]),
     "qe_ctx_trim": (C.c_int, [_vp]),
     "qe_jit_stats": (C.c_int, [C.POINTER(C.c_double)]),
+    "qe_yardstick": (C.c_int, [_vp, C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_float)]),
     "qe_result_agg_partials": (C.c_int, [_vp, C.c_int, C.POINTER(AggPartial), C.c_int64, C.POINTER(C.c_int64)]),
     "qe_aot_compile": (C.c_int, [C.POINTER(AotDesc), C.c_char_p, C.POINTER(C.c_int)]),
     "qe_partition_rows": (C.c_int, [C.c_int64, C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
@@ -187,6 +193,8 @@ SYMBOLS = {
     "qe_mgpu_pipeline_run": (C.c_int, [_vp, _vp, C.POINTER(PipelineDesc), C.POINTER(_vp)]),
     "qe_mgpu_groupby_run": (C.c_int, [_vp, _vp, C.POINTER(GroupByDesc), C.POINTER(_vp)]),
     "qe_mgpu_pipeline_stream": (C.c_int, [_vp, _vp, C.POINTER(StreamDesc)]),
+    "qe_groupby_merge": (C.c_int, [C.POINTER(GroupPart), C.c_int, C.c_int, C.POINTER(C.c_int32), C.c_int, C.c_int64,
+                                   _vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_int64)]),
     "qe_mresult_num_rows": (C.c_int, [_vp, C.POINTER(C.c_int64)]),
     "qe_mresult_num_columns": (C.c_int, [_vp, C.POINTER(C.c_int)]),
     "qe_mresult_part": (_vp, [_vp, C.c_int]),

@@ -129,6 +129,23 @@ __global__ void qe_generate_kernel(void *values, qe_u32 *validity, int type, int
 }
 
 
+// ---- yardsticks ---------------------------------------------------------------
+// What this device's HBM does for a pure read, a 1:1 copy and a pure write, measured with the access shapes the
+// pipelines use (256-bit loads / stores, evict-first): the denominators of bench.py's roofline for a launch's own
+// read / write mix (a filter at 1 % selectivity is 99 % reads, at 99 % it writes more than it reads).
+__global__ void __launch_bounds__(256) qe_yardstick_kernel(const qe_i64 *src, qe_i64 *dst, qe_i64 n4, int kind, qe_i64 *sink)
+{
+    qe_i64 acc = 0;
+    const qe_i64 stride = (qe_i64)gridDim.x * blockDim.x;
+    for (qe_i64 i = (qe_i64)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        qe_i64 a = i, b = i, c = i, d = i;
+        if (kind != 2) qe_ldg_i64x4(src + 4 * i, a, b, c, d);
+        if (kind == 0) acc ^= a ^ b ^ c ^ d;
+        else asm volatile("st.global.v4.s64 [%0], {%1,%2,%3,%4};" :: "l"(dst + 4 * i), "l"(a), "l"(b), "l"(c), "l"(d) : "memory");
+    }
+    if (kind == 0 && acc == 0x5eed5eed5eedLL) *sink = acc;      // keeps the loads alive
+}
+
 // ---- group-by helpers (the main kernels are generated; see "group-by" in qe_device.cuh)
 
 // every slot empty, every accumulator word at its initial value
@@ -228,6 +245,12 @@ cudaError_t launch_groupby_collect(const uint32_t *state, const uint64_t *keys, 
     const int block = 256;
     qe_groupby_collect_kernel<<<(unsigned)((nslots + block - 1) / block), block, 0, stream>>>(
         state, (const qe_u64 *)keys, nulls, (const qe_u64 *)acc, (qe_i64)nslots, nkeys, nwords, (qe_u64 *)records, ctl, capacity);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_yardstick(const void *src, void *dst, int64_t bytes, int kind, int sms, void *sink, cudaStream_t stream)
+{
+    qe_yardstick_kernel<<<sms * 8, 256, 0, stream>>>((const qe_i64 *)src, (qe_i64 *)dst, (qe_i64)(bytes / 32), kind, (qe_i64 *)sink);
     return cudaGetLastError();
 }
 

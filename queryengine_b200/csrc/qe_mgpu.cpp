@@ -460,6 +460,73 @@ extern "C" int qe_mresult_selection(qe_mresult *r, uint64_t *dst)
 // smallest global row at which they appear, which is the order a single scan would have produced (LinkedHashMap,
 // M/operator/GroupByAggregationOperator.kt:22,29-36).
 
+extern "C" int qe_groupby_merge(const qe_group_part *parts, int nparts, int nkeys, const int32_t *agg_fns, int nagg,
+                                int64_t capacity, uint64_t *out_keys, uint8_t *out_key_null, int64_t *out_first_row,
+                                double *out_values, uint8_t *out_null, int64_t *out_ngroups)
+{
+    if (!parts || nparts < 0 || nkeys < 0 || nkeys > 8 || nagg < 0 || (nagg && !agg_fns) || !out_ngroups)
+        return qe_fail(QE_ERR_INVALID_ARGUMENT, "bad merge arguments");
+    const size_t krec = (size_t)nkeys * 9;                    // per key 8 value bytes + 1 null byte
+    struct Group { int64_t first; std::vector<qe_agg_partial> parts; };
+    std::unordered_map<std::string, size_t> index;
+    std::vector<std::string> keys;
+    std::vector<Group> groups;
+    for (int p = 0; p < nparts; p++) {
+        const qe_group_part &gp = parts[p];
+        if (gp.ngroups < 0 || (gp.ngroups > 0 && ((nkeys && (!gp.keys || !gp.key_null)) || !gp.first_row || (nagg && !gp.partials))))
+            return qe_fail(QE_ERR_INVALID_ARGUMENT, "bad group partition");
+        for (int64_t g = 0; g < gp.ngroups; g++) {
+            std::string key(krec, '\0');
+            for (int k = 0; k < nkeys; k++) {
+                const bool null = gp.key_null[(size_t)g * (size_t)nkeys + (size_t)k] != 0;
+                const uint64_t bits = null ? 0 : gp.keys[(size_t)g * (size_t)nkeys + (size_t)k];
+                memcpy(&key[(size_t)k * 9], &bits, 8);
+                key[(size_t)k * 9 + 8] = null ? 1 : 0;
+            }
+            auto it = index.find(key);
+            size_t gi;
+            if (it == index.end()) {
+                gi = groups.size();
+                index.emplace(key, gi);
+                keys.push_back(key);
+                groups.push_back(Group{gp.first_row[g], {}});
+            } else {
+                gi = it->second;
+                groups[gi].first = std::min(groups[gi].first, gp.first_row[g]);
+            }
+            for (int j = 0; j < nagg; j++) groups[gi].parts.push_back(gp.partials[(size_t)g * (size_t)nagg + (size_t)j]);   // partition order
+        }
+    }
+    const int64_t ng = (int64_t)groups.size();
+    *out_ngroups = ng;
+    if (ng > capacity) return qe_fail(QE_ERR_CAPACITY, "merged group-by has " + std::to_string(ng) + " groups, the output arrays hold " + std::to_string(capacity));
+    std::vector<size_t> order((size_t)ng);
+    for (size_t i = 0; i < order.size(); i++) order[i] = i;
+    std::sort(order.begin(), order.end(), [&](size_t a, size_t b) { return groups[a].first < groups[b].first; });
+    std::vector<qe_agg_partial> one;
+    for (int64_t o = 0; o < ng; o++) {
+        const size_t gi = order[(size_t)o];
+        for (int k = 0; k < nkeys; k++) {
+            if (out_keys) memcpy(&out_keys[(size_t)o * (size_t)nkeys + (size_t)k], &keys[gi][(size_t)k * 9], 8);
+            if (out_key_null) out_key_null[(size_t)o * (size_t)nkeys + (size_t)k] = (uint8_t)keys[gi][(size_t)k * 9 + 8];
+        }
+        if (out_first_row) out_first_row[o] = groups[gi].first;
+        const std::vector<qe_agg_partial> &ps = groups[gi].parts;
+        const int nseen = nagg ? (int)(ps.size() / (size_t)nagg) : 0;
+        one.resize((size_t)nseen);
+        for (int j = 0; j < nagg; j++) {
+            for (int s = 0; s < nseen; s++) one[(size_t)s] = ps[(size_t)s * (size_t)nagg + (size_t)j];
+            double v = 0.0;
+            int is_null = 0;
+            const int rc = qe_agg_combine(agg_fns[j], one.data(), nseen, &v, &is_null);
+            if (rc) return rc;
+            if (out_values) out_values[(size_t)o * (size_t)nagg + (size_t)j] = is_null ? 0.0 : v;
+            if (out_null) out_null[(size_t)o * (size_t)nagg + (size_t)j] = is_null ? 1 : 0;
+        }
+    }
+    return QE_OK;
+}
+
 extern "C" int qe_mgpu_groupby_run(qe_mgpu *m, const qe_mtable *t, const qe_groupby_desc *desc, qe_mresult **result)
 {
     if (!desc) return qe_fail(QE_ERR_INVALID_ARGUMENT, "desc is NULL");
@@ -481,61 +548,55 @@ extern "C" int qe_mgpu_groupby_run(qe_mgpu *m, const qe_mtable *t, const qe_grou
         if ((rc = qe_result_column_type(r->parts[0], k, &type, &hv))) return rc;
         r->g_types[(size_t)k] = type;
     }
-    // merged groups: key record = per key 8 value bytes + 1 null byte
-    const size_t krec = (size_t)nkeys * 9;
-    struct Group { int64_t first; std::vector<qe_agg_partial> parts; };
-    std::unordered_map<std::string, size_t> index;
-    std::vector<std::string> keys;
-    std::vector<Group> groups;
+    // every partition's groups as fixed-width records: key bits, null flags, global first row, partials
+    struct PartData { std::vector<uint64_t> keys; std::vector<uint8_t> nulls; std::vector<int64_t> first; std::vector<qe_agg_partial> partials; };
+    std::vector<PartData> data((size_t)nparts);
+    std::vector<qe_group_part> gparts((size_t)nparts);
+    int64_t total = 0;
     for (int p = 0; p < nparts; p++) {
         qe_result *x = r->parts[(size_t)p];
+        PartData &pd = data[(size_t)p];
         int64_t ng = 0;
         if ((rc = qe_result_num_rows(x, &ng))) return rc;
-        if (ng == 0) continue;
-        std::vector<std::vector<uint8_t>> kv((size_t)nkeys), kn((size_t)nkeys);
-        for (int k = 0; k < nkeys; k++) {
-            kv[(size_t)k].assign((size_t)ng * 8 + 8, 0);
-            kn[(size_t)k].assign((size_t)(ng + 7) / 8 + 1, 0);
-            if ((rc = qe_result_column(x, k, kv[(size_t)k].data(), kn[(size_t)k].data()))) return rc;
-        }
-        std::vector<int64_t> first((size_t)ng, 0);
-        if ((rc = qe_result_group_first_rows(x, first.data()))) return rc;
-        for (int64_t g = 0; g < ng; g++) {
-            std::string key(krec, '\0');
+        total += ng;
+        pd.keys.assign((size_t)ng * (size_t)std::max(nkeys, 1), 0);
+        pd.nulls.assign((size_t)ng * (size_t)std::max(nkeys, 1), 0);
+        pd.first.assign((size_t)ng, 0);
+        pd.partials.assign((size_t)ng * (size_t)std::max(nagg, 1), qe_agg_partial());
+        if (ng > 0) {
+            std::vector<uint8_t> kv((size_t)ng * 8 + 8), kn((size_t)(ng + 7) / 8 + 1);
             for (int k = 0; k < nkeys; k++) {
-                const bool valid = (kn[(size_t)k][(size_t)(g / 8)] >> (g % 8)) & 1u;
+                std::fill(kv.begin(), kv.end(), 0);
+                std::fill(kn.begin(), kn.end(), 0);
+                if ((rc = qe_result_column(x, k, kv.data(), kn.data()))) return rc;
                 const int type = r->g_types[(size_t)k];
-                uint64_t bits = 0;
-                if (valid) {
-                    if (type == QE_TYPE_BOOLEAN) bits = (kv[(size_t)k][(size_t)(g / 8)] >> (g % 8)) & 1u;
-                    else if (width_of(type) == 8) memcpy(&bits, kv[(size_t)k].data() + (size_t)g * 8, 8);
-                    else { uint32_t v32; memcpy(&v32, kv[(size_t)k].data() + (size_t)g * 4, 4); bits = v32; }
+                for (int64_t g = 0; g < ng; g++) {
+                    const bool valid = (kn[(size_t)(g / 8)] >> (g % 8)) & 1u;
+                    uint64_t bits = 0;
+                    if (valid) {
+                        if (type == QE_TYPE_BOOLEAN) bits = (kv[(size_t)(g / 8)] >> (g % 8)) & 1u;
+                        else if (width_of(type) == 8) memcpy(&bits, kv.data() + (size_t)g * 8, 8);
+                        else { uint32_t v32; memcpy(&v32, kv.data() + (size_t)g * 4, 4); bits = v32; }
+                    }
+                    pd.keys[(size_t)g * (size_t)nkeys + (size_t)k] = bits;
+                    pd.nulls[(size_t)g * (size_t)nkeys + (size_t)k] = valid ? 0 : 1;
                 }
-                memcpy(&key[(size_t)k * 9], &bits, 8);
-                key[(size_t)k * 9 + 8] = valid ? 1 : 0;
             }
-            auto it = index.find(key);
-            size_t gi;
-            if (it == index.end()) {
-                gi = groups.size();
-                index.emplace(key, gi);
-                keys.push_back(key);
-                groups.push_back(Group{first[(size_t)g] + r->begin[(size_t)p], {}});
-            } else {
-                gi = it->second;
-                groups[gi].first = std::min(groups[gi].first, first[(size_t)g] + r->begin[(size_t)p]);
-            }
-            for (int j = 0; j < nagg; j++) {
-                qe_agg_partial part;
-                if ((rc = qe_result_group_partial(x, g, j, &part))) return rc;
-                groups[gi].parts.push_back(part);               // [partition-major][aggregate]
+            if ((rc = qe_result_group_first_rows(x, pd.first.data()))) return rc;
+            for (int64_t g = 0; g < ng; g++) {
+                pd.first[(size_t)g] += r->begin[(size_t)p];
+                for (int j = 0; j < nagg; j++)
+                    if ((rc = qe_result_group_partial(x, g, j, &pd.partials[(size_t)g * (size_t)nagg + (size_t)j]))) return rc;
             }
         }
+        gparts[(size_t)p] = qe_group_part{ng, pd.keys.data(), pd.nulls.data(), pd.first.data(), pd.partials.data()};
     }
-    std::vector<size_t> order(groups.size());
-    for (size_t i = 0; i < order.size(); i++) order[i] = i;
-    std::sort(order.begin(), order.end(), [&](size_t a, size_t b) { return groups[a].first < groups[b].first; });
-    const int64_t ng = (int64_t)groups.size();
+    std::vector<uint64_t> mk((size_t)total * (size_t)std::max(nkeys, 1) + 1);
+    std::vector<uint8_t> mn((size_t)total * (size_t)std::max(nkeys, 1) + 1), vn((size_t)total * (size_t)std::max(nagg, 1) + 1);
+    std::vector<double> mv((size_t)total * (size_t)std::max(nagg, 1) + 1);
+    int64_t ng = 0;
+    if ((rc = qe_groupby_merge(gparts.data(), nparts, nkeys, desc->agg_fns, nagg, total, mk.data(), mn.data(), nullptr, mv.data(), vn.data(), &ng)))
+        return rc;
     r->g_rows = ng;
     r->g_values.assign((size_t)ncols, std::vector<uint8_t>());
     r->g_valid.assign((size_t)ncols, std::vector<uint8_t>());
@@ -546,31 +607,20 @@ extern "C" int qe_mgpu_groupby_run(qe_mgpu *m, const qe_mtable *t, const qe_grou
         r->g_valid[(size_t)c].assign(vbytes, 0);
     }
     for (int64_t o = 0; o < ng; o++) {
-        const size_t gi = order[(size_t)o];
-        const std::string &key = keys[gi];
         for (int k = 0; k < nkeys; k++) {
-            if (!key[(size_t)k * 9 + 8]) continue;
+            if (mn[(size_t)o * (size_t)nkeys + (size_t)k]) continue;
             r->g_valid[(size_t)k][(size_t)(o / 8)] |= (uint8_t)(1u << (o % 8));
-            uint64_t bits;
-            memcpy(&bits, &key[(size_t)k * 9], 8);
+            const uint64_t bits = mk[(size_t)o * (size_t)nkeys + (size_t)k];
             const int type = r->g_types[(size_t)k];
             uint8_t *dst = r->g_values[(size_t)k].data();
             if (type == QE_TYPE_BOOLEAN) { if (bits) dst[o / 8] |= (uint8_t)(1u << (o % 8)); }
             else if (width_of(type) == 8) memcpy(dst + (size_t)o * 8, &bits, 8);
             else { const uint32_t v32 = (uint32_t)bits; memcpy(dst + (size_t)o * 4, &v32, 4); }
         }
-        const std::vector<qe_agg_partial> &ps = groups[gi].parts;
-        const int nseen = nagg ? (int)ps.size() / nagg : 0;
-        std::vector<qe_agg_partial> one((size_t)nseen);
         for (int j = 0; j < nagg; j++) {
-            for (int s = 0; s < nseen; s++) one[(size_t)s] = ps[(size_t)s * (size_t)nagg + (size_t)j];
-            double v = 0.0;
-            int is_null = 0;
-            if ((rc = qe_agg_combine(desc->agg_fns[j], one.data(), nseen, &v, &is_null))) return rc;
-            if (!is_null) {
-                memcpy(r->g_values[(size_t)(nkeys + j)].data() + (size_t)o * 8, &v, 8);
-                r->g_valid[(size_t)(nkeys + j)][(size_t)(o / 8)] |= (uint8_t)(1u << (o % 8));
-            }
+            if (vn[(size_t)o * (size_t)nagg + (size_t)j]) continue;
+            memcpy(r->g_values[(size_t)(nkeys + j)].data() + (size_t)o * 8, &mv[(size_t)o * (size_t)nagg + (size_t)j], 8);
+            r->g_valid[(size_t)(nkeys + j)][(size_t)(o / 8)] |= (uint8_t)(1u << (o % 8));
         }
     }
     *result = r;

@@ -326,6 +326,46 @@ extern "C" int qe_ctx_trim(qe_ctx *ctx)
     return QE_OK;
 }
 
+extern "C" int qe_yardstick(qe_ctx *ctx, int kind, int64_t bytes, int reps, float *best_ms)
+{
+    if (!ctx || !best_ms) return fail(QE_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (kind < 0 || kind > 2 || bytes < (1 << 20) || reps < 1) return fail(QE_ERR_INVALID_ARGUMENT, "bad yardstick arguments");
+    DeviceGuard g(ctx->device);
+    bytes = bytes / 4096 * 4096;
+    void *src = nullptr, *dst = nullptr, *sink = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    int rc = QE_OK;
+    float best = 1e30f;
+    do {
+        cudaError_t e = cudaSuccess;
+        if (kind != 2 && (e = ctx->pool.alloc((size_t)bytes, &src)) != cudaSuccess) { rc = fail_cuda("yardstick allocation", e); break; }
+        if (kind != 0 && (e = ctx->pool.alloc((size_t)bytes, &dst)) != cudaSuccess) { rc = fail_cuda("yardstick allocation", e); break; }
+        if ((e = ctx->pool.alloc(64, &sink)) != cudaSuccess) { rc = fail_cuda("yardstick allocation", e); break; }
+        if (src) cudaMemsetAsync(src, 1, (size_t)bytes, ctx->stream);
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        for (int i = 0; i < reps + 1; i++) {                  // the first pass is a warm-up
+            cudaEventRecord(e0, ctx->stream);
+            if ((e = qe::launch_yardstick(src, dst, bytes, kind, ctx->num_sms, sink, ctx->stream)) != cudaSuccess) break;
+            cudaEventRecord(e1, ctx->stream);
+            if ((e = cudaEventSynchronize(e1)) != cudaSuccess) break;
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, e0, e1);
+            if (i > 0) best = std::min(best, ms);
+            ctx->launches++;
+        }
+        if (e != cudaSuccess) rc = fail_cuda("yardstick kernel", e);
+    } while (false);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    cudaStreamSynchronize(ctx->stream);
+    ctx->pool.free(src);
+    ctx->pool.free(dst);
+    ctx->pool.free(sink);
+    *best_ms = best;
+    return rc;
+}
+
 extern "C" int qe_jit_stats(double out[6])
 {
     if (!out) return fail(QE_ERR_INVALID_ARGUMENT, "out is NULL");

@@ -75,11 +75,15 @@ def unpack_bits(bitmap: np.ndarray, n: int) -> np.ndarray:
 class Context:
     """qe_ctx: one device, one stream, one memory pool."""
 
-    def __init__(self, device: int = 0):
+    def __init__(self, device: int = 0, _handle=None, dictionary: Optional[StringDictionary] = None):
         self.handle = C.c_void_p()
-        capi.check(capi.lib().qe_ctx_create(device, C.byref(self.handle)))
+        self._owned = _handle is None
+        if _handle is None:
+            capi.check(capi.lib().qe_ctx_create(device, C.byref(self.handle)))
+        else:
+            self.handle = C.c_void_p(_handle)               # a context of a MultiGpu group (owned by the group)
         self.device = device
-        self.dictionary = StringDictionary()
+        self.dictionary = dictionary if dictionary is not None else StringDictionary()
 
     def set_option(self, key: str, value: int) -> None:
         capi.check(capi.lib().qe_ctx_set_option(self.handle, key.encode(), int(value)))
@@ -95,16 +99,28 @@ class Context:
     def launch_count(self) -> int:
         return capi.lib().qe_ctx_launch_count(self.handle)
 
+    def trim(self) -> None:
+        """Return the device memory the context's pool holds but does not use to the driver."""
+        capi.check(capi.lib().qe_ctx_trim(self.handle))
+
     def close(self) -> None:
-        if self.handle:
+        if self.handle and self._owned:
             capi.lib().qe_ctx_destroy(self.handle)
-            self.handle = C.c_void_p()
+        self.handle = C.c_void_p()
 
     def __del__(self):
         try:
             self.close()
         except Exception:
             pass
+
+
+def jit_stats() -> dict:
+    """Where compiled pipelines came from, process-wide (qe_jit_stats)."""
+    st = (C.c_double * 6)()
+    capi.check(capi.lib().qe_jit_stats(st))
+    return {"memory": int(st[0]), "aot": int(st[1]), "disk": int(st[2]), "nvrtc": int(st[3]), "nvrtc_ms": float(st[4]),
+            "aot_table_entries": int(st[5])}
 
 
 class Program:
@@ -140,10 +156,14 @@ class Field:
 class ColumnarTable:
     """Columnar counterpart of MemoryTable (.../data/MemoryTable.kt:7-19), resident in HBM."""
 
-    def __init__(self, ctx: Context, fields: Sequence[Field], nrows: int):
+    def __init__(self, ctx: Context, fields: Sequence[Field], nrows: int, _handle=None):
         self.ctx = ctx
         self.fields = list(fields)
         self.nrows = int(nrows)
+        self._owned = _handle is None
+        if _handle is not None:                             # a partition of a ShardedTable (owned by it)
+            self.handle = C.c_void_p(_handle)
+            return
         descs = (capi.ColDesc * len(self.fields))(*[capi.ColDesc(int(f.type), 1 if f.nullable else 0) for f in self.fields])
         self.handle = C.c_void_p()
         capi.check(capi.lib().qe_table_create(ctx.handle, len(self.fields), descs, self.nrows, C.byref(self.handle)))
@@ -207,9 +227,9 @@ class ColumnarTable:
         return GpuPipelineOperator(self, None, exprs, None)
 
     def close(self) -> None:
-        if self.handle and self.ctx.handle:
+        if self.handle and self.ctx.handle and self._owned:
             capi.lib().qe_table_destroy(self.handle)
-            self.handle = C.c_void_p()
+        self.handle = C.c_void_p()
 
     def __del__(self):
         try:
@@ -221,9 +241,10 @@ class ColumnarTable:
 class PipelineResult:
     """qe_result: device buffers of one pipeline run."""
 
-    def __init__(self, ctx: Context):
+    def __init__(self, ctx: Context, _handle=None):
         self.ctx = ctx
-        self.handle = C.c_void_p()
+        self._owned = _handle is None
+        self.handle = C.c_void_p(_handle) if _handle is not None else C.c_void_p()
 
     @property
     def num_rows(self) -> int:
@@ -273,6 +294,17 @@ class PipelineResult:
         capi.check(capi.lib().qe_result_agg_partial(self.handle, k, C.byref(p)))
         return p
 
+    def agg_partials(self, k: int) -> np.ndarray:
+        """The partials of aggregate k per super-tile of QE_AGG_SUPER_ROWS rows, in row order: float64[n, 4] =
+        sum, count (int64 bit pattern), min, max.  Concatenated over partitions in order and folded by
+        qe_agg_combine they give the same bits for any number of partitions (qe_result_agg_partials)."""
+        n = C.c_int64(0)
+        capi.check(capi.lib().qe_result_agg_partials(self.handle, k, None, 0, C.byref(n)))
+        out = np.zeros((max(n.value, 1), 4), np.float64)
+        if n.value:
+            capi.check(capi.lib().qe_result_agg_partials(self.handle, k, out.ctypes.data_as(C.POINTER(capi.AggPartial)), n.value, C.byref(n)))
+        return out[:n.value]
+
     @property
     def kernel_ms(self) -> float:
         ms = C.c_float(0.0)
@@ -293,9 +325,9 @@ class PipelineResult:
         return capi.lib().qe_result_device_ptr(self.handle, k, which) or 0
 
     def close(self) -> None:
-        if self.handle and self.ctx.handle:
+        if self.handle and self.ctx.handle and self._owned:
             capi.lib().qe_result_destroy(self.handle)
-            self.handle = C.c_void_p()
+        self.handle = C.c_void_p()
 
     def __del__(self):
         try:
@@ -318,13 +350,16 @@ class Pipeline:
     def __init__(self, table: ColumnarTable, filter: Optional[Expression] = None,
                  projections: Optional[Sequence[Expression]] = None,
                  aggregates: Optional[Sequence[AggregationFunction]] = None,
-                 interpreter: bool = False, selection: bool = True, out_capacity_rows: int = 0):
+                 interpreter: bool = False, selection: bool = True, out_capacity_rows: int = 0, values: bool = True):
+        """values=False (QE_RUN_NO_VALUES): a filter's selection vector is its whole output -- for callers that hold
+        the table themselves, as FilterOperator hands back the row it was given (.../operator/FilterOperator.kt:20-22)."""
         self.table = table
         self.ctx = table.ctx
         self.filter = Program(self.ctx, filter) if filter is not None else None
         self.projs = [Program(self.ctx, e) for e in (projections or [])]
         self.aggs = [int(a) for a in (aggregates or [])]
-        self.flags = (capi.QE_RUN_INTERPRETER if interpreter else 0) | (0 if selection else capi.QE_RUN_NO_SELECTION)
+        self.flags = ((capi.QE_RUN_INTERPRETER if interpreter else 0) | (0 if selection else capi.QE_RUN_NO_SELECTION) |
+                      (0 if values else capi.QE_RUN_NO_VALUES))
         self.out_capacity_rows = out_capacity_rows
         self._proj_arr = (C.c_void_p * max(1, len(self.projs)))(*[p.handle for p in self.projs])
         self._agg_arr = (C.c_int32 * max(1, len(self.aggs)))(*self.aggs)
@@ -370,9 +405,16 @@ def stream_pipelines(table: ColumnarTable, pipelines: Sequence[Pipeline], host_v
                      results: Optional[List[Optional[PipelineResult]]] = None,
                      host_selection: Optional[Sequence[Optional[int]]] = None,
                      host_out_values: Optional[Sequence[Sequence[Optional[int]]]] = None,
-                     host_out_validity: Optional[Sequence[Sequence[Optional[int]]]] = None) -> List[PipelineResult]:
+                     host_out_validity: Optional[Sequence[Sequence[Optional[int]]]] = None,
+                     total_rows: int = 0, chunk_relative: bool = False, gen: Optional[Sequence[Optional[tuple]]] = None,
+                     gen_row_offset: int = 0, chunk_kept: Optional[List[np.ndarray]] = None, _desc_only: bool = False):
     """qe_pipeline_stream: host columns in (addresses of caller-owned, ideally pinned buffers), host results
-    out, chunk by chunk with uploads, kernels and downloads overlapped.  Returns the (complete) results."""
+    out, chunk by chunk with uploads, kernels and downloads overlapped.  Returns the (complete) results.
+
+    total_rows > 0: bounded mode -- `table` is a window of >= 2 chunks, the host table has total_rows rows (which
+    may exceed the device memory and 2^32).  chunk_relative: selection vectors count from their chunk's first row;
+    chunk_kept[q] (int64 array of one entry per chunk) receives the rows kept up to and including each chunk.
+    gen[col] = (kind, seed, p0, p1, null_rate) generates that column on the device instead of uploading it."""
     ctx = table.ctx
     np_ = len(pipelines)
     res = [(results[q] if results and results[q] is not None else PipelineResult(ctx)) for q in range(np_)]
@@ -416,6 +458,28 @@ def stream_pipelines(table: ColumnarTable, pipelines: Sequence[Pipeline], host_v
     if host_out_validity is not None:
         on = ptr_matrix(host_out_validity)
         sd.host_out_validity = on
+    sd.total_rows = int(total_rows)
+    sd.flags = capi.QE_STREAM_CHUNK_RELATIVE if chunk_relative else 0
+    sd.gen_row_offset = int(gen_row_offset)
+    if gen is not None:
+        garr = (capi.StreamGen * ncols)()
+        for c in range(ncols):
+            g = gen[c] if c < len(gen) else None
+            if g is None:
+                garr[c].kind = -1
+            else:
+                garr[c].kind, garr[c].seed, garr[c].p0, garr[c].p1 = int(g[0]), int(g[1]), float(g[2]), float(g[3])
+                garr[c].null_rate = float(g[4]) if len(g) > 4 else 0.0
+        keep.append(garr)
+        sd.gen = garr
+    if chunk_kept is not None:
+        ck = (C.POINTER(C.c_int64) * np_)()
+        for q in range(np_):
+            ck[q] = chunk_kept[q].ctypes.data_as(C.POINTER(C.c_int64)) if chunk_kept[q] is not None else None
+        keep.append(ck)
+        sd.chunk_kept = ck
+    if _desc_only:                                            # MultiGpu.stream runs the descriptors of all partitions at once
+        return sd, res, handles, (hv, hn, descs, hs, keep)
     try:
         capi.check(capi.lib().qe_pipeline_stream(ctx.handle, table.handle, C.byref(sd)))
     finally:

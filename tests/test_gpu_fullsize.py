@@ -10,8 +10,14 @@ bit: torch's elementwise f64 kernels are one IEEE operation each (no contraction
 across ops), which is also what the JVM's DADD/DSUB/DMUL/DDIV/DREM do
 (M/evaluator/BytecodeCompiler.kt:328-332).
 
+On top of that, three random 32 Mi-row windows of every full-size result are checked against the ORACLE itself
+(oracle/qe_oracle.c, the restatement pinned to the reference's vectors): the window's input rows are copied to the
+host, the oracle runs the same plan over them on all host threads, and its rows must equal the slice of the
+full-size GPU result that belongs to the window, bit for bit.
+
 Needs a B200-sized HBM (the largest case holds ~70 GB); skipped below 100 GB.
 """
+import ctypes as C
 import os
 import sys
 
@@ -66,6 +72,47 @@ def _bits(torch, ptr, row0, n):
     return ((by[:, None] >> sh[None, :]) & 1).bool().reshape(-1)[:n]
 
 
+WINDOW = 32 << 20
+
+
+def _windows(n, seed):
+    """three random window starts (multiples of 2^20 rows)"""
+    rng = np.random.default_rng(seed)
+    return [int(x) << 20 for x in rng.integers(0, (n - WINDOW) >> 20, 3)]
+
+
+def oracle_window(dtypes, host_cols, host_valid, filt, projs, aggregates=None):
+    """The oracle's plan over the rows of one window, split over the host threads (ctypes releases the GIL).  Returns
+    (row index inside the window, values[k], valid[k]) of the rows it emits, in scan order -- or, with aggregates, the
+    list of per-slice (count, terms) needed to check a SUM."""
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle_binding import OraclePlan, OracleTable
+    from queryengine_b200.ast import Mode
+    n = len(host_cols[0])
+    threads = max(1, min(32, os.cpu_count() or 1))
+    step = -(-n // threads) // 8 * 8 + 8
+    D = DataType.DOUBLE
+
+    def one(lo):
+        hi = min(n, lo + step)
+        t = OracleTable(list(dtypes) + [D], hi - lo)
+        for c in range(len(dtypes)):
+            v = None if host_valid[c] is None else np.packbits(host_valid[c][lo:hi].astype(np.uint8), bitorder="little")
+            t.set_column(c, host_cols[c][lo:hi], v)
+        t.set_column(len(dtypes), np.arange(lo, hi, dtype=np.float64))
+        row = col(len(dtypes))
+        plan = OraclePlan(t, list(range(len(dtypes) + 1)), filter=filt, projections=list(projs) + [row], mode=Mode.BYTECODE_COMPILER)
+        return plan.columns()
+
+    with ThreadPoolExecutor(threads) as ex:
+        parts = list(ex.map(one, range(0, n, step)))
+    k = len(projs)
+    rows = np.concatenate([p[1][k] for p in parts]).astype(np.int64)
+    vals = [np.concatenate([p[1][j] for p in parts]) for j in range(k)]
+    valid = [np.concatenate([p[2][j] for p in parts]) for j in range(k)]
+    return rows, vals, valid
+
+
 @pytest.mark.parametrize("held_as", ["int64", "f64"])
 def test_config_b_single_column_filter_1e9(ctx, torch_mod, held_as):
     """configs[1]: one column, 10^9 rows, `col < k` at 1 / 50 / 99 %: selection vector and compacted column.  The column is
@@ -108,6 +155,17 @@ def test_config_b_single_column_filter_1e9(ctx, torch_mod, held_as):
         vals2 = dev(torch, res2.device_ptr(0, 0), m2, "<i8")
         assert (int(vals.sum()) + int(vals2.sum()) - total) % 2 ** 64 == 0   # checksum of checksums
         torch.cuda.synchronize()
+        # the oracle itself over three random windows of the full-size result
+        for a in _windows(n, 100 + int(s * 100)):
+            host = column[a:a + WINDOW].cpu().numpy()
+            rows_o, vals_o, valid_o = oracle_window([ctype], [host], [None], fn(Function.CMP_LT, col(0, ctype), float(k)), [col(0, ctype)])
+            lo = int(torch.searchsorted(sel, torch.tensor([a], device="cuda", dtype=sel.dtype)).item())
+            hi = int(torch.searchsorted(sel, torch.tensor([a + WINDOW], device="cuda", dtype=sel.dtype)).item())
+            assert hi - lo == rows_o.size
+            assert np.array_equal(sel[lo:hi].cpu().numpy().astype(np.int64), rows_o + a)
+            got = vals[lo:hi].cpu().numpy()
+            got = got.astype(np.float64) if held_as == "int64" else got.view(np.float64)
+            assert np.array_equal(got, vals_o[0]) and valid_o[0].all()
         res.close()
         res2.close()
     t.close()
@@ -138,6 +196,21 @@ def test_config_c_q6_sum_600m(ctx, torch_mod):
     bound = 2.0 * (count - 1) * 2.0 ** -53 * abs_sum
     assert abs(res.agg(0) - expect) <= bound
     assert abs(res.agg(0) - expect) <= 64 * np.spacing(expect)             # what is actually seen (terms are all positive)
+    # the oracle itself: the same aggregation over three random row-range batches (windows) of the table
+    import math
+    from queryengine_b200 import workloads as W
+    for a in _windows(n, 7):
+        host = [x[a:a + WINDOW].cpu().numpy() for x in (qty, ep, disc, sd)]
+        rows_o, vals_o, valid_o = oracle_window([DataType.DOUBLE] * 4, host, [None] * 4, W.q6_filter(), [W.q6_projection()])
+        rw = pipe.run(None, a, a + WINDOW)
+        pw = rw.agg_partial(0)
+        assert pw.count == rows_o.size                                     # COUNT exact
+        seq = 0.0
+        for x in vals_o[0]:
+            seq += float(x)                                                # the reference's own order (Accumulators.kt:44)
+        exact = math.fsum(vals_o[0].tolist())
+        assert abs(rw.agg(0) - exact) <= max(abs(seq - exact), 4 * math.ulp(exact))
+        rw.close()
     res.close()
     t.close()
 
@@ -180,6 +253,18 @@ def test_config_d_nullable_tree_1e9(ctx, torch_mod):
         del exp, same, valid, got_valid
     torch.cuda.synchronize()
     assert 0.54 < nulls / n < 0.57                                         # 1 - 0.99 * 0.9 * 0.5
+    # the oracle itself over three random windows (8 Mi rows each: the tree costs the oracle ~1 us per row and thread)
+    wn = 8 << 20
+    for a in _windows(n, 11):
+        host = [x[a:a + wn].cpu().numpy() for x in cols]
+        hv = [_bits(torch, t.device_ptr(c, 1), a, wn).cpu().numpy() for c in range(4)]
+        rows_o, vals_o, valid_o = oracle_window([D] * 4, host, hv, None, [bench.tree_expr()])
+        assert rows_o.size == wn
+        gv = _bits(torch, res.device_ptr(0, 1), a, wn).cpu().numpy()
+        assert np.array_equal(gv, valid_o[0])
+        g = out[a:a + wn].cpu().numpy()
+        same = (g.view(np.uint64) == vals_o[0].view(np.uint64)) | (np.isnan(g) & np.isnan(vals_o[0]))
+        assert (same | ~gv).all()
     res.close()
     t.close()
 
@@ -211,5 +296,60 @@ def test_config_e_partition_filter_and_projections_1e9(ctx, torch_mod):
         del idx, keep, e_net, e_gross
     torch.cuda.synchronize()
     assert done == m and 0.1 < m / n < 0.3
+    # the oracle itself over three random windows
+    from queryengine_b200 import workloads as W
+    for a in _windows(n, 13):
+        host = [x[a:a + WINDOW].cpu().numpy() for x in (qty, ep, disc, tax, sd)]
+        rows_o, vals_o, valid_o = oracle_window([DataType.DOUBLE] * 5, host, [None] * 5, W.lineitem_filter(), W.lineitem_projections())
+        lo = int(torch.searchsorted(sel, torch.tensor([a], device="cuda", dtype=sel.dtype)).item())
+        hi = int(torch.searchsorted(sel, torch.tensor([a + WINDOW], device="cuda", dtype=sel.dtype)).item())
+        assert hi - lo == rows_o.size and np.array_equal(sel[lo:hi].cpu().numpy().astype(np.int64), rows_o + a)
+        assert np.array_equal(net[lo:hi].cpu().numpy().view(np.uint64), vals_o[0].view(np.uint64))
+        assert np.array_equal(gross[lo:hi].cpu().numpy().view(np.uint64), vals_o[1].view(np.uint64))
     res.close()
     t.close()
+
+
+def test_config_e_full_sf1000_through_a_bounded_window(ctx, torch_mod):
+    """configs[4] at its FULL size on one GPU: 5 999 989 709 rows (more than 2^32, more than the HBM holds) stream
+    through a three-chunk device window (qe_pipeline_stream, bounded mode, columns generated chunk by chunk).  The same
+    filter over the first chunks, run resident, must keep the same rows; counts add up chunk by chunk."""
+    torch = torch_mod
+    from queryengine_b200 import workloads as W
+    from queryengine_b200.engine import stream_pipelines
+    total, chunk = 5_999_989_709, 1 << 27
+    fields = [Field(nm, tp, nl) for nm, tp, nl in W.lineitem_schema()]
+    window = ColumnarTable(ctx, fields, 3 * chunk)
+    gen = [(capi.QE_GEN_UNIFORM_INT, bench.SEED + 1, 1, 50), (capi.QE_GEN_CENTS, bench.SEED + 2, 90000, 10499999),
+           (capi.QE_GEN_CENTS, bench.SEED + 3, 0, 10), (capi.QE_GEN_CENTS, bench.SEED + 5, 0, 8),
+           (capi.QE_GEN_UNIFORM_INT, bench.SEED + 4, 8036, 10561)]
+    nchunks = -(-total // chunk)
+    kept = np.zeros(nchunks, np.int64)
+    # the selection vector is downloaded (chunk-relative, ~1.3e9 x 4 B): pinned host buffer
+    cap = int(total * 0.23)
+    hp = C.c_void_p()
+    capi.check(capi.lib().qe_host_alloc(cap * 4, C.byref(hp)))
+    pipe = Pipeline(window, W.lineitem_filter(), W.lineitem_projections(), out_capacity_rows=cap)
+    res = stream_pipelines(window, [pipe], [None] * 5, chunk_rows=chunk, total_rows=total, chunk_relative=True, gen=gen,
+                           chunk_kept=[kept], host_selection=[hp.value])
+    m = res[0].num_rows
+    assert kept[-1] == m and (np.diff(kept) > 0).all() and 0.1 < m / total < 0.3
+    sel = np.frombuffer((C.c_char * (m * 4)).from_address(hp.value), dtype=np.uint32)
+    # chunk by chunk: ascending inside the chunk, below the chunk's row count
+    bounds = np.concatenate([[0], kept])
+    for c in (0, 1, nchunks // 2, nchunks - 2, nchunks - 1):
+        sc = sel[bounds[c]:bounds[c + 1]].astype(np.int64)
+        rows_c = min(chunk, total - c * chunk)
+        assert (np.diff(sc) > 0).all() and sc[-1] < rows_c
+    # against a resident run over the same global rows (first two chunks and the last, short one)
+    for c in (0, 1, nchunks - 1):
+        rows_c = min(chunk, total - c * chunk)
+        t, p1 = bench.sf_filter_pipeline(ctx, rows_c, row_offset=c * chunk)
+        r1 = p1.run()
+        assert r1.num_rows == bounds[c + 1] - bounds[c]
+        assert np.array_equal(r1.selection(), sel[bounds[c]:bounds[c + 1]])
+        r1.close()
+        t.close()
+    res[0].close()
+    window.close()
+    capi.lib().qe_host_free(hp)

@@ -87,6 +87,30 @@ def test_single_process_combine_matches_global_oracle():
     assert sharding.combine([A.SUM, A.COUNT, A.MIN], [[empty] * 3, [empty] * 3]) == [None, 0.0, None]
 
 
+def test_super_tile_lists_fold_to_the_same_bits_for_any_partition_count():
+    """SUM over lists of super-tile partials (qe_result_agg_partials) concatenated in partition order: the fold is the
+    same sequence of additions for 1, 2, 3 or 8 partitions, so the bits agree -- unlike a fold of per-partition totals."""
+    rng = np.random.default_rng(3)
+    n = 4096                                                   # super-tiles of the whole table
+    lists = np.zeros((n, 2, 4))
+    lists[:, 0, 0] = rng.uniform(-1e9, 1e9, n)
+    lists[:, 0, 1] = np.full(n, 1000, np.int64).view(np.float64)
+    lists[:, 1, :] = lists[:, 0, :]
+    lists[:, 0, 2] = lists[:, 1, 2] = -5.0
+    lists[:, 0, 3] = lists[:, 1, 3] = 7.0
+    want = sharding.combine_lists([A.SUM, A.AVG], lists)
+    seq = 0.0
+    for x in lists[:, 0, 0]:
+        seq += float(x)
+    assert want[0] == seq and want[1] == seq / (1000 * n)
+    for world in (2, 3, 8):
+        per = -(-n // world)
+        chunks = [lists[r * per:(r + 1) * per] for r in range(world)]
+        assert sharding.combine_lists([A.SUM, A.AVG], np.concatenate(chunks, axis=0)) == want
+    totals = [capi.AggPartial(float(np.sum(lists[r * 512:(r + 1) * 512, 0, 0])), 512000, -5.0, 7.0) for r in range(8)]
+    assert sharding.combine([A.SUM], [[t] for t in totals])[0] != want[0]       # what round 1 did: depends on the split
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -106,6 +130,11 @@ def _worker(rank, world, port, q):
         mine = [_partial_of_shard(a[lo:hi], b[lo:hi], vb[lo:hi])] * len(FNS)
         by_rank = sharding.all_gather_partials(mine)
         got = sharding.combine(FNS, by_rank)
+        # super-tile partial lists of unequal length: gathered in rank order = row order
+        whole = np.random.default_rng(5).uniform(-1, 1, (8, len(FNS), 4))
+        cut = 5
+        lists = sharding.all_gather_partial_lists(whole[:cut] if rank == 0 else whole[cut:])
+        assert lists.shape == whole.shape and np.array_equal(lists, whole)
         # selection vectors: partition-relative + base, concatenated in rank order
         keep = (a[lo:hi] >= -250.0) & (b[lo:hi] < 0.07) & vb[lo:hi]
         local = np.nonzero(keep)[0].astype(np.uint32)
@@ -164,17 +193,29 @@ def _group_rows():
     return [[flag[i], k[i], x[i]] for i in range(n)]
 
 
-def _shard_groups(rows, lo, hi):
-    """What sharding.group_partials returns for rows [lo, hi): computed here with plain Python (no GPU in this suite)."""
+def _shard_groups(rows, lo, hi, dictionary):
+    """What sharding.group_arrays returns for rows [lo, hi): fixed-width arrays, computed here with plain Python
+    (no GPU in this suite).  `dictionary`: the process's StringDictionary (codes are private to a process)."""
+    S = DataType.STRING
     groups = {}
     for i in range(lo, hi):
         flag, k, x = rows[i]
-        kid = (sharding._key_id(flag), sharding._key_id(k))
-        g = groups.setdefault(kid, [(flag, k), i, [0.0, 0, float("inf"), float("-inf")]])
+        kid = (None if flag is None else dictionary.encode(flag), sharding.canonical_key_bits(k, D))
+        g = groups.setdefault(kid, [i, [0.0, 0, float("inf"), float("-inf")]])
         if x is not None:
-            a = g[2]
+            a = g[1]
             a[0] += x; a[1] += 1; a[2] = min(a[2], x); a[3] = max(a[3], x)
-    return [(key, first, [tuple(a)] * 4) for key, first, a in groups.values()]
+    n = len(groups)
+    keys = np.zeros((n, 2), np.uint64)
+    nulls = np.zeros((n, 2), np.uint8)
+    first = np.zeros(n, np.int64)
+    parts = np.zeros((n, 4, 4), np.float64)
+    for g, ((code, kbits), (i, a)) in enumerate(groups.items()):
+        keys[g] = (0 if code is None else code, kbits)
+        nulls[g, 0] = code is None
+        first[g] = i
+        parts[g, :] = (a[0], np.array([a[1]], np.int64).view(np.float64)[0], a[2], a[3])
+    return keys, nulls, first, parts
 
 
 GFNS = [A.SUM, A.COUNT, A.MIN, A.MAX]
@@ -200,10 +241,15 @@ def _rows_equal(got, want):
 
 
 def test_group_partials_merge_by_key_in_first_appearance_order():
+    from queryengine_b200.engine import StringDictionary
     rows = _group_rows()
     parts = sharding.partitions(len(rows), 3)
-    by_rank = [_shard_groups(rows, lo, hi) for lo, hi in parts]
-    _rows_equal(sharding.combine_groups(GFNS, by_rank), _oracle_groups(rows))      # integer-valued x: sums are exact
+    dic = StringDictionary()
+    by_rank = [_shard_groups(rows, lo, hi, dic) for lo, hi in parts]
+    merged = sharding.merge_group_arrays(GFNS, 2, by_rank)                       # qe_groupby_merge, fixed-width arrays
+    got = sharding.merged_rows(GFNS, [DataType.STRING, D], merged, dic.decode)
+    _rows_equal(got, _oracle_groups(rows))                                       # integer-valued x: sums are exact
+    assert list(merged[2]) == sorted(merged[2])                                  # ordered by first appearance
 
 
 def _group_worker(rank, world, port, q):
@@ -212,11 +258,23 @@ def _group_worker(rank, world, port, q):
         os.environ["MASTER_ADDR"] = "127.0.0.1"
         os.environ["MASTER_PORT"] = str(port)
         dist.init_process_group("gloo", rank=rank, world_size=world)
+        from queryengine_b200.engine import StringDictionary
         rows = _group_rows()
         lo, hi = sharding.partition(len(rows), world, rank)
-        gathered = [None] * world
-        dist.all_gather_object(gathered, _shard_groups(rows, lo, hi))
-        q.put((rank, sharding.combine_groups(GFNS, gathered)))
+        dic = StringDictionary()
+        if rank == 1:
+            dic.encode("zz")                                     # the ranks' codes differ: the merge must re-code them
+        keys, nulls, first, parts = _shard_groups(rows, lo, hi, dic)
+
+        class FakeResult:                                        # stands in for a qe_groupby_run result of this partition
+            pass
+        orig = sharding.group_arrays
+        sharding.group_arrays = lambda result, nkeys, nagg, row_offset=0: (keys, nulls, first, parts, [DataType.STRING, D])
+        try:
+            got = sharding.sharded_groupby(FakeResult(), 2, GFNS, dic, 0)
+        finally:
+            sharding.group_arrays = orig
+        q.put((rank, got))
         dist.destroy_process_group()
     except Exception as e:
         q.put((rank, repr(e)))

@@ -23,6 +23,7 @@ from queryengine_b200.engine import ColumnarTable, Context, Field, Pipeline  # n
 ap = argparse.ArgumentParser()
 ap.add_argument("--rows", type=int, default=1_000_000_000)
 ap.add_argument("--reps", type=int, default=3)
+ap.add_argument("--skip-interpreter", action="store_true")
 args = ap.parse_args()
 I = DataType.INT64
 out = {"tool": "cold_start", "rows": args.rows}
@@ -62,9 +63,21 @@ r.close()
 p2, r2, n2, ms2 = first(0.25)
 out["other_literal_first_ms"] = ms2
 r2.close()
+# a pipeline that is not in the ahead-of-time table (the one bench.py's cold_start leg compiled before): disk cache or NVRTC
+from queryengine_b200.engine import jit_stats  # noqa: E402
+s0 = jit_stats()
+t1 = time.perf_counter()
+odd = fn(Function.CMP_LT, fn(Function.SUB, col(0, I), 12345.0), float(int(0.25 * 2 ** 40)))
+r4 = Pipeline(t, odd, [col(0, I)]).run()
+n4 = r4.num_rows
+out["uncached_pipeline_first_result_ms"] = (time.perf_counter() - t1) * 1e3
+s1 = jit_stats()
+out["uncached_pipeline_origin"] = {k: s1[k] - s0[k] for k in ("aot", "disk", "nvrtc")}
+out["jit_stats"] = s1
+r4.close()
 # interpreter kernels (what a deployment without libnvrtc runs)
 interp = []
-for s in (0.01, 0.5, 0.99):
+for s in (() if args.skip_interpreter else (0.01, 0.5, 0.99)):
     p3, r3, n3, ms3 = first(s, interpreter=True)
     for _ in range(args.reps):
         r3 = p3.run(r3)
