@@ -56,7 +56,12 @@ typedef enum qe_status {
 
 /* Physical column types.  STRING, DOUBLE and BOOLEAN are the reference's DataType
  * members (M/data/Schema.kt:3-5, same ordinals); INT64 and DATE32 are
- * extensions that widen exactly to DOUBLE when loaded (|x| < 2^53).
+ * extensions that widen exactly to DOUBLE when loaded.  CONTRACT: every value of an
+ * INT64 column satisfies |x| < 2^53 -- the column stands for the DOUBLE values the
+ * reference would hold, and only below 2^53 is that one-to-one.  The library does not
+ * scan uploads (qe_table_generate rejects ranges beyond it); with larger values the
+ * generated code (exact integer compare against literals) and the interpreter kernels
+ * (compare after widening) may disagree, and neither is "the reference's answer".
  * STRING columns hold dictionary codes: the caller interns every string of a
  * context (column values AND literals) in ONE dictionary, so that equal codes
  * <=> equal strings.  That is all the reference's type checker lets a query do

@@ -1216,6 +1216,42 @@ __device__ __forceinline__ void qe_ring_scatter_step(const QeParams &p, const ty
     off += __popc(m);
 }
 
+// Two warp steps at once (the sparse path): both rows are loaded and evaluated before either is stored.  m1 may be 0.
+template <class P, bool CHECK_CAP, bool HAS_SEL>
+__device__ __forceinline__ void qe_ring_scatter_step2(const QeParams &p, const typename P::Ptrs &ptrs, qe_u32 *selp,
+                                                      qe_u32 stage, int wrow0, int c0, int c1, qe_u32 row_id0, qe_u32 row_id1,
+                                                      qe_u64 wbase, qe_u32 cap_left, qe_u32 m0, qe_u32 m1, qe_u32 &off)
+{
+    const qe_u32 lane = qe_lane();
+    typename P::Row r0, r1;
+    typename P::Out o0, o1;
+    P::load_row(stage, wrow0, c0, r0);
+    P::load_row(stage, wrow0, c1, r1);
+    const qe_u32 lt = qe_lanemask_lt();
+    const qe_u32 n0 = __popc(m0);
+    const qe_u32 idx0 = off + __popc(m0 & lt), idx1 = off + n0 + __popc(m1 & lt);
+    const bool kept0 = (m0 >> lane) & 1u, kept1 = (m1 >> lane) & 1u;
+    (void)P::eval(p, r0, o0);
+    (void)P::eval(p, r1, o1);
+    const bool ok0 = kept0 && (!CHECK_CAP || idx0 < cap_left), ok1 = kept1 && (!CHECK_CAP || idx1 < cap_left);
+    if (HAS_SEL) {
+        qe_stg_if(ok0, selp + idx0, row_id0);
+        qe_stg_if(ok1, selp + idx1, row_id1);
+    }
+    P::emit_ptr(ptrs, idx0, o0, ok0);
+    P::emit_ptr(ptrs, idx1, o1, ok1);
+    if (P::NBITCOLS > 0) {
+        const qe_u32 rk0[1] = {idx0 - off}, rk1[1] = {idx1 - off - n0};
+#pragma unroll
+        for (int b = 0; b < P::NBITCOLS; b++) {
+            qe_u32 *bm = P::bitcol(p, b);
+            if (bm && (!CHECK_CAP || off < cap_left)) qe_store_bits_compact<1>(bm, wbase + off, rk0, kept0 ? 1u : 0u, P::bit(o0, b) ? 1u : 0u);
+            if (bm && m1 && (!CHECK_CAP || off + n0 < cap_left)) qe_store_bits_compact<1>(bm, wbase + off + n0, rk1, kept1 ? 1u : 0u, P::bit(o1, b) ? 1u : 0u);
+        }
+    }
+    off += n0 + __popc(m1);
+}
+
 template <class P, int STEPS, bool CHECK_CAP, bool HAS_SEL>
 __device__ __forceinline__ void qe_ring_scatter(const QeParams &p, qe_u32 stage, int wrow0, qe_u32 first_row,
                                                 qe_u64 wbase, qe_u32 masks, qe_u32 cnt)
@@ -1251,12 +1287,26 @@ __device__ __forceinline__ void qe_ring_scatter(const QeParams &p, qe_u32 stage,
             qe_ring_scatter_step<P, CHECK_CAP, HAS_SEL>(p, ptrs, selp, stage, wrow0, s * 32, first_row + (qe_u32)(s * 32), wbase,
                                                         cap_left, mk[s], off);
     } else {
-        while (act) {
+        // Sparse tiles: two non-empty steps per iteration.  One step at a time is a serial chain (shuffle -> shared-memory
+        // load -> evaluate -> rank -> store, ~350 cycles) and at 1 % selectivity that chain, not the issue rate, set the
+        // consumer warps' pace; the two loads and the two evaluations of a pair are independent.
+        while ((QE_DEBUG_FLAGS & 64) && act) {                 // A/B measurements only: one step per iteration (round 1)
             const int s = __ffs((int)act) - 1;
             act &= act - 1u;
             const qe_u32 m = __shfl_sync(QE_FULL_MASK, mine, s);
             qe_ring_scatter_step<P, CHECK_CAP, HAS_SEL>(p, ptrs, selp, stage, wrow0, s * 32, first_row + (qe_u32)(s * 32), wbase,
                                                         cap_left, m, off);
+        }
+        while (act) {
+            const int s0 = __ffs((int)act) - 1;
+            act &= act - 1u;
+            const bool two = act != 0u;
+            const int s1 = two ? __ffs((int)act) - 1 : s0;
+            act &= act - 1u;                                   // 0 stays 0
+            const qe_u32 m0 = __shfl_sync(QE_FULL_MASK, mine, s0);
+            const qe_u32 m1 = two ? __shfl_sync(QE_FULL_MASK, mine, s1) : 0u;
+            qe_ring_scatter_step2<P, CHECK_CAP, HAS_SEL>(p, ptrs, selp, stage, wrow0, s0 * 32, s1 * 32, first_row + (qe_u32)(s0 * 32),
+                                                         first_row + (qe_u32)(s1 * 32), wbase, cap_left, m0, m1, off);
         }
     }
 }

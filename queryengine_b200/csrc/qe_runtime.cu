@@ -559,6 +559,10 @@ extern "C" int qe_table_generate(qe_table *table, int col, int kind, uint64_t se
     if (!table) return fail(QE_ERR_INVALID_ARGUMENT, "table is NULL");
     if (col < 0 || col >= (int)table->cols.size()) return fail(QE_ERR_INVALID_ARGUMENT, "column index out of range");
     if (kind < 0 || kind > 4) return fail(QE_ERR_INVALID_ARGUMENT, "unknown generator kind");
+    // INT64 columns widen exactly to the reference's DOUBLE only below 2^53 (include/qegpu.h, qe_type)
+    if (table->cols[col].type == QE_TYPE_INT64 && kind == QE_GEN_UNIFORM_INT &&
+        (std::fabs(p0) >= 9007199254740992.0 || std::fabs(p1) >= 9007199254740992.0))
+        return fail(QE_ERR_INVALID_ARGUMENT, "INT64 columns must hold |x| < 2^53 (they stand for the reference's DOUBLE values)");
     qe_ctx *ctx = table->ctx;
     DeviceGuard g(ctx->device);
     QE_CUDA(qe::launch_generate(table->values[col], table->valid[col], table->cols[col].type, kind, seed, p0, p1,

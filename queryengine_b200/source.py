@@ -126,10 +126,45 @@ def upload_arrow(ctx: Context, arrow_table, fields: Optional[Sequence[Field]] = 
     return table
 
 
+_JAVA_DECIMAL = r"^[+-]?(\d+\.?\d*|\.\d+)([eE][+-]?\d+)?$"
+_JAVA_DOUBLE = None
+
+
+def java_parse_double(text: str) -> float:
+    """java.lang.Double.parseDouble / Kotlin String.toDouble(): optional sign, then `NaN`, `Infinity`, a decimal or a
+    hexadecimal floating-point literal, an optional type suffix d / D / f / F; surrounding whitespace is trimmed.
+    Anything else is a NumberFormatException (ValueError here) -- e.g. `inf`, `nan`, `1_000`, `0x10` (no exponent)."""
+    import re
+    global _JAVA_DOUBLE
+    if _JAVA_DOUBLE is None:
+        dec = r"(?:\d+\.?\d*|\.\d+)(?:[eE][+-]?\d+)?"
+        hexa = r"0[xX](?:[0-9a-fA-F]+\.?[0-9a-fA-F]*|\.[0-9a-fA-F]+)[pP][+-]?\d+"
+        _JAVA_DOUBLE = re.compile(r"^([+-]?)(NaN|Infinity|(" + hexa + r")|(" + dec + r"))[dDfF]?$")
+    t = text.strip(" \t\n\r\x0b\x0c" + "".join(chr(c) for c in range(0, 32)))
+    m = _JAVA_DOUBLE.match(t)
+    if not m:
+        raise ValueError(f'For input string: "{text}"')            # NumberFormatException
+    sign, body, hexa, dec = m.group(1), m.group(2), m.group(3), m.group(4)
+    if body == "NaN":
+        return float("nan")
+    if body == "Infinity":
+        v = float("inf")
+    elif hexa:
+        v = float.fromhex(hexa)
+    else:
+        v = float(dec)
+    return -v if sign == "-" else v
+
+
 def read_reference_csv(path: str, fields: Sequence[Field], projection: Optional[Sequence[str]] = None):
-    """The reference's CSV dialect (UnivocityCsvTable.kt:12-15,53-64): comma separated, header row, an empty
-    field is null, BOOLEAN is `toBoolean()` (true iff the text is "true" in any case), DOUBLE is `toDouble()`.
-    Returns a pyarrow.Table of the projected columns with the types of `fields`."""
+    """The reference's CSV dialect (UnivocityCsvTable.kt:10-67 with univocity's default CsvParserSettings): comma
+    separated, header row, leading and trailing whitespace of a value is dropped (ignoreLeading/TrailingWhitespaces
+    are on by default), an empty field -- also a quoted empty one, `isNullOrEmpty` :55 -- is null, BOOLEAN is
+    `toBoolean()` (true iff the text is "true" in any case, :59), DOUBLE is `toDouble()` (:60, the grammar of
+    java.lang.Double.parseDouble: see java_parse_double; a malformed number raises like NumberFormatException).
+    Returns a pyarrow.Table of the projected columns with the types of `fields`.
+    Not reproduced: whitespace INSIDE quotes, which univocity keeps (pyarrow's reader does not say which values were
+    quoted); such a value is trimmed here."""
     pa = _arrow()
     import pyarrow.compute as pc
     import pyarrow.csv as pcsv
@@ -139,14 +174,19 @@ def read_reference_csv(path: str, fields: Sequence[Field], projection: Optional[
         if name not in names:
             raise ValueError(f"Field {name} not found in schema")           # IllegalArgumentException, UnivocityCsvTable.kt:19
     conv = pcsv.ConvertOptions(column_types={n: pa.string() for n in want}, include_columns=want,
-                               strings_can_be_null=True, null_values=[""])
+                               strings_can_be_null=True, null_values=[""], quoted_strings_can_be_null=True)
     raw = pcsv.read_csv(path, convert_options=conv)
     cols = []
     for name in want:
         f = fields[names.index(name)]
-        c = raw.column(name)
+        c = pc.utf8_trim(raw.column(name), characters="".join(chr(x) for x in range(0, 33)))      # univocity: chars <= ' '
+        c = pc.if_else(pc.equal(pc.utf8_length(c), 0), pa.scalar(None, pa.string()), c)           # all blanks -> empty -> null
         if f.type == DataType.DOUBLE:
-            c = pc.cast(c, pa.float64())
+            plain = pc.fill_null(pc.match_substring_regex(c, _JAVA_DECIMAL), True)
+            if pc.all(plain).as_py() is not False:
+                c = pc.cast(c, pa.float64())
+            else:                                                           # NaN, Infinity, hex floats, d / f suffixes
+                c = pa.array([None if v is None else java_parse_double(v) for v in c.to_pylist()], pa.float64())
         elif f.type == DataType.BOOLEAN:
             c = pc.equal(pc.utf8_lower(c), "true")
         cols.append(c)

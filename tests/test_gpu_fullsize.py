@@ -326,7 +326,7 @@ def test_config_e_full_sf1000_through_a_bounded_window(ctx, torch_mod):
     nchunks = -(-total // chunk)
     kept = np.zeros(nchunks, np.int64)
     # the selection vector is downloaded (chunk-relative, ~1.3e9 x 4 B): pinned host buffer
-    cap = int(total * 0.23)
+    cap = int(total * 0.25)
     hp = C.c_void_p()
     capi.check(capi.lib().qe_host_alloc(cap * 4, C.byref(hp)))
     pipe = Pipeline(window, W.lineitem_filter(), W.lineitem_projections(), out_capacity_rows=cap)

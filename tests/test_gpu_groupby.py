@@ -293,11 +293,13 @@ def test_row_range_partitions_merge_to_the_whole_table_result(ctx):
     fns = [A.SUM, A.COUNT, A.MIN, A.MAX]
     t = _gpu_table(ctx, FIELDS, rows)
     pipe = GroupByPipeline(t, fn(Function.CMP_GT, x, -90.0), [s, k], [x, y, x, x], fns)
-    whole = sharding.combine_groups(fns, [sharding.group_partials(pipe.run(), 2, fns, ctx.dictionary)])
+    # fixed-width group records (key bits, null flags, global first row, partials) merged by qe_groupby_merge
+    keys, nulls, first, partials, types = sharding.group_arrays(pipe.run(), 2, len(fns))
+    whole = sharding.merged_rows(fns, types, sharding.merge_group_arrays(fns, 2, [(keys, nulls, first, partials)]), ctx.dictionary.decode)
     parts = []
     for lo, hi in ((0, 2432), (2432, 6000)):
-        parts.append(sharding.group_partials(pipe.run(row_begin=lo, row_end=hi), 2, fns, ctx.dictionary))
-    merged = sharding.combine_groups(fns, parts)
+        parts.append(sharding.group_arrays(pipe.run(row_begin=lo, row_end=hi), 2, len(fns), row_offset=0)[:4])
+    merged = sharding.merged_rows(fns, types, sharding.merge_group_arrays(fns, 2, parts), ctx.dictionary.decode)
     assert len(whole) == len(merged) and len(whole) > 10
     for w, m in zip(whole, merged):
         assert all(_same(a, c) for a, c in zip(w, m)), (w, m)

@@ -82,6 +82,25 @@ def test_one_kernel_serves_every_literal_of_a_class(ctx):
     compare_pipeline(ctx, spec, fn(Function.CMP_LT, e, 100.0), [e])
 
 
+def test_int64_columns_up_to_the_2p53_contract(ctx):
+    """INT64 columns stand for the reference's DOUBLE values: exact below 2^53 (include/qegpu.h).  At the edge of the
+    contract the generated code (integer-domain compare) and the interpreter kernels (compare after widening) still
+    agree with the oracle; a generator range beyond it is refused."""
+    top = (1 << 53) - 1
+    vals = np.array([top, -top, top - 1, -(top - 1), 0, 1, -1, 1 << 52, -(1 << 52), (1 << 52) + 1], dtype=np.int64)
+    vals = np.tile(vals, 1000)
+    spec = TableSpec([Field("x", I, True)], [vals], [np.tile(np.array([1, 1, 1, 0, 1, 1, 1, 1, 1, 1], bool), 1000)])
+    for k in (float(top), float(top - 1), -float(top), float(1 << 52), 0.5, float(1 << 52) + 1.0):
+        for op in (Function.CMP_LT, Function.CMP_LE, Function.CMP_EQ, Function.CMP_GE, Function.CMP_NE):
+            for interp in (False, True):
+                compare_pipeline(ctx, spec, fn(op, col(0, I), k), [col(0, I), fn(Function.ADD, col(0, I), 1.0)], interpreter=interp)
+    t = ColumnarTable(ctx, [Field("x", I, False)], 1024)
+    with pytest.raises(capi.QeError) as ei:
+        t.generate(0, capi.QE_GEN_UNIFORM_INT, 1, 0.0, float(1 << 53))
+    assert "2^53" in ei.value.message
+    t.close()
+
+
 def test_loaded_kernels_are_bounded_by_an_lru(ctx):
     c2 = Context(0)
     c2.set_option("jit_cache_entries", 2)

@@ -72,3 +72,25 @@ def test_reference_csv_dialect(tmp_path):
     assert t.column_names == ["flag", "foo"]
     with pytest.raises(ValueError):
         read_reference_csv(str(p), fields, ["nope"])
+
+
+def test_reference_csv_whitespace_and_java_numerals(tmp_path):
+    """univocity trims values by default; toDouble() takes what java.lang.Double.parseDouble takes."""
+    from queryengine_b200.source import java_parse_double
+    p = tmp_path / "w.csv"
+    p.write_text('foo,bar,flag\n 1.5 ,  a b ,  true \n1d,"",TRUE\n0x1p3, x,\tTrue\nNaN,   ,false\n-Infinity,q, yes \n+.5e1,r,\n')
+    fields = [Field("foo", D, True), Field("bar", S, True), Field("flag", B, True)]
+    t = read_reference_csv(str(p), fields)
+    foo = t.column("foo").to_pylist()
+    assert foo[:3] == [1.5, 1.0, 8.0] and foo[3] != foo[3] and foo[4:] == [float("-inf"), 5.0]
+    assert t.column("bar").to_pylist() == ["a b", None, "x", None, "q", "r"]            # quoted empty and all-blank: null
+    assert t.column("flag").to_pylist() == [True, True, True, False, False, None]
+    for good, v in (("1e3", 1000.0), ("  -0.0\t", -0.0), ("0X.8P1", 1.0), ("3.F", 3.0), ("Infinity", float("inf"))):
+        assert java_parse_double(good) == v
+    for bad in ("inf", "nan", "1_000", "0x10", "", "1e", "--1", "1.5 x"):
+        with pytest.raises(ValueError):
+            java_parse_double(bad)
+    q = tmp_path / "bad.csv"
+    q.write_text("foo\n1.5\ninf\n")
+    with pytest.raises(ValueError):
+        read_reference_csv(str(q), [Field("foo", D, True)])
