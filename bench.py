@@ -357,7 +357,7 @@ def extra_q1(ctx, rows, steps, warmup, peak):
     out = {"rows": rows, "groups": groups, "kernel_ms": kms, "rows_per_s": rows / (kms * 1e-3),
            "gb_per_s": rows * 48 / (kms * 1e-3) / 1e9, "frac_of_peak": rows * 48 / (kms * 1e-3) / 1e9 / peak,
            "algorithmic_bytes_per_row": 48, "selectivity": float(counts.sum()) / rows,
-           "variant": ["private", "atomic", "shared", "registers", "lanes", "lanes8"][capi.lib().qe_result_group_variant(res.handle)],
+           "variant": ["private", "atomic", "shared", "registers", "lanes", "lanes8", "warps"][capi.lib().qe_result_group_variant(res.handle)],
            "threads_per_cta": capi.lib().qe_result_group_threads(res.handle)}
     res.close()
     t.close()

@@ -160,7 +160,8 @@ QE_API void *qe_ctx_stream(qe_ctx *ctx);
  * ring variant: "stage_kb" (bytes of column data per stage, 0 = auto), "tile_rows" (0 = auto), "ncw" (consumer
  * warps, 0 = auto: 20 for a single 8-byte column, else 16), "defer" (tiles between evaluation and scatter, 0 = auto);
  * group-by: "groupby_registers" (1 default: accumulators in registers when the cost rule allows; 0 never; 2 whenever
- * the registers suffice), "groupby_lanes" (1 default; 0 skips the 32-copies-per-CTA variant) */
+ * the registers suffice), "groupby_lanes" (1 default; 0 skips the 32-copies-per-CTA variant), "groupby_warps" (1 default; 0 skips the
+ * one-copy-per-warp variant), "jit_cache_entries" (kernels kept loaded per context, default 128) */
 QE_API int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value);
 /* kernels launched by this context so far */
 QE_API int64_t qe_ctx_launch_count(const qe_ctx *ctx);
@@ -313,8 +314,8 @@ QE_API int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_groupby_d
 QE_API int qe_result_group_partial(qe_result *result, int64_t group, int k, qe_agg_partial *out);
 QE_API int qe_result_group_first_rows(qe_result *result, int64_t *dst);
 /* 3: accumulators in registers (few groups; reproducible), 0: private accumulators in shared memory (reproducible),
- * 4: one shared-memory copy per lane index (32 per CTA), 5: eight copies per CTA, 2: one shared-memory copy per CTA,
- * 1: global atomics,
+ * 4: one shared-memory copy per lane index (32 per CTA), 5: eight copies per CTA, 6: one copy per warp updated
+ * without atomics (reproducible), 2: one shared-memory copy per CTA, 1: global atomics,
  * -1: not a group-by result */
 QE_API int qe_result_group_variant(const qe_result *result);
 /* threads per CTA of the variant that produced the result (private: 512 when the groups fit, else 256) */
@@ -434,7 +435,7 @@ QE_API int qe_debug_generate(const qe_col_desc *cols, int ncols,
                              int steps, int vec, int staging, int compile,
                              char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes);
 
-/* Same for a group-by: programs = [filter,] nkeys key programs, nagg aggregate inputs; atomic: 0 private, 1 global atomics, 2 CTA-shared, 3 registers, 4 lane copies, 5 eight copies. */
+/* Same for a group-by: programs = [filter,] nkeys key programs, nagg aggregate inputs; atomic: 0 private, 1 global atomics, 2 CTA-shared, 3 registers, 4 lane copies, 5 eight copies, 6 one copy per warp. */
 QE_API int qe_debug_generate_groupby(const qe_col_desc *cols, int ncols,
                                      const uint32_t *const *programs, const size_t *nwords,
                                      int has_filter, int nkeys, const int32_t *agg_fns, int nagg, int atomic, int compile,

@@ -335,6 +335,12 @@ size_t GroupPlan::shared_smem32() const
     return (size_t)slmax32 * (size_t)nwords * 8u * 32u + (size_t)scslots32 * (8u * nk + 12u) + 4u * (size_t)slmax32 + 16u;
 }
 
+size_t GroupPlan::shared_smemw() const
+{
+    const size_t nk = nkeys > 0 ? (size_t)nkeys : 1;
+    return (size_t)slmaxw * (size_t)nwords * 8u * (size_t)(threads / 32) + (size_t)scslotsw * (8u * nk + 12u) + 4u * (size_t)slmaxw + 16u;
+}
+
 size_t GroupPlan::shared_smem8() const
 {
     const size_t nk = nkeys > 0 ? (size_t)nkeys : 1;
@@ -422,6 +428,16 @@ GroupPlan plan_groupby(const BoundPipeline &bp, int threads, int lane_acc_kb)
         if (g.shared_smem8() <= (208u << 10)) break;
     }
     if (g.slmax8 < 64 || g.slmax8 <= g.slmax32) { g.slmax8 = 0; g.scslots8 = 64; }
+    // one copy per warp (plain loads / stores, no atomics): threads / 32 copies, four key-cache slots per group while
+    // they fit, two otherwise; up to 224 KB of the 227 KB a CTA may have
+    for (g.slmaxw = 2048; g.slmaxw >= 64; g.slmaxw -= 64) {
+        g.scslotsw = 64;
+        while (g.scslotsw < 4 * g.slmaxw) g.scslotsw *= 2;
+        if (g.shared_smemw() <= (224u << 10)) break;
+        g.scslotsw /= 2;
+        if (g.scslotsw >= 2 * g.slmaxw && g.shared_smemw() <= (224u << 10)) break;
+    }
+    if (g.slmaxw < 64) { g.slmaxw = 0; g.scslotsw = 64; }
     // register variant: per group two 32-bit registers (first row, rows) + two per further word; ~96 registers
     // of accumulators leave room for the row and the expression temporaries under the 168 a 384-thread CTA (1 producer + 11 consumer warps) gets
     const int reg_per_group = 2 + 2 * (g.nwords - 1);
@@ -711,6 +727,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
             snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = 32;\n", gp.slmax32 > 0 ? gp.slmax32 : 32, gp.scslots32);
         else if (shape.scopies == 8)
             snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = 8;\n", gp.slmax8 > 0 ? gp.slmax8 : 64, gp.scslots8);
+        else if (shape.scopies < 0)     // one copy per warp, plain loads and stores (qe_groupby_shared_body, WARPC)
+            snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = 0;\n", gp.slmaxw > 0 ? gp.slmaxw : 64, gp.scslotsw);
         else
             snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = 1;\n", gp.slmax > 0 ? gp.slmax : 64, gp.scslots);
         s += b;
@@ -764,8 +782,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
             s += atomic ? "    template <int AS> static __device__ __forceinline__ void acc_atomic(qe_u64 *a, const Out &o, qe_u64 row) {\n"
                : rfma ? "    static __device__ __forceinline__ void acc_regs_fma(qe_u32 &first, qe_u32 &rows, qe_u64 (&a)[NWORDS], const Out &o, qe_u32 row, int l, int g) {\n"
                : regs ? "    static __device__ __forceinline__ void acc_regs(qe_u32 &first, qe_u32 &rows, qe_u64 (&a)[NWORDS], const Out &o, qe_u32 row, int l, int g) {\n"
-                        : "    static __device__ __forceinline__ void acc_private(qe_u64 *a, const Out &o, qe_u64 row) {\n"
-                          "        constexpr size_t WS = (size_t)LMAX * GTHREADS;\n";
+                        : "    template <int WS> static __device__ __forceinline__ void acc_plain(qe_u64 *a, const Out &o, qe_u64 row) {\n";
             auto at = [&](int w) {
                 char a[48];
                 if (atomic) snprintf(a, sizeof a, "a + %d * AS", w);
@@ -839,6 +856,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                 if (!stmts.empty()) s += "        " + guard + "{ " + stmts + "}\n";
             }
             s += "    }\n";
+            if (variant == 0)      // thread-private copies: word stride = groups x threads
+                s += "    static __device__ __forceinline__ void acc_private(qe_u64 *a, const Out &o, qe_u64 row) { acc_plain<LMAX * GTHREADS>(a, o, row); }\n";
         }
         // every SUM / AVG input of the row is finite (whether null or not: a null's value bits are arbitrary)
         s += "    static __device__ __forceinline__ bool all_finite(const Out &o) {\n        bool f = true;\n";
@@ -877,7 +896,8 @@ const char *jit_entry_name(KernelMode mode, const TileShape &shape)
     case KM_PROJECT: return shape.pring ? "qe_project_ring_kernel" : "qe_project_kernel";
     case KM_AGG: return "qe_agg_kernel";
     case KM_GROUPBY_PRIVATE: return "qe_groupby_private_kernel";
-    case KM_GROUPBY_SHARED: return shape.scopies == 32 ? "qe_groupby_lane_kernel" : shape.scopies == 8 ? "qe_groupby_lane8_kernel" : "qe_groupby_shared_kernel";
+    case KM_GROUPBY_SHARED: return shape.scopies == 32 ? "qe_groupby_lane_kernel" : shape.scopies == 8 ? "qe_groupby_lane8_kernel"
+                                 : shape.scopies < 0 ? "qe_groupby_warp_kernel" : "qe_groupby_shared_kernel";
     case KM_GROUPBY_REG: return "qe_groupby_reg_kernel";
     default: return "qe_groupby_atomic_kernel";
     }

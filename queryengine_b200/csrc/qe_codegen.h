@@ -37,6 +37,8 @@ struct GroupPlan {
     size_t shared_smem32() const;
     int slmax8 = 0, scslots8 = 0;          // ... and with 8 copies (lane & 7): more groups, contention / 8
     size_t shared_smem8() const;
+    int slmaxw = 0, scslotsw = 0;          // ... and with one copy per WARP, updated without atomics (threads / 32 copies)
+    size_t shared_smemw() const;
     int rmax = 0;                          // register variant: groups per CTA whose accumulators every thread keeps in registers (0: not applicable)
     int rmax_regs = 0;                     // ... by the register budget alone, without the cost rule
 };
@@ -64,7 +66,8 @@ struct TileShape {
     // dense projection through the same ring of stages (qe_project_ring_body): one producer warp + ncw consumer warps
     bool pring = false;
     int lane_acc_kb = 0;    // group-by, lane copies: cap on the KB of the copies (0 = none, see plan_groupby)
-    int scopies = 1;        // group-by, CTA-shared variant: copies of the accumulator words per CTA (1, 8 = one per lane & 7, or 32 = one per lane)
+    int scopies = 1;        // group-by, CTA-shared variant: copies of the accumulator words per CTA (1, 8 = one per lane & 7, 32 = one
+                            // per lane, or -1 = one per warp, updated with plain loads and stores)
     int rmax_hint = 0;      // register variant: compile for this many groups instead of the plan's maximum (0: the maximum)
 
     int rows_per_tile() const { return (ring || greg || pring) ? tile_rows : (gthreads / 32) * steps * 32 * vec; }

@@ -1216,42 +1216,6 @@ __device__ __forceinline__ void qe_ring_scatter_step(const QeParams &p, const ty
     off += __popc(m);
 }
 
-// Two warp steps at once (the sparse path): both rows are loaded and evaluated before either is stored.  m1 may be 0.
-template <class P, bool CHECK_CAP, bool HAS_SEL>
-__device__ __forceinline__ void qe_ring_scatter_step2(const QeParams &p, const typename P::Ptrs &ptrs, qe_u32 *selp,
-                                                      qe_u32 stage, int wrow0, int c0, int c1, qe_u32 row_id0, qe_u32 row_id1,
-                                                      qe_u64 wbase, qe_u32 cap_left, qe_u32 m0, qe_u32 m1, qe_u32 &off)
-{
-    const qe_u32 lane = qe_lane();
-    typename P::Row r0, r1;
-    typename P::Out o0, o1;
-    P::load_row(stage, wrow0, c0, r0);
-    P::load_row(stage, wrow0, c1, r1);
-    const qe_u32 lt = qe_lanemask_lt();
-    const qe_u32 n0 = __popc(m0);
-    const qe_u32 idx0 = off + __popc(m0 & lt), idx1 = off + n0 + __popc(m1 & lt);
-    const bool kept0 = (m0 >> lane) & 1u, kept1 = (m1 >> lane) & 1u;
-    (void)P::eval(p, r0, o0);
-    (void)P::eval(p, r1, o1);
-    const bool ok0 = kept0 && (!CHECK_CAP || idx0 < cap_left), ok1 = kept1 && (!CHECK_CAP || idx1 < cap_left);
-    if (HAS_SEL) {
-        qe_stg_if(ok0, selp + idx0, row_id0);
-        qe_stg_if(ok1, selp + idx1, row_id1);
-    }
-    P::emit_ptr(ptrs, idx0, o0, ok0);
-    P::emit_ptr(ptrs, idx1, o1, ok1);
-    if (P::NBITCOLS > 0) {
-        const qe_u32 rk0[1] = {idx0 - off}, rk1[1] = {idx1 - off - n0};
-#pragma unroll
-        for (int b = 0; b < P::NBITCOLS; b++) {
-            qe_u32 *bm = P::bitcol(p, b);
-            if (bm && (!CHECK_CAP || off < cap_left)) qe_store_bits_compact<1>(bm, wbase + off, rk0, kept0 ? 1u : 0u, P::bit(o0, b) ? 1u : 0u);
-            if (bm && m1 && (!CHECK_CAP || off + n0 < cap_left)) qe_store_bits_compact<1>(bm, wbase + off + n0, rk1, kept1 ? 1u : 0u, P::bit(o1, b) ? 1u : 0u);
-        }
-    }
-    off += n0 + __popc(m1);
-}
-
 template <class P, int STEPS, bool CHECK_CAP, bool HAS_SEL>
 __device__ __forceinline__ void qe_ring_scatter(const QeParams &p, qe_u32 stage, int wrow0, qe_u32 first_row,
                                                 qe_u64 wbase, qe_u32 masks, qe_u32 cnt)
@@ -1287,26 +1251,16 @@ __device__ __forceinline__ void qe_ring_scatter(const QeParams &p, qe_u32 stage,
             qe_ring_scatter_step<P, CHECK_CAP, HAS_SEL>(p, ptrs, selp, stage, wrow0, s * 32, first_row + (qe_u32)(s * 32), wbase,
                                                         cap_left, mk[s], off);
     } else {
-        // Sparse tiles: two non-empty steps per iteration.  One step at a time is a serial chain (shuffle -> shared-memory
-        // load -> evaluate -> rank -> store, ~350 cycles) and at 1 % selectivity that chain, not the issue rate, set the
-        // consumer warps' pace; the two loads and the two evaluations of a pair are independent.
-        while ((QE_DEBUG_FLAGS & 64) && act) {                 // A/B measurements only: one step per iteration (round 1)
+        // Sparse tiles: one non-empty step per iteration.  (Two steps per iteration -- both rows loaded and evaluated
+        // before either is stored, to break the serial shuffle -> load -> evaluate -> rank -> store chain -- measured
+        // SLOWER at 1 % selectivity, 1.36 against 1.32 ms per 10^9 rows, and equal at 5 %: most warps meet a single
+        // non-empty step per tile and pay for the empty second one; profiles/r02_sweep_01_sparse_path.jsonl.)
+        while (act) {
             const int s = __ffs((int)act) - 1;
             act &= act - 1u;
             const qe_u32 m = __shfl_sync(QE_FULL_MASK, mine, s);
             qe_ring_scatter_step<P, CHECK_CAP, HAS_SEL>(p, ptrs, selp, stage, wrow0, s * 32, first_row + (qe_u32)(s * 32), wbase,
                                                         cap_left, m, off);
-        }
-        while (act) {
-            const int s0 = __ffs((int)act) - 1;
-            act &= act - 1u;
-            const bool two = act != 0u;
-            const int s1 = two ? __ffs((int)act) - 1 : s0;
-            act &= act - 1u;                                   // 0 stays 0
-            const qe_u32 m0 = __shfl_sync(QE_FULL_MASK, mine, s0);
-            const qe_u32 m1 = two ? __shfl_sync(QE_FULL_MASK, mine, s1) : 0u;
-            qe_ring_scatter_step2<P, CHECK_CAP, HAS_SEL>(p, ptrs, selp, stage, wrow0, s0 * 32, s1 * 32, first_row + (qe_u32)(s0 * 32),
-                                                         first_row + (qe_u32)(s1 * 32), wbase, cap_left, m0, m1, off);
         }
     }
 }
@@ -2279,16 +2233,22 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
     // COPIES = 32 ("lane" kernel): one copy of the words per LANE index, shared by the lanes of that index in all
     // warps ([group][word][lane]: lane-consecutive, conflict-free).  The same atomics, but two threads meet on a
     // word only when they have the same lane AND the same group: the CAS loops of the f64 words hardly ever retry.
-    constexpr int COPIES = P::SCOPIES;
+    // SCOPIES = 0 ("warp" kernel): one copy per WARP, laid out [warp][word][group], updated with plain loads and stores --
+    // no atomics at all.  Lanes of a warp that meet the same group in one step are ranked with match.any and take
+    // turns, so a group's rows are added in row order per warp and the result is reproducible.  The shared-memory atomic
+    // unit was what bounded the single-copy kernel (three to five ATOMS per row; 4.7 ms per 6e8 rows whatever the
+    // contention), LDS / STS run at the full 32 lanes per clock.
+    constexpr bool WARPC = P::SCOPIES == 0;
+    constexpr int COPIES = WARPC ? GW : P::SCOPIES;
     typedef QeGroupCache<NKEYS, CS, LMAX> Cache;
     extern __shared__ __align__(16) unsigned char qe_gsmem[];
-    qe_u64 *s_acc = (qe_u64 *)qe_gsmem;                       // [LMAX][NWORDS][COPIES]
+    qe_u64 *s_acc = (qe_u64 *)qe_gsmem;                       // [LMAX][NWORDS][COPIES], or [COPIES][NWORDS][LMAX] (WARPC)
     Cache &gc = *(Cache *)(qe_gsmem + (size_t)LMAX * NWORDS * COPIES * 8);
     const qe_u32 warp = qe_warp(), lane = qe_lane(), tid = threadIdx.x;
 
     for (int i = (int)tid; i < CS; i += GT) gc.state[i] = 0u;
     if (tid == 0) { gc.nlocal = 0u; gc.over = 0u; }
-    for (int i = (int)tid; i < LMAX * NWORDS * COPIES; i += GT) s_acc[i] = P::word_init((i / COPIES) % NWORDS);
+    for (int i = (int)tid; i < LMAX * NWORDS * COPIES; i += GT) s_acc[i] = P::word_init(WARPC ? (i / LMAX) % NWORDS : (i / COPIES) % NWORDS);
     __syncthreads();
 
     typename P::Row rows[STEPS][VEC];
@@ -2356,8 +2316,17 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
 #pragma unroll
             for (int j = 0; j < VEC; j++) {
                 const int l = lg[s][j];
-                if (l >= 0) {
-                    const qe_u64 row = (qe_u64)p.sel_base + (qe_u64)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j);
+                const qe_u64 row = (qe_u64)p.sel_base + (qe_u64)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j);
+                if (WARPC) {
+                    // lanes with the same group take turns, lowest lane (= lowest row of this step) first
+                    const qe_u32 peers = __match_any_sync(QE_FULL_MASK, l);
+                    const qe_u32 rank = (qe_u32)__popc(peers & qe_lanemask_lt());
+                    const qe_u32 last = __reduce_max_sync(QE_FULL_MASK, l >= 0 ? rank : 0u);
+                    for (qe_u32 r = 0; r <= last; r++) {
+                        if (l >= 0 && rank == r) P::template acc_plain<LMAX>(s_acc + (size_t)warp * NWORDS * LMAX + l, outs[s][j], row);
+                        __syncwarp();
+                    }
+                } else if (l >= 0) {
                     P::template acc_atomic<COPIES>(s_acc + (size_t)l * NWORDS * COPIES + (lane & (qe_u32)(COPIES - 1)), outs[s][j], row);
                 }
             }
@@ -2370,10 +2339,15 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
     __syncthreads();
     const int nlocal = (int)(gc.nlocal < (qe_u32)LMAX ? gc.nlocal : (qe_u32)LMAX);
     for (int i = (int)tid; i < nlocal * NWORDS; i += GT) {
-        qe_u64 v = s_acc[(size_t)i * COPIES];
-        if (COPIES > 1) {                                     // the lane copies in lane order
-            const int kind = P::word_kind(i % NWORDS);
-            for (int c = 1; c < COPIES; c++) v = qe_group_combine(kind, v, s_acc[(size_t)i * COPIES + c]);
+        const int kind = P::word_kind(i % NWORDS);
+        qe_u64 v;
+        if (WARPC) {                                          // the warps' copies in warp order
+            const size_t at = (size_t)(i % NWORDS) * LMAX + (size_t)(i / NWORDS);
+            v = s_acc[at];
+            for (int c = 1; c < COPIES; c++) v = qe_group_combine(kind, v, s_acc[(size_t)c * NWORDS * LMAX + at]);
+        } else {
+            v = s_acc[(size_t)i * COPIES];
+            for (int c = 1; c < COPIES; c++) v = qe_group_combine(kind, v, s_acc[(size_t)i * COPIES + c]);   // the lane copies in lane order
         }
         p.g_part[(size_t)blockIdx.x * LMAX * NWORDS + i] = v;
     }

@@ -148,6 +148,7 @@ struct qe_ctx {
     // options
     int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = -1, opt_stages = 0, opt_debug_flags = 0, opt_pipeline = 1, opt_groupby_registers = 1, opt_groupby_lanes = 1, opt_lane_acc_kb = 0;
     int64_t opt_min_blocks = 0;
+    int64_t opt_groupby_warps = 1;
     int64_t opt_nlb = 0, opt_loads = 0, opt_tile_rows = 0, opt_ncw = 0, opt_defer = 0, opt_stage_kb = 0;
     int64_t launches = 0;
     bool warned_no_nvrtc = false;
@@ -281,6 +282,8 @@ extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
         ctx->opt_lane_acc_kb = value;
     } else if (k == "groupby_lanes") {
         ctx->opt_groupby_lanes = value != 0;                 // 0: skip the lane-copies variant (32 copies per CTA)
+    } else if (k == "groupby_warps") {
+        ctx->opt_groupby_warps = value != 0;                 // 0 skips the one-copy-per-warp variant
     } else if (k == "groupby_registers") {
         if (value < 0 || value > 2) return fail(QE_ERR_INVALID_ARGUMENT, "groupby_registers must be 0 (off), 1 (by the cost rule) or 2 (whenever the registers suffice)");
         ctx->opt_groupby_registers = value;                  // 0: group-by starts with the private (shared-memory) variant
@@ -900,7 +903,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     char suffix[128];
     snprintf(suffix, sizeof suffix, "|M%d|B%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d.%d|G%d", (int)mode, shape.min_blocks, shape.steps, shape.vec, shape.staged ? 1 : 0,
              shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0, shape.ring ? 1 : 0, shape.tile_rows, shape.ncw,
-             shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0) + (shape.pring ? 200000 : 0) + (shape.scopies == 32 ? 400000 + 1000000 * shape.lane_acc_kb : shape.scopies == 8 ? 800000 : 0));
+             shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0) + (shape.pring ? 200000 : 0) + (shape.scopies == 32 ? 400000 + 1000000 * shape.lane_acc_kb : shape.scopies == 8 ? 800000 : shape.scopies < 0 ? 1600000 : 0));
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) {
@@ -1047,14 +1050,17 @@ static int run_pipeline(qe_ctx *ctx, const qe_table *table, const qe_pipeline_de
         }
         shape = choose_shape(ctx, bp, mode, sel_hint);
         // Dense projection: four CTAs per SM (64 registers) hide the latency of the FP64 divide / MOD sequences better
-        // than three (measured on the nullable tree: 6.83 -> 6.34 ms); kept only when the tighter bound does not spill.
+        // than three; kept unless the tighter bound spills more than a few words.  (Nullable tree, 1e9 rows: 84
+        // registers / three CTAs 7.06 ms, 64 registers with 16 bytes of stack / four CTAs 6.14 ms, __launch_bounds__(256, 3)
+        // 6.48 ms -- profiles/r02_tree_*.log.  With literals as kernel parameters the 64-register build keeps two values on
+        // the stack; refusing it for that cost 13 %.)
         rc = QE_OK;
         if (mode == qe::KM_PROJECT && !ctx->opt_min_blocks && !shape.pring) {
             qe::TileShape tight = shape;
             tight.min_blocks = 4;
             JitEntry *cand = nullptr;
             rc = get_jit_kernel(ctx, bp, mode, tight, &cand);
-            if (rc == QE_OK && cand->kernel.local_bytes == 0) { shape = tight; jit = cand; }
+            if (rc == QE_OK && cand->kernel.local_bytes <= 64) { shape = tight; jit = cand; }
             else if (rc > 0) return rc;
         }
         if (!jit && rc >= 0) rc = get_jit_kernel(ctx, bp, mode, shape, &jit);
@@ -1491,9 +1497,10 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     // a result that is reused remembers which variants this group-by has overflowed
     const std::string sig = query_key(bp);
     // levels: 0 registers, 1 private 512 threads, 2 private 256 threads, 3 lane copies (32 per CTA), 4 eight copies,
+    // 5 one copy per warp (256 threads, no atomics), 6 CTA-shared (one copy), 7 global atomics   [older numbering below]
     // 5 CTA-shared (one copy), 6 global atomics
     int level = r->g_overflowed == sig ? r->g_level : 0;
-    if (d->flags & QE_GROUPBY_ATOMIC) level = 6;
+    if (d->flags & QE_GROUPBY_ATOMIC) level = 7;
     else if (d->flags & QE_GROUPBY_SHARED) level = std::max(level, 3);
     // register variant: every group's words are touched for every row, so compile for the group count the same
     // group-by found last time (a reused result remembers it); more groups than that -> once more with the maximum
@@ -1517,13 +1524,14 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
         if (level == 2 && gp.nwords <= 3 && ctx->opt_groupby_lanes && gp512.slmax32 >= gp.lmax) continue;
         if (level == 3 && (gp512.slmax32 < 16 || !ctx->opt_groupby_lanes)) continue;
         if (level == 4 && (gp512.slmax8 < 64 || !ctx->opt_groupby_lanes)) continue;
-        if (level == 5 && gp512.slmax < 64) continue;
-        const bool atomic = level >= 6, shared = level >= 3 && level <= 5, lanes = level == 3, lanes8 = level == 4;
-        const qe::GroupPlan &plan = (level == 1 || shared) ? gp512 : gp;
+        if (level == 5 && (gp.slmaxw < 64 || !ctx->opt_groupby_warps)) continue;
+        if (level == 6 && gp512.slmax < 64) continue;
+        const bool atomic = level >= 7, shared = level >= 3 && level <= 6, lanes = level == 3, lanes8 = level == 4, warpc = level == 5;
+        const qe::GroupPlan &plan = (level == 1 || (shared && !warpc)) ? gp512 : gp;
         const qe::KernelMode mode = regs ? qe::KM_GROUPBY_REG : atomic ? qe::KM_GROUPBY_ATOMIC : shared ? qe::KM_GROUPBY_SHARED : qe::KM_GROUPBY_PRIVATE;
-        const int part_groups = regs ? rmax_use : lanes ? plan.slmax32 : lanes8 ? plan.slmax8 : shared ? plan.slmax : plan.lmax;
+        const int part_groups = regs ? rmax_use : lanes ? plan.slmax32 : lanes8 ? plan.slmax8 : warpc ? plan.slmaxw : shared ? plan.slmax : plan.lmax;
         qe::TileShape shape = regs ? reg_shape : choose_shape(ctx, bp, mode);
-        shape.scopies = lanes ? 32 : lanes8 ? 8 : 1;
+        shape.scopies = lanes ? 32 : lanes8 ? 8 : warpc ? -1 : 1;
         shape.lane_acc_kb = (int)ctx->opt_lane_acc_kb;
         if (!atomic && !regs) {
             shape.gthreads = plan.threads;
@@ -1537,7 +1545,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
             return fail(QE_ERR_INVALID_ARGUMENT, "group-by tile of " + std::to_string(shape.rows_per_tile()) + " rows (threads / 32 * steps * 32 * vec) exceeds " +
                                                  std::to_string(kPadRows) + ": lower the \"steps\" / \"vec\" options");
         JitEntry *jit = nullptr;
-        rc = get_jit_kernel(ctx, bp, mode, shape, &jit, (atomic || regs) ? 0 : lanes ? plan.shared_smem32() : lanes8 ? plan.shared_smem8() : shared ? plan.shared_smem() : plan.private_smem());
+        rc = get_jit_kernel(ctx, bp, mode, shape, &jit, (atomic || regs) ? 0 : lanes ? plan.shared_smem32() : lanes8 ? plan.shared_smem8() : warpc ? plan.shared_smemw() : shared ? plan.shared_smem() : plan.private_smem());
         if (rc < 0) return fail(QE_ERR_JIT, "group-by needs generated code: " + tls_error);
         if (rc) return rc;
         const int64_t tile_rows = shape.rows_per_tile();
@@ -1553,7 +1561,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
             p.g_part_slot = (qe_u32 *)r->g_part_slot.ptr;
         }
         r->mode = (int)mode;
-        r->g_variant = regs ? 3 : atomic ? 1 : lanes ? 4 : lanes8 ? 5 : shared ? 2 : 0;
+        r->g_variant = regs ? 3 : atomic ? 1 : lanes ? 4 : lanes8 ? 5 : warpc ? 6 : shared ? 2 : 0;
         const int threads = regs ? shape.block_threads() : atomic ? QE_BLOCK : plan.threads;
         r->g_threads = threads;
         QE_CUDA(qe::launch_groupby_init((uint32_t *)r->g_state.ptr, (uint64_t *)r->g_acc.ptr, (uint32_t *)r->g_ctl.ptr, nslots, gw, ctx->stream));
@@ -2191,7 +2199,7 @@ static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *co
     qe::BoundPipeline bp;
     int rc = qe::bind_pipeline(schema, has_filter ? &progs[0] : nullptr, proj, aggs, bp, err, group_keys);
     if (rc) return fail(rc, err);
-    const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : (atomic == 2 || atomic == 4 || atomic == 5) ? qe::KM_GROUPBY_SHARED : atomic == 3 ? qe::KM_GROUPBY_REG : qe::KM_GROUPBY_PRIVATE)
+    const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : (atomic == 2 || atomic == 4 || atomic == 5 || atomic == 6) ? qe::KM_GROUPBY_SHARED : atomic == 3 ? qe::KM_GROUPBY_REG : qe::KM_GROUPBY_PRIVATE)
                               : !bp.agg_fns.empty() ? qe::KM_AGG : bp.has_filter ? qe::KM_FILTER : qe::KM_PROJECT;
     qe_ctx dummy;
     dummy.opt_steps = o.steps;
@@ -2200,6 +2208,7 @@ static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *co
     qe::TileShape shape = choose_shape(&dummy, bp, mode, o.sel_hint);
     if (o.min_blocks > 0) shape.min_blocks = o.min_blocks;
     if (mode == qe::KM_GROUPBY_SHARED) { shape.gthreads = 512; shape.steps = 1; shape.vec = qe::jit_wide_loads_supported() ? 4 : 2; shape.scopies = atomic == 4 ? 32 : atomic == 5 ? 8 : 1; }
+    if (mode == qe::KM_GROUPBY_SHARED && atomic == 6) { shape = choose_shape(&dummy, bp, mode); shape.gthreads = 256; shape.scopies = -1; }
     if (mode == qe::KM_GROUPBY_REG && o.runtime_shapes) {       // as qe_groupby_run, level 0
         const qe::GroupPlan gp = qe::plan_groupby(bp, 256);
         if (gp.rmax < 2 || !shape.greg) return fail(QE_ERR_UNSUPPORTED, "the register variant does not apply to this group-by");

@@ -104,7 +104,7 @@ def _check_against_oracle(ctx, rows, keys, inputs, fns, filter_, atomic, expect_
         allowed = expect_variant if isinstance(expect_variant, tuple) else (expect_variant,)
         assert capi.lib().qe_result_group_variant(res.handle) in allowed
     elif atomic or shared:
-        assert capi.lib().qe_result_group_variant(res.handle) in ((1,) if atomic else (2, 4, 5))
+        assert capi.lib().qe_result_group_variant(res.handle) in ((1,) if atomic else (2, 4, 5, 6))
     op = GpuGroupByOperator(t, filter_, list(keys) + [agg(f, e) for f, e in zip(fns, inputs)], atomic=atomic, shared=shared, max_groups=max_groups)
     got = op.map()
     if not rows:
@@ -211,17 +211,41 @@ def test_many_groups_fall_back_to_atomics_and_capacity_is_checked(ctx):
     k, x = col(2), col(3)
     # 5000 groups: no private variant holds them; a CTA of this small table meets only a few hundred, so the
     # CTA-shared variant takes over (a CTA that met more than its shared memory holds would fall back to atomics)
-    got = _check_against_oracle(ctx, rows, [k], [x, x], [A.SUM, A.COUNT], None, False, expect_variant=(2, 4, 5))
+    got = _check_against_oracle(ctx, rows, [k], [x, x], [A.SUM, A.COUNT], None, False, expect_variant=(2, 4, 5, 6))
     assert len(got) == len({r[2] for r in rows})
     # ~1000 groups: more than the private copies hold, one shared-memory copy per CTA takes them
     rows1k = [[r[0], r[1], float(int(r[2]) % 1000), r[3], r[4]] for r in rows]
-    got = _check_against_oracle(ctx, rows1k, [k], [x, x, x], [A.SUM, A.COUNT, A.MIN], None, False, expect_variant=(2, 4, 5))
+    got = _check_against_oracle(ctx, rows1k, [k], [x, x, x], [A.SUM, A.COUNT, A.MIN], None, False, expect_variant=(2, 4, 5, 6))
     assert len(got) == 1000
     t = _gpu_table(ctx, FIELDS, rows)
     with pytest.raises(capi.QeError) as e:
         GroupByPipeline(t, None, [k], [x], [A.SUM], max_groups=1000).run()
     assert "max_groups" in str(e.value)
     t.close()
+
+
+def test_warp_copies_variant_for_up_to_a_thousand_groups(ctx):
+    """One accumulator copy per warp, updated with plain loads and stores; lanes of a warp that meet the same group in
+    one step take turns (match.any), so a group's rows are added in a fixed order: variant 6, reproducible.  Few distinct
+    keys per step force the taking of turns (40 groups), many spread the accesses (700 groups, nulls, a filter)."""
+    ctx.set_option("groupby_lanes", 0)                      # skip the lane-copies variants, which would hold these groups
+    ctx.set_option("groupby_registers", 0)
+    try:
+        for ngroups, seed in ((700, 1), (40, 2)):
+            rng = np.random.default_rng(900 + seed)
+            n = 120000
+            rows = [[None, bool(rng.random() < 0.5) if rng.random() > 0.1 else None, float(int(rng.integers(ngroups))),
+                     float(np.round(rng.uniform(-10, 10), 1)), None if rng.random() < 0.2 else float(rng.uniform(-1e3, 1e3))] for _ in range(n)]
+            k, x, y = col(2), col(3), col(4)
+            got = _check_against_oracle(ctx, rows, [k], [x, y, x, y, y], [A.SUM, A.COUNT, A.AVG, A.MIN, A.MAX], fn(Function.CMP_GT, x, -9.0), "shared",
+                                        expect_variant=6)
+            assert len(got) == ngroups
+            again = _check_against_oracle(ctx, rows, [k], [x, y, x, y, y], [A.SUM, A.COUNT, A.AVG, A.MIN, A.MAX], fn(Function.CMP_GT, x, -9.0), "shared",
+                                          expect_variant=6)
+            assert all(_same(a, b) for ra, rb in zip(got, again) for a, b in zip(ra, rb))      # bit for bit, run to run
+    finally:
+        ctx.set_option("groupby_lanes", 1)
+        ctx.set_option("groupby_registers", 1)
 
 
 @pytest.mark.parametrize("ngroups", [30, 60])

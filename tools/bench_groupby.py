@@ -17,6 +17,7 @@ ap.add_argument("--rows", type=int, default=600_000_000)
 ap.add_argument("--reps", type=int, default=3)
 ap.add_argument("--cards", default="4,32,1024,65536")
 ap.add_argument("--opts", default="")
+ap.add_argument("--skip-q1", action="store_true")
 args = ap.parse_args()
 peak, _ = bench.measured_peak_gbs()
 ctx = Context(0)
@@ -39,10 +40,10 @@ def timed(pipe, reps):
     return ms, v, g
 
 
-for atomic in (False, True):
+for atomic in (() if args.skip_q1 else (False, True)):
     t, pipe = bench.q1_pipeline(ctx, args.rows, atomic=atomic)
     ms, v, g = timed(pipe, args.reps)
-    print(json.dumps({"what": "q1", "rows": args.rows, "variant": ["private", "atomic", "shared", "registers", "lanes", "lanes8"][v], "groups": g[0], "threads": g[1], "kernel_ms": round(ms, 3),
+    print(json.dumps({"what": "q1", "rows": args.rows, "variant": ["private", "atomic", "shared", "registers", "lanes", "lanes8", "warps"][v], "groups": g[0], "threads": g[1], "kernel_ms": round(ms, 3),
                       "gb_per_s": round(args.rows * 48 / ms / 1e6, 1), "frac": round(args.rows * 48 / ms / 1e6 / peak, 3)}), flush=True)
     t.close()
 D = DataType.DOUBLE
@@ -52,6 +53,6 @@ for card in (int(c) for c in args.cards.split(",")):
     t.generate(0, capi.QE_GEN_UNIFORM_INT, 6, 0, card - 1)
     pipe = GroupByPipeline(t, None, [col(0)], [col(1), col(1)], [A.SUM, A.COUNT], max_groups=max(65536, 2 * card))
     ms, v, g = timed(pipe, args.reps)
-    print(json.dumps({"what": "sum_count_by_k", "cardinality": card, "variant": ["private", "atomic", "shared", "registers", "lanes", "lanes8"][v], "groups": g[0], "threads": g[1],
+    print(json.dumps({"what": "sum_count_by_k", "cardinality": card, "variant": ["private", "atomic", "shared", "registers", "lanes", "lanes8", "warps"][v], "groups": g[0], "threads": g[1],
                       "kernel_ms": round(ms, 3), "gb_per_s": round(args.rows * 16 / ms / 1e6, 1),
                       "frac": round(args.rows * 16 / ms / 1e6 / peak, 3)}), flush=True)
