@@ -338,7 +338,9 @@ size_t GroupPlan::shared_smem32() const
 size_t GroupPlan::shared_smemw() const
 {
     const size_t nk = nkeys > 0 ? (size_t)nkeys : 1;
-    return (size_t)slmaxw * (size_t)nwords * 8u * (size_t)(threads / 32) + (size_t)scslotsw * (8u * nk + 12u) + 4u * (size_t)slmaxw + 16u;
+    // accumulators + QeGroupCache + one tag byte per warp and group
+    return (size_t)slmaxw * (size_t)nwords * 8u * (size_t)(threads / 32) + (size_t)scslotsw * (8u * nk + 12u) + 4u * (size_t)slmaxw + 16u +
+           (size_t)slmaxw * (size_t)(threads / 32);
 }
 
 size_t GroupPlan::shared_smem8() const
@@ -430,12 +432,12 @@ GroupPlan plan_groupby(const BoundPipeline &bp, int threads, int lane_acc_kb)
     if (g.slmax8 < 64 || g.slmax8 <= g.slmax32) { g.slmax8 = 0; g.scslots8 = 64; }
     // one copy per warp (plain loads / stores, no atomics): threads / 32 copies, four key-cache slots per group while
     // they fit, two otherwise; up to 224 KB of the 227 KB a CTA may have
-    for (g.slmaxw = 2048; g.slmaxw >= 64; g.slmaxw -= 64) {
+    // (>= 8 key-cache slots per group: with 4, a tenth of 1 024 keys sat past their home slot and every warp step took
+    // the probing loop: 46 ms per 6e8 rows)
+    for (g.slmaxw = 2048; g.slmaxw >= 64; g.slmaxw -= 32) {
         g.scslotsw = 64;
-        while (g.scslotsw < 4 * g.slmaxw) g.scslotsw *= 2;
+        while (g.scslotsw < 8 * g.slmaxw) g.scslotsw *= 2;
         if (g.shared_smemw() <= (224u << 10)) break;
-        g.scslotsw /= 2;
-        if (g.scslotsw >= 2 * g.slmaxw && g.shared_smemw() <= (224u << 10)) break;
     }
     if (g.slmaxw < 64) { g.slmaxw = 0; g.scslotsw = 64; }
     // register variant: per group two 32-bit registers (first row, rows) + two per further word; ~96 registers

@@ -2234,16 +2234,17 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
     // warps ([group][word][lane]: lane-consecutive, conflict-free).  The same atomics, but two threads meet on a
     // word only when they have the same lane AND the same group: the CAS loops of the f64 words hardly ever retry.
     // SCOPIES = 0 ("warp" kernel): one copy per WARP, laid out [warp][word][group], updated with plain loads and stores --
-    // no atomics at all.  Lanes of a warp that meet the same group in one step are ranked with match.any and take
-    // turns, so a group's rows are added in row order per warp and the result is reproducible.  The shared-memory atomic
-    // unit was what bounded the single-copy kernel (three to five ATOMS per row; 4.7 ms per 6e8 rows whatever the
-    // contention), LDS / STS run at the full 32 lanes per clock.
+    // no atomics at all.  Lanes of a warp that meet the same group in one step find out by writing their lane number to
+    // a per-warp tag byte of the group and reading it back: the lane whose number stuck updates, the others try again.
+    // (match.any does the same in one instruction, but its latency grows with the number of distinct values: ~500
+    // cycles per step with 30 distinct groups among 32 lanes, 7-9 ms per 6e8 rows.)
     constexpr bool WARPC = P::SCOPIES == 0;
     constexpr int COPIES = WARPC ? GW : P::SCOPIES;
     typedef QeGroupCache<NKEYS, CS, LMAX> Cache;
     extern __shared__ __align__(16) unsigned char qe_gsmem[];
     qe_u64 *s_acc = (qe_u64 *)qe_gsmem;                       // [LMAX][NWORDS][COPIES], or [COPIES][NWORDS][LMAX] (WARPC)
     Cache &gc = *(Cache *)(qe_gsmem + (size_t)LMAX * NWORDS * COPIES * 8);
+    volatile unsigned char *s_tag = qe_gsmem + (size_t)LMAX * NWORDS * COPIES * 8 + sizeof(Cache);   // WARPC: [warp][LMAX] lane numbers
     const qe_u32 warp = qe_warp(), lane = qe_lane(), tid = threadIdx.x;
 
     for (int i = (int)tid; i < CS; i += GT) gc.state[i] = 0u;
@@ -2318,12 +2319,16 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
                 const int l = lg[s][j];
                 const qe_u64 row = (qe_u64)p.sel_base + (qe_u64)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j);
                 if (WARPC) {
-                    // lanes with the same group take turns, lowest lane (= lowest row of this step) first
-                    const qe_u32 peers = __match_any_sync(QE_FULL_MASK, l);
-                    const qe_u32 rank = (qe_u32)__popc(peers & qe_lanemask_lt());
-                    const qe_u32 last = __reduce_max_sync(QE_FULL_MASK, l >= 0 ? rank : 0u);
-                    for (qe_u32 r = 0; r <= last; r++) {
-                        if (l >= 0 && rank == r) P::template acc_plain<LMAX>(s_acc + (size_t)warp * NWORDS * LMAX + l, outs[s][j], row);
+                    // lanes with the same group take turns: whose lane number sticks in the group's tag byte goes first
+                    bool todo = l >= 0;
+                    volatile unsigned char *tag = s_tag + (size_t)warp * LMAX + (l >= 0 ? l : 0);
+                    while (__any_sync(QE_FULL_MASK, todo)) {
+                        if (todo) *tag = (unsigned char)lane;
+                        __syncwarp();
+                        if (todo && *tag == (unsigned char)lane) {
+                            P::template acc_plain<LMAX>(s_acc + (size_t)warp * NWORDS * LMAX + l, outs[s][j], row);
+                            todo = false;
+                        }
                         __syncwarp();
                     }
                 } else if (l >= 0) {

@@ -148,7 +148,7 @@ struct qe_ctx {
     // options
     int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = -1, opt_stages = 0, opt_debug_flags = 0, opt_pipeline = 1, opt_groupby_registers = 1, opt_groupby_lanes = 1, opt_lane_acc_kb = 0;
     int64_t opt_min_blocks = 0;
-    int64_t opt_groupby_warps = 1;
+    int64_t opt_groupby_warps = 0;      // one copy per warp: measured slower than the CAS loops, on request only
     int64_t opt_nlb = 0, opt_loads = 0, opt_tile_rows = 0, opt_ncw = 0, opt_defer = 0, opt_stage_kb = 0;
     int64_t launches = 0;
     bool warned_no_nvrtc = false;
@@ -283,7 +283,7 @@ extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
     } else if (k == "groupby_lanes") {
         ctx->opt_groupby_lanes = value != 0;                 // 0: skip the lane-copies variant (32 copies per CTA)
     } else if (k == "groupby_warps") {
-        ctx->opt_groupby_warps = value != 0;                 // 0 skips the one-copy-per-warp variant
+        ctx->opt_groupby_warps = value != 0;                 // 1 tries the one-copy-per-warp variant before the single-copy one
     } else if (k == "groupby_registers") {
         if (value < 0 || value > 2) return fail(QE_ERR_INVALID_ARGUMENT, "groupby_registers must be 0 (off), 1 (by the cost rule) or 2 (whenever the registers suffice)");
         ctx->opt_groupby_registers = value;                  // 0: group-by starts with the private (shared-memory) variant
