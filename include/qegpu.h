@@ -461,6 +461,32 @@ typedef struct qe_aot_desc {
 } qe_aot_desc;
 QE_API int qe_aot_compile(const qe_aot_desc *desc, char key_out[33], int *origin);
 
+/* ------------------------------------------------------------------ no device allocation
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * SUM / COUNT / MIN / MAX over the non-null rows of one DOUBLE column that is already on the device: the global
+ * aggregation's fixed shape (sub-tiles of 16 384 rows, 64 of them per super-tile of QE_AGG_SUPER_ROWS rows, super-tiles
+ * in row order; -fmad=false), so the result does not depend on the grid.  The per-sub-tile and per-super-tile partials --
+ * the scratch memory qe_pipeline_run takes from the context's pool -- live in one file-scope __device__ array of
+ * QE_NOALLOC_SCRATCH_BYTES instead: every GPU that loads the library holds that much until the process exits.  The call
+ * allocates nothing (no cudaMalloc / cudaFree, no context, no pool) and only enqueues three kernels on `stream`; it does not
+ * synchronize.
+ *   device      CUDA device index that owns d_values / d_validity / d_out (made current for the call, then restored)
+ *   d_values    nrows doubles, 16-byte aligned              d_validity  Arrow bitmap (bit i = row i non-null) or NULL
+ *   d_out       4 doubles, written by the last kernel: [0] SUM (0.0 without rows), [1] COUNT of non-null rows as a double
+ *               (exact below 2^53), [2] MIN (+Infinity without rows), [3] MAX (-Infinity without rows); Math.min / Math.max
+ *               and unfused adds as everywhere else in the library
+ *   stream      cudaStream_t, or NULL for the default stream
+ * nrows > QE_NOALLOC_MAX_ROWS is refused with QE_ERR_INVALID_ARGUMENT (the array has a fixed size; split the column or use
+ * qe_pipeline_run).  EVERY call on a device shares the array and the array keeps the last call's contents: a call writes
+ * every word before it reads it, so nothing needs clearing, but two calls that overlap on the GPU (different streams, or two
+ * host threads) RACE for it -- keep calls to this function on one stream per device, or order them with events. */
+#define QE_NOALLOC_MAX_ROWS 268435456LL        /* 2^28 rows = 2 GiB of doubles */
+#define QE_NOALLOC_SCRATCH_BYTES 532480        /* (16 384 sub-tile + 256 super-tile partials) x 32 B */
+QE_API int qe_agg_column_noalloc(int device, const double *d_values, const uint8_t *d_validity, int64_t nrows,
+                                 double *d_out, void *stream);
+
 QE_API const char *qe_last_error(void);
 QE_API const char *qe_version(void);
 

@@ -27,6 +27,8 @@ QE_RUN_APPEND = 4
 QE_RUN_NO_VALUES = 8
 QE_STREAM_CHUNK_RELATIVE = 1
 QE_AGG_SUPER_ROWS = 1 << 20
+QE_NOALLOC_MAX_ROWS = 1 << 28
+QE_NOALLOC_SCRATCH_BYTES = 532480
 QE_GROUPBY_ATOMIC = 1
 QE_GROUPBY_SHARED = 2
 
@@ -179,6 +181,7 @@ SYMBOLS = {
     "qe_yardstick": (C.c_int, [_vp, C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_float)]),
     "qe_result_agg_partials": (C.c_int, [_vp, C.c_int, C.POINTER(AggPartial), C.c_int64, C.POINTER(C.c_int64)]),
     "qe_aot_compile": (C.c_int, [C.POINTER(AotDesc), C.c_char_p, C.POINTER(C.c_int)]),
+    "qe_agg_column_noalloc": (C.c_int, [C.c_int, _vp, _vp, C.c_int64, _vp, _vp]),
     "qe_partition_rows": (C.c_int, [C.c_int64, C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "qe_mgpu_create": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(_vp)]),
     "qe_mgpu_destroy": (C.c_int, [_vp]),
