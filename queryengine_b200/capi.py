@@ -176,6 +176,7 @@ SYMBOLS = {
     "qe_result_group_first_rows": (C.c_int, [_vp, _vp]),
     "qe_result_group_variant": (C.c_int, [_vp]),
     "qe_result_group_threads": (C.c_int, [_vp]),
+    "qe_result_group_copies": (C.c_int, [_vp]),
     "qe_ctx_trim": (C.c_int, [_vp]),
     "qe_jit_stats": (C.c_int, [C.POINTER(C.c_double)]),
     "qe_yardstick": (C.c_int, [_vp, C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_float)]),

@@ -322,17 +322,13 @@ size_t staged_smem_bytes(const BoundPipeline &bp, const TileShape &shape)
     return (size_t)stage_layout(bp, shape).stride * (size_t)shape.nstages;
 }
 
-size_t GroupPlan::shared_smem() const
+size_t GroupPlan::copies_smem(int copies) const
 {
-    // QeGroupCache<NKEYS, CS, LMAX> of qe_device.cuh: keys, nulls, local, state per slot; slot per group; two words
+    // qe_groupby_copies_body: [group][word][copy] accumulators + QeGroupCache2<NKEYS, CS, LMAX> (one 32-bit entry per
+    // slot; key and table slot per group; four control words)
     const size_t nk = nkeys > 0 ? (size_t)nkeys : 1;
-    return (size_t)slmax * (size_t)nwords * 8u + (size_t)scslots * (8u * nk + 12u) + 4u * (size_t)slmax + 16u;
-}
-
-size_t GroupPlan::shared_smem32() const
-{
-    const size_t nk = nkeys > 0 ? (size_t)nkeys : 1;
-    return (size_t)slmax32 * (size_t)nwords * 8u * 32u + (size_t)scslots32 * (8u * nk + 12u) + 4u * (size_t)slmax32 + 16u;
+    const int ci = copies_index(copies);
+    return (size_t)clmax[ci] * ((size_t)nwords * 8u * (size_t)copies + 8u * nk + 4u) + (size_t)ccslots[ci] * 4u + 16u;
 }
 
 size_t GroupPlan::shared_smemw() const
@@ -341,12 +337,6 @@ size_t GroupPlan::shared_smemw() const
     // accumulators + QeGroupCache + one tag byte per warp and group
     return (size_t)slmaxw * (size_t)nwords * 8u * (size_t)(threads / 32) + (size_t)scslotsw * (8u * nk + 12u) + 4u * (size_t)slmaxw + 16u +
            (size_t)slmaxw * (size_t)(threads / 32);
-}
-
-size_t GroupPlan::shared_smem8() const
-{
-    const size_t nk = nkeys > 0 ? (size_t)nkeys : 1;
-    return (size_t)slmax8 * (size_t)nwords * 8u * 8u + (size_t)scslots8 * (8u * nk + 12u) + 4u * (size_t)slmax8 + 16u;
 }
 
 GroupPlan plan_groupby(const BoundPipeline &bp, int threads, int lane_acc_kb)
@@ -405,31 +395,45 @@ GroupPlan plan_groupby(const BoundPipeline &bp, int threads, int lane_acc_kb)
         if ((size_t)g.lmax * per_group + cache <= (220u << 10)) break;
     }
     if (g.lmax < 1) { g.lmax = 0; g.cslots = 64; }
-    // shared variant: one copy of the words per CTA + a key cache of 4 slots per group, all in dynamic shared memory
-    for (g.slmax = 8192; g.slmax >= 64; g.slmax /= 2) {
-        g.scslots = 4 * g.slmax;
-        if (g.shared_smem() <= (208u << 10)) break;
+    // Shared-memory variants with 32 / 16 / 8 / 4 / 2 / 1 copies of the words per CTA (qe_groupby_copies_body): as many
+    // groups as fit 224 KB with a key cache of >= 8 slots per group (a power of two; a slot is one 32-bit entry), then
+    // 16 slots per group if they still fit: with buckets of two slots fewer than one key in a thousand sits outside its
+    // home bucket, and only those rows (and new keys) leave the straight-line lookup.  (Round 1's cache took 20 bytes per
+    // slot and four loads per lookup; with 8 slots per group a sixth of the keys sat past their first slot and the loop
+    // those rows took made the kernel 6-18 x slower.)  `lane_acc_kb` caps the bytes of the copies (experiments; 0 = no cap).
+    {
+        const size_t budget = 224u << 10;
+        const size_t acc_cap = (size_t)(lane_acc_kb > 0 ? lane_acc_kb : 224) << 10;
+        for (int ci = 0; ci < 6; ci++) {
+            const int copies = 1 << ci;
+            int best = 0, best_cs = 64;
+            for (int lm = 4096; lm >= 16; lm -= 8) {
+                if ((size_t)lm * (size_t)g.nwords * 8u * (size_t)copies > acc_cap) continue;
+                int cs = 64;
+                while (cs < 8 * lm) cs *= 2;
+                g.clmax[ci] = lm;
+                g.ccslots[ci] = cs;
+                if (g.copies_smem(copies) <= budget) { best = lm; best_cs = cs; break; }
+            }
+            if (copies == 1) {
+                // the last stop before global atomics: 4 slots per group if that holds more groups (a few keys in a
+                // hundred then sit outside their home bucket and are found by the in-line probe of the next slots)
+                for (int lm = 4096; lm > best; lm -= 8) {
+                    int cs = 64;
+                    while (cs < 4 * lm) cs *= 2;
+                    g.clmax[ci] = lm;
+                    g.ccslots[ci] = cs;
+                    if (g.copies_smem(copies) <= budget) { best = lm; best_cs = cs; break; }
+                }
+            }
+            g.clmax[ci] = best;
+            g.ccslots[ci] = best_cs;
+            if (best > 0 && g.ccslots[ci] < 16 * best) {
+                g.ccslots[ci] *= 2;
+                if (g.copies_smem(copies) > budget) g.ccslots[ci] /= 2;
+            }
+        }
     }
-    if (g.slmax < 64) { g.slmax = 0; g.scslots = 64; }
-    // lane-private copies: 32 x the accumulator bytes, 8 key-cache slots per group
-    // Key cache: >= 16 slots per group.  With 8 (256 groups in 2 048 slots) a sixth of the keys sat past their first
-    // slot and the probing loop those rows take made the kernel 6-18 x slower (SUM + COUNT over 16-byte rows: 2.2 ms
-    // with 128 groups, 13.8 / 24.8 / 40.8 ms with 160 / 192 / 256); with 16 the same 160 groups take 2.25 ms.  A
-    // straight-line second probe did not help.  `lane_acc_kb` caps the bytes of the copies (experiments; 0 = no cap).
-    const size_t lane_cap = (size_t)(lane_acc_kb > 0 ? lane_acc_kb : 200) << 10;
-    g.slmax32 = (int)std::min<size_t>(1024, lane_cap / ((size_t)g.nwords * 8u * 32u));
-    for (; g.slmax32 >= 16; g.slmax32--) {
-        g.scslots32 = 64;
-        while (g.scslots32 < 16 * g.slmax32) g.scslots32 *= 2;
-        if (g.shared_smem32() <= (208u << 10)) break;
-    }
-    if (g.slmax32 < 16) { g.slmax32 = 0; g.scslots32 = 64; }
-    for (g.slmax8 = 2048; g.slmax8 >= 64; g.slmax8--) {
-        g.scslots8 = 64;
-        while (g.scslots8 < 16 * g.slmax8) g.scslots8 *= 2;
-        if (g.shared_smem8() <= (208u << 10)) break;
-    }
-    if (g.slmax8 < 64 || g.slmax8 <= g.slmax32) { g.slmax8 = 0; g.scslots8 = 64; }
     // one copy per warp (plain loads / stores, no atomics): threads / 32 copies, four key-cache slots per group while
     // they fit, two otherwise; up to 224 KB of the 227 KB a CTA may have
     // (>= 8 key-cache slots per group: with 4, a tenth of 1 024 keys sat past their home slot and every warp step took
@@ -725,14 +729,13 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         snprintf(b, sizeof b, "    static constexpr int NKEYS = %d, NWORDS = %d, LMAX = %d, CSLOTS = %d, GTHREADS = %d;\n", gp.nkeys > 0 ? gp.nkeys : 1,
                  gp.nwords, gp.lmax > 0 ? gp.lmax : 1, gp.cslots, gp.threads);
         s += b;
-        if (shape.scopies == 32)
-            snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = 32;\n", gp.slmax32 > 0 ? gp.slmax32 : 32, gp.scslots32);
-        else if (shape.scopies == 8)
-            snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = 8;\n", gp.slmax8 > 0 ? gp.slmax8 : 64, gp.scslots8);
-        else if (shape.scopies < 0)     // one copy per warp, plain loads and stores (qe_groupby_shared_body, WARPC)
+        if (shape.scopies < 0)          // one copy per warp, plain loads and stores (qe_groupby_shared_body, WARPC)
             snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = 0;\n", gp.slmaxw > 0 ? gp.slmaxw : 64, gp.scslotsw);
-        else
-            snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = 1;\n", gp.slmax > 0 ? gp.slmax : 64, gp.scslots);
+        else {                          // 32 / 16 / 8 / 4 / 2 / 1 copies per CTA (qe_groupby_copies_body)
+            const int ci = GroupPlan::copies_index(shape.scopies);
+            snprintf(b, sizeof b, "    static constexpr int SLMAX = %d, SCSLOTS = %d, SCOPIES = %d;\n", gp.clmax[ci] > 0 ? gp.clmax[ci] : 16,
+                     gp.clmax[ci] > 0 ? gp.ccslots[ci] : 64, 1 << ci);
+        }
         s += b;
         {
             int rcs = 64;
@@ -781,7 +784,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
             // register variant: called for every g in [0, RMAX), branch-free -- every update is a predicated
             // instruction or a select on (l == g).  (As `if (l == g) update` the compiler built a divergent switch:
             // every group met by the warp ran as its own branch, ~140 cycles per group and warp step.)
-            s += atomic ? "    template <int AS> static __device__ __forceinline__ void acc_atomic(qe_u64 *a, const Out &o, qe_u64 row) {\n"
+            s += atomic ? "    template <int AS, bool FIRST = true> static __device__ __forceinline__ void acc_atomic(qe_u64 *a, const Out &o, qe_u64 row) {\n"
                : rfma ? "    static __device__ __forceinline__ void acc_regs_fma(qe_u32 &first, qe_u32 &rows, qe_u64 (&a)[NWORDS], const Out &o, qe_u32 row, int l, int g) {\n"
                : regs ? "    static __device__ __forceinline__ void acc_regs(qe_u32 &first, qe_u32 &rows, qe_u64 (&a)[NWORDS], const Out &o, qe_u32 row, int l, int g) {\n"
                         : "    template <int WS> static __device__ __forceinline__ void acc_plain(qe_u64 *a, const Out &o, qe_u64 row) {\n";
@@ -795,7 +798,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
             if (atomic) {
                 // word 0, little endian: rows in the low half, first row in the high half.  After the first few rows
                 // of a group nothing is smaller any more -- look before the atomic.
-                s += "        if ((qe_u32)row < ((volatile qe_u32 *)a)[1]) atomicMin(((unsigned int *)a) + 1, (unsigned int)row);\n";
+                // (FIRST = false: the caller knows whether the group is young enough for this row to matter, qe_groupby_copies_body)
+                s += "        if (FIRST && (qe_u32)row < ((volatile qe_u32 *)a)[1]) atomicMin(((unsigned int *)a) + 1, (unsigned int)row);\n";
                 s += "        atomicAdd((unsigned int *)a, 1u);\n";
             } else if (regs) {
                 // a thread meets its rows in ascending order, but min() keeps this independent of that
@@ -879,7 +883,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                      : mode == KM_PROJECT ? (shape.pring ? "qe_project_ring_body" : "qe_project_body") : mode == KM_AGG ? "qe_agg_body"
                      : mode == KM_GROUPBY_PRIVATE ? "qe_groupby_private_body"
                      : mode == KM_GROUPBY_REG ? "qe_groupby_reg_body"
-                     : mode == KM_GROUPBY_SHARED ? "qe_groupby_shared_body" : "qe_groupby_atomic_body";
+                     : mode == KM_GROUPBY_SHARED ? (shape.scopies < 0 ? "qe_groupby_shared_body" : "qe_groupby_copies_body") : "qe_groupby_atomic_body";
     snprintf(b, sizeof b,
              "extern \"C\" __global__ void __launch_bounds__(%d, %d) %s"
              "(const __grid_constant__ QeParams p)\n{\n    %s<P>(p);\n}\n",
@@ -898,7 +902,9 @@ const char *jit_entry_name(KernelMode mode, const TileShape &shape)
     case KM_PROJECT: return shape.pring ? "qe_project_ring_kernel" : "qe_project_kernel";
     case KM_AGG: return "qe_agg_kernel";
     case KM_GROUPBY_PRIVATE: return "qe_groupby_private_kernel";
-    case KM_GROUPBY_SHARED: return shape.scopies == 32 ? "qe_groupby_lane_kernel" : shape.scopies == 8 ? "qe_groupby_lane8_kernel"
+    case KM_GROUPBY_SHARED: return shape.scopies == 32 ? "qe_groupby_lane_kernel" : shape.scopies == 16 ? "qe_groupby_lane16_kernel"
+                                 : shape.scopies == 8 ? "qe_groupby_lane8_kernel" : shape.scopies == 4 ? "qe_groupby_lane4_kernel"
+                                 : shape.scopies == 2 ? "qe_groupby_lane2_kernel"
                                  : shape.scopies < 0 ? "qe_groupby_warp_kernel" : "qe_groupby_shared_kernel";
     case KM_GROUPBY_REG: return "qe_groupby_reg_kernel";
     default: return "qe_groupby_atomic_kernel";

@@ -31,12 +31,11 @@ struct GroupPlan {
     int threads = 256;                     // private variant: threads per CTA (512 when enough groups still fit)
     int lmax = 0, cslots = 0;              // private variant: groups per CTA that fit shared memory, key-cache slots
     size_t private_smem() const { return (size_t)nwords * (size_t)lmax * (size_t)threads * 8u; }
-    int slmax = 0, scslots = 0;            // shared variant: groups per CTA (one copy of the words), key-cache slots
-    size_t shared_smem() const;            // accumulators + key cache, all dynamic
-    int slmax32 = 0, scslots32 = 0;        // the same with one copy of the words per LANE (32 per CTA): contention / 32
-    size_t shared_smem32() const;
-    int slmax8 = 0, scslots8 = 0;          // ... and with 8 copies (lane & 7): more groups, contention / 8
-    size_t shared_smem8() const;
+    // shared-memory variants with 2^i copies of the words per CTA, i = 0..5 (qe_groupby_copies_body): groups per CTA and
+    // key-cache slots; 0 groups = the variant does not fit
+    int clmax[6] = {0, 0, 0, 0, 0, 0}, ccslots[6] = {64, 64, 64, 64, 64, 64};
+    static int copies_index(int copies) { int i = 0; while ((1 << i) < copies && i < 5) i++; return i; }
+    size_t copies_smem(int copies) const;  // accumulators + key cache, all dynamic
     int slmaxw = 0, scslotsw = 0;          // ... and with one copy per WARP, updated without atomics (threads / 32 copies)
     size_t shared_smemw() const;
     int rmax = 0;                          // register variant: groups per CTA whose accumulators every thread keeps in registers (0: not applicable)

@@ -1799,6 +1799,21 @@ __device__ __forceinline__ qe_u32 qe_group_hash(const qe_u64 (&k)[NKEYS], qe_u32
     return (qe_u32)h;
 }
 
+// all 64 bits of the same hash (its low half is qe_group_hash): four 16-bit fields = four independent home slots
+template <int NKEYS>
+__device__ __forceinline__ qe_u64 qe_group_hash64(const qe_u64 (&k)[NKEYS], qe_u32 nulls)
+{
+    qe_u64 h = 0x9e3779b97f4a7c15ULL ^ (qe_u64)nulls;
+#pragma unroll
+    for (int i = 0; i < NKEYS; i++) {
+        h ^= k[i];
+        h ^= h >> 32;
+        h *= 0xff51afd7ed558ccdULL;
+        h ^= h >> 29;
+    }
+    return h;
+}
+
 __device__ __forceinline__ qe_u32 qe_ld_acquire_u32(const qe_u32 *p)
 {
     qe_u32 v;
@@ -1906,6 +1921,96 @@ __device__ __noinline__ int qe_group_local_slow(const QeParams &p, QeGroupCache<
                 __threadfence_block();
                 gc.state[c] = 2u;
                 l = nl;
+                done = true;
+            }
+        } else if (++spins > (1u << 24)) {
+            gc.over = 1u;
+            done = true;
+        }
+    }
+    return l;
+}
+
+// Key cache of the shared-memory variants with copies (qe_groupby_copies_body): key -> local group.  These kernels are
+// bound by the number of shared-memory wavefronts per row (ncu: l1tex data-pipe wavefronts 85-95 % of peak), and a miss
+// in the straight-line lookup sends the whole warp through a loop, so the cache is built for two things: few loads per
+// lookup and (nearly) no misses, whatever the keys look like.
+//   * a slot is ONE 32-bit entry: ready | young | local group (13 bits) | null flags of the key (8) | 9 hash bits;
+//     0 = empty, 1 = being written.  The key itself is stored once per GROUP (gkeys[local]).
+//   * a bucket is two adjacent entries, read with one 64-bit load.  A key lives in the first free slot of its home
+//     bucket, else of the following buckets.  With >= 8 slots per group a bucket holds 0.25 keys on average and fewer
+//     than one key in a thousand sits outside its home bucket.
+//   * lookup: load the bucket, pick the entry whose null flags and hash bits match, load that group's key and compare
+//     (two dependent loads: 6 + 6 wavefronts per 32 rows at random addresses; round 1's cache took four loads, 16.5).
+//     Everything else -- new keys, the rare displaced key, a 9-bit false positive next to the right entry -- takes
+//     qe_group_local_slow2.
+// YOUNG marks a group inserted in the current epoch (QE_GM_EPOCH_TILES tiles of the CTA between two barriers): only rows
+// that see it, or come out of the slow path, update the group's first-row word -- in later epochs every row of the CTA
+// has a larger row index than the row that inserted the group.
+#define QE_GM_READY 0x80000000u
+#define QE_GM_YOUNG 0x40000000u
+#define QE_GM_MATCH 0x8001ffffu      /* ready + null flags + hash bits */
+#define QE_GM_EPOCH_TILES 32u
+
+template <int NKEYS, int CS, int LMAX>
+struct QeGroupCache2 {
+    qe_u32 entry[CS];           // CS / 2 buckets
+    qe_u64 gkeys[LMAX][NKEYS];  // key of every local group
+    qe_u32 slot[LMAX];          // table slot of every local group
+    qe_u32 nlocal, over, inserted, pad;
+};
+
+__device__ __forceinline__ qe_u32 qe_group_entry_tag(qe_u64 h, qe_u32 nulls)
+{
+    return QE_GM_READY | (nulls << 9) | ((qe_u32)(h >> 40) & 0x1ffu);
+}
+
+// finds the key or inserts it; the local group, or -1 when the run has to be discarded (gc.over)
+template <int NKEYS, int CS, int LMAX>
+__device__ __noinline__ int qe_group_local_slow2(const QeParams &p, QeGroupCache2<NKEYS, CS, LMAX> *gcp, const qe_u64 (&k)[NKEYS],
+                                                 qe_u32 nulls, qe_u64 h)
+{
+    static_assert(LMAX <= 8192 && (CS & (CS - 1)) == 0 && CS >= 2, "13 bits of local group; buckets of two");
+    volatile QeGroupCache2<NKEYS, CS, LMAX> &gc = *gcp;
+    const qe_u32 tag = qe_group_entry_tag(h, nulls);
+    int l = -1;
+    qe_u32 c = ((qe_u32)h & (qe_u32)(CS / 2 - 1)) * 2u;      // first slot of the home bucket
+    int probe = 0;
+    qe_u32 spins = 0;
+    bool done = false;
+    while (!done) {                                           // same loop shape as qe_group_global_slot
+        const qe_u32 e = gc.entry[c];
+        if (gc.over) {
+            done = true;                                      // the run is discarded anyway
+        } else if (e & QE_GM_READY) {
+            bool same = (e & QE_GM_MATCH) == tag;
+            if (same) {
+                const int cand = (int)((e >> 17) & 0x1fffu);
+#pragma unroll
+                for (int i = 0; i < NKEYS; i++) same = same && gc.gkeys[cand][i] == k[i];
+                if (same) l = cand;
+            }
+            if (same) {
+                done = true;
+            } else {
+                c = (c + 1u) & (qe_u32)(CS - 1);
+                if (++probe >= CS) { gc.over = 1u; done = true; }
+            }
+        } else if (e == 0u) {
+            if (atomicCAS(&gcp->entry[c], 0u, 1u) == 0u) {
+                const int nl = (int)atomicAdd(&gcp->nlocal, 1u);
+                if (nl >= LMAX) {
+                    gc.over = 1u;                             // the slot stays "being written": whoever waits for it sees `over`
+                } else {
+#pragma unroll
+                    for (int i = 0; i < NKEYS; i++) gc.gkeys[nl][i] = k[i];
+                    const int gs = qe_group_global_slot<NKEYS>(p, k, nulls, (qe_u32)h);
+                    gc.slot[nl] = gs < 0 ? 0xffffffffu : (qe_u32)gs;
+                    gc.inserted = 1u;
+                    __threadfence_block();
+                    gc.entry[c] = tag | QE_GM_YOUNG | ((qe_u32)nl << 17);
+                    l = nl;
+                }
                 done = true;
             }
         } else if (++spins > (1u << 24)) {
@@ -2354,6 +2459,178 @@ __device__ __forceinline__ void qe_groupby_shared_body(const QeParams &p)
             v = s_acc[(size_t)i * COPIES];
             for (int c = 1; c < COPIES; c++) v = qe_group_combine(kind, v, s_acc[(size_t)i * COPIES + c]);   // the lane copies in lane order
         }
+        p.g_part[(size_t)blockIdx.x * LMAX * NWORDS + i] = v;
+    }
+    qe_u32 *ps = p.g_part_slot + (size_t)blockIdx.x * (1 + LMAX);
+    if (tid == 0) {
+        ps[0] = (qe_u32)nlocal;
+        if (gc.over) atomicOr(p.g_ctl + 1, 1u);
+    }
+    for (int i = (int)tid; i < nlocal; i += GT) ps[1 + i] = gc.slot[i];
+}
+
+// The shared-memory variants with COPIES = 32, 16, 8, 4, 2 or 1 copies of the accumulator words per CTA
+// ([group][word][copy], copy = lane & (COPIES - 1): with 32 -- 16 for the 8-byte words -- every lane has its own bank),
+// updated with shared-memory atomics like qe_groupby_shared_body, around the two-load key cache above.  What the
+// kernel is bound by is the number of shared-memory wavefronts per row: a probe was 4 loads at random addresses (16.5
+// wavefronts per 32 rows), now 2 (9.5); the look at the first-row word (3.5) is gone for all but young groups; more
+// copies in the same shared memory (a slot is 12 bytes instead of 20, four slots per group instead of sixteen) cut the
+// bank conflicts of the atomics.
+template <class P>
+__device__ __forceinline__ void qe_groupby_copies_body(const QeParams &p)
+{
+    constexpr int STEPS = P::STEPS, VEC = P::VEC, NKEYS = P::NKEYS, NWORDS = P::NWORDS, LMAX = P::SLMAX, CS = P::SCSLOTS;
+    constexpr int GT = P::GTHREADS, GW = GT / 32;
+    constexpr int WARP_ROWS = STEPS * 32 * VEC;
+    constexpr int TILE = GW * WARP_ROWS;
+    constexpr int COPIES = P::SCOPIES;
+    static_assert(COPIES >= 1 && COPIES <= 32 && (COPIES & (COPIES - 1)) == 0, "copies per CTA: a power of two up to 32");
+    static_assert(STEPS * VEC <= 32, "one miss bit per row of a thread");
+    typedef QeGroupCache2<NKEYS, CS, LMAX> Cache;
+    extern __shared__ __align__(16) unsigned char qe_gsmem[];
+    qe_u64 *s_acc = (qe_u64 *)qe_gsmem;                       // [LMAX][NWORDS][COPIES]
+    Cache &gc = *(Cache *)(qe_gsmem + (size_t)LMAX * NWORDS * COPIES * 8);
+    const qe_u32 warp = qe_warp(), lane = qe_lane(), tid = threadIdx.x;
+
+    for (int i = (int)tid; i < CS; i += GT) gc.entry[i] = 0u;
+    if (tid == 0) { gc.nlocal = 0u; gc.over = 0u; gc.inserted = 0u; }
+    for (int i = (int)tid; i < LMAX * NWORDS * COPIES; i += GT) s_acc[i] = P::word_init((i / COPIES) % NWORDS);
+    __syncthreads();
+
+    typename P::Row rows[STEPS][VEC];
+    if (blockIdx.x < p.ntiles) {
+#pragma unroll
+        for (int s = 0; s < STEPS; s++)
+            P::load(p, (qe_i64)blockIdx.x * TILE + (qe_i64)warp * WARP_ROWS + (qe_i64)s * 32 * VEC + lane * VEC, rows[s]);
+    }
+    qe_u32 it = 0;
+    for (qe_u32 tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+        // End of an epoch (every warp of the CTA runs the same tiles, so the barriers match).  More groups than this
+        // variant holds, here or in another CTA: the run is discarded, stop reading.  Groups inserted during the
+        // epoch stop being young: no warp is inside a tile now, and every later row of this CTA has a larger index.
+        if ((++it & (QE_GM_EPOCH_TILES - 1u)) == 0u) {
+            const bool mine = ((const volatile qe_u32 &)gc.over) != 0u;
+            if (__syncthreads_or((mine || (tid == 0 && (qe_ld_relaxed_u32(p.g_ctl + 1) & 1u))) ? 1 : 0)) break;
+            if (__syncthreads_or(((const volatile qe_u32 &)gc.inserted) != 0u ? 1 : 0)) {
+                for (int i = (int)tid; i < CS; i += GT) {
+                    const qe_u32 m = gc.entry[i];
+                    if (m & QE_GM_YOUNG) gc.entry[i] = m & ~QE_GM_YOUNG;
+                }
+                if (tid == 0) gc.inserted = 0u;
+                __syncthreads();
+            }
+        }
+        const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
+        typename P::Row next[STEPS][VEC];
+        const qe_u32 ntile = tile + gridDim.x < p.ntiles ? tile + gridDim.x : tile;
+#pragma unroll
+        for (int s = 0; s < STEPS; s++)
+            P::load(p, (qe_i64)ntile * TILE + (qe_i64)warp * WARP_ROWS + (qe_i64)s * 32 * VEC + lane * VEC, next[s]);
+        typename P::Out outs[STEPS][VEC];
+        qe_u32 keep[STEPS];
+        qe_rows_eval<P>(p, warp_row0, rows, outs, keep);
+        // home buckets of all rows first (unconditional reads, all in flight together), the rare misses second, updates third
+        const volatile Cache &vc = gc;
+        int lg[STEPS][VEC];                                   // local group | young << 22, or -1
+        qe_u32 miss = 0;
+#pragma unroll
+        for (int s = 0; s < STEPS; s++) {
+#pragma unroll
+            for (int j = 0; j < VEC; j++) {
+                const bool kept = (keep[s] >> j) & 1u;
+                qe_u64 k[NKEYS];
+                qe_u32 nulls;
+                P::key_pack(outs[s][j], k, nulls);
+                const qe_u64 h = qe_group_hash64<NKEYS>(k, nulls);
+                const qe_u32 tag = qe_group_entry_tag(h, nulls);
+                const qe_u64 e = *(const volatile qe_u64 *)&gc.entry[((qe_u32)h & (qe_u32)(CS / 2 - 1)) * 2u];    // the home bucket
+                const qe_u32 e0 = (qe_u32)e, e1 = (qe_u32)(e >> 32);
+                const bool m0 = (e0 & QE_GM_MATCH) == tag, m1 = (e1 & QE_GM_MATCH) == tag;
+                const qe_u32 pick = m0 ? e0 : e1;
+                const int cand = (m0 || m1) ? (int)((pick >> 17) & 0x1fffu) : 0;
+                bool hit = m0 || m1;
+#pragma unroll
+                for (int i = 0; i < NKEYS; i++) hit &= vc.gkeys[cand][i] == k[i];
+                lg[s][j] = (kept && hit) ? (cand | (int)((pick >> 8) & 0x400000u)) : -1;
+                miss |= (kept && !hit) ? (1u << (s * VEC + j)) : 0u;
+            }
+        }
+        if (miss) {
+            // A key that found its home bucket full sits in one of the next buckets (or, after a false match of the 9
+            // hash bits, in the other slot of its home bucket): look there in line -- a single displaced key among a
+            // few hundred sends a row of nearly every other tile this way, and the loop below costs ~10 x as much.
+            // Measured alternatives (profiles/r02_groupby_copies_steps.jsonl): the next bucket loaded in the lookup above
+            // for the rows that need it, predicated: +0.5 ms for every key set (the rows that do not need it wait for the
+            // load as well); behind one vote per tile: +0.2 ms for every key set, none for displaced keys; here: nothing
+            // for key sets without displaced keys, two shared-memory round trips for a displaced row's warp.
+#pragma unroll
+            for (int s = 0; s < STEPS; s++) {
+#pragma unroll
+                for (int j = 0; j < VEC; j++) {
+                    if (!((miss >> (s * VEC + j)) & 1u)) continue;
+                    qe_u64 k[NKEYS];
+                    qe_u32 nulls;
+                    P::key_pack(outs[s][j], k, nulls);
+                    const qe_u64 h = qe_group_hash64<NKEYS>(k, nulls);
+                    const qe_u32 tag = qe_group_entry_tag(h, nulls);
+                    int l = -1;
+                    {                                                          // the next bucket: one load for its two slots
+                        const qe_u64 f = *(const volatile qe_u64 *)&gc.entry[((((qe_u32)h & (qe_u32)(CS / 2 - 1)) + 1u) & (qe_u32)(CS / 2 - 1)) * 2u];
+                        const qe_u32 f0 = (qe_u32)f, f1 = (qe_u32)(f >> 32);
+                        const bool n0 = (f0 & QE_GM_MATCH) == tag, n1 = (f1 & QE_GM_MATCH) == tag;
+                        if (n0 || n1) {
+                            const qe_u32 pick = n0 ? f0 : f1;
+                            const int cand = (int)((pick >> 17) & 0x1fffu);
+                            bool same = true;
+#pragma unroll
+                            for (int i = 0; i < NKEYS; i++) same &= vc.gkeys[cand][i] == k[i];
+                            if (same) l = cand | (int)((pick >> 8) & 0x400000u);
+                        }
+                    }
+                    for (qe_u32 d = 0; d < 8u && l < 0; d++) {                 // slots 0..7 from the home bucket on
+                        const qe_u32 e = vc.entry[(((qe_u32)h & (qe_u32)(CS / 2 - 1)) * 2u + d) & (qe_u32)(CS - 1)];
+                        if ((e & QE_GM_MATCH) != tag) continue;
+                        const int cand = (int)((e >> 17) & 0x1fffu);
+                        bool same = true;
+#pragma unroll
+                        for (int i = 0; i < NKEYS; i++) same &= vc.gkeys[cand][i] == k[i];
+                        if (same) l = cand | (int)((e >> 8) & 0x400000u);
+                    }
+                    if (l < 0) {
+                        l = qe_group_local_slow2<NKEYS, CS, LMAX>(p, &gc, k, nulls, h);
+                        if (l >= 0) l |= 1 << 22;                             // out of the loop: treat as young
+                    }
+                    lg[s][j] = l;
+                }
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < STEPS; s++) {
+#pragma unroll
+            for (int j = 0; j < VEC; j++) {
+                const int l = lg[s][j];
+                if (l >= 0) {
+                    const qe_u64 row = (qe_u64)p.sel_base + (qe_u64)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j);
+                    qe_u64 *a = s_acc + (size_t)(l & 0x3fffff) * NWORDS * COPIES + (lane & (qe_u32)(COPIES - 1));
+                    if (l >> 22) atomicMin(((unsigned int *)a) + 1, (unsigned int)row);
+                    // Row after row: overlapping the compare-and-swap loops of a thread's rows (all loads, then all CAS)
+                    // widens the window between a load and its CAS and most of them fail -- 2.1 -> 2.9 ms at 256 groups,
+                    // 6 ms at 32 (profiles/r02_groupby_copies_steps.jsonl, step 4).
+                    P::template acc_atomic<COPIES, false>(a, outs[s][j], row);
+                }
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < STEPS; s++)
+#pragma unroll
+            for (int j = 0; j < VEC; j++) rows[s][j] = next[s][j];
+    }
+    __syncthreads();
+    const int nlocal = (int)(gc.nlocal < (qe_u32)LMAX ? gc.nlocal : (qe_u32)LMAX);
+    for (int i = (int)tid; i < nlocal * NWORDS; i += GT) {
+        const int kind = P::word_kind(i % NWORDS);
+        qe_u64 v = s_acc[(size_t)i * COPIES];
+        for (int c = 1; c < COPIES; c++) v = qe_group_combine(kind, v, s_acc[(size_t)i * COPIES + c]);   // the copies in lane order
         p.g_part[(size_t)blockIdx.x * LMAX * NWORDS + i] = v;
     }
     qe_u32 *ps = p.g_part_slot + (size_t)blockIdx.x * (1 + LMAX);

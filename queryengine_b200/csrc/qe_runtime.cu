@@ -622,6 +622,7 @@ struct qe_result {
     DevBuf g_state, g_keys, g_nulls, g_acc, g_ctl, g_part, g_part_slot, g_records;
     std::vector<std::vector<uint8_t>> h_values, h_valid;    // per output column: values in the column's layout, Arrow bitmap
     int64_t h_rows = 0;
+    int g_copies = 0;                                        // shared-memory variants: copies of the accumulator words per CTA
     int g_nkeys = 0, g_variant = 0, g_threads = 0;          // variant: 0 private accumulators, 1 global atomics, 2 CTA-shared, 3 registers, 4 lane copies, 5 eight copies
     std::string g_seen_sig;                                 // signature of the last group-by that completed into this result ...
     int g_seen_groups = 0;                                  // ... and how many groups it found (sizes the register variant next time)
@@ -903,7 +904,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     char suffix[128];
     snprintf(suffix, sizeof suffix, "|M%d|B%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d.%d|G%d", (int)mode, shape.min_blocks, shape.steps, shape.vec, shape.staged ? 1 : 0,
              shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0, shape.ring ? 1 : 0, shape.tile_rows, shape.ncw,
-             shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0) + (shape.pring ? 200000 : 0) + (shape.scopies == 32 ? 400000 + 1000000 * shape.lane_acc_kb : shape.scopies == 8 ? 800000 : shape.scopies < 0 ? 1600000 : 0));
+             shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0) + (shape.pring ? 200000 : 0) + (shape.scopies < 0 ? 1600000 : shape.scopies > 1 ? 400000 * shape.scopies + 100000000 * shape.lane_acc_kb : 0));
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) {
@@ -1507,6 +1508,11 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     const int rmax_full = ctx->opt_groupby_registers == 2 ? gp.rmax_regs : gp.rmax;
     int rmax_use = rmax_full;
     if (r->g_seen_sig == sig && r->g_seen_groups > 0) rmax_use = std::min(rmax_full, std::max(4, r->g_seen_groups));
+    // the most copies per CTA that hold the groups the same group-by found last time (every CTA meets nearly all of them)
+    int hint_copies = 0;
+    if (r->g_seen_sig == sig && r->g_seen_groups > 0)
+        for (int c = 32; c >= 1 && !hint_copies; c /= 2)
+            if (gp512.clmax[qe::GroupPlan::copies_index(c)] >= r->g_seen_groups) hint_copies = c;
     for (;; level++) {
         const bool regs = level == 0;
         qe::TileShape reg_shape;
@@ -1521,17 +1527,24 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
         if (level == 2 && (gp.lmax < 1 || gp.lmax <= gp512.lmax)) continue;
         // few words per group: the lane copies are faster than the 256-thread private copies (SUM + COUNT over 16-byte
         // rows: 2.2 ms against 2.5 ms at 32-48 groups) and hold more groups
-        if (level == 2 && gp.nwords <= 3 && ctx->opt_groupby_lanes && gp512.slmax32 >= gp.lmax) continue;
-        if (level == 3 && (gp512.slmax32 < 16 || !ctx->opt_groupby_lanes)) continue;
-        if (level == 4 && (gp512.slmax8 < 64 || !ctx->opt_groupby_lanes)) continue;
+        if (level == 2 && gp.nwords <= 3 && ctx->opt_groupby_lanes && gp512.clmax[5] >= gp.lmax) continue;
+        // shared-memory copies: level 3 = 32 per CTA, 4 = 8, 6 = 2 (1 where one copy holds more groups); a group-by that knows how many groups it found last
+        // time goes straight to the most copies that hold them (16 and 4 included)
+        int copies = level == 3 ? 32 : level == 4 ? 8 : level == 6 ? (gp512.clmax[0] > gp512.clmax[1] ? 1 : 2) : 0;
+        if (copies) {
+            if (!ctx->opt_groupby_lanes && copies > 2) continue;
+            if (hint_copies > 0 && copies > hint_copies) continue;                       // would overflow again
+            if (hint_copies > copies) copies = hint_copies;
+            if (gp512.clmax[qe::GroupPlan::copies_index(copies)] < 16) continue;
+        }
         if (level == 5 && (gp.slmaxw < 64 || !ctx->opt_groupby_warps)) continue;
-        if (level == 6 && gp512.slmax < 64) continue;
-        const bool atomic = level >= 7, shared = level >= 3 && level <= 6, lanes = level == 3, lanes8 = level == 4, warpc = level == 5;
+        const bool atomic = level >= 7, shared = level >= 3 && level <= 6, warpc = level == 5;
         const qe::GroupPlan &plan = (level == 1 || (shared && !warpc)) ? gp512 : gp;
         const qe::KernelMode mode = regs ? qe::KM_GROUPBY_REG : atomic ? qe::KM_GROUPBY_ATOMIC : shared ? qe::KM_GROUPBY_SHARED : qe::KM_GROUPBY_PRIVATE;
-        const int part_groups = regs ? rmax_use : lanes ? plan.slmax32 : lanes8 ? plan.slmax8 : warpc ? plan.slmaxw : shared ? plan.slmax : plan.lmax;
+        const int ci = qe::GroupPlan::copies_index(copies ? copies : 1);
+        const int part_groups = regs ? rmax_use : warpc ? plan.slmaxw : shared ? plan.clmax[ci] : plan.lmax;
         qe::TileShape shape = regs ? reg_shape : choose_shape(ctx, bp, mode);
-        shape.scopies = lanes ? 32 : lanes8 ? 8 : warpc ? -1 : 1;
+        shape.scopies = warpc ? -1 : copies ? copies : 1;
         shape.lane_acc_kb = (int)ctx->opt_lane_acc_kb;
         if (!atomic && !regs) {
             shape.gthreads = plan.threads;
@@ -1545,7 +1558,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
             return fail(QE_ERR_INVALID_ARGUMENT, "group-by tile of " + std::to_string(shape.rows_per_tile()) + " rows (threads / 32 * steps * 32 * vec) exceeds " +
                                                  std::to_string(kPadRows) + ": lower the \"steps\" / \"vec\" options");
         JitEntry *jit = nullptr;
-        rc = get_jit_kernel(ctx, bp, mode, shape, &jit, (atomic || regs) ? 0 : lanes ? plan.shared_smem32() : lanes8 ? plan.shared_smem8() : warpc ? plan.shared_smemw() : shared ? plan.shared_smem() : plan.private_smem());
+        rc = get_jit_kernel(ctx, bp, mode, shape, &jit, (atomic || regs) ? 0 : warpc ? plan.shared_smemw() : shared ? plan.copies_smem(copies) : plan.private_smem());
         if (rc < 0) return fail(QE_ERR_JIT, "group-by needs generated code: " + tls_error);
         if (rc) return rc;
         const int64_t tile_rows = shape.rows_per_tile();
@@ -1561,7 +1574,8 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
             p.g_part_slot = (qe_u32 *)r->g_part_slot.ptr;
         }
         r->mode = (int)mode;
-        r->g_variant = regs ? 3 : atomic ? 1 : lanes ? 4 : lanes8 ? 5 : warpc ? 6 : shared ? 2 : 0;
+        r->g_variant = regs ? 3 : atomic ? 1 : warpc ? 6 : copies == 32 ? 4 : copies >= 8 ? 5 : shared ? 2 : 0;
+        r->g_copies = shared && !warpc ? copies : 0;
         const int threads = regs ? shape.block_threads() : atomic ? QE_BLOCK : plan.threads;
         r->g_threads = threads;
         QE_CUDA(qe::launch_groupby_init((uint32_t *)r->g_state.ptr, (uint64_t *)r->g_acc.ptr, (uint32_t *)r->g_ctl.ptr, nslots, gw, ctx->stream));
@@ -1594,6 +1608,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
         }
         r->g_overflowed = sig;   // a CTA met more groups than fit its shared memory: next variant
         r->g_level = level + 1;
+        hint_copies = 0;         // the hint was wrong (other data): the plain ladder from here
     }
     const int64_t ngroups = ctl[0];
     r->g_seen_sig = sig;
@@ -1635,6 +1650,11 @@ extern "C" int qe_result_group_first_rows(qe_result *r, int64_t *dst)
 extern "C" int qe_result_group_variant(const qe_result *r)
 {
     return r && is_groupby(r) ? r->g_variant : -1;
+}
+
+extern "C" int qe_result_group_copies(const qe_result *r)
+{
+    return r && is_groupby(r) ? r->g_copies : -1;
 }
 
 extern "C" int qe_result_group_threads(const qe_result *r)
@@ -2199,7 +2219,7 @@ static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *co
     qe::BoundPipeline bp;
     int rc = qe::bind_pipeline(schema, has_filter ? &progs[0] : nullptr, proj, aggs, bp, err, group_keys);
     if (rc) return fail(rc, err);
-    const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : (atomic == 2 || atomic == 4 || atomic == 5 || atomic == 6) ? qe::KM_GROUPBY_SHARED : atomic == 3 ? qe::KM_GROUPBY_REG : qe::KM_GROUPBY_PRIVATE)
+    const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : (atomic == 2 || (atomic >= 4 && atomic <= 9)) ? qe::KM_GROUPBY_SHARED : atomic == 3 ? qe::KM_GROUPBY_REG : qe::KM_GROUPBY_PRIVATE)
                               : !bp.agg_fns.empty() ? qe::KM_AGG : bp.has_filter ? qe::KM_FILTER : qe::KM_PROJECT;
     qe_ctx dummy;
     dummy.opt_steps = o.steps;
@@ -2207,7 +2227,7 @@ static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *co
     dummy.opt_staging = o.staging;
     qe::TileShape shape = choose_shape(&dummy, bp, mode, o.sel_hint);
     if (o.min_blocks > 0) shape.min_blocks = o.min_blocks;
-    if (mode == qe::KM_GROUPBY_SHARED) { shape.gthreads = 512; shape.steps = 1; shape.vec = qe::jit_wide_loads_supported() ? 4 : 2; shape.scopies = atomic == 4 ? 32 : atomic == 5 ? 8 : 1; }
+    if (mode == qe::KM_GROUPBY_SHARED) { shape.gthreads = 512; shape.steps = 1; shape.vec = qe::jit_wide_loads_supported() ? 4 : 2; shape.scopies = atomic == 4 ? 32 : atomic == 5 ? 8 : atomic == 7 ? 16 : atomic == 8 ? 4 : atomic == 9 ? 2 : 1; }
     if (mode == qe::KM_GROUPBY_SHARED && atomic == 6) { shape = choose_shape(&dummy, bp, mode); shape.gthreads = 256; shape.scopies = -1; }
     if (mode == qe::KM_GROUPBY_REG && o.runtime_shapes) {       // as qe_groupby_run, level 0
         const qe::GroupPlan gp = qe::plan_groupby(bp, 256);

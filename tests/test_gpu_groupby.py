@@ -13,7 +13,7 @@ import pytest
 
 from oracle_binding import OraclePlan, OracleTable
 from parity import ulp
-from queryengine_b200 import capi
+from queryengine_b200 import capi, sharding
 from queryengine_b200.ast import AggregationFunction, DataType, Function, StringLiteralExpression, agg, col, fn
 from queryengine_b200.engine import ColumnarTable, Context, Field, GpuGroupByOperator, GroupByPipeline
 
@@ -194,12 +194,13 @@ def test_register_variant_with_nulls_and_non_finite_inputs(ctx, nrows):
 
 
 def test_eight_copies_variant_for_hundreds_of_groups(ctx):
-    # more groups than the lane copies hold (85 with three words), few enough for eight copies per CTA (variant 5)
+    # more groups than the lane copies hold, few enough for eight copies per CTA (variant 5)
     rng = np.random.default_rng(808)
     n = 60000
-    rows = [[None, bool(rng.random() < 0.5) if rng.random() > 0.1 else None, float(int(rng.integers(60))),
+    rows = [[None, bool(rng.random() < 0.5) if rng.random() > 0.1 else None, float(int(rng.integers(120))),
              float(np.round(rng.uniform(-10, 10), 1)), None if rng.random() < 0.2 else float(rng.uniform(-1e3, 1e3))] for _ in range(n)]
     b, k, x, y = col(1, B), col(2), col(3), col(4)
+    # 360 groups of three words and two keys: more than the 32 lane copies hold (~250), few enough for eight copies
     got = _check_against_oracle(ctx, rows, [b, k], [x, y, x], [A.SUM, A.COUNT, A.AVG], None, False, expect_variant=5)
     assert len(got) == len({(r[1], r[2]) for r in rows})
 
@@ -353,4 +354,58 @@ def test_int64_and_date32_key_columns(ctx):
     ot.set_column(2, x)
     want = OraclePlan(ot, [0, 1, 2], projections=[col(0), col(1), col(2), col(2)], aggregates=[A.SUM, A.COUNT], group_count=2).rows()
     assert got == want and len(got) == 7 * 5
+    t.close()
+
+
+# five words per group (first row | rows, sum, count, min, max): 168 / 320 / 592 / 1024 / 1776 / 2048 groups per CTA with
+# 32 / 16 / 8 / 4 / 2 / 1 copies.  First run: the ladder 32 -> 8 -> 1; second run: the most copies that hold the groups.
+@pytest.mark.parametrize("ngroups,first_copies,again_copies", [(100, 32, 32), (250, 8, 16), (400, 8, 8), (800, 1, 4), (1200, 1, 2), (1800, 1, 1)])
+def test_copies_variants_over_many_tiles_per_cta(ctx, ngroups, first_copies, again_copies):
+    """The shared-memory variants with 32 / 16 / 8 / 4 / 2 copies per CTA on a table large enough that every CTA runs
+    several epochs (32 tiles between two barriers): groups that first appear late are inserted in a later epoch, rows of
+    older groups skip the first-row word.  Keys are not small integers (k * 0.37).  Checked against numpy: groups in order
+    of first appearance, first rows, COUNT / MIN / MAX exact, SUM within the tolerance of tests/parity.py.  The second
+    run reuses the result: it knows the group count and goes straight to the most copies that hold it."""
+    rng = np.random.default_rng(ngroups)
+    n = 148 * 2048 * 40 + 777
+    k = rng.integers(0, ngroups // 2, n).astype(np.float64)
+    late = n - n // 5
+    k[late:] = rng.integers(0, ngroups, n - late).astype(np.float64)       # half of the groups first appear in the last fifth
+    k[rng.integers(0, n, 5)] = np.nan
+    k[rng.integers(0, n, 5)] = -0.0
+    x = np.round(rng.uniform(-1000.0, 1000.0, n), 2)
+    xv = rng.random(n) >= 0.1
+    t = ColumnarTable.from_arrays(ctx, [Field("k", D, False), Field("x", D, True)], [k, x], [None, xv])
+    key = fn(Function.MUL, col(0), 0.37)
+    pipe = GroupByPipeline(t, None, [key], [col(1), col(1), col(1), col(1)], [A.SUM, A.COUNT, A.MIN, A.MAX])
+    kk = k * 0.37
+    bits = kk.view(np.uint64).copy()
+    bits[np.isnan(kk)] = 0x7ff8000000000000
+    uniq, first, inv = np.unique(bits, return_index=True, return_inverse=True)
+    order = np.argsort(first, kind="stable")
+    rank = np.empty(len(uniq), np.int64)
+    rank[order] = np.arange(len(uniq))
+    g_of_row = rank[inv]
+    ng = len(uniq)
+    cnt = np.bincount(g_of_row[xv], minlength=ng)
+    res = None
+    for copies in (first_copies, again_copies):
+        res = pipe.run(res)
+        assert capi.lib().qe_result_group_copies(res.handle) == copies
+        assert res.num_rows == ng
+        keys, nulls, first_row, parts, _ = sharding.group_arrays(res, 1, 4)
+        assert np.array_equal(keys[:, 0], uniq[order]) and not nulls.any()
+        assert np.array_equal(first_row, first[order])
+        assert np.array_equal(parts[:, 1, 1].view(np.int64), cnt)
+        xs = np.where(xv, x, np.inf)
+        mn = np.full(ng, np.inf); np.minimum.at(mn, g_of_row, xs)
+        mx = np.full(ng, -np.inf); np.maximum.at(mx, g_of_row, np.where(xv, x, -np.inf))
+        assert np.array_equal(parts[:, 2, 2], mn) and np.array_equal(parts[:, 3, 3], mx)
+        for g in rng.integers(0, ng, 40):
+            terms = x[(g_of_row == g) & xv]
+            exact = math.fsum(terms.tolist())
+            seq = float(np.cumsum(terms)[-1]) if len(terms) else 0.0
+            tol = max(abs(seq - exact), 4 * ulp(exact), len(terms) * 2.0 ** -53 * math.fsum(np.abs(terms).tolist()))
+            assert abs(parts[g, 0, 0] - exact) <= tol
+    res.close()
     t.close()
