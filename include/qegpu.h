@@ -315,8 +315,8 @@ QE_API int qe_result_group_partial(qe_result *result, int64_t group, int k, qe_a
 QE_API int qe_result_group_first_rows(qe_result *result, int64_t *dst);
 /* 3: accumulators in registers (few groups; reproducible), 0: private accumulators in shared memory (reproducible),
  * 4: one shared-memory copy per lane index (32 per CTA), 5: sixteen or eight copies per CTA, 6: one copy per warp updated
- * without atomics (reproducible), 2: four, two or one shared-memory copies per CTA, 1: global atomics,
- * -1: not a group-by result */
+ * without atomics (reproducible), 2: four, two or one shared-memory copies per CTA, 7: two passes (rows partitioned by
+ * key hash, one CTA per partition), 1: global atomics, -1: not a group-by result */
 QE_API int qe_result_group_variant(const qe_result *result);
 /* copies of the accumulator words per CTA of variants 4 / 5 / 2 (32, 16, 8, 4, 2 or 1); 0 for the other variants */
 QE_API int qe_result_group_copies(const qe_result *result);
@@ -437,7 +437,7 @@ QE_API int qe_debug_generate(const qe_col_desc *cols, int ncols,
                              int steps, int vec, int staging, int compile,
                              char *src_buf, size_t src_cap, char *cubin_buf, size_t cubin_cap, size_t *cubin_bytes);
 
-/* Same for a group-by: programs = [filter,] nkeys key programs, nagg aggregate inputs; atomic: 0 private, 1 global atomics, 2 CTA-shared (one copy), 3 registers, 4 lane copies (32), 5 eight copies, 6 one copy per warp, 7 / 8 / 9 sixteen / four / two copies. */
+/* Same for a group-by: programs = [filter,] nkeys key programs, nagg aggregate inputs; atomic: 0 private, 1 global atomics, 2 CTA-shared (one copy), 3 registers, 4 lane copies (32), 5 eight copies, 6 one copy per warp, 7 / 8 / 9 sixteen / four / two copies, 10 / 11 the two passes (scatter, gather). */
 QE_API int qe_debug_generate_groupby(const qe_col_desc *cols, int ncols,
                                      const uint32_t *const *programs, const size_t *nwords,
                                      int has_filter, int nkeys, const int32_t *agg_fns, int nagg, int atomic, int compile,

@@ -339,6 +339,17 @@ size_t GroupPlan::shared_smemw() const
            (size_t)slmaxw * (size_t)(threads / 32);
 }
 
+void GroupPlan::scatter_shape(int rec_words, int &npart, int &pcap)
+{
+    // 512 partitions x 16 staging records for three-word records (196 KB); wider records: fewer records, then fewer partitions
+    static const int cand[][2] = {{512, 16}, {512, 8}, {256, 8}, {128, 8}, {64, 8}, {32, 8}};
+    for (const auto &c : cand) {
+        npart = c[0];
+        pcap = c[1];
+        if (scatter_smem(rec_words, npart, pcap) <= (200u << 10)) return;
+    }
+}
+
 GroupPlan plan_groupby(const BoundPipeline &bp, int threads, int lane_acc_kb)
 {
     GroupPlan g;
@@ -383,6 +394,16 @@ GroupPlan plan_groupby(const BoundPipeline &bp, int threads, int lane_acc_kb)
         g.cnt_word.push_back(in.nullable ? shared_word("cnt|", 1, 0) : -1);
     }
     g.nwords = (int)g.kind.size();
+    {
+        std::map<std::string, int> rec;
+        for (size_t k = 0; k < bp.agg_fns.size(); k++) {
+            const std::string sg = expr_sig(bp.proj[(size_t)g.nkeys + k]);
+            auto it = rec.find(sg);
+            if (it == rec.end()) it = rec.emplace(sg, (int)rec.size()).first;
+            g.rec_word.push_back(1 + std::max(g.nkeys, 1) + it->second);
+        }
+        g.rec_words = 1 + std::max(g.nkeys, 1) + (int)rec.size();
+    }
     const size_t per_group = (size_t)g.nwords * (size_t)threads * 8u;
     // shared memory of the private variant: LMAX groups of thread-private words + the key cache (>= 32 slots
     // per group, so that nearly every key sits in its first probe slot and the per-row path is straight-line
@@ -865,6 +886,49 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
             if (variant == 0)      // thread-private copies: word stride = groups x threads
                 s += "    static __device__ __forceinline__ void acc_private(qe_u64 *a, const Out &o, qe_u64 row) { acc_plain<LMAX * GTHREADS>(a, o, row); }\n";
         }
+        // two-pass variant: the record of a row (see GroupPlan::rec_words)
+        {
+            snprintf(b, sizeof b, "    static constexpr int RW = %d, NPART = %d, PCAP = %d;\n", gp.rec_words, shape.npart > 0 ? shape.npart : 32,
+                     shape.pcap > 0 ? shape.pcap : 8);
+            s += b;
+            auto to_word = [&](int k) {
+                char v[96];
+                const int t = bp.outs[k].type;
+                if (t == 1) snprintf(v, sizeof v, "(qe_u64)qe_f64_bits(o.o%d)", k);
+                else if (t == 2) snprintf(v, sizeof v, "(o.o%d ? 1ull : 0ull)", k);
+                else snprintf(v, sizeof v, "(qe_u64)(qe_i64)o.o%d", k);
+                return std::string(v);
+            };
+            auto from_word = [&](int k, int w) {
+                char v[96];
+                const int t = bp.outs[k].type;
+                if (t == 1) snprintf(v, sizeof v, "qe_bits_f64((qe_i64)rec[%d])", w);
+                else if (t == 2) snprintf(v, sizeof v, "rec[%d] != 0ull", w);
+                else if (t == 3) snprintf(v, sizeof v, "(qe_i64)rec[%d]", w);
+                else snprintf(v, sizeof v, "(qe_i32)(qe_i64)rec[%d]", w);
+                return std::string(v);
+            };
+            const int nk = gp.nkeys > 0 ? gp.nkeys : 1;
+            s += "    static __device__ __forceinline__ void record_pack(const Out &o, qe_u32 row, const qe_u64 (&k)[NKEYS], qe_u32 nulls, qe_u64 (&rec)[RW]) {\n"
+                 "        qe_u64 m = (qe_u64)row | ((qe_u64)nulls << 32);\n";
+            for (int i = 0; i < nk; i++) { snprintf(b, sizeof b, "        rec[%d] = k[%d];\n", 1 + i, i); s += b; }
+            std::vector<bool> packed((size_t)gp.rec_words, false);
+            for (size_t j = 0; j < bp.agg_fns.size(); j++) {
+                const int k = gp.nkeys + (int)j, w = gp.rec_word[j];
+                if (packed[(size_t)w]) continue;
+                packed[(size_t)w] = true;
+                snprintf(b, sizeof b, "        rec[%d] = %s;\n", w, to_word(k).c_str()); s += b;
+                if (bp.proj[k].nullable) { snprintf(b, sizeof b, "        m |= o.n%d ? (1ull << %d) : 0ull;\n", k, 40 + w - 1 - nk); s += b; }
+            }
+            s += "        rec[0] = m;\n    }\n";
+            s += "    static __device__ __forceinline__ void record_unpack(const qe_u64 (&rec)[RW], Out &o) {\n";
+            for (size_t j = 0; j < bp.agg_fns.size(); j++) {
+                const int k = gp.nkeys + (int)j, w = gp.rec_word[j];
+                snprintf(b, sizeof b, "        o.o%d = %s;\n", k, from_word(k, w).c_str()); s += b;
+                if (bp.proj[k].nullable) { snprintf(b, sizeof b, "        o.n%d = (rec[0] >> %d) & 1ull;\n", k, 40 + w - 1 - nk); s += b; }
+            }
+            s += "    }\n";
+        }
         // every SUM / AVG input of the row is finite (whether null or not: a null's value bits are arbitrary)
         s += "    static __device__ __forceinline__ bool all_finite(const Out &o) {\n        bool f = true;\n";
         {
@@ -883,7 +947,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                      : mode == KM_PROJECT ? (shape.pring ? "qe_project_ring_body" : "qe_project_body") : mode == KM_AGG ? "qe_agg_body"
                      : mode == KM_GROUPBY_PRIVATE ? "qe_groupby_private_body"
                      : mode == KM_GROUPBY_REG ? "qe_groupby_reg_body"
-                     : mode == KM_GROUPBY_SHARED ? (shape.scopies < 0 ? "qe_groupby_shared_body" : "qe_groupby_copies_body") : "qe_groupby_atomic_body";
+                     : mode == KM_GROUPBY_SHARED ? (shape.gpass == 1 ? "qe_groupby_scatter_body" : shape.gpass == 2 ? "qe_groupby_gather_body"
+                                                    : shape.scopies < 0 ? "qe_groupby_shared_body" : "qe_groupby_copies_body") : "qe_groupby_atomic_body";
     snprintf(b, sizeof b,
              "extern \"C\" __global__ void __launch_bounds__(%d, %d) %s"
              "(const __grid_constant__ QeParams p)\n{\n    %s<P>(p);\n}\n",
@@ -902,7 +967,8 @@ const char *jit_entry_name(KernelMode mode, const TileShape &shape)
     case KM_PROJECT: return shape.pring ? "qe_project_ring_kernel" : "qe_project_kernel";
     case KM_AGG: return "qe_agg_kernel";
     case KM_GROUPBY_PRIVATE: return "qe_groupby_private_kernel";
-    case KM_GROUPBY_SHARED: return shape.scopies == 32 ? "qe_groupby_lane_kernel" : shape.scopies == 16 ? "qe_groupby_lane16_kernel"
+    case KM_GROUPBY_SHARED: return shape.gpass == 1 ? "qe_groupby_scatter_kernel" : shape.gpass == 2 ? "qe_groupby_gather_kernel"
+                                 : shape.scopies == 32 ? "qe_groupby_lane_kernel" : shape.scopies == 16 ? "qe_groupby_lane16_kernel"
                                  : shape.scopies == 8 ? "qe_groupby_lane8_kernel" : shape.scopies == 4 ? "qe_groupby_lane4_kernel"
                                  : shape.scopies == 2 ? "qe_groupby_lane2_kernel"
                                  : shape.scopies < 0 ? "qe_groupby_warp_kernel" : "qe_groupby_shared_kernel";

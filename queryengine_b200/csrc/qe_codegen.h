@@ -38,6 +38,12 @@ struct GroupPlan {
     size_t copies_smem(int copies) const;  // accumulators + key cache, all dynamic
     int slmaxw = 0, scslotsw = 0;          // ... and with one copy per WARP, updated without atomics (threads / 32 copies)
     size_t shared_smemw() const;
+    // two-pass variant: a record is rec_words 8-byte words -- [0] row | key null flags << 32 | input validity << 40, then
+    // the key words, then one word per DISTINCT aggregate input (rec_word[j] of aggregate j; SUM(x), COUNT(x) share one)
+    int rec_words = 0;
+    std::vector<int> rec_word;
+    static void scatter_shape(int rec_words, int &npart, int &pcap);   // partitions and staging records that fit 200 KB
+    static size_t scatter_smem(int rec_words, int npart, int pcap) { return (size_t)npart * ((size_t)rec_words * (size_t)pcap * 8u + 4u); }
     int rmax = 0;                          // register variant: groups per CTA whose accumulators every thread keeps in registers (0: not applicable)
     int rmax_regs = 0;                     // ... by the register budget alone, without the cost rule
 };
@@ -68,6 +74,10 @@ struct TileShape {
     int scopies = 1;        // group-by, CTA-shared variant: copies of the accumulator words per CTA (1, 8 = one per lane & 7, 32 = one
                             // per lane, or -1 = one per warp, updated with plain loads and stores)
     int rmax_hint = 0;      // register variant: compile for this many groups instead of the plan's maximum (0: the maximum)
+    // group-by in two passes for more groups than a CTA's shared memory holds (qe_groupby_scatter_body / _gather_body):
+    // gpass 1 = rows -> records, partitioned by key hash into npart partitions (pcap records of staging each);
+    // gpass 2 = one CTA per partition aggregates its records with `scopies` copies.  0 = neither.
+    int gpass = 0, npart = 0, pcap = 0;
 
     int rows_per_tile() const { return (ring || greg || pring) ? tile_rows : (gthreads / 32) * steps * 32 * vec; }
     int block_threads() const { return (greg || pring) ? 32 * (1 + ncw) : ring ? 32 * (2 + nlb + ncw) : 256; }

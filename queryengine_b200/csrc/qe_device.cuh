@@ -37,7 +37,8 @@
 #include "qe_ops.h"
 
 #ifndef QE_DEBUG_FLAGS
-#define QE_DEBUG_FLAGS 0      // timing experiments only (see qe_filter_body and the ring body)
+#define QE_DEBUG_FLAGS 0      // timing experiments only (see qe_filter_body and the ring body; two-pass group-by: 256 pass 2 without
+                              // the accumulator updates, 512 pass 2 loads only, 1024 pass 1 without appends, 2048 pass 1 without flushes)
 #endif
 
 #define QE_BLOCK 256
@@ -105,6 +106,11 @@ struct QeParams {
     qe_u32       *g_part_slot;                // private variant: [grid][1 + LMAX]: local groups, then the table slot of each
     qe_u32        g_slot_mask;                // slots - 1 (a power of two)
     qe_u32        g_max_groups;
+    // group-by in two passes (qe_groupby_scatter_body / qe_groupby_gather_body): records partitioned by key hash
+    qe_u64       *pt_words;                   // [RW][NPART * pt_cap]: word w of every record, partition q at [q * pt_cap, (q + 1) * pt_cap)
+    qe_u32       *pt_cursor;                  // [NPART] records written to every partition
+    qe_u32        pt_cap;                     // records a partition holds
+    qe_u32        pt_pad;
     // literals of the expression trees (generated code reads the values from here: one kernel per literal CLASS)
     double        lit_f64[QE_MAX_LITS];       // NumericLiteralExpression values
     qe_i64        lit_lo[QE_MAX_LITS];        // floor(k) for integer-domain comparisons; dictionary code of a string literal
@@ -1831,7 +1837,7 @@ __device__ __forceinline__ void qe_st_release_u32(qe_u32 *p, qe_u32 v)
 // lane runs to the end of the iteration, so a lane that waits for a slot owned by another lane of its own
 // warp cannot keep that lane from finishing (the usual intra-warp spin-lock hazard).  Spins are bounded:
 // a run that hits the bound is discarded through the overflow flags instead of hanging the device.
-template <int NKEYS>
+template <int NKEYS, bool COUNT = true>
 __device__ __noinline__ int qe_group_global_slot(const QeParams &p, const qe_u64 (&k)[NKEYS], qe_u32 nulls, qe_u32 h)
 {
     qe_u32 s = h & p.g_slot_mask;
@@ -1851,7 +1857,9 @@ __device__ __noinline__ int qe_group_global_slot(const QeParams &p, const qe_u64
             }
         } else if (st == 0u) {
             if (atomicCAS(p.g_state + s, 0u, 1u) == 0u) {
-                if (atomicAdd(p.g_ctl, 1u) >= p.g_max_groups) atomicOr(p.g_ctl + 1, 2u);   // over the limit: the run is discarded
+                // (COUNT = false: the caller counts a whole partition's groups at once -- a million increments of one
+                // word take milliseconds)
+                if (COUNT && atomicAdd(p.g_ctl, 1u) >= p.g_max_groups) atomicOr(p.g_ctl + 1, 2u);   // over the limit: the run is discarded
 #pragma unroll
                 for (int i = 0; i < NKEYS; i++) p.g_keys[(size_t)s * NKEYS + i] = k[i];
                 p.g_nulls[s] = nulls;
@@ -1966,7 +1974,7 @@ __device__ __forceinline__ qe_u32 qe_group_entry_tag(qe_u64 h, qe_u32 nulls)
 }
 
 // finds the key or inserts it; the local group, or -1 when the run has to be discarded (gc.over)
-template <int NKEYS, int CS, int LMAX>
+template <int NKEYS, int CS, int LMAX, bool GLOBAL = true>
 __device__ __noinline__ int qe_group_local_slow2(const QeParams &p, QeGroupCache2<NKEYS, CS, LMAX> *gcp, const qe_u64 (&k)[NKEYS],
                                                  qe_u32 nulls, qe_u64 h)
 {
@@ -2004,8 +2012,10 @@ __device__ __noinline__ int qe_group_local_slow2(const QeParams &p, QeGroupCache
                 } else {
 #pragma unroll
                     for (int i = 0; i < NKEYS; i++) gc.gkeys[nl][i] = k[i];
-                    const int gs = qe_group_global_slot<NKEYS>(p, k, nulls, (qe_u32)h);
-                    gc.slot[nl] = gs < 0 ? 0xffffffffu : (qe_u32)gs;
+                    if (GLOBAL) {                             // (the two-pass variant enters its groups into the table per partition)
+                        const int gs = qe_group_global_slot<NKEYS>(p, k, nulls, (qe_u32)h);
+                        gc.slot[nl] = gs < 0 ? 0xffffffffu : (qe_u32)gs;
+                    }
                     gc.inserted = 1u;
                     __threadfence_block();
                     gc.entry[c] = tag | QE_GM_YOUNG | ((qe_u32)nl << 17);
@@ -2639,6 +2649,279 @@ __device__ __forceinline__ void qe_groupby_copies_body(const QeParams &p)
         if (gc.over) atomicOr(p.g_ctl + 1, 1u);
     }
     for (int i = (int)tid; i < nlocal; i += GT) ps[1 + i] = gc.slot[i];
+}
+
+// ---- more groups than a CTA's shared memory holds: two passes ------------------------------------------------------
+// With global atomics every row costs ~6 L2 transactions at random addresses (probe of the table, first-row word, count,
+// sum): 22-29 ms per 6e8 rows, whatever the group count.  Instead:
+//   pass 1 (qe_groupby_scatter_body)  evaluates filter, keys and aggregate inputs once and writes each row as a record
+//          (P::record_pack: row, null flags, key words, distinct input values) into one of NPART partitions chosen by
+//          bits 49.. of the key hash.  Records are staged per partition in shared memory ([NPART][RW][PCAP] words) and
+//          written out PCAP/2..PCAP at a time (one global atomic per flush reserves the space; word arrays are separate,
+//          so pass 2 reads coalesced).  Order inside a partition is arbitrary -- the record carries its row.
+//   pass 2 (qe_groupby_gather_body)   one CTA per partition: the copies variant's shared-memory table over the
+//          partition's records (a partition holds 1/NPART of the groups), then the partition's groups -- complete, no
+//          other CTA has any of their rows -- go into the table in HBM with plain stores.
+// A partition that overflows its space (one key with a large share of the rows) or its CTA's table raises the overflow
+// flag: the run is discarded and the caller goes on to the atomic variant.
+#define QE_PT_VALID (1ull << 63)          /* word 0 of every record */
+
+template <class P>
+__device__ __forceinline__ void qe_groupby_scatter_flush(const QeParams &p, qe_u64 *st, volatile qe_u32 *fill, qe_u32 threshold)
+{
+    constexpr int NP = P::NPART, CAP = P::PCAP, RW = P::RW, GW = P::GTHREADS / 32;
+    constexpr int WPI = 32 / CAP;                             // record words a warp copies per instruction (CAP lanes each)
+    static_assert(CAP == 8 || CAP == 16 || CAP == 32, "staging records per partition");
+    const qe_u32 warp = qe_warp(), lane = qe_lane();
+    const size_t total = (size_t)NP * p.pt_cap;
+    for (qe_u32 base = warp * 32u; base < (qe_u32)NP; base += (qe_u32)GW * 32u) {
+        // Every lane reserves the space of its own partition: up to 32 global atomics in flight, one round trip (one
+        // partition after the other it was 16 round trips per warp and tile: 40 ms per 6e8 rows instead of 8.4).
+        // Measured and rejected: blocks of 128 records per CTA and partition, reserved one block ahead so that no tile
+        // waits for L2 -- 148 x 512 write frontiers instead of 512, 13.3 ms.
+        const qe_u32 f = fill[base + lane];
+        const qe_u32 n = f < (qe_u32)CAP ? f : (qe_u32)CAP;      // rows that found the staging full wait for the next round
+        const bool want = f >= threshold && n > 0u;
+        qe_u32 g0 = 0;
+        if (want && !(QE_DEBUG_FLAGS & 2048)) g0 = atomicAdd(p.pt_cursor + base + lane, n);
+        const bool ok = want && g0 + n <= p.pt_cap;
+        if (want && !ok) atomicOr(p.g_ctl + 1, 1u);
+        qe_u32 m = __ballot_sync(QE_FULL_MASK, ok && !(QE_DEBUG_FLAGS & 2048));
+        while (m) {
+            const qe_u32 bit = (qe_u32)__ffs((int)m) - 1u;
+            m &= m - 1u;
+            const qe_u32 q = base + bit;
+            const qe_u32 nn = __shfl_sync(QE_FULL_MASK, n, (int)bit), gg = __shfl_sync(QE_FULL_MASK, g0, (int)bit);
+            const qe_u32 j = lane & (qe_u32)(CAP - 1);
+#pragma unroll
+            for (int w0 = 0; w0 < RW; w0 += WPI) {
+                const int w = w0 + (int)(lane / (qe_u32)CAP);
+                if (w < RW && j < nn) p.pt_words[(size_t)w * total + (size_t)q * p.pt_cap + gg + j] = st[((size_t)q * RW + w) * CAP + j];
+            }
+        }
+        __syncwarp();
+        if (want) fill[base + lane] = 0u;
+    }
+}
+
+template <class P>
+__device__ __forceinline__ void qe_groupby_scatter_body(const QeParams &p)
+{
+    constexpr int STEPS = P::STEPS, VEC = P::VEC, NKEYS = P::NKEYS, NP = P::NPART, CAP = P::PCAP, RW = P::RW;
+    constexpr int GT = P::GTHREADS, GW = GT / 32;
+    constexpr int WARP_ROWS = STEPS * 32 * VEC;
+    constexpr int TILE = GW * WARP_ROWS;
+    static_assert((NP & (NP - 1)) == 0 && NP % 32 == 0 && NP <= 512, "partitions: a power of two, 9 hash bits at most");
+    static_assert(STEPS * VEC <= 32, "one pending bit per row of a thread");
+    extern __shared__ __align__(16) unsigned char qe_gsmem[];
+    qe_u64 *st = (qe_u64 *)qe_gsmem;                          // [NP][RW][CAP]
+    volatile qe_u32 *fill = (volatile qe_u32 *)(st + (size_t)NP * RW * CAP);
+    const qe_u32 warp = qe_warp(), lane = qe_lane(), tid = threadIdx.x;
+    for (int i = (int)tid; i < NP; i += GT) fill[i] = 0u;
+    __syncthreads();
+
+    typename P::Row rows[STEPS][VEC];
+    if (blockIdx.x < p.ntiles) {
+#pragma unroll
+        for (int s = 0; s < STEPS; s++)
+            P::load(p, (qe_i64)blockIdx.x * TILE + (qe_i64)warp * WARP_ROWS + (qe_i64)s * 32 * VEC + lane * VEC, rows[s]);
+    }
+    qe_u32 it = 0;
+    for (qe_u32 tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+        if ((++it & 31u) == 0u && __syncthreads_or((tid == 0 && (qe_ld_relaxed_u32(p.g_ctl + 1) & 1u)) ? 1 : 0)) break;   // discarded
+        const qe_i64 warp_row0 = (qe_i64)tile * TILE + (qe_i64)warp * WARP_ROWS;
+        typename P::Row next[STEPS][VEC];
+        const qe_u32 ntile = tile + gridDim.x < p.ntiles ? tile + gridDim.x : tile;
+#pragma unroll
+        for (int s = 0; s < STEPS; s++)
+            P::load(p, (qe_i64)ntile * TILE + (qe_i64)warp * WARP_ROWS + (qe_i64)s * 32 * VEC + lane * VEC, next[s]);
+        typename P::Out outs[STEPS][VEC];
+        qe_u32 keep[STEPS];
+        qe_rows_eval<P>(p, warp_row0, rows, outs, keep);
+        qe_u64 rec[STEPS * VEC][RW];
+        qe_u32 part[STEPS * VEC];
+        qe_u32 pending = 0;
+#pragma unroll
+        for (int s = 0; s < STEPS; s++) {
+#pragma unroll
+            for (int j = 0; j < VEC; j++) {
+                qe_u64 k[NKEYS];
+                qe_u32 nulls;
+                P::key_pack(outs[s][j], k, nulls);
+                part[s * VEC + j] = (qe_u32)(qe_group_hash64<NKEYS>(k, nulls) >> 49) & (qe_u32)(NP - 1);
+                P::record_pack(outs[s][j], p.sel_base + (qe_u32)(warp_row0 + (qe_i64)s * 32 * VEC + lane * VEC + j), k, nulls, rec[s * VEC + j]);
+                rec[s * VEC + j][0] |= QE_PT_VALID;
+                pending |= (((keep[s] >> j) & 1u) && !(QE_DEBUG_FLAGS & 1024)) ? (1u << (s * VEC + j)) : 0u;
+            }
+        }
+        if ((QE_DEBUG_FLAGS & 1024) && rec[0][0] == 0x1234567ull) p.pt_words[tid] = rec[0][1];      // keeps the evaluation alive
+        int more;
+        do {
+#pragma unroll
+            for (int r = 0; r < STEPS * VEC; r++) {
+                if ((pending >> r) & 1u) {
+                    const qe_u32 pos = atomicAdd((qe_u32 *)fill + part[r], 1u);
+                    if (pos < (qe_u32)CAP) {
+#pragma unroll
+                        for (int w = 0; w < RW; w++) st[((size_t)part[r] * RW + w) * CAP + pos] = rec[r][w];
+                        pending &= ~(1u << r);
+                    }
+                }
+            }
+            __syncthreads();
+            qe_groupby_scatter_flush<P>(p, st, fill, (qe_u32)CAP / 2u);
+            more = __syncthreads_or(pending != 0u ? 1 : 0);
+        } while (more);
+#pragma unroll
+        for (int s = 0; s < STEPS; s++)
+#pragma unroll
+            for (int j = 0; j < VEC; j++) rows[s][j] = next[s][j];
+    }
+    __syncthreads();
+    qe_groupby_scatter_flush<P>(p, st, fill, 1u);
+}
+
+// two adjacent records' word w (16 bytes), streamed: no L1 allocation, fixed place in the instruction stream
+__device__ __forceinline__ void qe_gather_load2(const qe_u64 *src, qe_u64 &a, qe_u64 &b)
+{
+    qe_i64 x, y;
+    qe_ldg_i64x2((const qe_i64 *)src, x, y);
+    a = (qe_u64)x;
+    b = (qe_u64)y;
+}
+
+template <class P>
+__device__ __forceinline__ void qe_groupby_gather_body(const QeParams &p)
+{
+    constexpr int NKEYS = P::NKEYS, NWORDS = P::NWORDS, LMAX = P::SLMAX, CS = P::SCSLOTS, NP = P::NPART, RW = P::RW;
+    constexpr int GT = P::GTHREADS;
+    constexpr int COPIES = P::SCOPIES;
+    constexpr int PAIRS = RW <= 4 ? 2 : 1, R = 2 * PAIRS;     // records per thread and step, loaded as pairs of neighbours
+    constexpr bool PREF = RW <= 6;                            // the next step's records live in registers too
+    static_assert(COPIES >= 1 && COPIES <= 32 && (COPIES & (COPIES - 1)) == 0, "copies per CTA: a power of two up to 32");
+    typedef QeGroupCache2<NKEYS, CS, LMAX> Cache;
+    extern __shared__ __align__(16) unsigned char qe_gsmem[];
+    qe_u64 *s_acc = (qe_u64 *)qe_gsmem;                       // [LMAX][NWORDS][COPIES]
+    Cache &gc = *(Cache *)(qe_gsmem + (size_t)LMAX * NWORDS * COPIES * 8);
+    const volatile Cache &vc = gc;
+    const qe_u32 lane = qe_lane(), tid = threadIdx.x;
+    const size_t total = (size_t)NP * p.pt_cap;
+
+    for (qe_u32 q = blockIdx.x; q < (qe_u32)NP; q += gridDim.x) {
+        if (__syncthreads_or((tid == 0 && (qe_ld_relaxed_u32(p.g_ctl + 1) & 1u)) ? 1 : 0)) break;   // discarded (pass 1, or another CTA)
+        const qe_u32 n = p.pt_cursor[q] < p.pt_cap ? p.pt_cursor[q] : p.pt_cap;
+        for (int i = (int)tid; i < CS; i += GT) gc.entry[i] = 0u;
+        if (tid == 0) { gc.nlocal = 0u; gc.over = 0u; gc.inserted = 0u; }
+        for (int i = (int)tid; i < LMAX * NWORDS * COPIES; i += GT) s_acc[i] = P::word_init((i / COPIES) % NWORDS);
+        __syncthreads();
+        const qe_u64 *src = p.pt_words + (size_t)q * p.pt_cap;
+        qe_u64 rec[R][RW], nxt[PREF ? R : 1][RW];
+        // records [i0, i0 + R * GT) of a step: thread t takes 2t, 2t + 1 of every 2 * GT (reads past n stay inside the
+        // partition's space -- its size is a multiple of 32 -- and fail the valid bit or the bound)
+#define QE_GATHER_LOAD(dst, first)                                                                          \
+        _Pragma("unroll") for (int pr = 0; pr < PAIRS; pr++) {                                               \
+            const qe_u32 i = (first) + ((qe_u32)pr * GT + tid) * 2u;                                         \
+            _Pragma("unroll") for (int w = 0; w < RW; w++) {                                                 \
+                if (i < n) qe_gather_load2(src + (size_t)w * total + i, dst[2 * pr][w], dst[2 * pr + 1][w]);  \
+                else dst[2 * pr][w] = dst[2 * pr + 1][w] = 0ull;                                             \
+            }                                                                                                \
+        }
+        if (PREF) { QE_GATHER_LOAD(rec, 0u) }
+        for (qe_u32 i0 = 0; i0 < n; i0 += (qe_u32)R * GT) {
+            if (PREF) { QE_GATHER_LOAD(nxt, i0 + (qe_u32)R * GT) } else { QE_GATHER_LOAD(rec, i0) }
+            int lg[R];
+            qe_u32 miss = 0;
+#pragma unroll
+            for (int r = 0; r < R; r++) {
+                const bool kept = i0 + ((qe_u32)(r / 2) * GT + tid) * 2u + (qe_u32)(r & 1) < n && (rec[r][0] & QE_PT_VALID) != 0ull;
+                qe_u64 k[NKEYS];
+#pragma unroll
+                for (int i = 0; i < NKEYS; i++) k[i] = rec[r][1 + i];
+                const qe_u32 nulls = (qe_u32)(rec[r][0] >> 32) & 0xffu;
+                const qe_u64 h = qe_group_hash64<NKEYS>(k, nulls);
+                const qe_u32 tag = qe_group_entry_tag(h, nulls);
+                const qe_u64 e = *(const volatile qe_u64 *)&gc.entry[((qe_u32)h & (qe_u32)(CS / 2 - 1)) * 2u];
+                const qe_u32 e0 = (qe_u32)e, e1 = (qe_u32)(e >> 32);
+                const bool m0 = (e0 & QE_GM_MATCH) == tag, m1 = (e1 & QE_GM_MATCH) == tag;
+                const qe_u32 pick = m0 ? e0 : e1;
+                const int cand = (m0 || m1) ? (int)((pick >> 17) & 0x1fffu) : 0;
+                bool hit = m0 || m1;
+#pragma unroll
+                for (int i = 0; i < NKEYS; i++) hit &= vc.gkeys[cand][i] == k[i];
+                lg[r] = (kept && hit) ? cand : -1;
+                miss |= (kept && !hit) ? (1u << r) : 0u;
+                if ((QE_DEBUG_FLAGS & 512) && rec[r][RW - 1] == 0x1234567ull) s_acc[tid] = rec[r][0];       // loads only
+            }
+            if (miss && !(QE_DEBUG_FLAGS & 512)) {
+#pragma unroll
+                for (int r = 0; r < R; r++) {
+                    if (!((miss >> r) & 1u)) continue;
+                    qe_u64 k[NKEYS];
+#pragma unroll
+                    for (int i = 0; i < NKEYS; i++) k[i] = rec[r][1 + i];
+                    const qe_u32 nulls = (qe_u32)(rec[r][0] >> 32) & 0xffu;
+                    const qe_u64 h = qe_group_hash64<NKEYS>(k, nulls);
+                    const qe_u32 tag = qe_group_entry_tag(h, nulls);
+                    int l = -1;
+                    for (qe_u32 d = 2; d < 8u && l < 0; d++) {             // the slots after the home bucket
+                        const qe_u32 e = vc.entry[(((qe_u32)h & (qe_u32)(CS / 2 - 1)) * 2u + d) & (qe_u32)(CS - 1)];
+                        if ((e & QE_GM_MATCH) != tag) continue;
+                        const int cand = (int)((e >> 17) & 0x1fffu);
+                        bool same = true;
+#pragma unroll
+                        for (int i = 0; i < NKEYS; i++) same &= vc.gkeys[cand][i] == k[i];
+                        if (same) l = cand;
+                    }
+                    if (l < 0) l = qe_group_local_slow2<NKEYS, CS, LMAX, false>(p, &gc, k, nulls, h);
+                    lg[r] = l;
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < R; r++) {
+                if (lg[r] >= 0 && !(QE_DEBUG_FLAGS & (256 | 512))) {
+                    typename P::Out o;
+                    P::record_unpack(rec[r], o);
+                    qe_u64 *a = s_acc + (size_t)lg[r] * NWORDS * COPIES + (lane & (qe_u32)(COPIES - 1));
+                    P::template acc_atomic<COPIES, true>(a, o, rec[r][0] & 0xffffffffull);     // rows of a partition come in any order
+                }
+            }
+            if (PREF) {
+#pragma unroll
+                for (int r = 0; r < R; r++)
+#pragma unroll
+                    for (int w = 0; w < RW; w++) rec[r][w] = nxt[r][w];
+            }
+        }
+#undef QE_GATHER_LOAD
+        __syncthreads();
+        if (((const volatile qe_u32 &)gc.over) != 0u) {
+            if (tid == 0) atomicOr(p.g_ctl + 1, 1u);
+            break;
+        }
+        // the partition's groups are complete: into the table, every slot written by exactly one thread
+        if (tid == 0) {
+            const qe_u32 ng = gc.nlocal < (qe_u32)LMAX ? gc.nlocal : (qe_u32)LMAX;
+            if (atomicAdd(p.g_ctl, ng) + ng > p.g_max_groups) atomicOr(p.g_ctl + 1, 2u);
+        }
+        for (int i = (int)tid; i < CS; i += GT) {
+            const qe_u32 e = gc.entry[i];
+            if (!(e & QE_GM_READY)) continue;
+            const int l = (int)((e >> 17) & 0x1fffu);
+            const qe_u32 nulls = (e >> 9) & 0xffu;
+            qe_u64 k[NKEYS];
+#pragma unroll
+            for (int j = 0; j < NKEYS; j++) k[j] = gc.gkeys[l][j];
+            const int gs = qe_group_global_slot<NKEYS, false>(p, k, nulls, qe_group_hash<NKEYS>(k, nulls));
+            if (gs < 0) continue;                             // table full: flagged
+            for (int w = 0; w < NWORDS; w++) {
+                const int kind = P::word_kind(w);
+                qe_u64 v = s_acc[((size_t)l * NWORDS + w) * COPIES];
+                for (int c = 1; c < COPIES; c++) v = qe_group_combine(kind, v, s_acc[((size_t)l * NWORDS + w) * COPIES + c]);
+                p.g_acc[(size_t)gs * NWORDS + w] = v;
+            }
+        }
+        __syncthreads();
+    }
 }
 
 template <class P>

@@ -148,6 +148,7 @@ struct qe_ctx {
     // options
     int64_t opt_jit = 1, opt_steps = 0, opt_vec = 0, opt_grid_per_sm = 0, opt_staging = -1, opt_stages = 0, opt_debug_flags = 0, opt_pipeline = 1, opt_groupby_registers = 1, opt_groupby_lanes = 1, opt_lane_acc_kb = 0;
     int64_t opt_min_blocks = 0;
+    int64_t opt_groupby_twopass = 1;    // more groups than a CTA holds: partition the rows by key hash before global atomics
     int64_t opt_groupby_warps = 0;      // one copy per warp: measured slower than the CAS loops, on request only
     int64_t opt_nlb = 0, opt_loads = 0, opt_tile_rows = 0, opt_ncw = 0, opt_defer = 0, opt_stage_kb = 0;
     int64_t launches = 0;
@@ -282,6 +283,8 @@ extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
         ctx->opt_lane_acc_kb = value;
     } else if (k == "groupby_lanes") {
         ctx->opt_groupby_lanes = value != 0;                 // 0: skip the lane-copies variant (32 copies per CTA)
+    } else if (k == "groupby_twopass") {
+        ctx->opt_groupby_twopass = value != 0;               // 0: more groups than a CTA's shared memory holds go straight to global atomics
     } else if (k == "groupby_warps") {
         ctx->opt_groupby_warps = value != 0;                 // 1 tries the one-copy-per-warp variant before the single-copy one
     } else if (k == "groupby_registers") {
@@ -620,6 +623,7 @@ struct qe_result {
     int64_t kernel_runs = 0;
     // group-by: the table of groups on the device, and the finished rows (one per group) on the host
     DevBuf g_state, g_keys, g_nulls, g_acc, g_ctl, g_part, g_part_slot, g_records;
+    DevBuf g_pt_words, g_pt_cursor;                          // two-pass variant: the partitioned records
     std::vector<std::vector<uint8_t>> h_values, h_valid;    // per output column: values in the column's layout, Arrow bitmap
     int64_t h_rows = 0;
     int g_copies = 0;                                        // shared-memory variants: copies of the accumulator words per CTA
@@ -727,7 +731,7 @@ extern "C" int qe_result_destroy(qe_result *r)
     for (ResultColumn &c : r->cols) { release(r->ctx, c.values); release(r->ctx, c.valid); }
     release(r->ctx, r->sel);
     release(r->ctx, r->ctl);
-    for (DevBuf *b : {&r->g_state, &r->g_keys, &r->g_nulls, &r->g_acc, &r->g_ctl, &r->g_part, &r->g_part_slot, &r->g_records})
+    for (DevBuf *b : {&r->g_state, &r->g_keys, &r->g_nulls, &r->g_acc, &r->g_ctl, &r->g_part, &r->g_part_slot, &r->g_records, &r->g_pt_words, &r->g_pt_cursor})
         release(r->ctx, *b);
     release(r->ctx, r->partials);
     release(r->ctx, r->final_aggs);
@@ -905,6 +909,7 @@ static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMo
     snprintf(suffix, sizeof suffix, "|M%d|B%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d.%d|G%d", (int)mode, shape.min_blocks, shape.steps, shape.vec, shape.staged ? 1 : 0,
              shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0, shape.ring ? 1 : 0, shape.tile_rows, shape.ncw,
              shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0) + (shape.pring ? 200000 : 0) + (shape.scopies < 0 ? 1600000 : shape.scopies > 1 ? 400000 * shape.scopies + 100000000 * shape.lane_acc_kb : 0));
+    snprintf(suffix + strlen(suffix), sizeof suffix - strlen(suffix), "|Q%d.%d.%d", shape.gpass, shape.npart, shape.pcap);
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) {
@@ -1498,10 +1503,10 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     // a result that is reused remembers which variants this group-by has overflowed
     const std::string sig = query_key(bp);
     // levels: 0 registers, 1 private 512 threads, 2 private 256 threads, 3 lane copies (32 per CTA), 4 eight copies,
-    // 5 one copy per warp (256 threads, no atomics), 6 CTA-shared (one copy), 7 global atomics   [older numbering below]
-    // 5 CTA-shared (one copy), 6 global atomics
+    // 5 one copy per warp (256 threads, no atomics), 6 two copies / one copy, 7 two passes (records partitioned by key
+    // hash, one CTA per partition), 8 global atomics
     int level = r->g_overflowed == sig ? r->g_level : 0;
-    if (d->flags & QE_GROUPBY_ATOMIC) level = 7;
+    if (d->flags & QE_GROUPBY_ATOMIC) level = 8;
     else if (d->flags & QE_GROUPBY_SHARED) level = std::max(level, 3);
     // register variant: every group's words are touched for every row, so compile for the group count the same
     // group-by found last time (a reused result remembers it); more groups than that -> once more with the maximum
@@ -1538,7 +1543,77 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
             if (gp512.clmax[qe::GroupPlan::copies_index(copies)] < 16) continue;
         }
         if (level == 5 && (gp.slmaxw < 64 || !ctx->opt_groupby_warps)) continue;
-        const bool atomic = level >= 7, shared = level >= 3 && level <= 6, warpc = level == 5;
+        if (level == 7) {
+            if (!ctx->opt_groupby_twopass || gp512.clmax[0] < 64 || n < (1 << 22)) continue;      // small batches: atomics do
+            // pass 2 holds a partition's share of the groups: the most copies that do, by the count of the last run
+            // (the groups spread evenly over the partitions: + 25 % and a few dozen), else one copy (the most groups)
+            int np = 0, pc = 0;
+            qe::GroupPlan::scatter_shape(gp512.rec_words, np, pc);
+            int copies2 = gp512.clmax[0] >= gp512.clmax[1] ? 1 : 2;
+            if (r->g_seen_sig == sig && r->g_seen_groups > 0) {
+                const int64_t per_part = (int64_t)r->g_seen_groups / np * 5 / 4 + 48;
+                for (int c = 32; c > copies2; c /= 2)
+                    if (gp512.clmax[qe::GroupPlan::copies_index(c)] >= per_part) { copies2 = c; break; }
+            }
+            qe::TileShape s1 = choose_shape(ctx, bp, qe::KM_GROUPBY_SHARED);
+            s1.gthreads = 512;
+            s1.steps = 1;
+            s1.vec = qe::jit_wide_loads_supported() ? 4 : 2;
+            s1.lane_acc_kb = (int)ctx->opt_lane_acc_kb;
+            s1.npart = np;
+            s1.pcap = pc;
+            s1.scopies = copies2;
+            qe::TileShape s2 = s1;
+            s1.gpass = 1;
+            s2.gpass = 2;
+            JitEntry *j1 = nullptr, *j2 = nullptr;
+            rc = get_jit_kernel(ctx, bp, qe::KM_GROUPBY_SHARED, s1, &j1, qe::GroupPlan::scatter_smem(gp512.rec_words, np, pc));
+            if (rc < 0) return fail(QE_ERR_JIT, "group-by needs generated code: " + tls_error);
+            if (rc) return rc;
+            rc = get_jit_kernel(ctx, bp, qe::KM_GROUPBY_SHARED, s2, &j2, gp512.copies_smem(copies2));
+            if (rc < 0) return fail(QE_ERR_JIT, "group-by needs generated code: " + tls_error);
+            if (rc) return rc;
+            const int64_t tile_rows = s1.rows_per_tile();
+            const int64_t ntiles64 = (n + tile_rows - 1) / tile_rows;
+            p.ntiles = (uint32_t)ntiles64;
+            // Space per partition: the rows spread like the groups do -- with g groups per partition the largest of the
+            // partitions holds about (1 + 4.5 / sqrt(g)) times the mean.  g from the count of the last run, else from
+            // the groups the table held when the last variant gave up (a lower bound).
+            const double g_est = (double)std::max<int64_t>(r->g_seen_sig == sig ? r->g_seen_groups : 0, std::max<int64_t>(ctl[0], gp512.clmax[0])) / np;
+            const double factor = std::min(3.0, 1.08 + 4.5 / std::sqrt(std::max(g_est, 1.0)));
+            const int64_t pt_cap = ((int64_t)((double)(n / np) * factor) + 4096 + 31) / 32 * 32;
+            if (pt_cap > 0xffffffffll) continue;
+            if ((rc = ensure(ctx, r->g_pt_words, (size_t)gp512.rec_words * (size_t)np * (size_t)pt_cap * 8))) return rc;
+            if ((rc = ensure(ctx, r->g_pt_cursor, (size_t)np * 4))) return rc;
+            p.pt_words = (qe_u64 *)r->g_pt_words.ptr;
+            p.pt_cursor = (qe_u32 *)r->g_pt_cursor.ptr;
+            p.pt_cap = (qe_u32)pt_cap;
+            r->mode = (int)qe::KM_GROUPBY_SHARED;
+            r->g_variant = 7;
+            r->g_copies = copies2;
+            r->g_threads = 512;
+            QE_CUDA(qe::launch_groupby_init((uint32_t *)r->g_state.ptr, (uint64_t *)r->g_acc.ptr, (uint32_t *)r->g_ctl.ptr, nslots, gw, ctx->stream));
+            QE_CUDA(cudaMemsetAsync(r->g_pt_cursor.ptr, 0, (size_t)np * 4, ctx->stream));
+            ctx->launches++;
+            QE_CUDA(cudaEventRecord(r->ev_begin, ctx->stream));
+            void *args[] = {&p};
+            const int grid1 = (int)std::min<int64_t>(std::max<int64_t>(ntiles64, 1), (int64_t)ctx->num_sms);
+            QE_CUDA(cudaLaunchKernel((const void *)j1->kernel.kernel, dim3(grid1), dim3(512), args, j1->kernel.dyn_smem, ctx->stream));
+            QE_CUDA(cudaLaunchKernel((const void *)j2->kernel.kernel, dim3(std::min(np, ctx->num_sms)), dim3(512), args, j2->kernel.dyn_smem, ctx->stream));
+            ctx->launches += 2;
+            QE_CUDA(cudaEventRecord(r->ev_end, ctx->stream));
+            r->timed = true;
+            QE_CUDA(cudaMemcpyAsync(ctl, r->g_ctl.ptr, sizeof ctl, cudaMemcpyDeviceToHost, ctx->stream));
+            QE_CUDA(cudaStreamSynchronize(ctx->stream));
+            if (ctl[1] & 2u)
+                return fail(QE_ERR_CAPACITY, "more than max_groups (" + std::to_string(max_groups) + ") groups; rerun with a larger max_groups");
+            if (!(ctl[1] & 1u)) break;
+            fold_timing(r);      // a partition outgrew its space or its CTA's table (one key with a large share of the rows): atomics
+            r->g_overflowed = sig;
+            r->g_level = level + 1;
+            continue;
+        }
+        const bool atomic = level >= 8, shared = level >= 3 && level <= 6, warpc = level == 5;
         const qe::GroupPlan &plan = (level == 1 || (shared && !warpc)) ? gp512 : gp;
         const qe::KernelMode mode = regs ? qe::KM_GROUPBY_REG : atomic ? qe::KM_GROUPBY_ATOMIC : shared ? qe::KM_GROUPBY_SHARED : qe::KM_GROUPBY_PRIVATE;
         const int ci = qe::GroupPlan::copies_index(copies ? copies : 1);
@@ -2219,7 +2294,7 @@ static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *co
     qe::BoundPipeline bp;
     int rc = qe::bind_pipeline(schema, has_filter ? &progs[0] : nullptr, proj, aggs, bp, err, group_keys);
     if (rc) return fail(rc, err);
-    const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : (atomic == 2 || (atomic >= 4 && atomic <= 9)) ? qe::KM_GROUPBY_SHARED : atomic == 3 ? qe::KM_GROUPBY_REG : qe::KM_GROUPBY_PRIVATE)
+    const qe::KernelMode mode = group_keys >= 0 ? (atomic == 1 ? qe::KM_GROUPBY_ATOMIC : (atomic == 2 || (atomic >= 4 && atomic <= 11)) ? qe::KM_GROUPBY_SHARED : atomic == 3 ? qe::KM_GROUPBY_REG : qe::KM_GROUPBY_PRIVATE)
                               : !bp.agg_fns.empty() ? qe::KM_AGG : bp.has_filter ? qe::KM_FILTER : qe::KM_PROJECT;
     qe_ctx dummy;
     dummy.opt_steps = o.steps;
@@ -2229,6 +2304,12 @@ static int debug_generate(const qe_col_desc *cols, int ncols, const uint32_t *co
     if (o.min_blocks > 0) shape.min_blocks = o.min_blocks;
     if (mode == qe::KM_GROUPBY_SHARED) { shape.gthreads = 512; shape.steps = 1; shape.vec = qe::jit_wide_loads_supported() ? 4 : 2; shape.scopies = atomic == 4 ? 32 : atomic == 5 ? 8 : atomic == 7 ? 16 : atomic == 8 ? 4 : atomic == 9 ? 2 : 1; }
     if (mode == qe::KM_GROUPBY_SHARED && atomic == 6) { shape = choose_shape(&dummy, bp, mode); shape.gthreads = 256; shape.scopies = -1; }
+    if (mode == qe::KM_GROUPBY_SHARED && (atomic == 10 || atomic == 11)) {       // the two passes (scatter, gather with 8 copies)
+        const qe::GroupPlan g2 = qe::plan_groupby(bp, 512);
+        qe::GroupPlan::scatter_shape(g2.rec_words, shape.npart, shape.pcap);
+        shape.gpass = atomic == 10 ? 1 : 2;
+        shape.scopies = 8;
+    }
     if (mode == qe::KM_GROUPBY_REG && o.runtime_shapes) {       // as qe_groupby_run, level 0
         const qe::GroupPlan gp = qe::plan_groupby(bp, 256);
         if (gp.rmax < 2 || !shape.greg) return fail(QE_ERR_UNSUPPORTED, "the register variant does not apply to this group-by");

@@ -354,7 +354,8 @@ def test_groupby_code_of_every_variant_compiles():
     aggarr = (C.c_int32 * len(aggs))(*[int(a) for a in aggs])
     for variant, body in ((0, "qe_groupby_private_body<P>"), (2, "qe_groupby_copies_body<P>"), (1, "qe_groupby_atomic_body<P>"),
                           (3, "qe_groupby_reg_body<P>"), (4, "SCOPIES = 32"), (5, "SCOPIES = 8"), (6, "qe_groupby_shared_body<P>"),
-                          (7, "SCOPIES = 16"), (8, "SCOPIES = 4"), (9, "SCOPIES = 2")):
+                          (7, "SCOPIES = 16"), (8, "SCOPIES = 4"), (9, "SCOPIES = 2"), (10, "qe_groupby_scatter_body<P>"),
+                          (11, "qe_groupby_gather_body<P>")):
         src = C.create_string_buffer(1 << 17)
         nb = C.c_size_t(0)
         rc = L.qe_debug_generate_groupby(descs, len(schema), ptrs, lens, 1, 2, aggarr, len(aggs), variant, 1, src, len(src), C.byref(nb))

@@ -409,3 +409,100 @@ def test_copies_variants_over_many_tiles_per_cta(ctx, ngroups, first_copies, aga
             assert abs(parts[g, 0, 0] - exact) <= tol
     res.close()
     t.close()
+
+
+def _numpy_groups(keys_bits, x, xv):
+    uniq, first, inv = np.unique(keys_bits, return_index=True, return_inverse=True)
+    order = np.argsort(first, kind="stable")
+    rank = np.empty(len(uniq), np.int64)
+    rank[order] = np.arange(len(uniq))
+    g = rank[inv]
+    ng = len(uniq)
+    cnt = np.bincount(g[xv], minlength=ng)
+    mn = np.full(ng, np.inf); np.minimum.at(mn, g, np.where(xv, x, np.inf))
+    mx = np.full(ng, -np.inf); np.maximum.at(mx, g, np.where(xv, x, -np.inf))
+    return uniq[order], first[order], g, cnt, mn, mx
+
+
+@pytest.mark.parametrize("ngroups", [20_000, 300_000])
+def test_two_pass_variant_for_more_groups_than_a_cta_holds(ctx, ngroups):
+    """More groups than any shared-memory variant holds: rows are partitioned by key hash (pass 1), one CTA per partition
+    aggregates its records (pass 2): variant 7.  Keys are not small integers, inputs are nullable, NaN and -0.0 are keys.
+    Against numpy: groups in order of first appearance, first rows, COUNT / MIN / MAX exact, SUM within the tolerance of
+    tests/parity.py.  The second run knows the group count and uses more copies per partition."""
+    rng = np.random.default_rng(ngroups)
+    n = (1 << 22) + 1_234_567
+    k = rng.integers(0, ngroups, n).astype(np.float64)
+    k[rng.integers(0, n, 5)] = np.nan
+    k[rng.integers(0, n, 5)] = -0.0
+    x = np.round(rng.uniform(-1000.0, 1000.0, n), 2)
+    xv = rng.random(n) >= 0.1
+    t = ColumnarTable.from_arrays(ctx, [Field("k", D, False), Field("x", D, True)], [k, x], [None, xv])
+    key = fn(Function.MUL, col(0), 0.37)
+    pipe = GroupByPipeline(t, None, [key], [col(1), col(1), col(1), col(1)], [A.SUM, A.COUNT, A.MIN, A.MAX], max_groups=2 * ngroups)
+    kk = k * 0.37
+    bits = kk.view(np.uint64).copy()
+    bits[np.isnan(kk)] = 0x7ff8000000000000
+    uniq, first, g_of_row, cnt, mn, mx = _numpy_groups(bits, x, xv)
+    ng = len(uniq)
+    res = None
+    copies = []
+    for _ in range(2):
+        res = pipe.run(res)
+        assert capi.lib().qe_result_group_variant(res.handle) == 7
+        copies.append(capi.lib().qe_result_group_copies(res.handle))
+        assert res.num_rows == ng
+        keys, nulls, first_row, parts, _ = sharding.group_arrays(res, 1, 4) if ng <= 30_000 else _group_arrays_fast(res)
+        assert np.array_equal(keys[:, 0], uniq) and not nulls.any()
+        assert np.array_equal(first_row, first)
+        if parts is not None:
+            assert np.array_equal(parts[:, 1, 1].view(np.int64), cnt)
+            assert np.array_equal(parts[:, 2, 2], mn) and np.array_equal(parts[:, 3, 3], mx)
+            for g in rng.integers(0, ng, 40):
+                terms = x[(g_of_row == g) & xv]
+                exact = math.fsum(terms.tolist())
+                seq = float(np.cumsum(terms)[-1]) if len(terms) else 0.0
+                tol = max(abs(seq - exact), 4 * ulp(exact), len(terms) * 2.0 ** -53 * math.fsum(np.abs(terms).tolist()))
+                assert abs(parts[g, 0, 0] - exact) <= tol
+        else:
+            vals = [res.column(1 + j) for j in range(4)]          # SUM, COUNT, MIN, MAX as the reference's rows hold them
+            assert np.array_equal(vals[1][0][cnt > 0].astype(np.int64), cnt[cnt > 0])
+            ok = cnt > 0
+            assert np.array_equal(vals[2][0][ok], mn[ok]) and np.array_equal(vals[3][0][ok], mx[ok])
+            assert not vals[2][1][~ok].any()                      # MIN of no rows is null
+            sums = np.bincount(g_of_row[xv], weights=x[xv], minlength=ng)
+            assert np.allclose(vals[0][0][ok], sums[ok], rtol=1e-12, atol=1e-6)
+    assert copies[1] >= copies[0]
+    res.close()
+    t.close()
+
+
+def _group_arrays_fast(res):
+    """keys / first rows of a large group-by result without one C call per group"""
+    n = res.num_rows
+    vals, valid = res.column(0)
+    bits = np.ascontiguousarray(vals, np.float64).view(np.uint64).copy()
+    bits[np.isnan(vals)] = 0x7ff8000000000000
+    first = np.zeros(max(n, 1), np.int64)
+    capi.check(capi.lib().qe_result_group_first_rows(res.handle, first.ctypes.data))
+    return bits.reshape(-1, 1), ~np.asarray(valid, bool).reshape(-1, 1), first[:n], None, None
+
+
+def test_two_pass_falls_back_to_atomics_when_one_key_has_most_rows(ctx):
+    rng = np.random.default_rng(99)
+    n = (1 << 22) + 4096
+    k = rng.integers(0, 50_000, n).astype(np.float64)
+    k[rng.random(n) < 0.6] = 7.0                                   # its partition outgrows the space a partition gets
+    x = rng.integers(-100, 100, n).astype(np.float64)
+    t = ColumnarTable.from_arrays(ctx, [Field("k", D, False), Field("x", D, False)], [k, x])
+    pipe = GroupByPipeline(t, None, [col(0)], [col(1), col(1)], [A.SUM, A.COUNT], max_groups=131072)
+    res = pipe.run()
+    assert capi.lib().qe_result_group_variant(res.handle) == 1
+    uniq, first, g_of_row, cnt, _, _ = _numpy_groups(k.view(np.uint64), x, np.ones(n, bool))
+    assert res.num_rows == len(uniq)
+    keys, _, first_row, _, _ = _group_arrays_fast(res)
+    assert np.array_equal(keys[:, 0], uniq) and np.array_equal(first_row, first)
+    sums = np.bincount(g_of_row, weights=x, minlength=len(uniq))
+    assert np.array_equal(res.column(1)[0], sums) and np.array_equal(res.column(2)[0].astype(np.int64), cnt)
+    res.close()
+    t.close()

@@ -51,7 +51,7 @@ def timed(pipe, reps):
 for atomic in (() if args.skip_q1 else (False, True)):
     t, pipe = bench.q1_pipeline(ctx, args.rows, atomic=atomic)
     ms, v, g = timed(pipe, args.reps)
-    print(json.dumps({"what": "q1", "rows": args.rows, "variant": ["private", "atomic", "shared", "registers", "lanes", "lanes8", "warps"][v], "groups": g[0], "threads": g[1], "kernel_ms": round(ms, 3),
+    print(json.dumps({"what": "q1", "rows": args.rows, "variant": ["private", "atomic", "shared", "registers", "lanes", "lanes8", "warps", "twopass"][v], "groups": g[0], "threads": g[1], "kernel_ms": round(ms, 3),
                       "gb_per_s": round(args.rows * 48 / ms / 1e6, 1), "frac": round(args.rows * 48 / ms / 1e6 / peak, 3)}), flush=True)
     t.close()
 D = DataType.DOUBLE
@@ -62,6 +62,6 @@ for card in (int(c) for c in args.cards.split(",")):
     key = fn(Function.MUL, col(0), args.key_scale) if args.key_scale else col(0)
     pipe = GroupByPipeline(t, None, [key], [col(1), col(1)], [A.SUM, A.COUNT], max_groups=max(65536, 2 * card))
     ms, v, g = timed(pipe, args.reps)
-    print(json.dumps({"what": "sum_count_by_k", "cardinality": card, "variant": ["private", "atomic", "shared", "registers", "lanes", "lanes8", "warps"][v], "groups": g[0], "threads": g[1], "copies": g[2],
+    print(json.dumps({"what": "sum_count_by_k", "cardinality": card, "variant": ["private", "atomic", "shared", "registers", "lanes", "lanes8", "warps", "twopass"][v], "groups": g[0], "threads": g[1], "copies": g[2],
                       "wall_ms": g[3], "first_run_ms": g[4], "kernel_ms": round(ms, 3), "gb_per_s": round(args.rows * 16 / ms / 1e6, 1),
                       "frac": round(args.rows * 16 / ms / 1e6 / peak, 3)}), flush=True)
