@@ -357,11 +357,45 @@ def extra_q1(ctx, rows, steps, warmup, peak):
     out = {"rows": rows, "groups": groups, "kernel_ms": kms, "rows_per_s": rows / (kms * 1e-3),
            "gb_per_s": rows * 48 / (kms * 1e-3) / 1e9, "frac_of_peak": rows * 48 / (kms * 1e-3) / 1e9 / peak,
            "algorithmic_bytes_per_row": 48, "selectivity": float(counts.sum()) / rows,
-           "variant": ["private", "atomic", "shared", "registers", "lanes", "lanes8", "warps"][capi.lib().qe_result_group_variant(res.handle)],
+           "variant": GROUP_VARIANTS[capi.lib().qe_result_group_variant(res.handle)],
            "threads_per_cta": capi.lib().qe_result_group_threads(res.handle)}
     res.close()
     t.close()
     return out
+
+
+GROUP_VARIANTS = ["private", "atomic", "shared", "registers", "lanes", "lanes8", "warps", "twopass"]
+
+
+def extra_groupby_cardinalities(ctx, rows, steps, warmup, pk_read, cards=(64, 1024, 65536)):
+    """SELECT k, SUM(x), COUNT(x) GROUP BY k over 16-byte rows for a few group counts: which
+    variant takes them and what it reaches of the device's read rate.  The first run of every cardinality walks the
+    variants until one holds the groups; the timed runs reuse the result, which remembers."""
+    from queryengine_b200 import capi
+    from queryengine_b200.ast import AggregationFunction as A, DataType, col
+    from queryengine_b200.engine import ColumnarTable, Field, GroupByPipeline
+    D = DataType.DOUBLE
+    t = ColumnarTable(ctx, [Field("k", D), Field("x", D)], rows)
+    t.generate(1, capi.QE_GEN_UNIFORM_REAL, SEED + 11, 0.0, 1.0)
+    out = []
+    for card in cards:
+        t.generate(0, capi.QE_GEN_UNIFORM_INT, SEED + 12, 0, card - 1)
+        pipe = GroupByPipeline(t, None, [col(0)], [col(1), col(1)], [A.SUM, A.COUNT], max_groups=max(65536, 2 * card))
+        res = pipe.run()
+        for _ in range(warmup):
+            pipe.run(res)
+        ms0, runs0 = res.kernel_stats()
+        for _ in range(steps):
+            pipe.run(res)
+        ms1, runs1 = res.kernel_stats()
+        kms = (ms1 - ms0) / max(1, runs1 - runs0)
+        out.append({"groups": res.num_rows, "kernel_ms": kms, "gb_per_s": rows * 16 / (kms * 1e-3) / 1e9,
+                    "frac_of_read_peak": rows * 16 / (kms * 1e-3) / 1e9 / pk_read,
+                    "variant": GROUP_VARIANTS[capi.lib().qe_result_group_variant(res.handle)],
+                    "copies_per_cta": capi.lib().qe_result_group_copies(res.handle)})
+        res.close()
+    t.close()
+    return {"rows": rows, "algorithmic_bytes_per_row": 16, "per_cardinality": out}
 
 
 def extra_f64_column(ctx, rows, steps, warmup, peak):
@@ -721,6 +755,11 @@ def run_ours(args):
             extra["q1_groupby_sf100"]["frac_of_peak_mix"] = extra["q1_groupby_sf100"]["gb_per_s"] / pk_read
         except Exception as e:
             extra["q1_groupby_sf100"] = {"error": repr(e)}
+        ctx.trim()
+        try:      # group-by beyond a handful of groups: the shared-memory copies and the two-pass variant
+            extra["groupby_sum_count_by_k"] = extra_groupby_cardinalities(ctx, args.q6_rows, max(3, args.steps), 2, pk_read)
+        except Exception as e:
+            extra["groupby_sum_count_by_k"] = {"error": repr(e)}
         ctx.trim()
         try:      # configs[4] at its FULL size on one GPU: 5 999 989 709 rows through a bounded device window
             extra["lineitem_sf1000_streamed_one_gpu"] = extra_sf1000_streamed(ctx, 5_999_989_709, peak, yard)

@@ -160,7 +160,7 @@ QE_API void *qe_ctx_stream(qe_ctx *ctx);
  * ring variant: "stage_kb" (bytes of column data per stage, 0 = auto), "tile_rows" (0 = auto), "ncw" (consumer
  * warps, 0 = auto: 20 for a single 8-byte column, else 16), "defer" (tiles between evaluation and scatter, 0 = auto);
  * group-by: "groupby_registers" (1 default: accumulators in registers when the cost rule allows; 0 never; 2 whenever
- * the registers suffice), "groupby_lanes" (1 default; 0 skips the 32-copies-per-CTA variant), "groupby_warps" (0 default; 1 tries the
+ * the registers suffice), "groupby_lanes" (1 default; 0 skips the 32-copies-per-CTA variant), "groupby_twopass" (1 default: more groups than a CTA's shared memory holds are partitioned by key hash and aggregated per partition before global atomics are tried; 0 skips that), "groupby_warps" (0 default; 1 tries the
  * one-copy-per-warp variant, which measured slower than the single shared copy), "jit_cache_entries" (kernels kept loaded per context, default 128) */
 QE_API int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value);
 /* kernels launched by this context so far */
