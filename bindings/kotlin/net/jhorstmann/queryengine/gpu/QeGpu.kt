@@ -8,7 +8,9 @@ import java.nio.ByteBuffer
  * A failing call throws IllegalStateException with qe_last_error().
  *
  * NOT COMPILED in the B200 build image (no JVM / Kotlin compiler there): source for the maintainer of
- * jhorstmann/queryengine (Kotlin 1.3.61, Java 11, pom.xml:13-17).
+ * jhorstmann/queryengine (Kotlin 1.3.61, Java 11, pom.xml:13-17).  The natives behind every `external fun` below ARE
+ * compiled and executed there, through a mock JNIEnv (tests/test_jni_cpu.py checks names and arities against this file,
+ * tests/test_gpu_jni.py runs them on the GPU).
  */
 object QeGpu {
     init {
@@ -36,6 +38,33 @@ object QeGpu {
     @JvmStatic external fun resultColumn(result: Long, k: Int, values: ByteBuffer, validity: ByteBuffer)
     @JvmStatic external fun resultAgg(result: Long, k: Int, isNull: BooleanArray): Double
     @JvmStatic external fun resultDestroy(result: Long)
+
+    // qe_pipeline_desc.flags
+    const val RUN_NO_SELECTION = 1
+    const val RUN_INTERPRETER = 2
+    const val RUN_NO_VALUES = 8      // the selection vector is the whole output: FilterOperator over rows the JVM already holds
+
+    @JvmStatic external fun pipelineRunFlags(ctx: Long, table: Long, filter: Long, proj: LongArray, aggFns: IntArray, flags: Int,
+                                             previous: Long): Long
+    @JvmStatic external fun resultSelection(result: Long, rows: ByteBuffer)            // uint32 per kept row
+
+    // every GPU of the box from this one process (qe_mgpu_*): contiguous row ranges, results concatenated in scan order,
+    // SUM / AVG bit-identical to one GPU, group-by partitions merged by key
+    @JvmStatic external fun mgpuCreate(devices: IntArray): Long
+    @JvmStatic external fun mgpuDestroy(group: Long)
+    @JvmStatic external fun mgpuCtx(group: Long, part: Int): Long                      // programs of any of them run on all
+    @JvmStatic external fun mtableCreate(group: Long, types: IntArray, nullable: BooleanArray, rows: Long): Long
+    @JvmStatic external fun mtableUpload(table: Long, col: Int, values: ByteBuffer, validity: ByteBuffer?)
+    @JvmStatic external fun mtableDestroy(table: Long)
+    @JvmStatic external fun mgpuPipelineRun(group: Long, table: Long, filter: Long, proj: LongArray, aggFns: IntArray, flags: Int): Long
+    @JvmStatic external fun mgpuGroupByRun(group: Long, table: Long, filter: Long, keys: LongArray, inputs: LongArray, aggFns: IntArray,
+                                           maxGroups: Long): Long
+    @JvmStatic external fun mresultNumRows(result: Long): Long
+    @JvmStatic external fun mresultNumColumns(result: Long): Int
+    @JvmStatic external fun mresultColumn(result: Long, k: Int, values: ByteBuffer, validity: ByteBuffer)
+    @JvmStatic external fun mresultSelection(result: Long, rows: ByteBuffer)           // uint64 per kept row, whole-table indices
+    @JvmStatic external fun mresultAgg(result: Long, k: Int, isNull: BooleanArray): Double
+    @JvmStatic external fun mresultDestroy(result: Long)
 }
 
 /** One dictionary per context: STRING columns and literals are int32 codes of it (equal codes <=> equal strings). */

@@ -63,6 +63,12 @@ class QeGpu:
             "groupByRun": (i64, [i64, i64, i64, vp, vp, vp, i64, i64]),
             "resultNumRows": (i64, [i64]), "resultNumColumns": (i32, [i64]), "resultColumnType": (i32, [i64, i32]),
             "resultColumn": (None, [i64, i32, vp, vp]), "resultAgg": (C.c_double, [i64, i32, vp]), "resultDestroy": (None, [i64]),
+            "pipelineRunFlags": (i64, [i64, i64, i64, vp, vp, i32, i64]), "resultSelection": (None, [i64, vp]),
+            "mgpuCreate": (i64, [vp]), "mgpuDestroy": (None, [i64]), "mgpuCtx": (i64, [i64, i32]),
+            "mtableCreate": (i64, [i64, vp, vp, i64]), "mtableUpload": (None, [i64, i32, vp, vp]), "mtableDestroy": (None, [i64]),
+            "mgpuPipelineRun": (i64, [i64, i64, i64, vp, vp, i32]), "mgpuGroupByRun": (i64, [i64, i64, i64, vp, vp, vp, i64]),
+            "mresultNumRows": (i64, [i64]), "mresultNumColumns": (i32, [i64]), "mresultColumn": (None, [i64, i32, vp, vp]),
+            "mresultSelection": (None, [i64, vp]), "mresultAgg": (C.c_double, [i64, i32, vp]), "mresultDestroy": (None, [i64]),
         }
         self.natives = sorted(sig)
         for name, (res, args) in sig.items():

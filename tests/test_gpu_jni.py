@@ -125,3 +125,90 @@ def test_filter_projection_aggregation_and_groupby_through_the_jni_natives(jni):
     jni.call("tableDestroy", table)
     jni.call("ctxDestroy", ctx)
     jni.free(proj_arr, none, fns, three, flag, keys, inputs, gfns, one)
+
+
+def test_selection_only_and_every_gpu_of_the_box_through_the_jni_natives(jni):
+    """QE_RUN_NO_VALUES + resultSelection, and the qe_mgpu natives a JVM adapter drives several GPUs with (two contexts
+    on one device when the box has one GPU): filter / projection concatenated in scan order, global row indices,
+    aggregates equal to the single-context run bit for bit, group-by merged by key."""
+    import torch
+    rng = np.random.default_rng(22)
+    n = 3 * (1 << 20) + 12_345                                        # partitions split at multiples of 2^20 rows
+    spec = random_table(rng, n, "dDb")
+    filt = fn(Function.OR, fn(Function.CMP_LT, col(0), -400.0), col(2, B))
+    projs = [fn(Function.ADD, col(0), col(1)), col(2, B)]
+    n_ref, ref_vals, ref_valid = OraclePlan(spec.with_row_index().oracle(), [0, 1, 2, 3], filter=filt, projections=projs + [col(3)],
+                                            mode=Mode.BYTECODE_COMPILER).columns()
+    ref_rows = ref_vals[2].astype(np.int64)
+    # ---- one context: the selection vector alone
+    ctx = jni.call("ctxCreate", 0)
+    table, keep = _table(jni, ctx, spec)
+    pf = _program(jni, ctx, filt)
+    pp = [_program(jni, ctx, e) for e in projs]
+    proj_arr, none = jni.long_array(pp), jni.int_array([])
+    res = jni.call("pipelineRunFlags", ctx, table, pf, proj_arr, none, 8, 0)
+    assert jni.call("resultNumRows", res) == n_ref and jni.call("resultNumColumns", res) == 0
+    sel = np.zeros(n_ref, np.uint32)
+    b = jni.direct_buffer(sel)
+    jni.call("resultSelection", res, b)
+    jni.free(b)
+    assert np.array_equal(sel.astype(np.int64), ref_rows)
+    fns = jni.int_array([int(A.SUM), int(A.COUNT)])
+    two = jni.long_array([pp[0], pp[0]])
+    agg1 = jni.call("pipelineRun", ctx, table, pf, two, fns, 0)
+    flag = jni.boolean_array([0])
+    want = [jni.call("resultAgg", agg1, k, flag) for k in range(2)]
+    # ---- the group: the same programs run on every context
+    devices = jni.int_array([0, 1] if torch.cuda.device_count() >= 2 else [0, 0])
+    g = jni.call("mgpuCreate", devices)
+    types = jni.int_array([int(f.type) for f in spec.fields])
+    nullable = jni.boolean_array([1 if f.nullable else 0 for f in spec.fields])
+    mt = jni.call("mtableCreate", g, types, nullable, n)
+    for c, f in enumerate(spec.fields):
+        data = np.packbits(spec.columns[c], bitorder="little") if f.type == B else np.ascontiguousarray(spec.columns[c], np.float64)
+        vb = np.packbits(spec.valid[c], bitorder="little") if f.nullable else None
+        bv, bn = jni.direct_buffer(data), (jni.direct_buffer(vb) if vb is not None else None)
+        jni.call("mtableUpload", mt, c, bv, bn)
+        jni.free(bv, bn)
+    gctx = jni.call("mgpuCtx", g, 0)
+    gf = _program(jni, gctx, filt)
+    gp = [_program(jni, gctx, e) for e in projs]
+    garr = jni.long_array(gp)
+    mres = jni.call("mgpuPipelineRun", g, mt, gf, garr, none, 0)
+    assert jni.call("mresultNumRows", mres) == n_ref and jni.call("mresultNumColumns", mres) == 2
+    vals, vb = np.zeros(n_ref, np.float64), np.zeros((n_ref + 7) // 8 + 1, np.uint8)
+    b1, b2 = jni.direct_buffer(vals), jni.direct_buffer(vb)
+    jni.call("mresultColumn", mres, 0, b1, b2)
+    jni.free(b1, b2)
+    ok = np.unpackbits(vb, bitorder="little")[:n_ref].astype(bool)
+    assert np.array_equal(ok, ref_valid[0]) and (f64_equal(vals, ref_vals[0]) | ~ok).all()
+    rows = np.zeros(n_ref, np.uint64)
+    b = jni.direct_buffer(rows)
+    jni.call("mresultSelection", mres, b)
+    jni.free(b)
+    assert np.array_equal(rows.astype(np.int64), ref_rows)
+    gtwo = jni.long_array([gp[0], gp[0]])
+    magg = jni.call("mgpuPipelineRun", g, mt, gf, gtwo, fns, 0)
+    got = [jni.call("mresultAgg", magg, k, flag) for k in range(2)]
+    assert np.array(got).tobytes() == np.array(want).tobytes()        # SUM has the same bits for any number of partitions
+    keys, inputs = jni.long_array([gp[1]]), jni.long_array([_program(jni, gctx, col(1)), _program(jni, gctx, col(1))])
+    gfns = jni.int_array([int(A.MAX), int(A.COUNT)])
+    mgrp = jni.call("mgpuGroupByRun", g, mt, 0, keys, inputs, gfns, 0)
+    wantg = OraclePlan(spec.oracle(), [0, 1, 2], projections=[col(2, B), col(1), col(1)], aggregates=[A.MAX, A.COUNT], group_count=1).rows()
+    assert jni.call("mresultNumRows", mgrp) == len(wantg)
+    cnt = np.zeros(len(wantg), np.float64)
+    vbits = np.zeros(2, np.uint8)
+    b1, b2 = jni.direct_buffer(cnt), jni.direct_buffer(vbits)
+    jni.call("mresultColumn", mgrp, 2, b1, b2)
+    jni.free(b1, b2)
+    assert [int(c) for c in cnt] == [w[2] for w in wantg]
+    assert jni.outstanding == 0
+    for r in (mres, magg, mgrp):
+        jni.call("mresultDestroy", r)
+    jni.call("mtableDestroy", mt)
+    jni.call("mgpuDestroy", g)
+    for r in (res, agg1):
+        jni.call("resultDestroy", r)
+    jni.call("tableDestroy", table)
+    jni.call("ctxDestroy", ctx)
+    jni.free(proj_arr, none, fns, two, flag, devices, types, nullable, garr, gtwo, keys, inputs, gfns)

@@ -19,7 +19,7 @@ def jni():
 def test_every_external_fun_has_its_native(jni):
     kt = open(os.path.join(ROOT, "bindings", "kotlin", "net", "jhorstmann", "queryengine", "gpu", "QeGpu.kt")).read()
     declared = set(re.findall(r"external fun (\w+)\(", kt))
-    assert declared == set(jni.natives) and len(declared) == 15
+    assert declared == set(jni.natives) and len(declared) == 31
     for name in declared:
         assert hasattr(jni.L, PREFIX + name)
     assert jni.L.mock_function_table_slots() == 234           # JNI specification: reserved0 .. GetModule
