@@ -353,3 +353,51 @@ def test_config_e_full_sf1000_through_a_bounded_window(ctx, torch_mod):
     res[0].close()
     window.close()
     capi.lib().qe_host_free(hp)
+
+
+@pytest.mark.parametrize("ngroups,variant", [(1024, (2, 5)), (65536, (7,))])
+def test_groupby_600m_against_torch(ctx, torch_mod, ngroups, variant):
+    """SURVEY.md 8f next-2 at BASELINE size: SELECT k, SUM(x), COUNT(x), MIN(x), MAX(x) GROUP BY k over 6e8 rows, 1 024
+    groups (shared-memory copies) and 65 536 groups (two passes), against an independent restatement in
+    torch ops over the table's columns where they lie in HBM.  x holds integers, so every SUM is exact in any order and
+    is compared bit for bit; groups must come out in order of first appearance (GroupByAggregationOperator.kt:22)."""
+    torch = torch_mod
+    from queryengine_b200.ast import AggregationFunction as A
+    from queryengine_b200.engine import GroupByPipeline
+    D = DataType.DOUBLE
+    n = 600_037_902
+    t = ColumnarTable(ctx, [Field("k", D, False), Field("x", D, False)], n)
+    t.generate(0, capi.QE_GEN_UNIFORM_INT, 71, 0, ngroups - 1)
+    t.generate(1, capi.QE_GEN_UNIFORM_INT, 72, -5000, 5000)
+    ctx.synchronize()
+    pipe = GroupByPipeline(t, None, [col(0)], [col(1)] * 4, [A.SUM, A.COUNT, A.MIN, A.MAX], max_groups=2 * ngroups)
+    res = pipe.run()
+    res = pipe.run(res)                                            # the run that knows the group count
+    assert capi.lib().qe_result_group_variant(res.handle) in variant and res.num_rows == ngroups
+    keys = res.column(0)[0]
+    got = [res.column(1 + j)[0] for j in range(4)]
+    first = np.zeros(ngroups, np.int64)
+    capi.check(capi.lib().qe_result_group_first_rows(res.handle, first.ctypes.data))
+    # torch: per-group sums / counts / extrema / first rows, chunk by chunk
+    sums = torch.zeros(ngroups, dtype=torch.int64, device="cuda")
+    cnts = torch.zeros(ngroups, dtype=torch.int64, device="cuda")
+    mins = torch.full((ngroups,), 1 << 40, dtype=torch.int64, device="cuda")
+    maxs = torch.full((ngroups,), -(1 << 40), dtype=torch.int64, device="cuda")
+    firsts = torch.full((ngroups,), 1 << 40, dtype=torch.int64, device="cuda")
+    for r0 in range(0, n, CHUNK):
+        m = min(CHUNK, n - r0)
+        k = dev(torch, t.device_ptr(0, 0) + 8 * r0, m, "<f8").long()
+        x = dev(torch, t.device_ptr(1, 0) + 8 * r0, m, "<f8").long()
+        sums.scatter_add_(0, k, x)
+        cnts += torch.bincount(k, minlength=ngroups)
+        mins.scatter_reduce_(0, k, x, "amin")
+        maxs.scatter_reduce_(0, k, x, "amax")
+        firsts.scatter_reduce_(0, k, torch.arange(r0, r0 + m, device="cuda"), "amin")
+        del k, x
+    order = torch.argsort(firsts).cpu().numpy()
+    assert np.array_equal(keys.astype(np.int64), order)
+    assert np.array_equal(first, firsts.cpu().numpy()[order])
+    for g, want in zip(got, (sums, cnts, mins, maxs)):
+        assert np.array_equal(g, want.cpu().numpy()[order].astype(np.float64))
+    res.close()
+    t.close()
