@@ -307,7 +307,8 @@ typedef struct qe_groupby_desc {
 } qe_groupby_desc;
 enum {
     QE_GROUPBY_ATOMIC = 1u << 0,       /* go straight to global atomics */
-    QE_GROUPBY_SHARED = 1u << 1        /* skip the private-accumulator variants: start with one shared-memory copy per CTA */
+    QE_GROUPBY_SHARED = 1u << 1,       /* skip the private-accumulator variants: start with the shared-memory copies */
+    QE_GROUPBY_TWOPASS = 1u << 2       /* go straight to the two-pass variant (rows partitioned by key hash), whatever the batch size */
 };
 QE_API int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_groupby_desc *desc, qe_result **result);
 /* per-group partial aggregates and first rows, for combining row-range partitions by key on the host */

@@ -31,6 +31,7 @@ QE_NOALLOC_MAX_ROWS = 1 << 28
 QE_NOALLOC_SCRATCH_BYTES = 532480
 QE_GROUPBY_ATOMIC = 1
 QE_GROUPBY_SHARED = 2
+QE_GROUPBY_TWOPASS = 4
 
 QE_GEN_UNIFORM_U40 = 0
 QE_GEN_UNIFORM_INT = 1

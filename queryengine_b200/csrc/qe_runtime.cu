@@ -1507,6 +1507,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
     // hash, one CTA per partition), 8 global atomics
     int level = r->g_overflowed == sig ? r->g_level : 0;
     if (d->flags & QE_GROUPBY_ATOMIC) level = 8;
+    else if (d->flags & QE_GROUPBY_TWOPASS) level = std::max(level, 7);
     else if (d->flags & QE_GROUPBY_SHARED) level = std::max(level, 3);
     // register variant: every group's words are touched for every row, so compile for the group count the same
     // group-by found last time (a reused result remembers it); more groups than that -> once more with the maximum
@@ -1544,7 +1545,7 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
         }
         if (level == 5 && (gp.slmaxw < 64 || !ctx->opt_groupby_warps)) continue;
         if (level == 7) {
-            if (!ctx->opt_groupby_twopass || gp512.clmax[0] < 64 || n < (1 << 22)) continue;      // small batches: atomics do
+            if (!ctx->opt_groupby_twopass || gp512.clmax[0] < 64 || (n < (1 << 22) && !(d->flags & QE_GROUPBY_TWOPASS))) continue;      // small batches: atomics do
             // pass 2 holds a partition's share of the groups: the most copies that do, by the count of the last run
             // (the groups spread evenly over the partitions: + 25 % and a few dozen), else one copy (the most groups)
             int np = 0, pc = 0;
@@ -1581,7 +1582,8 @@ extern "C" int qe_groupby_run(qe_ctx *ctx, const qe_table *table, const qe_group
             // the groups the table held when the last variant gave up (a lower bound).
             const double g_est = (double)std::max<int64_t>(r->g_seen_sig == sig ? r->g_seen_groups : 0, std::max<int64_t>(ctl[0], gp512.clmax[0])) / np;
             const double factor = std::min(3.0, 1.08 + 4.5 / std::sqrt(std::max(g_est, 1.0)));
-            const int64_t pt_cap = ((int64_t)((double)(n / np) * factor) + 4096 + 31) / 32 * 32;
+            // (a small batch -- only QE_GROUPBY_TWOPASS sends one here -- gets room for all its rows in any one partition)
+            const int64_t pt_cap = (std::max<int64_t>((int64_t)((double)(n / np) * factor) + 4096, std::min<int64_t>(n, 1 << 16)) + 31) / 32 * 32;
             if (pt_cap > 0xffffffffll) continue;
             if ((rc = ensure(ctx, r->g_pt_words, (size_t)gp512.rec_words * (size_t)np * (size_t)pt_cap * 8))) return rc;
             if ((rc = ensure(ctx, r->g_pt_cursor, (size_t)np * 4))) return rc;

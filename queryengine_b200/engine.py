@@ -577,7 +577,7 @@ class GroupByPipeline:
 
     def __init__(self, table: ColumnarTable, filter: Optional[Expression], keys: Sequence[Expression],
                  inputs: Sequence[Expression], aggregates: Sequence[AggregationFunction],
-                 max_groups: int = 0, atomic: bool = False, shared: bool = False):
+                 max_groups: int = 0, atomic: bool = False, shared: bool = False, twopass: bool = False):
         self.table = table
         self.ctx = table.ctx
         self.filter = Program(self.ctx, filter) if filter is not None else None
@@ -587,7 +587,7 @@ class GroupByPipeline:
         if len(self.aggs) != len(self.inputs):
             raise ValueError("one aggregation function per input")
         self.max_groups = max_groups
-        self.flags = (capi.QE_GROUPBY_ATOMIC if atomic else 0) | (capi.QE_GROUPBY_SHARED if shared else 0)
+        self.flags = (capi.QE_GROUPBY_ATOMIC if atomic else 0) | (capi.QE_GROUPBY_SHARED if shared else 0) | (capi.QE_GROUPBY_TWOPASS if twopass else 0)
         self._key_arr = (C.c_void_p * max(1, len(self.keys)))(*[p.handle for p in self.keys])
         self._in_arr = (C.c_void_p * max(1, len(self.inputs)))(*[p.handle for p in self.inputs])
         self._agg_arr = (C.c_int32 * max(1, len(self.aggs)))(*self.aggs)
@@ -636,12 +636,12 @@ class GpuGroupByOperator:
     (.../operator/GroupByAggregationOperator.kt:21-75).  Rows come out in order of first appearance."""
 
     def __init__(self, table: ColumnarTable, filter: Optional[Expression], select: Sequence[Expression],
-                 max_groups: int = 0, atomic: bool = False, shared: bool = False):
+                 max_groups: int = 0, atomic: bool = False, shared: bool = False, twopass: bool = False):
         self.select = list(select)
         keys, inputs, fns, self.finish = rewrite_aggregates(self.select)
         self.fns = fns
         self.nkeys = len(keys)
-        self.pipeline = GroupByPipeline(table, filter, keys, inputs, fns, max_groups=max_groups, atomic=atomic, shared=shared)
+        self.pipeline = GroupByPipeline(table, filter, keys, inputs, fns, max_groups=max_groups, atomic=atomic, shared=shared, twopass=twopass)
         self._result: Optional[PipelineResult] = None
         self._rows: Optional[List[list]] = None
         self._idx = 0
