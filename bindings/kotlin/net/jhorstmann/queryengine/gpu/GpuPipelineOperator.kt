@@ -18,7 +18,8 @@ import java.nio.ByteOrder
  */
 class GpuPipelineOperator(private val table: ColumnarGpuTable, private val filter: Expression?,
                           private val projections: List<Expression>, private val aggregates: List<AggregationFunction>,
-                          private val groupCount: Int = -1, private val scanColumns: IntArray? = null) : Operator() {
+                          private val groupCount: Int = -1, private val scanColumns: IntArray? = null,
+                          private val ieeeOrder: Boolean = false) : Operator() {
     private var result = 0L
     private var cursor = 0L
     private var rows = 0L
@@ -28,7 +29,7 @@ class GpuPipelineOperator(private val table: ColumnarGpuTable, private val filte
 
     override fun open() {
         val ctx = table.ctx
-        val ser = ProgramSerializer(ctx.dictionary, scanColumns)
+        val ser = ProgramSerializer(ctx.dictionary, scanColumns, ieeeOrder)     // true: the semantics of Mode.CLOSURE_COMPILER
         val f = filter?.let { QeGpu.programCreate(ctx.handle, ser.serialize(it)) } ?: 0L
         val progs = LongArray(projections.size) { QeGpu.programCreate(ctx.handle, ser.serialize(projections[it])) }
         val fns = IntArray(aggregates.size) { aggregates[it].ordinal }

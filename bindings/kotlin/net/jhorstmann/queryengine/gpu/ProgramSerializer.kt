@@ -9,8 +9,12 @@ import net.jhorstmann.queryengine.ast.*
  * maps it to the column of the HBM-resident table (scanColumns[i] = table column of pruned field i).
  * FunctionExpression.dataType is not consulted: the library infers and checks types with the rules of
  * evaluator/TypeCheck.kt:38-96 (hand-built trees leave it unset, test/.../ByteCodeCompilerTest.kt:28).
+ * `ieeeOrder` = the semantics of Mode.CLOSURE_COMPILER, whose ordering comparisons unbox to primitive doubles
+ * (evaluator/ClosureCompiler.kt:127-130): QE_CMP_IEEE in the argument of CMP_LT / LE / GE / GT.  The default is
+ * Double.compare's total order (evaluator/Interpreter.kt:104-107, BytecodeCompiler.kt:300).
  */
-class ProgramSerializer(private val dictionary: StringDictionary, private val scanColumns: IntArray? = null) : ExpressionVisitor<Unit> {
+class ProgramSerializer(private val dictionary: StringDictionary, private val scanColumns: IntArray? = null,
+                        private val ieeeOrder: Boolean = false) : ExpressionVisitor<Unit> {
     private val words = ArrayList<Int>()
 
     fun serialize(expr: Expression): IntArray {
@@ -41,7 +45,9 @@ class ProgramSerializer(private val dictionary: StringDictionary, private val sc
 
     override fun visitFunction(expr: FunctionExpression) {
         expr.operands.forEach { it.accept(this) }
-        words.add(expr.function.ordinal)
+        val f = expr.function
+        val ordering = f == Function.CMP_LT || f == Function.CMP_LE || f == Function.CMP_GE || f == Function.CMP_GT
+        words.add(if (ieeeOrder && ordering) f.ordinal or (QE_CMP_IEEE shl 8) else f.ordinal)
     }
 
     // identifiers never reach the evaluator (evaluator/Interpreter.kt:9-11); aggregates are split off by
@@ -56,5 +62,6 @@ class ProgramSerializer(private val dictionary: StringDictionary, private val sc
         const val OP_CONST_F64 = 33
         const val OP_CONST_BOOL = 34
         const val OP_CONST_STR = 35
+        const val QE_CMP_IEEE = 1
     }
 }

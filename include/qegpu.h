@@ -86,7 +86,8 @@ typedef enum qe_agg_fn {
  *   opcodes 0..16   the reference's Function enum ordinals (M/ast/Functions.kt:7-22):
  *                   AND OR IF NOT UNARY_MINUS UNARY_PLUS MUL DIV MOD ADD SUB
  *                   CMP_LT CMP_LE CMP_GE CMP_GT CMP_EQ CMP_NE; operands were
- *                   pushed left to right (IF: condition, then, else).
+ *                   pushed left to right (IF: condition, then, else).  Their argument
+ *                   is 0, except that CMP_LT / LE / GE / GT take QE_CMP_IEEE (below).
  *   QE_OP_LOAD_COL  ColumnExpression; argument = column index in the qe_table
  *   QE_OP_CONST_F64 NumericLiteralExpression; the next two words are the low
  *                   and high halves of the IEEE-754 bits
@@ -99,6 +100,13 @@ enum {
     QE_OP_CONST_BOOL = 34,
     QE_OP_CONST_STR = 35
 };
+/* Argument of CMP_LT / CMP_LE / CMP_GE / CMP_GT.  0: java.lang.Double.compare's total order (-0.0 < 0.0, NaN equal to itself
+ * and above +Infinity) -- Mode.INTERPRETER and Mode.BYTECODE_COMPILER, M/evaluator/Interpreter.kt:104-107,
+ * BytecodeCompiler.kt:300.  QE_CMP_IEEE: the unboxed `(a as Double) < (b as Double)` of Mode.CLOSURE_COMPILER,
+ * M/evaluator/ClosureCompiler.kt:127-130 -- any ordering comparison with a NaN is false, -0.0 equals 0.0.  It is the one
+ * place where that mode's results differ from the other two on well-typed trees; CMP_EQ / CMP_NE are
+ * boxed equals in all three (ClosureCompiler.kt:125-126). */
+#define QE_CMP_IEEE 1u
 #define QE_MAX_PROGRAM_WORDS 1024
 #define QE_MAX_STACK 32
 #define QE_MAX_PIPELINE_COLUMNS 16

@@ -46,7 +46,9 @@ def main() -> None:
     for dtype in (DataType.INT64, DataType.DOUBLE):
         schema = W.single_column_schema(dtype)
         filt = W.single_column_filter(0.5, dtype)
-        for hint in (-1.0, 0.99):                    # 20 consumer warps, and 16 once a run has kept > 40 %
+        # unknown / sparse: 20 consumer warps + row lists + sweeper warps; 11-40 % kept last time: 20 warps, masks only;
+        # above 40 %: 16 warps
+        for hint in (-1.0, 0.2, 0.99):
             for flags in (0, capi.QE_RUN_NO_VALUES):
                 compile_one(f"configs[1] {dtype.name} filter hint={hint} flags={flags}", schema, filt, [col(0, dtype, "col")],
                             sel_hint=hint, run_flags=flags)

@@ -143,6 +143,7 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
         if (in.op <= OP_CMP_NE) {                   // a function of the operands on top of the stack
             const int ar = op_arity(in.op);
             key = std::to_string((int)in.op);
+            if (in.arg) key += "/" + std::to_string(in.arg);      // QE_CMP_IEEE: `a < b` in both orderings may appear in one pipeline
             for (size_t i = st.size() - (size_t)ar; i < st.size(); i++) key += "|" + st[i].val + "?" + st[i].valid;
             auto hit = g.memo.find(key);
             if (hit != g.memo.end()) {
@@ -216,8 +217,15 @@ SV gen_expr(const BoundPipeline &bp, const BoundExpr &e, Gen &g)
             SV a = st.back(); st.pop_back();
             r.t = VT_BOOL; r.valid = and_valid(a.valid, b.valid); r.val = g.tmp("t");
             std::string rhs;
+            const bool ieee = in.op <= OP_CMP_GT && (in.arg & 1u);      // QE_CMP_IEEE
             if (a.t == VT_BOOL || a.t == VT_STR) {  // Boolean / String equality (TypeCheck.kt:65-71); equal codes <=> equal strings
                 rhs = std::string("(") + a.val + (in.op == OP_CMP_EQ ? " == " : " != ") + b.val + ")";
+            } else if (ieee && !(int_literal_ok(b) && !a.raw_int.empty()) && !(int_literal_ok(a) && !b.raw_int.empty())) {
+                // CLOSURE_COMPILER mode: (a as Double) < (b as Double) on unboxed doubles, ClosureCompiler.kt:127-130 --
+                // every ordering comparison with a NaN is false, -0.0 equals 0.0.  (An integer column against a finite
+                // literal other than -0.0 has neither case: the integer-domain forms below serve both orderings.)
+                const char *o = in.op == OP_CMP_LT ? " < " : in.op == OP_CMP_LE ? " <= " : in.op == OP_CMP_GE ? " >= " : " > ";
+                rhs = "(" + a.val + o + b.val + ")";
             } else if (int_literal_ok(b) && !a.raw_int.empty()) {
                 rhs = int_compare(in.op, a.raw_int, b);
             } else if (int_literal_ok(a) && !b.raw_int.empty()) {
@@ -564,8 +572,8 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
         snprintf(b, sizeof b, "    static constexpr int NSTAGES = %d, STAGE_BYTES = %d, STAGE_TX = %d;\n", shape.nstages, L.stride, L.tx);
         s += b;
         if (ringlike) {
-            snprintf(b, sizeof b, "    static constexpr int TILE_ROWS = %d, NCW = %d, NLB = %d, DEFER = %d, LOADS = %d;\n", shape.tile_rows, shape.ncw,
-                     shape.nlb, shape.defer, shape.loads);
+            snprintf(b, sizeof b, "    static constexpr int TILE_ROWS = %d, NCW = %d, NLB = %d, DEFER = %d, LOADS = %d, LIST_CAP = %d, NSW = %d;\n", shape.tile_rows, shape.ncw,
+                     shape.nlb, shape.defer, shape.loads, shape.ring ? shape.list_cap : 0, (shape.ring && shape.list_cap) ? shape.nsw : 0);
             s += b;
             // one row (lane-strided: a warp step reads 32 consecutive rows, conflict-free) from a stage
             s += "    static __device__ __forceinline__ void load_row(qe_u32 stage, int wrow0, int c, Row &row) {\n";
@@ -576,6 +584,19 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
                 s += b;
                 if (bp.slot_info[i].nullable) {
                     snprintf(b, sizeof b, "        row.v%d = qe_stage1_bit(stage + %d, wrow0, c);\n", i, L.valid_off[i]);
+                    s += b;
+                }
+            }
+            s += "    }\n";
+            // row r of the tile, any r (the sparse path of the ring kernel: one kept row per lane)
+            s += "    static __device__ __forceinline__ void load_at(qe_u32 stage, int r, Row &row) {\n";
+            for (int i = 0; i < nslots; i++) {
+                const int t = bp.slot_info[i].type;
+                if (t == 2) snprintf(b, sizeof b, "        row.c%d = qe_stage_at_bit(stage + %d, r);\n", i, L.val_off[i]);
+                else snprintf(b, sizeof b, "        row.c%d = qe_stage_at_%s(stage + %d, r);\n", i, suffix_of(t), L.val_off[i]);
+                s += b;
+                if (bp.slot_info[i].nullable) {
+                    snprintf(b, sizeof b, "        row.v%d = qe_stage_at_bit(stage + %d, r);\n", i, L.valid_off[i]);
                     s += b;
                 }
             }

@@ -64,6 +64,10 @@ struct TileShape {
     int nlb = 1;            // look-back warps
     int defer = 3;          // tiles between a tile's evaluation (phase A) and its scatter (phase C)
     int loads = 0;          // bulk-copy tiles in flight at most (0 = as many as there are free stages)
+    int list_cap = 0;       // sparse tiles: a consumer warp that kept at most this many rows of a tile leaves their row numbers
+                            // as a packed list in shared memory (0 = masks only; 32, 64, 96, 128) ...
+    int nsw = 0;            // ... and `nsw` sweeper warps store the listed rows of every consumer warp once the tile's prefix is known
+                            // (the consumers then never wait for a prefix); 0: every consumer warp stores its own list in phase C
     int gthreads = 256;     // group-by, private variant: threads per CTA (256 or 512)
     // group-by, register variant (qe_groupby_reg_body): the same ring of bulk-copy stages (tile_rows, ncw, nstages),
     // one producer warp + ncw consumer warps, no look-back
@@ -80,7 +84,7 @@ struct TileShape {
     int gpass = 0, npart = 0, pcap = 0;
 
     int rows_per_tile() const { return (ring || greg || pring) ? tile_rows : (gthreads / 32) * steps * 32 * vec; }
-    int block_threads() const { return (greg || pring) ? 32 * (1 + ncw) : ring ? 32 * (2 + nlb + ncw) : 256; }
+    int block_threads() const { return (greg || pring) ? 32 * (1 + ncw) : ring ? 32 * (2 + nlb + (list_cap ? nsw : 0) + ncw) : 256; }
 };
 
 // bytes of dynamic shared memory the staged filter kernel needs (0 when not staged)

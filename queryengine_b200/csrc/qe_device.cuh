@@ -984,11 +984,47 @@ __device__ __forceinline__ bool qe_stage1_bit(qe_u32 bitmap, int wrow0, int c)
     return (w >> qe_lane()) & 1u;
 }
 
+// row r of a staged column, any r (the ring kernel's sparse path: one kept row per lane, qe_ring_scatter_list)
+__device__ __forceinline__ double qe_stage_at_f64(qe_u32 col, int r)
+{
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(col + (qe_u32)r * 8u));
+    return v;
+}
+__device__ __forceinline__ qe_i64 qe_stage_at_i64(qe_u32 col, int r)
+{
+    qe_i64 v;
+    asm volatile("ld.shared.s64 %0, [%1];" : "=l"(v) : "r"(col + (qe_u32)r * 8u));
+    return v;
+}
+__device__ __forceinline__ qe_i32 qe_stage_at_i32(qe_u32 col, int r)
+{
+    qe_i32 v;
+    asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(col + (qe_u32)r * 4u));
+    return v;
+}
+__device__ __forceinline__ bool qe_stage_at_bit(qe_u32 bitmap, int r)
+{
+    qe_u32 w;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(bitmap + ((qe_u32)r >> 5) * 4u));
+    return (w >> ((qe_u32)r & 31u)) & 1u;
+}
+
 __device__ __forceinline__ qe_u32 qe_lds_u32(qe_u32 a)
 {
     qe_u32 v;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
     return v;
+}
+__device__ __forceinline__ qe_u32 qe_lds_u16(qe_u32 a)
+{
+    unsigned short v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void qe_sts_u16_if(bool ok, qe_u32 a, qe_u32 v)
+{
+    asm volatile("{ .reg .pred q; setp.ne.u32 q, %0, 0; @q st.shared.u16 [%1], %2; }" :: "r"((qe_u32)ok), "r"(a), "h"((unsigned short)v) : "memory");
 }
 __device__ __forceinline__ qe_u64 qe_lds_u64(qe_u32 a)
 {
@@ -1271,6 +1307,32 @@ __device__ __forceinline__ void qe_ring_scatter(const QeParams &p, qe_u32 stage,
     }
 }
 
+// Phase C for a warp whose slice kept at most P::LIST_CAP rows of the tile: phase A left their row numbers (within the
+// warp's slice, ascending) as a packed list in shared memory, so lane l stores entry l -- one pass of coalesced stores
+// whatever steps the rows came from, where the mask paths above walk the steps (~27 instructions per non-empty step).
+// Only for pipelines without compacted bit columns, and only when every output of the tile fits the capacity.
+template <class P, bool HAS_SEL>
+__device__ __forceinline__ void qe_ring_scatter_list(const QeParams &p, qe_u32 stage, int wrow0, qe_u32 first_row_of_slice,
+                                                     qe_u64 wbase, qe_u32 list, qe_u32 cnt)
+{
+    const qe_u32 lane = qe_lane();
+    const typename P::Ptrs ptrs = P::out_ptrs(p, wbase);
+    qe_u32 *const selp = HAS_SEL ? qe_opaque_ptr(p.sel + wbase) : (qe_u32 *)0;
+#pragma unroll
+    for (qe_u32 base = 0; base < (qe_u32)P::LIST_CAP; base += 32u) {
+        if (base >= cnt) break;
+        const qe_u32 i = base + lane;
+        const bool ok = i < cnt;
+        const qe_u32 r = qe_lds_u16(list + 2u * (ok ? i : 0u));
+        typename P::Row row;
+        typename P::Out o;
+        P::load_at(stage, wrow0 + (int)r, row);
+        (void)P::eval(p, row, o);
+        if (HAS_SEL) qe_stg_if(ok, selp + i, first_row_of_slice + r);
+        P::emit_ptr(ptrs, i, o, ok);
+    }
+}
+
 // bulk copy with an L2 evict-first policy: scanned columns are read exactly once, so they should not
 // push the (re-read) tile descriptors or the partially written output lines out of L2
 __device__ __forceinline__ void qe_bulk_g2s_stream(qe_u32 dst_smem, const void *src, qe_u32 bytes, qe_u32 mbar, qe_u64 policy)
@@ -1318,7 +1380,12 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
     constexpr qe_u32 O_LO = O_TILE + 4 * NST, O_ROW0 = O_LO + 4 * NST, O_FITS = O_ROW0 + 4 * NST;
     constexpr qe_u32 O_CNT = (O_FITS + 4 * NST + 15u) & ~15u; // u32 [NST][NCW]
     constexpr qe_u32 O_MASK = (O_CNT + 4 * NST * NCW + 15u) & ~15u;   // u32 [NST][TILE / 32]
-    constexpr qe_u32 CTL_BYTES = O_MASK + 4 * NST * (TILE / 32);
+    // sparse tiles (qe_ring_scatter_list): u16 [NST][NCW][LIST_CAP] row numbers within the warp's slice
+    constexpr bool LIST = P::LIST_CAP > 0 && P::NBITCOLS == 0;
+    constexpr qe_u32 LIST_CAP = LIST ? (qe_u32)P::LIST_CAP : 0u;
+    constexpr int NSW = LIST ? P::NSW : 0;                  // sweeper warps (0: a consumer warp stores its own list in phase C)
+    constexpr qe_u32 O_LIST = (O_MASK + 4 * NST * (TILE / 32) + 15u) & ~15u;
+    constexpr qe_u32 CTL_BYTES = O_LIST + 2u * NST * NCW * LIST_CAP;
 
     extern __shared__ __align__(128) unsigned char qe_dyn_smem[];
     __shared__ __align__(16) unsigned char s_ctl[CTL_BYTES];
@@ -1335,7 +1402,7 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
             qe_mbar_init(cb + O_CLAIM + 8u * st, 1);
             qe_mbar_init(cb + O_EVAL + 8u * st, NCW);
             qe_mbar_init(cb + O_PREF + 8u * st, 1);
-            qe_mbar_init(cb + O_EMPTY + 8u * st, NCW + 2);
+            qe_mbar_init(cb + O_EMPTY + 8u * st, NCW + 2 + NSW);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -1489,9 +1556,56 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                 if (t == p.ntiles - 1u) *p.out_count = (base_full & ~p.out_base_mask) + excl + c;   // stays the running total
             }
         }
+    } else if (NSW > 0 && warp < 2u + (qe_u32)NLB + (qe_u32)NSW) {
+        // ----------------------------------------------------------- sweepers
+        // Store the listed rows of every consumer warp that kept at most LIST_CAP rows of a tile, as soon as the tile's
+        // prefix is known.  Measured on B200 (profiles/r02_sweep_02_sweepers.jsonl): a consumer warp that never runs
+        // phase C and never waits for a prefix streams a 1 %-selective filter at the pure-read rate (1.19 ms per 10^9
+        // rows, 1.22 with the lists built), against 1.31 ms with phase C in the consumers.  Thread q of the 32 * NSW
+        // sweeper threads takes entries j0, j0 + JS, ... of consumer warp q % NCW.
+        constexpr qe_u32 JS = (32u * (qe_u32)NSW) / (qe_u32)NCW;
+        const qe_u32 q = (warp - (2u + (qe_u32)NLB)) * 32u + lane;
+        const qe_u32 l = q % (qe_u32)NCW, j0 = q / (qe_u32)NCW;
+        qe_u32 st = 0, par = 0;
+        for (;;) {
+            qe_mbar_wait(cb + O_CLAIM + 8u * st, par);
+            const qe_u32 t = qe_lds_u32(cb + O_TILE + 4u * st);
+            if (t >= p.ntiles) break;
+            qe_mbar_wait(cb + O_EVAL + 8u * st, par);                          // counts and lists of every consumer warp
+            const qe_u32 c = qe_lds_u32(cb + O_CNT + 4u * ((qe_u32)NCW * st + l));
+            const bool mine = j0 < JS && j0 < c && c <= LIST_CAP;
+            qe_mbar_wait(cb + O_PREF + 8u * st, par);                          // bases
+            if (mine) {
+                const qe_u64 wbase = qe_lds_u64(cb + O_WBASE + 8u * ((qe_u32)NCW * st + l));
+                qe_u32 room = 0xffffffffu;                                     // outputs of this consumer warp that still fit
+                if (qe_lds_u32(cb + O_FITS + 4u * st) == 0u) {
+                    const qe_u64 cap = (qe_u64)p.out_capacity;
+                    room = wbase >= cap ? 0u : (cap - wbase > 0xffffffffull ? 0xffffffffu : (qe_u32)(cap - wbase));
+                }
+                const qe_u32 stage = dyn + st * (qe_u32)P::STAGE_BYTES;
+                const qe_u32 la = cb + O_LIST + 2u * LIST_CAP * ((qe_u32)NCW * st + l);
+                const int slice0 = (int)l * WROWS;
+                const qe_u32 first_row = qe_lds_u32(cb + O_ROW0 + 4u * st) + (qe_u32)slice0;
+                const typename P::Ptrs ptrs = P::out_ptrs(p, wbase);
+                qe_u32 *const selp = p.sel ? p.sel + wbase : (qe_u32 *)0;
+                const qe_u32 end = c < room ? c : room;
+                for (qe_u32 j = j0; j < end; j += JS) {
+                    const qe_u32 r = qe_lds_u16(la + 2u * j);
+                    typename P::Row row;
+                    typename P::Out o;
+                    P::load_at(stage, slice0 + (int)r, row);
+                    (void)P::eval(p, row, o);
+                    if (selp) selp[j] = first_row + r;
+                    P::emit_ptr(ptrs, j, o, true);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) qe_mbar_arrive(cb + O_EMPTY + 8u * st);
+            QE_RING_NEXT(st, par, 1u);
+        }
     } else {
         // ----------------------------------------------------------- consumers
-        const qe_u32 cw = warp - (2u + (qe_u32)NLB);
+        const qe_u32 cw = warp - (2u + (qe_u32)NLB + (qe_u32)NSW);
         const int wrow0 = (int)cw * WROWS;                    // this warp's slice of every tile
         int n_valid = 0x7fffffff;                             // iterations that carry a tile (known once the end marker is seen)
         qe_u32 st_a = 0, par_a = 0;                           // stage / parity of phase A's tile (iteration it)
@@ -1532,17 +1646,35 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                     qe_u32 cnt = 0;
 #pragma unroll
                     for (int s = 0; s < STEPS; s++) cnt += __popc(mk[s]);
+                    if (LIST && cnt != 0u && cnt <= LIST_CAP) {
+                        // few rows kept: their row numbers, packed in row order (steps that kept nothing cost one branch)
+                        const qe_u32 la = cb + O_LIST + 2u * LIST_CAP * ((qe_u32)NCW * st_a + cw);
+                        const qe_u32 lt = qe_lanemask_lt();
+                        qe_u32 off = 0;
+#pragma unroll
+                        for (int s = 0; s < STEPS; s++) {
+                            if (mk[s] != 0u) {
+                                qe_sts_u16_if((mk[s] >> lane) & 1u, la + 2u * (off + (qe_u32)__popc(mk[s] & lt)), (qe_u32)(s * 32) + lane);
+                                off += (qe_u32)__popc(mk[s]);
+                            }
+                        }
+                    }
+                    const bool swept = NSW > 0 && cnt <= LIST_CAP;    // the sweepers store this slice's rows: this warp is done with the tile
+                    __syncwarp();                                     // the list is written before lane 0 says so
                     if (lane == 0) {
-                        const qe_u32 ma = cb + O_MASK + 4u * ((qe_u32)(TILE / 32) * st_a + cw * (qe_u32)STEPS);
-                        if (STEPS % 4 == 0) {
+                        if (!swept) {
+                            const qe_u32 ma = cb + O_MASK + 4u * ((qe_u32)(TILE / 32) * st_a + cw * (qe_u32)STEPS);
+                            if (STEPS % 4 == 0) {
 #pragma unroll
-                            for (int s = 0; s < STEPS; s += 4) qe_sts_u32x4(ma + 4u * s, mk[s], mk[s + 1], mk[s + 2], mk[s + 3]);
-                        } else {
+                                for (int s = 0; s < STEPS; s += 4) qe_sts_u32x4(ma + 4u * s, mk[s], mk[s + 1], mk[s + 2], mk[s + 3]);
+                            } else {
 #pragma unroll
-                            for (int s = 0; s < STEPS; s++) qe_sts_u32(ma + 4u * s, mk[s]);
+                                for (int s = 0; s < STEPS; s++) qe_sts_u32(ma + 4u * s, mk[s]);
+                            }
                         }
                         qe_sts_u32(cb + O_CNT + 4u * ((qe_u32)NCW * st_a + cw), cnt);
                         qe_mbar_arrive(cb + O_EVAL + 8u * st_a);
+                        if (swept) qe_mbar_arrive(cb + O_EMPTY + 8u * st_a);
                     }
                     __syncwarp();
                     QE_RT_ADD(10);
@@ -1553,15 +1685,22 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
             if (j >= 0 && j < n_valid) {
                 // ---- phase C: ordered scatter of tile j, whose prefix has had DEFER tile times to arrive
                 QE_RT_RESET();
-                qe_mbar_wait(cb + O_PREF + 8u * st_c, par_c);                      // pref follows eval
+                const qe_u32 cnt_c = qe_lds_u32(cb + O_CNT + 4u * ((qe_u32)NCW * st_c + cw));      // this warp's own store of phase A
+                const bool swept = NSW > 0 && cnt_c <= LIST_CAP;                   // nothing left to do here, the stage was released in phase A
+                if (!swept && !(QE_DEBUG_FLAGS & 4)) qe_mbar_wait(cb + O_PREF + 8u * st_c, par_c);   // pref follows eval
                 QE_RT_ADD(11);
-                const qe_u32 cnt = qe_lds_u32(cb + O_CNT + 4u * ((qe_u32)NCW * st_c + cw));
+                const qe_u32 cnt = (swept || (QE_DEBUG_FLAGS & 4)) ? 0u : cnt_c;   // 4: no phase C at all (timing only)
                 if (cnt != 0u) {
                     const qe_u32 stage = dyn + st_c * (qe_u32)P::STAGE_BYTES;
                     const qe_u32 first_row = qe_lds_u32(cb + O_ROW0 + 4u * st_c) + (qe_u32)wrow0 + lane;
                     const qe_u64 wbase = qe_lds_u64(cb + O_WBASE + 8u * ((qe_u32)NCW * st_c + cw));   // output position of this warp's first kept row
                     const qe_u32 mk = cb + O_MASK + 4u * ((qe_u32)(TILE / 32) * st_c + cw * (qe_u32)STEPS);
-                    if (qe_lds_u32(cb + O_FITS + 4u * st_c)) {
+                    const bool fits = qe_lds_u32(cb + O_FITS + 4u * st_c) != 0u;
+                    if (LIST && fits && cnt <= LIST_CAP) {
+                        const qe_u32 la = cb + O_LIST + 2u * LIST_CAP * ((qe_u32)NCW * st_c + cw);
+                        if (p.sel) qe_ring_scatter_list<P, true>(p, stage, wrow0, first_row - lane, wbase, la, cnt);
+                        else qe_ring_scatter_list<P, false>(p, stage, wrow0, first_row - lane, wbase, la, cnt);
+                    } else if (fits) {
                         if (p.sel) qe_ring_scatter<P, STEPS, false, true>(p, stage, wrow0, first_row, wbase, mk, cnt);
                         else qe_ring_scatter<P, STEPS, false, false>(p, stage, wrow0, first_row, wbase, mk, cnt);
                     } else {
@@ -1571,7 +1710,7 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                 }
                 __syncwarp();
                 QE_RT_ADD(12);
-                if (lane == 0) qe_mbar_arrive(cb + O_EMPTY + 8u * st_c);
+                if (lane == 0 && !swept) qe_mbar_arrive(cb + O_EMPTY + 8u * st_c);
                 QE_RING_NEXT(st_c, par_c, 1u);
             }
             if (n_valid != 0x7fffffff && j + 1 >= n_valid) { if (cw == 0) QE_RT_FLUSH(9, 12); break; }

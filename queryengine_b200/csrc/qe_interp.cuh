@@ -96,9 +96,9 @@ static __device__ __noinline__ QeInterpValue qe_interp_run(const QeParams &p, co
             const double fa = sf[a], fb = sf[b];
             bool valid = va && vb, bv = false;
             double f = 0.0;
-            // a comparison of two booleans?  Both payload doubles are then unused; the
-            // host marks it by setting bit 0 of arg.
-            const bool bool_cmp = arg & 1u;
+            // bit 0 of arg: CMP_EQ / CMP_NE of two booleans (both payload doubles are then unused; set when the
+            // pipeline is bound), or QE_CMP_IEEE on an ordering comparison (set by the caller)
+            const bool bool_cmp = arg & 1u, ieee = arg & 1u;
             switch (op) {
             case 0u: qe_and(ba, va, bb, vb, bv, valid); break;
             case 1u: qe_or(ba, va, bb, vb, bv, valid); break;
@@ -107,10 +107,10 @@ static __device__ __noinline__ QeInterpValue qe_interp_run(const QeParams &p, co
             case 8u: f = qe_mod(fa, fb); break;
             case 9u: f = qe_add(fa, fb); break;
             case 10u: f = qe_sub(fa, fb); break;
-            case 11u: bv = qe_cmp_lt(fa, fb); break;
-            case 12u: bv = qe_cmp_le(fa, fb); break;
-            case 13u: bv = qe_cmp_ge(fa, fb); break;
-            case 14u: bv = qe_cmp_gt(fa, fb); break;
+            case 11u: bv = ieee ? fa < fb : qe_cmp_lt(fa, fb); break;      // ClosureCompiler.kt:127-130 / Interpreter.kt:104-107
+            case 12u: bv = ieee ? fa <= fb : qe_cmp_le(fa, fb); break;
+            case 13u: bv = ieee ? fa >= fb : qe_cmp_ge(fa, fb); break;
+            case 14u: bv = ieee ? fa > fb : qe_cmp_gt(fa, fb); break;
             case 15u: bv = bool_cmp ? (ba == bb) : qe_cmp_eq(fa, fb); break;
             case 16u: bv = bool_cmp ? (ba != bb) : qe_cmp_ne(fa, fb); break;
             }

@@ -60,6 +60,9 @@ bool parse_program(const uint32_t *words, size_t n, Program &out, std::string &e
             pc += 1;
         }
         if (in.op == OP_CONST_BOOL && in.arg > 1) { err = "CONST_BOOL argument must be 0 or 1"; return false; }
+        // ordering comparisons: argument bit 0 = QE_CMP_IEEE (the CLOSURE_COMPILER mode's unboxed `<`, ClosureCompiler.kt:127-130)
+        if (in.op >= OP_CMP_LT && in.op <= OP_CMP_GT && in.arg > 1) { err = "comparison argument must be 0 or QE_CMP_IEEE"; return false; }
+        if (ar > 0 && !(in.op >= OP_CMP_LT && in.op <= OP_CMP_GT) && in.arg != 0) { err = std::string(op_name(in.op)) + " takes no argument"; return false; }
         if (depth < ar) {
             err = std::string("stack underflow at ") + op_name(in.op); return false;
         }

@@ -151,6 +151,8 @@ struct qe_ctx {
     int64_t opt_groupby_twopass = 1;    // more groups than a CTA holds: partition the rows by key hash before global atomics
     int64_t opt_groupby_warps = 0;      // one copy per warp: measured slower than the CAS loops, on request only
     int64_t opt_nlb = 0, opt_loads = 0, opt_tile_rows = 0, opt_ncw = 0, opt_defer = 0, opt_stage_kb = 0;
+    int64_t opt_list_cap = 0;                                // ring filter, sparse tiles: 0 auto (32), -1 off, 32 / 64 / 96 / 128
+    int64_t opt_nsw = 0;                                     // ... sweeper warps: 0 auto (2), -1 none (consumers store their own lists), 1..4
     int64_t launches = 0;
     bool warned_no_nvrtc = false;
     // pinned staging ring for uploads from pageable memory
@@ -306,6 +308,13 @@ extern "C" int qe_ctx_set_option(qe_ctx *ctx, const char *key, int64_t value)
     } else if (k == "loads") {
         if (value < 0 || value > 32) return fail(QE_ERR_INVALID_ARGUMENT, "loads must be in [0, 32] (0 = no limit)");
         ctx->opt_loads = value;
+    } else if (k == "list_cap") {
+        if (value != -1 && (value < 0 || value > 128 || value % 32))
+            return fail(QE_ERR_INVALID_ARGUMENT, "list_cap must be 0 (auto), -1 (off) or 32, 64, 96, 128");
+        ctx->opt_list_cap = value;
+    } else if (k == "nsw") {
+        if (value < -1 || value > 4) return fail(QE_ERR_INVALID_ARGUMENT, "nsw must be 0 (auto), -1 (none) or 1..4");
+        ctx->opt_nsw = value;
     } else if (k == "stage_kb") {
         if (value < 0 || value > 64) return fail(QE_ERR_INVALID_ARGUMENT, "stage_kb must be in [0, 64] (0 = auto)");
         ctx->opt_stage_kb = value;
@@ -809,7 +818,16 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         s.tile_rows = (int)rows;
         s.nstages = 1;
         const size_t stage = qe::staged_smem_bytes(bp, s);
-        const size_t meta = 64 + (size_t)s.tile_rows / 8 + 4 * (size_t)s.ncw;   // per stage: barriers, keep masks, counts
+        // sparse tiles: packed row lists instead of keep masks (qe_ring_scatter_list); pipelines that compact bit columns keep the masks
+        bool bit_outputs = false;
+        for (const qe::BoundOutput &o : bp.outs) bit_outputs |= o.type == QE_TYPE_BOOLEAN || o.has_validity;
+        // Measured on B200, one 8-byte column, 10^9 rows (profiles/r02_sweep_02_sweepers.jsonl): 1 / 2 / 5 / 10 % kept
+        // 1.32 / 1.50 / 1.61 / 1.64 ms with the masks only, 1.28 / 1.31 / 1.40 / 1.58 ms with lists of 32 and two sweeper
+        // warps; from ~12 % up most warps keep more than 32 rows of a tile and the mixed kernel loses (15 %: 1.79 against
+        // 1.65 ms; lists of 64 lose everywhere above 5 %).  So: lists unless the same query kept more than 11 % last time.
+        s.list_cap = (bit_outputs || ctx->opt_list_cap < 0) ? 0 : ctx->opt_list_cap ? (int)ctx->opt_list_cap : (sel_hint > 0.11 ? 0 : 32);
+        s.nsw = !s.list_cap || ctx->opt_nsw < 0 ? 0 : ctx->opt_nsw ? (int)ctx->opt_nsw : 2;
+        const size_t meta = 64 + (size_t)s.tile_rows / 8 + (4 + 8 + 2 * (size_t)s.list_cap) * (size_t)s.ncw;   // per stage: barriers, keep masks, counts, bases, lists
         size_t n = ctx->opt_stages ? (size_t)ctx->opt_stages : 16;
         while (n > 2 && n * (stage + meta) > (224u << 10)) n--;
         s.nstages = (int)n;
@@ -905,11 +923,12 @@ static void serialize_interp(const qe::BoundPipeline &bp, std::vector<uint32_t> 
 static int get_jit_kernel(qe_ctx *ctx, const qe::BoundPipeline &bp, qe::KernelMode mode, const qe::TileShape &shape,
                           JitEntry **out, size_t dyn_smem = 0)
 {
-    char suffix[128];
+    char suffix[192];
     snprintf(suffix, sizeof suffix, "|M%d|B%d|S%d|V%d|T%d.%d|D%d|P%d|R%d.%d.%d.%d.%d.%d|G%d", (int)mode, shape.min_blocks, shape.steps, shape.vec, shape.staged ? 1 : 0,
              shape.nstages, (int)ctx->opt_debug_flags, shape.pipelined ? 1 : 0, shape.ring ? 1 : 0, shape.tile_rows, shape.ncw,
              shape.defer, shape.loads, shape.nlb, shape.gthreads + (shape.greg ? 100000 + 1000 * shape.rmax_hint : 0) + (shape.pring ? 200000 : 0) + (shape.scopies < 0 ? 1600000 : shape.scopies > 1 ? 400000 * shape.scopies + 100000000 * shape.lane_acc_kb : 0));
-    snprintf(suffix + strlen(suffix), sizeof suffix - strlen(suffix), "|Q%d.%d.%d", shape.gpass, shape.npart, shape.pcap);
+    snprintf(suffix + strlen(suffix), sizeof suffix - strlen(suffix), "|Q%d.%d.%d|L%d.%d", shape.gpass, shape.npart, shape.pcap, shape.ring ? shape.list_cap : 0,
+             (shape.ring && shape.list_cap) ? shape.nsw : 0);
     const std::string key = bp.signature() + suffix;
     auto it = ctx->jit_cache.find(key);
     if (it != ctx->jit_cache.end()) {

@@ -21,7 +21,7 @@ from typing import List, Optional, Sequence
 import numpy as np
 
 from . import capi
-from .ast import AggregationFunction, AggregationFunctionExpression, ColumnExpression, DataType, Expression
+from .ast import AggregationFunction, AggregationFunctionExpression, ColumnExpression, DataType, Expression, Mode
 from .program import serialize
 
 _NP_OF = {DataType.DOUBLE: np.float64, DataType.INT64: np.int64, DataType.DATE32: np.int32, DataType.STRING: np.int32}
@@ -124,12 +124,18 @@ def jit_stats() -> dict:
 
 
 class Program:
-    """compileExpression(expr, Mode.GPU): the flattened tree, held by the library."""
+    """compileExpression(expr, mode) (.../evaluator/Compiler.kt:20-26): the flattened tree, held by the library.
 
-    def __init__(self, ctx: Context, expr: Expression):
+    `mode` picks the SEMANTICS the reference's three evaluators disagree on, not an implementation -- everything runs on
+    the GPU.  Mode.GPU, INTERPRETER and BYTECODE_COMPILER order doubles like Double.compare (Interpreter.kt:104-107,
+    BytecodeCompiler.kt:300); Mode.CLOSURE_COMPILER compares them unboxed, IEEE (ClosureCompiler.kt:127-130):
+    QE_CMP_IEEE on every ordering comparison of the tree."""
+
+    def __init__(self, ctx: Context, expr: Expression, mode: Mode = Mode.GPU):
         self.ctx = ctx
         self.expr = expr
-        self.words = serialize(expr, ctx.dictionary)
+        self.mode = Mode(mode)
+        self.words = serialize(expr, ctx.dictionary, ieee_order=self.mode == Mode.CLOSURE_COMPILER)
         self.handle = C.c_void_p()
         capi.check(capi.lib().qe_program_create(ctx.handle, self.words.ctypes.data, self.words.size, C.byref(self.handle)))
 
@@ -143,6 +149,11 @@ class Program:
             self.close()
         except Exception:
             pass
+
+
+def compileExpression(ctx: Context, expr: Expression, mode: Mode = Mode.GPU) -> Program:
+    """compileExpression(expr, mode), .../evaluator/Compiler.kt:20-26 (the context stands for the JVM)."""
+    return Program(ctx, expr, mode)
 
 
 @dataclass
@@ -350,13 +361,14 @@ class Pipeline:
     def __init__(self, table: ColumnarTable, filter: Optional[Expression] = None,
                  projections: Optional[Sequence[Expression]] = None,
                  aggregates: Optional[Sequence[AggregationFunction]] = None,
-                 interpreter: bool = False, selection: bool = True, out_capacity_rows: int = 0, values: bool = True):
+                 interpreter: bool = False, selection: bool = True, out_capacity_rows: int = 0, values: bool = True,
+                 mode: Mode = Mode.GPU):
         """values=False (QE_RUN_NO_VALUES): a filter's selection vector is its whole output -- for callers that hold
         the table themselves, as FilterOperator hands back the row it was given (.../operator/FilterOperator.kt:20-22)."""
         self.table = table
         self.ctx = table.ctx
-        self.filter = Program(self.ctx, filter) if filter is not None else None
-        self.projs = [Program(self.ctx, e) for e in (projections or [])]
+        self.filter = Program(self.ctx, filter, mode) if filter is not None else None
+        self.projs = [Program(self.ctx, e, mode) for e in (projections or [])]
         self.aggs = [int(a) for a in (aggregates or [])]
         self.flags = ((capi.QE_RUN_INTERPRETER if interpreter else 0) | (0 if selection else capi.QE_RUN_NO_SELECTION) |
                       (0 if values else capi.QE_RUN_NO_VALUES))
@@ -500,11 +512,11 @@ class GpuPipelineOperator:
     def __init__(self, table: ColumnarTable, filter: Optional[Expression],
                  projections: Optional[Sequence[Expression]],
                  aggregates: Optional[Sequence[AggregationFunction]], interpreter: bool = False,
-                 scan_columns: Optional[Sequence[int]] = None):
+                 scan_columns: Optional[Sequence[int]] = None, mode: Mode = Mode.GPU):
         if not projections:
             cols = scan_columns if scan_columns is not None else range(len(table.fields))
             projections = [ColumnExpression(table.fields[i].name, i, table.fields[i].type) for i in cols]
-        self.pipeline = Pipeline(table, filter, projections, aggregates, interpreter=interpreter)
+        self.pipeline = Pipeline(table, filter, projections, aggregates, interpreter=interpreter, mode=mode)
         self.aggregates = list(aggregates or [])
         self._result: Optional[PipelineResult] = None
         self._cols = None
@@ -577,12 +589,13 @@ class GroupByPipeline:
 
     def __init__(self, table: ColumnarTable, filter: Optional[Expression], keys: Sequence[Expression],
                  inputs: Sequence[Expression], aggregates: Sequence[AggregationFunction],
-                 max_groups: int = 0, atomic: bool = False, shared: bool = False, twopass: bool = False):
+                 max_groups: int = 0, atomic: bool = False, shared: bool = False, twopass: bool = False,
+                 mode: Mode = Mode.GPU):
         self.table = table
         self.ctx = table.ctx
-        self.filter = Program(self.ctx, filter) if filter is not None else None
-        self.keys = [Program(self.ctx, e) for e in keys]
-        self.inputs = [Program(self.ctx, e) for e in inputs]
+        self.filter = Program(self.ctx, filter, mode) if filter is not None else None
+        self.keys = [Program(self.ctx, e, mode) for e in keys]
+        self.inputs = [Program(self.ctx, e, mode) for e in inputs]
         self.aggs = [int(a) for a in aggregates]
         if len(self.aggs) != len(self.inputs):
             raise ValueError("one aggregation function per input")
@@ -636,12 +649,14 @@ class GpuGroupByOperator:
     (.../operator/GroupByAggregationOperator.kt:21-75).  Rows come out in order of first appearance."""
 
     def __init__(self, table: ColumnarTable, filter: Optional[Expression], select: Sequence[Expression],
-                 max_groups: int = 0, atomic: bool = False, shared: bool = False, twopass: bool = False):
+                 max_groups: int = 0, atomic: bool = False, shared: bool = False, twopass: bool = False,
+                 mode: Mode = Mode.GPU):
         self.select = list(select)
         keys, inputs, fns, self.finish = rewrite_aggregates(self.select)
         self.fns = fns
         self.nkeys = len(keys)
-        self.pipeline = GroupByPipeline(table, filter, keys, inputs, fns, max_groups=max_groups, atomic=atomic, shared=shared, twopass=twopass)
+        self.pipeline = GroupByPipeline(table, filter, keys, inputs, fns, max_groups=max_groups, atomic=atomic, shared=shared, twopass=twopass,
+                                        mode=mode)
         self._result: Optional[PipelineResult] = None
         self._rows: Optional[List[list]] = None
         self._idx = 0

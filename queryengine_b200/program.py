@@ -26,13 +26,15 @@ OP_LOAD_COL = 32
 OP_CONST_F64 = 33
 OP_CONST_BOOL = 34
 OP_CONST_STR = 35
+QE_CMP_IEEE = 1          # argument of CMP_LT / LE / GE / GT: IEEE ordering (include/qegpu.h)
+_ORDERING = (11, 12, 13, 14)
 
 
 class UnsupportedExpression(Exception):
     """The expression cannot run on the GPU path (e.g. a STRING literal without a dictionary)."""
 
 
-def _emit(e: Expression, out: List[int], dictionary=None) -> None:
+def _emit(e: Expression, out: List[int], dictionary=None, ieee: bool = False) -> None:
     if isinstance(e, ColumnExpression):
         if e.index < 0 or e.index >= (1 << 24):
             raise ValueError("column index out of range")
@@ -50,15 +52,18 @@ def _emit(e: Expression, out: List[int], dictionary=None) -> None:
         out += [OP_CONST_STR, dictionary.encode(e.value) & 0xFFFFFFFF]
     elif isinstance(e, FunctionExpression):
         for o in e.operands:
-            _emit(o, out, dictionary)
-        out.append(int(e.function))
+            _emit(o, out, dictionary, ieee)
+        f = int(e.function)
+        out.append(f | (QE_CMP_IEEE << 8) if ieee and f in _ORDERING else f)
     else:
         # IdentifierExpression must be resolved before evaluation
         # (src/main/java/net/jhorstmann/queryengine/evaluator/Interpreter.kt:9-11)
         raise TypeError(f"unexpected node {type(e).__name__} during evaluation")
 
 
-def serialize(e: Expression, dictionary=None) -> np.ndarray:
+def serialize(e: Expression, dictionary=None, ieee_order: bool = False) -> np.ndarray:
+    """ieee_order: the ordering comparisons of Mode.CLOSURE_COMPILER
+    (src/main/java/net/jhorstmann/queryengine/evaluator/ClosureCompiler.kt:127-130) instead of Double.compare's."""
     words: List[int] = []
-    _emit(e, words, dictionary)
+    _emit(e, words, dictionary, ieee_order)
     return np.asarray(words, dtype=np.uint32)

@@ -109,8 +109,11 @@ def check_sum(gpu: float, terms: np.ndarray, sequential: float) -> None:
 
 def compare_pipeline(ctx: Context, spec: TableSpec, filter: Optional[Expression],
                      projections: Sequence[Expression], interpreter: bool = False,
-                     gpu_table: Optional[ColumnarTable] = None) -> int:
+                     gpu_table: Optional[ColumnarTable] = None, mode: Mode = Mode.GPU) -> int:
     """Scan -> [Filter] -> Projection through the oracle and the GPU; asserts equality.
+
+    mode: the evaluator whose semantics both sides follow (Mode.GPU = BYTECODE_COMPILER's; Mode.CLOSURE_COMPILER: IEEE
+    ordering comparisons).
 
     The selection vector is checked by projecting the row-index column alongside."""
     full = spec.with_row_index()
@@ -119,12 +122,12 @@ def compare_pipeline(ctx: Context, spec: TableSpec, filter: Optional[Expression]
     projs = list(projections) + [row_expr]
 
     scan = list(range(len(full.fields)))
-    plan = OraclePlan(full.oracle(), scan, filter=filter, projections=projs, mode=Mode.BYTECODE_COMPILER)
+    plan = OraclePlan(full.oracle(), scan, filter=filter, projections=projs, mode=mode)
     n_ref, ref_vals, ref_valid = plan.columns()
 
     own_table = gpu_table is None
     table = gpu_table or full.gpu(ctx)
-    pipe = Pipeline(table, filter, projs, interpreter=interpreter)
+    pipe = Pipeline(table, filter, projs, interpreter=interpreter, mode=mode)
     res = pipe.run()
     assert res.used_jit == (not interpreter), "generated code was expected to run (is NVRTC missing?)"
     n_gpu = res.num_rows

@@ -150,6 +150,58 @@ def test_literals_are_kernel_parameters():
     assert s1 == s2 and "(qe_i32)p.lit_lo[0]" in s1
 
 
+def test_closure_compiler_mode_is_a_comparison_argument():
+    """Mode.CLOSURE_COMPILER (IEEE ordering, M/evaluator/ClosureCompiler.kt:127-130) travels as QE_CMP_IEEE in the
+    argument of CMP_LT / LE / GE / GT: another kernel than the total-order one, the same kernel for an integer column
+    against an ordinary literal (no NaN, no -0.0 on either side), and nothing else takes an argument."""
+    from queryengine_b200.program import QE_CMP_IEEE
+
+    def gen(schema, filt, ieee):
+        words = [serialize(filt, None, ieee_order=ieee), serialize(col(0, schema[0][0]))]
+        L = capi.lib()
+        descs = (capi.ColDesc * len(schema))(*[capi.ColDesc(int(t), 1 if n else 0) for t, n in schema])
+        ptrs = (C.c_void_p * 2)(*[w.ctypes.data for w in words])
+        lens = (C.c_size_t * 2)(*[w.size for w in words])
+        src = C.create_string_buffer(1 << 16)
+        nbytes = C.c_size_t(0)
+        rc = L.qe_debug_generate(descs, len(schema), ptrs, lens, 1, 1, (C.c_int32 * 1)(), 0, 0, 0, -1, 1, src, len(src),
+                                 None, 0, C.byref(nbytes))
+        assert rc == 0 and nbytes.value > 1000, L.qe_last_error().decode()
+        return src.value.decode()
+    lt = fn(Function.CMP_LT, col(0), col(1))
+    a, b = gen([(D, True), (D, True)], lt, False), gen([(D, True), (D, True)], lt, True)
+    assert "qe_cmp_lt(in.c0, in.c1)" in a and "(in.c0 < in.c1)" in b and "qe_cmp_lt(" not in b.split("struct P")[1]
+    ge = fn(Function.CMP_GE, col(0), 3.0)                       # NaN >= 3.0: true in the total order, false in IEEE
+    a, b = gen([(D, False)], ge, False), gen([(D, False)], ge, True)
+    assert "qe_cmp_ge_k(in.c0, p.lit_f64[0])" in a and "(in.c0 >= p.lit_f64[0])" in b
+    ik = fn(Function.CMP_LT, col(0, I), 10.0)
+    assert "((qe_i64)in.c0 < p.lit_hi[0])" in gen([(I, False)], ik, True)
+    # `a < b` in both orderings inside one tree: two values, not one common subexpression
+    words = np.concatenate([serialize(lt, None, ieee_order=False), serialize(lt, None, ieee_order=True),
+                            np.array([int(Function.CMP_NE)], np.uint32)])
+    descs = (capi.ColDesc * 2)(capi.ColDesc(int(D), 1), capi.ColDesc(int(D), 1))
+    pw = serialize(col(0))
+    src = C.create_string_buffer(1 << 16)
+    nbytes = C.c_size_t(0)
+    L = capi.lib()
+    rc = L.qe_debug_generate(descs, 2, (C.c_void_p * 2)(words.ctypes.data, pw.ctypes.data), (C.c_size_t * 2)(words.size, pw.size),
+                             1, 1, (C.c_int32 * 1)(), 0, 0, 0, -1, 0, src, len(src), None, 0, C.byref(nbytes))
+    assert rc == 0, L.qe_last_error().decode()
+    body = src.value.decode().split("struct P")[1]
+    assert "qe_cmp_lt(in.c0, in.c1)" in body and "(in.c0 < in.c1)" in body
+    # arguments anywhere else are refused
+    bad = serialize(fn(Function.ADD, col(0), col(1)))
+    bad[-1] |= QE_CMP_IEEE << 8
+    rc = L.qe_debug_generate(descs, 2, (C.c_void_p * 1)(bad.ctypes.data), (C.c_size_t * 1)(bad.size),
+                             0, 1, (C.c_int32 * 1)(), 0, 0, 0, -1, 0, src, len(src), None, 0, C.byref(nbytes))
+    assert rc != 0 and "takes no argument" in L.qe_last_error().decode()
+    bad = serialize(lt)
+    bad[-1] |= 2 << 8
+    rc = L.qe_debug_generate(descs, 2, (C.c_void_p * 1)(bad.ctypes.data), (C.c_size_t * 1)(bad.size),
+                             1, 0, (C.c_int32 * 1)(), 0, 0, 0, -1, 0, src, len(src), None, 0, C.byref(nbytes))
+    assert rc != 0 and "QE_CMP_IEEE" in L.qe_last_error().decode()
+
+
 def test_cubin_cache_memory_disk_and_aot(tmp_path):
     """A compiled pipeline comes from memory, from the ahead-of-time table baked into the library, from
     $QE_CACHE_DIR, or -- last -- from NVRTC (qe_cubin_cache.h).  Run in fresh processes: the caches are per process."""

@@ -12,7 +12,7 @@ from exprgen import ExprGen
 from parity import TableSpec, compare_aggregation, compare_pipeline, f64_equal, random_table
 from queryengine_b200 import capi
 from queryengine_b200.ast import (
-    AggregationFunction, BooleanLiteralExpression, ColumnExpression, DataType, Function, FunctionExpression,
+    AggregationFunction, BooleanLiteralExpression, ColumnExpression, DataType, Function, FunctionExpression, Mode,
     NumericLiteralExpression, StringLiteralExpression, col, fn, lit,
 )
 from queryengine_b200.engine import ColumnarTable, Context, Field, GpuPipelineOperator, Pipeline
@@ -177,6 +177,61 @@ def test_random_trees_interpreter(ctx, seed):
     compare_pipeline(ctx, spec, filt, [g.double(5), g.boolean(3)], interpreter=True)
 
 
+# ---- Mode.CLOSURE_COMPILER: IEEE ordering comparisons (QE_CMP_IEEE), M/evaluator/ClosureCompiler.kt:127-130 ------------------
+
+@pytest.mark.parametrize("interpreter", [False, True])
+def test_closure_compiler_mode_orders_like_ieee(ctx, interpreter):
+    """The one place the reference's CLOSURE_COMPILER mode differs from its other two on well-typed trees:
+    `<, <=, >=, >` unbox to primitive doubles, so a NaN compares false and -0.0 equals 0.0, while `=` / `<>` stay boxed
+    equals (ClosureCompiler.kt:125-130).  Known answers of IEEE 754 / JLS 15.20.1, and the same rows in the default mode."""
+    nan, inf = float("nan"), float("inf")
+    fields = [Field("a", D, True), Field("b", D, True)]
+    rows = [[nan, 1.0], [1.0, nan], [nan, nan], [-0.0, 0.0], [0.0, -0.0], [nan, inf], [inf, nan], [1.0, 2.0], [None, 1.0]]
+    F = Function
+    ieee = {F.CMP_LT: [False, False, False, False, False, False, False, True, None],
+            F.CMP_LE: [False, False, False, True, True, False, False, True, None],
+            F.CMP_GE: [False, False, False, True, True, False, False, False, None],
+            F.CMP_GT: [False, False, False, False, False, False, False, False, None],
+            F.CMP_EQ: [False, False, True, False, False, False, False, False, None],     # boxed equals in every mode
+            F.CMP_NE: [True, True, False, True, True, True, True, True, None]}
+    total = {F.CMP_LT: [False, True, False, True, False, False, True, True, None],
+             F.CMP_GE: [True, False, True, False, True, True, False, False, None]}
+    t = _rows_table(ctx, fields, rows)
+    for f, want in ieee.items():
+        op = GpuPipelineOperator(t, None, [fn(f, col(0), col(1))], None, interpreter=interpreter, mode=Mode.CLOSURE_COMPILER)
+        assert [r[0] for r in op.map()] == want, f
+    for f, want in total.items():
+        op = GpuPipelineOperator(t, None, [fn(f, col(0), col(1))], None, interpreter=interpreter)
+        assert [r[0] for r in op.map()] == want, f
+    # both orderings of one comparison in one pipeline stay two values (the code generator's common-subexpression key)
+    from queryengine_b200.program import QE_CMP_IEEE, serialize
+    w_ieee = serialize(fn(F.CMP_GE, col(0), col(1)), ieee_order=True)
+    assert int(w_ieee[-1]) == int(F.CMP_GE) | (QE_CMP_IEEE << 8)
+    t.close()
+
+
+@pytest.mark.parametrize("k", [-np.inf, -0.0, 0.0, 2.5, np.inf, np.nan])
+def test_closure_compiler_mode_against_literals(ctx, k):
+    rng = np.random.default_rng(12)
+    spec = random_table(rng, 5000, "dDiIt", special_rate=0.3)
+    for f in (Function.CMP_LT, Function.CMP_LE, Function.CMP_GE, Function.CMP_GT, Function.CMP_EQ, Function.CMP_NE):
+        for interpreter in (False, True):
+            compare_pipeline(ctx, spec, fn(f, col(0), float(k)),
+                             [fn(f, float(k), col(1)), fn(f, col(2, I), float(k)), fn(f, float(k), col(3, I)),
+                              fn(f, col(4, T), float(k) + 9000.0)], interpreter=interpreter, mode=Mode.CLOSURE_COMPILER)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_random_trees_closure_compiler_mode(ctx, seed):
+    rng = np.random.default_rng(3000 + seed)
+    layout = ["dDbB", "DDDD", "dibT", "DBIt"][seed % 4]
+    spec = random_table(rng, int(rng.integers(1, 20000)), layout, special_rate=0.25)
+    g = ExprGen(rng, spec.fields)
+    filt = g.boolean(4) if seed % 4 != 3 else None
+    compare_pipeline(ctx, spec, filt, [g.double(5), g.boolean(4), g.boolean(3)], interpreter=seed % 2 == 1,
+                     mode=Mode.CLOSURE_COMPILER)
+
+
 @pytest.mark.parametrize("steps,vec,staging", [(1, 2, 0), (2, 2, 0), (8, 2, 0), (1, 4, 0), (4, 4, 0), (8, 4, 0),
                                                (1, 2, 1), (2, 2, 1), (4, 2, 1), (8, 2, 1)])
 def test_every_tile_shape(ctx, steps, vec, staging):
@@ -237,6 +292,76 @@ def test_every_ring_shape(ctx, stage_kb, ncw, defer, stages, nlb):
     g = ExprGen(rng, spec.fields)
     compare_pipeline(c, spec, g.boolean(3), [g.double(4), g.boolean(2), col(2, I), col(3, T)])
     compare_pipeline(c, spec, g.boolean(4), [col(0), col(1, spec.fields[1].type)])
+    c.close()
+
+
+@pytest.mark.parametrize("list_cap,nsw", [(0, 0), (-1, 0), (32, -1), (32, 1), (32, 4), (64, 2), (128, 3)])
+def test_sparse_tiles_row_lists_and_sweeper_warps(ctx, list_cap, nsw):
+    """Ring filter, sparse tiles: a consumer warp that kept at most `list_cap` rows of a tile leaves their row numbers as a
+    packed list in shared memory; `nsw` sweeper warps (or, with nsw = -1, the warp itself) store them once the tile's
+    prefix is known, the other warps keep the mask paths.  Same rows, same order as the masks-only kernel (list_cap = -1)
+    and the oracle, over selectivities that mix both kinds of warps in one tile, with and without selection vector /
+    values, appended batches, and an output capacity that ends inside a swept list."""
+    c = Context(0)
+    c.set_option("list_cap", list_cap)
+    c.set_option("nsw", nsw)
+    rng = np.random.default_rng(77 + list_cap + nsw)
+    n = 300_007
+    x = rng.integers(0, 100_000, n).astype(np.int64)
+    y = rng.uniform(-1.0, 1.0, n)
+    yv = rng.random(n) < 0.9
+    b = rng.random(n) < 0.7
+    d = rng.integers(8000, 9000, n).astype(np.int32)
+    fields = [Field("x", I, False), Field("y", D, True), Field("b", B, False), Field("d", T, False)]
+    t = ColumnarTable.from_arrays(c, fields, [x, y, b, d], [None, yv, None, None])
+    for frac in (0.0, 0.002, 0.01, 0.03, 0.1, 0.15, 0.3, 1.0):
+        k = float(int(frac * 100_000))
+        # one 8-byte column: the benchmark's shape (20 consumer warps)
+        want = np.nonzero(x < k)[0].astype(np.uint32)
+        res = Pipeline(t, fn(Function.CMP_LT, col(0, I), k), [col(0, I)]).run()
+        assert res.num_rows == want.size and np.array_equal(res.selection(), want) and np.array_equal(res.column(0)[0], x[want])
+        res = Pipeline(t, fn(Function.CMP_LT, col(0, I), k), [col(0, I)]).run(res)        # reused: shape by the measured selectivity
+        assert res.num_rows == want.size and np.array_equal(res.selection(), want) and np.array_equal(res.column(0)[0], x[want])
+        res.close()
+        only = Pipeline(t, fn(Function.CMP_LT, col(0, I), k), [col(0, I)], values=False).run()
+        assert only.num_rows == want.size and np.array_equal(only.selection(), want)
+        only.close()
+        nosel = Pipeline(t, fn(Function.CMP_LT, col(0, I), k), [col(0, I)], selection=False).run()
+        assert nosel.num_rows == want.size and np.array_equal(nosel.column(0)[0], x[want])
+        nosel.close()
+        # nullable and bit inputs (read at arbitrary rows by the list paths), computed non-null outputs, 4-byte column
+        filt = fn(Function.AND, fn(Function.AND, fn(Function.CMP_LT, col(0, I), k * 2.0), fn(Function.CMP_GT, col(1), -0.5)), col(2, B))
+        keep = (x < k * 2.0) & yv & (y > -0.5) & b
+        want = np.nonzero(keep)[0].astype(np.uint32)
+        res = Pipeline(t, filt, [col(0, I), col(3, T), fn(Function.ADD, fn(Function.MUL, col(0, I), 0.5), col(3, T))]).run()
+        assert res.num_rows == want.size and np.array_equal(res.selection(), want)
+        assert np.array_equal(res.column(0)[0], x[want]) and np.array_equal(res.column(1)[0], d[want])
+        assert np.array_equal(res.column(2)[0], x[want] * 0.5 + d[want])
+        res.close()
+        # capacity: exactly enough, and five rows short (the last list is cut, the overflow is reported)
+        if want.size > 5:
+            res = Pipeline(t, filt, [col(0, I)], out_capacity_rows=int(want.size)).run()
+            assert res.num_rows == want.size and np.array_equal(res.column(0)[0], x[want])
+            res.close()
+            res = Pipeline(t, filt, [col(0, I)], out_capacity_rows=int(want.size) - 5).run()
+            with pytest.raises(capi.QeError) as ei:
+                _ = res.num_rows
+            assert ei.value.status == capi.QE_ERR_CAPACITY
+            res.close()
+    # appended batches (the running count is the base of the next batch's lists)
+    k = 1500.0
+    want = np.nonzero(x < k)[0].astype(np.uint32)
+    pipe = Pipeline(t, fn(Function.CMP_LT, col(0, I), k), [col(0, I)])
+    res = pipe.run(row_begin=0, row_end=100_096)
+    res = pipe.run_append(res, 100_096, 200_064)
+    res = pipe.run_append(res, 200_064, n)
+    assert res.num_rows == want.size and np.array_equal(res.selection(), want) and np.array_equal(res.column(0)[0], x[want])
+    res.close()
+    t.close()
+    # and against the oracle, with the specials
+    spec = random_table(rng, 50_021, "dDbi", special_rate=0.1)
+    compare_pipeline(c, spec, fn(Function.AND, fn(Function.CMP_LT, col(0), -950.0), col(2, B)), [col(0), col(3, I), fn(Function.SUB, col(0), 1.0)])
+    compare_pipeline(c, spec, fn(Function.CMP_GT, col(1), 900.0), [col(0), col(3, I)])
     c.close()
 
 

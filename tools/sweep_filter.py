@@ -50,7 +50,7 @@ def main():
     for cfg in args.configs.split(";"):
         opts = dict(kv.split("=") for kv in cfg.split(",") if kv)
         # options are per context; the table stays on ctx0, so reset every known option first
-        for k in ("steps", "vec", "grid_per_sm", "stages", "stage_kb", "tile_rows", "ncw", "defer", "debug_flags", "nlb", "loads"):
+        for k in ("steps", "vec", "grid_per_sm", "stages", "stage_kb", "tile_rows", "ncw", "defer", "debug_flags", "nlb", "loads", "list_cap", "nsw"):
             ctx0.set_option(k, 0)
         ctx0.set_option("staging", -1)
         ctx0.set_option("pipeline", 1)
