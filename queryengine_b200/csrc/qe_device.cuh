@@ -1574,6 +1574,7 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
             qe_mbar_wait(cb + O_EVAL + 8u * st, par);                          // counts and lists of every consumer warp
             const qe_u32 c = qe_lds_u32(cb + O_CNT + 4u * ((qe_u32)NCW * st + l));
             const bool mine = j0 < JS && j0 < c && c <= LIST_CAP;
+            if (QE_DEBUG_FLAGS & 64) { __syncwarp(); if (lane == 0) qe_mbar_arrive(cb + O_EMPTY + 8u * st); }   // timing only: the stage is released before the prefix is known (the rows are then read from a stage that may be refilled)
             qe_mbar_wait(cb + O_PREF + 8u * st, par);                          // bases
             if (mine) {
                 const qe_u64 wbase = qe_lds_u64(cb + O_WBASE + 8u * ((qe_u32)NCW * st + l));
@@ -1589,18 +1590,29 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                 const typename P::Ptrs ptrs = P::out_ptrs(p, wbase);
                 qe_u32 *const selp = p.sel ? p.sel + wbase : (qe_u32 *)0;
                 const qe_u32 end = c < room ? c : room;
-                for (qe_u32 j = j0; j < end; j += JS) {
-                    const qe_u32 r = qe_lds_u16(la + 2u * j);
-                    typename P::Row row;
-                    typename P::Out o;
-                    P::load_at(stage, slice0 + (int)r, row);
-                    (void)P::eval(p, row, o);
-                    if (selp) selp[j] = first_row + r;
-                    P::emit_ptr(ptrs, j, o, true);
+                // two entries per round: both list reads, then both rows, then the stores -- a round is a chain of
+                // shared-memory and store latencies, and a thread has up to LIST_CAP / JS entries of a dense-ish tile
+                for (qe_u32 j = j0; j < end; j += 2u * JS) {
+                    const qe_u32 j1 = j + JS;
+                    const bool two = j1 < end;
+                    const qe_u32 r0 = qe_lds_u16(la + 2u * j);
+                    const qe_u32 r1 = qe_lds_u16(la + 2u * (two ? j1 : j));
+                    typename P::Row row0, row1;
+                    typename P::Out o0, o1;
+                    P::load_at(stage, slice0 + (int)r0, row0);
+                    P::load_at(stage, slice0 + (int)r1, row1);
+                    (void)P::eval(p, row0, o0);
+                    (void)P::eval(p, row1, o1);
+                    if (selp) {
+                        selp[j] = first_row + r0;
+                        qe_stg_if(two, selp + j1, first_row + r1);
+                    }
+                    P::emit_ptr(ptrs, j, o0, true);
+                    P::emit_ptr(ptrs, j1, o1, two);
                 }
             }
             __syncwarp();
-            if (lane == 0) qe_mbar_arrive(cb + O_EMPTY + 8u * st);
+            if (lane == 0 && !(QE_DEBUG_FLAGS & 64)) qe_mbar_arrive(cb + O_EMPTY + 8u * st);
             QE_RING_NEXT(st, par, 1u);
         }
     } else {

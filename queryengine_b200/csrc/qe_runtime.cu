@@ -824,8 +824,12 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         // Measured on B200, one 8-byte column, 10^9 rows (profiles/r02_sweep_02_sweepers.jsonl): 1 / 2 / 5 / 10 % kept
         // 1.32 / 1.50 / 1.61 / 1.64 ms with the masks only, 1.28 / 1.31 / 1.40 / 1.58 ms with lists of 32 and two sweeper
         // warps; from ~12 % up most warps keep more than 32 rows of a tile and the mixed kernel loses (15 %: 1.79 against
-        // 1.65 ms; lists of 64 lose everywhere above 5 %).  So: lists unless the same query kept more than 11 % last time.
-        s.list_cap = (bit_outputs || ctx->opt_list_cap < 0) ? 0 : ctx->opt_list_cap ? (int)ctx->opt_list_cap : (sel_hint > 0.11 ? 0 : 32);
+        // 1.65 ms; lists of 64 lose everywhere above 5 %).  Wide rows are bound by HBM, not by the consumers' instruction
+        // issue: the 40-byte lineitem filter (24 % kept) runs at the copy peak with masks, 3.46 ms per 5*10^8 rows, and at
+        // 3.59 ms with lists and sweepers (profiles/r02_sweep_03_lineitem_lists.jsonl).  So: lists for rows of up to 16
+        // bytes, unless the same query kept more than 11 % last time.
+        s.list_cap = (bit_outputs || ctx->opt_list_cap < 0) ? 0 : ctx->opt_list_cap ? (int)ctx->opt_list_cap
+                     : ((row_bytes > 16 || sel_hint > 0.11) ? 0 : 32);
         s.nsw = !s.list_cap || ctx->opt_nsw < 0 ? 0 : ctx->opt_nsw ? (int)ctx->opt_nsw : 2;
         const size_t meta = 64 + (size_t)s.tile_rows / 8 + (4 + 8 + 2 * (size_t)s.list_cap) * (size_t)s.ncw;   // per stage: barriers, keep masks, counts, bases, lists
         size_t n = ctx->opt_stages ? (size_t)ctx->opt_stages : 16;
