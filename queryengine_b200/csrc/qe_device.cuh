@@ -1016,15 +1016,20 @@ __device__ __forceinline__ qe_u32 qe_lds_u32(qe_u32 a)
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
     return v;
 }
-__device__ __forceinline__ qe_u32 qe_lds_u16(qe_u32 a)
+// list entries of the ring kernel's sparse path: u8 when a consumer warp's slice has at most 256 rows, else u16
+template <int W>
+__device__ __forceinline__ qe_u32 qe_lds_entry(qe_u32 a)
 {
-    unsigned short v;
-    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a) : "memory");
+    qe_u32 v;
+    if (W == 1) asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    else asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
     return v;
 }
-__device__ __forceinline__ void qe_sts_u16_if(bool ok, qe_u32 a, qe_u32 v)
+template <int W>
+__device__ __forceinline__ void qe_sts_entry_if(bool ok, qe_u32 a, qe_u32 v)
 {
-    asm volatile("{ .reg .pred q; setp.ne.u32 q, %0, 0; @q st.shared.u16 [%1], %2; }" :: "r"((qe_u32)ok), "r"(a), "h"((unsigned short)v) : "memory");
+    if (W == 1) asm volatile("{ .reg .pred q; setp.ne.u32 q, %0, 0; @q st.shared.u8 [%1], %2; }" :: "r"((qe_u32)ok), "r"(a), "r"(v) : "memory");
+    else asm volatile("{ .reg .pred q; setp.ne.u32 q, %0, 0; @q st.shared.u16 [%1], %2; }" :: "r"((qe_u32)ok), "r"(a), "r"(v) : "memory");
 }
 __device__ __forceinline__ qe_u64 qe_lds_u64(qe_u32 a)
 {
@@ -1315,6 +1320,7 @@ template <class P, bool HAS_SEL>
 __device__ __forceinline__ void qe_ring_scatter_list(const QeParams &p, qe_u32 stage, int wrow0, qe_u32 first_row_of_slice,
                                                      qe_u64 wbase, qe_u32 list, qe_u32 cnt)
 {
+    constexpr int LW = P::TILE_ROWS / P::NCW <= 256 ? 1 : 2;  // bytes per list entry
     const qe_u32 lane = qe_lane();
     const typename P::Ptrs ptrs = P::out_ptrs(p, wbase);
     qe_u32 *const selp = HAS_SEL ? qe_opaque_ptr(p.sel + wbase) : (qe_u32 *)0;
@@ -1323,7 +1329,7 @@ __device__ __forceinline__ void qe_ring_scatter_list(const QeParams &p, qe_u32 s
         if (base >= cnt) break;
         const qe_u32 i = base + lane;
         const bool ok = i < cnt;
-        const qe_u32 r = qe_lds_u16(list + 2u * (ok ? i : 0u));
+        const qe_u32 r = qe_lds_entry<LW>(list + (qe_u32)LW * (ok ? i : 0u));
         typename P::Row row;
         typename P::Out o;
         P::load_at(stage, wrow0 + (int)r, row);
@@ -1380,12 +1386,13 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
     constexpr qe_u32 O_LO = O_TILE + 4 * NST, O_ROW0 = O_LO + 4 * NST, O_FITS = O_ROW0 + 4 * NST;
     constexpr qe_u32 O_CNT = (O_FITS + 4 * NST + 15u) & ~15u; // u32 [NST][NCW]
     constexpr qe_u32 O_MASK = (O_CNT + 4 * NST * NCW + 15u) & ~15u;   // u32 [NST][TILE / 32]
-    // sparse tiles (qe_ring_scatter_list): u16 [NST][NCW][LIST_CAP] row numbers within the warp's slice
-    constexpr bool LIST = P::LIST_CAP > 0 && P::NBITCOLS == 0;
+    // sparse tiles (qe_ring_scatter_list, sweepers): u8 / u16 [NST][NCW][LIST_CAP] row numbers within the warp's slice
+    constexpr bool LIST = P::LIST_CAP > 0 && (P::NBITCOLS == 0 || P::NSW > 0);   // compacted bit columns: through the sweepers only
     constexpr qe_u32 LIST_CAP = LIST ? (qe_u32)P::LIST_CAP : 0u;
     constexpr int NSW = LIST ? P::NSW : 0;                  // sweeper warps (0: a consumer warp stores its own list in phase C)
     constexpr qe_u32 O_LIST = (O_MASK + 4 * NST * (TILE / 32) + 15u) & ~15u;
-    constexpr qe_u32 CTL_BYTES = O_LIST + 2u * NST * NCW * LIST_CAP;
+    constexpr int LW = WROWS <= 256 ? 1 : 2;                  // bytes per list entry
+    constexpr qe_u32 CTL_BYTES = O_LIST + (qe_u32)LW * NST * NCW * LIST_CAP;
 
     extern __shared__ __align__(128) unsigned char qe_dyn_smem[];
     __shared__ __align__(16) unsigned char s_ctl[CTL_BYTES];
@@ -1584,7 +1591,7 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                     room = wbase >= cap ? 0u : (cap - wbase > 0xffffffffull ? 0xffffffffu : (qe_u32)(cap - wbase));
                 }
                 const qe_u32 stage = dyn + st * (qe_u32)P::STAGE_BYTES;
-                const qe_u32 la = cb + O_LIST + 2u * LIST_CAP * ((qe_u32)NCW * st + l);
+                const qe_u32 la = cb + O_LIST + (qe_u32)LW * LIST_CAP * ((qe_u32)NCW * st + l);
                 const int slice0 = (int)l * WROWS;
                 const qe_u32 first_row = qe_lds_u32(cb + O_ROW0 + 4u * st) + (qe_u32)slice0;
                 const typename P::Ptrs ptrs = P::out_ptrs(p, wbase);
@@ -1595,8 +1602,8 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                 for (qe_u32 j = j0; j < end; j += 2u * JS) {
                     const qe_u32 j1 = j + JS;
                     const bool two = j1 < end;
-                    const qe_u32 r0 = qe_lds_u16(la + 2u * j);
-                    const qe_u32 r1 = qe_lds_u16(la + 2u * (two ? j1 : j));
+                    const qe_u32 r0 = qe_lds_entry<LW>(la + (qe_u32)LW * j);
+                    const qe_u32 r1 = qe_lds_entry<LW>(la + (qe_u32)LW * (two ? j1 : j));
                     typename P::Row row0, row1;
                     typename P::Out o0, o1;
                     P::load_at(stage, slice0 + (int)r0, row0);
@@ -1609,6 +1616,20 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                     }
                     P::emit_ptr(ptrs, j, o0, true);
                     P::emit_ptr(ptrs, j1, o1, two);
+                    if (P::NBITCOLS > 0) {
+                        // compacted bit columns (validity, BOOLEAN values): one OR per set bit into the pre-zeroed bitmap --
+                        // a listed tile keeps a handful of rows per consumer warp, and runs of different warps, tiles and
+                        // CTAs meet inside a word anyway (qe_store_bits_compact)
+                        const qe_u64 g0 = wbase + j, g1 = wbase + j1;
+#pragma unroll
+                        for (int b = 0; b < P::NBITCOLS; b++) {
+                            qe_u32 *bm = P::bitcol(p, b);
+                            if (bm) {
+                                if (P::bit(o0, b)) atomicOr(bm + (g0 >> 5), 1u << ((qe_u32)g0 & 31u));
+                                if (two && P::bit(o1, b)) atomicOr(bm + (g1 >> 5), 1u << ((qe_u32)g1 & 31u));
+                            }
+                        }
+                    }
                 }
             }
             __syncwarp();
@@ -1660,13 +1681,13 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                     for (int s = 0; s < STEPS; s++) cnt += __popc(mk[s]);
                     if (LIST && cnt != 0u && cnt <= LIST_CAP) {
                         // few rows kept: their row numbers, packed in row order (steps that kept nothing cost one branch)
-                        const qe_u32 la = cb + O_LIST + 2u * LIST_CAP * ((qe_u32)NCW * st_a + cw);
+                        const qe_u32 la = cb + O_LIST + (qe_u32)LW * LIST_CAP * ((qe_u32)NCW * st_a + cw);
                         const qe_u32 lt = qe_lanemask_lt();
                         qe_u32 off = 0;
 #pragma unroll
                         for (int s = 0; s < STEPS; s++) {
                             if (mk[s] != 0u) {
-                                qe_sts_u16_if((mk[s] >> lane) & 1u, la + 2u * (off + (qe_u32)__popc(mk[s] & lt)), (qe_u32)(s * 32) + lane);
+                                qe_sts_entry_if<LW>((mk[s] >> lane) & 1u, la + (qe_u32)LW * (off + (qe_u32)__popc(mk[s] & lt)), (qe_u32)(s * 32) + lane);
                                 off += (qe_u32)__popc(mk[s]);
                             }
                         }
@@ -1709,7 +1730,7 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                     const qe_u32 mk = cb + O_MASK + 4u * ((qe_u32)(TILE / 32) * st_c + cw * (qe_u32)STEPS);
                     const bool fits = qe_lds_u32(cb + O_FITS + 4u * st_c) != 0u;
                     if (LIST && fits && cnt <= LIST_CAP) {
-                        const qe_u32 la = cb + O_LIST + 2u * LIST_CAP * ((qe_u32)NCW * st_c + cw);
+                        const qe_u32 la = cb + O_LIST + (qe_u32)LW * LIST_CAP * ((qe_u32)NCW * st_c + cw);
                         if (p.sel) qe_ring_scatter_list<P, true>(p, stage, wrow0, first_row - lane, wbase, la, cnt);
                         else qe_ring_scatter_list<P, false>(p, stage, wrow0, first_row - lane, wbase, la, cnt);
                     } else if (fits) {

@@ -818,7 +818,7 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         s.tile_rows = (int)rows;
         s.nstages = 1;
         const size_t stage = qe::staged_smem_bytes(bp, s);
-        // sparse tiles: packed row lists instead of keep masks (qe_ring_scatter_list); pipelines that compact bit columns keep the masks
+        // sparse tiles: packed row lists instead of keep masks (qe_ring_scatter_list, sweeper warps)
         bool bit_outputs = false;
         for (const qe::BoundOutput &o : bp.outs) bit_outputs |= o.type == QE_TYPE_BOOLEAN || o.has_validity;
         // Measured on B200, one 8-byte column, 10^9 rows (profiles/r02_sweep_02_sweepers.jsonl): 1 / 2 / 5 / 10 % kept
@@ -828,10 +828,11 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         // issue: the 40-byte lineitem filter (24 % kept) runs at the copy peak with masks, 3.46 ms per 5*10^8 rows, and at
         // 3.59 ms with lists and sweepers (profiles/r02_sweep_03_lineitem_lists.jsonl).  So: lists for rows of up to 16
         // bytes, unless the same query kept more than 11 % last time.
-        s.list_cap = (bit_outputs || ctx->opt_list_cap < 0) ? 0 : ctx->opt_list_cap ? (int)ctx->opt_list_cap
-                     : ((row_bytes > 16 || sel_hint > 0.11) ? 0 : 32);
+        s.list_cap = ctx->opt_list_cap < 0 ? 0 : ctx->opt_list_cap ? (int)ctx->opt_list_cap : ((row_bytes > 16 || sel_hint > 0.11) ? 0 : 32);
+        if (bit_outputs && ctx->opt_nsw < 0) s.list_cap = 0;              // compacted bit columns of listed rows are written by the sweepers only
         s.nsw = !s.list_cap || ctx->opt_nsw < 0 ? 0 : ctx->opt_nsw ? (int)ctx->opt_nsw : 2;
-        const size_t meta = 64 + (size_t)s.tile_rows / 8 + (4 + 8 + 2 * (size_t)s.list_cap) * (size_t)s.ncw;   // per stage: barriers, keep masks, counts, bases, lists
+        const size_t entry = (size_t)s.tile_rows / (size_t)s.ncw <= 256 ? 1 : 2;                                   // bytes per list entry
+        const size_t meta = 64 + (size_t)s.tile_rows / 8 + (4 + 8 + entry * (size_t)s.list_cap) * (size_t)s.ncw;   // per stage: barriers, keep masks, counts, bases, lists
         size_t n = ctx->opt_stages ? (size_t)ctx->opt_stages : 16;
         while (n > 2 && n * (stage + meta) > (224u << 10)) n--;
         s.nstages = (int)n;

@@ -338,6 +338,22 @@ def test_sparse_tiles_row_lists_and_sweeper_warps(ctx, list_cap, nsw):
         assert np.array_equal(res.column(0)[0], x[want]) and np.array_equal(res.column(1)[0], d[want])
         assert np.array_equal(res.column(2)[0], x[want] * 0.5 + d[want])
         res.close()
+        # nullable and BOOLEAN outputs: compacted bit columns (listed rows: one OR per set bit by the sweepers)
+        filt2 = fn(Function.AND, fn(Function.CMP_LT, col(0, I), k * 1.5), col(2, B))
+        keep2 = (x < k * 1.5) & b
+        want2 = np.nonzero(keep2)[0].astype(np.uint32)
+        res = Pipeline(t, filt2, [col(1), col(2, B), fn(Function.MUL, col(1), 2.0), fn(Function.CMP_GT, col(1), 0.0), col(0, I)]).run()
+        assert res.num_rows == want2.size and np.array_equal(res.selection(), want2)
+        v0, n0 = res.column(0)
+        assert np.array_equal(n0, yv[want2]) and np.array_equal(v0[n0], y[want2][n0])
+        v1, n1 = res.column(1)
+        assert n1.all() and np.array_equal(v1, b[want2])
+        v2, n2 = res.column(2)
+        assert np.array_equal(n2, yv[want2]) and np.array_equal(v2[n2], (y[want2] * 2.0)[n2])
+        v3, n3 = res.column(3)
+        assert np.array_equal(n3, yv[want2]) and np.array_equal(v3[n3], (y[want2] > 0.0)[n3])
+        assert np.array_equal(res.column(4)[0], x[want2])
+        res.close()
         # capacity: exactly enough, and five rows short (the last list is cut, the overflow is reported)
         if want.size > 5:
             res = Pipeline(t, filt, [col(0, I)], out_capacity_rows=int(want.size)).run()
@@ -362,6 +378,7 @@ def test_sparse_tiles_row_lists_and_sweeper_warps(ctx, list_cap, nsw):
     spec = random_table(rng, 50_021, "dDbi", special_rate=0.1)
     compare_pipeline(c, spec, fn(Function.AND, fn(Function.CMP_LT, col(0), -950.0), col(2, B)), [col(0), col(3, I), fn(Function.SUB, col(0), 1.0)])
     compare_pipeline(c, spec, fn(Function.CMP_GT, col(1), 900.0), [col(0), col(3, I)])
+    compare_pipeline(c, spec, fn(Function.CMP_GT, col(1), 900.0), [col(1), col(2, B), fn(Function.DIV, col(1), col(0))])
     c.close()
 
 

@@ -30,6 +30,7 @@ def pipelines():
     return {
         "filter_i64": ([(I, False)], fn(Function.CMP_LT, col(0, I), float(2 ** 39)), [col(0, I)], []),
         "filter_f64": ([(D, False)], fn(Function.CMP_LT, col(0), float(2 ** 39)), [col(0)], []),
+        "filter_f64_nullable": ([(D, True)], fn(Function.CMP_LT, col(0), float(2 ** 39)), [col(0)], []),
         "q6": ([(D, False)] * 4, q6f, [fn(Function.MUL, col(1), col(2))], [AggregationFunction.SUM]),
         "q6_filter": ([(D, False)] * 4, q6f, [fn(Function.MUL, col(1), col(2))], []),
         "tree": ([(D, True)] * 4, None, [tree], []),

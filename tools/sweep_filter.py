@@ -41,12 +41,16 @@ def main():
     ap.add_argument("--type", default="i64", choices=["i64", "f64"])
     ap.add_argument("--configs", default="staging=2")
     ap.add_argument("--sels", default="0.01,0.5,0.99")
+    ap.add_argument("--null-rate", type=float, default=-1.0, help=">= 0: the column is nullable (its compacted copy then has a validity bitmap)")
     args = ap.parse_args()
     peak, _ = measured_peak_gbs()
     dt = DataType.INT64 if args.type == "i64" else DataType.DOUBLE
     ctx0 = Context(0)
-    t = ColumnarTable(ctx0, [Field("col", dt, False)], args.rows)
-    t.generate(0, capi.QE_GEN_UNIFORM_U40, SEED)
+    t = ColumnarTable(ctx0, [Field("col", dt, args.null_rate >= 0)], args.rows)
+    if args.null_rate >= 0:
+        t.generate(0, capi.QE_GEN_UNIFORM_U40, SEED, null_rate=args.null_rate)
+    else:
+        t.generate(0, capi.QE_GEN_UNIFORM_U40, SEED)
     for cfg in args.configs.split(";"):
         opts = dict(kv.split("=") for kv in cfg.split(",") if kv)
         # options are per context; the table stays on ctx0, so reset every known option first
