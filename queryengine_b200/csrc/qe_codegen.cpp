@@ -490,12 +490,90 @@ GroupPlan plan_groupby(const BoundPipeline &bp, int threads, int lane_acc_kb)
     return g;
 }
 
+namespace {
+
+// An expression as a tree again (the bound code is postfix), for the two questions below.
+struct ExprTree {
+    struct Node { int op; uint32_t arg; int kid[3]; };
+    std::vector<Node> nodes;
+    int root = -1;
+    explicit ExprTree(const BoundExpr &e)
+    {
+        std::vector<int> st;
+        for (const Instr &in : e.code) {
+            Node n{in.op, in.arg, {-1, -1, -1}};
+            const int ar = op_arity(in.op);
+            for (int i = ar - 1; i >= 0; i--) { n.kid[i] = st.back(); st.pop_back(); }
+            nodes.push_back(n);
+            st.push_back((int)nodes.size() - 1);
+        }
+        root = st.empty() ? -1 : st.back();
+    }
+};
+
+// Columns (slots) that are certainly non-null in every row the filter keeps.  FilterOperator keeps a row iff the
+// predicate is non-null and true (M/operator/FilterOperator.kt:20).  A Kleene AND is true only if both sides are true
+// (Interpreter.kt:54-72); every function but AND / OR / IF is null as soon as one operand is (Interpreter.kt:35-42), so a
+// non-null result means non-null operands; IF needs a non-null condition (Interpreter.kt:46-53).  OR promises nothing.
+void slots_nonnull(const ExprTree &t, int n, std::vector<bool> &nn)
+{
+    const ExprTree::Node &x = t.nodes[(size_t)n];
+    if (x.op == OP_LOAD_COL) { nn[x.arg] = true; return; }
+    if (x.op == OP_AND || x.op == OP_OR || op_arity(x.op) == 0) return;
+    if (x.op == OP_IF) { slots_nonnull(t, x.kid[0], nn); return; }
+    for (int i = 0; i < op_arity(x.op); i++) slots_nonnull(t, x.kid[i], nn);
+}
+void slots_of_true(const ExprTree &t, int n, std::vector<bool> &nn)
+{
+    const ExprTree::Node &x = t.nodes[(size_t)n];
+    if (x.op == OP_AND) { slots_of_true(t, x.kid[0], nn); slots_of_true(t, x.kid[1], nn); return; }
+    slots_nonnull(t, n, nn);
+}
+
+// Is the expression null exactly when one of the columns it reads is (no AND / OR / IF), and which columns are those?
+bool strict_slots(const BoundExpr &e, std::vector<bool> &used)
+{
+    for (const Instr &in : e.code) {
+        if (in.op == OP_AND || in.op == OP_OR || in.op == OP_IF) return false;
+        if (in.op == OP_LOAD_COL) used[in.arg] = true;
+    }
+    return true;
+}
+
+}  // namespace
+
+// Outputs whose validity the filter already decides: every kept row has them non-null, so their compacted validity
+// bitmap is a run of ones as long as the output (written per tile by the ring kernel's look-back warp instead of bit by
+// bit by the warps that scatter).  `x < k` over a nullable x returning x is the plain case.
+std::vector<bool> implied_valid_outputs(const BoundPipeline &bp)
+{
+    std::vector<bool> implied(bp.proj.size(), false);
+    if (!bp.has_filter) return implied;
+    std::vector<bool> nn(bp.slot_info.size(), false);
+    const ExprTree ft(bp.filter);
+    if (ft.root < 0) return implied;
+    slots_of_true(ft, ft.root, nn);
+    for (size_t k = 0; k < bp.proj.size(); k++) {
+        if (!bp.proj[k].nullable) continue;
+        std::vector<bool> used(bp.slot_info.size(), false);
+        if (!strict_slots(bp.proj[k], used)) continue;
+        bool ok = true;
+        for (size_t sl = 0; sl < used.size(); sl++)
+            if (used[sl] && bp.slot_info[sl].nullable && !nn[sl]) ok = false;
+        implied[k] = ok;
+    }
+    return implied;
+}
+
 std::string generate_source(const BoundPipeline &bp, KernelMode mode, const TileShape &shape)
 {
     std::string s;
     char b[256];
     const int nslots = (int)bp.slot_info.size();
     const int nproj = (int)bp.proj.size();
+    // validity bitmaps the ring filter writes as runs of ones (see implied_valid_outputs); the other kernels write every bit
+    std::vector<bool> implied(bp.proj.size(), false);
+    if (mode == KM_FILTER && shape.ring) implied = implied_valid_outputs(bp);
 
     s += "// generated by qe_codegen.cpp -- pipeline: " + bp.signature() + "\n";
     s += "#include \"qe_device.cuh\"\n\nstruct P {\n";
@@ -505,7 +583,7 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
     const bool is_group = mode == KM_GROUPBY_PRIVATE || mode == KM_GROUPBY_ATOMIC || mode == KM_GROUPBY_SHARED || mode == KM_GROUPBY_REG;
     if (mode != KM_AGG && !is_group) {
         for (int k = 0; k < nproj; k++) {
-            if (bp.outs[k].has_validity) {
+            if (bp.outs[k].has_validity && !implied[(size_t)k]) {
                 snprintf(b, sizeof b, "p.out_valid[%d]", k);
                 BitCol bc; bc.ptr = b;
                 snprintf(b, sizeof b, "o.n%d", k); bc.bit = b;
@@ -721,6 +799,19 @@ std::string generate_source(const BoundPipeline &bp, KernelMode mode, const Tile
             s += b;
         }
         s += "    }\n";
+    }
+    if (mode == KM_FILTER && shape.ring) {
+        int n = 0;
+        std::string body;
+        for (int k = 0; k < nproj; k++) {
+            if (!(bp.outs[k].has_validity && implied[(size_t)k])) continue;
+            snprintf(b, sizeof b, "        case %d: return p.out_valid[%d];\n", n++, k);
+            body += b;
+        }
+        snprintf(b, sizeof b, "    static constexpr int NIMPLIED = %d;      // validity bitmaps that are all ones: the filter keeps no row where they are null\n", n);
+        s += b;
+        s += "    static __device__ __forceinline__ qe_u32 *implied_col(const QeParams &p, int i) {\n        switch (i) {\n" + body +
+             "        }\n        return 0;\n    }\n";
     }
     if (mode != KM_AGG && !is_group) {
         s += "    static __device__ __forceinline__ qe_u32 *bitcol(const QeParams &p, int b) {\n        switch (b) {\n";

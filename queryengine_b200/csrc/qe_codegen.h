@@ -87,6 +87,9 @@ struct TileShape {
     int block_threads() const { return (greg || pring) ? 32 * (1 + ncw) : ring ? 32 * (2 + nlb + (list_cap ? nsw : 0) + ncw) : 256; }
 };
 
+// outputs whose validity bitmap is all ones because the filter keeps no row where they are null (ring filter kernel)
+std::vector<bool> implied_valid_outputs(const BoundPipeline &bp);
+
 // bytes of dynamic shared memory the staged filter kernel needs (0 when not staged)
 size_t staged_smem_bytes(const BoundPipeline &bp, const TileShape &shape);
 

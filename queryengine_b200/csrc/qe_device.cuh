@@ -1359,6 +1359,21 @@ __device__ __forceinline__ void qe_prefetch_l2_keep(const void *p)
     asm volatile("prefetch.global.L2::evict_last [%0];" :: "l"(p));
 }
 
+// Bits [lo, hi) of a pre-zeroed bitmap to one, by one warp: whole words with plain stores (no other run reaches into
+// them), the two end words with an OR (neighbouring runs -- other tiles, other CTAs -- meet there).
+__device__ __forceinline__ void qe_set_bit_run(qe_u32 *bitmap, qe_u64 lo, qe_u64 hi)
+{
+    if (hi <= lo) return;
+    const qe_u64 w0 = lo >> 5, w1 = (hi - 1ull) >> 5;
+    for (qe_u64 w = w0 + qe_lane(); w <= w1; w += 32ull) {
+        qe_u32 m = 0xffffffffu;
+        if (w == w0) m &= 0xffffffffu << ((qe_u32)lo & 31u);
+        if (w == w1) m &= 0xffffffffu >> (31u - ((qe_u32)(hi - 1ull) & 31u));
+        if (w == w0 || w == w1) atomicOr(bitmap + w, m);
+        else bitmap[w] = m;
+    }
+}
+
 #define QE_RING_LB_PER_LANE 6        // descriptors per lane per look-back round trip (192 per warp)
 
 // phase timing of the ring kernel (QE_DEBUG_FLAGS & 16; tools/phase_timing.py): cycles per CTA in p.debug[cta][16]
@@ -1561,6 +1576,17 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                 qe_mbar_arrive(cb + O_PREF + 8u * st);
                 qe_mbar_arrive(cb + O_EMPTY + 8u * st);
                 if (t == p.ntiles - 1u) *p.out_count = (base_full & ~p.out_base_mask) + excl + c;   // stays the running total
+            }
+            if (P::NIMPLIED > 0 && c != 0u) {
+                // validity bitmaps the filter has decided (P::implied_col): this tile's rows are ones [excl, excl + c), as
+                // far as they fit.  After the prefix is out, so nobody waits for it.
+                const qe_u64 cap = (qe_u64)p.out_capacity;
+                const qe_u64 lo = excl < cap ? excl : cap, hi = excl + c < cap ? excl + c : cap;
+#pragma unroll
+                for (int i = 0; i < P::NIMPLIED; i++) {
+                    qe_u32 *bm = P::implied_col(p, i);
+                    if (bm) qe_set_bit_run(bm, lo, hi);
+                }
             }
         }
     } else if (NSW > 0 && warp < 2u + (qe_u32)NLB + (qe_u32)NSW) {

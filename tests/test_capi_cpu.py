@@ -150,6 +150,33 @@ def test_literals_are_kernel_parameters():
     assert s1 == s2 and "(qe_i32)p.lit_lo[0]" in s1
 
 
+def test_validity_the_filter_decides_is_written_as_runs():
+    """Ring filter: an output that cannot be null in a kept row -- it is null only if a column is that the predicate needs
+    non-null (FilterOperator.kt:20 keeps non-null true only; Kleene AND is true only if both sides are,
+    Interpreter.kt:54-72) -- has no per-row validity bit in the generated code (NBITCOLS), its bitmap is P::implied_col."""
+    def src_of(schema, filt, projs):
+        rc, src, _, err = _generate(schema, filt, projs, compile_=True)
+        assert rc == 0, err
+        return src
+    two = [(D, True), (D, True)]
+    a = src_of(two, fn(Function.CMP_LT, col(0), 5.0), [col(0), fn(Function.MUL, col(0), 2.0)])
+    assert "NBITCOLS = 0" in a and "NIMPLIED = 2" in a and "case 1: return p.out_valid[1];" in a
+    # the other column is not read by the predicate: its validity stays a bit column
+    b = src_of(two, fn(Function.CMP_LT, col(0), 5.0), [col(0), col(1)])
+    assert "NBITCOLS = 1" in b and "NIMPLIED = 1" in b and "case 0: return p.out_valid[1];" in b.split("bitcol(")[1]
+    # AND passes the promise on, OR and IF do not; NOT and arithmetic do
+    c = src_of(two, fn(Function.AND, fn(Function.CMP_LT, col(0), 5.0), fn(Function.NOT, fn(Function.CMP_GT, fn(Function.ADD, col(1), 1.0), 2.0))),
+               [fn(Function.ADD, col(0), col(1))])
+    assert "NBITCOLS = 0" in c and "NIMPLIED = 1" in c
+    d = src_of(two, fn(Function.OR, fn(Function.CMP_LT, col(0), 5.0), fn(Function.CMP_GT, col(1), 2.0)), [col(0), col(1)])
+    assert "NBITCOLS = 2" in d and "NIMPLIED = 0" in d
+    e = src_of(two, fn(Function.CMP_LT, col(0), 5.0), [fn(Function.IF, fn(Function.CMP_GT, col(0), 1.0), col(0), 0.0)])
+    assert "NBITCOLS = 1" in e and "NIMPLIED = 0" in e
+    # the other filter bodies write every bit themselves
+    rc, f, _, err = _generate(two, fn(Function.CMP_LT, col(0), 5.0), [col(0)], staging=0)
+    assert rc == 0 and "NBITCOLS = 1" in f and "NIMPLIED" not in f, err
+
+
 def test_closure_compiler_mode_is_a_comparison_argument():
     """Mode.CLOSURE_COMPILER (IEEE ordering, M/evaluator/ClosureCompiler.kt:127-130) travels as QE_CMP_IEEE in the
     argument of CMP_LT / LE / GE / GT: another kernel than the total-order one, the same kernel for an integer column

@@ -338,6 +338,13 @@ def test_sparse_tiles_row_lists_and_sweeper_warps(ctx, list_cap, nsw):
         assert np.array_equal(res.column(0)[0], x[want]) and np.array_equal(res.column(1)[0], d[want])
         assert np.array_equal(res.column(2)[0], x[want] * 0.5 + d[want])
         res.close()
+        # outputs the filter has made non-null (y is read by the predicate): validity = runs of ones, written per tile
+        res = Pipeline(t, filt, [col(1), fn(Function.MUL, col(1), 2.0), col(0, I), fn(Function.CMP_GT, col(1), 0.0)]).run()
+        assert res.num_rows == want.size and np.array_equal(res.selection(), want)
+        for kk, ref in ((0, y[want]), (1, y[want] * 2.0), (2, x[want]), (3, y[want] > 0.0)):
+            vv, nn = res.column(kk)
+            assert nn.all() and np.array_equal(vv, ref), kk
+        res.close()
         # nullable and BOOLEAN outputs: compacted bit columns (listed rows: one OR per set bit by the sweepers)
         filt2 = fn(Function.AND, fn(Function.CMP_LT, col(0, I), k * 1.5), col(2, B))
         keep2 = (x < k * 1.5) & b
