@@ -1237,10 +1237,34 @@ __device__ __forceinline__ T *qe_opaque_ptr(T *q)
 // warp step = one contiguous run of the outputs.  Two code paths, chosen per warp and
 // tile by the number of kept rows: a fully unrolled branch-free one (predicated
 // stores), and for sparse tiles a loop over the steps that kept anything.
+// Compacted bit columns of one consumer warp's slice of a tile: the kept rows' bits are appended step by step to a
+// 64-bit window per bit column (uniform over the warp; one REDUX.OR per step and column), and every time 32 bits are
+// complete the low word is OR-ed into the pre-zeroed bitmap by lane 0.  (Round 1 shifted and OR-ed two words per step and
+// column, qe_store_bits_compact: ~20 instructions and two atomics, against ~8 and one atomic per 32 kept rows.)
+template <int NB>
+struct QeBitRun {
+    qe_u64 acc[NB > 0 ? NB : 1];
+    qe_u64 word;              // index of the bitmap word the low half of acc belongs to
+    qe_u32 fill;              // bits of acc in use
+};
+
+template <class P>
+__device__ __forceinline__ void qe_bit_run_flush(const QeParams &p, QeBitRun<P::NBITCOLS> &br)
+{
+    if (qe_lane() == 0) {
+#pragma unroll
+        for (int b = 0; b < P::NBITCOLS; b++) {
+            qe_u32 *bm = P::bitcol(p, b);
+            const qe_u32 lo = (qe_u32)br.acc[b];
+            if (bm && lo) atomicOr(bm + br.word, lo);
+        }
+    }
+}
+
 template <class P, bool CHECK_CAP, bool HAS_SEL>
 __device__ __forceinline__ void qe_ring_scatter_step(const QeParams &p, const typename P::Ptrs &ptrs, qe_u32 *selp,
                                                      qe_u32 stage, int wrow0, int c, qe_u32 row_id, qe_u64 wbase,
-                                                     qe_u32 cap_left, qe_u32 m, qe_u32 &off)
+                                                     qe_u32 cap_left, qe_u32 m, qe_u32 &off, QeBitRun<P::NBITCOLS> &br)
 {
     const qe_u32 lane = qe_lane();
     const bool kept = (m >> lane) & 1u;
@@ -1252,12 +1276,21 @@ __device__ __forceinline__ void qe_ring_scatter_step(const QeParams &p, const ty
     const bool ok = kept && (!CHECK_CAP || idx < cap_left);
     if (HAS_SEL) qe_stg_if(ok, selp + idx, row_id);
     P::emit_ptr(ptrs, idx, o, ok);
-    if (P::NBITCOLS > 0 && (!CHECK_CAP || off < cap_left)) {
-        const qe_u32 rk[1] = {idx - off};
+    if (P::NBITCOLS > 0) {
+        (void)wbase;
+        const qe_u32 mine = 1u << (idx - off);                    // this row's place among the step's kept rows
 #pragma unroll
         for (int b = 0; b < P::NBITCOLS; b++) {
-            qe_u32 *bm = P::bitcol(p, b);
-            if (bm) qe_store_bits_compact<1>(bm, wbase + off, rk, kept ? 1u : 0u, P::bit(o, b) ? 1u : 0u);
+            const qe_u32 w = __reduce_or_sync(QE_FULL_MASK, (ok && P::bit(o, b)) ? mine : 0u);   // rows past the capacity leave no bit
+            br.acc[b] |= (qe_u64)w << br.fill;
+        }
+        br.fill += (qe_u32)__popc(m);
+        if (br.fill >= 32u) {                                     // uniform
+            qe_bit_run_flush<P>(p, br);
+#pragma unroll
+            for (int b = 0; b < P::NBITCOLS; b++) br.acc[b] >>= 32;
+            br.fill -= 32u;
+            br.word += 1ull;
         }
     }
     off += __popc(m);
@@ -1277,6 +1310,11 @@ __device__ __forceinline__ void qe_ring_scatter(const QeParams &p, qe_u32 stage,
         cap_left = wbase >= cap ? 0u : (cap - wbase > 0xffffffffull ? 0xffffffffu : (qe_u32)(cap - wbase));
     }
     qe_u32 off = 0;                                           // kept rows of this warp in earlier steps
+    QeBitRun<P::NBITCOLS> br;
+#pragma unroll
+    for (int b = 0; b < (P::NBITCOLS > 0 ? P::NBITCOLS : 1); b++) br.acc[b] = 0ull;
+    br.word = wbase >> 5;
+    br.fill = (qe_u32)wbase & 31u;
     // Which path is decided by the number of warp steps that kept anything, not by the row count: the loop
     // costs ~27 instructions per non-empty step, the unrolled path ~15 per step.  (Deciding by rows kept,
     // dense from 25 % up, left 5-20 % selectivity in the loop with every step non-empty: 2.2-2.55 ms per
@@ -1296,7 +1334,7 @@ __device__ __forceinline__ void qe_ring_scatter(const QeParams &p, qe_u32 stage,
 #pragma unroll
         for (int s = 0; s < STEPS; s++)
             qe_ring_scatter_step<P, CHECK_CAP, HAS_SEL>(p, ptrs, selp, stage, wrow0, s * 32, first_row + (qe_u32)(s * 32), wbase,
-                                                        cap_left, mk[s], off);
+                                                        cap_left, mk[s], off, br);
     } else {
         // Sparse tiles: one non-empty step per iteration.  (Two steps per iteration -- both rows loaded and evaluated
         // before either is stored, to break the serial shuffle -> load -> evaluate -> rank -> store chain -- measured
@@ -1307,9 +1345,10 @@ __device__ __forceinline__ void qe_ring_scatter(const QeParams &p, qe_u32 stage,
             act &= act - 1u;
             const qe_u32 m = __shfl_sync(QE_FULL_MASK, mine, s);
             qe_ring_scatter_step<P, CHECK_CAP, HAS_SEL>(p, ptrs, selp, stage, wrow0, s * 32, first_row + (qe_u32)(s * 32), wbase,
-                                                        cap_left, m, off);
+                                                        cap_left, m, off, br);
         }
     }
+    if (P::NBITCOLS > 0 && br.fill != 0u) qe_bit_run_flush<P>(p, br);     // the slice's last, partial word
 }
 
 // Phase C for a warp whose slice kept at most P::LIST_CAP rows of the tile: phase A left their row numbers (within the

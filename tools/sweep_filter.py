@@ -42,11 +42,16 @@ def main():
     ap.add_argument("--configs", default="staging=2")
     ap.add_argument("--sels", default="0.01,0.5,0.99")
     ap.add_argument("--null-rate", type=float, default=-1.0, help=">= 0: the column is nullable (its compacted copy then has a validity bitmap)")
+    ap.add_argument("--payload", action="store_true", help="a second, nullable f64 column (10 %% nulls) the filter does not read is returned too: "
+                                                           "its validity is a compacted bit column that has to be assembled row by row")
     args = ap.parse_args()
     peak, _ = measured_peak_gbs()
     dt = DataType.INT64 if args.type == "i64" else DataType.DOUBLE
     ctx0 = Context(0)
-    t = ColumnarTable(ctx0, [Field("col", dt, args.null_rate >= 0)], args.rows)
+    fields = [Field("col", dt, args.null_rate >= 0)] + ([Field("y", DataType.DOUBLE, True)] if args.payload else [])
+    t = ColumnarTable(ctx0, fields, args.rows)
+    if args.payload:
+        t.generate(1, capi.QE_GEN_UNIFORM_REAL, SEED + 1, 0.0, 1.0, null_rate=0.1)
     if args.null_rate >= 0:
         t.generate(0, capi.QE_GEN_UNIFORM_U40, SEED, null_rate=args.null_rate)
     else:
@@ -64,9 +69,10 @@ def main():
         try:
             for s in [float(x) for x in args.sels.split(",")]:
                 k = float(int(s * 2 ** 40))
-                pipe = Pipeline(t, fn(Function.CMP_LT, col(0, dt, "col"), k), [col(0, dt, "col")])
+                outs = [col(0, dt, "col")] + ([col(1, DataType.DOUBLE, "y")] if args.payload else [])
+                pipe = Pipeline(t, fn(Function.CMP_LT, col(0, dt, "col"), k), outs)
                 ms, kept = time_pipeline(pipe, args.reps)
-                gbs = (8.0 * args.rows + 12.0 * kept) / (ms * 1e-3) / 1e9
+                gbs = ((16.125 if args.payload else 8.0) * args.rows + (20.125 if args.payload else 12.0) * kept) / (ms * 1e-3) / 1e9
                 row[f"ms_{s}"] = round(ms, 3)
                 row[f"gbs_{s}"] = round(gbs, 1)
                 row[f"frac_{s}"] = round(gbs / peak, 3)
