@@ -1749,11 +1749,20 @@ __device__ __forceinline__ void qe_filter_ring_body(const QeParams &p)
                         const qe_u32 la = cb + O_LIST + (qe_u32)LW * LIST_CAP * ((qe_u32)NCW * st_a + cw);
                         const qe_u32 lt = qe_lanemask_lt();
                         qe_u32 off = 0;
+                        if (cnt > (qe_u32)STEPS) {
+                            // more kept rows than steps: hardly a step is empty, the branches only cost (5-10 % kept)
 #pragma unroll
-                        for (int s = 0; s < STEPS; s++) {
-                            if (mk[s] != 0u) {
+                            for (int s = 0; s < STEPS; s++) {
                                 qe_sts_entry_if<LW>((mk[s] >> lane) & 1u, la + (qe_u32)LW * (off + (qe_u32)__popc(mk[s] & lt)), (qe_u32)(s * 32) + lane);
                                 off += (qe_u32)__popc(mk[s]);
+                            }
+                        } else {
+#pragma unroll
+                            for (int s = 0; s < STEPS; s++) {
+                                if (mk[s] != 0u) {
+                                    qe_sts_entry_if<LW>((mk[s] >> lane) & 1u, la + (qe_u32)LW * (off + (qe_u32)__popc(mk[s] & lt)), (qe_u32)(s * 32) + lane);
+                                    off += (qe_u32)__popc(mk[s]);
+                                }
                             }
                         }
                     }
