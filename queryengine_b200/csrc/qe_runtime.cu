@@ -827,8 +827,9 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         // 1.65 ms; lists of 64 lose everywhere above 5 %).  Wide rows are bound by HBM, not by the consumers' instruction
         // issue: the 40-byte lineitem filter (24 % kept) runs at the copy peak with masks, 3.46 ms per 5*10^8 rows, and at
         // 3.59 ms with lists and sweepers (profiles/r02_sweep_03_lineitem_lists.jsonl).  So: lists for rows of up to 16
-        // bytes, unless the same query kept more than 11 % last time.
-        s.list_cap = ctx->opt_list_cap < 0 ? 0 : ctx->opt_list_cap ? (int)ctx->opt_list_cap : ((row_bytes > 16 || sel_hint > 0.11) ? 0 : 32);
+        // bytes, unless the same query kept more than 13.5 % last time (with the later list-building and sweeper changes the
+        // lists win up to 13 %: 1.60 against 1.65 ms; 15 %: 1.71 against 1.65).
+        s.list_cap = ctx->opt_list_cap < 0 ? 0 : ctx->opt_list_cap ? (int)ctx->opt_list_cap : ((row_bytes > 16 || sel_hint > 0.135) ? 0 : 32);
         if (bit_outputs && ctx->opt_nsw < 0) s.list_cap = 0;              // compacted bit columns of listed rows are written by the sweepers only
         s.nsw = !s.list_cap || ctx->opt_nsw < 0 ? 0 : ctx->opt_nsw ? (int)ctx->opt_nsw : 2;
         const size_t entry = (size_t)s.tile_rows / (size_t)s.ncw <= 256 ? 1 : 2;                                   // bytes per list entry
