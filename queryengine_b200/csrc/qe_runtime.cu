@@ -812,6 +812,13 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         // 1024 rows = 40 KB measured 96.7 % of the copy peak, 512 rows = 20 KB 64.5 %), down otherwise.
         size_t rows = stage_target / row_bytes / quantum * quantum;
         if (rows * row_bytes < stage_target && (rows + quantum) * row_bytes <= (44u << 10)) rows += quantum;
+        // A query that is known to keep little (at most 6 % the last time) runs on the row lists and the sweepers below: its
+        // consumer warps pay a fixed price per tile (barriers, counts, the look-back behind them) that is as large as the
+        // work of a 7-step slice, so 40 KB tiles (five stages) and a third sweeper warp win there -- 0.5 / 1 / 2 / 5 %:
+        // 1.146 / 1.198 / 1.258 / 1.349 ms against 1.238 / 1.253 / 1.302 / 1.381 ms per 10^9 rows; from 8 % up the smaller
+        // tiles win (10 %: 1.48 against 1.60; 50 %: 2.14 against 2.53) -- profiles/r02_sweep_07_tile_rows.jsonl
+        const bool known_sparse = row_bytes <= 8 && sel_hint >= 0.0 && sel_hint <= 0.06 && ctx->opt_list_cap >= 0 && ctx->opt_nsw >= 0;
+        if (known_sparse && !ctx->opt_stage_kb) rows = std::max(rows, (size_t)(40u << 10) / row_bytes / quantum * quantum);
         if (ctx->opt_tile_rows) rows = (size_t)ctx->opt_tile_rows;
         rows = std::min<size_t>(std::max(rows, quantum), (size_t)kPadRows / quantum * quantum);
         if (rows % quantum) rows = (rows + quantum - 1) / quantum * quantum;
@@ -831,7 +838,7 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         // lists win up to 13 %: 1.60 against 1.65 ms; 15 %: 1.71 against 1.65).
         s.list_cap = ctx->opt_list_cap < 0 ? 0 : ctx->opt_list_cap ? (int)ctx->opt_list_cap : ((row_bytes > 16 || sel_hint > 0.135) ? 0 : 32);
         if (bit_outputs && ctx->opt_nsw < 0) s.list_cap = 0;              // compacted bit columns of listed rows are written by the sweepers only
-        s.nsw = !s.list_cap || ctx->opt_nsw < 0 ? 0 : ctx->opt_nsw ? (int)ctx->opt_nsw : 2;
+        s.nsw = !s.list_cap || ctx->opt_nsw < 0 ? 0 : ctx->opt_nsw ? (int)ctx->opt_nsw : (known_sparse ? 3 : 2);
         const size_t entry = (size_t)s.tile_rows / (size_t)s.ncw <= 256 ? 1 : 2;                                   // bytes per list entry
         const size_t meta = 64 + (size_t)s.tile_rows / 8 + (4 + 8 + entry * (size_t)s.list_cap) * (size_t)s.ncw;   // per stage: barriers, keep masks, counts, bases, lists
         size_t n = ctx->opt_stages ? (size_t)ctx->opt_stages : 16;
