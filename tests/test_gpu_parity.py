@@ -389,6 +389,48 @@ def test_sparse_tiles_row_lists_and_sweeper_warps(ctx, list_cap, nsw):
     c.close()
 
 
+def test_sparse_path_stress_random_shapes_and_selectivities(ctx):
+    """compute-sanitizer is closed on this pool, so the hand-offs of the ring kernel (producer / publisher / look-back /
+    sweepers / consumers over five mbarrier arrays) are exercised the blunt way: many tiles per CTA, random shapes and
+    selectivities, repeated runs into one reused result (every run picks its shape from the selectivity the last one
+    measured), each compared with numpy -- a lost or doubled row, a stale list or a stage released too early shows."""
+    rng = np.random.default_rng(2024)
+    n = 6_000_011                                       # ~1 300 tiles of 4 480 rows: nine per CTA
+    x = rng.integers(0, 1 << 20, n).astype(np.int64)
+    y = rng.uniform(-1.0, 1.0, n)
+    yv = rng.random(n) < 0.85
+    for trial in range(6):
+        c = Context(0)
+        opts = {"list_cap": int(rng.choice([0, 0, 32, 64, -1])), "nsw": int(rng.choice([0, 0, 1, 3, 4, -1])),
+                "stages": int(rng.choice([0, 0, 3, 4, 5])), "ncw": int(rng.choice([0, 0, 8, 16, 24])), "nlb": int(rng.choice([0, 0, 2]))}
+        for k_, v_ in opts.items():
+            c.set_option(k_, v_)
+        t = ColumnarTable.from_arrays(c, [Field("x", I, False), Field("y", D, True)], [x, y], [None, yv])
+        res = None
+        res2 = None
+        for rep in range(8):
+            frac = float(rng.choice([0.0005, 0.004, 0.01, 0.03, 0.07, 0.12, 0.2, 0.6, 1.0]))
+            k = float(int(frac * (1 << 20)))
+            want = np.nonzero(x < k)[0].astype(np.uint32)
+            res = Pipeline(t, fn(Function.CMP_LT, col(0, I), k), [col(0, I)]).run(res)
+            assert res.num_rows == want.size, (opts, frac)
+            assert np.array_equal(res.selection(), want) and np.array_equal(res.column(0)[0], x[want]), (opts, frac)
+            # nullable payload + a nullable column the predicate reads: bit columns by runs, by the sweepers, by the masks
+            keep = (x < k) & yv & (y < 0.5)
+            want2 = np.nonzero(keep)[0].astype(np.uint32)
+            res2 = Pipeline(t, fn(Function.AND, fn(Function.CMP_LT, col(0, I), k), fn(Function.CMP_LT, col(1), 0.5)),
+                            [col(1), fn(Function.CMP_GT, col(1), 0.0)]).run(res2)
+            assert res2.num_rows == want2.size, (opts, frac)
+            v0, n0 = res2.column(0)
+            v1, n1 = res2.column(1)
+            assert np.array_equal(res2.selection(), want2) and n0.all() and n1.all(), (opts, frac)
+            assert np.array_equal(v0, y[want2]) and np.array_equal(v1, y[want2] > 0.0), (opts, frac)
+        res.close()
+        res2.close()
+        t.close()
+        c.close()
+
+
 @pytest.mark.parametrize("interpreter", [False, True])
 def test_aggregates(ctx, interpreter):
     rng = np.random.default_rng(5)

@@ -25,7 +25,8 @@ done = []
 
 
 def ring_filters():
-    for opts in ({}, {"ncw": 16}, {"ncw": 20, "stages": 4, "defer": 1}, {"stage_kb": 16, "nlb": 2}, {"staging": 0}, {"staging": 1}):
+    for opts in ({}, {"ncw": 16}, {"ncw": 20, "stages": 4, "defer": 1}, {"stage_kb": 16, "nlb": 2}, {"staging": 0}, {"staging": 1},
+                 {"list_cap": -1}, {"list_cap": 32, "nsw": -1}, {"list_cap": 64, "nsw": 3}, {"list_cap": 32, "nsw": 1, "stage_kb": 40}):
         c = Context(0)
         for k, v in opts.items():
             c.set_option(k, v)
