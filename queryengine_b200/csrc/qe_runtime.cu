@@ -2288,6 +2288,12 @@ extern "C" int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_
             r->streamed = true;
             r->batch_rows = n;
             r->host->count = r->mode == qe::KM_PROJECT ? (unsigned long long)n : st.counts[(size_t)(nchunks - 1) * np + q];
+            // the next stream of the same query picks its kernel shape by what this one kept (every chunk the same shape:
+            // the hint only changes here, between streams)
+            if (r->mode == qe::KM_FILTER && n > 0) {
+                r->f_sel = (double)r->host->count / (double)n;
+                for (qe_result *m : r->ring) m->f_sel = r->f_sel;
+            }
         }
     }
     return QE_OK;

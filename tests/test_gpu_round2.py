@@ -212,6 +212,45 @@ def test_bounded_stream_equals_the_oracle(ctx, chunk_relative):
         b.free()
 
 
+@pytest.mark.parametrize("frac", [0.004, 0.05, 0.3])
+def test_bounded_stream_of_a_narrow_nullable_column_takes_the_sparse_path(ctx, frac):
+    """One nullable f64 column streamed through a window of three chunk slots, `x < k` returning x: the chained chunks run
+    on the row lists + sweeper warps (8-byte rows), the column's validity is a run of ones per tile whose ends meet inside
+    bytes shared by two chunks, and the second stream picks its shape from what the first one kept (the whole stream, not
+    the chunk).  Against numpy, twice."""
+    rng = np.random.default_rng(int(frac * 1000) + 5)
+    chunk = 1 << 16
+    n = 9 * chunk + 12_345
+    x = rng.uniform(0.0, 1.0, n)
+    xv = rng.random(n) < 0.9
+    keep = xv & (x < frac)
+    want = np.nonzero(keep)[0]
+    window = ColumnarTable(ctx, [Field("x", D, True)], 3 * chunk)
+    h_x = Pinned(n * 8, np.float64); h_x.array[:n] = x
+    h_v = Pinned((n + 7) // 8, np.uint8); h_v.array[:(n + 7) // 8] = np.packbits(xv, bitorder="little")
+    cap = want.size + 64
+    h_sel = Pinned(cap * 4, np.uint32)
+    h_out = Pinned(cap * 8, np.float64)
+    h_on = Pinned(cap // 8 + 8, np.uint8)
+    pipe = Pipeline(window, fn(Function.CMP_LT, col(0), float(frac)), [col(0)], out_capacity_rows=cap)
+    res = None
+    for rep in range(3):
+        h_out.array[:] = -1.0
+        h_on.array[:] = 0
+        res = stream_pipelines(window, [pipe], [h_x.ptr.value], [h_v.ptr.value], chunk_rows=chunk, results=[res[0]] if res else None,
+                               host_selection=[h_sel.ptr.value], host_out_values=[[h_out.ptr.value]],
+                               host_out_validity=[[h_on.ptr.value]], total_rows=n)
+        assert res[0].num_rows == want.size, rep
+        assert np.array_equal(h_sel.array[:want.size].astype(np.int64), want), rep
+        assert np.array_equal(h_out.array[:want.size], x[want]), rep
+        bits = np.unpackbits(h_on.array, bitorder="little")
+        assert bits[:want.size].all() and not bits[want.size:].any(), rep          # ones as far as the output goes, nothing beyond
+    res[0].close()
+    window.close()
+    for b in (h_x, h_v, h_sel, h_out, h_on):
+        b.free()
+
+
 def test_bounded_stream_dense_projection_and_aggregation(ctx):
     """Dense projection (values + validity per chunk) and a global aggregation through the bounded window; the
     aggregation over streamed chunks of 2^20 rows has the bits of one run over the resident table."""
