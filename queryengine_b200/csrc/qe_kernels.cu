@@ -230,6 +230,18 @@ int interp_blocks_per_sm(int mode)
     return n;
 }
 
+__global__ void qe_store_u64_kernel(unsigned long long *dst, const unsigned long long *src)
+{
+    *dst = *src;
+    __threadfence_system();
+}
+
+cudaError_t launch_store_u64(unsigned long long *dst, const unsigned long long *src, cudaStream_t stream)
+{
+    qe_store_u64_kernel<<<1, 1, 0, stream>>>(dst, src);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_agg_final(const double *sub_partials, int64_t nsub, int nagg, double *super_partials, cudaStream_t stream)
 {
     const int64_t sps = QE_AGG_SUPER_ROWS / QE_AGG_SUB_ROWS;

@@ -32,6 +32,10 @@ cudaError_t launch_groupby_merge(const uint64_t *part, const uint32_t *part_slot
 cudaError_t launch_groupby_collect(const uint32_t *state, const uint64_t *keys, const uint32_t *nulls, const uint64_t *acc,
                                    int64_t nslots, int nkeys, int nwords, uint64_t *records, uint32_t *ctl, uint32_t capacity,
                                    cudaStream_t stream);
+// *dst = *src by one thread; dst may be pinned host memory (mapped under unified addressing).  For the counts a stream reads
+// back per chunk: a tiny cudaMemcpyAsync would queue behind the large downloads on the copy engine and hold the compute
+// stream for milliseconds.
+cudaError_t launch_store_u64(unsigned long long *dst, const unsigned long long *src, cudaStream_t stream);
 // kind: 0 read `bytes` of src, 1 copy src -> dst, 2 write dst
 cudaError_t launch_yardstick(const void *src, void *dst, int64_t bytes, int kind, int sms, void *sink, cudaStream_t stream);
 cudaError_t launch_generate(void *values, uint32_t *validity, int type, int kind, uint64_t seed, double p0, double p1,

@@ -1310,7 +1310,10 @@ static int run_pipeline(qe_ctx *ctx, const qe_table *table, const qe_pipeline_de
         QE_CUDA(cudaMemcpyAsync(r->h_super + (size_t)super_off * (size_t)nagg * 4, r->final_aggs.ptr,
                                 (size_t)nsuper * (size_t)nagg * 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     }
-    QE_CUDA(cudaMemcpyAsync(&r->host->count, r->ctl.ptr, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    if (extra && extra->chained)     // inside a stream the copy engine is busy with the downloads: see launch_store_u64
+        QE_CUDA(qe::launch_store_u64(&r->host->count, (const unsigned long long *)r->ctl.ptr, ctx->stream));
+    else
+        QE_CUDA(cudaMemcpyAsync(&r->host->count, r->ctl.ptr, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
     QE_CUDA(cudaEventRecord(r->ev_done, ctx->stream));
     r->pending = true;
     r->timed = true;
@@ -2135,7 +2138,10 @@ extern "C" int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_
     if (bounded) {
         const int64_t fit = table->nrows / chunk;
         if (fit < 2) return fail(QE_ERR_INVALID_ARGUMENT, "bounded streaming: the table must hold at least two chunks (nrows >= 2 * chunk_rows)");
-        nslots = (int)std::min<int64_t>(fit, 3);
+        // Every slot is a chunk of the table plus one output buffer set per pipeline.  Three keep upload, kernels and
+        // download of neighbouring chunks busy; more let the uploads run ahead of the downloads when those are the slower
+        // direction (the window the caller allocates decides).
+        nslots = (int)std::min<int64_t>(fit, 32);
     }
     if (chunk > 0xffffffffLL) return fail(QE_ERR_INVALID_ARGUMENT, "chunk_rows must fit 32 bits");
     const int64_t nchunks = std::max<int64_t>(1, (n + chunk - 1) / chunk);
@@ -2264,8 +2270,11 @@ extern "C" int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_
             if ((rc = run_pipeline(ctx, table, &d, slot, &extra))) return rc;
             qe_result *r = *slot;
             if (fresh && slot != &sd->results[q]) sd->results[q]->ring.push_back(r);      // owned by the pipeline's result
-            QE_CUDA(cudaMemcpyAsync(&st.counts[(size_t)c * np + q], r->ctl.ptr, sizeof(unsigned long long),
-                                    cudaMemcpyDeviceToHost, ctx->stream));
+            if (bounded)
+                QE_CUDA(qe::launch_store_u64(&st.counts[(size_t)c * np + q], (const unsigned long long *)r->ctl.ptr, ctx->stream));
+            else
+                QE_CUDA(cudaMemcpyAsync(&st.counts[(size_t)c * np + q], r->ctl.ptr, sizeof(unsigned long long),
+                                        cudaMemcpyDeviceToHost, ctx->stream));
         }
         QE_CUDA(st.new_event(&ev_run[(size_t)c]));
         QE_CUDA(cudaEventRecord(ev_run[(size_t)c], ctx->stream));

@@ -20,6 +20,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--rows", type=int, default=1_000_000_000)
 ap.add_argument("--chunk", type=int, default=1 << 25)
 ap.add_argument("--steps", type=int, default=3)
+ap.add_argument("--window", type=int, default=3, help="chunk slots of the device window")
 ap.add_argument("--configs", default="staging=2")
 args = ap.parse_args()
 import torch  # noqa: E402
@@ -47,7 +48,7 @@ for cfg in args.configs.split(";"):
         ctx.set_option(k, 0)
     for k, v in opts.items():
         ctx.set_option(k, int(v))
-    t = ColumnarTable(ctx, [Field("col", I64, False)], 3 * args.chunk)
+    t = ColumnarTable(ctx, [Field("col", I64, False)], args.window * args.chunk)
     row = dict(opts)
     for which, name in ((0, "full"), (1, "sel_only")):
         pipes = [Pipeline(t, bench.filter_expr(s), [col(0, I64, "col")], out_capacity_rows=c, values=(which == 0))
@@ -75,3 +76,44 @@ for cfg in args.configs.split(";"):
             r.close()
     t.close()
     print(json.dumps(row), flush=True)
+
+# ---- the same bytes as plain copies INTO / OUT OF THE SAME host buffers (distinct memory, not a recycled 1 GiB buffer)
+import glob  # noqa: E402
+cands = glob.glob(os.path.join(os.path.dirname(torch.__file__), "lib", "libcudart*.so*")) + ["libcudart.so.12", "libcudart.so"]
+rt = None
+for cnd in cands:
+    try:
+        rt = C.CDLL(cnd)
+        break
+    except OSError:
+        pass
+if rt is not None:
+    rt.cudaMemcpyAsync.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
+    s_up, s_down = torch.cuda.Stream(), torch.cuda.Stream()
+    dbuf_up = torch.empty(1 << 30, dtype=torch.uint8, device="cuda")
+    dbuf_down = torch.ones(1 << 30, dtype=torch.uint8, device="cuda")
+    piece = 64 << 20
+    for mode in ("both", "d2h_only", "h2d_only"):
+        per = []
+        for _ in range(3):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            if mode != "d2h_only":
+                off = 0
+                while off < n * 8:
+                    m = min(piece, n * 8 - off)
+                    rt.cudaMemcpyAsync(C.c_void_p(dbuf_up.data_ptr() + off % (1 << 30)), C.c_void_p(h_in.ptr.value + off), m, 1, C.c_void_p(s_up.cuda_stream))
+                    off += m
+            if mode != "h2d_only":
+                for hb, width in [(b, 4) for b in h_sel] + [(b, 8) for b in h_val]:
+                    total = (hb.nbytes if hasattr(hb, "nbytes") else 0)
+                for hb, cap_, width in [(h_sel[i], caps[i], 4) for i in range(3)] + [(h_val[i], caps[i], 8) for i in range(3)]:
+                    total = int(bench.SELECTIVITIES[[h_sel, h_val][width == 8].index(hb)] * n) * width
+                    off = 0
+                    while off < total:
+                        m = min(piece, total - off)
+                        rt.cudaMemcpyAsync(C.c_void_p(hb.ptr.value + off), C.c_void_p(dbuf_down.data_ptr() + off % ((1 << 30) - piece)), m, 2, C.c_void_p(s_down.cuda_stream))
+                        off += m
+            torch.cuda.synchronize()
+            per.append(round((time.perf_counter() - t0) * 1e3, 1))
+        print(json.dumps({"plain_copies_same_host_buffers": mode, "ms": per}), flush=True)
