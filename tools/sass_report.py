@@ -18,7 +18,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 
-KERNELS = {"filter_i64": "qe_filter_ring_kernel", "q6": "qe_agg_kernel", "tree": "qe_project_kernel", "q6_filter": "qe_filter_ring_kernel"}
+KERNELS = {"filter_i64": "qe_filter_ring_kernel", "q6": "qe_agg_kernel", "tree": "qe_project_kernel", "q6_filter": "qe_filter_ring_kernel",
+           "filter_f64_nullable": "qe_filter_ring_kernel"}
 MARKERS = ["UBLKCP", "SYNCS", "VOTE", "POPC", "REDUX", "SHFL", "LDG", "STG", "LDS", "STS", "ATOMS", "ATOMG", "ATOM", "RED", "DSETP", "ISETP",
            "DFMA", "DMUL", "DADD", "MUFU", "BAR", "NANOSLEEP", "S2R", "S2UR", "CCTL", "UTMALDG", "UTMAPF", "BSSY", "BSYNC", "LDC", "LDCU"]
 
@@ -46,7 +47,7 @@ def main():
         summary[name] = {"entry": entry, "instructions": total, "by_mnemonic": by_marker, "wide_memory_ops": wide,
                          "registers": int(usage.group(1)) if usage else None, "static_shared_bytes": int(usage.group(2)) if usage else None,
                          "top": ops.most_common(12)}
-        keep = [ln for ln in lines if re.search(r"UBLKCP|SYNCS|VOTE|POPC|REDUX|LDG|STG|ATOMS|NANOSLEEP|UTMA", ln)]
+        keep = [ln for ln in lines if re.search(r"UBLKCP|SYNCS|VOTE|POPC|REDUX|LDG|STG|ATOMS|ATOMG|RED\.|STS\.U8|STS\.U16|LDS\.U8|LDS\.U16|NANOSLEEP|UTMA", ln)]
         with open(os.path.join(out_dir, f"r02_sass_{name}.txt"), "w") as f:
             f.write(f"# {entry} of the '{name}' pipeline (tools/dump_kernel.py {name}; cuobjdump -sass): {total} instructions, "
                     f"{summary[name]['registers']} registers\n# the lines that carry the design (bulk copies, mbarriers, ballot / popc, wide loads and stores)\n")
