@@ -143,6 +143,9 @@ struct qe_ctx {
     // (The compiled cubins themselves live in the process-wide store of qe_cubin_cache.cpp.)
     std::unordered_map<std::string, JitEntry> jit_cache;
     std::list<std::string> jit_lru;
+    // what a filter kept the last time it ran in this context, by query (signature + literal values): the shape hint of a
+    // run that has no earlier result of its own to look at (a new operator running a query the context has seen)
+    std::unordered_map<std::string, double> sel_memo;
     int64_t opt_jit_cache_entries = 128;
     int64_t jit_loads = 0;                       // cudaLibraryLoadData calls (cold or evicted kernels)
     // options
@@ -1086,6 +1089,10 @@ static int run_pipeline(qe_ctx *ctx, const qe_table *table, const qe_pipeline_de
         } else if (qe_result *prev = *result; prev && prev->f_sig == qkey) {
             sel_hint = prev->f_sel;                           // appended / chained chunks keep the shape of the first
         }
+        if (sel_hint < 0.0 && mode == qe::KM_FILTER && !(d->flags & QE_RUN_APPEND)) {
+            auto memo = ctx->sel_memo.find(qkey);
+            if (memo != ctx->sel_memo.end()) sel_hint = memo->second;
+        }
         shape = choose_shape(ctx, bp, mode, sel_hint);
         // Dense projection: four CTAs per SM (64 registers) hide the latency of the FP64 divide / MOD sequences better
         // than three; kept unless the tighter bound spills more than a few words.  (Nullable tree, 1e9 rows: 84
@@ -1784,6 +1791,11 @@ static int wait_result(qe_result *r)
         QE_CUDA(cudaEventSynchronize(r->ev_done));
         r->pending = false;
     }
+    if (r->mode == qe::KM_FILTER && !r->chained && !r->streamed && r->batch_rows > 0 && !r->f_sig.empty() &&
+        (int64_t)r->host->count <= r->capacity) {
+        if (r->ctx->sel_memo.size() > 4096) r->ctx->sel_memo.clear();
+        r->ctx->sel_memo[r->f_sig] = (double)r->host->count / (double)r->batch_rows;
+    }
     fold_aggs(r);
     return QE_OK;
 }
@@ -2302,6 +2314,7 @@ extern "C" int qe_pipeline_stream(qe_ctx *ctx, qe_table *table, const qe_stream_
             if (r->mode == qe::KM_FILTER && n > 0) {
                 r->f_sel = (double)r->host->count / (double)n;
                 for (qe_result *m : r->ring) m->f_sel = r->f_sel;
+                if (!r->f_sig.empty()) ctx->sel_memo[r->f_sig] = r->f_sel;
             }
         }
     }
