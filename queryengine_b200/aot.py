@@ -48,7 +48,7 @@ def main() -> None:
         filt = W.single_column_filter(0.5, dtype)
         # unknown / sparse: 20 consumer warps + row lists + sweeper warps; 11-40 % kept last time: 20 warps, masks only;
         # above 40 %: 16 warps
-        # (known to keep at most 6 %: 40 KB tiles and a third sweeper warp)
+        # (known to keep at most 8 %: 24 consumer warps, 42 KB tiles and a third sweeper warp)
         for hint in (-1.0, 0.01, 0.2, 0.99):
             for flags in (0, capi.QE_RUN_NO_VALUES):
                 compile_one(f"configs[1] {dtype.name} filter hint={hint} flags={flags}", schema, filt, [col(0, dtype, "col")],

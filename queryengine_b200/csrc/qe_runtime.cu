@@ -807,7 +807,16 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         // 3.02); 40-byte rows lose with more warps (6.9 ms with 16, 7.7 with 24): profiles/r01_sweep_06_*.jsonl
         // ... unless the same pipeline kept more than 40 % of its rows the last time it ran into this result: from there
         // on the kernel is bound by HBM and 16 warps are the faster shape (99 %: 2.98 against 3.00-3.04 ms)
-        s.ncw = ctx->opt_ncw ? (int)ctx->opt_ncw : ((row_bytes <= 8 && !(sel_hint > 0.4)) ? 20 : 16);
+        // A query that is known to keep little (at most 8 % the last time) runs on the row lists and the sweepers below: its
+        // consumer warps pay a fixed price per tile (barriers, counts, the look-back behind them) that is as large as the
+        // work of a 7-step slice, so larger tiles, more consumer warps and a third sweeper warp win there.  24 consumer
+        // warps, 5 376-row / 42 KB tiles (five stages), three sweepers: 0.5 / 1 / 3 / 5 / 8 % 1.14-1.16 / 1.178 / 1.25 / 1.30 /
+        // 1.40 ms per 10^9 rows, against 1.238 / 1.253 / 1.33 / 1.38 / 1.44 ms with the default shape (20 warps, 4 480-row
+        // tiles, two sweepers) and 1.175 / 1.20 / 1.30 / 1.35 with 20 warps and 5 120-row tiles; at 10 % the default is as fast
+        // (1.49-1.50) and from there on the smaller tiles win (50 %: 2.14 against 2.53 ms) --
+        // profiles/r02_sweep_07_tile_rows.jsonl
+        const bool known_sparse = row_bytes <= 8 && sel_hint >= 0.0 && sel_hint <= 0.08 && ctx->opt_list_cap >= 0 && ctx->opt_nsw >= 0;
+        s.ncw = ctx->opt_ncw ? (int)ctx->opt_ncw : known_sparse ? 24 : ((row_bytes <= 8 && !(sel_hint > 0.4)) ? 20 : 16);
         const size_t quantum = (size_t)std::max(128, 32 * s.ncw);       // rows: whole warp steps, 16-byte bitmap runs
         const size_t stage_target = (size_t)(ctx->opt_stage_kb ? ctx->opt_stage_kb : 32) << 10;
         // One look-back per tile costs ~1500 cycles whatever the tile holds, so a tile must carry >= ~32 KB for
@@ -815,13 +824,7 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         // 1024 rows = 40 KB measured 96.7 % of the copy peak, 512 rows = 20 KB 64.5 %), down otherwise.
         size_t rows = stage_target / row_bytes / quantum * quantum;
         if (rows * row_bytes < stage_target && (rows + quantum) * row_bytes <= (44u << 10)) rows += quantum;
-        // A query that is known to keep little (at most 6 % the last time) runs on the row lists and the sweepers below: its
-        // consumer warps pay a fixed price per tile (barriers, counts, the look-back behind them) that is as large as the
-        // work of a 7-step slice, so 40 KB tiles (five stages) and a third sweeper warp win there -- 0.5 / 1 / 2 / 5 %:
-        // 1.146 / 1.198 / 1.258 / 1.349 ms against 1.238 / 1.253 / 1.302 / 1.381 ms per 10^9 rows; from 8 % up the smaller
-        // tiles win (10 %: 1.48 against 1.60; 50 %: 2.14 against 2.53) -- profiles/r02_sweep_07_tile_rows.jsonl
-        const bool known_sparse = row_bytes <= 8 && sel_hint >= 0.0 && sel_hint <= 0.06 && ctx->opt_list_cap >= 0 && ctx->opt_nsw >= 0;
-        if (known_sparse && !ctx->opt_stage_kb) rows = std::max(rows, (size_t)(40u << 10) / row_bytes / quantum * quantum);
+        if (known_sparse && !ctx->opt_stage_kb) rows = std::max(rows, (size_t)(42u << 10) / row_bytes / quantum * quantum);
         if (ctx->opt_tile_rows) rows = (size_t)ctx->opt_tile_rows;
         rows = std::min<size_t>(std::max(rows, quantum), (size_t)kPadRows / quantum * quantum);
         if (rows % quantum) rows = (rows + quantum - 1) / quantum * quantum;
@@ -851,6 +854,8 @@ static qe::TileShape choose_shape(const qe_ctx *ctx, const qe::BoundPipeline &bp
         if (s.defer >= s.nstages) s.defer = s.nstages - 1;
         s.loads = (int)ctx->opt_loads;
         s.nlb = std::min(ctx->opt_nlb ? (int)ctx->opt_nlb : 1, s.nstages);   // the end markers need a stage each
+        while (2 + s.nlb + s.nsw + s.ncw > 32 && s.nsw > 1) s.nsw--;         // a CTA has at most 32 warps
+        while (2 + s.nlb + s.nsw + s.ncw > 32 && s.nlb > 1) s.nlb--;
         if (n * (stage + meta) > (224u << 10) || s.defer < 1) s.ring = false;   // a single tile does not fit: register-sourced kernel
     }
     // Dense projection through the same ring of stages (one producer warp + 16 consumer warps): on request only
