@@ -524,6 +524,54 @@ def hostlink_yardstick(torch, dist, device, up_bytes, down_bytes, chunk=64 << 20
     return ms
 
 
+def hostlink_same_buffers(torch, dist, device, h_in, in_bytes, outs, piece=64 << 20):
+    """The end-to-end step's bytes as plain cudaMemcpyAsync calls out of / into the SAME pinned host buffers the step uses
+    (distinct host memory, not a recycled buffer), H2D and D2H at once on two streams, no kernels: what the link does for
+    exactly this traffic.  outs = [(pinned buffer, bytes)]; max over ranks, milliseconds, or None without libcudart."""
+    import glob
+    rt = None
+    for cand in glob.glob(os.path.join(os.path.dirname(torch.__file__), "lib", "libcudart*.so*")) + ["libcudart.so.12", "libcudart.so"]:
+        try:
+            rt = C.CDLL(cand)
+            break
+        except OSError:
+            continue
+    if rt is None:
+        return None
+    rt.cudaMemcpyAsync.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
+    rt.cudaMemcpyAsync.restype = C.c_int
+    win = 1 << 30
+    d_up = torch.empty(win, dtype=torch.uint8, device=device)
+    d_down = torch.ones(win, dtype=torch.uint8, device=device)
+    s_up, s_down = torch.cuda.Stream(device), torch.cuda.Stream(device)
+
+    def run():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ups = [(off, min(piece, in_bytes - off)) for off in range(0, in_bytes, piece)]
+        downs = [(b, off, min(piece, nb - off)) for b, nb in outs for off in range(0, nb, piece)]
+        for i in range(max(len(ups), len(downs))):                 # interleaved, as the step issues them
+            if i < len(ups):
+                off, m = ups[i]
+                assert rt.cudaMemcpyAsync(d_up.data_ptr() + off % (win - piece), h_in.ptr.value + off, m, 1, s_up.cuda_stream) == 0
+            if i < len(downs):
+                b, off, m = downs[i]
+                assert rt.cudaMemcpyAsync(b.ptr.value + off, d_down.data_ptr() + off % (win - piece), m, 2, s_down.cuda_stream) == 0
+        torch.cuda.synchronize()
+        ms = (time.perf_counter() - t0) * 1e3
+        if dist is not None:
+            t = torch.tensor([ms], dtype=torch.float64, device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+    run()
+    ms = min(run(), run())
+    del d_up, d_down
+    return ms
+
+
 def cold_start_leg(ctx, table, rows):
     """First-query latency of this process (the caches as they are on this box) and of a pipeline that is in no
     cache (NVRTC), plus a fresh process that finds the latter in the disk cache."""
@@ -1086,6 +1134,8 @@ def run_e2e(args, torch, ctx, dist, device, rows, world, rank, kept_full):
             rs[i] = r
             kept[i] = r.num_rows                                     # d2h read of the step's result sizes
 
+    per_step = {0: [], 1: []}
+
     def timed(which, steps):
         one_step(which)                                              # warm-up
         if dist is not None:
@@ -1093,7 +1143,9 @@ def run_e2e(args, torch, ctx, dist, device, rows, world, rank, kept_full):
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         for _ in range(steps):
-            one_step(which)
+            t1 = time.perf_counter()
+            one_step(which)                                          # returns after the step's results are in host memory
+            per_step[which].append(round((time.perf_counter() - t1) * 1e3, 1))
         torch.cuda.synchronize()
         secs = time.perf_counter() - t0
         if dist is not None:
@@ -1123,10 +1175,16 @@ def run_e2e(args, torch, ctx, dist, device, rows, world, rank, kept_full):
     t.close()
     ctx.trim()
     # the ceiling: the same bytes over the same link with no kernels, all ranks at once
-    link_ms = link_sel_ms = None
+    link_ms = link_sel_ms = same_ms = same_sel_ms = None
     try:
         link_ms = hostlink_yardstick(torch, dist, device, h2d, d2h)
         link_sel_ms = hostlink_yardstick(torch, dist, device, h2d, d2h_sel)
+    except Exception:
+        pass
+    try:      # ... and into the very buffers the step used (the overwritten outputs were checked above)
+        outs_sel = [(h_sel[i], kept_full_run[i] * 4) for i in range(len(pipes))]
+        same_ms = hostlink_same_buffers(torch, dist, device, h_in, h2d, outs_sel + [(h_val[i], kept_full_run[i] * 8) for i in range(len(pipes))])
+        same_sel_ms = hostlink_same_buffers(torch, dist, device, h_in, h2d, outs_sel)
     except Exception:
         pass
     for b in bufs:
@@ -1136,10 +1194,14 @@ def run_e2e(args, torch, ctx, dist, device, rows, world, rank, kept_full):
            "ms_per_step": ms_step, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "chunk_rows": chunk, "device_window_rows": 3 * chunk,
            "hostlink_ms_same_bytes_no_kernels": link_ms, "frac_of_hostlink": (link_ms / ms_step) if link_ms else None,
+           "plain_copies_same_buffers_ms": same_ms, "frac_of_plain_copies_same_buffers": (same_ms / ms_step) if same_ms else None,
+           "step_ms": per_step[0],
            "selection_only": {"value": world * len(pipes) * e2e_rows * steps / secs_sel, "unit": UNIT, "ms_per_step": ms_step_sel,
                               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h_sel,
                               "hostlink_ms_same_bytes_no_kernels": link_sel_ms,
                               "frac_of_hostlink": (link_sel_ms / ms_step_sel) if link_sel_ms else None,
+                              "plain_copies_same_buffers_ms": same_sel_ms,
+                              "frac_of_plain_copies_same_buffers": (same_sel_ms / ms_step_sel) if same_sel_ms else None,
                               "what": "QE_RUN_NO_VALUES: the selection vectors are the whole output (the host holds the table)"},
            "what": "per step one qe_pipeline_stream call (bounded mode): the column is copied from pinned host memory once, in chunks, into "
                    "a window of three chunk slots; the three filters run chunk by chunk; selection vectors + compacted columns land in "
