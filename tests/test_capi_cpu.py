@@ -177,6 +177,43 @@ def test_validity_the_filter_decides_is_written_as_runs():
     assert rc == 0 and "NBITCOLS = 1" in f and "NIMPLIED" not in f, err
 
 
+@pytest.mark.parametrize("seed", range(40))
+def test_implied_validity_is_sound_against_the_oracle(seed):
+    """Soundness of the static analysis behind the runs of ones (implied_valid_outputs, qe_codegen.cpp): for random
+    well-typed filter / projection trees over nullable columns, every output the generated code treats as "never null in
+    a kept row" must be non-null in every row the ORACLE's FilterOperator keeps (no GPU needed: the generated source
+    names the outputs, the oracle evaluates the rows)."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from exprgen import ExprGen
+    from oracle_binding import OraclePlan
+    from parity import random_table
+    from queryengine_b200.ast import Mode
+    rng = np.random.default_rng(9000 + seed)
+    spec = random_table(rng, 600, ["DDDB", "DDBB", "DdDB", "DDDD"][seed % 4], special_rate=0.2)
+    g = ExprGen(rng, spec.fields)
+    # filters that are conjunctions of comparisons more often than not: those are the ones that promise something
+    parts = [g.boolean(2) for _ in range(int(rng.integers(1, 4)))]
+    filt = parts[0]
+    for q in parts[1:]:
+        filt = fn(Function.AND, filt, q) if rng.random() < 0.8 else fn(Function.OR, filt, q)
+    projs = [g.double(int(rng.integers(0, 4))) for _ in range(3)] + [g.boolean(2)]
+    schema = [(f.type, f.nullable) for f in spec.fields]
+    rc, src, _, err = _generate(schema, filt, projs, compile_=False)
+    assert rc == 0, err
+    body = src.split("implied_col(")[1].split("}")[0]
+    implied = [int(k) for k in re.findall(r"return p\.out_valid\[(\d+)\];", body)]
+    n_ref, vals, valid = OraclePlan(spec.oracle(), list(range(len(spec.fields))), filter=filt, projections=projs,
+                                    mode=Mode.BYTECODE_COMPILER).columns()
+    for k in implied:
+        assert valid[k][:n_ref].all(), (k, seed)
+    # and the analysis is not vacuous over the forty seeds: a plain conjunction over the columns an output reads qualifies
+    if seed == 0:
+        rc, src2, _, err = _generate(schema, fn(Function.AND, fn(Function.CMP_LT, col(0), 1.0), fn(Function.CMP_GT, col(1), -1.0)),
+                                     [fn(Function.ADD, col(0), col(1))], compile_=False)
+        assert rc == 0 and "NIMPLIED = 1" in src2, err
+
+
 def test_closure_compiler_mode_is_a_comparison_argument():
     """Mode.CLOSURE_COMPILER (IEEE ordering, M/evaluator/ClosureCompiler.kt:127-130) travels as QE_CMP_IEEE in the
     argument of CMP_LT / LE / GE / GT: another kernel than the total-order one, the same kernel for an integer column
