@@ -37,6 +37,23 @@ def test_library_exports_every_declared_symbol():
     assert capi.lib().qe_version().decode().count(".") == 2
 
 
+def test_ffm_binding_source_names_real_entry_points_with_the_right_arity():
+    """bindings/ffm/QeGpuFfm.java (Panama FFM, JDK 22+; source only, no JDK here): every downcall handle names a function
+    the library exports, with as many arguments as include/qegpu.h declares."""
+    src = open(os.path.join(ROOT, "bindings", "ffm", "QeGpuFfm.java")).read()
+    header = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "qegpu.h")).read(), flags=re.S)
+    handles = re.findall(r'h\("(qe_\w+)",\s*FunctionDescriptor\.of\(([^;]*?)\)\);', src, flags=re.S)
+    assert len(handles) >= 14
+    L = C.CDLL(capi.LIB_PATH)
+    for name, layouts in handles:
+        assert hasattr(L, name), name
+        decl = re.search(r"QE_API\s+[\w\s\*]+?\b" + name + r"\s*\(([^;]*?)\)\s*;", header, flags=re.S)
+        assert decl, name
+        params = [x for x in decl.group(1).split(",") if x.strip() and x.strip() != "void"]
+        nargs = len([x for x in layouts.split(",") if x.strip()]) - 1          # the first layout is the return value
+        assert nargs == len(params), (name, nargs, params)
+
+
 def test_serializer_postfix_words():
     e = fn(Function.CMP_LT, col(3), 5.0)
     w = serialize(e)
