@@ -389,6 +389,50 @@ def test_sparse_tiles_row_lists_and_sweeper_warps(ctx, list_cap, nsw):
     c.close()
 
 
+def test_single_narrow_columns_under_every_remembered_selectivity(ctx):
+    """One 4-byte column (DATE32), one bit column (BOOLEAN, nullable) and one 8-byte column, each filtered three times into
+    one reused result at selectivities on both sides of every shape threshold (known-sparse up to 8 %, lists up to 13.5 %,
+    20 / 16 consumer warps at 40 %): the tile sizes these shapes derive for narrow rows (7 680-row tiles of a 4-byte column,
+    u16 list entries) are run at least once each."""
+    rng = np.random.default_rng(99)
+    n = 3_000_017
+    d = rng.integers(0, 100_000, n).astype(np.int32)
+    b = rng.random(n) < 0.03
+    bv = rng.random(n) < 0.9
+    x = rng.uniform(0.0, 1.0, n)
+    t = ColumnarTable.from_arrays(ctx, [Field("d", T, False), Field("b", B, True), Field("x", D, False)], [d, b, x], [None, bv, None])
+    for frac in (0.002, 0.05, 0.1, 0.3, 0.9):
+        k = float(int(frac * 100_000))
+        want = np.nonzero(d < k)[0].astype(np.uint32)
+        res = None
+        for rep in range(3):
+            res = Pipeline(t, fn(Function.CMP_LT, col(0, T), k), [col(0, T)]).run(res)
+            assert res.num_rows == want.size and np.array_equal(res.selection(), want) and np.array_equal(res.column(0)[0], d[want]), (frac, rep)
+        res.close()
+        want = np.nonzero(x < frac)[0].astype(np.uint32)
+        res = None
+        for rep in range(3):
+            res = Pipeline(t, fn(Function.CMP_LT, col(2), float(frac)), [col(2)]).run(res)
+            assert res.num_rows == want.size and np.array_equal(res.selection(), want) and np.array_equal(res.column(0)[0], x[want]), (frac, rep)
+        res.close()
+    want = np.nonzero(b & bv)[0].astype(np.uint32)                  # the column is its own predicate: null drops the row
+    res = None
+    for rep in range(3):
+        res = Pipeline(t, col(1, B), [col(1, B)]).run(res)
+        vals, valid = res.column(0)
+        assert res.num_rows == want.size and np.array_equal(res.selection(), want) and vals.all() and valid.all(), rep
+    res.close()
+    res = None
+    for rep in range(3):                                            # ... and its complement (most rows kept)
+        res = Pipeline(t, fn(Function.NOT, col(1, B)), [col(1, B), col(0, T)]).run(res)
+        want = np.nonzero(~b & bv)[0].astype(np.uint32)
+        vals, valid = res.column(0)
+        assert res.num_rows == want.size and np.array_equal(res.selection(), want) and not vals.any() and valid.all(), rep
+        assert np.array_equal(res.column(1)[0], d[want])
+    res.close()
+    t.close()
+
+
 def test_sparse_path_stress_random_shapes_and_selectivities(ctx):
     """compute-sanitizer is closed on this pool, so the hand-offs of the ring kernel (producer / publisher / look-back /
     sweepers / consumers over five mbarrier arrays) are exercised the blunt way: many tiles per CTA, random shapes and
