@@ -18,7 +18,7 @@ from typing import List, Optional, Sequence
 import numpy as np
 
 from . import capi
-from .ast import AggregationFunction, DataType, Expression
+from .ast import AggregationFunction, DataType, Expression, Mode
 from .engine import (_NP_OF, ColumnarTable, Context, Field, GroupByPipeline, Pipeline, PipelineResult, StringDictionary,
                      pack_bits, stream_pipelines, unpack_bits)
 
@@ -183,12 +183,12 @@ class ShardedPipeline:
 
     def __init__(self, table: ShardedTable, filter: Optional[Expression] = None, projections: Optional[Sequence[Expression]] = None,
                  aggregates: Optional[Sequence[AggregationFunction]] = None, out_capacity_rows: int = 0, values: bool = True,
-                 interpreter: bool = False):
+                 interpreter: bool = False, mode: Mode = Mode.GPU):
         self.table = table
         self.group = table.group
         # programs are host objects: created with the first context, run on all of them
         self.pipe = Pipeline(table.parts[0], filter, projections, aggregates, interpreter=interpreter, out_capacity_rows=out_capacity_rows,
-                             values=values)
+                             values=values, mode=mode)
 
     def run(self, result: Optional[ShardedResult] = None) -> ShardedResult:
         r = result or ShardedResult(self.group)
@@ -235,10 +235,10 @@ class ShardedGroupBy:
     """Scan -> [Filter] -> Projection -> GroupByAggregation over a ShardedTable (qe_mgpu_groupby_run)."""
 
     def __init__(self, table: ShardedTable, filter: Optional[Expression], keys: Sequence[Expression], inputs: Sequence[Expression],
-                 aggregates: Sequence[AggregationFunction], max_groups: int = 0):
+                 aggregates: Sequence[AggregationFunction], max_groups: int = 0, mode: Mode = Mode.GPU):
         self.table = table
         self.group = table.group
-        self.pipe = GroupByPipeline(table.parts[0], filter, keys, inputs, aggregates, max_groups=max_groups)
+        self.pipe = GroupByPipeline(table.parts[0], filter, keys, inputs, aggregates, max_groups=max_groups, mode=mode)
         self.nkeys = len(keys)
         self.fns = [AggregationFunction(a) for a in aggregates]
 
